@@ -1,0 +1,100 @@
+/*
+ * oracle_abi.h -- TEST INFRASTRUCTURE ONLY (never linked into the product library).
+ *
+ * One C ABI implemented twice:
+ *   - oracle/oracle.c        (prefix orc_)  plain-C restatement of the reference algorithms
+ *   - oracle/ref_wrap.cpp    (prefix ref_)  thin wrapper that compiles the reference's OWN
+ *                                           headers from /root/reference (built into oracle/_ref/)
+ * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
+ * load either library.
+ *
+ * Conventions (all follow the reference, cited in oracle.c):
+ *   symbols   : one uint8 per symbol, 0..3 = A,C,G,T, >3 = N
+ *   string set: concatenated symbols + offsets[count+1]  (ConcatenatedStringSet)
+ *   aligner   : kind 0=EDIT_DISTANCE 1=SMITH_WATERMAN 2=GOTOH ; type 0=GLOBAL 1=LOCAL 2=SEMI_GLOBAL
+ *               SW   : p0=match p1=mismatch p2=deletion p3=insertion
+ *               GOTOH: p0=match p1=mismatch p2=gap_open p3=gap_ext
+ *               ED   : params ignored (0,-1,-1,-1)
+ *   sink      : {score, text_end(x), pattern_end(y)}  == aln::BestSink<int32>
+ *   alignment : {score, source.x, source.y, sink.x, sink.y} == aln::Alignment<int32>
+ *   ops       : uint8 per op in PUSH ORDER (end -> start): 0=M(substitution) 1=I 2=D
+ */
+#ifndef NVB_ORACLE_ABI_H
+#define NVB_ORACLE_ABI_H
+
+#include <stdint.h>
+#include <stddef.h>
+
+#ifndef ORC_PREFIX
+#define ORC_PREFIX orc_
+#endif
+#define ORC_CAT2(a, b) a##b
+#define ORC_CAT(a, b) ORC_CAT2(a, b)
+#define ORC(name) ORC_CAT(ORC_PREFIX, name)
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct {
+    uint32_t        length;     /* number of text symbols                       */
+    uint32_t        primary;    /* row of the full text in the BWT matrix       */
+    uint32_t        L2[5];      /* cumulative symbol counts                     */
+    const uint32_t* bwt_occ;    /* fused nvBWT array: per 64 symbols 4 bwt words + 4 occ counters */
+    const uint32_t* ssa;        /* (length+16)/16 entries, ssa[0] = 0xFFFFFFFF  */
+} orc_fmindex;
+
+typedef struct { int32_t kind, type, p0, p1, p2, p3; } orc_aligner;
+typedef struct { int32_t score; uint32_t x, y; } orc_sink;
+typedef struct { int32_t score; uint32_t src_x, src_y, sink_x, sink_y; } orc_alignment;
+
+/* number of uint32 words of the fused bwt_occ array for a text of n symbols */
+size_t ORC(bwt_occ_words)(uint32_t n);
+/* number of uint32 entries of the sampled suffix array */
+size_t ORC(ssa_words)(uint32_t n);
+
+/* build SA -> BWT -> occ -> fused layout -> SSA(16). sa_out (n+1 int32) may be NULL. */
+int ORC(build_index)(const uint8_t* text, uint32_t n, uint32_t* primary, uint32_t* L2,
+                     uint32_t* bwt_occ, uint32_t* ssa, int32_t* sa_out);
+
+/* exact backward search; ranges = 2 uint32 per query (inclusive SA interval, raw).
+ * blocks (optional, may be NULL) receives per query the number of distinct fused 32-byte
+ * blocks the reference algorithm touches (the roofline's algorithmic bytes / 32). */
+int ORC(fm_match)(const orc_fmindex* fmi, const uint8_t* symbols, const uint32_t* offsets,
+                  uint32_t count, uint32_t* ranges, uint32_t* blocks, int threads);
+
+/* rank of symbol c[i] over the range pairs (x,y); out = 2 uint32 per query */
+int ORC(fm_rank)(const orc_fmindex* fmi, const uint32_t* ranges, const uint8_t* c,
+                 uint32_t count, uint32_t* out, int threads);
+
+/* all four symbol counts in [0,k]; out = 4 uint32 per query */
+int ORC(fm_rank4)(const orc_fmindex* fmi, const uint32_t* k, uint32_t count, uint32_t* out, int threads);
+
+/* SA row -> text coordinate; steps (optional) = LF steps walked */
+int ORC(fm_locate)(const orc_fmindex* fmi, const uint32_t* rows, uint32_t count, uint32_t* pos,
+                   uint32_t* steps, int threads);
+
+/* full-matrix scoring, one sink per pair */
+int ORC(score)(orc_aligner a, const uint8_t* pat, const uint32_t* pat_off, const uint8_t* txt,
+               const uint32_t* txt_off, uint32_t count, orc_sink* sinks, int threads);
+
+/* banded scoring */
+int ORC(banded_score)(orc_aligner a, uint32_t band, const uint8_t* pat, const uint32_t* pat_off,
+                      const uint8_t* txt, const uint32_t* txt_off, uint32_t count, orc_sink* sinks,
+                      int threads);
+
+/* full-matrix checkpointed traceback. ops: ops_stride bytes per pair, n_ops[i] valid entries. */
+int ORC(traceback)(orc_aligner a, uint32_t checkpoints, const uint8_t* pat, const uint32_t* pat_off,
+                   const uint8_t* txt, const uint32_t* txt_off, uint32_t count, orc_alignment* out,
+                   uint8_t* ops, uint32_t ops_stride, uint32_t* n_ops, int threads);
+
+/* banded checkpointed traceback */
+int ORC(banded_traceback)(orc_aligner a, uint32_t band, uint32_t checkpoints, const uint8_t* pat,
+                          const uint32_t* pat_off, const uint8_t* txt, const uint32_t* txt_off,
+                          uint32_t count, orc_alignment* out, uint8_t* ops, uint32_t ops_stride,
+                          uint32_t* n_ops, int threads);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,212 @@
+"""ctypes binding of oracle_abi.h -- TEST INFRASTRUCTURE ONLY.
+
+Loads either oracle/liboracle.so (prefix ``orc_``: the plain-C restatement) or
+oracle/_ref/libnvbio_ref.so (prefix ``ref_``: the reference's own headers, compiled by oracle/Makefile).
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may import this.
+"""
+import ctypes as C
+import os
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+ED, SW, GOTOH = 0, 1, 2
+GLOBAL, LOCAL, SEMI_GLOBAL = 0, 1, 2
+
+SINK_DT = np.dtype([("score", "<i4"), ("x", "<u4"), ("y", "<u4")])
+ALN_DT = np.dtype([("score", "<i4"), ("src_x", "<u4"), ("src_y", "<u4"), ("sink_x", "<u4"), ("sink_y", "<u4")])
+
+
+class FMIndexC(C.Structure):
+    _fields_ = [("length", C.c_uint32), ("primary", C.c_uint32), ("L2", C.c_uint32 * 5),
+                ("bwt_occ", C.c_void_p), ("ssa", C.c_void_p)]
+
+
+class AlignerC(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("type", C.c_int32), ("p0", C.c_int32), ("p1", C.c_int32),
+                ("p2", C.c_int32), ("p3", C.c_int32)]
+
+
+def aligner(kind, type_, p=(0, -1, -1, -1)):
+    return AlignerC(kind, type_, *[int(v) for v in p])
+
+
+def _ptr(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+def concat(strings):
+    """list of uint8 arrays -> (symbols, offsets) ConcatenatedStringSet."""
+    offs = np.zeros(len(strings) + 1, dtype=np.uint32)
+    if len(strings):
+        offs[1:] = np.cumsum([len(s) for s in strings])
+    sym = np.concatenate([np.asarray(s, dtype=np.uint8) for s in strings]) if len(strings) and offs[-1] else np.zeros(0, np.uint8)
+    return np.ascontiguousarray(sym, dtype=np.uint8), offs
+
+
+def dna(s):
+    """ASCII ACGT -> 0..3 (others -> 4)"""
+    lut = np.full(256, 4, np.uint8)
+    for i, ch in enumerate("ACGT"):
+        lut[ord(ch)] = i
+        lut[ord(ch.lower())] = i
+    return lut[np.frombuffer(s.encode(), dtype=np.uint8)]
+
+
+def rle(ops):
+    """run-length encode an op array in the given order, e.g. [0,0,2] -> '2M1D'"""
+    out, prev, cnt = [], None, 0
+    for o in ops:
+        if o == prev:
+            cnt += 1
+        else:
+            if prev is not None:
+                out.append("%d%s" % (cnt, "MID"[prev]))
+            prev, cnt = int(o), 1
+    if prev is not None:
+        out.append("%d%s" % (cnt, "MID"[prev]))
+    return "".join(out)
+
+
+class Index:
+    """host-side nvBWT index image (numpy arrays)"""
+
+    def __init__(self, length, primary, L2, bwt_occ, ssa, sa=None):
+        self.length, self.primary = int(length), int(primary)
+        self.L2 = np.asarray(L2, dtype=np.uint32)
+        self.bwt_occ, self.ssa, self.sa = bwt_occ, ssa, sa
+
+    def c(self):
+        f = FMIndexC()
+        f.length, f.primary = self.length, self.primary
+        for i in range(5):
+            f.L2[i] = int(self.L2[i])
+        f.bwt_occ = self.bwt_occ.ctypes.data
+        f.ssa = self.ssa.ctypes.data if self.ssa is not None else None
+        return f
+
+
+class Oracle:
+    def __init__(self, which="oracle"):
+        if which == "oracle":
+            path, self.prefix = os.path.join(HERE, "liboracle.so"), "orc_"
+        elif which == "ref":
+            path, self.prefix = os.path.join(HERE, "_ref", "libnvbio_ref.so"), "ref_"
+        else:
+            raise ValueError(which)
+        if not os.path.exists(path):
+            raise FileNotFoundError(path)
+        self.which = which
+        self.lib = C.CDLL(path)
+        f = self._f
+        f("bwt_occ_words").restype = C.c_size_t
+        f("bwt_occ_words").argtypes = [C.c_uint32]
+        f("ssa_words").restype = C.c_size_t
+        f("ssa_words").argtypes = [C.c_uint32]
+
+    @staticmethod
+    def available(which):
+        p = os.path.join(HERE, "liboracle.so") if which == "oracle" else os.path.join(HERE, "_ref", "libnvbio_ref.so")
+        return os.path.exists(p)
+
+    def _f(self, name):
+        return getattr(self.lib, self.prefix + name)
+
+    # ---------------- FM-index ----------------
+    def build_index(self, text, want_sa=False):
+        text = np.ascontiguousarray(text, dtype=np.uint8)
+        n = len(text)
+        bwt_occ = np.zeros(self._f("bwt_occ_words")(n), dtype=np.uint32)
+        ssa = np.zeros(self._f("ssa_words")(n), dtype=np.uint32)
+        sa = np.zeros(n + 1, dtype=np.int32) if want_sa else None
+        primary = C.c_uint32(0)
+        L2 = np.zeros(5, dtype=np.uint32)
+        rc = self._f("build_index")(_ptr(text), C.c_uint32(n), C.byref(primary), _ptr(L2), _ptr(bwt_occ), _ptr(ssa), _ptr(sa))
+        assert rc == 0, rc
+        return Index(n, primary.value, L2, bwt_occ, ssa, sa)
+
+    def fm_match(self, idx, symbols, offsets, want_blocks=False, threads=0):
+        n = len(offsets) - 1
+        symbols = np.ascontiguousarray(symbols, dtype=np.uint8)
+        offsets = np.ascontiguousarray(offsets, dtype=np.uint32)
+        ranges = np.zeros((n, 2), dtype=np.uint32)
+        blocks = np.zeros(n, dtype=np.uint32) if want_blocks else None
+        f = idx.c()
+        rc = self._f("fm_match")(C.byref(f), _ptr(symbols), _ptr(offsets), C.c_uint32(n), _ptr(ranges), _ptr(blocks), C.c_int(threads))
+        assert rc == 0, rc
+        return (ranges, blocks) if want_blocks else ranges
+
+    def fm_rank(self, idx, ranges, c, threads=0):
+        ranges = np.ascontiguousarray(ranges, dtype=np.uint32)
+        c = np.ascontiguousarray(c, dtype=np.uint8)
+        out = np.zeros((len(c), 2), dtype=np.uint32)
+        f = idx.c()
+        rc = self._f("fm_rank")(C.byref(f), _ptr(ranges), _ptr(c), C.c_uint32(len(c)), _ptr(out), C.c_int(threads))
+        assert rc == 0, rc
+        return out
+
+    def fm_rank4(self, idx, k, threads=0):
+        k = np.ascontiguousarray(k, dtype=np.uint32)
+        out = np.zeros((len(k), 4), dtype=np.uint32)
+        f = idx.c()
+        rc = self._f("fm_rank4")(C.byref(f), _ptr(k), C.c_uint32(len(k)), _ptr(out), C.c_int(threads))
+        assert rc == 0, rc
+        return out
+
+    def fm_locate(self, idx, rows, want_steps=False, threads=0):
+        rows = np.ascontiguousarray(rows, dtype=np.uint32)
+        pos = np.zeros(len(rows), dtype=np.uint32)
+        steps = np.zeros(len(rows), dtype=np.uint32) if want_steps else None
+        f = idx.c()
+        rc = self._f("fm_locate")(C.byref(f), _ptr(rows), C.c_uint32(len(rows)), _ptr(pos), _ptr(steps), C.c_int(threads))
+        assert rc == 0, rc
+        return (pos, steps) if want_steps else pos
+
+    # ---------------- alignment ----------------
+    @staticmethod
+    def _sets(pat, pat_off, txt, txt_off):
+        return (np.ascontiguousarray(pat, dtype=np.uint8), np.ascontiguousarray(pat_off, dtype=np.uint32),
+                np.ascontiguousarray(txt, dtype=np.uint8), np.ascontiguousarray(txt_off, dtype=np.uint32))
+
+    def score(self, a, pat, pat_off, txt, txt_off, threads=0):
+        pat, pat_off, txt, txt_off = self._sets(pat, pat_off, txt, txt_off)
+        n = len(pat_off) - 1
+        sinks = np.zeros(n, dtype=SINK_DT)
+        rc = self._f("score")(a, _ptr(pat), _ptr(pat_off), _ptr(txt), _ptr(txt_off), C.c_uint32(n), _ptr(sinks), C.c_int(threads))
+        assert rc == 0, rc
+        return sinks
+
+    def banded_score(self, a, band, pat, pat_off, txt, txt_off, threads=0):
+        pat, pat_off, txt, txt_off = self._sets(pat, pat_off, txt, txt_off)
+        n = len(pat_off) - 1
+        sinks = np.zeros(n, dtype=SINK_DT)
+        rc = self._f("banded_score")(a, C.c_uint32(band), _ptr(pat), _ptr(pat_off), _ptr(txt), _ptr(txt_off), C.c_uint32(n), _ptr(sinks), C.c_int(threads))
+        assert rc == 0, rc
+        return sinks
+
+    def traceback(self, a, chk, pat, pat_off, txt, txt_off, threads=0):
+        pat, pat_off, txt, txt_off = self._sets(pat, pat_off, txt, txt_off)
+        n = len(pat_off) - 1
+        M = int(np.max(np.diff(pat_off.astype(np.int64)))) if n else 0
+        N = int(np.max(np.diff(txt_off.astype(np.int64)))) if n else 0
+        stride = M + N + 8
+        out = np.zeros(n, dtype=ALN_DT)
+        ops = np.zeros((n, stride), dtype=np.uint8)
+        n_ops = np.zeros(n, dtype=np.uint32)
+        rc = self._f("traceback")(a, C.c_uint32(chk), _ptr(pat), _ptr(pat_off), _ptr(txt), _ptr(txt_off), C.c_uint32(n),
+                                  _ptr(out), _ptr(ops), C.c_uint32(stride), _ptr(n_ops), C.c_int(threads))
+        assert rc == 0, rc
+        return out, ops, n_ops
+
+    def banded_traceback(self, a, band, chk, pat, pat_off, txt, txt_off, threads=0):
+        pat, pat_off, txt, txt_off = self._sets(pat, pat_off, txt, txt_off)
+        n = len(pat_off) - 1
+        M = int(np.max(np.diff(pat_off.astype(np.int64)))) if n else 0
+        stride = 2 * M + band + 8
+        out = np.zeros(n, dtype=ALN_DT)
+        ops = np.zeros((n, stride), dtype=np.uint8)
+        n_ops = np.zeros(n, dtype=np.uint32)
+        rc = self._f("banded_traceback")(a, C.c_uint32(band), C.c_uint32(chk), _ptr(pat), _ptr(pat_off), _ptr(txt), _ptr(txt_off),
+                                         C.c_uint32(n), _ptr(out), _ptr(ops), C.c_uint32(stride), _ptr(n_ops), C.c_int(threads))
+        assert rc == 0, rc
+        return out, ops, n_ops
