@@ -1,0 +1,72 @@
+"""Pins the plain-C restatement (oracle/liboracle.so) bit-for-bit against the reference's own headers
+compiled into oracle/_ref/libnvbio_ref.so, on seeded random inputs (incl. binary alphabets = many ties).
+Skipped when oracle/_ref is not built."""
+import numpy as np
+import pytest
+import pyoracle as po
+import util
+
+
+@pytest.mark.parametrize("n,alpha", [(1, 4), (2, 4), (63, 4), (64, 4), (65, 4), (1000, 2), (4096, 4), (100000, 4)])
+def test_fm_index_build_and_queries(oracle, ref, n, alpha):
+    rng = np.random.default_rng(n * 7 + alpha)
+    text = rng.integers(0, alpha, n).astype(np.uint8)
+    a, b = ref.build_index(text, True), oracle.build_index(text, True)
+    assert a.primary == b.primary and (a.L2 == b.L2).all()
+    assert (a.bwt_occ == b.bwt_occ).all() and (a.ssa == b.ssa).all() and (a.sa == b.sa).all()
+    Q, qo = util.rand_queries(rng, text, 3000, alpha=alpha)
+    ra, rb = ref.fm_match(a, Q, qo), oracle.fm_match(b, Q, qo)
+    assert (ra == rb).all()
+    ok = ra[:, 0] <= ra[:, 1]
+    rows = np.concatenate([ra[ok, 0], ra[ok, 1], rng.integers(0, n + 1, 500).astype(np.uint32)])
+    pa, sa = ref.fm_locate(a, rows, True)
+    pb, sb = oracle.fm_locate(b, rows, True)
+    assert (pa == pb).all() and (sa == sb).all()
+    k = rng.integers(0, n + 1, 1000).astype(np.uint32)
+    k[:3] = [0xFFFFFFFF, n, 0]
+    assert (ref.fm_rank4(a, k) == oracle.fm_rank4(b, k)).all()
+    rg = np.stack([rng.integers(0, n + 1, 1000), rng.integers(0, n + 1, 1000)], 1).astype(np.uint32)
+    rg.sort(1)
+    rg[:50, 0] = 0xFFFFFFFF
+    rg[50:60, 1] = n
+    c = rng.integers(0, 4, 1000).astype(np.uint8)
+    assert (ref.fm_rank(a, rg, c) == oracle.fm_rank(b, rg, c)).all()
+
+
+CASES = [(k, sc, ty) for k in (po.ED, po.SW, po.GOTOH) for sc in util.SCHEMES[k] for ty in (0, 1, 2)]
+
+
+@pytest.mark.parametrize("kind,scheme,ty", CASES)
+def test_full_dp_score_and_traceback(oracle, ref, kind, scheme, ty):
+    rng = np.random.default_rng(hash((kind, scheme, ty)) & 0xFFFF)
+    a = po.aligner(kind, ty, scheme)
+    for alpha in (4, 2):
+        P, Po, T, To = util.rand_pairs(rng, 150, (1, 70), lambda M: int(rng.integers(0, 120)), alpha)
+        assert (ref.score(a, P, Po, T, To) == oracle.score(a, P, Po, T, To)).all()
+        for chk in (16, 32, 64):
+            assert util.ops_equal(ref.traceback(a, chk, P, Po, T, To), oracle.traceback(a, chk, P, Po, T, To))
+
+
+@pytest.mark.parametrize("kind,scheme,ty", CASES)
+def test_banded_dp_score_and_traceback(oracle, ref, kind, scheme, ty):
+    rng = np.random.default_rng(hash((kind, scheme, ty, 1)) & 0xFFFF)
+    a = po.aligner(kind, ty, scheme)
+    for alpha in (4, 2):
+        for band in (3, 5, 7, 15, 31):
+            P, Po, T, To = util.rand_pairs(rng, 120, (1, 80), util.banded_text_len(rng, ty, band), alpha)
+            assert (ref.banded_score(a, band, P, Po, T, To) == oracle.banded_score(a, band, P, Po, T, To)).all()
+            for chk in (16, 32):
+                assert util.ops_equal(ref.banded_traceback(a, band, chk, P, Po, T, To),
+                                      oracle.banded_traceback(a, band, chk, P, Po, T, To))
+
+
+def test_config_shapes(oracle, ref):
+    """the BASELINE.json shapes at small counts: C1 150x500 SW LOCAL, C3 250x265 band 15 ED/Gotoh SEMI_GLOBAL"""
+    rng = np.random.default_rng(77)
+    P, Po, T, To = util.rand_pairs(rng, 64, (150, 151), lambda M: 500)
+    a = po.aligner(po.SW, po.LOCAL, (2, -1, -1, -1))
+    assert (ref.score(a, P, Po, T, To) == oracle.score(a, P, Po, T, To)).all()
+    P, Po, T, To = util.rand_pairs(rng, 64, (250, 251), lambda M: 265)
+    for a in (po.aligner(po.ED, po.SEMI_GLOBAL), po.aligner(po.GOTOH, po.SEMI_GLOBAL, (0, -5, -8, -3))):
+        assert (ref.banded_score(a, 15, P, Po, T, To) == oracle.banded_score(a, 15, P, Po, T, To)).all()
+        assert util.ops_equal(ref.banded_traceback(a, 15, 16, P, Po, T, To), oracle.banded_traceback(a, 15, 16, P, Po, T, To))
