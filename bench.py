@@ -1,0 +1,441 @@
+#!/usr/bin/env python
+"""bench.py -- the reference's headline metric on B200: FM-index seed lookups/s (BASELINE.json configs[1]:
+exact 20-mer backward search, 10 M queries on a synthetic 100 Mbp 2-bit genome), with the SW / banded
+GCUPS of configs[0] and configs[2] reported beside it in `extra`.
+
+  python bench.py --gpus N --steps K --warmup W            (N > 1: launched with torch.distributed.run)
+  python bench.py --impl reference ...                     the reference's own host code on the box's cores
+
+A step = one pass of nvb_fm_match over one batch of 10 M resident queries (per GPU: weak scaling, the
+index is replicated, read batches are sharded, no collective on the data path). One JSON line on rank 0.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+QLEN = 20
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--genome", type=int, default=100_000_000)
+    ap.add_argument("--queries", type=int, default=10_000_000)
+    ap.add_argument("--sw-pairs", type=int, default=100_000)
+    ap.add_argument("--banded-pairs", type=int, default=1_000_000)
+    ap.add_argument("--no-extra", action="store_true", help="skip the SW / banded secondary measurements")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
+    ap.add_argument("--only", default="", help="profiling aid: run only this leg (fm|sw|banded) with no cpu leg")
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------------------------------------
+# oracle access: ONLY the cpu_baseline leg and --impl reference use this (test infrastructure)
+# ------------------------------------------------------------------------------------------------
+def load_checker():
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import pyoracle as po
+    if po.Oracle.available("ref"):
+        return po, po.Oracle("ref"), "reference"
+    if not po.Oracle.available("oracle"):
+        subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle"), os.path.join(ROOT, "oracle", "liboracle.so")])
+    return po, po.Oracle("oracle"), "port"
+
+
+def host_threads():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+# ------------------------------------------------------------------------------------------------
+# clocks
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.p = None
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(gpu_index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                                       "-lms", "100"], stdout=self.f, stderr=subprocess.DEVNULL)
+        except OSError:
+            pass
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+        if self.p is None:
+            return out
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.p.kill()
+        self.f.flush()
+        rows = [l.strip().split(", ") for l in open(self.f.name) if l.strip()]
+        os.unlink(self.f.name)
+        sm, mx, reasons = [], [], set()
+        for r in rows:
+            if len(r) < 9:
+                continue
+            try:
+                sm.append(float(r[1])); mx.append(float(r[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[5:9]):
+                if v.strip().lower() == "active":
+                    reasons.add(name)
+        if sm:
+            out = {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons), "samples": len(sm)}
+        return out
+
+
+# ------------------------------------------------------------------------------------------------
+# synthetic workloads
+# ------------------------------------------------------------------------------------------------
+def gen_genome(n, seed, dev):
+    import torch
+    g = torch.Generator(device=dev); g.manual_seed(seed)
+    return torch.randint(0, 4, (n,), dtype=torch.uint8, device=dev, generator=g)
+
+
+def gen_queries(genome, nq, seed, dev):
+    """90 % 20-mers cut from the genome, 10 % random, 0.1 % with an N; shuffled order by construction"""
+    import torch
+    g = torch.Generator(device=dev); g.manual_seed(seed)
+    n = genome.numel()
+    pos = torch.randint(0, n - QLEN, (nq,), device=dev, generator=g)
+    q = genome[(pos[:, None] + torch.arange(QLEN, device=dev)[None, :]).reshape(-1)].reshape(nq, QLEN)
+    rnd = torch.rand(nq, device=dev, generator=g) < 0.10
+    q[rnd] = torch.randint(0, 4, (int(rnd.sum().item()), QLEN), dtype=torch.uint8, device=dev, generator=g)
+    hasn = torch.nonzero(torch.rand(nq, device=dev, generator=g) < 0.001)[:, 0]
+    q[hasn, torch.randint(0, QLEN, (hasn.numel(),), device=dev, generator=g)] = 4
+    off = (torch.arange(nq + 1, device=dev, dtype=torch.int64) * QLEN).to(torch.int32)
+    return q.reshape(-1).contiguous(), off
+
+
+def gen_pairs(n, M, N, seed, dev, sub=0.05, implant_frac=0.5):
+    """n pairs: pattern M symbols, text N symbols; a fraction has the pattern implanted with substitutions"""
+    import torch
+    g = torch.Generator(device=dev); g.manual_seed(seed)
+    P = torch.randint(0, 4, (n, M), dtype=torch.uint8, device=dev, generator=g)
+    T = torch.randint(0, 4, (n, N), dtype=torch.uint8, device=dev, generator=g)
+    k = int(n * implant_frac)
+    if k:
+        start = torch.randint(0, N - M + 1, (k,), device=dev, generator=g)
+        mut = P[:k].clone()
+        m = torch.rand((k, M), device=dev, generator=g) < sub
+        mut[m] = torch.randint(0, 4, (int(m.sum().item()),), dtype=torch.uint8, device=dev, generator=g)
+        cols = start[:, None] + torch.arange(M, device=dev)[None, :]
+        T[:k].scatter_(1, cols, mut)
+    po_ = (torch.arange(n + 1, device=dev, dtype=torch.int64) * M).to(torch.int32)
+    to_ = (torch.arange(n + 1, device=dev, dtype=torch.int64) * N).to(torch.int32)
+    return P.reshape(-1).contiguous(), po_, T.reshape(-1).contiguous(), to_
+
+
+def time_steps(fn, steps, warmup, flush):
+    """CUDA-event time of `steps` calls of fn on the current stream, L2 flushed between calls"""
+    import torch
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    times = []
+    for _ in range(steps):
+        flush()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); fn(); e1.record()
+        torch.cuda.synchronize()
+        times.append(e0.elapsed_time(e1))
+    return times
+
+
+# ------------------------------------------------------------------------------------------------
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    import ctypes
+    import nvbio_gpl_b200 as nvb
+    from nvbio_gpl_b200._lib import check, current_stream_ptr
+    from nvbio_gpl_b200.fmindex import _set_c
+    L = nvb.lib()
+
+    rank = int(os.environ.get("RANK", 0)); world = int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the hot path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    ctx = nvb.Context.default(local)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+
+    def flush():
+        flush_buf.fill_(1)
+
+    only = args.only
+    out = {}
+    # ---------------- index: built once on rank 0, replicated over NVLink (outside the timed region)
+    t0 = time.time()
+    if only in ("", "fm"):
+        if rank == 0:
+            genome = gen_genome(args.genome, 2, dev)
+            fmi = nvb.build_index(genome)
+            meta = torch.tensor([fmi.length, fmi.primary] + fmi.L2, dtype=torch.int64, device=dev)
+        else:
+            meta = torch.zeros(7, dtype=torch.int64, device=dev)
+        if world > 1:
+            dist.broadcast(meta, 0)
+            if rank != 0:
+                n = int(meta[0].item())
+                genome = torch.empty(n, dtype=torch.uint8, device=dev)
+                fmi = nvb.FMIndex(n, int(meta[1].item()), [int(v) for v in meta[2:].tolist()],
+                                  torch.empty(nvb.lib().nvb_bwt_occ_words(n), dtype=torch.int32, device=dev),
+                                  torch.empty(nvb.lib().nvb_ssa_words(n), dtype=torch.int32, device=dev))
+            dist.broadcast(genome, 0); dist.broadcast(fmi.bwt_occ, 0); dist.broadcast(fmi.ssa, 0)
+        build_s = time.time() - t0
+        qsym, qoff = gen_queries(genome, args.queries, 100 + rank, dev)
+        nq = args.queries
+        ranges = torch.empty((nq, 2), dtype=torch.int32, device=dev)
+
+        def _match():   # resident inputs, resident output: exactly one nvb_fm_match launch
+            check(L.nvb_fm_match(ctx.h, ctypes.byref(fc), qset, ranges.data_ptr(), current_stream_ptr()), ctx.h)
+
+        fc = fmi.c()
+        qset = _set_c(qsym, qoff)
+        l0 = ctx.launches
+        barrier()
+        sampler = ClockSampler(local) if rank == 0 else None
+        times = time_steps(_match, args.steps, args.warmup, flush)
+        barrier()
+        clocks = sampler.stop() if sampler else None
+        launches = (ctx.launches - l0) - args.warmup
+        step_ms = max_over_ranks(sum(times) / len(times))
+        out["fm"] = dict(step_ms=step_ms, value=world * nq / (step_ms * 1e-3), launches=launches, clocks=clocks,
+                         build_s=build_s, kernel_ms=sum(times) / len(times))
+
+        # ---- e2e: host buffers (pinned) through the C-ABI *_host call: H2D + kernel + D2H per step
+        hs = torch.empty(qsym.numel(), dtype=torch.uint8).pin_memory(); hs.copy_(qsym)
+        ho = torch.empty(qoff.numel(), dtype=torch.int32).pin_memory(); ho.copy_(qoff)
+        hr = torch.empty((nq, 2), dtype=torch.int32).pin_memory()
+        hs_n, ho_n, hr_n = hs.numpy(), ho.numpy().view(np.uint32), hr.numpy().view(np.uint32)
+        cstream = torch.cuda.ExternalStream(ctx.stream, device=dev)
+        for _ in range(max(1, args.warmup)):
+            nvb.match_host(fmi, hs_n, ho_n, hr_n, ctx=ctx)
+        barrier()
+        e2e_t = []
+        for _ in range(args.steps):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(cstream)
+            nvb.match_host(fmi, hs_n, ho_n, hr_n, ctx=ctx)
+            e1.record(cstream); e1.synchronize()
+            e2e_t.append(e0.elapsed_time(e1))
+        barrier()
+        e2e_ms = max_over_ranks(sum(e2e_t) / len(e2e_t))
+        out["fm"]["e2e"] = dict(value=world * nq / (e2e_ms * 1e-3), unit="lookups/s", ms_per_step=e2e_ms,
+                                h2d_bytes_per_step=int(hs.numel() + ho.numel() * 4), d2h_bytes_per_step=int(hr.numel() * 4))
+        assert (hr_n == ranges.cpu().numpy().view(np.uint32)).all(), "host and device entry points disagree"
+
+        # ---- cpu_baseline + parity + algorithmic bytes (rank 0, N == 1 only): the ONLY use of oracle/
+        if rank == 0 and world == 1 and not args.no_cpu and only == "":
+            po, chk, kind = load_checker()
+            bwt_occ, ssa = fmi.host_arrays()
+            oidx = po.Index(fmi.length, fmi.primary, np.array(fmi.L2, dtype=np.uint32), bwt_occ, ssa)
+            threads = host_threads()
+            probe = 100_000
+            t = time.time(); chk.fm_match(oidx, hs_n[:probe * QLEN], ho_n[:probe + 1], threads=threads); dt = time.time() - t
+            sample = int(min(nq, max(probe, 12.0 / max(dt, 1e-6) * probe)))
+            best = 1e30
+            for _ in range(2):
+                t = time.time(); want = chk.fm_match(oidx, hs_n[:sample * QLEN], ho_n[:sample + 1], threads=threads)
+                best = min(best, time.time() - t)
+            mism = int((want != hr_n[:sample]).any(axis=1).sum())
+            # distinct 32-byte blocks the reference algorithm touches (counted by the C restatement)
+            _, orc, _ = (po, po.Oracle("oracle"), None)
+            nb = min(sample, 1_000_000)
+            _, blocks = orc.fm_match(oidx, hs_n[:nb * QLEN], ho_n[:nb + 1], want_blocks=True, threads=threads)
+            out["fm"]["cpu"] = dict(value=sample / best, unit="lookups/s", cores=threads, kind=kind,
+                                    sample="first %d of the %d queries, best of 2, extrapolation-free rate" % (sample, nq))
+            out["fm"]["parity"] = dict(checked=sample, mismatches=mism)
+            out["fm"]["blocks_per_query"] = float(blocks.mean())
+        del hs, ho, hr
+
+    # ---------------- secondary: SW local scoring (configs[0]) and banded scoring/traceback (configs[2])
+    if not args.no_extra or only in ("sw", "banded"):
+        if only in ("", "sw"):
+            M, N, n = 150, 500, args.sw_pairs
+            P, Po, T, To = gen_pairs(n, M, N, 1 + rank, dev)
+            ps, ts = nvb.StringSet(P, Po, 8, M), nvb.StringSet(T, To, 8, N)
+            a = nvb.SmithWatermanAligner(nvb.LOCAL, 2, -1, -1, -1)
+            sinks = torch.empty((n, 3), dtype=torch.int32, device=dev)
+            temp = torch.empty(int(nvb.lib().nvb_temp_bytes(0, a.c(), 0, 0, M, N, n)), dtype=torch.uint8, device=dev)
+            fn = lambda: nvb.batch_alignment_score(a, ps, ts, sinks=sinks, temp=temp, ctx=ctx)
+            barrier()
+            tms = time_steps(fn, max(3, args.steps // 2), 2, flush)
+            ms = max_over_ranks(sum(tms) / len(tms))
+            out["sw"] = dict(gcups=world * n * M * N / (ms * 1e-3) / 1e9, ms=ms, pairs=n, M=M, N=N, paths=ctx.last_paths)
+            if rank == 0 and world == 1 and not args.no_cpu and only == "":
+                po, chk, kind = load_checker()
+                k = min(n, 20000)
+                Ph, Th = P[:k * M].cpu().numpy(), T[:k * N].cpu().numpy()
+                Poh, Toh = (np.arange(k + 1) * M).astype(np.uint32), (np.arange(k + 1) * N).astype(np.uint32)
+                oa = po.aligner(po.SW, po.LOCAL, (2, -1, -1, -1))
+                t = time.time(); want = chk.score(oa, Ph, Poh, Th, Toh, threads=host_threads()); dt = time.time() - t
+                got = sinks[:k].cpu().numpy()
+                mism = int(((got[:, 0] != want["score"]) | (got[:, 1].view(np.uint32) != want["x"]) | (got[:, 2].view(np.uint32) != want["y"])).sum())
+                out["sw"]["cpu_gcups"] = k * M * N / dt / 1e9
+                out["sw"]["cpu_kind"] = kind
+                out["sw"]["parity"] = dict(checked=k, mismatches=mism)
+            del P, T, temp
+        if only in ("", "banded"):
+            M, W, n = 250, 15, args.banded_pairs
+            N = M + W
+            P, Po, T, To = gen_pairs(n, M, N, 3 + rank, dev, sub=0.04, implant_frac=1.0)
+            ps, ts = nvb.StringSet(P, Po, 8, M), nvb.StringSet(T, To, 8, N)
+            res = {}
+            for name, a in (("ed_semi", nvb.EditDistanceAligner(nvb.SEMI_GLOBAL)),
+                            ("gotoh_semi", nvb.GotohAligner(nvb.SEMI_GLOBAL, 0, -5, -8, -3)),
+                            ("sw_local", nvb.SmithWatermanAligner(nvb.LOCAL, 2, -1, -1, -1))):
+                sinks = torch.empty((n, 3), dtype=torch.int32, device=dev)
+                fn = lambda: nvb.batch_banded_alignment_score(a, W, ps, ts, sinks=sinks, ctx=ctx)
+                barrier()
+                tms = time_steps(fn, max(3, args.steps // 2), 2, flush)
+                ms = max_over_ranks(sum(tms) / len(tms))
+                res[name] = dict(gcups=world * n * M * W / (ms * 1e-3) / 1e9, ms=ms, paths=ctx.last_paths)
+            # traceback (CHK = 16 as nvBowtie, defs.h:95) on a slice that keeps scratch modest
+            nt = min(n, 200_000)
+            pt, tt = nvb.StringSet(P[:nt * M], Po[:nt + 1], 8, M), nvb.StringSet(T[:nt * N], To[:nt + 1], 8, N)
+            a = nvb.GotohAligner(nvb.SEMI_GLOBAL, 0, -5, -8, -3)
+            fn = lambda: nvb.batch_banded_alignment_traceback(a, W, 16, pt, tt, ctx=ctx)
+            tms = time_steps(fn, 3, 1, flush)
+            ms = max_over_ranks(sum(tms) / len(tms))
+            res["gotoh_semi_traceback"] = dict(pairs_per_s=world * nt / (ms * 1e-3), ms=ms, pairs=nt)
+            out["banded"] = dict(pairs=n, M=M, N=N, band=W, **res)
+
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    if rank != 0:
+        return
+
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except (OSError, ValueError):
+        pass
+    hbm_peak, peak_src = (peaks["hbm_gbs"], "measured") if "hbm_gbs" in peaks else (6650.0, "fallback")
+
+    line = {"metric": "fm_index_seed_lookups_per_s", "unit": "lookups/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u32",
+            "data": "synthetic", "impl": "b200"}
+    if "fm" in out:
+        fm = out["fm"]
+        bpq = fm.get("blocks_per_query")
+        # algorithmic bytes per query: 32 B x distinct blocks + query symbols + offset + 8 B result
+        alg_per_q = (32.0 * bpq + QLEN + 4 + 8) if bpq else None
+        line.update(value=fm["value"], ms_per_step=fm["step_ms"], gpu_launches=fm["launches"], clocks=fm["clocks"],
+                    e2e={k: fm["e2e"][k] for k in ("value", "unit", "h2d_bytes_per_step", "d2h_bytes_per_step")},
+                    config={"workload": "configs[1]: FM-index exact 20-mer backward search, %d queries per GPU on a synthetic %d bp 2-bit genome"
+                                        % (args.queries, args.genome),
+                            "queries": "90% cut from the genome, 10% random, 0.1% with an N, unsorted",
+                            "index_bytes": int(fmi.bwt_occ.numel() * 4), "partition": "queries sharded, index replicated, no collective",
+                            "l2": "flushed (256 MiB write) between timed steps, outside the event-timed region",
+                            "index_build_s": round(fm["build_s"], 2)})
+        if alg_per_q:
+            ach = alg_per_q * args.queries / (fm["kernel_ms"] * 1e-3) / 1e9
+            line["roofline"] = {"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
+                                "traffic": None, "kernel": "fm_match_kernel<8,false>", "peak_source": peak_src,
+                                "algorithmic_bytes_per_query": alg_per_q, "blocks_per_query": bpq}
+        if "cpu" in fm:
+            line["cpu_baseline"] = fm["cpu"]
+            line["parity"] = fm["parity"]
+    extra = {k: out[k] for k in ("sw", "banded") if k in out}
+    if extra:
+        line["extra"] = extra
+    print(json.dumps(line))
+
+
+# ------------------------------------------------------------------------------------------------
+def run_reference(args):
+    """the reference's own host implementation of the path (oracle/_ref when built, else the C port) on all
+    host threads; each step = one bounded sample of the configs[1] workload"""
+    rank = int(os.environ.get("RANK", 0))
+    if rank != 0:
+        return
+    po, chk, kind = load_checker()
+    threads = host_threads()
+    rng = np.random.default_rng(2)
+    n = args.genome
+    text = rng.integers(0, 4, n, dtype=np.uint8)
+    t0 = time.time()
+    idx = chk.build_index(text)
+    build_s = time.time() - t0
+    probe = 100_000
+
+    def queries(k, seed):
+        r = np.random.default_rng(seed)
+        pos = r.integers(0, n - QLEN, k)
+        q = text[(pos[:, None] + np.arange(QLEN)[None, :]).reshape(-1)].reshape(k, QLEN).copy()
+        rnd = r.random(k) < 0.10
+        q[rnd] = r.integers(0, 4, (int(rnd.sum()), QLEN), dtype=np.uint8)
+        hasn = np.nonzero(r.random(k) < 0.001)[0]
+        q[hasn, r.integers(0, QLEN, len(hasn))] = 4
+        return q.reshape(-1), (np.arange(k + 1) * QLEN).astype(np.uint32)
+
+    Q, qo = queries(probe, 100)
+    t = time.time(); chk.fm_match(idx, Q, qo, threads=threads); dt = time.time() - t
+    total = max(1, args.steps + args.warmup)
+    sample = int(min(args.queries, max(probe, (120.0 / total) / max(dt, 1e-6) * probe)))
+    Q, qo = queries(sample, 100)
+    for _ in range(args.warmup):
+        chk.fm_match(idx, Q, qo, threads=threads)
+    t = time.time()
+    for _ in range(args.steps):
+        chk.fm_match(idx, Q, qo, threads=threads)
+    ms = (time.time() - t) / max(1, args.steps) * 1e3
+    v = sample / (ms * 1e-3)
+    print(json.dumps({
+        "impl": "reference", "metric": "fm_index_seed_lookups_per_s", "value": v, "unit": "lookups/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u32", "data": "synthetic",
+        "config": {"workload": "configs[1]: FM-index exact 20-mer backward search on a synthetic %d bp 2-bit genome" % n,
+                   "index_build_s": round(build_s, 2)},
+        "cpu_baseline": {"value": v, "unit": "lookups/s", "cores": threads, "kind": kind,
+                         "sample": "%d queries per step (bounded sample of the 10 M-query workload)" % sample},
+        "e2e": {"value": v, "unit": "lookups/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}))
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_b200(a)

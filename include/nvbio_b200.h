@@ -1,0 +1,241 @@
+/*
+ * nvbio_b200.h -- C ABI of libnvbio_b200.so: the B200-native (sm_100a) seed-and-extend hot path.
+ *
+ * This is the drop-in boundary. Every entry point names the reference interface it replaces
+ * (file:line into the nvbio-gpl tree). The reference API is header-only C++ templates over
+ * "storage-free" views with no error channel; here the same views are plain structs of pointers
+ * and sizes, every call returns an nvb_status, and nothing but CUDA is required to link.
+ *
+ * Conventions
+ *   - pointers are DEVICE pointers unless the parameter name ends in _h or the function name
+ *     ends in _host; `stream` is a cudaStream_t passed as void* (NULL = the default stream);
+ *   - device entry points never synchronise and never allocate (scratch is passed in as `temp`,
+ *     sized by nvb_temp_bytes); the *_host entry points stage through buffers owned by the
+ *     nvb_ctx, run on the ctx stream and return after the results are in the host buffers;
+ *   - one nvb_ctx per (device, host thread): it holds the device ordinal, a stream, the staging
+ *     buffers of the *_host calls and the small "dirty pair" worklists of the DP kernels;
+ *   - symbols: one uint8 per symbol (bits = 8), 0..3 = A,C,G,T, anything else = N (compares equal
+ *     only to the same code, as `r == q` does in nvbio/alignment/sw/sw_inl.h:452);
+ *     bits = 2 / 4: big-endian packed 32-bit words, the layout of
+ *     PackedStream<const uint32*,uint8,BITS,true> (nvbio/basic/packedstream_inl.h:30-52);
+ *   - there is NO CPU fallback: without a CUDA device every compute entry point returns
+ *     NVB_ERR_CUDA.
+ */
+#ifndef NVBIO_B200_H
+#define NVBIO_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+#if defined(__GNUC__)
+#pragma GCC visibility push(default)   /* the library itself is built with -fvisibility=hidden */
+#endif
+
+#define NVB_VERSION 100
+
+typedef enum {
+    NVB_OK            = 0,
+    NVB_ERR_ARG       = -1,  /* NULL / out-of-contract argument                         */
+    NVB_ERR_CUDA      = -2,  /* a CUDA runtime call failed (see nvb_last_cuda_error)    */
+    NVB_ERR_TEMP      = -3,  /* temp buffer smaller than nvb_temp_bytes(...)            */
+    NVB_ERR_UNSUPPORTED = -4 /* combination outside the contract        */
+} nvb_status;
+
+typedef struct nvb_ctx nvb_ctx;
+
+/* ---------------------------------------------------------------------------------------------
+ * FM-index view == nvbio::fm_index< rank_dictionary<2,64,...>, SSA_index_multiple_context<16> >
+ * (nvbio/fmindex/fmindex.h:320-361) over the fused nvBWT image of io::FMIndexData
+ * (nvbio/io/fmindex/fmindex.h:81-86,126-163; fusing loop nvbio/io/fmindex/fmindex_impl.cu:296-318):
+ * per 64 BWT symbols one 32-byte block = 4 big-endian 2-bit words + 4 uint32 counters (A,C,G,T
+ * occurrences BEFORE the block). bwt_occ must be 32-byte aligned.
+ * ------------------------------------------------------------------------------------------- */
+typedef struct {
+    uint32_t        length;     /* fm_index::m_length  : text symbols                           */
+    uint32_t        primary;    /* fm_index::m_primary : BWT row of the full text               */
+    uint32_t        L2[5];      /* fm_index::m_L2      : cumulative symbol counts               */
+    uint32_t        occ_int;    /* must be 64  (FMIndexDataCore::OCC_INT)                       */
+    uint32_t        sa_int;     /* must be 16  (FMIndexDataCore::SA_INT)                        */
+    const void*     bwt_occ;    /* fused array, 32 B per 64 symbols                             */
+    const uint32_t* ssa;        /* (length+16)/16 entries, ssa[0] = 0xFFFFFFFF; may be NULL     */
+} nvb_fmindex;
+
+/* ConcatenatedStringSet<symbols, offsets> (nvbio/strings/string_set.h:405-492) */
+typedef struct {
+    const void*     symbols;    /* bits==8: uint8 per symbol; bits==2|4: packed uint32 words    */
+    const uint32_t* offsets;    /* count+1 symbol offsets                                       */
+    uint32_t        count;
+    uint32_t        bits;       /* 8, 4 or 2                                                    */
+} nvb_string_set;
+
+/* aligner tag objects (nvbio/alignment/alignment.h:365-519) with the "simple" scoring schemes
+ * (nvbio/alignment/utils.h:81-124, ed/ed_utils.h:36-43) */
+enum { NVB_EDIT_DISTANCE = 0, NVB_SMITH_WATERMAN = 1, NVB_GOTOH = 2 };
+enum { NVB_GLOBAL = 0, NVB_LOCAL = 1, NVB_SEMI_GLOBAL = 2 };          /* alignment.h:242 */
+typedef struct {
+    int32_t kind;      /* NVB_EDIT_DISTANCE | NVB_SMITH_WATERMAN | NVB_GOTOH                    */
+    int32_t type;      /* NVB_GLOBAL | NVB_LOCAL | NVB_SEMI_GLOBAL                              */
+    int32_t match;     /* SimpleSmithWatermanScheme / SimpleGotohScheme ::m_match               */
+    int32_t mismatch;  /* ::m_mismatch                                                          */
+    int32_t gap_a;     /* SW: m_deletion   ; Gotoh: m_gap_open                                  */
+    int32_t gap_b;     /* SW: m_insertion  ; Gotoh: m_gap_ext                                   */
+} nvb_aligner;         /* kind == ED ignores the four scores: (0,-1,-1,-1)                      */
+
+/* aln::BestSink<int32> (nvbio/alignment/sink.h, sink_inl.h:31-48): sink = (text end, pattern end),
+ * 1-based; "no cell reported" = score -(1<<30), sink (0xFFFFFFFF,0xFFFFFFFF) */
+typedef struct { int32_t score; uint32_t sink_x, sink_y; } nvb_best_sink;
+
+/* aln::Alignment<int32> (nvbio/alignment/alignment.h:310-322) */
+typedef struct { int32_t score; uint32_t source_x, source_y, sink_x, sink_y; } nvb_alignment;
+
+/* traceback ops, one uint8 per op in PUSH order (end -> start), as a Backtracer receives them
+ * (nvbio/alignment/alignment.h:126-143, DirectionVector :326-337) */
+enum { NVB_OP_SUBSTITUTION = 0, NVB_OP_INSERTION = 1, NVB_OP_DELETION = 2 };
+
+/* ----------------------------------------------------------------------------------------- */
+/* context                                                                                     */
+/* ----------------------------------------------------------------------------------------- */
+int         nvb_version(void);
+const char* nvb_status_string(int status);
+int         nvb_ctx_create(int device, nvb_ctx** ctx);
+void        nvb_ctx_destroy(nvb_ctx* ctx);
+void*       nvb_ctx_stream(nvb_ctx* ctx);              /* the ctx's own cudaStream_t */
+int         nvb_ctx_synchronize(nvb_ctx* ctx);
+const char* nvb_last_cuda_error(nvb_ctx* ctx);
+/* number of kernels this library has launched through ctx since creation */
+uint64_t    nvb_ctx_launch_count(nvb_ctx* ctx);
+
+/* pinned host memory for the *_host entry points (plain cudaHostAlloc / cudaFreeHost) */
+int         nvb_host_alloc(size_t bytes, void** ptr_h);
+void        nvb_host_free(void* ptr_h);
+
+/* ----------------------------------------------------------------------------------------- */
+/* FM-index: index image                                                                       */
+/* ----------------------------------------------------------------------------------------- */
+/* io::FMIndexDataDevice(host_data) (nvbio/io/fmindex/fmindex_impl.cu:740-826): upload a host image
+ * (fmi_h: bwt_occ / ssa are HOST pointers) and fill *fmi_d with device pointers owned by ctx. */
+int nvb_fmindex_upload(nvb_ctx* ctx, const nvb_fmindex* fmi_h, nvb_fmindex* fmi_d);
+int nvb_fmindex_release(nvb_ctx* ctx, nvb_fmindex* fmi_d);
+/* pin the first `bytes` of the fused array (the hot BWT prefix) in L2 for work on the ctx stream
+ * (cudaAccessPolicyWindow); bytes = 0 removes the window. Replaces the reference's texture/__ldg
+ * cache hint (nvbio/fmindex/fmindex.h:564-583). */
+int nvb_fmindex_pin_l2(nvb_ctx* ctx, const nvb_fmindex* fmi_d, size_t bytes);
+/* fuse a plain BWT (2-bit big-endian words, as in a .bwt file: nvBWT/nvBWT.cu:303-321) into the
+ * interleaved bwt|occ image and compute L2; all pointers DEVICE; bwt_occ_out has
+ * nvb_bwt_occ_words(length) words. Replaces nvbio/io/fmindex/fmindex_impl.cu:283-318 +
+ * build_occurrence_table<64> (nvbio/fmindex/rank_dictionary_inl.h:34-66). */
+size_t nvb_bwt_occ_words(uint32_t length);
+size_t nvb_ssa_words(uint32_t length);
+int nvb_fmindex_fuse(nvb_ctx* ctx, const uint32_t* bwt_words, uint32_t length, uint32_t* bwt_occ_out,
+                     uint32_t* L2_out_h, void* stream);
+
+/* ----------------------------------------------------------------------------------------- */
+/* FM-index: queries                                                                           */
+/* ----------------------------------------------------------------------------------------- */
+/* match(fmi, pattern, len) for every string of the set (nvbio/fmindex/fmindex_inl.h:186-239; batch
+ * form FMIndexFilter::rank, nvbio/fmindex/filter_inl.h:36-67,261-291).
+ * ranges: 2 uint32 per query = the raw inclusive SA interval (x,y); empty iff x > y. */
+int nvb_fm_match(nvb_ctx* ctx, const nvb_fmindex* fmi, nvb_string_set queries, uint32_t* ranges,
+                 void* stream);
+/* match continued from given ranges: match(fmi, pattern, len, range) (fmindex_inl.h:212-239);
+ * ranges is in/out */
+int nvb_fm_match_from(nvb_ctx* ctx, const nvb_fmindex* fmi, nvb_string_set queries, uint32_t* ranges,
+                      void* stream);
+/* rank(fmi, range, c) (fmindex_inl.h:60-88): out[2i],out[2i+1] = occurrences of c[i] in
+ * BWT[0..ranges[2i]] and BWT[0..ranges[2i+1]] (0xFFFFFFFF = -1 -> 0) */
+int nvb_fm_rank(nvb_ctx* ctx, const nvb_fmindex* fmi, const uint32_t* ranges, const uint8_t* c,
+                uint32_t n, uint32_t* out, void* stream);
+/* rank4(fmi, k) (fmindex_inl.h:100-125): out[4i+c] for c = A,C,G,T */
+int nvb_fm_rank4(nvb_ctx* ctx, const nvb_fmindex* fmi, const uint32_t* k, uint32_t n, uint32_t* out,
+                 void* stream);
+/* locate(fmi, row) (fmindex_inl.h:364-394): SA row -> text coordinate through the sampled SA */
+int nvb_fm_locate(nvb_ctx* ctx, const nvb_fmindex* fmi, const uint32_t* rows, uint32_t n,
+                  uint32_t* pos, void* stream);
+/* the two-phase form nvBowtie uses: locate_ssa_iterator / lookup_ssa_iterator
+ * (fmindex_inl.h:408-460): walk[2i] = sampled row, walk[2i+1] = steps; then pos = ssa[row/16]+steps */
+int nvb_fm_locate_walk(nvb_ctx* ctx, const nvb_fmindex* fmi, const uint32_t* rows, uint32_t n,
+                       uint32_t* walk, void* stream);
+int nvb_fm_locate_lookup(nvb_ctx* ctx, const nvb_fmindex* fmi, const uint32_t* walk, uint32_t n,
+                         uint32_t* pos, void* stream);
+
+/* host-buffer forms: H2D + kernel + D2H on the ctx stream, synchronous */
+int nvb_fm_match_host(nvb_ctx* ctx, const nvb_fmindex* fmi_d, const uint8_t* symbols_h,
+                      const uint32_t* offsets_h, uint32_t count, uint32_t* ranges_h);
+int nvb_fm_locate_host(nvb_ctx* ctx, const nvb_fmindex* fmi_d, const uint32_t* rows_h, uint32_t n,
+                       uint32_t* pos_h);
+
+/* ----------------------------------------------------------------------------------------- */
+/* alignment                                                                                   */
+/* ----------------------------------------------------------------------------------------- */
+enum { NVB_OP_SCORE = 0, NVB_OP_BANDED_SCORE = 1, NVB_OP_TRACEBACK = 2, NVB_OP_BANDED_TRACEBACK = 3 };
+
+/* scratch bytes for n pairs: BatchedAlignmentScore::min/max_temp_storage
+ * (nvbio/alignment/batched.h:279-289, batched_inl.h:340-363,699-745) */
+size_t nvb_temp_bytes(int op, nvb_aligner aligner, uint32_t band, uint32_t checkpoints,
+                      uint32_t max_pattern_len, uint32_t max_text_len, uint32_t n);
+
+/* aln::batch_alignment_score(aligner, patterns, texts, sinks, DeviceThreadScheduler(), maxM, maxN)
+ * (nvbio/alignment/batched.h:98-140, batched_inl.h:980-1007; kernels batched_inl.h:79-128) */
+int nvb_batch_score(nvb_ctx* ctx, nvb_aligner aligner, nvb_string_set patterns, nvb_string_set texts,
+                    nvb_best_sink* sinks, uint32_t max_pattern_len, uint32_t max_text_len,
+                    void* temp, size_t temp_bytes, void* stream);
+
+/* aln::batch_banded_alignment_score<BAND_LEN>(...) (nvbio/alignment/batched.h:142-192,
+ * batched_banded_inl.h:34-81,152-157). band in 2..64; pairs with text shorter than the pattern
+ * are refused exactly as the reference does (sink left at "no cell reported"). */
+int nvb_batch_banded_score(nvb_ctx* ctx, nvb_aligner aligner, uint32_t band, nvb_string_set patterns,
+                           nvb_string_set texts, nvb_best_sink* sinks, uint32_t max_pattern_len,
+                           uint32_t max_text_len, void* temp, size_t temp_bytes, void* stream);
+
+/* BatchedAlignmentTraceback<CHECKPOINTS,...>::enact (nvbio/alignment/batched.h:335-380,
+ * batched_inl.h:599-680,760-830; per pair aln::alignment_traceback, alignment_inl.h:355-455).
+ * ops: ops_stride bytes per pair, n_ops[i] of them valid (if n_ops[i] > ops_stride the list was
+ * truncated); checkpoints must be a positive multiple of 16 (64 in nvBowtie, defs.h:96). */
+int nvb_batch_traceback(nvb_ctx* ctx, nvb_aligner aligner, uint32_t checkpoints,
+                        nvb_string_set patterns, nvb_string_set texts, nvb_alignment* out,
+                        uint8_t* ops, uint32_t ops_stride, uint32_t* n_ops,
+                        uint32_t max_pattern_len, uint32_t max_text_len,
+                        void* temp, size_t temp_bytes, void* stream);
+
+/* BatchedBandedAlignmentTraceback<BAND_LEN,CHECKPOINTS,...>::enact
+ * (nvbio/alignment/batched.h:382-438, batched_banded_inl.h:243-321,331-453; per pair
+ * aln::banded_alignment_traceback, banded_inl.h:354-430) */
+int nvb_batch_banded_traceback(nvb_ctx* ctx, nvb_aligner aligner, uint32_t band, uint32_t checkpoints,
+                               nvb_string_set patterns, nvb_string_set texts, nvb_alignment* out,
+                               uint8_t* ops, uint32_t ops_stride, uint32_t* n_ops,
+                               uint32_t max_pattern_len, uint32_t max_text_len,
+                               void* temp, size_t temp_bytes, void* stream);
+
+/* push-order ops -> run-length CIGAR in forward (start -> end) order, io::Cigar encoding
+ * (nvbio/io/alignments.h:48-65: 2-bit op in the low bits | 14-bit length << 2); cigar_stride
+ * uint16 per pair, n_cigar[i] entries written */
+int nvb_ops_to_cigar(nvb_ctx* ctx, const uint8_t* ops, uint32_t ops_stride, const uint32_t* n_ops,
+                     uint32_t n, uint16_t* cigar, uint32_t cigar_stride, uint32_t* n_cigar,
+                     void* stream);
+
+/* host-buffer forms (H2D of both string sets, kernel(s), D2H of the results; synchronous) */
+int nvb_batch_score_host(nvb_ctx* ctx, nvb_aligner aligner, uint32_t band /* 0 = full matrix */,
+                         const uint8_t* pat_h, const uint32_t* pat_off_h, const uint8_t* txt_h,
+                         const uint32_t* txt_off_h, uint32_t n, nvb_best_sink* sinks_h);
+int nvb_batch_traceback_host(nvb_ctx* ctx, nvb_aligner aligner, uint32_t band /* 0 = full matrix */,
+                             uint32_t checkpoints, const uint8_t* pat_h, const uint32_t* pat_off_h,
+                             const uint8_t* txt_h, const uint32_t* txt_off_h, uint32_t n,
+                             nvb_alignment* out_h, uint8_t* ops_h, uint32_t ops_stride,
+                             uint32_t* n_ops_h);
+
+/* which kernel family served the last alignment call on ctx: bit 0 = packed DPX fast path,
+ * bit 1 = int32 generic path (for tests and profiling; both may be set) */
+uint32_t nvb_last_paths(nvb_ctx* ctx);
+/* force the int32 generic kernels (parity anchor) : 0 = auto, 1 = generic only */
+void nvb_force_generic(nvb_ctx* ctx, int on);
+
+#if defined(__GNUC__)
+#pragma GCC visibility pop
+#endif
+#ifdef __cplusplus
+}
+#endif
+#endif /* NVBIO_B200_H */

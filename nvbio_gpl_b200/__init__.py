@@ -1,0 +1,18 @@
+"""nvbio_gpl_b200 -- B200-native (sm_100a) seed-and-extend hot path of NVBIO / nvBowtie.
+
+The product is ``libnvbio_b200.so`` (hand-written CUDA behind the C ABI of ``include/nvbio_b200.h``).
+This package is the thin host-side mirror of the reference's operator interface for that path
+(``fm_index`` + ``match/rank/rank4/locate``; aligner tag objects + ``batch_alignment_score`` /
+``batch_banded_alignment_score`` / batched traceback), used by the tests and ``bench.py``. PyTorch is
+only plumbing here (device buffers, streams, torch.distributed). There is no CPU fallback: every
+compute call raises if the CUDA library or a CUDA device is missing.
+"""
+from ._lib import lib, build, LIB_PATH, NvbError, Context  # noqa: F401
+from .fmindex import FMIndex, match, match_host, rank, rank4, locate, locate_host, build_index  # noqa: F401
+from .alignment import (  # noqa: F401
+    EDIT_DISTANCE, SMITH_WATERMAN, GOTOH, GLOBAL, LOCAL, SEMI_GLOBAL,
+    Aligner, EditDistanceAligner, SmithWatermanAligner, GotohAligner, StringSet,
+    batch_alignment_score, batch_banded_alignment_score,
+    batch_alignment_traceback, batch_banded_alignment_traceback,
+    batch_score_host, batch_traceback_host, ops_to_cigar, SINK_DT, ALN_DT,
+)

@@ -1,0 +1,192 @@
+"""Host-side mirror of the reference's batched alignment interface for the hot path.
+
+Aligner tag objects follow nvbio/alignment/alignment.h:365-519 (``EditDistanceAligner<TYPE>``,
+``SmithWatermanAligner<TYPE, SimpleSmithWatermanScheme>``, ``GotohAligner<TYPE, SimpleGotohScheme>``,
+schemes at nvbio/alignment/utils.h:81-124); ``batch_alignment_score`` /
+``batch_banded_alignment_score`` follow nvbio/alignment/batched.h:98-192 and the traceback calls the
+``Batched[Banded]AlignmentTraceback::enact`` contexts (batched.h:335-438). Sinks are
+``aln::BestSink<int32>`` records, alignments ``aln::Alignment<int32>`` records. All compute goes
+through the C ABI; there is no CPU implementation here.
+"""
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import lib, check, Context, AlignerC, StringSetC
+
+EDIT_DISTANCE, SMITH_WATERMAN, GOTOH = 0, 1, 2
+GLOBAL, LOCAL, SEMI_GLOBAL = 0, 1, 2
+
+SINK_DT = np.dtype([("score", "<i4"), ("x", "<u4"), ("y", "<u4")])
+ALN_DT = np.dtype([("score", "<i4"), ("src_x", "<u4"), ("src_y", "<u4"), ("sink_x", "<u4"), ("sink_y", "<u4")])
+
+
+class Aligner:
+    def __init__(self, kind, type_, match=0, mismatch=-1, gap_a=-1, gap_b=-1):
+        self.kind, self.type = int(kind), int(type_)
+        self.match, self.mismatch, self.gap_a, self.gap_b = int(match), int(mismatch), int(gap_a), int(gap_b)
+
+    def c(self):
+        return AlignerC(self.kind, self.type, self.match, self.mismatch, self.gap_a, self.gap_b)
+
+
+def EditDistanceAligner(type_):
+    """aln::EditDistanceAligner<TYPE> (alignment.h:365-393); scheme fixed to (0,-1,-1,-1) (ed_utils.h:36-43)"""
+    return Aligner(EDIT_DISTANCE, type_, 0, -1, -1, -1)
+
+
+def SmithWatermanAligner(type_, match, mismatch, deletion, insertion):
+    """aln::SmithWatermanAligner<TYPE, SimpleSmithWatermanScheme(match,mismatch,deletion,insertion)>"""
+    return Aligner(SMITH_WATERMAN, type_, match, mismatch, deletion, insertion)
+
+
+def GotohAligner(type_, match, mismatch, gap_open, gap_ext):
+    """aln::GotohAligner<TYPE, SimpleGotohScheme(match,mismatch,gap_open,gap_ext)>"""
+    return Aligner(GOTOH, type_, match, mismatch, gap_open, gap_ext)
+
+
+class StringSet:
+    """ConcatenatedStringSet (nvbio/strings/string_set.h:405-492): symbols + count+1 offsets, on a CUDA device"""
+
+    def __init__(self, symbols, offsets, bits=8, max_len=None):
+        self.symbols, self.offsets, self.bits = symbols, offsets, bits
+        self.count = offsets.numel() - 1
+        self._max_len = max_len
+
+    @classmethod
+    def from_numpy(cls, symbols, offsets, device, bits=8):
+        sym = torch.from_numpy(np.ascontiguousarray(symbols)).to(device)
+        if sym.numel() == 0:
+            sym = torch.zeros(16, dtype=torch.uint8, device=device)
+        off = torch.from_numpy(np.ascontiguousarray(offsets, dtype=np.uint32).view(np.int32)).to(device)
+        o64 = np.asarray(offsets, dtype=np.int64)
+        ml = int(np.max(np.diff(o64))) if len(o64) > 1 else 0
+        return cls(sym, off, bits, ml)
+
+    @property
+    def max_len(self):
+        if self._max_len is None:
+            o = self.offsets.to(torch.int64) & 0xFFFFFFFF
+            self._max_len = int((o[1:] - o[:-1]).max().item()) if self.count else 0
+        return self._max_len
+
+    def c(self):
+        s = StringSetC()
+        s.symbols, s.offsets = self.symbols.data_ptr(), self.offsets.data_ptr()
+        s.count, s.bits = self.count, self.bits
+        return s
+
+
+def _ctx(t, ctx):
+    if not t.is_cuda:
+        raise _lib.NvbError("nvbio_gpl_b200 has no CPU path: tensors must live on a CUDA device")
+    return ctx or Context.default(t.device.index)
+
+
+def _temp(op, aligner, band, chk, maxM, maxN, n, device, temp):
+    need = int(lib().nvb_temp_bytes(op, aligner.c(), band, chk, maxM, maxN, n))
+    if temp is None:
+        temp = torch.empty(need, dtype=torch.uint8, device=device)
+    return temp
+
+
+def batch_alignment_score(aligner, patterns, texts, sinks=None, temp=None, ctx=None):
+    """aln::batch_alignment_score(aligner, patterns, texts, sinks, scheduler, maxM, maxN) (batched.h:98-140).
+    sinks: int32 [n,3] = (score, sink.x = text end, sink.y = pattern end)"""
+    ctx = _ctx(patterns.offsets, ctx)
+    n = patterns.count
+    dev = patterns.offsets.device
+    if sinks is None:
+        sinks = torch.empty((n, 3), dtype=torch.int32, device=dev)
+    maxM, maxN = patterns.max_len, texts.max_len
+    temp = _temp(_lib.OP_SCORE, aligner, 0, 0, maxM, maxN, n, dev, temp)
+    check(lib().nvb_batch_score(ctx.h, aligner.c(), patterns.c(), texts.c(), sinks.data_ptr(), maxM, maxN,
+                                temp.data_ptr(), temp.numel(), _lib.current_stream_ptr()), ctx.h)
+    return sinks
+
+
+def batch_banded_alignment_score(aligner, band, patterns, texts, sinks=None, ctx=None):
+    """aln::batch_banded_alignment_score<BAND_LEN>(...) (batched.h:142-192)"""
+    ctx = _ctx(patterns.offsets, ctx)
+    n = patterns.count
+    dev = patterns.offsets.device
+    if sinks is None:
+        sinks = torch.empty((n, 3), dtype=torch.int32, device=dev)
+    check(lib().nvb_batch_banded_score(ctx.h, aligner.c(), band, patterns.c(), texts.c(), sinks.data_ptr(),
+                                       patterns.max_len, texts.max_len, None, 0, _lib.current_stream_ptr()), ctx.h)
+    return sinks
+
+
+def batch_alignment_traceback(aligner, checkpoints, patterns, texts, ops_stride=None, temp=None, ctx=None):
+    """BatchedAlignmentTraceback<CHECKPOINTS,...>::enact (batched.h:335-380).
+    Returns (alignments int32 [n,5], ops uint8 [n,ops_stride] in push order, n_ops int32 [n])"""
+    ctx = _ctx(patterns.offsets, ctx)
+    n = patterns.count
+    dev = patterns.offsets.device
+    maxM, maxN = patterns.max_len, texts.max_len
+    if ops_stride is None:
+        ops_stride = maxM + maxN + 8
+    out = torch.empty((n, 5), dtype=torch.int32, device=dev)
+    ops = torch.zeros((n, ops_stride), dtype=torch.uint8, device=dev)
+    n_ops = torch.empty(n, dtype=torch.int32, device=dev)
+    temp = _temp(_lib.OP_TRACEBACK, aligner, 0, checkpoints, maxM, maxN, n, dev, temp)
+    check(lib().nvb_batch_traceback(ctx.h, aligner.c(), checkpoints, patterns.c(), texts.c(), out.data_ptr(), ops.data_ptr(),
+                                    ops_stride, n_ops.data_ptr(), maxM, maxN, temp.data_ptr(), temp.numel(),
+                                    _lib.current_stream_ptr()), ctx.h)
+    return out, ops, n_ops
+
+
+def batch_banded_alignment_traceback(aligner, band, checkpoints, patterns, texts, ops_stride=None, temp=None, ctx=None):
+    """BatchedBandedAlignmentTraceback<BAND_LEN,CHECKPOINTS,...>::enact (batched.h:382-438)"""
+    ctx = _ctx(patterns.offsets, ctx)
+    n = patterns.count
+    dev = patterns.offsets.device
+    maxM, maxN = patterns.max_len, texts.max_len
+    if ops_stride is None:
+        ops_stride = 2 * maxM + band + 8
+    out = torch.empty((n, 5), dtype=torch.int32, device=dev)
+    ops = torch.zeros((n, ops_stride), dtype=torch.uint8, device=dev)
+    n_ops = torch.empty(n, dtype=torch.int32, device=dev)
+    temp = _temp(_lib.OP_BANDED_TRACEBACK, aligner, band, checkpoints, maxM, maxN, n, dev, temp)
+    check(lib().nvb_batch_banded_traceback(ctx.h, aligner.c(), band, checkpoints, patterns.c(), texts.c(), out.data_ptr(),
+                                           ops.data_ptr(), ops_stride, n_ops.data_ptr(), maxM, maxN, temp.data_ptr(),
+                                           temp.numel(), _lib.current_stream_ptr()), ctx.h)
+    return out, ops, n_ops
+
+
+def ops_to_cigar(ops, n_ops, cigar_stride=None, ctx=None):
+    """push-order ops -> forward run-length io::Cigar words (nvbio/io/alignments.h:48-65)"""
+    ctx = _ctx(ops, ctx)
+    n, stride = ops.shape
+    if cigar_stride is None:
+        cigar_stride = stride
+    cigar = torch.zeros((n, cigar_stride), dtype=torch.int16, device=ops.device)
+    n_cigar = torch.empty(n, dtype=torch.int32, device=ops.device)
+    check(lib().nvb_ops_to_cigar(ctx.h, ops.data_ptr(), stride, n_ops.data_ptr(), n, cigar.data_ptr(), cigar_stride,
+                                 n_cigar.data_ptr(), _lib.current_stream_ptr()), ctx.h)
+    return cigar, n_cigar
+
+
+# host-buffer forms --------------------------------------------------------------------------------
+def batch_score_host(aligner, band, pat, pat_off, txt, txt_off, sinks_h=None, device=0, ctx=None):
+    ctx = ctx or Context.default(device)
+    n = len(pat_off) - 1
+    if sinks_h is None:
+        sinks_h = np.empty(n, dtype=SINK_DT)
+    check(lib().nvb_batch_score_host(ctx.h, aligner.c(), band, pat.ctypes.data, pat_off.ctypes.data, txt.ctypes.data,
+                                     txt_off.ctypes.data, n, sinks_h.ctypes.data), ctx.h)
+    return sinks_h
+
+
+def batch_traceback_host(aligner, band, checkpoints, pat, pat_off, txt, txt_off, ops_stride, device=0, ctx=None):
+    ctx = ctx or Context.default(device)
+    n = len(pat_off) - 1
+    out = np.empty(n, dtype=ALN_DT)
+    ops = np.zeros((n, ops_stride), dtype=np.uint8)
+    n_ops = np.empty(n, dtype=np.uint32)
+    check(lib().nvb_batch_traceback_host(ctx.h, aligner.c(), band, checkpoints, pat.ctypes.data, pat_off.ctypes.data,
+                                         txt.ctypes.data, txt_off.ctypes.data, n, out.ctypes.data, ops.ctypes.data,
+                                         ops_stride, n_ops.ctypes.data), ctx.h)
+    return out, ops, n_ops

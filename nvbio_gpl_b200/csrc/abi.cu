@@ -1,0 +1,282 @@
+// abi.cu -- context, index image management and the host-buffer (*_host) entry points.
+#include "common.cuh"
+#include <stdlib.h>
+#include <string.h>
+#include <new>
+
+extern "C" int nvb_version(void) { return NVB_VERSION; }
+
+extern "C" const char* nvb_status_string(int status)
+{
+    switch (status)
+    {
+    case NVB_OK:              return "ok";
+    case NVB_ERR_ARG:         return "invalid argument";
+    case NVB_ERR_CUDA:        return "CUDA error (no CPU fallback exists)";
+    case NVB_ERR_TEMP:        return "temp buffer too small";
+    case NVB_ERR_UNSUPPORTED: return "combination outside the contract";
+    default:                  return "unknown status";
+    }
+}
+
+extern "C" int nvb_ctx_create(int device, nvb_ctx** out)
+{
+    if (!out) return NVB_ERR_ARG;
+    *out = nullptr;
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || device < 0 || device >= n) { cudaGetLastError(); return NVB_ERR_CUDA; }
+    if (cudaSetDevice(device) != cudaSuccess) return NVB_ERR_CUDA;
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return NVB_ERR_CUDA;
+    if (prop.major < 10) return NVB_ERR_UNSUPPORTED;   // sm_100a cubins only
+    nvb_ctx* c = new (std::nothrow) nvb_ctx();
+    if (!c) return NVB_ERR_ARG;
+    memset(c, 0, sizeof(*c));
+    c->device = device;
+    c->sm_count = prop.multiProcessorCount;
+    if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return NVB_ERR_CUDA; }
+    *out = c;
+    return NVB_OK;
+}
+
+extern "C" void nvb_ctx_destroy(nvb_ctx* c)
+{
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    for (int i = 0; i < 8; ++i) if (c->d_stage[i]) cudaFree(c->d_stage[i]);
+    if (c->d_worklist) cudaFree(c->d_worklist);
+    cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+extern "C" void* nvb_ctx_stream(nvb_ctx* c) { return c ? (void*)c->stream : nullptr; }
+extern "C" int nvb_ctx_synchronize(nvb_ctx* c)
+{
+    if (!c) return NVB_ERR_ARG;
+    NVB_CUDA(c, cudaStreamSynchronize(c->stream));
+    return NVB_OK;
+}
+extern "C" const char* nvb_last_cuda_error(nvb_ctx* c) { return c ? cudaGetErrorString(c->last_err) : "no context"; }
+extern "C" uint64_t nvb_ctx_launch_count(nvb_ctx* c) { return c ? c->launches : 0; }
+extern "C" uint32_t nvb_last_paths(nvb_ctx* c) { return c ? c->last_paths : 0; }
+extern "C" void nvb_force_generic(nvb_ctx* c, int on) { if (c) c->force_generic = on; }
+
+extern "C" int nvb_host_alloc(size_t bytes, void** p)
+{
+    if (!p) return NVB_ERR_ARG;
+    return cudaHostAlloc(p, bytes ? bytes : 1, cudaHostAllocDefault) == cudaSuccess ? NVB_OK : NVB_ERR_CUDA;
+}
+extern "C" void nvb_host_free(void* p) { if (p) cudaFreeHost(p); }
+
+int nvb_stage(nvb_ctx* ctx, int slot, size_t bytes, void** out)
+{
+    if (bytes == 0) bytes = 256;
+    if (ctx->d_stage_bytes[slot] < bytes)
+    {
+        if (ctx->d_stage[slot]) { NVB_CUDA(ctx, cudaStreamSynchronize(ctx->stream)); NVB_CUDA(ctx, cudaFree(ctx->d_stage[slot])); }
+        ctx->d_stage[slot] = nullptr; ctx->d_stage_bytes[slot] = 0;
+        const size_t cap = bytes + bytes / 4 + 4096;
+        NVB_CUDA(ctx, cudaMalloc(&ctx->d_stage[slot], cap));
+        ctx->d_stage_bytes[slot] = cap;
+    }
+    *out = ctx->d_stage[slot];
+    return NVB_OK;
+}
+
+int nvb_worklist(nvb_ctx* ctx, size_t entries, uint32_t** out)
+{
+    if (ctx->d_worklist_cap < entries + 4)
+    {
+        if (ctx->d_worklist) { NVB_CUDA(ctx, cudaDeviceSynchronize()); NVB_CUDA(ctx, cudaFree(ctx->d_worklist)); }
+        ctx->d_worklist = nullptr; ctx->d_worklist_cap = 0;
+        NVB_CUDA(ctx, cudaMalloc(&ctx->d_worklist, sizeof(uint32_t) * (entries + 4)));
+        ctx->d_worklist_cap = entries + 4;
+    }
+    *out = ctx->d_worklist;
+    return NVB_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// index image
+// ---------------------------------------------------------------------------------------------
+extern "C" int nvb_fmindex_upload(nvb_ctx* ctx, const nvb_fmindex* h, nvb_fmindex* d)
+{
+    if (!ctx || !h || !d || !h->bwt_occ) return NVB_ERR_ARG;
+    if (h->occ_int != 64u || h->sa_int != 16u) return NVB_ERR_UNSUPPORTED;
+    *d = *h; d->bwt_occ = nullptr; d->ssa = nullptr;
+    const size_t bw = nvb_bwt_occ_words(h->length) * sizeof(uint32_t);
+    void* p = nullptr;
+    NVB_CUDA(ctx, cudaMalloc(&p, bw ? bw : 32));
+    NVB_CUDA(ctx, cudaMemcpyAsync(p, h->bwt_occ, bw, cudaMemcpyHostToDevice, ctx->stream));
+    d->bwt_occ = p;
+    if (h->ssa)
+    {
+        const size_t sw = nvb_ssa_words(h->length) * sizeof(uint32_t);
+        void* s = nullptr;
+        NVB_CUDA(ctx, cudaMalloc(&s, sw));
+        NVB_CUDA(ctx, cudaMemcpyAsync(s, h->ssa, sw, cudaMemcpyHostToDevice, ctx->stream));
+        d->ssa = (const uint32_t*)s;
+    }
+    NVB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return NVB_OK;
+}
+
+extern "C" int nvb_fmindex_release(nvb_ctx* ctx, nvb_fmindex* d)
+{
+    if (!ctx || !d) return NVB_ERR_ARG;
+    if (d->bwt_occ) NVB_CUDA(ctx, cudaFree((void*)d->bwt_occ));
+    if (d->ssa) NVB_CUDA(ctx, cudaFree((void*)d->ssa));
+    d->bwt_occ = nullptr; d->ssa = nullptr;
+    return NVB_OK;
+}
+
+extern "C" int nvb_fmindex_pin_l2(nvb_ctx* ctx, const nvb_fmindex* d, size_t bytes)
+{
+    if (!ctx || !d || !d->bwt_occ) return NVB_ERR_ARG;
+    cudaDeviceProp prop;
+    NVB_CUDA(ctx, cudaGetDeviceProperties(&prop, ctx->device));
+    cudaStreamAttrValue attr;
+    memset(&attr, 0, sizeof(attr));
+    if (bytes)
+    {
+        size_t win = bytes;
+        if ((size_t)prop.accessPolicyMaxWindowSize < win) win = (size_t)prop.accessPolicyMaxWindowSize;
+        size_t carve = win;
+        if ((size_t)prop.persistingL2CacheMaxSize < carve) carve = (size_t)prop.persistingL2CacheMaxSize;
+        NVB_CUDA(ctx, cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, carve));
+        attr.accessPolicyWindow.base_ptr  = (void*)d->bwt_occ;
+        attr.accessPolicyWindow.num_bytes = win;
+        attr.accessPolicyWindow.hitRatio  = win ? (float)((double)carve / (double)win) : 0.f;
+        attr.accessPolicyWindow.hitProp   = cudaAccessPropertyPersisting;
+        attr.accessPolicyWindow.missProp  = cudaAccessPropertyStreaming;
+    }
+    else
+    {
+        attr.accessPolicyWindow.num_bytes = 0;
+        attr.accessPolicyWindow.hitProp   = cudaAccessPropertyNormal;
+        attr.accessPolicyWindow.missProp  = cudaAccessPropertyNormal;
+    }
+    NVB_CUDA(ctx, cudaStreamSetAttribute(ctx->stream, cudaStreamAttributeAccessPolicyWindow, &attr));
+    if (!bytes) NVB_CUDA(ctx, cudaCtxResetPersistingL2Cache());
+    return NVB_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// host-buffer forms
+// ---------------------------------------------------------------------------------------------
+extern "C" int nvb_fm_match_host(nvb_ctx* ctx, const nvb_fmindex* fmi_d, const uint8_t* symbols_h,
+                                 const uint32_t* offsets_h, uint32_t count, uint32_t* ranges_h)
+{
+    if (!ctx || !fmi_d) return NVB_ERR_ARG;
+    if (count == 0) return NVB_OK;
+    if (!symbols_h || !offsets_h || !ranges_h) return NVB_ERR_ARG;
+    NVB_CUDA(ctx, cudaSetDevice(ctx->device));
+    const size_t n_sym = offsets_h[count];
+    void *d_sym, *d_off, *d_rng;
+    int rc;
+    if ((rc = nvb_stage(ctx, 0, n_sym + 32, &d_sym))) return rc;
+    if ((rc = nvb_stage(ctx, 1, sizeof(uint32_t) * ((size_t)count + 1), &d_off))) return rc;
+    if ((rc = nvb_stage(ctx, 2, sizeof(uint32_t) * 2 * (size_t)count, &d_rng))) return rc;
+    NVB_CUDA(ctx, cudaMemcpyAsync(d_sym, symbols_h, n_sym, cudaMemcpyHostToDevice, ctx->stream));
+    NVB_CUDA(ctx, cudaMemcpyAsync(d_off, offsets_h, sizeof(uint32_t) * ((size_t)count + 1), cudaMemcpyHostToDevice, ctx->stream));
+    nvb_string_set q; q.symbols = d_sym; q.offsets = (const uint32_t*)d_off; q.count = count; q.bits = 8;
+    if ((rc = nvb_fm_match(ctx, fmi_d, q, (uint32_t*)d_rng, ctx->stream))) return rc;
+    NVB_CUDA(ctx, cudaMemcpyAsync(ranges_h, d_rng, sizeof(uint32_t) * 2 * (size_t)count, cudaMemcpyDeviceToHost, ctx->stream));
+    NVB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return NVB_OK;
+}
+
+extern "C" int nvb_fm_locate_host(nvb_ctx* ctx, const nvb_fmindex* fmi_d, const uint32_t* rows_h, uint32_t n, uint32_t* pos_h)
+{
+    if (!ctx || !fmi_d) return NVB_ERR_ARG;
+    if (n == 0) return NVB_OK;
+    if (!rows_h || !pos_h) return NVB_ERR_ARG;
+    NVB_CUDA(ctx, cudaSetDevice(ctx->device));
+    void *d_rows, *d_pos; int rc;
+    if ((rc = nvb_stage(ctx, 0, sizeof(uint32_t) * (size_t)n, &d_rows))) return rc;
+    if ((rc = nvb_stage(ctx, 1, sizeof(uint32_t) * (size_t)n, &d_pos))) return rc;
+    NVB_CUDA(ctx, cudaMemcpyAsync(d_rows, rows_h, sizeof(uint32_t) * (size_t)n, cudaMemcpyHostToDevice, ctx->stream));
+    if ((rc = nvb_fm_locate(ctx, fmi_d, (const uint32_t*)d_rows, n, (uint32_t*)d_pos, ctx->stream))) return rc;
+    NVB_CUDA(ctx, cudaMemcpyAsync(pos_h, d_pos, sizeof(uint32_t) * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
+    NVB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return NVB_OK;
+}
+
+static uint32_t max_len(const uint32_t* off, uint32_t n)
+{
+    uint32_t m = 0;
+    for (uint32_t i = 0; i < n; ++i) { const uint32_t l = off[i + 1] - off[i]; if (l > m) m = l; }
+    return m;
+}
+
+extern "C" int nvb_batch_score_host(nvb_ctx* ctx, nvb_aligner aligner, uint32_t band,
+                                    const uint8_t* pat_h, const uint32_t* pat_off_h, const uint8_t* txt_h,
+                                    const uint32_t* txt_off_h, uint32_t n, nvb_best_sink* sinks_h)
+{
+    if (!ctx) return NVB_ERR_ARG;
+    if (n == 0) return NVB_OK;
+    if (!pat_h || !pat_off_h || !txt_h || !txt_off_h || !sinks_h) return NVB_ERR_ARG;
+    NVB_CUDA(ctx, cudaSetDevice(ctx->device));
+    const size_t np = pat_off_h[n], nt = txt_off_h[n];
+    const uint32_t maxM = max_len(pat_off_h, n), maxN = max_len(txt_off_h, n);
+    const size_t tb = nvb_temp_bytes(band ? NVB_OP_BANDED_SCORE : NVB_OP_SCORE, aligner, band, 0, maxM, maxN, n);
+    void *d_p, *d_po, *d_t, *d_to, *d_s, *d_tmp; int rc;
+    const size_t ob = sizeof(uint32_t) * ((size_t)n + 1);
+    if ((rc = nvb_stage(ctx, 0, np + 32, &d_p))) return rc;
+    if ((rc = nvb_stage(ctx, 1, ob, &d_po))) return rc;
+    if ((rc = nvb_stage(ctx, 2, nt + 32, &d_t))) return rc;
+    if ((rc = nvb_stage(ctx, 3, ob, &d_to))) return rc;
+    if ((rc = nvb_stage(ctx, 4, sizeof(nvb_best_sink) * (size_t)n, &d_s))) return rc;
+    if ((rc = nvb_stage(ctx, 5, tb, &d_tmp))) return rc;
+    NVB_CUDA(ctx, cudaMemcpyAsync(d_p, pat_h, np, cudaMemcpyHostToDevice, ctx->stream));
+    NVB_CUDA(ctx, cudaMemcpyAsync(d_po, pat_off_h, ob, cudaMemcpyHostToDevice, ctx->stream));
+    NVB_CUDA(ctx, cudaMemcpyAsync(d_t, txt_h, nt, cudaMemcpyHostToDevice, ctx->stream));
+    NVB_CUDA(ctx, cudaMemcpyAsync(d_to, txt_off_h, ob, cudaMemcpyHostToDevice, ctx->stream));
+    nvb_string_set P = { d_p, (const uint32_t*)d_po, n, 8 }, T = { d_t, (const uint32_t*)d_to, n, 8 };
+    if (band) rc = nvb_batch_banded_score(ctx, aligner, band, P, T, (nvb_best_sink*)d_s, maxM, maxN, d_tmp, tb, ctx->stream);
+    else      rc = nvb_batch_score(ctx, aligner, P, T, (nvb_best_sink*)d_s, maxM, maxN, d_tmp, tb, ctx->stream);
+    if (rc) return rc;
+    NVB_CUDA(ctx, cudaMemcpyAsync(sinks_h, d_s, sizeof(nvb_best_sink) * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
+    NVB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return NVB_OK;
+}
+
+extern "C" int nvb_batch_traceback_host(nvb_ctx* ctx, nvb_aligner aligner, uint32_t band, uint32_t checkpoints,
+                                        const uint8_t* pat_h, const uint32_t* pat_off_h, const uint8_t* txt_h,
+                                        const uint32_t* txt_off_h, uint32_t n, nvb_alignment* out_h,
+                                        uint8_t* ops_h, uint32_t ops_stride, uint32_t* n_ops_h)
+{
+    if (!ctx) return NVB_ERR_ARG;
+    if (n == 0) return NVB_OK;
+    if (!pat_h || !pat_off_h || !txt_h || !txt_off_h || !out_h || !ops_h || !n_ops_h) return NVB_ERR_ARG;
+    NVB_CUDA(ctx, cudaSetDevice(ctx->device));
+    const size_t np = pat_off_h[n], nt = txt_off_h[n];
+    const uint32_t maxM = max_len(pat_off_h, n), maxN = max_len(txt_off_h, n);
+    const size_t tb = nvb_temp_bytes(band ? NVB_OP_BANDED_TRACEBACK : NVB_OP_TRACEBACK, aligner, band, checkpoints, maxM, maxN, n);
+    void *d_p, *d_po, *d_t, *d_to, *d_o, *d_tmp, *d_ops, *d_nops; int rc;
+    const size_t ob = sizeof(uint32_t) * ((size_t)n + 1);
+    if ((rc = nvb_stage(ctx, 0, np + 32, &d_p))) return rc;
+    if ((rc = nvb_stage(ctx, 1, ob, &d_po))) return rc;
+    if ((rc = nvb_stage(ctx, 2, nt + 32, &d_t))) return rc;
+    if ((rc = nvb_stage(ctx, 3, ob, &d_to))) return rc;
+    if ((rc = nvb_stage(ctx, 4, sizeof(nvb_alignment) * (size_t)n, &d_o))) return rc;
+    if ((rc = nvb_stage(ctx, 5, tb, &d_tmp))) return rc;
+    if ((rc = nvb_stage(ctx, 6, (size_t)ops_stride * n, &d_ops))) return rc;
+    if ((rc = nvb_stage(ctx, 7, sizeof(uint32_t) * (size_t)n, &d_nops))) return rc;
+    NVB_CUDA(ctx, cudaMemcpyAsync(d_p, pat_h, np, cudaMemcpyHostToDevice, ctx->stream));
+    NVB_CUDA(ctx, cudaMemcpyAsync(d_po, pat_off_h, ob, cudaMemcpyHostToDevice, ctx->stream));
+    NVB_CUDA(ctx, cudaMemcpyAsync(d_t, txt_h, nt, cudaMemcpyHostToDevice, ctx->stream));
+    NVB_CUDA(ctx, cudaMemcpyAsync(d_to, txt_off_h, ob, cudaMemcpyHostToDevice, ctx->stream));
+    nvb_string_set P = { d_p, (const uint32_t*)d_po, n, 8 }, T = { d_t, (const uint32_t*)d_to, n, 8 };
+    if (band) rc = nvb_batch_banded_traceback(ctx, aligner, band, checkpoints, P, T, (nvb_alignment*)d_o, (uint8_t*)d_ops,
+                                              ops_stride, (uint32_t*)d_nops, maxM, maxN, d_tmp, tb, ctx->stream);
+    else      rc = nvb_batch_traceback(ctx, aligner, checkpoints, P, T, (nvb_alignment*)d_o, (uint8_t*)d_ops,
+                                       ops_stride, (uint32_t*)d_nops, maxM, maxN, d_tmp, tb, ctx->stream);
+    if (rc) return rc;
+    NVB_CUDA(ctx, cudaMemcpyAsync(out_h, d_o, sizeof(nvb_alignment) * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
+    NVB_CUDA(ctx, cudaMemcpyAsync(ops_h, d_ops, (size_t)ops_stride * n, cudaMemcpyDeviceToHost, ctx->stream));
+    NVB_CUDA(ctx, cudaMemcpyAsync(n_ops_h, d_nops, sizeof(uint32_t) * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
+    NVB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return NVB_OK;
+}

@@ -1,0 +1,93 @@
+// common.cuh -- shared declarations of libnvbio_b200 (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stddef.h>
+#include "../../include/nvbio_b200.h"
+
+#if defined(__CUDA_ARCH__) && (__CUDA_ARCH__ < 1000)
+#error "libnvbio_b200 is written for sm_100a (B200) only"
+#endif
+
+#define NVB_SM_COUNT 148
+
+struct nvb_ctx
+{
+    int          device;
+    cudaStream_t stream;
+    cudaError_t  last_err;
+    uint64_t     launches;
+    uint32_t     last_paths;
+    int          force_generic;
+    // grow-only device/pinned staging owned by the *_host entry points
+    void*        d_stage[8];
+    size_t       d_stage_bytes[8];
+    // dirty-pair worklist of the packed DP kernels: [0] = count, [1..] = pair ids
+    uint32_t*    d_worklist;
+    size_t       d_worklist_cap;
+    int          sm_count;
+};
+
+#define NVB_CUDA(ctx, call)                                                 \
+    do { cudaError_t e_ = (call);                                           \
+         if (e_ != cudaSuccess) { if (ctx) (ctx)->last_err = e_; return NVB_ERR_CUDA; } } while (0)
+
+#define NVB_LAUNCHED(ctx)                                                   \
+    do { (ctx)->launches++;                                                 \
+         cudaError_t e_ = cudaPeekAtLastError();                            \
+         if (e_ != cudaSuccess) { (ctx)->last_err = cudaGetLastError(); return NVB_ERR_CUDA; } } while (0)
+
+int   nvb_stage(nvb_ctx* ctx, int slot, size_t bytes, void** out);
+int   nvb_worklist(nvb_ctx* ctx, size_t entries, uint32_t** out);
+
+// ---------------------------------------------------------------------------------------------
+// device-side view of the fused nvBWT index
+// ---------------------------------------------------------------------------------------------
+struct FMView
+{
+    uint32_t        length, primary;
+    uint32_t        L2[5];
+    const uint4*    blk;      // 2 uint4 per 64 symbols: words, counters
+    const uint32_t* ssa;
+};
+
+static inline FMView make_view(const nvb_fmindex* f)
+{
+    FMView v;
+    v.length = f->length; v.primary = f->primary;
+    for (int i = 0; i < 5; ++i) v.L2[i] = f->L2[i];
+    v.blk = (const uint4*)f->bwt_occ; v.ssa = f->ssa;
+    return v;
+}
+
+// string-set view passed by value to kernels
+struct StrSet
+{
+    const uint8_t*  sym;
+    const uint32_t* off;
+    uint32_t        count;
+    uint32_t        bits;
+};
+static inline StrSet make_set(nvb_string_set s)
+{
+    StrSet r; r.sym = (const uint8_t*)s.symbols; r.off = s.offsets; r.count = s.count; r.bits = s.bits;
+    return r;
+}
+
+#ifdef __CUDACC__
+// symbol i of a string set's symbol stream (absolute symbol index)
+template <int BITS>
+__device__ __forceinline__ uint32_t sym_at(const uint8_t* base, uint32_t i)
+{
+    if (BITS == 8) return base[i];
+    const uint32_t* w = (const uint32_t*)base;
+    if (BITS == 4) return (__ldg(w + (i >> 3)) >> (28u - 4u * (i & 7u))) & 15u;
+    return (__ldg(w + (i >> 4)) >> (30u - 2u * (i & 15u))) & 3u;
+}
+__device__ __forceinline__ uint32_t sym_at_rt(const uint8_t* base, uint32_t bits, uint32_t i)
+{
+    if (bits == 8) return base[i];
+    if (bits == 4) return sym_at<4>(base, i);
+    return sym_at<2>(base, i);
+}
+#endif

@@ -1,0 +1,239 @@
+// dp_api.cu -- C-ABI entry points of the alignment half: argument checks, scratch carving, choice
+// between the packed DPX kernels (dp_fast_*.cu) and the int32 generic kernels, CIGAR packing.
+#include "dp_launch.h"
+#include "dp_fast.h"
+
+static int check_aligner(const nvb_aligner& a)
+{
+    if (a.kind < NVB_EDIT_DISTANCE || a.kind > NVB_GOTOH) return NVB_ERR_ARG;
+    if (a.type < NVB_GLOBAL || a.type > NVB_SEMI_GLOBAL) return NVB_ERR_ARG;
+    return NVB_OK;
+}
+static int check_sets(const nvb_string_set& P, const nvb_string_set& T)
+{
+    if (P.count != T.count) return NVB_ERR_ARG;
+    if (P.count == 0) return NVB_OK;
+    if (!P.symbols || !P.offsets || !T.symbols || !T.offsets) return NVB_ERR_ARG;
+    if (!(P.bits == 8 || P.bits == 4 || P.bits == 2) || !(T.bits == 8 || T.bits == 4 || T.bits == 2)) return NVB_ERR_ARG;
+    return NVB_OK;
+}
+
+struct TempPlan { size_t i16_per_pair, flow_per_pair; };
+
+static TempPlan plan(int op, const nvb_aligner& a, uint32_t band, uint32_t chk, uint32_t maxM, uint32_t maxN)
+{
+    TempPlan p = { 0, 0 };
+    const bool g = a.kind == NVB_GOTOH;
+    switch (op)
+    {
+    case NVB_OP_SCORE:           p.i16_per_pair = (size_t)maxN * (g ? 2 : 1); break;
+    case NVB_OP_BANDED_SCORE:    break;
+    case NVB_OP_TRACEBACK:
+    {
+        const size_t nchk = chk ? (maxM + chk - 1) / chk + 1 : 1;
+        p.i16_per_pair = 2 * (size_t)maxN + 2 * nchk * maxN;
+        p.flow_per_pair = (size_t)maxN * chk;
+        break;
+    }
+    case NVB_OP_BANDED_TRACEBACK:
+    {
+        const size_t nrows = chk ? 2 + (maxM + chk - 1) / chk : 2;
+        p.i16_per_pair = 2 * nrows * band;
+        p.flow_per_pair = (size_t)band * chk;
+        break;
+    }
+    }
+    return p;
+}
+
+extern "C" size_t nvb_temp_bytes(int op, nvb_aligner a, uint32_t band, uint32_t chk, uint32_t maxM, uint32_t maxN, uint32_t n)
+{
+    const TempPlan p = plan(op, a, band, chk, maxM, maxN);
+    const size_t n128 = ((size_t)n + 127) & ~(size_t)127;
+    return (p.i16_per_pair * 2 + p.flow_per_pair) * n128 + 256;
+}
+
+// pairs per launch that fit the scratch (multiple of 128 unless everything fits)
+static uint32_t batch_pairs(const TempPlan& p, size_t temp_bytes, uint32_t n)
+{
+    const size_t per = p.i16_per_pair * 2 + p.flow_per_pair;
+    if (per == 0) return n;
+    if (temp_bytes < 256) return 0;
+    size_t fit = (temp_bytes - 256) / per;
+    if (fit >= n) return n;
+    fit &= ~(size_t)127;
+    return (uint32_t)fit;
+}
+
+extern "C" int nvb_batch_score(nvb_ctx* ctx, nvb_aligner a, nvb_string_set patterns, nvb_string_set texts,
+                               nvb_best_sink* sinks, uint32_t maxM, uint32_t maxN, void* temp, size_t temp_bytes, void* stream)
+{
+    if (!ctx) return NVB_ERR_ARG;
+    int rc;
+    if ((rc = check_aligner(a)) || (rc = check_sets(patterns, texts))) return rc;
+    const uint32_t n = patterns.count;
+    if (n == 0) return NVB_OK;
+    if (!sinks) return NVB_ERR_ARG;
+    cudaStream_t s = (cudaStream_t)stream;
+    const StrSet P = make_set(patterns), T = make_set(texts);
+    const TempPlan p = plan(NVB_OP_SCORE, a, 0, 0, maxM, maxN);
+    ctx->last_paths = 0;
+
+    if (!ctx->force_generic && dpf_full_score_supported(a, P, T, maxM, maxN))
+    {
+        // packed DPX kernel; pairs it cannot represent exactly are appended to the ctx worklist and
+        // re-scored by the int32 kernel, which reads the count on the device (no host sync)
+        uint32_t* wl = nullptr;
+        if ((rc = nvb_worklist(ctx, n, &wl))) return rc;
+        NVB_CUDA(ctx, cudaMemsetAsync(wl, 0, sizeof(uint32_t), s));
+        if ((rc = dpf_full_score(ctx, a, P, T, sinks, maxM, maxN, wl, s))) return rc;
+        ctx->last_paths |= 1u;
+        if (!temp && p.i16_per_pair) return NVB_ERR_TEMP;
+        uint32_t n_dirty = n;
+        if (batch_pairs(p, temp_bytes, n) < n)
+        {
+            // scratch smaller than n columns: read the count back and batch
+            NVB_CUDA(ctx, cudaMemcpyAsync(&n_dirty, wl, sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+            NVB_CUDA(ctx, cudaStreamSynchronize(s));
+            if (n_dirty == 0) return NVB_OK;
+        }
+        const uint32_t bp = batch_pairs(p, temp_bytes, n_dirty);
+        if (bp == 0) return NVB_ERR_TEMP;
+        for (uint32_t first = 0; first < n_dirty; first += bp)
+        {
+            const uint32_t cnt = n_dirty - first < bp ? n_dirty - first : bp;
+            if ((rc = dpg_full_score(ctx, a, P, T, wl + 1, wl, first, cnt, sinks, (int16_t*)temp, maxN, s))) return rc;
+        }
+        return NVB_OK;
+    }
+    ctx->last_paths |= 2u;
+    if (!temp && p.i16_per_pair) return NVB_ERR_TEMP;
+    const uint32_t bp = batch_pairs(p, temp_bytes, n);
+    if (bp == 0) return NVB_ERR_TEMP;
+    for (uint32_t first = 0; first < n; first += bp)
+    {
+        const uint32_t cnt = n - first < bp ? n - first : bp;
+        if ((rc = dpg_full_score(ctx, a, P, T, nullptr, nullptr, first, cnt, sinks, (int16_t*)temp, maxN, s))) return rc;
+    }
+    return NVB_OK;
+}
+
+extern "C" int nvb_batch_banded_score(nvb_ctx* ctx, nvb_aligner a, uint32_t band, nvb_string_set patterns,
+                                      nvb_string_set texts, nvb_best_sink* sinks, uint32_t maxM, uint32_t maxN,
+                                      void* temp, size_t temp_bytes, void* stream)
+{
+    (void)temp; (void)temp_bytes;
+    if (!ctx) return NVB_ERR_ARG;
+    int rc;
+    if ((rc = check_aligner(a)) || (rc = check_sets(patterns, texts))) return rc;
+    if (band < 2 || band > NVB_MAX_BAND_LEN) return NVB_ERR_UNSUPPORTED;
+    const uint32_t n = patterns.count;
+    if (n == 0) return NVB_OK;
+    if (!sinks) return NVB_ERR_ARG;
+    cudaStream_t s = (cudaStream_t)stream;
+    const StrSet P = make_set(patterns), T = make_set(texts);
+    ctx->last_paths = 0;
+    if (!ctx->force_generic && dpf_banded_score_supported(a, band, P, T, maxM, maxN))
+    {
+        uint32_t* wl = nullptr;
+        if ((rc = nvb_worklist(ctx, n, &wl))) return rc;
+        NVB_CUDA(ctx, cudaMemsetAsync(wl, 0, sizeof(uint32_t), s));
+        if ((rc = dpf_banded_score(ctx, a, band, P, T, sinks, maxM, maxN, wl, s))) return rc;
+        ctx->last_paths |= 1u;
+        return dpg_banded_score(ctx, a, band, P, T, wl + 1, wl, 0, n, sinks, s);
+    }
+    ctx->last_paths |= 2u;
+    return dpg_banded_score(ctx, a, band, P, T, nullptr, nullptr, 0, n, sinks, s);
+}
+
+extern "C" int nvb_batch_traceback(nvb_ctx* ctx, nvb_aligner a, uint32_t chk, nvb_string_set patterns,
+                                   nvb_string_set texts, nvb_alignment* out, uint8_t* ops, uint32_t ops_stride,
+                                   uint32_t* n_ops, uint32_t maxM, uint32_t maxN, void* temp, size_t temp_bytes, void* stream)
+{
+    if (!ctx) return NVB_ERR_ARG;
+    int rc;
+    if ((rc = check_aligner(a)) || (rc = check_sets(patterns, texts))) return rc;
+    if (chk == 0 || (chk & 15u)) return NVB_ERR_UNSUPPORTED;   // stripes of 16/8 must tile a checkpoint window
+    const uint32_t n = patterns.count;
+    if (n == 0) return NVB_OK;
+    if (!out || !ops || !n_ops || !temp) return NVB_ERR_ARG;
+    cudaStream_t s = (cudaStream_t)stream;
+    const StrSet P = make_set(patterns), T = make_set(texts);
+    const TempPlan p = plan(NVB_OP_TRACEBACK, a, 0, chk, maxM, maxN);
+    const uint32_t bp = batch_pairs(p, temp_bytes, n);
+    if (bp == 0) return NVB_ERR_TEMP;
+    ctx->last_paths = 2u;
+    const uint32_t bp128 = (bp + 127u) & ~127u;
+    for (uint32_t first = 0; first < n; first += bp)
+    {
+        const uint32_t cnt = n - first < bp ? n - first : bp;
+        int16_t* t16 = (int16_t*)temp;
+        uint8_t* flow = (uint8_t*)temp + p.i16_per_pair * 2 * (size_t)bp128;
+        if ((rc = dpg_full_traceback(ctx, a, P, T, first, cnt, chk, out, ops, ops_stride, n_ops, t16, flow, maxM, maxN, s))) return rc;
+    }
+    return NVB_OK;
+}
+
+extern "C" int nvb_batch_banded_traceback(nvb_ctx* ctx, nvb_aligner a, uint32_t band, uint32_t chk,
+                                          nvb_string_set patterns, nvb_string_set texts, nvb_alignment* out,
+                                          uint8_t* ops, uint32_t ops_stride, uint32_t* n_ops, uint32_t maxM,
+                                          uint32_t maxN, void* temp, size_t temp_bytes, void* stream)
+{
+    (void)maxN;
+    if (!ctx) return NVB_ERR_ARG;
+    int rc;
+    if ((rc = check_aligner(a)) || (rc = check_sets(patterns, texts))) return rc;
+    if (band < 2 || band > NVB_MAX_BAND_LEN || chk == 0) return NVB_ERR_UNSUPPORTED;
+    const uint32_t n = patterns.count;
+    if (n == 0) return NVB_OK;
+    if (!out || !ops || !n_ops || !temp) return NVB_ERR_ARG;
+    cudaStream_t s = (cudaStream_t)stream;
+    const StrSet P = make_set(patterns), T = make_set(texts);
+    const TempPlan p = plan(NVB_OP_BANDED_TRACEBACK, a, band, chk, maxM, maxN);
+    const uint32_t bp = batch_pairs(p, temp_bytes, n);
+    if (bp == 0) return NVB_ERR_TEMP;
+    ctx->last_paths = 2u;
+    const uint32_t bp128 = (bp + 127u) & ~127u;
+    for (uint32_t first = 0; first < n; first += bp)
+    {
+        const uint32_t cnt = n - first < bp ? n - first : bp;
+        int16_t* t16 = (int16_t*)temp;
+        uint8_t* flow = (uint8_t*)temp + p.i16_per_pair * 2 * (size_t)bp128;
+        if ((rc = dpg_banded_traceback(ctx, a, band, P, T, first, cnt, chk, out, ops, ops_stride, n_ops, t16, flow, maxM, s))) return rc;
+    }
+    return NVB_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// push-order ops -> forward run-length CIGAR (io::Cigar, nvbio/io/alignments.h:48-65)
+// ---------------------------------------------------------------------------------------------
+__global__ void ops_to_cigar_kernel(const uint8_t* __restrict__ ops, uint32_t ops_stride, const uint32_t* __restrict__ n_ops,
+                                    uint32_t n, uint16_t* __restrict__ cigar, uint32_t cigar_stride, uint32_t* __restrict__ n_cigar)
+{
+    const uint32_t id = blockIdx.x * blockDim.x + threadIdx.x;
+    if (id >= n) return;
+    const uint8_t* o = ops + (size_t)id * ops_stride;
+    uint16_t* c = cigar + (size_t)id * cigar_stride;
+    uint32_t len = n_ops[id]; if (len > ops_stride) len = ops_stride;
+    uint32_t out = 0, run = 0, prev = 0xFFu;
+    for (uint32_t k = len; k-- > 0;)
+    {
+        const uint32_t op = o[k] & 3u;
+        if (op == prev && run < 16383u) { ++run; continue; }
+        if (run) { if (out < cigar_stride) c[out] = (uint16_t)(prev | (run << 2)); ++out; }
+        prev = op; run = 1;
+    }
+    if (run) { if (out < cigar_stride) c[out] = (uint16_t)(prev | (run << 2)); ++out; }
+    n_cigar[id] = out;
+}
+
+extern "C" int nvb_ops_to_cigar(nvb_ctx* ctx, const uint8_t* ops, uint32_t ops_stride, const uint32_t* n_ops, uint32_t n,
+                                uint16_t* cigar, uint32_t cigar_stride, uint32_t* n_cigar, void* stream)
+{
+    if (!ctx) return NVB_ERR_ARG;
+    if (n == 0) return NVB_OK;
+    if (!ops || !n_ops || !cigar || !n_cigar) return NVB_ERR_ARG;
+    ops_to_cigar_kernel<<<(n + 127) / 128, 128, 0, (cudaStream_t)stream>>>(ops, ops_stride, n_ops, n, cigar, cigar_stride, n_cigar);
+    NVB_LAUNCHED(ctx);
+    return NVB_OK;
+}

@@ -1,0 +1,47 @@
+// dp_common.cuh -- shared pieces of the DP (alignment) kernels.
+#pragma once
+#include "common.cuh"
+
+enum { T_GLOBAL = NVB_GLOBAL, T_LOCAL = NVB_LOCAL, T_SEMI = NVB_SEMI_GLOBAL };
+enum { OP_SUB = 0, OP_INS = 1, OP_DEL = 2, OP_SINK = 3, OP_INS_EXT = 4, OP_DEL_EXT = 8 };   // alignment.h:326-337
+enum { ST_H = 0, ST_E = 1, ST_F = 2 };                                                      // alignment.h:341-346
+
+// SW/ED: ga = deletion (consumes text), gb = insertion (consumes pattern); Gotoh: ga = open, gb = ext
+struct Scheme { int32_t match, mismatch, ga, gb; };
+
+static inline Scheme make_scheme(const nvb_aligner& a)
+{
+    Scheme s;
+    if (a.kind == NVB_EDIT_DISTANCE) { s.match = 0; s.mismatch = -1; s.ga = -1; s.gb = -1; }   // ed_utils.h:36-43
+    else { s.match = a.match; s.mismatch = a.mismatch; s.ga = a.gap_a; s.gb = a.gap_b; }
+    return s;
+}
+
+#define NVB_SINK_MIN (-(1 << 30))   // Field_traits<int32>::min(), nvbio/basic/numbers.h:738-741
+
+#ifdef __CUDACC__
+struct Best
+{
+    int32_t score; uint32_t x, y;
+    __device__ __forceinline__ void init() { score = NVB_SINK_MIN; x = y = 0xFFFFFFFFu; }
+    // BestSink::report uses '<=': the last visited maximal cell wins (sink_inl.h:40-48)
+    __device__ __forceinline__ void report(int32_t s, uint32_t xx, uint32_t yy)
+    { if (score <= s) { score = s; x = xx; y = yy; } }
+};
+
+struct PairView
+{
+    const uint8_t* pat; uint32_t pbits; uint32_t pbeg; uint32_t M;
+    const uint8_t* txt; uint32_t tbits; uint32_t tbeg; uint32_t N;
+    __device__ __forceinline__ uint32_t p(uint32_t j) const { return sym_at_rt(pat, pbits, pbeg + j); }
+    __device__ __forceinline__ uint32_t t(uint32_t i) const { return sym_at_rt(txt, tbits, tbeg + i); }
+};
+
+__device__ __forceinline__ PairView make_pair_view(const StrSet& P, const StrSet& T, uint32_t id)
+{
+    PairView v;
+    v.pat = P.sym; v.pbits = P.bits; v.pbeg = P.off[id]; v.M = P.off[id + 1] - v.pbeg;
+    v.txt = T.sym; v.tbits = T.bits; v.tbeg = T.off[id]; v.N = T.off[id + 1] - v.tbeg;
+    return v;
+}
+#endif

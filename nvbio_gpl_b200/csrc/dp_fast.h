@@ -1,0 +1,16 @@
+// dp_fast.h -- the packed s16x2 DPX kernel family (dp_fast_full.cu, dp_fast_banded.cu).
+// Each kernel scores two pairs per thread in the halves of 32-bit registers with
+// VIADDMNMX.S16x2 / VIMNMX3.S16x2; pairs it cannot represent exactly (a symbol > 3, a length over
+// the kernel's limits) are appended to worklist (worklist[0] = count, ids from worklist[1]) and left
+// for the int32 kernels.
+#pragma once
+#include "dp_common.cuh"
+
+#define NVB_MAX_BAND_LEN 64
+
+bool dpf_full_score_supported(const nvb_aligner& a, const StrSet& P, const StrSet& T, uint32_t maxM, uint32_t maxN);
+int  dpf_full_score(nvb_ctx* ctx, const nvb_aligner& a, StrSet P, StrSet T, nvb_best_sink* sinks, uint32_t maxM,
+                    uint32_t maxN, uint32_t* worklist, cudaStream_t s);
+bool dpf_banded_score_supported(const nvb_aligner& a, uint32_t band, const StrSet& P, const StrSet& T, uint32_t maxM, uint32_t maxN);
+int  dpf_banded_score(nvb_ctx* ctx, const nvb_aligner& a, uint32_t band, StrSet P, StrSet T, nvb_best_sink* sinks,
+                      uint32_t maxM, uint32_t maxN, uint32_t* worklist, cudaStream_t s);

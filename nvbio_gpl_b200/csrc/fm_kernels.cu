@@ -1,0 +1,322 @@
+// fm_kernels.cu -- FM-index kernels and their C-ABI entry points.
+//
+//   fm_match_kernel    match(fmi, pattern, len[, range])  nvbio/fmindex/fmindex_inl.h:186-239
+//   fm_rank_kernel     rank(fmi, range, c)                nvbio/fmindex/fmindex_inl.h:60-88
+//   fm_rank4_kernel    rank4(fmi, k)                      nvbio/fmindex/fmindex_inl.h:100-125
+//   fm_locate_*        locate / locate_ssa_iterator / lookup_ssa_iterator   fmindex_inl.h:364-460
+//   fm_fuse_*          bwt + occ fusing                   nvbio/io/fmindex/fmindex_impl.cu:283-318
+//
+// The reference ships these only as device *functions* (its test kernel is
+// nvbio-test/fmindex_test.cu:56-85, its batch form thrust::transform in filter_inl.h:261-291).
+#include "fm_device.cuh"
+#include <cub/device/device_scan.cuh>
+
+#define FM_THREADS 256
+#define FM_STAGE_BYTES 8192   // staged query symbols per CTA (queries up to ~31 symbols on average)
+
+// ---------------------------------------------------------------------------------------------
+// backward search, one query per thread.
+// The query symbols of a CTA are one contiguous span of the concatenated set: it is staged into
+// shared memory with coalesced 16-byte loads, so the dependent loop only touches the index.
+// ---------------------------------------------------------------------------------------------
+template <int BITS, bool FROM>
+__global__ void __launch_bounds__(FM_THREADS)
+fm_match_kernel(const FMView f, const StrSet q, uint32_t* __restrict__ ranges)
+{
+    __shared__ __align__(16) uint8_t s_sym[FM_STAGE_BYTES];
+    const uint32_t first = blockIdx.x * FM_THREADS;
+    const uint32_t tid   = first + threadIdx.x;
+    const uint32_t last  = min(first + FM_THREADS, q.count);
+
+    // stage the CTA's symbol span (bits == 8 only; packed sets are read in place)
+    const uint32_t span_begin = q.off[first];
+    const uint32_t span_end   = q.off[last];
+    const uint32_t span_len   = span_end - span_begin;
+    const bool staged = (BITS == 8) && (span_len <= FM_STAGE_BYTES - 32u);
+    uint32_t skew = 0;
+    if (staged)
+    {
+        // align the global side to 16 bytes; the shared copy keeps the same skew
+        const uintptr_t gaddr = (uintptr_t)(q.sym + span_begin);
+        skew = (uint32_t)(gaddr & 15u);
+        const uint4* g = (const uint4*)(gaddr - skew);
+        const uint32_t n16 = (span_len + skew + 15u) >> 4;
+        uint4* s = (uint4*)s_sym;
+        for (uint32_t i = threadIdx.x; i < n16; i += FM_THREADS) s[i] = __ldg(g + i);
+        __syncthreads();
+    }
+    if (tid >= q.count) return;
+
+    const uint32_t beg = q.off[tid];
+    const uint32_t len = q.off[tid + 1] - beg;
+
+    uint32_t x, y;
+    if (FROM) { x = ranges[2 * tid]; y = ranges[2 * tid + 1]; }
+    else      { x = 0; y = f.length; }
+
+    for (int32_t i = (int32_t)len - 1; i >= 0 && x <= y; --i)
+    {
+        const uint32_t c = staged ? (uint32_t)s_sym[skew + (beg - span_begin) + (uint32_t)i]
+                                  : sym_at<BITS>(q.sym, beg + (uint32_t)i);
+        if (c > 3u) { x = 1; y = 0; break; }
+        const uint2 r = fm_rank2(f, x - 1u, y, c);
+        x = f.L2[c] + r.x + 1u;
+        y = f.L2[c] + r.y;
+    }
+    *(uint2*)(ranges + 2 * (size_t)tid) = make_uint2(x, y);
+}
+
+__global__ void __launch_bounds__(FM_THREADS)
+fm_rank_kernel(const FMView f, const uint32_t* __restrict__ ranges, const uint8_t* __restrict__ c,
+               uint32_t n, uint32_t* __restrict__ out)
+{
+    const uint32_t tid = blockIdx.x * FM_THREADS + threadIdx.x;
+    if (tid >= n) return;
+    const uint2 rg = *(const uint2*)(ranges + 2 * (size_t)tid);
+    const uint32_t cc = c[tid] & 3u;
+    uint2 r;
+    if (rg.x == rg.y) { r.x = r.y = fm_rank1(f, rg.x, cc); }   // fmindex_inl.h:66-70
+    else r = fm_rank2(f, rg.x, rg.y, cc);
+    *(uint2*)(out + 2 * (size_t)tid) = r;
+}
+
+__global__ void __launch_bounds__(FM_THREADS)
+fm_rank4_kernel(const FMView f, const uint32_t* __restrict__ k, uint32_t n, uint32_t* __restrict__ out)
+{
+    const uint32_t tid = blockIdx.x * FM_THREADS + threadIdx.x;
+    if (tid >= n) return;
+    uint32_t kk = k[tid];
+    uint4 r = make_uint4(0, 0, 0, 0);
+    if (kk == f.length)
+        r = make_uint4(f.L2[1] - f.L2[0], f.L2[2] - f.L2[1], f.L2[3] - f.L2[2], f.L2[4] - f.L2[3]);
+    else if (kk != 0xFFFFFFFFu)
+    {
+        if (kk >= f.primary) --kk;
+        if (kk != 0xFFFFFFFFu)
+        {
+            const FMBlock b = fm_load_block(f.blk, kk >> 6);
+            r = fm_block_rank4(b, kk & 63u);
+        }
+    }
+    *(uint4*)(out + 4 * (size_t)tid) = r;
+}
+
+// LF-walk from SA row j to the nearest sampled row (j % 16 == 0). One block load per step: the
+// BWT symbol and its rank come from the same 32-byte block.
+__device__ __forceinline__ uint2 fm_locate_walk_one(const FMView& f, uint32_t j)
+{
+    uint32_t t = 0;
+    while (j & 15u)
+    {
+        if (j != f.primary)
+        {
+            const uint32_t jj = j < f.primary ? j : j - 1u;        // fmindex_inl.h:384
+            const FMBlock b = fm_load_block(f.blk, jj >> 6);
+            const uint32_t c = fm_bwt_symbol(b, jj & 63u);
+            // rank(fmi, j, c) with the FM special cases (fmindex_inl.h:31-47)
+            uint32_t r;
+            if (j == f.length) r = f.L2[c + 1] - f.L2[c];
+            else r = fm_block_rank(b, jj & 63u, c);
+            j = f.L2[c] + r;
+        }
+        else j = 0;
+        ++t;
+    }
+    return make_uint2(j, t);
+}
+
+__global__ void __launch_bounds__(FM_THREADS)
+fm_locate_kernel(const FMView f, const uint32_t* __restrict__ rows, uint32_t n, uint32_t* __restrict__ pos)
+{
+    const uint32_t tid = blockIdx.x * FM_THREADS + threadIdx.x;
+    if (tid >= n) return;
+    const uint2 w = fm_locate_walk_one(f, rows[tid]);
+    pos[tid] = __ldg(f.ssa + (w.x >> 4)) + w.y;
+}
+
+__global__ void __launch_bounds__(FM_THREADS)
+fm_locate_walk_kernel(const FMView f, const uint32_t* __restrict__ rows, uint32_t n, uint32_t* __restrict__ walk)
+{
+    const uint32_t tid = blockIdx.x * FM_THREADS + threadIdx.x;
+    if (tid >= n) return;
+    *(uint2*)(walk + 2 * (size_t)tid) = fm_locate_walk_one(f, rows[tid]);
+}
+
+__global__ void __launch_bounds__(FM_THREADS)
+fm_locate_lookup_kernel(const FMView f, const uint32_t* __restrict__ walk, uint32_t n, uint32_t* __restrict__ pos)
+{
+    const uint32_t tid = blockIdx.x * FM_THREADS + threadIdx.x;
+    if (tid >= n) return;
+    const uint2 w = *(const uint2*)(walk + 2 * (size_t)tid);
+    pos[tid] = __ldg(f.ssa + (w.x >> 4)) + w.y;
+}
+
+// ---------------------------------------------------------------------------------------------
+// fusing: per 64-symbol block, symbol counts -> exclusive scan -> interleaved image
+// ---------------------------------------------------------------------------------------------
+struct U4Add { __host__ __device__ uint4 operator()(const uint4& a, const uint4& b) const
+{ return make_uint4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w); } };
+
+__global__ void fm_fuse_count_kernel(const uint4* __restrict__ bwt, uint32_t n_blocks, uint32_t length,
+                                     uint4* __restrict__ counts)
+{
+    const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= n_blocks) return;
+    const uint4 w = bwt[b];
+    const uint32_t ws[4] = { w.x, w.y, w.z, w.w };
+    uint32_t cnt[4] = { 0, 0, 0, 0 };
+    #pragma unroll
+    for (int wi = 0; wi < 4; ++wi)
+    {
+        const int64_t remain = (int64_t)length - ((int64_t)b * 64 + wi * 16);
+        const int32_t nv = remain < 0 ? 0 : remain > 16 ? 16 : (int32_t)remain;   // valid symbols
+        const uint32_t m = (uint32_t)(0xFFFFFFFF00000000ull >> (2 * nv));
+        #pragma unroll
+        for (uint32_t c = 0; c < 4; ++c) cnt[c] += __popc(fm_eq_bits(ws[wi], c * 0x55555555u) & m);
+    }
+    counts[b] = make_uint4(cnt[0], cnt[1], cnt[2], cnt[3]);
+}
+
+__global__ void fm_fuse_write_kernel(const uint4* __restrict__ bwt, const uint4* __restrict__ occ,
+                                     uint32_t n_blocks, uint4* __restrict__ fused)
+{
+    const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= n_blocks) return;
+    fused[2 * (size_t)b]     = bwt[b];
+    fused[2 * (size_t)b + 1] = occ[b];
+}
+
+// ---------------------------------------------------------------------------------------------
+// entry points
+// ---------------------------------------------------------------------------------------------
+static int check_fmi(const nvb_fmindex* f, bool need_ssa)
+{
+    if (!f || !f->bwt_occ) return NVB_ERR_ARG;
+    if (f->occ_int != 64u || f->sa_int != 16u) return NVB_ERR_UNSUPPORTED;
+    if (((uintptr_t)f->bwt_occ) & 31u) return NVB_ERR_ARG;
+    if (need_ssa && !f->ssa) return NVB_ERR_ARG;
+    return NVB_OK;
+}
+static inline uint32_t grid_for(uint32_t n) { return (n + FM_THREADS - 1) / FM_THREADS; }
+
+template <bool FROM>
+static int fm_match_launch(nvb_ctx* ctx, const nvb_fmindex* fmi, nvb_string_set queries, uint32_t* ranges,
+                           void* stream)
+{
+    if (!ctx || !ranges) return NVB_ERR_ARG;
+    int rc = check_fmi(fmi, false); if (rc) return rc;
+    if (queries.count == 0) return NVB_OK;
+    if (!queries.symbols || !queries.offsets) return NVB_ERR_ARG;
+    const FMView f = make_view(fmi);
+    const StrSet q = make_set(queries);
+    cudaStream_t s = (cudaStream_t)stream;
+    const uint32_t grid = grid_for(q.count);
+    switch (queries.bits)
+    {
+    case 8: fm_match_kernel<8, FROM><<<grid, FM_THREADS, 0, s>>>(f, q, ranges); break;
+    case 4: fm_match_kernel<4, FROM><<<grid, FM_THREADS, 0, s>>>(f, q, ranges); break;
+    case 2: fm_match_kernel<2, FROM><<<grid, FM_THREADS, 0, s>>>(f, q, ranges); break;
+    default: return NVB_ERR_ARG;
+    }
+    NVB_LAUNCHED(ctx);
+    return NVB_OK;
+}
+
+extern "C" int nvb_fm_match(nvb_ctx* ctx, const nvb_fmindex* fmi, nvb_string_set queries, uint32_t* ranges, void* stream)
+{ return fm_match_launch<false>(ctx, fmi, queries, ranges, stream); }
+
+extern "C" int nvb_fm_match_from(nvb_ctx* ctx, const nvb_fmindex* fmi, nvb_string_set queries, uint32_t* ranges, void* stream)
+{ return fm_match_launch<true>(ctx, fmi, queries, ranges, stream); }
+
+extern "C" int nvb_fm_rank(nvb_ctx* ctx, const nvb_fmindex* fmi, const uint32_t* ranges, const uint8_t* c,
+                           uint32_t n, uint32_t* out, void* stream)
+{
+    if (!ctx) return NVB_ERR_ARG;
+    int rc = check_fmi(fmi, false); if (rc) return rc;
+    if (n == 0) return NVB_OK;
+    if (!ranges || !c || !out) return NVB_ERR_ARG;
+    fm_rank_kernel<<<grid_for(n), FM_THREADS, 0, (cudaStream_t)stream>>>(make_view(fmi), ranges, c, n, out);
+    NVB_LAUNCHED(ctx);
+    return NVB_OK;
+}
+
+extern "C" int nvb_fm_rank4(nvb_ctx* ctx, const nvb_fmindex* fmi, const uint32_t* k, uint32_t n, uint32_t* out, void* stream)
+{
+    if (!ctx) return NVB_ERR_ARG;
+    int rc = check_fmi(fmi, false); if (rc) return rc;
+    if (n == 0) return NVB_OK;
+    if (!k || !out) return NVB_ERR_ARG;
+    fm_rank4_kernel<<<grid_for(n), FM_THREADS, 0, (cudaStream_t)stream>>>(make_view(fmi), k, n, out);
+    NVB_LAUNCHED(ctx);
+    return NVB_OK;
+}
+
+extern "C" int nvb_fm_locate(nvb_ctx* ctx, const nvb_fmindex* fmi, const uint32_t* rows, uint32_t n, uint32_t* pos, void* stream)
+{
+    if (!ctx) return NVB_ERR_ARG;
+    int rc = check_fmi(fmi, true); if (rc) return rc;
+    if (n == 0) return NVB_OK;
+    if (!rows || !pos) return NVB_ERR_ARG;
+    fm_locate_kernel<<<grid_for(n), FM_THREADS, 0, (cudaStream_t)stream>>>(make_view(fmi), rows, n, pos);
+    NVB_LAUNCHED(ctx);
+    return NVB_OK;
+}
+
+extern "C" int nvb_fm_locate_walk(nvb_ctx* ctx, const nvb_fmindex* fmi, const uint32_t* rows, uint32_t n, uint32_t* walk, void* stream)
+{
+    if (!ctx) return NVB_ERR_ARG;
+    int rc = check_fmi(fmi, false); if (rc) return rc;
+    if (n == 0) return NVB_OK;
+    if (!rows || !walk) return NVB_ERR_ARG;
+    fm_locate_walk_kernel<<<grid_for(n), FM_THREADS, 0, (cudaStream_t)stream>>>(make_view(fmi), rows, n, walk);
+    NVB_LAUNCHED(ctx);
+    return NVB_OK;
+}
+
+extern "C" int nvb_fm_locate_lookup(nvb_ctx* ctx, const nvb_fmindex* fmi, const uint32_t* walk, uint32_t n, uint32_t* pos, void* stream)
+{
+    if (!ctx) return NVB_ERR_ARG;
+    int rc = check_fmi(fmi, true); if (rc) return rc;
+    if (n == 0) return NVB_OK;
+    if (!walk || !pos) return NVB_ERR_ARG;
+    fm_locate_lookup_kernel<<<grid_for(n), FM_THREADS, 0, (cudaStream_t)stream>>>(make_view(fmi), walk, n, pos);
+    NVB_LAUNCHED(ctx);
+    return NVB_OK;
+}
+
+extern "C" size_t nvb_bwt_occ_words(uint32_t length) { return (size_t)((((length + 15u) / 16u) + 3u) & ~3u) * 2u; }
+extern "C" size_t nvb_ssa_words(uint32_t length) { return ((size_t)length + 16u) / 16u; }
+
+extern "C" int nvb_fmindex_fuse(nvb_ctx* ctx, const uint32_t* bwt_words, uint32_t length, uint32_t* bwt_occ_out,
+                                uint32_t* L2_out_h, void* stream)
+{
+    if (!ctx || !bwt_words || !bwt_occ_out || !L2_out_h) return NVB_ERR_ARG;
+    if ((((uintptr_t)bwt_words) & 15u) || (((uintptr_t)bwt_occ_out) & 31u)) return NVB_ERR_ARG;
+    cudaStream_t s = (cudaStream_t)stream;
+    const uint32_t n_blocks = (uint32_t)(nvb_bwt_occ_words(length) / 8u);
+    L2_out_h[0] = 0;
+    if (n_blocks == 0) { for (int c = 0; c < 4; ++c) L2_out_h[c + 1] = 0; return NVB_OK; }
+    uint4 *counts = nullptr, *occ = nullptr; void* tmp = nullptr; size_t tmp_bytes = 0;
+    NVB_CUDA(ctx, cudaMallocAsync(&counts, sizeof(uint4) * ((size_t)n_blocks + 1), s));
+    NVB_CUDA(ctx, cudaMallocAsync(&occ, sizeof(uint4) * ((size_t)n_blocks + 1), s));
+    NVB_CUDA(ctx, cudaMemsetAsync(counts + n_blocks, 0, sizeof(uint4), s));
+    const uint32_t g = (n_blocks + 255) / 256;
+    fm_fuse_count_kernel<<<g, 256, 0, s>>>((const uint4*)bwt_words, n_blocks, length, counts);
+    NVB_LAUNCHED(ctx);
+    // exclusive scan over n_blocks+1 items: the last output is the total = symbol counts
+    cub::DeviceScan::ExclusiveScan(nullptr, tmp_bytes, counts, occ, U4Add(), make_uint4(0, 0, 0, 0), (int)(n_blocks + 1), s);
+    NVB_CUDA(ctx, cudaMallocAsync(&tmp, tmp_bytes, s));
+    NVB_CUDA(ctx, cub::DeviceScan::ExclusiveScan(tmp, tmp_bytes, counts, occ, U4Add(), make_uint4(0, 0, 0, 0), (int)(n_blocks + 1), s));
+    ctx->launches++;
+    fm_fuse_write_kernel<<<g, 256, 0, s>>>((const uint4*)bwt_words, occ, n_blocks, (uint4*)bwt_occ_out);
+    NVB_LAUNCHED(ctx);
+    uint4 total;
+    NVB_CUDA(ctx, cudaMemcpyAsync(&total, occ + n_blocks, sizeof(uint4), cudaMemcpyDeviceToHost, s));
+    NVB_CUDA(ctx, cudaStreamSynchronize(s));
+    NVB_CUDA(ctx, cudaFreeAsync(counts, s));
+    NVB_CUDA(ctx, cudaFreeAsync(occ, s));
+    NVB_CUDA(ctx, cudaFreeAsync(tmp, s));
+    L2_out_h[1] = total.x; L2_out_h[2] = L2_out_h[1] + total.y;
+    L2_out_h[3] = L2_out_h[2] + total.z; L2_out_h[4] = L2_out_h[3] + total.w;
+    return NVB_OK;
+}

@@ -30,3 +30,14 @@ def ref():
     if not pyoracle.Oracle.available("ref"):
         pytest.skip("oracle/_ref/libnvbio_ref.so not built (needs /root/reference)")
     return pyoracle.Oracle("ref")
+
+
+def pytest_collection_modifyitems(config, items):
+    """GPU tests need a CUDA device; without one they are reported as skipped (run them with -m gpu on a B200)"""
+    import torch
+    if torch.cuda.is_available():
+        return
+    skip = pytest.mark.skip(reason="no CUDA device")
+    for item in items:
+        if "gpu" in item.keywords:
+            item.add_marker(skip)

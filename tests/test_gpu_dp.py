@@ -1,0 +1,145 @@
+"""-m gpu: DP kernels through the C ABI vs the oracle: scores, sinks (incl. tie-breaks on binary
+alphabets), sources and op lists must be bit-identical. Golden vectors of the reference
+(nvbio-test/alignment_test.cu:641-863) are checked on the GPU path too."""
+import numpy as np
+import pytest
+import torch
+
+import nvbio_gpl_b200 as nvb
+import pyoracle as po
+import util
+import gpu_util as gu
+
+pytestmark = pytest.mark.gpu
+
+CASES = [(k, sc, ty) for k in (po.ED, po.SW, po.GOTOH) for sc in util.SCHEMES[k] for ty in (0, 1, 2)]
+
+
+@pytest.fixture(params=[False, True], ids=["auto", "generic"])
+def ctx(request):
+    c = nvb.Context.default(0)
+    c.force_generic(request.param)
+    yield c
+    c.force_generic(False)
+
+
+@pytest.mark.parametrize("kind,scheme,ty", CASES)
+def test_full_score_and_traceback(oracle, ctx, kind, scheme, ty):
+    rng = np.random.default_rng(hash((kind, scheme, ty)) & 0xFFFF)
+    a, oa = gu.aligner(kind, ty, scheme), po.aligner(kind, ty, scheme)
+    for alpha in (4, 2):
+        P, Po, T, To = util.rand_pairs(rng, 700, (1, 70), lambda M: int(rng.integers(0, 120)), alpha)
+        ps, ts = gu.sset(P, Po), gu.sset(T, To)
+        got = gu.sinks_np(nvb.batch_alignment_score(a, ps, ts))
+        want = oracle.score(oa, P, Po, T, To)
+        assert (got == want).all(), np.nonzero(got != want)[0][:5]
+        for chk in (16, 64):
+            got = gu.tb_np(nvb.batch_alignment_traceback(a, chk, ps, ts))
+            assert gu.tb_equal(got, oracle.traceback(oa, chk, P, Po, T, To))
+
+
+@pytest.mark.parametrize("kind,scheme,ty", CASES)
+def test_banded_score_and_traceback(oracle, ctx, kind, scheme, ty):
+    rng = np.random.default_rng(hash((kind, scheme, ty, 1)) & 0xFFFF)
+    a, oa = gu.aligner(kind, ty, scheme), po.aligner(kind, ty, scheme)
+    for alpha in (4, 2):
+        for band in (3, 5, 7, 15, 31, 12):
+            P, Po, T, To = util.rand_pairs(rng, 500, (1, 80), util.banded_text_len(rng, ty, band), alpha)
+            ps, ts = gu.sset(P, Po), gu.sset(T, To)
+            got = gu.sinks_np(nvb.batch_banded_alignment_score(a, band, ps, ts))
+            want = oracle.banded_score(oa, band, P, Po, T, To)
+            assert (got == want).all(), (band, np.nonzero(got != want)[0][:5])
+            for chk in (16, 32):
+                got = gu.tb_np(nvb.batch_banded_alignment_traceback(a, band, chk, ps, ts))
+                assert gu.tb_equal(got, oracle.banded_traceback(oa, band, chk, P, Po, T, To)), (band, chk)
+
+
+def test_symbols_with_n_and_long_shapes(oracle, ctx):
+    """N symbols (codes > 3) compare equal only to the same code; C1/C3-shaped pairs"""
+    rng = np.random.default_rng(77)
+    for kind, scheme, ty in [(po.SW, (2, -1, -1, -1), 1), (po.GOTOH, (2, -1, -2, -1), 1), (po.ED, (0, -1, -1, -1), 2)]:
+        a, oa = gu.aligner(kind, ty, scheme), po.aligner(kind, ty, scheme)
+        P, Po, T, To = util.rand_pairs(rng, 600, (140, 151), lambda M: 500, 4)
+        P = P.copy(); T = T.copy()
+        P[rng.integers(0, len(P), 300)] = 4
+        T[rng.integers(0, len(T), 300)] = rng.integers(4, 7, 300)
+        ps, ts = gu.sset(P, Po), gu.sset(T, To)
+        got = gu.sinks_np(nvb.batch_alignment_score(a, ps, ts))
+        assert (got == oracle.score(oa, P, Po, T, To)).all()
+        P, Po, T, To = util.rand_pairs(rng, 600, (240, 251), lambda M: M + 15, 4)
+        P = P.copy(); P[rng.integers(0, len(P), 200)] = 4
+        ps, ts = gu.sset(P, Po), gu.sset(T, To)
+        got = gu.sinks_np(nvb.batch_banded_alignment_score(a, 15, ps, ts))
+        assert (got == oracle.banded_score(oa, 15, P, Po, T, To)).all()
+        got = gu.tb_np(nvb.batch_banded_alignment_traceback(a, 15, 16, ps, ts))
+        assert gu.tb_equal(got, oracle.banded_traceback(oa, 15, 16, P, Po, T, To))
+
+
+def test_empty_and_degenerate(oracle, ctx):
+    a, oa = gu.aligner(po.SW, 1, (2, -1, -1, -1)), po.aligner(po.SW, 1, (2, -1, -1, -1))
+    # empty batch
+    z = nvb.StringSet.from_numpy(np.zeros(0, np.uint8), np.zeros(1, np.uint32), gu.dev())
+    assert nvb.batch_alignment_score(a, z, z).shape[0] == 0
+    # empty patterns / texts inside a batch
+    P, Po = po.concat([np.zeros(0, np.uint8), po.dna("ACGT"), po.dna("A"), np.zeros(0, np.uint8)])
+    T, To = po.concat([po.dna("ACGT"), np.zeros(0, np.uint8), po.dna("A"), np.zeros(0, np.uint8)])
+    ps, ts = gu.sset(P, Po), gu.sset(T, To)
+    for kind, scheme in [(po.SW, (2, -1, -1, -1)), (po.GOTOH, (2, -1, -2, -1)), (po.ED, (0, -1, -1, -1))]:
+        a, oa = gu.aligner(kind, 1, scheme), po.aligner(kind, 1, scheme)
+        assert (gu.sinks_np(nvb.batch_alignment_score(a, ps, ts)) == oracle.score(oa, P, Po, T, To)).all()
+    # banded: text shorter than the pattern is refused exactly as the reference does
+    a, oa = gu.aligner(po.ED, 2, (0, -1, -1, -1)), po.aligner(po.ED, 2, (0, -1, -1, -1))
+    P, Po = po.concat([po.dna("ACGTACGT"), po.dna("ACGT")])
+    T, To = po.concat([po.dna("ACGT"), po.dna("ACGTAC")])
+    ps, ts = gu.sset(P, Po), gu.sset(T, To)
+    assert (gu.sinks_np(nvb.batch_banded_alignment_score(a, 7, ps, ts)) == oracle.banded_score(oa, 7, P, Po, T, To)).all()
+
+
+GOLD_P, GOLD_T = "ACAACTA", "AAACACCCTAACACACTAAA"
+
+
+def cigar_of(ops, n):
+    return po.rle(ops[:n][::-1])
+
+
+@pytest.mark.parametrize("kind,ty,want", [
+    (po.SW, 0, "1M2D3M1D3M10D"), (po.SW, 1, "4M1D3M"), (po.SW, 2, "4M1D3M"),
+    (po.GOTOH, 0, "1M2D3M1D3M10D"), (po.GOTOH, 1, "4M1D3M"), (po.GOTOH, 2, "4M1D3M")])
+def test_golden_cigars(ctx, kind, ty, want):
+    """nvbio-test/alignment_test.cu:721-753"""
+    a = gu.aligner(kind, ty, (2, -1, -1, -1))
+    P, Po = po.concat([po.dna(GOLD_P)]); T, To = po.concat([po.dna(GOLD_T)])
+    out, ops, n_ops = gu.tb_np(nvb.batch_alignment_traceback(a, 16, gu.sset(P, Po), gu.sset(T, To)))
+    assert cigar_of(ops[0], n_ops[0]) == want
+    if kind == po.GOTOH and ty != 0:
+        out, ops, n_ops = gu.tb_np(nvb.batch_banded_alignment_traceback(a, 7, 16, gu.sset(P, Po), gu.sset(T, To)))
+        assert cigar_of(ops[0], n_ops[0]) == want
+
+
+def test_host_entry_points_and_cigar(oracle, ctx):
+    rng = np.random.default_rng(9)
+    a, oa = gu.aligner(po.GOTOH, 2, (0, -5, -8, -3)), po.aligner(po.GOTOH, 2, (0, -5, -8, -3))
+    P, Po, T, To = util.rand_pairs(rng, 3000, (100, 151), lambda M: M + 15, 4)
+    got = nvb.batch_score_host(a, 15, P, Po, T, To)
+    want = oracle.banded_score(oa, 15, P, Po, T, To)
+    assert (got["score"] == want["score"]).all() and (got["x"] == want["x"]).all() and (got["y"] == want["y"]).all()
+    stride = 2 * 151 + 15 + 8
+    got = nvb.batch_traceback_host(a, 15, 16, P, Po, T, To, stride)
+    want = oracle.banded_traceback(oa, 15, 16, P, Po, T, To)
+    assert gu.tb_equal(got, want)
+    # full-matrix host forms
+    a, oa = gu.aligner(po.SW, 1, (2, -1, -1, -1)), po.aligner(po.SW, 1, (2, -1, -1, -1))
+    P, Po, T, To = util.rand_pairs(rng, 1000, (50, 151), lambda M: 300, 4)
+    got = nvb.batch_score_host(a, 0, P, Po, T, To)
+    want = oracle.score(oa, P, Po, T, To)
+    assert (got["score"] == want["score"]).all() and (got["x"] == want["x"]).all() and (got["y"] == want["y"]).all()
+    tb = nvb.batch_traceback_host(a, 0, 64, P, Po, T, To, 151 + 300 + 8)
+    want = oracle.traceback(oa, 64, P, Po, T, To)
+    assert gu.tb_equal(tb, want)
+    # CIGAR packing (io::Cigar: op | len << 2, forward order)
+    ops_d = torch.from_numpy(tb[1]).to(gu.dev()); nops_d = torch.from_numpy(tb[2].view(np.int32)).to(gu.dev())
+    cig, ncig = nvb.ops_to_cigar(ops_d, nops_d)
+    cig = cig.cpu().numpy().view(np.uint16); ncig = ncig.cpu().numpy()
+    for i in range(50):
+        s = "".join("%d%s" % (w >> 2, "MID"[w & 3]) for w in cig[i, :ncig[i]])
+        assert s == po.rle(tb[1][i, :tb[2][i]][::-1])

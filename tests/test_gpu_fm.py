@@ -1,0 +1,116 @@
+"""-m gpu: FM-index kernels through the C ABI vs the oracle (bit-exact raw uint32 results).
+Follows the reference's own method: nvbio-test/rank_test.cu:46-79 (rank vs counts) and
+nvbio-test/fmindex_test.cu:576-707 (match/locate vs SA; host == device)."""
+import numpy as np
+import pytest
+import torch
+
+import nvbio_gpl_b200 as nvb
+from nvbio_gpl_b200 import fmindex as fmx
+import pyoracle as po
+import util
+import gpu_util as gu
+
+pytestmark = pytest.mark.gpu
+
+
+def u32(t):
+    return t.cpu().numpy().view(np.uint32)
+
+
+@pytest.mark.parametrize("n,alpha", [(1, 4), (2, 4), (63, 4), (64, 4), (65, 4), (1000, 2), (4096, 4), (300000, 4), (5000, 1)])
+def test_match_rank_locate(oracle, n, alpha):
+    rng = np.random.default_rng(n * 7 + alpha)
+    text = rng.integers(0, alpha, n).astype(np.uint8)
+    fmi, oidx = gu.fm_index_pair(oracle, text)
+    ref_idx = oracle.build_index(text)
+    assert fmi.primary == ref_idx.primary and (oidx.bwt_occ == ref_idx.bwt_occ).all() and (oidx.ssa == ref_idx.ssa).all()
+
+    Q, qo = util.rand_queries(rng, text, 20000, len_range=(0, 40), alpha=alpha)
+    qs = gu.sset(Q, qo)
+    got = u32(nvb.match(fmi, qs.symbols, qs.offsets))
+    want = oracle.fm_match(oidx, Q, qo)
+    assert (got == want).all()
+
+    # continuing from given ranges == matching the concatenation (fmindex_inl.h:212-239)
+    start = torch.from_numpy(want.view(np.int32).copy()).to(gu.dev())
+    got2 = u32(nvb.match(fmi, qs.symbols, qs.offsets, ranges=start))
+    QQ = [np.concatenate([Q[qo[i]:qo[i + 1]], Q[qo[i]:qo[i + 1]]]) for i in range(2000)]
+    Q2, q2o = po.concat(QQ)
+    assert (got2[:2000] == oracle.fm_match(oidx, Q2, q2o)).all()
+
+    ok = want[:, 0] <= want[:, 1]
+    rows = np.concatenate([want[ok, 0], want[ok, 1], rng.integers(0, n + 1, 5000).astype(np.uint32),
+                           np.array([0, n, fmi.primary], dtype=np.uint32)])
+    rows_d = torch.from_numpy(rows.view(np.int32)).to(gu.dev())
+    want_pos = oracle.fm_locate(oidx, rows)
+    assert (u32(nvb.locate(fmi, rows_d)) == want_pos).all()
+    assert (u32(nvb.locate(fmi, rows_d, two_phase=True)) == want_pos).all()
+
+    k = rng.integers(0, n + 1, 5000).astype(np.uint32)
+    k[:3] = [0xFFFFFFFF, n, 0]
+    assert (u32(nvb.rank4(fmi, torch.from_numpy(k.view(np.int32)).to(gu.dev()))) == oracle.fm_rank4(oidx, k)).all()
+
+    rg = np.stack([rng.integers(0, n + 1, 5000), rng.integers(0, n + 1, 5000)], 1).astype(np.uint32)
+    rg.sort(1)
+    rg[:50, 0] = 0xFFFFFFFF
+    rg[50:60, 1] = n
+    rg[60:80, 0] = rg[60:80, 1]
+    c = rng.integers(0, 4, 5000).astype(np.uint8)
+    got = u32(nvb.rank(fmi, torch.from_numpy(rg.view(np.int32)).to(gu.dev()), torch.from_numpy(c).to(gu.dev())))
+    assert (got == oracle.fm_rank(oidx, rg, c)).all()
+
+
+def test_located_positions_are_occurrences(oracle):
+    """every locate() of a non-empty match points at an occurrence (fmindex_test.cu:604-656)"""
+    rng = np.random.default_rng(5)
+    n = 200000
+    text = rng.integers(0, 4, n).astype(np.uint8)
+    fmi, _ = gu.fm_index_pair(oracle, text)
+    starts = rng.integers(0, n - 12, 4000)
+    Q, qo = po.concat([text[s:s + 12] for s in starts])
+    qs = gu.sset(Q, qo)
+    r = u32(nvb.match(fmi, qs.symbols, qs.offsets))
+    assert (r[:, 0] <= r[:, 1]).all()
+    for col in (0, 1):
+        pos = u32(nvb.locate(fmi, torch.from_numpy(r[:, col].copy().view(np.int32)).to(gu.dev())))
+        for p, s in zip(pos[:500], starts[:500]):
+            assert (text[p:p + 12] == text[s:s + 12]).all()
+
+
+def test_host_entry_points_and_fuse(oracle):
+    rng = np.random.default_rng(11)
+    n = 100000
+    text = rng.integers(0, 4, n).astype(np.uint8)
+    fmi, oidx = gu.fm_index_pair(oracle, text)
+    Q, qo = util.rand_queries(rng, text, 30000, len_range=(18, 23))
+    want = oracle.fm_match(oidx, Q, qo)
+    got = nvb.match_host(fmi, Q, qo)
+    assert (got == want).all()
+    rows = want[want[:, 0] <= want[:, 1], 0].copy()
+    assert (nvb.locate_host(fmi, rows) == oracle.fm_locate(oidx, rows)).all()
+    # fusing a plain BWT on the device reproduces the image (fmindex_impl.cu:283-318)
+    words = oidx.bwt_occ.reshape(-1, 8)[:, :4].reshape(-1).copy()
+    fused, L2 = fmx.fuse(torch.from_numpy(words.view(np.int32)).to(gu.dev()), n)
+    assert (u32(fused) == oidx.bwt_occ).all() and L2 == fmi.L2
+
+
+def test_packed_query_sets(oracle):
+    """2-bit and 4-bit big-endian packed query sets (PackedStream<...,true>) give the same ranges"""
+    rng = np.random.default_rng(3)
+    n = 50000
+    text = rng.integers(0, 4, n).astype(np.uint8)
+    fmi, oidx = gu.fm_index_pair(oracle, text)
+    Q, qo = util.rand_queries(rng, text, 5000, len_range=(1, 30), p_n=0.0)
+    want = oracle.fm_match(oidx, Q, qo)
+    off = torch.from_numpy(qo.view(np.int32)).to(gu.dev())
+    for bits in (2, 4):
+        per = 32 // bits
+        nw = (len(Q) + per - 1) // per + 1
+        sym = np.zeros(nw * per, dtype=np.uint64)
+        sym[:len(Q)] = Q
+        sh = (32 - bits - bits * np.arange(per)).astype(np.uint64)
+        words = (sym.reshape(nw, per) << sh).sum(1).astype(np.uint32)
+        wd = torch.from_numpy(words.view(np.int32)).to(gu.dev())
+        got = u32(nvb.match(fmi, wd, off, bits=bits))
+        assert (got == want).all()
