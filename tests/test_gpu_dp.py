@@ -99,7 +99,8 @@ GOLD_P, GOLD_T = "ACAACTA", "AAACACCCTAACACACTAAA"
 
 
 def cigar_of(ops, n):
-    return po.rle(ops[:n][::-1])
+    # the reference test's backtracer appends ops as pushed (end -> start): alignment_test.cu:96-135
+    return po.rle(ops[:n])
 
 
 @pytest.mark.parametrize("kind,ty,want", [
