@@ -79,14 +79,14 @@ extern "C" int nvb_batch_score(nvb_ctx* ctx, nvb_aligner a, nvb_string_set patte
     const TempPlan p = plan(NVB_OP_SCORE, a, 0, 0, maxM, maxN);
     ctx->last_paths = 0;
 
-    if (!ctx->force_generic && dpf_full_score_supported(a, P, T, maxM, maxN))
+    if (!ctx->force_generic && temp && batch_pairs(p, temp_bytes, n) >= n && dpf_full_score_supported(a, P, T, maxM, maxN))
     {
         // packed DPX kernel; pairs it cannot represent exactly are appended to the ctx worklist and
         // re-scored by the int32 kernel, which reads the count on the device (no host sync)
         uint32_t* wl = nullptr;
         if ((rc = nvb_worklist(ctx, n, &wl))) return rc;
         NVB_CUDA(ctx, cudaMemsetAsync(wl, 0, sizeof(uint32_t), s));
-        if ((rc = dpf_full_score(ctx, a, P, T, sinks, maxM, maxN, wl, s))) return rc;
+        if ((rc = dpf_full_score(ctx, a, P, T, sinks, maxM, maxN, wl, temp, s))) return rc;
         ctx->last_paths |= 1u;
         if (!temp && p.i16_per_pair) return NVB_ERR_TEMP;
         uint32_t n_dirty = n;

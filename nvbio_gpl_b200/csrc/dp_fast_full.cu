@@ -1,43 +1,57 @@
-// dp_fast_full.cu -- packed s16x2 DPX kernel for full-matrix LOCAL Smith-Waterman / edit distance
-// scoring (replaces lmem_batched_alignment_score_kernel / sw_alignment_score_dispatch for the
-// reference's speed-test shape: nvbio/alignment/batched_inl.h:79-91, sw/sw_inl.h:419-526,610-749).
+// dp_fast_full.cu -- packed s16x2 DPX wavefront kernel for full-matrix LOCAL Smith-Waterman / edit
+// distance scoring (replaces lmem_batched_alignment_score_kernel + sw_alignment_score_dispatch and the
+// warp-per-alignment kernel of the reference for its speed-test shape:
+// nvbio/alignment/batched_inl.h:79-91,183-205, sw/sw_inl.h:419-526,610-749, sw/sw_warp_inl.h).
 //
-// Inter-sequence parallelism: one thread scores TWO pairs, pair A in the low and pair B in the high
-// half of every 32-bit register. Cells are visited exactly like the reference (pattern stripes of 16
-// columns -> text rows -> columns), the stripe lives in 16 registers, the boundary column goes through
-// global scratch ([row][thread], coalesced, software-prefetched one row ahead).
+// Parallelism, both kinds at once:
+//   inter-sequence : every 32-bit register holds TWO pairs (pair A in the low, pair B in the high half);
+//   intra-sequence : the pattern stripes of 16 columns (the reference's BAND_LEN) of one such couple are
+//                    spread over adjacent lanes; lane k sweeps stripe k down the text one row per step,
+//                    one row behind lane k-1, and receives the stripe boundary cell by warp shuffle
+//                    (anti-diagonal wavefront). A warp carries floor(32 / stripes) couples.
+// Nothing but the packed text (4 bits per row and couple, shared memory) is read inside the sweep.
 //
-// Per packed cell (= 2 DP cells):
-//   S  = PRMT(profA[j], profB[j], sel_row)     substitution scores of both pairs in one byte permute:
-//                                              prof*[j] holds S(r, q_j) for r = A,C,G,T as 4 bytes, the
-//                                              selector picks byte r (+ its sign replication) per half
-//   u  = VIADD.16x2(top, G)
-//   v  = VIADDMNMX.S16x2(diag, S, u)           max(diag + S, top + G)
-//   h  = VIADDMNMX.S16x2.RELU(left, I, v)      max(left + I, v, 0)
-//   k  = IMAD(h, 16, j)                        arg-max key, issued on the FMA pipe
-// BestSink's "last maximal cell wins" (sink_inl.h:44) is reproduced with keys: within a stripe row the
-// key (score << 4 | column) is maximised with VIMNMX3.S16x2; across rows and stripes a later row
-// replaces the best whenever its score is >= (the column bits of the running best are cleared before
-// the row is folded in). Scores must stay below 2048 (match * min(M,N)); pairs beyond that, or holding
-// a symbol > 3, are appended to the worklist for the int32 kernel.
+// Per packed cell (= 2 DP cells), scores biased by B = max(|G|,|I|) so that the two gap additions
+// can be plain 32-bit IMADs on the FMA pipe (the low half never borrows):
+//   S   = PRMT(profA[j], profB[j], sel_row)   both substitution scores by one byte permute: prof*[j] holds
+//                                             S(r, q_j) for r = A,C,G,T as 4 bytes; the row selector picks
+//                                             byte r and replicates its sign into the upper byte
+//   u   = IMAD(top, 1, G')                    top + G
+//   v   = VIADDMNMX.S16x2(diag, S, u)         max(diag + S, top + G)
+//   l   = IMAD(left, 1, I')                   left + I
+//   h   = VIMNMX3.S16x2(l, v, B)              max(left + I, v, 0)          (LOCAL floor)
+//   key = IMAD(h, 16, j)                      arg-max key
+// BestSink's "last maximal cell wins" (sink_inl.h:44) with the reference's visiting order
+// (stripe, text row, column) is reproduced by keys: inside a stripe row (score << 4 | column) is
+// maximised with VIMNMX3.S16x2; a later row replaces the running best whenever its score is >= ; across
+// stripes the higher stripe wins ties (final shuffle reduction). Pairs with a symbol > 3, or whose
+// score could reach 2048 - B, go to the worklist for the int32 kernel.
 #include "dp_fast.h"
 
-#define DPF_THREADS 128
+#define DPF_WARPS   4
+#define DPF_THREADS (DPF_WARPS * 32)
 
 struct FullFastParams
 {
     StrSet         P, T;
     nvb_best_sink* sinks;
-    uint32_t*      col;        // [maxN][threads] packed boundary column
     uint32_t*      worklist;   // [0] = count, [1..] = pair ids
     uint32_t       n_pairs;
-    uint32_t       n_threads;  // total threads = ceil(n_pairs / 2)
-    uint32_t       tstride;    // per-thread text words in shared memory = ceil(maxN / 8)
-    int32_t        match, mismatch, G, I;
-    uint32_t       sixteen;    // = 16, a runtime value so that the key is an IMAD
+    uint32_t       n_tasks;    // couples = ceil(n_pairs / 2)
+    uint32_t       lanes;      // lanes (= stripes) per couple
+    uint32_t       tpw;        // couples per warp = 32 / lanes
+    uint32_t       tstride;    // shared-memory words per couple = ceil(maxN / 8)
+    int32_t        match, mismatch, G, I, B;
+    uint32_t       one, sixteen;   // runtime 1 and 16: keep the IMADs IMADs
 };
 
 __device__ __forceinline__ uint32_t pack2(int32_t v) { return ((uint32_t)v & 0xFFFFu) * 0x00010001u; }
+// addend that adds the negative g to both halves of a register whose low half never drops below -g
+__device__ __forceinline__ uint32_t fix2(int32_t g) { return (((uint32_t)(g - 1) & 0xFFFFu) << 16) | ((uint32_t)g & 0xFFFFu); }
+__device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t s)
+{ uint32_t d; asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(s)); return d; }
+__device__ __forceinline__ uint32_t imad(uint32_t a, uint32_t b, uint32_t c)
+{ uint32_t d; asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c)); return d; }
 
 __device__ __forceinline__ void mark_dirty(uint32_t* wl, uint32_t id)
 {
@@ -48,129 +62,156 @@ __device__ __forceinline__ void mark_dirty(uint32_t* wl, uint32_t id)
 __global__ void __launch_bounds__(DPF_THREADS)
 dpf_full_sw_local_kernel(const FullFastParams p)
 {
-    extern __shared__ uint32_t s_text[];   // [tstride][DPF_THREADS]: 8 rows per word, nibble = rA | rB << 2
-    const uint32_t tid = blockIdx.x * DPF_THREADS + threadIdx.x;
-    if (tid >= p.n_threads) return;        // no block-wide synchronisation below
-    const uint32_t idA = 2 * tid;
-    const bool     hasB = idA + 1 < p.n_pairs;
-    const uint32_t idB = hasB ? idA + 1 : idA;
+    extern __shared__ uint32_t s_text[];   // [warp][couple slot][tstride]: 8 rows per word, nibble = rA | rB << 2
+    const uint32_t lane = threadIdx.x & 31u, wib = threadIdx.x >> 5;
+    const uint32_t warp = blockIdx.x * DPF_WARPS + wib;
+    const uint32_t g = lane / p.lanes, k = lane - g * p.lanes;       // couple slot, stripe
+    const uint32_t task = warp * p.tpw + g;
+    const bool live = g < p.tpw && task < p.n_tasks;
+    const uint32_t gbase = g * p.lanes;                               // first lane of this couple
 
-    const uint32_t pbA = p.P.off[idA], MA = p.P.off[idA + 1] - pbA;
-    const uint32_t pbB = p.P.off[idB], MB = p.P.off[idB + 1] - pbB;
-    const uint32_t tbA = p.T.off[idA], NA = p.T.off[idA + 1] - tbA;
-    const uint32_t tbB = p.T.off[idB], NB = p.T.off[idB + 1] - tbB;
-    const uint32_t Nmax = max(NA, NB), Mmax = max(MA, MB);
+    uint32_t idA = 0, idB = 0, pbA = 0, pbB = 0, tbA = 0, tbB = 0, MA = 0, MB = 0, NA = 0, NB = 0;
+    bool hasB = false;
+    if (live)
+    {
+        idA = 2 * task; hasB = idA + 1 < p.n_pairs; idB = hasB ? idA + 1 : idA;
+        pbA = p.P.off[idA]; MA = p.P.off[idA + 1] - pbA; pbB = p.P.off[idB]; MB = p.P.off[idB + 1] - pbB;
+        tbA = p.T.off[idA]; NA = p.T.off[idA + 1] - tbA; tbB = p.T.off[idB]; NB = p.T.off[idB + 1] - tbB;
+    }
+    const uint32_t Nmax = max(NA, NB);
     bool dirtyA = false, dirtyB = false;
 
-    // scores must fit the 11 score bits of the arg-max key
-    if (p.match > 0)
+    // ---- prologue: the couple's lanes pack its two texts into the nibble stream
+    uint32_t* my_text = s_text + ((size_t)wib * p.tpw + (live ? g : 0)) * p.tstride;
+    if (live)
     {
-        if ((uint64_t)p.match * min(MA, NA) >= 2048u) dirtyA = true;
-        if ((uint64_t)p.match * min(MB, NB) >= 2048u) dirtyB = true;
-    }
-
-    // ---- prologue: text -> nibble stream in shared memory
-    uint32_t* my_text = s_text + threadIdx.x;
-    for (uint32_t w = 0; w * 8 < Nmax; ++w)
-    {
-        uint32_t word = 0;
-        #pragma unroll
-        for (uint32_t k = 0; k < 8; ++k)
+        for (uint32_t w = k; w * 8 < Nmax; w += p.lanes)
         {
-            const uint32_t i = w * 8 + k;
-            const uint32_t rA = i < NA ? sym_at_rt(p.T.sym, p.T.bits, tbA + i) : 0u;
-            const uint32_t rB = i < NB ? sym_at_rt(p.T.sym, p.T.bits, tbB + i) : 0u;
-            dirtyA |= rA > 3u; dirtyB |= rB > 3u;
-            word |= ((rA & 3u) | ((rB & 3u) << 2)) << (4 * k);
+            uint32_t word = 0;
+            #pragma unroll
+            for (uint32_t e = 0; e < 8; ++e)
+            {
+                const uint32_t i = w * 8 + e;
+                const uint32_t rA = i < NA ? sym_at_rt(p.T.sym, p.T.bits, tbA + i) : 0u;
+                const uint32_t rB = i < NB ? sym_at_rt(p.T.sym, p.T.bits, tbB + i) : 0u;
+                dirtyA |= rA > 3u; dirtyB |= rB > 3u;
+                word |= ((rA & 3u) | ((rB & 3u) << 2)) << (4 * e);
+            }
+            my_text[w] = word;
         }
-        my_text[w * DPF_THREADS] = word;
     }
+    __syncwarp();
 
-    const uint32_t G2 = pack2(p.G), I2 = pack2(p.I);
+    // ---- this lane's stripe: substitution profiles of 16 pattern columns of both pairs
+    const uint32_t B2 = pack2(p.B), Gf = fix2(p.G), If = fix2(p.I);
     const uint32_t base  = ((uint32_t)p.mismatch & 0xFFu) * 0x01010101u;     // 4 x mismatch
     const uint32_t delta = ((uint32_t)(p.mismatch ^ p.match)) & 0xFFu;       // flips one byte to match
-    const uint32_t nstripes = (Mmax + 15u) / 16u;
-    uint32_t* colp = p.col + tid;
-    const size_t  cstride = p.n_threads;
-
-    uint32_t bestkey = 0;               // packed (score << 4 | column-in-stripe)
-    uint32_t posA = 0, posB = 0;        // stripe << 16 | row of the best
-
-    for (uint32_t s = 0; s < nstripes; ++s)
+    const uint32_t block = k * 16u;
+    uint32_t TA[16], TB[16], H[16];
+    #pragma unroll
+    for (int j = 0; j < 16; ++j)
     {
-        const uint32_t block = s * 16u;
-        uint32_t TA[16], TB[16], H[16];
-        #pragma unroll
-        for (int j = 0; j < 16; ++j)
-        {
-            const uint32_t c = block + j;
-            uint32_t wa = 0x80808080u, wb = 0x80808080u;       // columns past the pattern: S = -128
-            if (c < MA) { const uint32_t q = sym_at_rt(p.P.sym, p.P.bits, pbA + c); dirtyA |= q > 3u; wa = base ^ (delta << (8u * (q & 3u))); }
-            if (c < MB) { const uint32_t q = sym_at_rt(p.P.sym, p.P.bits, pbB + c); dirtyB |= q > 3u; wb = base ^ (delta << (8u * (q & 3u))); }
-            TA[j] = wa; TB[j] = wb; H[j] = 0;
-        }
-        const bool svA = block < MA, svB = block < MB;
-        const bool rd = s > 0, wr = s + 1 < nstripes;
-        uint32_t carry = 0;
-        uint32_t cin_next = rd && Nmax ? colp[0] : 0u;
-        uint32_t tw = 0;
+        const uint32_t c = block + j;
+        uint32_t wa = 0x80808080u, wb = 0x80808080u;       // columns past the pattern: S = -128
+        if (live && c < MA) { const uint32_t q = sym_at_rt(p.P.sym, p.P.bits, pbA + c); dirtyA |= q > 3u; wa = base ^ (delta << (8u * (q & 3u))); }
+        if (live && c < MB) { const uint32_t q = sym_at_rt(p.P.sym, p.P.bits, pbB + c); dirtyB |= q > 3u; wb = base ^ (delta << (8u * (q & 3u))); }
+        TA[j] = wa; TB[j] = wb; H[j] = B2;
+    }
+    // halves that own cells in this stripe
+    const uint32_t smask = (block < MA ? 0x0000FFFFu : 0u) | (block < MB ? 0xFFFF0000u : 0u);
 
-        for (uint32_t i = 0; i < Nmax; ++i)
+    uint32_t bestkey = B2 << 4;          // packed (biased score << 4 | column in stripe)
+    uint32_t bestrow = 0;                // packed text rows of the best
+    uint32_t carry = B2, send = B2, tw = 0;
+
+    const uint32_t steps = __reduce_max_sync(0xFFFFFFFFu, live ? Nmax + p.lanes - 1 : 0u);
+    for (uint32_t t = 0; t < steps; ++t)
+    {
+        uint32_t cin = __shfl_up_sync(0xFFFFFFFFu, send, 1);
+        if (k == 0) cin = B2;                                   // column 0 of a LOCAL matrix is all zeros
+        const uint32_t i = t - k;                               // this lane's text row
+        if (live && i < Nmax)                                   // (unsigned: also false while t < k)
         {
-            const uint32_t cin = cin_next;
-            if (rd && i + 1 < Nmax) cin_next = colp[(size_t)(i + 1) * cstride];
-            if ((i & 7u) == 0) tw = my_text[(i >> 3) * DPF_THREADS];
+            if ((i & 7u) == 0) tw = my_text[i >> 3];
             const uint32_t nib = tw & 15u; tw >>= 4;
-            // selector: byte rA of profA -> byte 0 (+ sign replica in byte 1), byte rB of profB -> bytes 2,3
-            const uint32_t sel = ((nib & 3u) | ((nib & 12u) << 6)) * 0x11u + 0xC480u;
+            // selector: byte rA of profA -> byte 0, its sign -> byte 1; byte rB of profB -> byte 2, sign -> byte 3
+            const uint32_t sel = imad((nib & 3u) | ((nib & 12u) << 6), 0x11u, 0xC480u);
 
             uint32_t diag = carry, left = cin;
             carry = cin;
-            const uint32_t kb = bestkey & 0xFFF0FFF0u;
+            // running best with its column bits cleared, minus one: a cell of equal score compares greater
+            const uint32_t kb = __vadd2(bestkey & 0xFFF0FFF0u, 0xFFFFFFFFu);
             uint32_t acc = kb;
             uint32_t key[16];
             #pragma unroll
             for (int j = 0; j < 16; ++j)
             {
-                const uint32_t S = __byte_perm(TA[j], TB[j], sel);
-                const uint32_t u = __vadd2(H[j], G2);
+                const uint32_t S = prmt(TA[j], TB[j], sel);
+                const uint32_t u = imad(H[j], p.one, Gf);
                 const uint32_t v = __viaddmax_s16x2(diag, S, u);
-                const uint32_t h = __viaddmax_s16x2_relu(left, I2, v);
+                const uint32_t l = imad(left, p.one, If);
+                const uint32_t h = __vimax3_s16x2(l, v, B2);
                 diag = H[j]; H[j] = h; left = h;
-                asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(key[j]) : "r"(h), "r"(p.sixteen), "r"((uint32_t)j * 0x00010001u));
+                key[j] = imad(h, p.sixteen, (uint32_t)j * 0x00010001u);
             }
             #pragma unroll
             for (int j = 0; j < 16; j += 2) acc = __vimax3_s16x2(acc, key[j], key[j + 1]);
-            if (wr) colp[(size_t)i * cstride] = left;
+            send = left;
 
-            // a later row wins whenever its score is >= the best so far
-            bool keep_hi, keep_lo;
-            (void)__vibmax_s16x2(kb, acc, &keep_hi, &keep_lo);      // keep = kb >= acc  (nothing >= in this row)
-            const bool updA = !keep_lo && svA && i < NA;
-            const bool updB = !keep_hi && svB && i < NB;
-            const uint32_t rowpos = (s << 16) | i;
-            if (updA) { bestkey = (bestkey & 0xFFFF0000u) | (acc & 0x0000FFFFu); posA = rowpos; }
-            if (updB) { bestkey = (bestkey & 0x0000FFFFu) | (acc & 0xFFFF0000u); posB = rowpos; }
+            // halves whose row holds a score >= the best so far take the row (later rows win ties)
+            const uint32_t rmask = smask & ((i < NA ? 0x0000FFFFu : 0u) | (i < NB ? 0xFFFF0000u : 0u));
+            const uint32_t d = __vsub2(kb, acc);                          // < 0 in a half that improved
+            const uint32_t m = prmt(d, d, 0xBB99u) & rmask;               // 0xFFFF per improved, valid half
+            bestkey = (acc & m) | (bestkey & ~m);
+            bestrow = ((i * 0x00010001u) & m) | (bestrow & ~m);
         }
     }
 
-    // ---- epilogue
+    // ---- epilogue: the highest stripe among those with the best score wins (stripes are visited in order)
+    const uint32_t dmaskA = __ballot_sync(0xFFFFFFFFu, dirtyA), dmaskB = __ballot_sync(0xFFFFFFFFu, dirtyB);
+    const uint32_t gmask = (p.lanes >= 32 ? 0xFFFFFFFFu : ((1u << p.lanes) - 1u)) << gbase;
+    uint32_t wkA = 0, wkB = 0, wlaneA = 0, wlaneB = 0;
+    for (uint32_t d = 0; d < p.lanes; ++d)
+    {
+        const uint32_t src = min(gbase + d, 31u);
+        const uint32_t ok = __shfl_sync(0xFFFFFFFFu, bestkey, src);
+        const uint32_t sA = (ok & 0xFFFFu) >> 4, sB = ok >> 20;
+        if (sA >= (wkA >> 4)) { wkA = ok & 0xFFFFu; wlaneA = d; }
+        if (sB >= (wkB >> 4)) { wkB = ok >> 16; wlaneB = d; }
+    }
+    const uint32_t rowsA = __shfl_sync(0xFFFFFFFFu, bestrow, min(gbase + wlaneA, 31u));
+    const uint32_t rowsB = __shfl_sync(0xFFFFFFFFu, bestrow, min(gbase + wlaneB, 31u));
+    if (!live || k != 0) return;
+
     #pragma unroll
     for (int h = 0; h < 2; ++h)
     {
         if (h == 1 && !hasB) break;
         const uint32_t id = h ? idB : idA;
-        const bool dirty = h ? dirtyB : dirtyA;
-        if (dirty) { mark_dirty(p.worklist, id); continue; }
         const uint32_t M = h ? MB : MA, N = h ? NB : NA;
-        const uint32_t k = h ? (bestkey >> 16) : (bestkey & 0xFFFFu);
-        const uint32_t pos = h ? posB : posA;
+        bool dirty = ((h ? dmaskB : dmaskA) & gmask) != 0;
+        // key overflow; the other pair's rows are swept too, hence the couple's longer text in the bound
+        if (p.match > 0 && (uint64_t)p.match * min(M, Nmax) + (uint32_t)p.B >= 2047u) dirty = true;
+        if (dirty) { mark_dirty(p.worklist, id); continue; }
+        const uint32_t wk = h ? wkB : wkA;
+        const uint32_t stripe = h ? wlaneB : wlaneA;
+        const uint32_t row = h ? (rowsB >> 16) : (rowsA & 0xFFFFu);
+        const int32_t score = (int32_t)(wk >> 4) - p.B;
         nvb_best_sink out;
         if (M == 0 || N == 0) { out.score = NVB_SINK_MIN; out.sink_x = out.sink_y = 0xFFFFFFFFu; }
-        else if ((k >> 4) == 0) { out.score = 0; out.sink_x = N; out.sink_y = M; }   // all cells tie at 0: the last one visited
-        else { out.score = (int32_t)(k >> 4); out.sink_x = (pos & 0xFFFFu) + 1u; out.sink_y = (pos >> 16) * 16u + (k & 15u) + 1u; }
+        else if (score <= 0) { out.score = 0; out.sink_x = N; out.sink_y = M; }   // all cells tie at 0: the last one visited
+        else { out.score = score; out.sink_x = row + 1u; out.sink_y = stripe * 16u + (wk & 15u) + 1u; }
         p.sinks[id] = out;
     }
+}
+
+static bool full_geometry(uint32_t maxM, uint32_t maxN, uint32_t* lanes, uint32_t* tpw, uint32_t* tstride, size_t* smem)
+{
+    const uint32_t stripes = (maxM + 15u) / 16u;
+    if (stripes == 0 || stripes > 32u) return false;
+    *lanes = stripes; *tpw = 32u / stripes; *tstride = (maxN + 7u) / 8u;
+    *smem = (size_t)DPF_WARPS * *tpw * *tstride * sizeof(uint32_t);
+    return *smem <= 160u * 1024u;
 }
 
 bool dpf_full_score_supported(const nvb_aligner& a, const StrSet& P, const StrSet& T, uint32_t maxM, uint32_t maxN)
@@ -180,29 +221,33 @@ bool dpf_full_score_supported(const nvb_aligner& a, const StrSet& P, const StrSe
     if (a.kind != NVB_SMITH_WATERMAN && a.kind != NVB_EDIT_DISTANCE) return false;
     const Scheme s = make_scheme(a);
     if (s.match < -127 || s.match > 127 || s.mismatch < -127 || s.mismatch > 127) return false;
-    if (s.ga >= 0 || s.gb >= 0 || s.ga < -1024 || s.gb < -1024) return false;
-    if (maxN == 0 || maxM == 0 || maxN > 2048 || maxM > 65535) return false;
-    return true;
+    if (s.ga >= 0 || s.gb >= 0 || s.ga < -64 || s.gb < -64) return false;
+    if (maxN == 0 || maxM == 0 || maxN > 65535u) return false;
+    uint32_t lanes, tpw, tstride; size_t smem;
+    return full_geometry(maxM, maxN, &lanes, &tpw, &tstride, &smem);
 }
 
 int dpf_full_score(nvb_ctx* ctx, const nvb_aligner& a, StrSet P, StrSet T, nvb_best_sink* sinks, uint32_t maxM,
                    uint32_t maxN, uint32_t* worklist, void* temp, cudaStream_t st)
 {
-    (void)maxM;
+    (void)temp;
     const Scheme s = make_scheme(a);
     FullFastParams p;
-    p.P = P; p.T = T; p.sinks = sinks; p.col = (uint32_t*)temp; p.worklist = worklist;
-    p.n_pairs = P.count; p.n_threads = (P.count + 1) / 2;
-    p.tstride = (maxN + 7) / 8;
-    p.match = s.match; p.mismatch = s.mismatch; p.G = s.ga; p.I = s.gb; p.sixteen = 16;
-    const size_t smem = (size_t)p.tstride * DPF_THREADS * sizeof(uint32_t);
+    size_t smem;
+    if (!full_geometry(maxM, maxN, &p.lanes, &p.tpw, &p.tstride, &smem)) return NVB_ERR_UNSUPPORTED;
+    p.P = P; p.T = T; p.sinks = sinks; p.worklist = worklist;
+    p.n_pairs = P.count; p.n_tasks = (P.count + 1) / 2;
+    p.match = s.match; p.mismatch = s.mismatch; p.G = s.ga; p.I = s.gb;
+    p.B = -(s.ga < s.gb ? s.ga : s.gb);
+    p.one = 1; p.sixteen = 16;
     static bool attr_set = false;
     if (!attr_set)
     {
-        NVB_CUDA(ctx, cudaFuncSetAttribute(dpf_full_sw_local_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        NVB_CUDA(ctx, cudaFuncSetAttribute(dpf_full_sw_local_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
         attr_set = true;
     }
-    const uint32_t grid = (p.n_threads + DPF_THREADS - 1) / DPF_THREADS;
+    const uint32_t n_warps = (p.n_tasks + p.tpw - 1) / p.tpw;
+    const uint32_t grid = (n_warps + DPF_WARPS - 1) / DPF_WARPS;
     dpf_full_sw_local_kernel<<<grid, DPF_THREADS, smem, st>>>(p);
     NVB_LAUNCHED(ctx);
     return NVB_OK;

@@ -10,53 +10,66 @@
 #pragma once
 #include "common.cuh"
 
-struct __align__(32) FMBlock { uint32_t w[4]; uint32_t occ[4]; };
+struct FMBlock { uint32_t w0, w1, w2, w3; uint32_t o0, o1, o2, o3; };
 
 __device__ __forceinline__ FMBlock fm_load_block(const uint4* blk, uint32_t b)
 {
     FMBlock r;
     const void* p = (const void*)(blk + 2ull * b);
     asm volatile("ld.global.nc.L1::no_allocate.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-                 : "=r"(r.w[0]), "=r"(r.w[1]), "=r"(r.w[2]), "=r"(r.w[3]),
-                   "=r"(r.occ[0]), "=r"(r.occ[1]), "=r"(r.occ[2]), "=r"(r.occ[3])
+                 : "=r"(r.w0), "=r"(r.w1), "=r"(r.w2), "=r"(r.w3), "=r"(r.o0), "=r"(r.o1), "=r"(r.o2), "=r"(r.o3)
                  : "l"(p));
     return r;
 }
 
-// one bit (at the even bit of its 2-bit slot) per symbol of w equal to c
+// Position masks of a block, one entry per pos = 0..63, staged in shared memory by every kernel:
+// x = mask over the flag word of words 0|1, y = over words 2|3. Flags of an even word sit on the even
+// bit of each 2-bit slot, flags of an odd word on the odd bit, so two words share one popcount.
+#define FM_LUT_ENTRIES 64
+__device__ __forceinline__ uint32_t fm_top_bits(int32_t k) { return k > 0 ? 0xFFFFFFFFu << (32 - 2 * k) : 0u; }
+__device__ __forceinline__ void fm_lut_init(uint2* lut)
+{
+    for (uint32_t pos = threadIdx.x; pos < FM_LUT_ENTRIES; pos += blockDim.x)
+    {
+        const int32_t n = (int32_t)pos + 1;   // big-endian packing: symbol 0 sits in bits 31:30
+        uint2 m;
+        m.x = (fm_top_bits(min(n, 16)) & 0x55555555u) | (fm_top_bits(min(max(n - 16, 0), 16)) & 0xAAAAAAAAu);
+        m.y = (fm_top_bits(min(max(n - 32, 0), 16)) & 0x55555555u) | (fm_top_bits(min(max(n - 48, 0), 16)) & 0xAAAAAAAAu);
+        lut[pos] = m;
+    }
+    __syncthreads();
+}
+
+// one flag per symbol equal to c: on the even bit of the slot for w_even, on the odd bit for w_odd
+__device__ __forceinline__ uint32_t fm_eq_pair(uint32_t w_even, uint32_t w_odd, uint32_t cpat)
+{
+    const uint32_t x0 = w_even ^ cpat, x1 = w_odd ^ cpat;   // 00 where the symbol equals c
+    const uint32_t a = x0 | (x0 >> 1), b = x1 | (x1 << 1);
+    return ~((a & 0x55555555u) | (b & 0xAAAAAAAAu));
+}
+
 __device__ __forceinline__ uint32_t fm_eq_bits(uint32_t w, uint32_t cpat)
 {
-    const uint32_t x = w ^ cpat;              // 00 where the symbol equals c
+    const uint32_t x = w ^ cpat;
     return ~(x | (x >> 1)) & 0x55555555u;
 }
 
 // occurrences of c among symbols 0..pos (inclusive, pos in 0..63) of the block, plus the counter
-__device__ __forceinline__ uint32_t fm_block_rank(const FMBlock& b, uint32_t pos, uint32_t c)
+__device__ __forceinline__ uint32_t fm_block_rank(const FMBlock& b, uint32_t pos, uint32_t c, const uint2* lut)
 {
     const uint32_t cpat = c * 0x55555555u;
-    const int32_t  n    = (int32_t)pos + 1;   // symbols to count
-    uint32_t acc = 0;
-    #pragma unroll
-    for (int wi = 0; wi < 4; wi += 2)
-    {
-        const int32_t n0 = min(max(n - 16 * wi, 0), 16);
-        const int32_t n1 = min(max(n - 16 * (wi + 1), 0), 16);
-        // big-endian packing: symbol 0 sits in bits 31:30 -> keep the top 2*n bits
-        const uint32_t m0 = (uint32_t)(0xFFFFFFFF00000000ull >> (2 * n0));
-        const uint32_t m1 = (uint32_t)(0xFFFFFFFF00000000ull >> (2 * n1));
-        const uint32_t t0 = fm_eq_bits(b.w[wi], cpat) & m0;
-        const uint32_t t1 = fm_eq_bits(b.w[wi + 1], cpat) & m1;
-        acc += __popc(t0 | (t1 << 1));
-    }
-    const uint32_t base = c == 0 ? b.occ[0] : c == 1 ? b.occ[1] : c == 2 ? b.occ[2] : b.occ[3];
-    return base + acc;
+    const uint2 m = lut[pos];
+    const uint32_t f01 = fm_eq_pair(b.w0, b.w1, cpat) & m.x;
+    const uint32_t f23 = fm_eq_pair(b.w2, b.w3, cpat) & m.y;
+    const uint32_t base = (c & 2u) ? ((c & 1u) ? b.o3 : b.o2) : ((c & 1u) ? b.o1 : b.o0);
+    return base + __popc(f01) + __popc(f23);
 }
 
 // all four symbol counts (rank4: nvbio/fmindex/rank_dictionary_inl.h:450-478)
-__device__ __forceinline__ uint4 fm_block_rank4(const FMBlock& b, uint32_t pos)
+__device__ __forceinline__ uint4 fm_block_rank4(const FMBlock& b, uint32_t pos, const uint2* lut)
 {
-    return make_uint4(fm_block_rank(b, pos, 0), fm_block_rank(b, pos, 1),
-                      fm_block_rank(b, pos, 2), fm_block_rank(b, pos, 3));
+    return make_uint4(fm_block_rank(b, pos, 0, lut), fm_block_rank(b, pos, 1, lut),
+                      fm_block_rank(b, pos, 2, lut), fm_block_rank(b, pos, 3, lut));
 }
 
 // A rank request after the FM-index special cases (fmindex_inl.h:31-47):
@@ -74,33 +87,34 @@ __device__ __forceinline__ FMReq fm_make_req(const FMView& f, uint32_t k, uint32
     return r;
 }
 
-__device__ __forceinline__ uint32_t fm_rank1(const FMView& f, uint32_t k, uint32_t c)
+__device__ __forceinline__ uint32_t fm_rank1(const FMView& f, uint32_t k, uint32_t c, const uint2* lut)
 {
     const FMReq q = fm_make_req(f, k, c);
     if (!q.load) return q.value;
     const FMBlock b = fm_load_block(f.blk, q.k >> 6);
-    return fm_block_rank(b, q.k & 63u, c);
+    return fm_block_rank(b, q.k & 63u, c, lut);
 }
 
 // rank(fmi, (x,y), c): both blocks are requested before either is consumed (2 loads in flight);
 // when both indices fall in one block it is fetched once (rank_dictionary_inl.h:425-448)
-__device__ __forceinline__ uint2 fm_rank2(const FMView& f, uint32_t x, uint32_t y, uint32_t c)
+__device__ __forceinline__ uint2 fm_rank2(const FMView& f, uint32_t x, uint32_t y, uint32_t c, const uint2* lut)
 {
     const FMReq qx = fm_make_req(f, x, c);
     const FMReq qy = fm_make_req(f, y, c);
-    FMBlock bx, by;
     const bool same = qx.load && qy.load && ((qx.k >> 6) == (qy.k >> 6));
+    FMBlock by = { 0, 0, 0, 0, 0, 0, 0, 0 }, bx = by;
     if (qy.load) by = fm_load_block(f.blk, qy.k >> 6);
     if (qx.load && !same) bx = fm_load_block(f.blk, qx.k >> 6);
+    if (same) bx = by;
     uint2 r;
-    r.y = qy.load ? fm_block_rank(by, qy.k & 63u, c) : qy.value;
-    r.x = qx.load ? fm_block_rank(same ? by : bx, qx.k & 63u, c) : qx.value;
+    r.y = qy.load ? fm_block_rank(by, qy.k & 63u, c, lut) : qy.value;
+    r.x = qx.load ? fm_block_rank(bx, qx.k & 63u, c, lut) : qx.value;
     return r;
 }
 
 __device__ __forceinline__ uint32_t fm_bwt_symbol(const FMBlock& b, uint32_t pos)
 {
     const uint32_t wi = pos >> 4;
-    const uint32_t w = wi == 0 ? b.w[0] : wi == 1 ? b.w[1] : wi == 2 ? b.w[2] : b.w[3];
+    const uint32_t w = (wi & 2u) ? ((wi & 1u) ? b.w3 : b.w2) : ((wi & 1u) ? b.w1 : b.w0);
     return (w >> (30u - 2u * (pos & 15u))) & 3u;
 }

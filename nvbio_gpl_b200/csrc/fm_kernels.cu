@@ -24,6 +24,8 @@ __global__ void __launch_bounds__(FM_THREADS)
 fm_match_kernel(const FMView f, const StrSet q, uint32_t* __restrict__ ranges)
 {
     __shared__ __align__(16) uint8_t s_sym[FM_STAGE_BYTES];
+    __shared__ uint2 s_lut[FM_LUT_ENTRIES];
+    fm_lut_init(s_lut);
     const uint32_t first = blockIdx.x * FM_THREADS;
     const uint32_t tid   = first + threadIdx.x;
     const uint32_t last  = min(first + FM_THREADS, q.count);
@@ -59,7 +61,7 @@ fm_match_kernel(const FMView f, const StrSet q, uint32_t* __restrict__ ranges)
         const uint32_t c = staged ? (uint32_t)s_sym[skew + (beg - span_begin) + (uint32_t)i]
                                   : sym_at<BITS>(q.sym, beg + (uint32_t)i);
         if (c > 3u) { x = 1; y = 0; break; }
-        const uint2 r = fm_rank2(f, x - 1u, y, c);
+        const uint2 r = fm_rank2(f, x - 1u, y, c, s_lut);
         x = f.L2[c] + r.x + 1u;
         y = f.L2[c] + r.y;
     }
@@ -70,19 +72,23 @@ __global__ void __launch_bounds__(FM_THREADS)
 fm_rank_kernel(const FMView f, const uint32_t* __restrict__ ranges, const uint8_t* __restrict__ c,
                uint32_t n, uint32_t* __restrict__ out)
 {
+    __shared__ uint2 s_lut[FM_LUT_ENTRIES];
+    fm_lut_init(s_lut);
     const uint32_t tid = blockIdx.x * FM_THREADS + threadIdx.x;
     if (tid >= n) return;
     const uint2 rg = *(const uint2*)(ranges + 2 * (size_t)tid);
     const uint32_t cc = c[tid] & 3u;
     uint2 r;
-    if (rg.x == rg.y) { r.x = r.y = fm_rank1(f, rg.x, cc); }   // fmindex_inl.h:66-70
-    else r = fm_rank2(f, rg.x, rg.y, cc);
+    if (rg.x == rg.y) { r.x = r.y = fm_rank1(f, rg.x, cc, s_lut); }   // fmindex_inl.h:66-70
+    else r = fm_rank2(f, rg.x, rg.y, cc, s_lut);
     *(uint2*)(out + 2 * (size_t)tid) = r;
 }
 
 __global__ void __launch_bounds__(FM_THREADS)
 fm_rank4_kernel(const FMView f, const uint32_t* __restrict__ k, uint32_t n, uint32_t* __restrict__ out)
 {
+    __shared__ uint2 s_lut[FM_LUT_ENTRIES];
+    fm_lut_init(s_lut);
     const uint32_t tid = blockIdx.x * FM_THREADS + threadIdx.x;
     if (tid >= n) return;
     uint32_t kk = k[tid];
@@ -95,7 +101,7 @@ fm_rank4_kernel(const FMView f, const uint32_t* __restrict__ k, uint32_t n, uint
         if (kk != 0xFFFFFFFFu)
         {
             const FMBlock b = fm_load_block(f.blk, kk >> 6);
-            r = fm_block_rank4(b, kk & 63u);
+            r = fm_block_rank4(b, kk & 63u, s_lut);
         }
     }
     *(uint4*)(out + 4 * (size_t)tid) = r;
@@ -103,7 +109,7 @@ fm_rank4_kernel(const FMView f, const uint32_t* __restrict__ k, uint32_t n, uint
 
 // LF-walk from SA row j to the nearest sampled row (j % 16 == 0). One block load per step: the
 // BWT symbol and its rank come from the same 32-byte block.
-__device__ __forceinline__ uint2 fm_locate_walk_one(const FMView& f, uint32_t j)
+__device__ __forceinline__ uint2 fm_locate_walk_one(const FMView& f, uint32_t j, const uint2* lut)
 {
     uint32_t t = 0;
     while (j & 15u)
@@ -116,7 +122,7 @@ __device__ __forceinline__ uint2 fm_locate_walk_one(const FMView& f, uint32_t j)
             // rank(fmi, j, c) with the FM special cases (fmindex_inl.h:31-47)
             uint32_t r;
             if (j == f.length) r = f.L2[c + 1] - f.L2[c];
-            else r = fm_block_rank(b, jj & 63u, c);
+            else r = fm_block_rank(b, jj & 63u, c, lut);
             j = f.L2[c] + r;
         }
         else j = 0;
@@ -128,18 +134,22 @@ __device__ __forceinline__ uint2 fm_locate_walk_one(const FMView& f, uint32_t j)
 __global__ void __launch_bounds__(FM_THREADS)
 fm_locate_kernel(const FMView f, const uint32_t* __restrict__ rows, uint32_t n, uint32_t* __restrict__ pos)
 {
+    __shared__ uint2 s_lut[FM_LUT_ENTRIES];
+    fm_lut_init(s_lut);
     const uint32_t tid = blockIdx.x * FM_THREADS + threadIdx.x;
     if (tid >= n) return;
-    const uint2 w = fm_locate_walk_one(f, rows[tid]);
+    const uint2 w = fm_locate_walk_one(f, rows[tid], s_lut);
     pos[tid] = __ldg(f.ssa + (w.x >> 4)) + w.y;
 }
 
 __global__ void __launch_bounds__(FM_THREADS)
 fm_locate_walk_kernel(const FMView f, const uint32_t* __restrict__ rows, uint32_t n, uint32_t* __restrict__ walk)
 {
+    __shared__ uint2 s_lut[FM_LUT_ENTRIES];
+    fm_lut_init(s_lut);
     const uint32_t tid = blockIdx.x * FM_THREADS + threadIdx.x;
     if (tid >= n) return;
-    *(uint2*)(walk + 2 * (size_t)tid) = fm_locate_walk_one(f, rows[tid]);
+    *(uint2*)(walk + 2 * (size_t)tid) = fm_locate_walk_one(f, rows[tid], s_lut);
 }
 
 __global__ void __launch_bounds__(FM_THREADS)
