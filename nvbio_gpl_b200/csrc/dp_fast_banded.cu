@@ -46,6 +46,22 @@ __device__ __forceinline__ uint32_t b_imad(uint32_t a, uint32_t b, uint32_t c)
 __device__ __forceinline__ int32_t b_lo(uint32_t x) { return (int32_t)(int16_t)(x & 0xFFFFu); }
 __device__ __forceinline__ int32_t b_hi(uint32_t x) { return (int32_t)(int16_t)(x >> 16); }
 
+// mask of the low n bytes of a word (n <= 0: none, n >= 4: all)
+__device__ __forceinline__ uint32_t b_bytemask(int32_t n)
+{ return n <= 0 ? 0u : n >= 4 ? 0xFFFFFFFFu : (1u << (8 * n)) - 1u; }
+// 4 symbols starting at an arbitrarily aligned address, from one or two aligned words; `remain` = symbols
+// left in the string from ptr on (nothing is read at or past the aligned word that holds the string's end)
+__device__ __forceinline__ uint32_t b_load4(const uint8_t* ptr, uint32_t remain, uint32_t mask)
+{
+    if (mask == 0u) return 0u;
+    const uintptr_t a = (uintptr_t)ptr;
+    const uint32_t sh = (uint32_t)(a & 3u);
+    const uint32_t* w = (const uint32_t*)(a - sh);
+    const uint32_t lo = __ldg(w);
+    const uint32_t hi = (sh != 0u && remain + sh > 4u) ? __ldg(w + 1) : 0u;
+    return __funnelshift_r(lo, hi, 8u * sh);
+}
+
 #define DPB_INF2 0x83008300u   // packed -32000: "minus infinity" of the F band (never wins, never wraps)
 
 template <int W, int TYPE, bool GOTOH>
@@ -90,35 +106,45 @@ dpf_banded_kernel(const BandFastParams p)
     bool dirtyA = MA == 0 || MA > p.rows_cap, dirtyB = MB == 0 || MB > p.rows_cap;
     const uint32_t rows = min(Mmax, p.rows_cap);
     {
+        // word-wise: a lane builds 4 consecutive stream bytes from one (funnel-shifted) 32-bit word of each
+        // pair; ~25 instructions per 128 positions, 4 independent loads per lane and iteration
         const uint32_t wbase = threadIdx.x & ~31u;
+        const uint8_t* Psym = p.P.sym; const uint8_t* Tsym = p.T.sym;
+        uint32_t dmA = 0, dmB = 0;
+        #pragma unroll 2
         for (uint32_t c = 0; c < 32; ++c)
         {
             const uint32_t c_rows = __shfl_sync(0xFFFFFFFFu, rows, c);
-            if (c_rows == 0) continue;
             const uint32_t c_pbA = __shfl_sync(0xFFFFFFFFu, pbA, c), c_pbB = __shfl_sync(0xFFFFFFFFu, pbB, c);
             const uint32_t c_tbA = __shfl_sync(0xFFFFFFFFu, tbA, c), c_tbB = __shfl_sync(0xFFFFFFFFu, tbB, c);
             const uint32_t c_MA = __shfl_sync(0xFFFFFFFFu, MA, c), c_MB = __shfl_sync(0xFFFFFFFFu, MB, c);
             const uint32_t c_NA = __shfl_sync(0xFFFFFFFFu, NA, c), c_NB = __shfl_sync(0xFFFFFFFFu, NB, c);
-            uint8_t* c_pat = s_pat + (size_t)(wbase + c) * p.rows_cap;
-            uint8_t* c_txt = s_txt + (size_t)(wbase + c) * p.text_cap;
-            bool dA = false, dB = false;
-            for (uint32_t i = lane; i < c_rows; i += 32)
+            uint32_t* c_pat = (uint32_t*)(s_pat + (size_t)(wbase + c) * p.rows_cap);
+            uint32_t* c_txt = (uint32_t*)(s_txt + (size_t)(wbase + c) * p.text_cap);
+            uint32_t bad = 0;
+            for (uint32_t i = 4 * lane; i < c_rows; i += 128)
             {
-                const uint32_t qA = i < c_MA ? sym_at_rt(p.P.sym, p.P.bits, c_pbA + i) : 0u;
-                const uint32_t qB = i < c_MB ? sym_at_rt(p.P.sym, p.P.bits, c_pbB + i) : 0u;
-                dA |= qA > 3u; dB |= qB > 3u;
-                c_pat[i] = (uint8_t)((qA & 3u) | ((qB & 3u) << 2));
+                const uint32_t mA = b_bytemask((int32_t)(c_MA - i)), mB = b_bytemask((int32_t)(c_MB - i));
+                const uint32_t a = b_load4(Psym + c_pbA + i, c_MA - i, mA) & mA;
+                const uint32_t b = b_load4(Psym + c_pbB + i, c_MB - i, mB) & mB;
+                bad |= ((a & 0xFCFCFCFCu) ? 1u : 0u) | ((b & 0xFCFCFCFCu) ? 2u : 0u);
+                c_pat[i >> 2] = (a & 0x03030303u) | ((b & 0x03030303u) << 2);
             }
-            for (uint32_t q = lane; q < c_rows + W - 1; q += 32)
+            const uint32_t c_text = c_rows ? c_rows + W - 1 : 0u;
+            for (uint32_t q = 4 * lane; q < c_text; q += 128)
             {
-                uint32_t rA = 4u, rB = 4u;                          // 4 = past the end: mismatches everything
-                if (q < c_NA) { rA = sym_at_rt(p.T.sym, p.T.bits, c_tbA + q); dA |= rA > 3u; rA &= 3u; }
-                if (q < c_NB) { rB = sym_at_rt(p.T.sym, p.T.bits, c_tbB + q); dB |= rB > 3u; rB &= 3u; }
-                c_txt[q] = (uint8_t)(rA | (rB << 3));
+                const uint32_t mA = b_bytemask((int32_t)(c_NA - q)), mB = b_bytemask((int32_t)(c_NB - q));
+                const uint32_t a = b_load4(Tsym + c_tbA + q, c_NA - q, mA) & mA;
+                const uint32_t b = b_load4(Tsym + c_tbB + q, c_NB - q, mB) & mB;
+                bad |= ((a & 0xFCFCFCFCu) ? 1u : 0u) | ((b & 0xFCFCFCFCu) ? 2u : 0u);
+                // past the end of a text: code 4 = mismatches everything
+                const uint32_t wa = (a & 0x03030303u) | (0x04040404u & ~mA), wb = (b & 0x03030303u) | (0x04040404u & ~mB);
+                c_txt[q >> 2] = wa | (wb << 3);
             }
-            const bool anyA = __any_sync(0xFFFFFFFFu, dA), anyB = __any_sync(0xFFFFFFFFu, dB);
-            if (lane == c) { dirtyA |= anyA; dirtyB |= anyB; }
+            dmA |= (bad & 1u) << c; dmB |= ((bad >> 1) & 1u) << c;
         }
+        dmA = __reduce_or_sync(0xFFFFFFFFu, dmA); dmB = __reduce_or_sync(0xFFFFFFFFu, dmB);
+        dirtyA |= (dmA >> lane) & 1u; dirtyB |= (dmB >> lane) & 1u;
         __syncwarp();
     }
     if (!live) return;
@@ -129,16 +155,22 @@ dpf_banded_kernel(const BandFastParams p)
     const uint32_t Af = b_fix2(p.ga);                 // SW: top + deletion ; Gotoh: H + gap_open
     const uint32_t Bf = b_fix2(p.gb);                 // SW: left + insertion
     const uint32_t ext2 = b_pack2(p.gb);              // Gotoh: gap extension (added inside VIADDMNMX)
+    const uint32_t ins2 = ext2;                       // SW: insertion, likewise
 
-    uint32_t X[W], F[W], TA[W], TB[W], fin[W];
+    // rows are unrolled RU at a time: inside a group the window slots are static (slot = row-in-group + band
+    // cell), after it the window is shifted down by RU (keeps the loop body within the instruction cache)
+    constexpr int RU = W > 8 ? 5 : W;
+    constexpr int WS = W + RU - 1;
+    uint32_t X[W], F[W], TA[WS], TB[WS], fin[W];
     #pragma unroll
     for (int j = 0; j < W; ++j)
     {
         int32_t h0 = 0;                                                     // init_row_zero
         if (TYPE == T_GLOBAL) h0 = GOTOH ? (j > 0 ? p.ga + (j - 1) * p.gb : 0) : j * p.ga;
         X[j] = b_pack2(h0 + p.bias); F[j] = DPB_INF2; fin[j] = X[j];
-        TA[j] = 0; TB[j] = 0;
     }
+    #pragma unroll
+    for (int j = 0; j < WS; ++j) { TA[j] = 0; TB[j] = 0; }
     #pragma unroll
     for (int j = 0; j < W - 1; ++j)
     {
@@ -147,10 +179,10 @@ dpf_banded_kernel(const BandFastParams p)
     }
     uint32_t bestkey = B2 << 4, bestrow = 0;
 
-    for (uint32_t i0 = 0; i0 < rows; i0 += W)
+    for (uint32_t i0 = 0; i0 < rows; i0 += RU)
     {
         #pragma unroll
-        for (int r = 0; r < W; ++r)
+        for (int r = 0; r < RU; ++r)
         {
             const uint32_t i = i0 + r;
             if (i < rows)
@@ -158,7 +190,7 @@ dpf_banded_kernel(const BandFastParams p)
                 // the text position entering the band on this row takes the slot of the one that left
                 {
                     const uint2 pr = lut_prof[my_txt[i + W - 1]];
-                    TA[(r + W - 1) % W] = pr.x; TB[(r + W - 1) % W] = pr.y;
+                    TA[r + W - 1] = pr.x; TB[r + W - 1] = pr.y;
                 }
                 const uint32_t sel = lut_sel[my_pat[i]];
                 uint32_t left = 0, E = 0;
@@ -166,7 +198,7 @@ dpf_banded_kernel(const BandFastParams p)
                 #pragma unroll
                 for (int j = 0; j < W; ++j)
                 {
-                    const uint32_t S = b_prmt(TA[(r + j) % W], TB[(r + j) % W], sel);
+                    const uint32_t S = b_prmt(TA[r + j], TB[r + j], sel);
                     uint32_t h;
                     if (!GOTOH)
                     {
@@ -180,8 +212,8 @@ dpf_banded_kernel(const BandFastParams p)
                         {
                             const uint32_t u = b_imad(X[j + 1 < W ? j + 1 : j], p.one, Af);
                             const uint32_t v = __viaddmax_s16x2(X[j], S, u);
-                            const uint32_t l = b_imad(left, p.one, Bf);
-                            h = LOCAL ? __vimax3_s16x2(l, v, B2) : __vmaxs2(l, v);
+                            if (LOCAL) h = __vimax3_s16x2(b_imad(left, p.one, Bf), v, B2);
+                            else       h = __viaddmax_s16x2(left, ins2, v);                        // max(left + I, v)
                         }
                         else
                         {
@@ -234,6 +266,8 @@ dpf_banded_kernel(const BandFastParams p)
                 }
             }
         }
+        #pragma unroll
+        for (int j = 0; j < W - 1; ++j) { TA[j] = TA[j + RU]; TB[j] = TB[j + RU]; }
     }
 
     // ---- epilogue
@@ -293,8 +327,9 @@ static bool band_geometry(uint32_t band, uint32_t maxM, uint32_t* rows_cap, uint
 
 bool dpf_banded_score_supported(const nvb_aligner& a, uint32_t band, const StrSet& P, const StrSet& T, uint32_t maxM, uint32_t maxN)
 {
-    (void)P; (void)T; (void)maxN;
+    (void)maxN;
     if (band != 7 && band != 15) return false;
+    if (P.bits != 8 || T.bits != 8) return false;       // packed sets take the int32 kernels
     const Scheme s = make_scheme(a);
     if (s.match < -127 || s.match > 127 || s.mismatch < -127 || s.mismatch > 127) return false;
     if (s.ga >= 0 || s.gb >= 0 || s.ga < -512 || s.gb < -512) return false;
