@@ -137,7 +137,7 @@ class Context:
         return int(lib().nvb_last_paths(self.h))
 
     def force_generic(self, on):
-        lib().nvb_force_generic(self.h, 1 if on else 0)
+        lib().nvb_force_generic(self.h, int(on))
 
     def synchronize(self):
         check(lib().nvb_ctx_synchronize(self.h), self.h)

@@ -79,7 +79,7 @@ extern "C" int nvb_batch_score(nvb_ctx* ctx, nvb_aligner a, nvb_string_set patte
     const TempPlan p = plan(NVB_OP_SCORE, a, 0, 0, maxM, maxN);
     ctx->last_paths = 0;
 
-    if (!ctx->force_generic && temp && batch_pairs(p, temp_bytes, n) >= n && dpf_full_score_supported(a, P, T, maxM, maxN))
+    if (ctx->force_generic != 1 && temp && batch_pairs(p, temp_bytes, n) >= n && dpf_full_score_supported(a, P, T, maxM, maxN))
     {
         // packed DPX kernel; pairs it cannot represent exactly are appended to the ctx worklist and
         // re-scored by the int32 kernel, which reads the count on the device (no host sync)
@@ -133,12 +133,14 @@ extern "C" int nvb_batch_banded_score(nvb_ctx* ctx, nvb_aligner a, uint32_t band
     cudaStream_t s = (cudaStream_t)stream;
     const StrSet P = make_set(patterns), T = make_set(texts);
     ctx->last_paths = 0;
-    if (!ctx->force_generic && dpf_banded_score_supported(a, band, P, T, maxM, maxN))
+    const bool use_b2 = ctx->force_generic == 0 && dpb2_score_supported(a, band, P, T, maxM, maxN);
+    if (use_b2 || (ctx->force_generic != 1 && dpf_banded_score_supported(a, band, P, T, maxM, maxN)))   // force_generic: 1 = int32 kernels only, 2 = no sheared-coordinate kernels
     {
         uint32_t* wl = nullptr;
         if ((rc = nvb_worklist(ctx, n, &wl))) return rc;
         NVB_CUDA(ctx, cudaMemsetAsync(wl, 0, sizeof(uint32_t), s));
-        if ((rc = dpf_banded_score(ctx, a, band, P, T, sinks, maxM, maxN, wl, s))) return rc;
+        if (use_b2) { if ((rc = dpb2_score(ctx, a, band, P, T, sinks, maxM, maxN, wl, s))) return rc; ctx->last_paths |= 4u; }
+        else if ((rc = dpf_banded_score(ctx, a, band, P, T, sinks, maxM, maxN, wl, s))) return rc;
         ctx->last_paths |= 1u;
         return dpg_banded_score(ctx, a, band, P, T, wl + 1, wl, 0, n, sinks, s);
     }

@@ -14,3 +14,7 @@ int  dpf_full_score(nvb_ctx* ctx, const nvb_aligner& a, StrSet P, StrSet T, nvb_
 bool dpf_banded_score_supported(const nvb_aligner& a, uint32_t band, const StrSet& P, const StrSet& T, uint32_t maxM, uint32_t maxN);
 int  dpf_banded_score(nvb_ctx* ctx, const nvb_aligner& a, uint32_t band, StrSet P, StrSet T, nvb_best_sink* sinks,
                       uint32_t maxM, uint32_t maxN, uint32_t* worklist, cudaStream_t s);
+// sheared-coordinate banded kernels (dp_band2.cu): GLOBAL / SEMI_GLOBAL, bands 7 and 15, 8-bit string sets
+bool dpb2_score_supported(const nvb_aligner& a, uint32_t band, const StrSet& P, const StrSet& T, uint32_t maxM, uint32_t maxN);
+int  dpb2_score(nvb_ctx* ctx, const nvb_aligner& a, uint32_t band, StrSet P, StrSet T, nvb_best_sink* sinks,
+                uint32_t maxM, uint32_t maxN, uint32_t* worklist, cudaStream_t s);

@@ -15,12 +15,13 @@ pytestmark = pytest.mark.gpu
 CASES = [(k, sc, ty) for k in (po.ED, po.SW, po.GOTOH) for sc in util.SCHEMES[k] for ty in (0, 1, 2)]
 
 
-@pytest.fixture(params=[False, True], ids=["auto", "generic"])
+@pytest.fixture(params=[0, 1, 2], ids=["auto", "generic", "v1"])
 def ctx(request):
+    """0 = the library's own choice, 1 = int32 kernels only, 2 = packed kernels without the sheared-coordinate ones"""
     c = nvb.Context.default(0)
     c.force_generic(request.param)
     yield c
-    c.force_generic(False)
+    c.force_generic(0)
 
 
 @pytest.mark.parametrize("kind,scheme,ty", CASES)
@@ -73,6 +74,27 @@ def test_symbols_with_n_and_long_shapes(oracle, ctx):
         assert (got == oracle.banded_score(oa, 15, P, Po, T, To)).all()
         got = gu.tb_np(nvb.batch_banded_alignment_traceback(a, 15, 16, ps, ts))
         assert gu.tb_equal(got, oracle.banded_traceback(oa, 15, 16, P, Po, T, To))
+
+
+@pytest.mark.parametrize("kind,scheme", [(po.ED, (0, -1, -1, -1)), (po.SW, (2, -1, -1, -1)), (po.SW, (1, -3, -2, -2)),
+                                         (po.SW, (3, -2, -4, -1)), (po.GOTOH, (0, -5, -8, -3)), (po.GOTOH, (2, -6, -5, -3)),
+                                         (po.GOTOH, (1, -1, -1, -1)), (po.GOTOH, (2, -7, -4, -3))])
+@pytest.mark.parametrize("ty", [0, 2])
+def test_banded_long_ragged(oracle, ctx, kind, scheme, ty):
+    """patterns spanning several staging chunks, couples of unequal lengths, texts ending inside the band, a few N"""
+    rng = np.random.default_rng(hash((kind, scheme, ty, 7)) & 0xFFFF)
+    a, oa = gu.aligner(kind, ty, scheme), po.aligner(kind, ty, scheme)
+    for band in (15, 7):
+        for alpha in (4, 2):
+            P, Po, T, To = util.rand_pairs(rng, 1501, (1, 330), util.banded_text_len(rng, ty, band), alpha)
+            if alpha == 4:
+                P = P.copy(); T = T.copy()
+                P[rng.integers(0, len(P), 20)] = 4
+                T[rng.integers(0, len(T), 20)] = rng.integers(4, 256, 20)
+            ps, ts = gu.sset(P, Po), gu.sset(T, To)
+            got = gu.sinks_np(nvb.batch_banded_alignment_score(a, band, ps, ts))
+            want = oracle.banded_score(oa, band, P, Po, T, To)
+            assert (got == want).all(), (band, alpha, np.nonzero(got != want)[0][:5])
 
 
 def test_empty_and_degenerate(oracle, ctx):

@@ -16,7 +16,7 @@ __device__ __forceinline__ uint32_t op_max3(uint32_t a, uint32_t b, uint32_t c) 
 __device__ __forceinline__ uint32_t op_max2(uint32_t a, uint32_t b) { return __vmaxs2(a, b); }
 __device__ __forceinline__ uint32_t op_add2(uint32_t a, uint32_t b) { return __vadd2(a, b); }
 __device__ __forceinline__ uint32_t op_hmax(uint32_t a, uint32_t b) { uint32_t d; asm volatile("max.f16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b)); return d; }
-__device__ __forceinline__ uint32_t op_hmax3(uint32_t a, uint32_t b, uint32_t c) { uint32_t d; asm volatile("max.f16x2 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c)); return d; }
+__device__ __forceinline__ uint32_t op_hmax3(uint32_t a, uint32_t b, uint32_t c) { uint32_t d; d = op_hmax(op_hmax(a, b), c); return d; }
 __device__ __forceinline__ uint32_t op_hadd(uint32_t a, uint32_t b) { uint32_t d; asm volatile("add.rn.f16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b)); return d; }
 __device__ __forceinline__ uint32_t op_hfma(uint32_t a, uint32_t b, uint32_t c) { uint32_t d; asm volatile("fma.rn.f16x2 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c)); return d; }
 __device__ __forceinline__ uint32_t op_hset(uint32_t a, uint32_t b) { uint32_t d; asm volatile("set.eq.f16x2.f16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b)); return d; }
