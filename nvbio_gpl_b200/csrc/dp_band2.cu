@@ -19,13 +19,14 @@
 // plain 32-bit adds that never carry between the halves; the true score is recovered in the epilogue:
 // H = stored - bias + alpha*M + beta*j.
 //
-// Staging: pattern rows and text positions are consumed front to back, so each thread copies its four strings
-// R rows at a time with 16-byte loads into a private shared-memory slot (thread stride = 4 mod 8 bytes: byte
-// loads of a warp fall in distinct banks) and the row loop reads them back with immediate-offset LDS.U8. The
-// profile of a pattern row comes from a 16-entry shared table, the selector of a text position is two IMADs.
+// Staging: pattern rows and text positions are consumed front to back, one byte per row, so each of a thread's
+// four strings streams through a private 64-byte shared-memory ring (struct Stream below): one 16-byte global load
+// per string and row group, issued a whole group ahead of its use, and immediate-offset LDS.U8 in the row loop.
+// The profile of a pattern row comes from a 16-entry shared table, the selector of a text position is two IMADs.
 // A thread whose 16-byte blocks held a byte > 3 re-checks its own strings exactly and sends both of its pairs
 // to the int32 kernel through the worklist (dp_fast.h).
 #include "dp_fast.h"
+#include <cstdlib>
 
 #define B2_THREADS 128
 #define B2_INF2    0x83008300u    // packed -32000: F'' before any gap was opened (only ever max'ed)
@@ -41,7 +42,7 @@ struct Band2Params
     int32_t        init_rest;
     uint32_t       s_match, s_mis;      // profile bytes S' (SW) / S'' (Gotoh), 0..127
     int32_t        d;                   // Gotoh: go - ge (<= 0)
-    uint32_t       one;
+    uint32_t       one, k8, k32;        // runtime 1, 8, 32
 };
 
 __device__ __forceinline__ uint32_t c_pack2(int32_t v) { return ((uint32_t)v & 0xFFFFu) * 0x00010001u; }
@@ -53,48 +54,157 @@ __device__ __forceinline__ uint32_t c_imad(uint32_t a, uint32_t b, uint32_t c)
 __device__ __forceinline__ int32_t c_lo(uint32_t x) { return (int32_t)(int16_t)(x & 0xFFFFu); }
 __device__ __forceinline__ int32_t c_hi(uint32_t x) { return (int32_t)(int16_t)(x >> 16); }
 
-// copies string bytes [c, c+span) (clipped to the string) into `slot` in 16-byte blocks, zero-fills the rest of
-// the span, ORs every loaded word into `seen`; returns the offset of byte c inside the slot
-template <int MAXBLK>
-__device__ __forceinline__ uint32_t c_stage(const uint8_t* sym, uint32_t beg, uint32_t L, uint32_t c, uint32_t span,
-                                            uint8_t* slot, uint32_t& seen)
-{
-    const uint8_t* a = sym + (size_t)beg + c;
-    const uint32_t lead = (uint32_t)((uintptr_t)a & 15u);
-    const uint32_t avail = L > c ? min(L - c, span) : 0u;
-    const uint4* g = (const uint4*)(a - lead);
-    const uint32_t nblk = avail ? (lead + avail + 15u) >> 4 : 0u;
-    #pragma unroll
-    for (int m = 0; m < MAXBLK; ++m)
-    {
-        if ((uint32_t)m < nblk)
-        {
-            const uint4 v = __ldg(g + m);
-            seen |= v.x | v.y | v.z | v.w;
-            uint32_t* s = (uint32_t*)(slot + 16 * m);
-            s[0] = v.x; s[1] = v.y; s[2] = v.z; s[3] = v.w;
-        }
-    }
-    for (uint32_t x = avail; x < span; ++x) slot[lead + x] = 0;
-    return lead;
-}
-
 __device__ __noinline__ bool c_has_high_symbol(const uint8_t* sym, uint32_t beg, uint32_t L)
 {
     for (uint32_t x = 0; x < L; ++x) if (sym[(size_t)beg + x] > 3u) return true;
     return false;
 }
 
-template <int W, int TYPE, bool GOTOH, int RU, int R>
-__global__ void __launch_bounds__(B2_THREADS, 4)
+__device__ __forceinline__ uint2 c_lds64(uint32_t addr)
+{ uint2 v; asm("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr)); return v; }
+
+// ---- byte streams. Each of a thread's four strings (pattern A/B; text A/B from position W-1 on) is consumed one
+// byte per row. It is kept as a ring of three aligned 16-byte blocks of the symbol array plus a copy of the first
+// slot after the last, so that the 16 bytes of a row group are contiguous wherever they start. While a group is
+// computed, the block after the two resident ones sits in registers (one LDG.128 per stream and group, issued
+// before the group, stored after it): the load latency is covered by the thread's own arithmetic.
+struct Stream
+{
+    const uint8_t* base;   // symbol array rounded down to 16 bytes
+    uint32_t       nb;     // offset (from base) of the next block to fetch = block of the current byte + 32
+    uint32_t       end;    // offset of the end of the string
+    uint8_t*       ring;   // 64 bytes of shared memory
+    const uint8_t* ptr;    // shared-memory address of the byte the next row reads: ring <= ptr < ring + 48
+};
+
+// the aligned block at offset bstart, or zeros when it holds no byte of the string (nothing past the string's last
+// block is ever read). volatile + "memory": the load is issued where it is written, a whole row group ahead of c_put
+__device__ __forceinline__ uint4 c_load(const Stream& s, uint32_t bstart)
+{
+    uint4 v;
+    const uint32_t ok = bstart < s.end ? 1u : 0u;
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %5, 0;\n\tmov.u32 %0, 0;\n\tmov.u32 %1, 0;\n\tmov.u32 %2, 0;\n\tmov.u32 %3, 0;\n\t"
+                 "@p ld.global.nc.v4.u32 {%0, %1, %2, %3}, [%4];\n\t}"
+                 : "=&r"(v.x), "=&r"(v.y), "=&r"(v.z), "=&r"(v.w) : "l"(s.base + bstart), "r"(ok) : "memory");
+    return v;
+}
+// zeroes the bytes of block bstart that lie past the end of the string
+__device__ __forceinline__ uint4 c_clip(const Stream& s, uint32_t bstart, uint4 v)
+{
+    if (bstart < s.end && s.end - bstart < 16u)
+    {
+        const uint32_t n = s.end - bstart;
+        uint32_t w[4] = { v.x, v.y, v.z, v.w };
+        #pragma unroll
+        for (int k = 0; k < 4; ++k)
+        {
+            const uint32_t keep = n > 4u * k ? min(n - 4u * k, 4u) : 0u;
+            w[k] = keep == 4u ? w[k] : (keep == 0u ? 0u : (w[k] & ((1u << (8u * keep)) - 1u)));
+        }
+        v = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+    return v;
+}
+// stores a block in ring slot slot_off (slot 0 is mirrored after slot 2)
+__device__ __forceinline__ void c_put(uint8_t* ring, uint32_t slot_off, const uint4 v)
+{
+    uint32_t* d = (uint32_t*)(ring + slot_off);
+    d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
+    if (slot_off == 0u) { d[12] = v.x; d[13] = v.y; d[14] = v.z; d[15] = v.w; }
+}
+// skip = bytes of the string that are not streamed (the text positions the window starts with)
+__device__ __forceinline__ void c_open(Stream& s, const uint8_t* sym, uint32_t beg, uint32_t L, uint32_t skip, uint8_t* ring, uint32_t& seen)
+{
+    const uint32_t delta = (uint32_t)((uintptr_t)sym & 15u);
+    s.base = sym - delta;
+    const uint32_t pos = delta + beg + skip, b0 = pos & ~15u;
+    s.end = delta + beg + L; s.nb = b0 + 32u;
+    s.ring = ring; s.ptr = ring + (pos & 15u);
+    const uint4 v0 = c_load(s, b0), v1 = c_load(s, b0 + 16u);
+    seen |= v0.x | v0.y | v0.z | v0.w | v1.x | v1.y | v1.z | v1.w;      // neighbours' bytes included: a filter, confirmed exactly later
+    c_put(ring, 0u, c_clip(s, b0, v0));
+    c_put(ring, 16u, c_clip(s, b0 + 16u, v1));
+}
+// one byte on (single rows): fetches synchronously when the stream enters its next block
+__device__ __forceinline__ void c_step(Stream& s, uint32_t& seen)
+{
+    const uint32_t at = (uint32_t)(s.ptr - s.ring);
+    if ((at & 15u) == 15u)
+    {
+        const uint4 v = c_load(s, s.nb);
+        seen |= v.x | v.y | v.z | v.w;
+        const uint32_t o = at & 0x30u;                                  // slot of the current block: 0, 16, 32
+        c_put(s.ring, o == 0u ? 32u : o - 16u, c_clip(s, s.nb, v));     // slot (o + 32) mod 48
+        s.nb += 16u;
+        if (o == 32u) s.ptr -= 48;
+    }
+    ++s.ptr;
+}
+
+// one pattern row: cell j reads window slot (R0 + j) % WS
+template <int W, bool GOTOH, int WS, int R0>
+__device__ __forceinline__ void c_row(uint32_t (&X)[W], uint32_t (&F)[W], const uint32_t (&win)[WS], const uint2 pq,
+                                      const uint32_t dfix, const uint32_t one)
+{
+    uint32_t left = 0, E = 0;
+    #pragma unroll
+    for (int j = 0; j < W; ++j)
+    {
+        const uint32_t S = c_prmt(pq.x, pq.y, win[(R0 + j) % WS]);
+        const uint32_t dg = X[j] + S;
+        uint32_t h;
+        if (!GOTOH)
+        {
+            if (j == 0)          h = __vmaxs2(dg, X[1 < W ? 1 : 0]);
+            else if (j < W - 1)  h = __vimax3_s16x2(dg, X[j + 1 < W ? j + 1 : j], left);
+            else                 h = __vmaxs2(dg, left);
+            X[j] = h; left = h;
+        }
+        else
+        {
+            if (j < W - 1) F[j] = __vmaxs2(F[j + 1 < W ? j + 1 : j], X[j + 1 < W ? j + 1 : j]);
+            else           F[j] = B2_INF2;
+            if (j == 0)          h = __vmaxs2(dg, F[0]);
+            else if (j < W - 1)  h = __vimax3_s16x2(dg, F[j], E);
+            else                 h = __vmaxs2(dg, E);
+            const uint32_t ho = c_imad(h, one, dfix);
+            E = (j == 0) ? ho : __vmaxs2(E, ho);
+            X[j] = ho;
+        }
+    }
+}
+
+// rows R0 .. RU-1 of a group
+template <int W, int RU, int R0>
+struct RowUnroll
+{
+    template <bool GOTOH, int WS>
+    static __device__ __forceinline__ void run(uint32_t (&X)[W], uint32_t (&F)[W], uint32_t (&win)[WS], const uint8_t* pA, const uint8_t* pB,
+                                               const uint8_t* tA, const uint8_t* tB, uint32_t lut_addr, uint32_t dfix, uint32_t one,
+                                               uint32_t k8, uint32_t k32)
+    {
+        const uint2 pq = c_lds64(c_imad(pA[R0], k8, c_imad(pB[R0], k32, lut_addr)));     // runtime 8 and 32: IMADs stay IMADs (FMA pipe)
+        win[(R0 + W - 1) % WS] = c_imad(tB[R0], 0x1100u, c_imad(tA[R0], 0x11u, 0xC480u));
+        c_row<W, GOTOH, WS, R0>(X, F, win, pq, dfix, one);
+        RowUnroll<W, RU, R0 + 1>::template run<GOTOH, WS>(X, F, win, pA, pB, tA, tB, lut_addr, dfix, one, k8, k32);
+    }
+};
+template <int W, int RU>
+struct RowUnroll<W, RU, RU>
+{
+    template <bool GOTOH, int WS>
+    static __device__ __forceinline__ void run(uint32_t (&)[W], uint32_t (&)[W], uint32_t (&)[WS], const uint8_t*, const uint8_t*,
+                                               const uint8_t*, const uint8_t*, uint32_t, uint32_t, uint32_t, uint32_t, uint32_t) {}
+};
+
+template <int W, int TYPE, bool GOTOH, int MINB>
+__global__ void __launch_bounds__(B2_THREADS, MINB)
 band2_kernel(const Band2Params p)
 {
-    constexpr int PS = ((15 + R + 15) / 16) * 16;               // pattern slot: R rows at any 16-byte phase
-    constexpr int TS = ((15 + R + W - 1 + 15) / 16) * 16;       // text slot: R + W - 1 positions
-    constexpr int STRIDE = 2 * PS + 2 * TS + 4;
-    static_assert((STRIDE & 7) == 4, "thread stride must be 4 mod 8 bytes");
-    static_assert(R % RU == 0, "chunk must hold whole row groups");
-    constexpr int WS = W + RU - 1;
+    constexpr int WS = W + 1;                                    // circular window of text selectors; one group = WS rows
+    constexpr int RU = WS;
+    static_assert(RU <= 16, "a row group may not outrun a 16-byte block");
+    constexpr int STRIDE = 4 * 64 + 4;                           // 4 mod 8 bytes: the slots of a warp start in distinct banks
 
     extern __shared__ __align__(16) uint8_t s_raw[];
     uint2* lut = (uint2*)s_raw;                                  // [qA + 4 qB] -> (profile A, profile B); byte offset qA*8 + qB*32
@@ -114,86 +224,120 @@ band2_kernel(const Band2Params p)
     const uint32_t pbA = p.P.off[idA], MA = p.P.off[idA + 1] - pbA, pbB = p.P.off[idB], MB = p.P.off[idB + 1] - pbB;
     const uint32_t tbA = p.T.off[idA], NA = p.T.off[idA + 1] - tbA, tbB = p.T.off[idB], NB = p.T.off[idB + 1] - tbB;
     const uint32_t Mmax = max(MA, MB), Mmin = min(MA, MB);
-    const uint32_t rows = ((Mmax + RU - 1) / RU) * RU;
 
     uint8_t* slot = s_raw + 128 + (size_t)threadIdx.x * STRIDE;
-    uint8_t* const sPA = slot, * const sPB = slot + PS, * const sTA = slot + 2 * PS, * const sTB = slot + 2 * PS + TS;
-    const uint8_t* lutb = s_raw;
-
+    const uint32_t lut_addr = (uint32_t)__cvta_generic_to_shared(s_raw);
     const uint32_t dfix = p.d ? c_fix2(p.d) : 0u;        // c_fix2(0) would borrow from the high half
-    uint32_t X[W], F[W], fin[W], win[WS];
-    #pragma unroll
-    for (int j = 0; j < W; ++j)
-    {
-        X[j] = c_pack2(j == 0 ? p.init0 : p.init_rest + j * p.init_step);
-        F[j] = B2_INF2; fin[j] = X[j];
-    }
-    #pragma unroll
-    for (int j = 0; j < WS; ++j) win[j] = 0;
 
     uint32_t seen = 0;
-    uint32_t nextcap = Mmin;
-    for (uint32_t c = 0; c < rows; c += R)
+    Stream sPA, sPB, sTA, sTB;
+    c_open(sPA, p.P.sym, pbA, MA, 0, slot, seen);
+    c_open(sPB, p.P.sym, pbB, MB, 0, slot + 64, seen);
+    c_open(sTA, p.T.sym, tbA, NA, W - 1, slot + 128, seen);
+    c_open(sTB, p.T.sym, tbB, NB, W - 1, slot + 192, seen);
+
+    uint32_t X[W], F[W], win[WS];
+    #pragma unroll
+    for (int j = 0; j < W; ++j) { X[j] = c_pack2(j == 0 ? p.init0 : p.init_rest + j * p.init_step); F[j] = B2_INF2; }
+    win[WS - 1] = win[WS - 2] = 0;
+    #pragma unroll
+    for (int j = 0; j < W - 1; ++j)                       // text positions 0 .. W-2 (their bytes also pass the filter: first blocks)
     {
-        const uint8_t* pA = sPA + c_stage<PS / 16>(p.P.sym, pbA, MA, c, R, sPA, seen);
-        const uint8_t* pB = sPB + c_stage<PS / 16>(p.P.sym, pbB, MB, c, R, sPB, seen);
-        const uint8_t* tA = sTA + c_stage<TS / 16>(p.T.sym, tbA, NA, c, R + W - 1, sTA, seen);
-        const uint8_t* tB = sTB + c_stage<TS / 16>(p.T.sym, tbB, NB, c, R + W - 1, sTB, seen);
-        if (c == 0)
+        const uint32_t ra = (uint32_t)j < NA ? __ldg(p.T.sym + (size_t)tbA + j) : 0u;
+        const uint32_t rb = (uint32_t)j < NB ? __ldg(p.T.sym + (size_t)tbB + j) : 0u;
+        seen |= ra | rb;
+        win[j] = c_imad(rb, 0x1100u, c_imad(ra, 0x11u, 0xC480u));
+    }
+
+    int32_t scoreA = NVB_SINK_MIN, scoreB = NVB_SINK_MIN;
+    uint32_t sxA = 0xFFFFFFFFu, sxB = 0xFFFFFFFFu;
+    uint32_t i = 0;
+
+    #pragma unroll 1
+    for (int seg = 0; seg < 2; ++seg)
+    {
+        const uint32_t target = seg ? Mmax : Mmin;
+        // groups of RU rows, all four streams in step (only before the first single row, i.e. in the first segment):
+        // the window rotates in place and is linear again (slot s <-> text position i + s) after each group
+        if (seg == 0)
         {
-            #pragma unroll
-            for (int j = 0; j < W - 1; ++j) win[j] = c_imad(tB[j], 0x1100u, c_imad(tA[j], 0x11u, 0xC480u));
-        }
-        const uint32_t gend = min((uint32_t)R, rows - c);
-        for (uint32_t g = 0; g < gend; g += RU, pA += RU, pB += RU, tA += RU, tB += RU)
-        {
-            #pragma unroll
-            for (int r = 0; r < RU; ++r)
+            uint32_t o = 0;                                    // ring slot of the streams' current blocks: 0, 16, 32
+            #pragma unroll 1
+            for (uint32_t g = target / RU; g > 0; --g)
             {
-                const uint32_t i = c + g + r;
-                const uint2 pq = *(const uint2*)(lutb + c_imad(pB[r], 32u, (uint32_t)pA[r] * 8u));
-                win[r + W - 1] = c_imad(tB[r + W - 1], 0x1100u, c_imad(tA[r + W - 1], 0x11u, 0xC480u));
-                uint32_t left = 0, E = 0;
+                const uint4 vPA = c_load(sPA, sPA.nb), vPB = c_load(sPB, sPB.nb), vTA = c_load(sTA, sTA.nb), vTB = c_load(sTB, sTB.nb);
+                RowUnroll<W, RU, 0>::template run<GOTOH, WS>(X, F, win, sPA.ptr, sPB.ptr, sTA.ptr, sTB.ptr, lut_addr, dfix, p.one, p.k8, p.k32);
+                seen |= vPA.x | vPA.y | vPA.z | vPA.w | vPB.x | vPB.y | vPB.z | vPB.w;
+                seen |= vTA.x | vTA.y | vTA.z | vTA.w | vTB.x | vTB.y | vTB.z | vTB.w;
+                // bytes past the end of a string are read: text right of the band's last cells, and the shorter pattern of
+                // a couple while the longer one goes on; they must be symbols (the profile table is indexed by both patterns)
+                const uint4 cPA = c_clip(sPA, sPA.nb, vPA), cPB = c_clip(sPB, sPB.nb, vPB);
+                const uint4 cTA = c_clip(sTA, sTA.nb, vTA), cTB = c_clip(sTB, sTB.nb, vTB);
+                if (RU == 16)
+                {
+                    const uint32_t so = o == 0u ? 32u : o - 16u;   // (o + 32) mod 48
+                    c_put(sPA.ring, so, cPA); c_put(sPB.ring, so, cPB); c_put(sTA.ring, so, cTA); c_put(sTB.ring, so, cTB);
+                    const int32_t step = o == 32u ? -32 : 16;
+                    o = o == 32u ? 0u : o + 16u;
+                    sPA.ptr += step; sPB.ptr += step; sTA.ptr += step; sTB.ptr += step;
+                    sPA.nb += 16u; sPB.nb += 16u; sTA.nb += 16u; sTB.nb += 16u;
+                }
+                else
+                {
+                    // shorter groups: a stream enters its next block only every other group or so
+                    Stream* st[4] = { &sPA, &sPB, &sTA, &sTB };
+                    const uint4 vv[4] = { cPA, cPB, cTA, cTB };
+                    #pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                    {
+                        Stream& t = *st[k];
+                        const uint32_t at = (uint32_t)(t.ptr - t.ring), ob = at & 0x30u;
+                        c_put(t.ring, ob == 0u ? 32u : ob - 16u, vv[k]);
+                        if ((at & 15u) + RU >= 16u) { t.nb += 16u; if (at + RU >= 48u) t.ptr -= 48; }
+                        t.ptr += RU;
+                    }
+                }
+                i += RU;
+            }
+        }
+        // single rows (the window is shifted down after each and stays linear)
+        #pragma unroll 1
+        while (i < target)
+        {
+            RowUnroll<W, 1, 0>::template run<GOTOH, WS>(X, F, win, sPA.ptr, sPB.ptr, sTA.ptr, sTB.ptr, lut_addr, dfix, p.one, p.k8, p.k32);
+            #pragma unroll
+            for (int j = 0; j < W - 1; ++j) win[j] = win[j + 1];
+            c_step(sPA, seen); c_step(sPB, seen); c_step(sTA, seen); c_step(sTB, seen);
+            ++i;
+        }
+        // the pairs that end here: read their result off the band (H = stored - bias + alpha*M + beta*j)
+        #pragma unroll
+        for (int h = 0; h < 2; ++h)
+        {
+            const uint32_t M = h ? MB : MA, N = h ? NB : NA;
+            if (M != target || (seg == 1 && Mmin == Mmax) || M == 0 || N < M) continue;   // shorter texts are refused (sw_banded_inl.h:356-357)
+            const int32_t back = p.alpha * (int32_t)M - p.bias - (GOTOH ? p.d : 0);
+            int32_t best = NVB_SINK_MIN; uint32_t bx = 0xFFFFFFFFu;
+            if (TYPE == T_GLOBAL) { best = (h ? c_hi(X[W - 1]) : c_lo(X[W - 1])) + back + p.beta * (W - 1); bx = M + W - 1; }
+            else
+            {
+                const uint32_t lim = (M + W - 1 < N ? M + W - 1 : N) - (M - 1);
                 #pragma unroll
                 for (int j = 0; j < W; ++j)
                 {
-                    const uint32_t S = c_prmt(pq.x, pq.y, win[r + j]);
-                    const uint32_t dg = X[j] + S;
-                    uint32_t h;
-                    if (!GOTOH)
-                    {
-                        if (j == 0)          h = __vmaxs2(dg, X[1 < W ? 1 : 0]);
-                        else if (j < W - 1)  h = __vimax3_s16x2(dg, X[j + 1 < W ? j + 1 : j], left);
-                        else                 h = __vmaxs2(dg, left);
-                        X[j] = h; left = h;
-                    }
-                    else
-                    {
-                        if (j < W - 1) F[j] = __vmaxs2(F[j + 1 < W ? j + 1 : j], X[j + 1 < W ? j + 1 : j]);
-                        else           F[j] = B2_INF2;
-                        if (j == 0)          h = __vmaxs2(dg, F[0]);
-                        else if (j < W - 1)  h = __vimax3_s16x2(dg, F[j], E);
-                        else                 h = __vmaxs2(dg, E);
-                        const uint32_t ho = c_imad(h, p.one, dfix);
-                        E = (j == 0) ? ho : __vmaxs2(E, ho);
-                        X[j] = ho;
-                    }
-                }
-                if (i + 1 == nextcap)
-                {
-                    const uint32_t m = (i + 1 == MA ? 0x0000FFFFu : 0u) | (i + 1 == MB ? 0xFFFF0000u : 0u);
-                    #pragma unroll
-                    for (int j = 0; j < W; ++j) fin[j] = (X[j] & m) | (fin[j] & ~m);
-                    nextcap = (nextcap == Mmax) ? 0xFFFFFFFFu : Mmax;
+                    const int32_t s = (h ? c_hi(X[j]) : c_lo(X[j])) + back + p.beta * j;
+                    if ((j == 0 || (uint32_t)j < lim) && best <= s) { best = s; bx = M + j; }
                 }
             }
-            #pragma unroll
-            for (int j = 0; j < W - 1; ++j) win[j] = win[j + RU];
+            if (h) { scoreB = best; sxB = bx; } else { scoreA = best; sxA = bx; }
         }
     }
 
     // ---- epilogue
     bool dirty = MA == 0 || MB == 0;
+    // GLOBAL reports the band's last cell; when that lies right of the text the reference's score depends on the 255s it
+    // reads there (sw_banded_inl.h:444), which this kernel's text stream does not reproduce
+    if (TYPE == T_GLOBAL) dirty = dirty || NA < MA + W - 1 || NB < MB + W - 1;
     if (seen & 0xFCFCFCFCu)
         dirty = dirty || c_has_high_symbol(p.P.sym, pbA, MA) || c_has_high_symbol(p.P.sym, pbB, MB) ||
                 c_has_high_symbol(p.T.sym, tbA, NA) || c_has_high_symbol(p.T.sym, tbB, NB);
@@ -202,7 +346,6 @@ band2_kernel(const Band2Params p)
     {
         if (h == 1 && !hasB) break;
         const uint32_t id = h ? idB : idA;
-        const uint32_t M = h ? MB : MA, N = h ? NB : NA;
         if (dirty)
         {
             const uint32_t at = atomicAdd(p.worklist, 1u);
@@ -210,26 +353,8 @@ band2_kernel(const Band2Params p)
             continue;
         }
         nvb_best_sink out;
-        out.score = NVB_SINK_MIN; out.sink_x = out.sink_y = 0xFFFFFFFFu;
-        if (N >= M)                                           // shorter texts are refused (sw_banded_inl.h:356-357)
-        {
-            const int32_t back = p.alpha * (int32_t)M - p.bias - (GOTOH ? p.d : 0);
-            if (TYPE == T_GLOBAL)
-            {
-                out.score = (h ? c_hi(fin[W - 1]) : c_lo(fin[W - 1])) + back + p.beta * (W - 1);
-                out.sink_x = M + W - 1; out.sink_y = M;
-            }
-            else
-            {
-                const uint32_t lim = (M + W - 1 < N ? M + W - 1 : N) - (M - 1);
-                #pragma unroll
-                for (int j = 0; j < W; ++j)
-                {
-                    const int32_t s = (h ? c_hi(fin[j]) : c_lo(fin[j])) + back + p.beta * j;
-                    if ((j == 0 || (uint32_t)j < lim) && out.score <= s) { out.score = s; out.sink_x = M + j; out.sink_y = M; }
-                }
-            }
-        }
+        out.score = h ? scoreB : scoreA; out.sink_x = h ? sxB : sxA;
+        out.sink_y = out.sink_x == 0xFFFFFFFFu ? 0xFFFFFFFFu : (h ? MB : MA);
         p.sinks[id] = out;
     }
 }
@@ -280,7 +405,7 @@ static Band2Plan band2_plan(const nvb_aligner& a, uint32_t band, uint32_t maxM)
     if (p.bias > 30000 || high > 32000) return pl;
     // the band is kept biased; for Gotoh as HO = H'' + d
     p.init0 += p.bias + p.d; p.init_rest += p.bias + p.d;
-    p.one = 1;
+    p.one = 1; p.k8 = 8; p.k32 = 32;
     pl.ok = true;
     return pl;
 }
@@ -292,21 +417,28 @@ bool dpb2_score_supported(const nvb_aligner& a, uint32_t band, const StrSet& P, 
     return band2_plan(a, band, maxM).ok;
 }
 
-template <int W, int TYPE, bool GOTOH>
-static int band2_launch(nvb_ctx* ctx, const Band2Params& p, cudaStream_t st)
+template <int W, int TYPE, bool GOTOH, int MINB>
+static int band2_launch_as(nvb_ctx* ctx, const Band2Params& p, cudaStream_t st)
 {
-    constexpr int RU = 8, R = 48;
-    constexpr int PS = ((15 + R + 15) / 16) * 16, TS = ((15 + R + W - 1 + 15) / 16) * 16;
-    constexpr size_t smem = 128 + (size_t)B2_THREADS * (2 * PS + 2 * TS + 4);
+    constexpr size_t smem = 128 + (size_t)B2_THREADS * (4 * 64 + 4);
     static bool attr_set = false;
     if (!attr_set)
     {
-        NVB_CUDA(ctx, cudaFuncSetAttribute(band2_kernel<W, TYPE, GOTOH, RU, R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        NVB_CUDA(ctx, cudaFuncSetAttribute(band2_kernel<W, TYPE, GOTOH, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         attr_set = true;
     }
-    band2_kernel<W, TYPE, GOTOH, RU, R><<<(p.n_threads + B2_THREADS - 1) / B2_THREADS, B2_THREADS, smem, st>>>(p);
+    band2_kernel<W, TYPE, GOTOH, MINB><<<(p.n_threads + B2_THREADS - 1) / B2_THREADS, B2_THREADS, smem, st>>>(p);
     NVB_LAUNCHED(ctx);
     return NVB_OK;
+}
+template <int W, int TYPE, bool GOTOH>
+static int band2_launch(nvb_ctx* ctx, const Band2Params& p, cudaStream_t st)
+{
+    static int minb = -1;
+    if (minb < 0) { const char* e = getenv("NVB_B2_MINB"); minb = e ? atoi(e) : 4; }
+    if (minb == 6) return band2_launch_as<W, TYPE, GOTOH, 6>(ctx, p, st);
+    if (minb == 4) return band2_launch_as<W, TYPE, GOTOH, 4>(ctx, p, st);
+    return band2_launch_as<W, TYPE, GOTOH, 5>(ctx, p, st);
 }
 
 template <int W>
