@@ -34,7 +34,7 @@ def parse():
     ap.add_argument("--genome", type=int, default=100_000_000)
     ap.add_argument("--queries", type=int, default=10_000_000)
     ap.add_argument("--sw-pairs", type=int, default=100_000)
-    ap.add_argument("--banded-pairs", type=int, default=1_000_000)
+    ap.add_argument("--banded-pairs", type=int, default=10_000_000)
     ap.add_argument("--no-extra", action="store_true", help="skip the SW / banded secondary measurements")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
     ap.add_argument("--only", default="", help="profiling aid: run only this leg (fm|sw|banded) with no cpu leg")
@@ -134,9 +134,19 @@ def gen_queries(genome, nq, seed, dev):
     return q.reshape(-1).contiguous(), off
 
 
-def gen_pairs(n, M, N, seed, dev, sub=0.05, implant_frac=0.5):
+def gen_pairs(n, M, N, seed, dev, sub=0.05, implant_frac=0.5, chunk=1_000_000):
     """n pairs: pattern M symbols, text N symbols; a fraction has the pattern implanted with substitutions"""
     import torch
+    if n > chunk:   # bounded transients: generate in slices
+        P = torch.empty(n * M, dtype=torch.uint8, device=dev); T = torch.empty(n * N, dtype=torch.uint8, device=dev)
+        for k, b in enumerate(range(0, n, chunk)):
+            e = min(n, b + chunk)
+            p, _, t, _ = gen_pairs(e - b, M, N, seed * 1000 + k, dev, sub, implant_frac, chunk)
+            P[b * M:e * M] = p; T[b * N:e * N] = t
+            del p, t
+        po_ = (torch.arange(n + 1, device=dev, dtype=torch.int64) * M).to(torch.int32)
+        to_ = (torch.arange(n + 1, device=dev, dtype=torch.int64) * N).to(torch.int32)
+        return P, po_, T, to_
     g = torch.Generator(device=dev); g.manual_seed(seed)
     P = torch.randint(0, 4, (n, M), dtype=torch.uint8, device=dev, generator=g)
     T = torch.randint(0, 4, (n, N), dtype=torch.uint8, device=dev, generator=g)
@@ -382,6 +392,19 @@ def run_b200(args):
         if "cpu" in fm:
             line["cpu_baseline"] = fm["cpu"]
             line["parity"] = fm["parity"]
+    # DPX-pipe roofline of the DP legs: measured s16x2 DPX issue rate (tools/pipe_peak.cu on this pool's
+    # B200s, profiles/r1b_pipe_peak.jsonl) x 2 cells / DPX instructions per packed cell of the textbook recurrence
+    dpx = 1.8306e13
+    peak = {"sw": dpx * 2 / 2 / 1e9, "ed": dpx * 2 / 2 / 1e9, "gotoh": dpx * 2 / 5 / 1e9}
+    def _roof(gcups, kind):
+        return {"bound": "dpx", "achieved": gcups, "peak": peak[kind], "unit": "GCUPS", "frac": gcups / peak[kind],
+                "peak_source": "measured DPX issue rate (profiles/r1b_pipe_peak.jsonl) x 2 cells / %d DPX per packed cell" % (5 if kind == "gotoh" else 2)}
+    if "sw" in out:
+        out["sw"]["roofline"] = _roof(out["sw"]["gcups"], "sw")
+    if "banded" in out:
+        for k, kind in (("ed_semi", "ed"), ("gotoh_semi", "gotoh"), ("sw_local", "sw")):
+            if k in out["banded"]:
+                out["banded"][k]["roofline"] = _roof(out["banded"][k]["gcups"], kind)
     extra = {k: out[k] for k in ("sw", "banded") if k in out}
     if extra:
         line["extra"] = extra
