@@ -138,7 +138,7 @@ def batch_alignment_traceback(aligner, checkpoints, patterns, texts, ops_stride=
     return out, ops, n_ops
 
 
-def batch_banded_alignment_traceback(aligner, band, checkpoints, patterns, texts, ops_stride=None, temp=None, ctx=None):
+def batch_banded_alignment_traceback(aligner, band, checkpoints, patterns, texts, ops_stride=None, temp=None, ctx=None, bufs=None):
     """BatchedBandedAlignmentTraceback<BAND_LEN,CHECKPOINTS,...>::enact (batched.h:382-438)"""
     ctx = _ctx(patterns.offsets, ctx)
     n = patterns.count
@@ -146,9 +146,13 @@ def batch_banded_alignment_traceback(aligner, band, checkpoints, patterns, texts
     maxM, maxN = patterns.max_len, texts.max_len
     if ops_stride is None:
         ops_stride = 2 * maxM + band + 8
-    out = torch.empty((n, 5), dtype=torch.int32, device=dev)
-    ops = torch.zeros((n, ops_stride), dtype=torch.uint8, device=dev)
-    n_ops = torch.empty(n, dtype=torch.int32, device=dev)
+    if bufs is not None:            # caller-owned (out, ops, n_ops) of a previous call with the same shapes
+        out, ops, n_ops = bufs
+        ops_stride = ops.shape[1]
+    else:
+        out = torch.empty((n, 5), dtype=torch.int32, device=dev)
+        ops = torch.zeros((n, ops_stride), dtype=torch.uint8, device=dev)
+        n_ops = torch.empty(n, dtype=torch.int32, device=dev)
     temp = _temp(_lib.OP_BANDED_TRACEBACK, aligner, band, checkpoints, maxM, maxN, n, dev, temp)
     check(lib().nvb_batch_banded_traceback(ctx.h, aligner.c(), band, checkpoints, patterns.c(), texts.c(), out.data_ptr(),
                                            ops.data_ptr(), ops_stride, n_ops.data_ptr(), maxM, maxN, temp.data_ptr(),

@@ -194,14 +194,39 @@ extern "C" int nvb_batch_banded_traceback(nvb_ctx* ctx, nvb_aligner a, uint32_t 
     const TempPlan p = plan(NVB_OP_BANDED_TRACEBACK, a, band, chk, maxM, maxN);
     const uint32_t bp = batch_pairs(p, temp_bytes, n);
     if (bp == 0) return NVB_ERR_TEMP;
-    ctx->last_paths = 2u;
     const uint32_t bp128 = (bp + 127u) & ~127u;
+    ctx->last_paths = 0;
+    const uint32_t* list = nullptr; const uint32_t* d_count = nullptr;
+    if (ctx->force_generic == 0 && dpb2_traceback_supported(a, band, P, T, maxM))
+    {
+        // one tagged forward pass + a walk per pair; the flow of a launch lives in temp ([row][couple]).
+        // Pairs the packed kernel cannot represent (a symbol > 3, ...) are re-done below by the int32 kernel.
+        const size_t per_couple = dpb2_tb_bytes_per_couple(a, maxM);
+        uint8_t* flow = (uint8_t*)(((uintptr_t)temp + 15u) & ~(uintptr_t)15u);
+        const size_t avail = temp_bytes > 32 ? temp_bytes - 32 : 0;
+        uint64_t fit = per_couple ? 2ull * (avail / per_couple) : 0;
+        if (fit >= 2)
+        {
+            if (fit > n) fit = ((uint64_t)n + 1) & ~1ull;
+            uint32_t* wl = nullptr;
+            if ((rc = nvb_worklist(ctx, n, &wl))) return rc;
+            NVB_CUDA(ctx, cudaMemsetAsync(wl, 0, sizeof(uint32_t), s));
+            for (uint64_t first = 0; first < n; first += fit)
+            {
+                const uint32_t cnt = (uint32_t)(n - first < fit ? n - first : fit);
+                if ((rc = dpb2_traceback(ctx, a, band, P, T, (uint32_t)first, cnt, out, ops, ops_stride, n_ops, maxM, flow, wl, s))) return rc;
+            }
+            ctx->last_paths |= 1u | 4u;
+            list = wl + 1; d_count = wl;
+        }
+    }
+    if (!list) ctx->last_paths |= 2u;
     for (uint32_t first = 0; first < n; first += bp)
     {
         const uint32_t cnt = n - first < bp ? n - first : bp;
         int16_t* t16 = (int16_t*)temp;
         uint8_t* flow = (uint8_t*)temp + p.i16_per_pair * 2 * (size_t)bp128;
-        if ((rc = dpg_banded_traceback(ctx, a, band, P, T, first, cnt, chk, out, ops, ops_stride, n_ops, t16, flow, maxM, s))) return rc;
+        if ((rc = dpg_banded_traceback(ctx, a, band, P, T, list, d_count, first, cnt, chk, out, ops, ops_stride, n_ops, t16, flow, maxM, s))) return rc;
     }
     return NVB_OK;
 }

@@ -18,3 +18,10 @@ int  dpf_banded_score(nvb_ctx* ctx, const nvb_aligner& a, uint32_t band, StrSet 
 bool dpb2_score_supported(const nvb_aligner& a, uint32_t band, const StrSet& P, const StrSet& T, uint32_t maxM, uint32_t maxN);
 int  dpb2_score(nvb_ctx* ctx, const nvb_aligner& a, uint32_t band, StrSet P, StrSet T, nvb_best_sink* sinks,
                 uint32_t maxM, uint32_t maxN, uint32_t* worklist, cudaStream_t s);
+// sheared-coordinate banded traceback (dp_band2_tb.cu): one tagged forward pass writing the flow of a launch to
+// scratch ([row][couple]), then one walk thread per pair; pairs [first, first + n), first even
+bool   dpb2_traceback_supported(const nvb_aligner& a, uint32_t band, const StrSet& P, const StrSet& T, uint32_t maxM);
+size_t dpb2_tb_bytes_per_couple(const nvb_aligner& a, uint32_t maxM);
+int    dpb2_traceback(nvb_ctx* ctx, const nvb_aligner& a, uint32_t band, StrSet P, StrSet T, uint32_t first, uint32_t n,
+                      nvb_alignment* out, uint8_t* ops, uint32_t ops_stride, uint32_t* n_ops, uint32_t maxM,
+                      uint8_t* flow, uint32_t* worklist, cudaStream_t s);

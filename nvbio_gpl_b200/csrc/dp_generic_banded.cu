@@ -45,21 +45,21 @@ int dpg_banded_score(nvb_ctx* ctx, const nvb_aligner& a, uint32_t band, StrSet P
 }
 
 template <bool GOTOH, int TYPE, int WT>
-static int tb_w(nvb_ctx* ctx, Scheme sc, uint32_t band, StrSet P, StrSet T, uint32_t first, uint32_t n, uint32_t chk,
+static int tb_w(nvb_ctx* ctx, Scheme sc, uint32_t band, StrSet P, StrSet T, const uint32_t* list, const uint32_t* d_count, uint32_t first, uint32_t n, uint32_t chk,
                 nvb_alignment* out, uint8_t* ops, uint32_t ops_stride, uint32_t* n_ops, int16_t* temp16, uint8_t* flow,
                 uint32_t maxM, cudaStream_t s)
 {
     dpg_banded_traceback_kernel<GOTOH, TYPE, WT><<<(n + 127) / 128, 128, 0, s>>>(
-        sc, band, P, T, first, n, chk, out, ops, ops_stride, n_ops, temp16, flow, maxM);
+        sc, band, P, T, list, d_count, first, n, chk, out, ops, ops_stride, n_ops, temp16, flow, maxM);
     NVB_LAUNCHED(ctx);
     return NVB_OK;
 }
 template <bool GOTOH, int TYPE>
-static int tb_t(nvb_ctx* ctx, Scheme sc, uint32_t band, StrSet P, StrSet T, uint32_t first, uint32_t n, uint32_t chk,
+static int tb_t(nvb_ctx* ctx, Scheme sc, uint32_t band, StrSet P, StrSet T, const uint32_t* list, const uint32_t* d_count, uint32_t first, uint32_t n, uint32_t chk,
                 nvb_alignment* out, uint8_t* ops, uint32_t ops_stride, uint32_t* n_ops, int16_t* temp16, uint8_t* flow,
                 uint32_t maxM, cudaStream_t s)
 {
-    #define W_(WT) return tb_w<GOTOH, TYPE, WT>(ctx, sc, band, P, T, first, n, chk, out, ops, ops_stride, n_ops, temp16, flow, maxM, s)
+    #define W_(WT) return tb_w<GOTOH, TYPE, WT>(ctx, sc, band, P, T, list, d_count, first, n, chk, out, ops, ops_stride, n_ops, temp16, flow, maxM, s)
     switch (band)
     {
     case 3:  W_(3);
@@ -72,14 +72,14 @@ static int tb_t(nvb_ctx* ctx, Scheme sc, uint32_t band, StrSet P, StrSet T, uint
     #undef W_
 }
 
-int dpg_banded_traceback(nvb_ctx* ctx, const nvb_aligner& a, uint32_t band, StrSet P, StrSet T, uint32_t first, uint32_t n,
+int dpg_banded_traceback(nvb_ctx* ctx, const nvb_aligner& a, uint32_t band, StrSet P, StrSet T, const uint32_t* list, const uint32_t* d_count, uint32_t first, uint32_t n,
                          uint32_t chk, nvb_alignment* out, uint8_t* ops, uint32_t ops_stride, uint32_t* n_ops,
                          int16_t* temp16, uint8_t* flow, uint32_t maxM, cudaStream_t s)
 {
     if (n == 0) return NVB_OK;
     const Scheme sc = make_scheme(a);
     const bool g = a.kind == NVB_GOTOH;
-    #define GO(G, TY) return tb_t<G, TY>(ctx, sc, band, P, T, first, n, chk, out, ops, ops_stride, n_ops, temp16, flow, maxM, s)
+    #define GO(G, TY) return tb_t<G, TY>(ctx, sc, band, P, T, list, d_count, first, n, chk, out, ops, ops_stride, n_ops, temp16, flow, maxM, s)
     switch (a.type)
     {
     case NVB_GLOBAL:      if (g) GO(true, T_GLOBAL); else GO(false, T_GLOBAL);

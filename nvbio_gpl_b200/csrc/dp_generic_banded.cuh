@@ -253,14 +253,16 @@ dpg_banded_score_kernel(Scheme s, uint32_t W, StrSet P, StrSet T, const uint32_t
 
 template <bool GOTOH, int TYPE, int WT>
 __global__ void __launch_bounds__(128)
-dpg_banded_traceback_kernel(Scheme s, uint32_t W, StrSet P, StrSet T, uint32_t first, uint32_t n, uint32_t CHK,
+dpg_banded_traceback_kernel(Scheme s, uint32_t W, StrSet P, StrSet T, const uint32_t* __restrict__ list, const uint32_t* __restrict__ d_count,
+                            uint32_t first, uint32_t n, uint32_t CHK,
                             nvb_alignment* __restrict__ out, uint8_t* __restrict__ ops, uint32_t ops_stride,
                             uint32_t* __restrict__ n_ops, int16_t* __restrict__ temp16, uint8_t* __restrict__ flow,
                             uint32_t maxM)
 {
     const uint32_t lp = blockIdx.x * 128 + threadIdx.x;
     if (lp >= n) return;
-    const uint32_t id = first + lp;
+    if (d_count && first + lp >= *d_count) return;
+    const uint32_t id = list ? list[first + lp] : first + lp;
     const uint32_t nrows = 2u + (maxM + CHK - 1) / CHK;
     BandDP<GOTOH, TYPE, WT> dp;
     dp.s = s; dp.v = make_pair_view(P, T, id); dp.Wrt = W; dp.cs = n;

@@ -11,6 +11,6 @@ int dpg_full_traceback(nvb_ctx* ctx, const nvb_aligner& a, StrSet P, StrSet T, u
                        uint8_t* flow, uint32_t maxM, uint32_t maxN, cudaStream_t s);
 int dpg_banded_score(nvb_ctx* ctx, const nvb_aligner& a, uint32_t band, StrSet P, StrSet T, const uint32_t* list,
                      const uint32_t* d_count, uint32_t first, uint32_t n, nvb_best_sink* sinks, cudaStream_t s);
-int dpg_banded_traceback(nvb_ctx* ctx, const nvb_aligner& a, uint32_t band, StrSet P, StrSet T, uint32_t first, uint32_t n,
+int dpg_banded_traceback(nvb_ctx* ctx, const nvb_aligner& a, uint32_t band, StrSet P, StrSet T, const uint32_t* list, const uint32_t* d_count, uint32_t first, uint32_t n,
                          uint32_t chk, nvb_alignment* out, uint8_t* ops, uint32_t ops_stride, uint32_t* n_ops,
                          int16_t* temp16, uint8_t* flow, uint32_t maxM, cudaStream_t s);
