@@ -145,7 +145,7 @@ def batch_banded_alignment_traceback(aligner, band, checkpoints, patterns, texts
     dev = patterns.offsets.device
     maxM, maxN = patterns.max_len, texts.max_len
     if ops_stride is None:
-        ops_stride = 2 * maxM + band + 8
+        ops_stride = (2 * maxM + band + 8 + 15) & ~15     # rows 16-byte aligned: the walk stores 16 ops at a time
     if bufs is not None:            # caller-owned (out, ops, n_ops) of a previous call with the same shapes
         out, ops, n_ops = bufs
         ops_stride = ops.shape[1]

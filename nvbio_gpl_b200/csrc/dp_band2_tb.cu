@@ -286,6 +286,45 @@ band2_tb_forward_kernel(const Band2TbParams q)
     }
 }
 
+// ops of one pair, pushed one at a time; written 16 at a time when the pair's op row is 16-byte aligned (a byte
+// store per op costs a 32-byte sector write each: the walk would be bound by them)
+struct OpSink
+{
+    uint8_t* ops; uint32_t cap, n; bool wide;
+    uint32_t cur, w0, w1, w2;          // the block of 16 ops being filled: three finished words + the current one
+    __device__ __forceinline__ void init(uint8_t* o, uint32_t c)
+    { ops = o; cap = c; n = 0; cur = w0 = w1 = w2 = 0; wide = (((uintptr_t)o) & 15u) == 0u; }
+    // bytes [0, cnt) of the current block go to ops[base ..], clipped to cap; `done` words of the block are finished
+    __device__ __forceinline__ void spill(uint32_t base, uint32_t cnt, uint32_t done)
+    {
+        for (uint32_t k = 0; k < cnt; ++k)
+        {
+            const uint32_t wi = k >> 2;
+            const uint32_t word = wi >= done ? cur : (wi == 0u ? w0 : wi == 1u ? w1 : w2);
+            if (base + k < cap) ops[base + k] = (uint8_t)(word >> (8u * (k & 3u)));
+        }
+    }
+    __device__ __forceinline__ void push(uint32_t op)
+    {
+        if (!wide) { if (n < cap) ops[n] = (uint8_t)op; ++n; return; }
+        cur |= op << (8u * (n & 3u));
+        if ((n & 3u) == 3u)
+        {
+            const uint32_t k = (n >> 2) & 3u;
+            if (k == 0u) w0 = cur; else if (k == 1u) w1 = cur; else if (k == 2u) w2 = cur;
+            else if (n < cap) *(uint4*)(ops + (n & ~15u)) = make_uint4(w0, w1, w2, cur);
+            else spill(n & ~15u, 16u, 3u);
+            cur = 0;
+        }
+        ++n;
+    }
+    __device__ __forceinline__ void finish()
+    {
+        const uint32_t pend = n & 15u;
+        if (wide && pend) spill(n - pend, pend, pend >> 2);
+    }
+};
+
 // ---------------------------------------------------------------------------------------------
 // the walk: one thread per pair (sw_banded_inl.h:740-800, gotoh_banded_inl.h:883-950 without the windows)
 // ---------------------------------------------------------------------------------------------
@@ -299,11 +338,10 @@ band2_tb_walk_kernel(const Band2TbParams q)
     const nvb_alignment a = q.out[id];
     if (a.sink_x == 0xFFFFFFFFu) return;                       // invalid, or left to the int32 kernel
     const uint32_t half = lp & 1u, t = lp >> 1;
-    uint8_t* ops = q.ops + (size_t)id * q.ops_stride;
-    const uint32_t cap = q.ops_stride;
+    OpSink sink; sink.init(q.ops + (size_t)id * q.ops_stride, q.ops_stride);
     int32_t entry = (int32_t)(a.sink_x - a.sink_y);
     int32_t row = (int32_t)a.sink_y - 1;
-    uint32_t n = 0, state = ST_H;
+    uint32_t state = ST_H;
     int32_t have = -1;
     uint32_t bits0 = 0, bits1 = 0;                              // this pair's flow of row `have`
     while (row >= 0)
@@ -323,36 +361,34 @@ band2_tb_walk_kernel(const Band2TbParams q)
             }
             have = row;
         }
-        uint32_t op;
         if (!GOTOH)
         {
             const uint32_t tag = (bits0 >> (2 * entry)) & 3u;   // 2 = SUBSTITUTION, 1 = DELETION (text), 0 = INSERTION
-            if (tag == 1u)      { --entry; op = OP_DEL; }
-            else if (tag == 0u) { ++entry; --row; op = OP_INS; }
-            else                { --row; op = OP_SUB; }
-            if (n < cap) ops[n] = (uint8_t)op;
-            ++n;
+            if (tag == 1u)      { --entry; sink.push(OP_DEL); }
+            else if (tag == 0u) { ++entry; --row; sink.push(OP_INS); }
+            else                { --row; sink.push(OP_SUB); }
         }
         else
         {
             const uint32_t nib = ((entry < 8 ? bits0 : bits1) >> (4 * (entry & 7))) & 15u;
             const uint32_t tag = nib & 3u;
             const bool e_ext = (nib & 4u) == 0u, f_ext = (nib & 8u) == 0u;
-            if (state == ST_E)      { if (!e_ext) state = ST_H; --entry; if (n < cap) ops[n] = OP_DEL; ++n; }
-            else if (state == ST_F) { if (!f_ext) state = ST_H; ++entry; --row; if (n < cap) ops[n] = OP_INS; ++n; }
+            if (state == ST_E)      { if (!e_ext) state = ST_H; --entry; sink.push(OP_DEL); }
+            else if (state == ST_F) { if (!f_ext) state = ST_H; ++entry; --row; sink.push(OP_INS); }
             else
             {
                 if (tag == 1u)      state = ST_E;
                 else if (tag == 0u) state = ST_F;
-                else                { --row; if (n < cap) ops[n] = OP_SUB; ++n; }
+                else                { --row; sink.push(OP_SUB); }
             }
         }
         if (entry < 0 || entry >= W) break;
     }
+    sink.finish();
     const uint32_t sy = row < 0 ? 0u : (uint32_t)row + 1u;
     q.out[id].source_x = (uint32_t)entry + sy;
     q.out[id].source_y = sy;
-    q.n_ops[id] = n;
+    q.n_ops[id] = sink.n;
 }
 
 // ---------------------------------------------------------------------------------------------
