@@ -278,6 +278,25 @@ def run_b200(args):
         out["fm"]["e2e"] = dict(value=world * nq / (e2e_ms * 1e-3), unit="lookups/s", ms_per_step=e2e_ms,
                                 h2d_bytes_per_step=int(hs.numel() + ho.numel() * 4), d2h_bytes_per_step=int(hr.numel() * 4))
         assert (hr_n == ranges.cpu().numpy().view(np.uint32)).all(), "host and device entry points disagree"
+        # the same through the 4-bit packed host stream (the layout of the reference's read streams): 2x fewer symbol bytes
+        hp = torch.from_numpy(nvb.pack_symbols(hs_n, 4).view(np.int32)).pin_memory()
+        hp_n = hp.numpy().view(np.uint32)
+        hr_n[:] = 0
+        nvb.match_host(fmi, hp_n, ho_n, hr_n, ctx=ctx, bits=4)
+        assert (hr_n == ranges.cpu().numpy().view(np.uint32)).all(), "packed host entry point disagrees"
+        barrier()
+        p4_t = []
+        for _ in range(args.steps):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(cstream)
+            nvb.match_host(fmi, hp_n, ho_n, hr_n, ctx=ctx, bits=4)
+            e1.record(cstream); e1.synchronize()
+            p4_t.append(e0.elapsed_time(e1))
+        barrier()
+        p4_ms = max_over_ranks(sum(p4_t) / len(p4_t))
+        out["fm"]["e2e_packed4"] = dict(value=world * nq / (p4_ms * 1e-3), unit="lookups/s", ms_per_step=p4_ms,
+                                        h2d_bytes_per_step=int(hp.numel() * 4 + ho.numel() * 4), d2h_bytes_per_step=int(hr.numel() * 4))
+        del hp
 
         # ---- cpu_baseline + parity + algorithmic bytes (rank 0, N == 1 only): the ONLY use of oracle/
         if rank == 0 and world == 1 and not args.no_cpu and only == "":
@@ -388,7 +407,8 @@ def run_b200(args):
                             "queries": "90% cut from the genome, 10% random, 0.1% with an N, unsorted",
                             "index_bytes": int(fmi.bwt_occ.numel() * 4), "partition": "queries sharded, index replicated, no collective",
                             "l2": "flushed (256 MiB write) between timed steps, outside the event-timed region",
-                            "index_build_s": round(fm["build_s"], 2)})
+                            "index_build_s": round(fm["build_s"], 2),
+                            "e2e_packed4": fm.get("e2e_packed4")})
         if alg_per_q:
             ach = alg_per_q * args.queries / (fm["kernel_ms"] * 1e-3) / 1e9
             line["roofline"] = {"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,

@@ -164,6 +164,10 @@ int nvb_fm_locate_lookup(nvb_ctx* ctx, const nvb_fmindex* fmi, const uint32_t* w
 /* host-buffer forms: H2D + kernel + D2H on the ctx stream, synchronous */
 int nvb_fm_match_host(nvb_ctx* ctx, const nvb_fmindex* fmi_d, const uint8_t* symbols_h,
                       const uint32_t* offsets_h, uint32_t count, uint32_t* ranges_h);
+/* the same over a packed host stream (bits = 4 or 2; big-endian 32-bit words as in the reference's read streams,
+ * PackedStream<uint32*,uint8,BITS,true>: nvbio/io/sequence/sequence.h, nvbio/basic/packedstream.h) */
+int nvb_fm_match_host_packed(nvb_ctx* ctx, const nvb_fmindex* fmi_d, const void* words_h, uint32_t bits,
+                             const uint32_t* offsets_h, uint32_t count, uint32_t* ranges_h);
 int nvb_fm_locate_host(nvb_ctx* ctx, const nvb_fmindex* fmi_d, const uint32_t* rows_h, uint32_t n,
                        uint32_t* pos_h);
 

@@ -35,6 +35,8 @@ extern "C" int nvb_ctx_create(int device, nvb_ctx** out)
     c->device = device;
     c->sm_count = prop.multiProcessorCount;
     if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return NVB_ERR_CUDA; }
+    for (int i = 0; i < 2; ++i)
+        if (cudaStreamCreateWithFlags(&c->aux[i], cudaStreamNonBlocking) != cudaSuccess) { delete c; return NVB_ERR_CUDA; }
     *out = c;
     return NVB_OK;
 }
@@ -46,6 +48,7 @@ extern "C" void nvb_ctx_destroy(nvb_ctx* c)
     cudaStreamSynchronize(c->stream);
     for (int i = 0; i < 8; ++i) if (c->d_stage[i]) cudaFree(c->d_stage[i]);
     if (c->d_worklist) cudaFree(c->d_worklist);
+    for (int i = 0; i < 2; ++i) if (c->aux[i]) { cudaStreamSynchronize(c->aux[i]); cudaStreamDestroy(c->aux[i]); }
     cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -165,27 +168,73 @@ extern "C" int nvb_fmindex_pin_l2(nvb_ctx* ctx, const nvb_fmindex* d, size_t byt
 // ---------------------------------------------------------------------------------------------
 // host-buffer forms
 // ---------------------------------------------------------------------------------------------
-extern "C" int nvb_fm_match_host(nvb_ctx* ctx, const nvb_fmindex* fmi_d, const uint8_t* symbols_h,
-                                 const uint32_t* offsets_h, uint32_t count, uint32_t* ranges_h)
+#define NVB_HOST_CHUNK (1u << 19)   // queries per pipelined chunk of the host entry points
+
+// Host buffers in, host buffers out. Large batches are cut into chunks that alternate between two streams, so that
+// the H2D copy of one chunk, the kernel of another and the D2H copy of a third overlap (PCIe is full duplex):
+// the call costs about max(H2D, D2H) instead of their sum. Pinned host memory (nvb_host_alloc) is needed for that.
+static int fm_match_host_impl(nvb_ctx* ctx, const nvb_fmindex* fmi_d, const uint8_t* symbols_h, uint32_t bits,
+                              const uint32_t* offsets_h, uint32_t count, uint32_t* ranges_h)
 {
     if (!ctx || !fmi_d) return NVB_ERR_ARG;
     if (count == 0) return NVB_OK;
     if (!symbols_h || !offsets_h || !ranges_h) return NVB_ERR_ARG;
+    if (bits != 8 && bits != 4 && bits != 2) return NVB_ERR_ARG;
     NVB_CUDA(ctx, cudaSetDevice(ctx->device));
-    const size_t n_sym = offsets_h[count];
-    void *d_sym, *d_off, *d_rng;
     int rc;
-    if ((rc = nvb_stage(ctx, 0, n_sym + 32, &d_sym))) return rc;
-    if ((rc = nvb_stage(ctx, 1, sizeof(uint32_t) * ((size_t)count + 1), &d_off))) return rc;
-    if ((rc = nvb_stage(ctx, 2, sizeof(uint32_t) * 2 * (size_t)count, &d_rng))) return rc;
-    NVB_CUDA(ctx, cudaMemcpyAsync(d_sym, symbols_h, n_sym, cudaMemcpyHostToDevice, ctx->stream));
-    NVB_CUDA(ctx, cudaMemcpyAsync(d_off, offsets_h, sizeof(uint32_t) * ((size_t)count + 1), cudaMemcpyHostToDevice, ctx->stream));
-    nvb_string_set q; q.symbols = d_sym; q.offsets = (const uint32_t*)d_off; q.count = count; q.bits = 8;
-    if ((rc = nvb_fm_match(ctx, fmi_d, q, (uint32_t*)d_rng, ctx->stream))) return rc;
-    NVB_CUDA(ctx, cudaMemcpyAsync(ranges_h, d_rng, sizeof(uint32_t) * 2 * (size_t)count, cudaMemcpyDeviceToHost, ctx->stream));
-    NVB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    const uint32_t spw = 32u / bits;                                  // symbols per 32-bit word of a packed stream
+    // bytes [b0, b1) of the host symbol array that hold symbols [s0, s1) (whole words for packed streams)
+    #define SPAN_BEGIN(s0) (bits == 8 ? (size_t)(s0) : (size_t)((s0) / spw) * 4u)
+    #define SPAN_END(s1)   (bits == 8 ? (size_t)(s1) : (size_t)(((s1) + spw - 1) / spw) * 4u)
+    const uint32_t chunk = count > NVB_HOST_CHUNK ? NVB_HOST_CHUNK : count;
+    const uint32_t n_chunks = (count + chunk - 1) / chunk;
+    const int n_sets = n_chunks > 1 ? 2 : 1;
+    size_t max_bytes = 0;
+    for (uint32_t k = 0; k < n_chunks; ++k)
+    {
+        const uint32_t c0 = k * chunk, c1 = c0 + chunk < count ? c0 + chunk : count;
+        const size_t nb = SPAN_END(offsets_h[c1]) - SPAN_BEGIN(offsets_h[c0]);
+        if (nb > max_bytes) max_bytes = nb;
+    }
+    void *d_sym[2], *d_off[2], *d_rng[2];
+    for (int b = 0; b < n_sets; ++b)
+    {
+        if ((rc = nvb_stage(ctx, 3 * b + 0, max_bytes + 32, &d_sym[b]))) return rc;
+        if ((rc = nvb_stage(ctx, 3 * b + 1, sizeof(uint32_t) * ((size_t)chunk + 1), &d_off[b]))) return rc;
+        if ((rc = nvb_stage(ctx, 3 * b + 2, sizeof(uint32_t) * 2 * (size_t)chunk, &d_rng[b]))) return rc;
+    }
+    for (uint32_t k = 0; k < n_chunks; ++k)
+    {
+        const int b = (int)(k & 1u) % n_sets;
+        cudaStream_t s = n_sets > 1 ? ctx->aux[b] : ctx->stream;
+        const uint32_t c0 = k * chunk, c1 = c0 + chunk < count ? c0 + chunk : count, cnt = c1 - c0;
+        const size_t b0 = SPAN_BEGIN(offsets_h[c0]), nb = SPAN_END(offsets_h[c1]) - b0;
+        NVB_CUDA(ctx, cudaMemcpyAsync(d_sym[b], symbols_h + b0, nb, cudaMemcpyHostToDevice, s));
+        NVB_CUDA(ctx, cudaMemcpyAsync(d_off[b], offsets_h + c0, sizeof(uint32_t) * ((size_t)cnt + 1), cudaMemcpyHostToDevice, s));
+        // the chunk keeps its absolute offsets: rebase the symbol pointer instead
+        nvb_string_set q; q.symbols = (const uint8_t*)d_sym[b] - b0; q.offsets = (const uint32_t*)d_off[b]; q.count = cnt; q.bits = bits;
+        if ((rc = nvb_fm_match(ctx, fmi_d, q, (uint32_t*)d_rng[b], s))) return rc;
+        NVB_CUDA(ctx, cudaMemcpyAsync(ranges_h + 2 * (size_t)c0, d_rng[b], sizeof(uint32_t) * 2 * (size_t)cnt, cudaMemcpyDeviceToHost, s));
+    }
+    #undef SPAN_BEGIN
+    #undef SPAN_END
+    if (n_sets > 1) { NVB_CUDA(ctx, cudaStreamSynchronize(ctx->aux[0])); NVB_CUDA(ctx, cudaStreamSynchronize(ctx->aux[1])); }
+    else NVB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return NVB_OK;
 }
+
+// Host buffers in, host buffers out. Large batches are cut into chunks that alternate between two streams, so that
+// the H2D copy of one chunk, the kernel of another and the D2H copy of a third overlap (PCIe is full duplex):
+// the call costs about max(H2D, D2H) instead of their sum. Pinned host memory (nvb_host_alloc) is needed for that.
+extern "C" int nvb_fm_match_host(nvb_ctx* ctx, const nvb_fmindex* fmi_d, const uint8_t* symbols_h,
+                                 const uint32_t* offsets_h, uint32_t count, uint32_t* ranges_h)
+{ return fm_match_host_impl(ctx, fmi_d, symbols_h, 8, offsets_h, count, ranges_h); }
+
+// the same over a packed host stream (bits = 4 or 2, big-endian 32-bit words: the layout of the reference's
+// io::SequenceData read streams, nvbio/io/sequence/sequence.h), which moves 2x / 4x fewer bytes over PCIe
+extern "C" int nvb_fm_match_host_packed(nvb_ctx* ctx, const nvb_fmindex* fmi_d, const void* words_h, uint32_t bits,
+                                        const uint32_t* offsets_h, uint32_t count, uint32_t* ranges_h)
+{ return fm_match_host_impl(ctx, fmi_d, (const uint8_t*)words_h, bits, offsets_h, count, ranges_h); }
 
 extern "C" int nvb_fm_locate_host(nvb_ctx* ctx, const nvb_fmindex* fmi_d, const uint32_t* rows_h, uint32_t n, uint32_t* pos_h)
 {

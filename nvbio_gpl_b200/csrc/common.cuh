@@ -26,6 +26,7 @@ struct nvb_ctx
     uint32_t*    d_worklist;
     size_t       d_worklist_cap;
     int          sm_count;
+    cudaStream_t aux[2];       // the *_host entry points pipeline chunks over these (H2D of one chunk under the kernel / D2H of another)
 };
 
 #define NVB_CUDA(ctx, call)                                                 \

@@ -238,14 +238,30 @@ def fuse(bwt_words, length, ctx=None):
 
 
 # host-buffer forms: numpy (ideally pinned) in, numpy out; H2D + kernel + D2H inside the call
-def match_host(fmi, symbols_h, offsets_h, ranges_h=None, ctx=None):
+def match_host(fmi, symbols_h, offsets_h, ranges_h=None, ctx=None, bits=8):
+    """bits = 8: one symbol per byte; bits = 4 | 2: symbols_h is the packed big-endian uint32 word stream (pack_symbols)"""
     ctx = _ctx(fmi.bwt_occ, ctx)
     n = len(offsets_h) - 1
     if ranges_h is None:
         ranges_h = np.empty((n, 2), dtype=np.uint32)
     f = fmi.c()
-    check(lib().nvb_fm_match_host(ctx.h, C.byref(f), symbols_h.ctypes.data, offsets_h.ctypes.data, n, ranges_h.ctypes.data), ctx.h)
+    if bits == 8:
+        check(lib().nvb_fm_match_host(ctx.h, C.byref(f), symbols_h.ctypes.data, offsets_h.ctypes.data, n, ranges_h.ctypes.data), ctx.h)
+    else:
+        check(lib().nvb_fm_match_host_packed(ctx.h, C.byref(f), symbols_h.ctypes.data, bits, offsets_h.ctypes.data, n, ranges_h.ctypes.data), ctx.h)
     return ranges_h
+
+
+def pack_symbols(symbols, bits):
+    """uint8 symbols -> big-endian packed uint32 words (PackedStream<uint32*, uint8, BITS, true>: symbol 0 in the top bits)"""
+    spw = 32 // bits
+    s = np.asarray(symbols, dtype=np.uint8)
+    pad = (-len(s)) % spw
+    if pad:
+        s = np.concatenate([s, np.zeros(pad, dtype=np.uint8)])
+    s = s.reshape(-1, spw).astype(np.uint32) & ((1 << bits) - 1)
+    shifts = (32 - bits * (np.arange(spw, dtype=np.uint32) + 1)).astype(np.uint32)
+    return (s << shifts[None, :]).sum(axis=1, dtype=np.uint64).astype(np.uint32)
 
 
 def locate_host(fmi, rows_h, pos_h=None, ctx=None):

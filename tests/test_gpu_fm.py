@@ -114,3 +114,17 @@ def test_packed_query_sets(oracle):
         wd = torch.from_numpy(words.view(np.int32)).to(gu.dev())
         got = u32(nvb.match(fmi, wd, off, bits=bits))
         assert (got == want).all()
+
+
+def test_host_entry_packed_and_chunked(oracle):
+    """host buffers: 8-bit and 4-bit packed streams, batch large enough to be pipelined in several chunks"""
+    rng = np.random.default_rng(31)
+    text = rng.integers(0, 4, 50000).astype(np.uint8)
+    fmi, oidx = gu.fm_index_pair(oracle, text)
+    Q, qo = util.rand_queries(rng, text, 1_200_000 // 8, len_range=(5, 28))
+    Q = np.tile(Q, 9); qo = np.concatenate([[0], np.cumsum(np.tile(np.diff(qo.astype(np.int64)), 9))]).astype(np.uint32)
+    want = oracle.fm_match(oidx, Q, qo)
+    assert (nvb.match_host(fmi, Q, qo) == want).all()
+    assert (nvb.match_host(fmi, nvb.pack_symbols(Q, 4), qo, bits=4) == want).all()
+    Q2 = Q.copy(); Q2[Q2 > 3] = 0
+    assert (nvb.match_host(fmi, nvb.pack_symbols(Q2, 2), qo, bits=2) == oracle.fm_match(oidx, Q2, qo)).all()
