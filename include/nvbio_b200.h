@@ -164,6 +164,17 @@ int nvb_fm_locate_lookup(nvb_ctx* ctx, const nvb_fmindex* fmi, const uint32_t* w
 /* host-buffer forms: H2D + kernel + D2H on the ctx stream, synchronous */
 int nvb_fm_match_host(nvb_ctx* ctx, const nvb_fmindex* fmi_d, const uint8_t* symbols_h,
                       const uint32_t* offsets_h, uint32_t count, uint32_t* ranges_h);
+/* FMIndexFilter<device_tag, fm_index>::rank(index, string_set) (nvbio/fmindex/filter.h:108-165, filter_inl.h:261-300):
+ * ranges[2 n] = match() of every string, slots[n] = inclusive scan of the range sizes (1 + y - x); both stay on the
+ * device. *n_hits_h (optional) receives slots[n-1] = the total number of hits and synchronises the stream. */
+int nvb_fm_filter_rank(nvb_ctx* ctx, const nvb_fmindex* fmi, nvb_string_set queries, uint32_t* ranges,
+                       uint64_t* slots, uint64_t* n_hits_h, void* stream);
+/* FMIndexFilter::locate(begin, end, hits) (filter_inl.h:75-110,302-393): output slot begin + i is the
+ * (slot - slots[q-1])-th suffix-array row of query q = upper_bound(slot, slots); hits[2 i] = its text position,
+ * hits[2 i + 1] = q. One thread per hit. */
+int nvb_fm_filter_locate(nvb_ctx* ctx, const nvb_fmindex* fmi, const uint32_t* ranges, const uint64_t* slots,
+                         uint32_t n_queries, uint64_t begin, uint64_t end, uint32_t* hits, void* stream);
+
 /* the same over a packed host stream (bits = 4 or 2; big-endian 32-bit words as in the reference's read streams,
  * PackedStream<uint32*,uint8,BITS,true>: nvbio/io/sequence/sequence.h, nvbio/basic/packedstream.h) */
 int nvb_fm_match_host_packed(nvb_ctx* ctx, const nvb_fmindex* fmi_d, const void* words_h, uint32_t bits,

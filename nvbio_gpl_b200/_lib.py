@@ -67,6 +67,8 @@ _PROTOS = {
     "nvb_fm_locate": (_i, [_vp, C.POINTER(FMIndexC), _vp, _u32, _vp, _vp]),
     "nvb_fm_locate_walk": (_i, [_vp, C.POINTER(FMIndexC), _vp, _u32, _vp, _vp]),
     "nvb_fm_locate_lookup": (_i, [_vp, C.POINTER(FMIndexC), _vp, _u32, _vp, _vp]),
+    "nvb_fm_filter_rank": (_i, [_vp, C.POINTER(FMIndexC), StringSetC, _vp, _vp, _vp, _vp]),
+    "nvb_fm_filter_locate": (_i, [_vp, C.POINTER(FMIndexC), _vp, _vp, _u32, C.c_uint64, C.c_uint64, _vp, _vp]),
     "nvb_fm_match_host": (_i, [_vp, C.POINTER(FMIndexC), _vp, _vp, _u32, _vp]),
     "nvb_fm_match_host_packed": (_i, [_vp, C.POINTER(FMIndexC), _vp, _u32, _vp, _u32, _vp]),
     "nvb_fm_locate_host": (_i, [_vp, C.POINTER(FMIndexC), _vp, _u32, _vp]),

@@ -294,6 +294,91 @@ extern "C" int nvb_fm_locate_lookup(nvb_ctx* ctx, const nvb_fmindex* fmi, const 
     return NVB_OK;
 }
 
+// ---------------------------------------------------------------------------------------------
+// FMIndexFilter (nvbio/fmindex/filter.h:40-200, filter_inl.h:193-393): rank = match every string + inclusive scan
+// of the range sizes; locate = for output slot i the (text position, string id) of the i-th occurrence.
+// The expansion is one thread per hit (upper_bound over the scanned sizes, filter_inl.h:75-110), so queries
+// with many occurrences are spread over as many threads as they have hits.
+// ---------------------------------------------------------------------------------------------
+struct RangeSize
+{
+    const uint32_t* r;
+    __host__ __device__ uint64_t operator()(uint32_t i) const { return (uint64_t)(uint32_t)(1u + r[2 * (size_t)i + 1] - r[2 * (size_t)i]); }   // filter_inl.h:30-33
+};
+
+__global__ void __launch_bounds__(FM_THREADS)
+fm_range_size_kernel(const uint32_t* __restrict__ ranges, uint32_t n, uint64_t* __restrict__ sizes)
+{
+    const uint32_t tid = blockIdx.x * FM_THREADS + threadIdx.x;
+    if (tid < n) sizes[tid] = (uint64_t)(uint32_t)(1u + ranges[2 * (size_t)tid + 1] - ranges[2 * (size_t)tid]);
+}
+
+__global__ void __launch_bounds__(FM_THREADS)
+fm_filter_locate_kernel(const FMView f, const uint32_t* __restrict__ ranges, const uint64_t* __restrict__ slots, uint32_t n_queries,
+                        uint64_t begin, uint64_t count, uint32_t* __restrict__ hits)
+{
+    __shared__ uint2 s_lut[FM_LUT_ENTRIES];
+    fm_lut_init(s_lut);
+    const uint64_t tid = (uint64_t)blockIdx.x * FM_THREADS + threadIdx.x;
+    if (tid >= count) return;
+    const uint64_t out = begin + tid;
+    // upper_bound(out, slots, n_queries): first slot with slots[slot] > out
+    uint32_t lo = 0, hi = n_queries;
+    while (lo < hi) { const uint32_t mid = lo + ((hi - lo) >> 1); if (__ldg(slots + mid) <= out) lo = mid + 1; else hi = mid; }
+    const uint32_t slot = lo;
+    uint32_t pos = 0xFFFFFFFFu;
+    if (slot < n_queries)
+    {
+        const uint64_t base = slot ? __ldg(slots + slot - 1) : 0ull;
+        const uint32_t row = __ldg(ranges + 2 * (size_t)slot) + (uint32_t)(out - base);
+        const uint2 w = fm_locate_walk_one(f, row, s_lut);
+        pos = __ldg(f.ssa + (w.x >> 4)) + w.y;
+    }
+    *(uint2*)(hits + 2 * tid) = make_uint2(pos, slot);
+}
+
+// FMIndexFilter::rank: ranges[2n] and slots[n] (inclusive scan of the range sizes) stay on the device;
+// *n_hits_h (optional) = slots[n-1], which costs one synchronisation of the stream
+extern "C" int nvb_fm_filter_rank(nvb_ctx* ctx, const nvb_fmindex* fmi, nvb_string_set queries, uint32_t* ranges,
+                                  uint64_t* slots, uint64_t* n_hits_h, void* stream)
+{
+    if (!ctx || !ranges || !slots) return NVB_ERR_ARG;
+    if (n_hits_h) *n_hits_h = 0;
+    int rc = fm_match_launch<false>(ctx, fmi, queries, ranges, stream); if (rc) return rc;
+    const uint32_t n = queries.count;
+    if (n == 0) return NVB_OK;
+    cudaStream_t s = (cudaStream_t)stream;
+    fm_range_size_kernel<<<grid_for(n), FM_THREADS, 0, s>>>(ranges, n, slots);
+    NVB_LAUNCHED(ctx);
+    void* tmp = nullptr; size_t tmp_bytes = 0;
+    cub::DeviceScan::InclusiveSum(nullptr, tmp_bytes, slots, slots, (int)n, s);
+    if ((rc = nvb_stage(ctx, 7, tmp_bytes, &tmp))) return rc;
+    NVB_CUDA(ctx, cub::DeviceScan::InclusiveSum(tmp, tmp_bytes, slots, slots, (int)n, s));
+    ctx->launches++;
+    if (n_hits_h)
+    {
+        NVB_CUDA(ctx, cudaMemcpyAsync(n_hits_h, slots + (n - 1), sizeof(uint64_t), cudaMemcpyDeviceToHost, s));
+        NVB_CUDA(ctx, cudaStreamSynchronize(s));
+    }
+    return NVB_OK;
+}
+
+// FMIndexFilter::locate(begin, end, hits): hits[2 i] = text position, hits[2 i + 1] = string id, i in [0, end - begin)
+extern "C" int nvb_fm_filter_locate(nvb_ctx* ctx, const nvb_fmindex* fmi, const uint32_t* ranges, const uint64_t* slots,
+                                    uint32_t n_queries, uint64_t begin, uint64_t end, uint32_t* hits, void* stream)
+{
+    if (!ctx) return NVB_ERR_ARG;
+    int rc = check_fmi(fmi, true); if (rc) return rc;
+    if (end <= begin || n_queries == 0) return NVB_OK;
+    if (!ranges || !slots || !hits) return NVB_ERR_ARG;
+    const uint64_t count = end - begin;
+    if (count > 0x7FFFFFFFull * FM_THREADS) return NVB_ERR_ARG;
+    const uint32_t grid = (uint32_t)((count + FM_THREADS - 1) / FM_THREADS);
+    fm_filter_locate_kernel<<<grid, FM_THREADS, 0, (cudaStream_t)stream>>>(make_view(fmi), ranges, slots, n_queries, begin, count, hits);
+    NVB_LAUNCHED(ctx);
+    return NVB_OK;
+}
+
 extern "C" size_t nvb_bwt_occ_words(uint32_t length) { return (size_t)((((length + 15u) / 16u) + 3u) & ~3u) * 2u; }
 extern "C" size_t nvb_ssa_words(uint32_t length) { return ((size_t)length + 16u) / 16u; }
 

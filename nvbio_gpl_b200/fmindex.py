@@ -237,6 +237,45 @@ def fuse(bwt_words, length, ctx=None):
     return out, [int(v) for v in L2]
 
 
+class FMIndexFilter:
+    """FMIndexFilter<device_tag, fm_index_type> (nvbio/fmindex/filter.h:108-165): rank() matches every string of a set
+    and scans the range sizes; locate(begin, end) enumerates hits [begin, end) as (text position, string id)."""
+
+    def __init__(self, ctx=None):
+        self.ctx = ctx
+        self.index = None
+        self.n_queries = 0
+        self.n_occurrences = 0
+        self.ranges = None     # int32 [n, 2]  (raw uint32 inclusive SA intervals)
+        self.slots = None      # int64 [n]     (inclusive scan of the range sizes)
+
+    def rank(self, fmi, symbols, offsets, bits=8):
+        ctx = _ctx(fmi.bwt_occ, self.ctx)
+        n = offsets.numel() - 1
+        self.index, self.n_queries = fmi, n
+        self.ranges = torch.empty((n, 2), dtype=torch.int32, device=fmi.device)
+        self.slots = torch.empty(n, dtype=torch.int64, device=fmi.device)
+        total = C.c_uint64(0)
+        f = fmi.c()
+        check(lib().nvb_fm_filter_rank(ctx.h, C.byref(f), _set_c(symbols, offsets, bits), self.ranges.data_ptr(), self.slots.data_ptr(),
+                                       C.addressof(total), _lib.current_stream_ptr()), ctx.h)
+        self.n_occurrences = int(total.value)
+        return self.n_occurrences
+
+    def n_hits(self):
+        return self.n_occurrences
+
+    def locate(self, begin, end, hits=None):
+        fmi = self.index
+        ctx = _ctx(fmi.bwt_occ, self.ctx)
+        if hits is None:
+            hits = torch.empty((max(0, end - begin), 2), dtype=torch.int32, device=fmi.device)
+        f = fmi.c()
+        check(lib().nvb_fm_filter_locate(ctx.h, C.byref(f), self.ranges.data_ptr(), self.slots.data_ptr(), self.n_queries,
+                                         begin, end, hits.data_ptr(), _lib.current_stream_ptr()), ctx.h)
+        return hits
+
+
 # host-buffer forms: numpy (ideally pinned) in, numpy out; H2D + kernel + D2H inside the call
 def match_host(fmi, symbols_h, offsets_h, ranges_h=None, ctx=None, bits=8):
     """bits = 8: one symbol per byte; bits = 4 | 2: symbols_h is the packed big-endian uint32 word stream (pack_symbols)"""

@@ -128,3 +128,28 @@ def test_host_entry_packed_and_chunked(oracle):
     assert (nvb.match_host(fmi, nvb.pack_symbols(Q, 4), qo, bits=4) == want).all()
     Q2 = Q.copy(); Q2[Q2 > 3] = 0
     assert (nvb.match_host(fmi, nvb.pack_symbols(Q2, 2), qo, bits=2) == oracle.fm_match(oidx, Q2, qo)).all()
+
+
+def test_fmindex_filter_rank_and_locate(oracle):
+    """FMIndexFilter (filter_inl.h:75-110,261-393): scanned range sizes and (position, string id) hits, checked against the
+    composition of the oracle's match / locate with the reference's slot arithmetic"""
+    rng = np.random.default_rng(41)
+    text = rng.integers(0, 4, 40000).astype(np.uint8)
+    fmi, oidx = gu.fm_index_pair(oracle, text)
+    Q, qo = util.rand_queries(rng, text, 5000, len_range=(0, 14))      # short queries: many multi-hit ranges, some empty
+    qs = gu.sset(Q, qo)
+    flt = nvb.FMIndexFilter()
+    n_hits = flt.rank(fmi, qs.symbols, qs.offsets)
+    want_r = oracle.fm_match(oidx, Q, qo)
+    sizes = (1 + want_r[:, 1].astype(np.int64) - want_r[:, 0].astype(np.int64)) & 0xFFFFFFFF
+    want_slots = np.cumsum(sizes)
+    assert (flt.ranges.cpu().numpy().view(np.uint32) == want_r).all()
+    assert (flt.slots.cpu().numpy() == want_slots).all() and n_hits == int(want_slots[-1])
+    for b, e in [(0, min(n_hits, 200000)), (n_hits // 3, min(n_hits, n_hits // 3 + 50001)), (max(0, n_hits - 7), n_hits)]:
+        hits = flt.locate(b, e).cpu().numpy().view(np.uint32)
+        idx = np.arange(b, e, dtype=np.int64)
+        slot = np.searchsorted(want_slots, idx, side="right")
+        base = np.where(slot > 0, want_slots[np.maximum(slot, 1) - 1], 0)
+        rows = (want_r[slot, 0].astype(np.int64) + (idx - base)).astype(np.uint32)
+        assert (hits[:, 1] == slot).all()
+        assert (hits[:, 0] == oracle.fm_locate(oidx, rows)).all()
