@@ -119,6 +119,12 @@ void        nvb_host_free(void* ptr_h);
  * (fmi_h: bwt_occ / ssa are HOST pointers) and fill *fmi_d with device pointers owned by ctx. */
 int nvb_fmindex_upload(nvb_ctx* ctx, const nvb_fmindex* fmi_h, nvb_fmindex* fmi_d);
 int nvb_fmindex_release(nvb_ctx* ctx, nvb_fmindex* fmi_d);
+/* io::FMIndexDataHost::load + FMIndexDataDevice (nvbio/io/fmindex/fmindex_impl.cu:111-321,333-479): reads the files the
+ * reference's nvBWT tool writes (nvBWT/nvBWT.cu:303-340) -- <prefix>.bwt + .sa, or .rbwt + .rsa when reverse != 0 --
+ * and rebuilds the fused occurrence image on the device. A missing .sa leaves fmi_d->ssa NULL (match/rank only). */
+int nvb_fmindex_load(nvb_ctx* ctx, const char* prefix, int reverse, nvb_fmindex* fmi_d);
+/* the inverse: writes a device index in nvBWT's on-disk format */
+int nvb_fmindex_save(nvb_ctx* ctx, const nvb_fmindex* fmi_d, const char* prefix, int reverse);
 /* pin the first `bytes` of the fused array (the hot BWT prefix) in L2 for work on the ctx stream
  * (cudaAccessPolicyWindow); bytes = 0 removes the window. Replaces the reference's texture/__ldg
  * cache hint (nvbio/fmindex/fmindex.h:564-583). */

@@ -67,6 +67,8 @@ _PROTOS = {
     "nvb_fm_locate": (_i, [_vp, C.POINTER(FMIndexC), _vp, _u32, _vp, _vp]),
     "nvb_fm_locate_walk": (_i, [_vp, C.POINTER(FMIndexC), _vp, _u32, _vp, _vp]),
     "nvb_fm_locate_lookup": (_i, [_vp, C.POINTER(FMIndexC), _vp, _u32, _vp, _vp]),
+    "nvb_fmindex_load": (_i, [_vp, C.c_char_p, _i, C.POINTER(FMIndexC)]),
+    "nvb_fmindex_save": (_i, [_vp, C.POINTER(FMIndexC), C.c_char_p, _i]),
     "nvb_fm_filter_rank": (_i, [_vp, C.POINTER(FMIndexC), StringSetC, _vp, _vp, _vp, _vp]),
     "nvb_fm_filter_locate": (_i, [_vp, C.POINTER(FMIndexC), _vp, _vp, _u32, C.c_uint64, C.c_uint64, _vp, _vp]),
     "nvb_fm_match_host": (_i, [_vp, C.POINTER(FMIndexC), _vp, _vp, _u32, _vp]),

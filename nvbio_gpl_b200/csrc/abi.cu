@@ -1,5 +1,6 @@
 // abi.cu -- context, index image management and the host-buffer (*_host) entry points.
 #include "common.cuh"
+#include <string>
 #include <stdlib.h>
 #include <string.h>
 #include <new>
@@ -122,6 +123,102 @@ extern "C" int nvb_fmindex_upload(nvb_ctx* ctx, const nvb_fmindex* h, nvb_fminde
         d->ssa = (const uint32_t*)s;
     }
     NVB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return NVB_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// nvBWT on-disk index (written by the reference's nvBWT tool, nvBWT/nvBWT.cu:303-340; read by
+// io::FMIndexDataHost::load, nvbio/io/fmindex/fmindex_impl.cu:111-321,333-479):
+//   <prefix>.bwt / .rbwt : uint32 primary, uint32 cumFreq[4] (cumFreq[3] = text length), BWT words
+//                          (2-bit symbols, 16 per big-endian uint32; padded here to a multiple of 4 words with zeros)
+//   <prefix>.sa  / .rsa  : uint32 primary, 4 x uint32 (ignored: nvBWT.cu:337 writes pointer bytes there), uint32 SA_INT,
+//                          uint32 text length, then ssa[1 ..] (ssa[0] = 0xFFFFFFFF is implied)
+// The occurrence counters are not stored: the fused image is rebuilt on the device (nvb_fmindex_fuse).
+// ---------------------------------------------------------------------------------------------
+#include <cstdio>
+#include <vector>
+extern "C" int nvb_fmindex_load(nvb_ctx* ctx, const char* prefix, int reverse, nvb_fmindex* d)
+{
+    if (!ctx || !prefix || !d) return NVB_ERR_ARG;
+    memset(d, 0, sizeof(*d));
+    d->occ_int = 64; d->sa_int = 16;
+    NVB_CUDA(ctx, cudaSetDevice(ctx->device));
+    std::string name = std::string(prefix) + (reverse ? ".rbwt" : ".bwt");
+    FILE* f = fopen(name.c_str(), "rb");
+    if (!f) return NVB_ERR_ARG;
+    uint32_t hdr[5];
+    if (fread(hdr, sizeof(uint32_t), 5, f) != 5) { fclose(f); return NVB_ERR_ARG; }
+    const uint32_t primary = hdr[0], length = hdr[4];
+    const size_t words = nvb_bwt_occ_words(length) / 2;                  // ceil(length / 16) rounded up to 4
+    std::vector<uint32_t> bwt(words ? words : 4, 0u);
+    const size_t got = fread(bwt.data(), sizeof(uint32_t), words, f);
+    fclose(f);
+    if (((got + 3) & ~(size_t)3) != words) return NVB_ERR_ARG;           // fmindex_impl.cu:153-158
+    void *d_bwt = nullptr, *d_img = nullptr;
+    NVB_CUDA(ctx, cudaMalloc(&d_bwt, (words ? words : 4) * sizeof(uint32_t)));
+    NVB_CUDA(ctx, cudaMalloc(&d_img, (words ? words : 4) * 2 * sizeof(uint32_t)));
+    NVB_CUDA(ctx, cudaMemcpyAsync(d_bwt, bwt.data(), words * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
+    uint32_t L2[5];
+    int rc = nvb_fmindex_fuse(ctx, (const uint32_t*)d_bwt, length, (uint32_t*)d_img, L2, ctx->stream);
+    cudaFree(d_bwt);
+    if (rc) { cudaFree(d_img); return rc; }
+    d->length = length; d->primary = primary;
+    for (int i = 0; i < 5; ++i) d->L2[i] = L2[i];
+    d->bwt_occ = d_img;
+    // the counts recomputed from the words must agree with the file's cumulative frequencies
+    if (L2[1] != hdr[1] || L2[2] != hdr[2] || L2[3] != hdr[3] || L2[4] != hdr[4]) { nvb_fmindex_release(ctx, d); return NVB_ERR_ARG; }
+    // sampled suffix array (optional, like the reference: a missing or mismatching file leaves ssa = NULL)
+    name = std::string(prefix) + (reverse ? ".rsa" : ".sa");
+    f = fopen(name.c_str(), "rb");
+    if (f)
+    {
+        uint32_t sh[7];
+        const size_t n_ssa = nvb_ssa_words(length);
+        if (fread(sh, sizeof(uint32_t), 7, f) == 7 && sh[0] == primary && sh[5] == 16u && sh[6] == length)
+        {
+            std::vector<uint32_t> ssa(n_ssa, 0xFFFFFFFFu);
+            if (n_ssa <= 1 || fread(ssa.data() + 1, sizeof(uint32_t), n_ssa - 1, f) == n_ssa - 1)
+            {
+                void* d_ssa = nullptr;
+                if (cudaMalloc(&d_ssa, n_ssa * sizeof(uint32_t)) == cudaSuccess &&
+                    cudaMemcpy(d_ssa, ssa.data(), n_ssa * sizeof(uint32_t), cudaMemcpyHostToDevice) == cudaSuccess)
+                    d->ssa = (const uint32_t*)d_ssa;
+            }
+        }
+        fclose(f);
+    }
+    return NVB_OK;
+}
+
+// writes <prefix>.bwt/.sa (or .rbwt/.rsa) from a device index: the inverse of nvb_fmindex_load, in nvBWT's format
+extern "C" int nvb_fmindex_save(nvb_ctx* ctx, const nvb_fmindex* d, const char* prefix, int reverse)
+{
+    if (!ctx || !d || !prefix || !d->bwt_occ) return NVB_ERR_ARG;
+    NVB_CUDA(ctx, cudaSetDevice(ctx->device));
+    const size_t img_words = nvb_bwt_occ_words(d->length);
+    std::vector<uint32_t> img(img_words ? img_words : 8);
+    NVB_CUDA(ctx, cudaMemcpy(img.data(), d->bwt_occ, img_words * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+    std::string name = std::string(prefix) + (reverse ? ".rbwt" : ".bwt");
+    FILE* f = fopen(name.c_str(), "wb");
+    if (!f) return NVB_ERR_ARG;
+    const uint32_t hdr[5] = { d->primary, d->L2[1], d->L2[2], d->L2[3], d->L2[4] };
+    fwrite(hdr, sizeof(uint32_t), 5, f);
+    const size_t n_words = ((size_t)d->length + 15) / 16;                // nvBWT writes exactly the used words
+    for (size_t w = 0; w < n_words; ++w) fwrite(&img[(w / 4) * 8 + (w & 3)], sizeof(uint32_t), 1, f);
+    fclose(f);
+    if (d->ssa)
+    {
+        const size_t n_ssa = nvb_ssa_words(d->length);
+        std::vector<uint32_t> ssa(n_ssa);
+        NVB_CUDA(ctx, cudaMemcpy(ssa.data(), d->ssa, n_ssa * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+        name = std::string(prefix) + (reverse ? ".rsa" : ".sa");
+        f = fopen(name.c_str(), "wb");
+        if (!f) return NVB_ERR_ARG;
+        const uint32_t sh[7] = { d->primary, 0, 0, 0, 0, 16u, d->length };
+        fwrite(sh, sizeof(uint32_t), 7, f);
+        if (n_ssa > 1) fwrite(ssa.data() + 1, sizeof(uint32_t), n_ssa - 1, f);
+        fclose(f);
+    }
     return NVB_OK;
 }
 

@@ -153,3 +153,36 @@ def test_fmindex_filter_rank_and_locate(oracle):
         rows = (want_r[slot, 0].astype(np.int64) + (idx - base)).astype(np.uint32)
         assert (hits[:, 1] == slot).all()
         assert (hits[:, 0] == oracle.fm_locate(oidx, rows)).all()
+
+
+def test_nvbwt_files_round_trip(oracle, tmp_path):
+    """nvBWT on-disk format (nvBWT.cu:303-340 / fmindex_impl.cu:111-321): what the library writes is what an independent
+    writer following the reference produces; both loaders (numpy + device fuse, and the C entry point) give back the index"""
+    rng = np.random.default_rng(51)
+    for n in (1, 63, 64, 1000, 40037):
+        text = rng.integers(0, 4, n).astype(np.uint8)
+        fmi, oidx = gu.fm_index_pair(oracle, text)
+        prefix = str(tmp_path / ("idx%d" % n))
+        nvb.save_index(fmi, prefix)
+        # independent writer from the oracle's image: de-interleave the BWT words, header as nvBWT writes it
+        img = oidx.bwt_occ.reshape(-1, 8)
+        words = img[:, :4].reshape(-1)[: (n + 15) // 16]
+        want_bwt = np.concatenate([np.array([oidx.primary] + [int(v) for v in oidx.L2[1:5]], dtype=np.uint32), words.astype(np.uint32)])
+        got_bwt = np.fromfile(prefix + ".bwt", dtype=np.uint32)
+        assert (got_bwt == want_bwt).all()
+        got_sa = np.fromfile(prefix + ".sa", dtype=np.uint32)
+        assert got_sa[0] == oidx.primary and got_sa[5] == 16 and got_sa[6] == n and (got_sa[7:] == oidx.ssa[1:]).all()
+        back = nvb.load_index(prefix, gu.dev())
+        b2, s2 = back.host_arrays()
+        assert back.length == n and back.primary == oidx.primary and list(back.L2) == [int(v) for v in oidx.L2]
+        assert (b2 == oidx.bwt_occ).all() and (s2 == oidx.ssa).all()
+        c = nvb.CLoadedIndex(prefix)
+        Q, qo = util.rand_queries(rng, text, 2000, len_range=(0, 12))
+        qs = gu.sset(Q, qo)
+        want = oracle.fm_match(oidx, Q, qo)
+        assert (c.match(qs.symbols, qs.offsets).cpu().numpy().view(np.uint32) == want).all()
+        rows = want[want[:, 0] <= want[:, 1], 0].copy()
+        if len(rows):
+            pos = c.locate(torch.from_numpy(rows.view(np.int32)).to(gu.dev())).cpu().numpy().view(np.uint32)
+            assert (pos == oracle.fm_locate(oidx, rows)).all()
+        c.close()
