@@ -27,60 +27,126 @@
 // to the int32 kernel through the worklist (dp_fast.h).
 #include "dp_band2.cuh"
 
+// per-launch constants of the row loop, and the running arg-max of LOCAL alignments
+struct RowConst
+{
+    uint32_t lut_addr, dfix, one, k8, k32;
+    uint32_t Af, Bf, ext2, B2, sixteen;      // LOCAL (unsheared, biased): top/open addend, left addend, packed extension, packed zero, runtime 16
+};
+struct LocalBest { uint32_t key, row, rmask; };   // packed (biased score << 4 | band cell), packed pattern rows, halves still running
+
 // one pattern row: cell j reads window slot (R0 + j) % WS
-template <int W, bool GOTOH, int WS, int R0>
+template <int W, int TYPE, bool GOTOH, int WS, int R0>
 __device__ __forceinline__ void c_row(uint32_t (&X)[W], uint32_t (&F)[W], const uint32_t (&win)[WS], const uint2 pq,
-                                      const uint32_t dfix, const uint32_t one)
+                                      const RowConst& rc, LocalBest& lb, const uint32_t i)
 {
     uint32_t left = 0, E = 0;
-    #pragma unroll
-    for (int j = 0; j < W; ++j)
+    if (TYPE != T_LOCAL)
     {
-        const uint32_t S = c_prmt(pq.x, pq.y, win[(R0 + j) % WS]);
-        const uint32_t dg = X[j] + S;
-        uint32_t h;
-        if (!GOTOH)
+        #pragma unroll
+        for (int j = 0; j < W; ++j)
         {
-            if (j == 0)          h = __vmaxs2(dg, X[1 < W ? 1 : 0]);
-            else if (j < W - 1)  h = __vimax3_s16x2(dg, X[j + 1 < W ? j + 1 : j], left);
-            else                 h = __vmaxs2(dg, left);
+            const uint32_t S = c_prmt(pq.x, pq.y, win[(R0 + j) % WS]);
+            const uint32_t dg = X[j] + S;
+            uint32_t h;
+            if (!GOTOH)
+            {
+                if (j == 0)          h = __vmaxs2(dg, X[1 < W ? 1 : 0]);
+                else if (j < W - 1)  h = __vimax3_s16x2(dg, X[j + 1 < W ? j + 1 : j], left);
+                else                 h = __vmaxs2(dg, left);
+                X[j] = h; left = h;
+            }
+            else
+            {
+                if (j < W - 1) F[j] = __vmaxs2(F[j + 1 < W ? j + 1 : j], X[j + 1 < W ? j + 1 : j]);
+                else           F[j] = B2_INF2;
+                if (j == 0)          h = __vmaxs2(dg, F[0]);
+                else if (j < W - 1)  h = __vimax3_s16x2(dg, F[j], E);
+                else                 h = __vmaxs2(dg, E);
+                const uint32_t ho = c_imad(h, rc.one, rc.dfix);
+                E = (j == 0) ? ho : __vmaxs2(E, ho);
+                X[j] = ho;
+            }
+        }
+    }
+    else
+    {
+        // LOCAL: unsheared scores biased by the largest gap penalty (zero = B2), so that the gap additions are plain IMADs;
+        // every cell is reported: rows ascending, band cells ascending, the last maximum wins (sw_banded_inl.h:407-456)
+        uint32_t key[W];
+        #pragma unroll
+        for (int j = 0; j < W; ++j)
+        {
+            const uint32_t S = c_prmt(pq.x, pq.y, win[(R0 + j) % WS]);
+            uint32_t h;
+            if (!GOTOH)
+            {
+                if (j == 0)
+                {
+                    const uint32_t u = c_imad(X[1 < W ? 1 : 0], rc.one, rc.Af);
+                    h = __vmaxs2(__viaddmax_s16x2(X[0], S, u), rc.B2);
+                }
+                else if (j < W - 1)
+                {
+                    const uint32_t u = c_imad(X[j + 1 < W ? j + 1 : j], rc.one, rc.Af);
+                    const uint32_t v = __viaddmax_s16x2(X[j], S, u);
+                    h = __vimax3_s16x2(c_imad(left, rc.one, rc.Bf), v, rc.B2);
+                }
+                else h = __vmaxs2(__viaddmax_s16x2(X[j], S, c_imad(left, rc.one, rc.Bf)), rc.B2);
+            }
+            else
+            {
+                if (j < W - 1)
+                {
+                    const uint32_t o = c_imad(X[j + 1 < W ? j + 1 : j], rc.one, rc.Af);
+                    F[j] = __viaddmax_s16x2(F[j + 1 < W ? j + 1 : j], rc.ext2, o);        // max(F + ext, H + open)
+                    const uint32_t v = __viaddmax_s16x2(X[j], S, F[j]);
+                    h = (j == 0) ? __vmaxs2(v, rc.B2) : __vimax3_s16x2(v, E, rc.B2);
+                    const uint32_t o2 = c_imad(h, rc.one, rc.Af);
+                    E = (j == 0) ? o2 : __viaddmax_s16x2(E, rc.ext2, o2);                  // max(E + ext, H + open)
+                }
+                else
+                {
+                    F[j] = B2_INF2;
+                    h = __vmaxs2(__viaddmax_s16x2(X[j], S, E), rc.B2);
+                }
+            }
             X[j] = h; left = h;
+            key[j] = c_imad(h, rc.sixteen, (uint32_t)j * 0x00010001u);
         }
-        else
-        {
-            if (j < W - 1) F[j] = __vmaxs2(F[j + 1 < W ? j + 1 : j], X[j + 1 < W ? j + 1 : j]);
-            else           F[j] = B2_INF2;
-            if (j == 0)          h = __vmaxs2(dg, F[0]);
-            else if (j < W - 1)  h = __vimax3_s16x2(dg, F[j], E);
-            else                 h = __vmaxs2(dg, E);
-            const uint32_t ho = c_imad(h, one, dfix);
-            E = (j == 0) ? ho : __vmaxs2(E, ho);
-            X[j] = ho;
-        }
+        // later rows win ties: compare against the best with its cell bits cleared, minus one
+        const uint32_t kb = __vadd2(lb.key & 0xFFF0FFF0u, 0xFFFFFFFFu);
+        uint32_t acc = kb;
+        #pragma unroll
+        for (int j = 0; j + 1 < W; j += 2) acc = __vimax3_s16x2(acc, key[j], key[j + 1]);
+        if (W & 1) acc = __vmaxs2(acc, key[W - 1]);
+        const uint32_t d = __vsub2(kb, acc);                              // < 0 in a half that improved
+        const uint32_t m = c_prmt(d, d, 0xBB99u) & lb.rmask;             // 0xFFFF per improved, running half
+        lb.key = (acc & m) | (lb.key & ~m);
+        lb.row = ((i * 0x00010001u) & m) | (lb.row & ~m);
     }
 }
 
-// rows R0 .. RU-1 of a group
+// rows R0 .. RU-1 of a group starting at pattern row i0
 template <int W, int RU, int R0>
 struct RowUnroll
 {
-    template <bool GOTOH, int WS>
+    template <int TYPE, bool GOTOH, int WS>
     static __device__ __forceinline__ void run(uint32_t (&X)[W], uint32_t (&F)[W], uint32_t (&win)[WS], const uint8_t* pA, const uint8_t* pB,
-                                               const uint8_t* tA, const uint8_t* tB, uint32_t lut_addr, uint32_t dfix, uint32_t one,
-                                               uint32_t k8, uint32_t k32)
+                                               const uint8_t* tA, const uint8_t* tB, const RowConst& rc, LocalBest& lb, uint32_t i0)
     {
-        const uint2 pq = c_lds64(c_imad(pA[R0], k8, c_imad(pB[R0], k32, lut_addr)));     // runtime 8 and 32: IMADs stay IMADs (FMA pipe)
+        const uint2 pq = c_lds64(c_imad(pA[R0], rc.k8, c_imad(pB[R0], rc.k32, rc.lut_addr)));     // runtime 8 and 32: IMADs stay IMADs (FMA pipe)
         win[(R0 + W - 1) % WS] = c_imad(tB[R0], 0x1100u, c_imad(tA[R0], 0x11u, 0xC480u));
-        c_row<W, GOTOH, WS, R0>(X, F, win, pq, dfix, one);
-        RowUnroll<W, RU, R0 + 1>::template run<GOTOH, WS>(X, F, win, pA, pB, tA, tB, lut_addr, dfix, one, k8, k32);
+        c_row<W, TYPE, GOTOH, WS, R0>(X, F, win, pq, rc, lb, i0 + R0);
+        RowUnroll<W, RU, R0 + 1>::template run<TYPE, GOTOH, WS>(X, F, win, pA, pB, tA, tB, rc, lb, i0);
     }
 };
 template <int W, int RU>
 struct RowUnroll<W, RU, RU>
 {
-    template <bool GOTOH, int WS>
+    template <int TYPE, bool GOTOH, int WS>
     static __device__ __forceinline__ void run(uint32_t (&)[W], uint32_t (&)[W], uint32_t (&)[WS], const uint8_t*, const uint8_t*,
-                                               const uint8_t*, const uint8_t*, uint32_t, uint32_t, uint32_t, uint32_t, uint32_t) {}
+                                               const uint8_t*, const uint8_t*, const RowConst&, LocalBest&, uint32_t) {}
 };
 
 template <int W, int TYPE, bool GOTOH, int MINB>
@@ -112,8 +178,12 @@ band2_kernel(const Band2Params p)
     const uint32_t Mmax = max(MA, MB), Mmin = min(MA, MB);
 
     uint8_t* slot = s_raw + 128 + (size_t)threadIdx.x * STRIDE;
-    const uint32_t lut_addr = (uint32_t)__cvta_generic_to_shared(s_raw);
-    const uint32_t dfix = p.d ? c_fix2(p.d) : 0u;        // c_fix2(0) would borrow from the high half
+    RowConst rc;
+    rc.lut_addr = (uint32_t)__cvta_generic_to_shared(s_raw);
+    rc.dfix = p.d ? c_fix2(p.d) : 0u;                    // c_fix2(0) would borrow from the high half
+    rc.one = p.one; rc.k8 = p.k8; rc.k32 = p.k32;
+    rc.Af = c_fix2(p.ga); rc.Bf = c_fix2(p.gb); rc.ext2 = c_pack2(p.gb); rc.B2 = c_pack2(p.bias); rc.sixteen = p.k8 * 2u;
+    LocalBest lb; lb.key = rc.B2 << 4; lb.row = 0; lb.rmask = 0xFFFFFFFFu;
 
     uint32_t seen = 0;
     Stream sPA, sPB, sTA, sTB;
@@ -136,13 +206,14 @@ band2_kernel(const Band2Params p)
     }
 
     int32_t scoreA = NVB_SINK_MIN, scoreB = NVB_SINK_MIN;
-    uint32_t sxA = 0xFFFFFFFFu, sxB = 0xFFFFFFFFu;
+    uint32_t sxA = 0xFFFFFFFFu, sxB = 0xFFFFFFFFu, syA = 0xFFFFFFFFu, syB = 0xFFFFFFFFu;
     uint32_t i = 0;
 
     #pragma unroll 1
     for (int seg = 0; seg < 2; ++seg)
     {
         const uint32_t target = seg ? Mmax : Mmin;
+        if (seg) lb.rmask = MA > MB ? 0x0000FFFFu : 0xFFFF0000u;     // only the couple's longer pattern goes on
         // groups of RU rows, all four streams in step (only before the first single row, i.e. in the first segment):
         // the window rotates in place and is linear again (slot s <-> text position i + s) after each group
         if (seg == 0)
@@ -152,7 +223,7 @@ band2_kernel(const Band2Params p)
             for (uint32_t g = target / RU; g > 0; --g)
             {
                 const uint4 vPA = c_load(sPA, sPA.nb), vPB = c_load(sPB, sPB.nb), vTA = c_load(sTA, sTA.nb), vTB = c_load(sTB, sTB.nb);
-                RowUnroll<W, RU, 0>::template run<GOTOH, WS>(X, F, win, sPA.ptr, sPB.ptr, sTA.ptr, sTB.ptr, lut_addr, dfix, p.one, p.k8, p.k32);
+                RowUnroll<W, RU, 0>::template run<TYPE, GOTOH, WS>(X, F, win, sPA.ptr, sPB.ptr, sTA.ptr, sTB.ptr, rc, lb, i);
                 seen |= vPA.x | vPA.y | vPA.z | vPA.w | vPB.x | vPB.y | vPB.z | vPB.w;
                 seen |= vTA.x | vTA.y | vTA.z | vTA.w | vTB.x | vTB.y | vTB.z | vTB.w;
                 // bytes past the end of a string are read: text right of the band's last cells, and the shorter pattern of
@@ -190,7 +261,7 @@ band2_kernel(const Band2Params p)
         #pragma unroll 1
         while (i < target)
         {
-            RowUnroll<W, 1, 0>::template run<GOTOH, WS>(X, F, win, sPA.ptr, sPB.ptr, sTA.ptr, sTB.ptr, lut_addr, dfix, p.one, p.k8, p.k32);
+            RowUnroll<W, 1, 0>::template run<TYPE, GOTOH, WS>(X, F, win, sPA.ptr, sPB.ptr, sTA.ptr, sTB.ptr, rc, lb, i);
             #pragma unroll
             for (int j = 0; j < W - 1; ++j) win[j] = win[j + 1];
             c_step(sPA, seen); c_step(sPB, seen); c_step(sTA, seen); c_step(sTB, seen);
@@ -202,6 +273,14 @@ band2_kernel(const Band2Params p)
         {
             const uint32_t M = h ? MB : MA, N = h ? NB : NA;
             if (M != target || (seg == 1 && Mmin == Mmax) || M == 0 || N < M) continue;   // shorter texts are refused (sw_banded_inl.h:356-357)
+            if (TYPE == T_LOCAL)
+            {
+                const uint32_t k = h ? (lb.key >> 16) : (lb.key & 0xFFFFu), row = h ? (lb.row >> 16) : (lb.row & 0xFFFFu);
+                const int32_t best = (int32_t)(k >> 4) - p.bias;
+                const uint32_t bx = row + (k & 15u) + 1u;
+                if (h) { scoreB = best; sxB = bx; syB = row + 1u; } else { scoreA = best; sxA = bx; syA = row + 1u; }
+                continue;
+            }
             const int32_t back = p.alpha * (int32_t)M - p.bias - (GOTOH ? p.d : 0);
             int32_t best = NVB_SINK_MIN; uint32_t bx = 0xFFFFFFFFu;
             if (TYPE == T_GLOBAL) { best = (h ? c_hi(X[W - 1]) : c_lo(X[W - 1])) + back + p.beta * (W - 1); bx = M + W - 1; }
@@ -215,7 +294,7 @@ band2_kernel(const Band2Params p)
                     if ((j == 0 || (uint32_t)j < lim) && best <= s) { best = s; bx = M + j; }
                 }
             }
-            if (h) { scoreB = best; sxB = bx; } else { scoreA = best; sxA = bx; }
+            if (h) { scoreB = best; sxB = bx; syB = M; } else { scoreA = best; sxA = bx; syA = M; }
         }
     }
 
@@ -223,7 +302,8 @@ band2_kernel(const Band2Params p)
     bool dirty = MA == 0 || MB == 0;
     // GLOBAL reports the band's last cell; when that lies right of the text the reference's score depends on the 255s it
     // reads there (sw_banded_inl.h:444), which this kernel's text stream does not reproduce
-    if (TYPE == T_GLOBAL) dirty = dirty || NA < MA + W - 1 || NB < MB + W - 1;
+    // LOCAL reports every band cell, the ones right of the text included (where the reference reads 255s as well)
+    if (TYPE != T_SEMI) dirty = dirty || NA < MA + W - 1 || NB < MB + W - 1;
     if (seen & 0xFCFCFCFCu)
         dirty = dirty || c_has_high_symbol(p.P.sym, pbA, MA) || c_has_high_symbol(p.P.sym, pbB, MB) ||
                 c_has_high_symbol(p.T.sym, tbA, NA) || c_has_high_symbol(p.T.sym, tbB, NB);
@@ -240,7 +320,7 @@ band2_kernel(const Band2Params p)
         }
         nvb_best_sink out;
         out.score = h ? scoreB : scoreA; out.sink_x = h ? sxB : sxA;
-        out.sink_y = out.sink_x == 0xFFFFFFFFu ? 0xFFFFFFFFu : (h ? MB : MA);
+        out.sink_y = out.sink_x == 0xFFFFFFFFu ? 0xFFFFFFFFu : (h ? syB : syA);
         p.sinks[id] = out;
     }
 }
@@ -281,6 +361,7 @@ static int band2_dispatch(nvb_ctx* ctx, const nvb_aligner& a, const Band2Params&
 {
     const bool g = a.kind == NVB_GOTOH;
     if (a.type == NVB_GLOBAL) return g ? band2_launch<W, T_GLOBAL, true>(ctx, p, st) : band2_launch<W, T_GLOBAL, false>(ctx, p, st);
+    if (a.type == NVB_LOCAL)  return g ? band2_launch<W, T_LOCAL, true>(ctx, p, st) : band2_launch<W, T_LOCAL, false>(ctx, p, st);
     return g ? band2_launch<W, T_SEMI, true>(ctx, p, st) : band2_launch<W, T_SEMI, false>(ctx, p, st);
 }
 

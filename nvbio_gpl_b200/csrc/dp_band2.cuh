@@ -20,6 +20,7 @@ struct Band2Params
     uint32_t       s_match, s_mis;      // profile bytes S' (SW) / S'' (Gotoh), 0..127
     int32_t        d;                   // Gotoh: go - ge (<= 0)
     uint32_t       one, k8, k32;        // runtime 1, 8, 32
+    int32_t        ga, gb;              // LOCAL (unsheared): SW deletion / insertion, Gotoh open / extension
 };
 
 __device__ __forceinline__ uint32_t c_pack2(int32_t v) { return ((uint32_t)v & 0xFFFFu) * 0x00010001u; }
@@ -129,9 +130,24 @@ static inline Band2Plan band2_plan(const nvb_aligner& a, uint32_t band, uint32_t
     Band2Params& p = pl.p;
     const Scheme s = make_scheme(a);
     const bool g = a.kind == NVB_GOTOH;
-    if (a.type == NVB_LOCAL) return pl;
     if (band != 7 && band != 15) return pl;
     if (maxM == 0) return pl;
+    p.ga = s.ga; p.gb = s.gb;
+    if (a.type == NVB_LOCAL)
+    {
+        // unsheared, biased by the largest gap penalty; raw signed profile bytes; 11 score bits in the arg-max key
+        if (s.match < -127 || s.match > 127 || s.mismatch < -127 || s.mismatch > 127) return pl;
+        if (s.ga >= 0 || s.gb >= 0 || s.ga < -64 || s.gb < -64) return pl;
+        if (g && s.ga > s.gb) return pl;
+        if ((uint64_t)max(s.match, 0) * maxM + 64u >= 2047u) return pl;
+        p.alpha = p.beta = 0; p.d = 0;
+        p.bias = max(iabs2(s.ga), iabs2(s.gb));
+        p.s_match = (uint32_t)s.match & 0xFFu; p.s_mis = (uint32_t)s.mismatch & 0xFFu;
+        p.init0 = p.init_rest = p.bias; p.init_step = 0;
+        p.one = 1; p.k8 = 8; p.k32 = 32;
+        pl.ok = true;
+        return pl;
+    }
     const int32_t W = (int32_t)band;
     int32_t smin, lo0, hi0;          // smallest diagonal increment; range of the true first row H''_0
     if (!g)
