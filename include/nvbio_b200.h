@@ -253,6 +253,47 @@ uint32_t nvb_last_paths(nvb_ctx* ctx);
 /* force the int32 generic kernels (parity anchor) : 0 = auto, 1 = generic only */
 void nvb_force_generic(nvb_ctx* ctx, int on);
 
+/* ----------------------------------------------------------------------------------------- */
+/* seed -> locate -> extend -> reduce -> traceback over a read batch.         */
+/* The nvBowtie steps it replaces, as one call: seed matching (nvBowtie/bowtie2/cuda/          */
+/* mapping_inl.h:73-86), SA-row selection and locate (locate_inl.h:115-200), banded window     */
+/* scoring (score_inl.h:85-130,482-583), best/second-best reduction (reduce_inl.h) and the     */
+/* banded traceback of the best hit (traceback_inl.h:224-277). Seed priorities, re-seeding,    */
+/* effort limits, MAPQ and mate pairing of nvBowtie are NOT part of it.                         */
+/* ----------------------------------------------------------------------------------------- */
+typedef struct {
+    uint32_t    seed_len;       /* symbols per seed                              (params.h:131 seed_len)  */
+    uint32_t    seed_interval;  /* a seed every seed_interval symbols, both strands                        */
+    uint32_t    max_hits;       /* SA rows located per seed: the first max_hits rows of its range          */
+    uint32_t    max_range;      /* seeds whose SA range is wider are skipped; 0 = no limit                 */
+    uint32_t    band;           /* band of the extension; window = [g - band/2, g - band/2 + band + len)   */
+    uint32_t    both_strands;   /* 0 = forward read only, 1 = also its reverse complement                  */
+    int32_t     min_score;      /* reads whose best window scores less stay unaligned                      */
+    nvb_aligner aligner;        /* type must be NVB_SEMI_GLOBAL                                            */
+} nvb_map_params;
+
+/* flags: bit 0 = reverse-complement strand, bit 1 = aligned. begin/end = genome coordinates of the first
+ * aligned symbol / one past the last. Unaligned: score = second_score = INT32_MIN, begin = end = 0xFFFFFFFF. */
+typedef struct { int32_t score, second_score; uint32_t begin, end, flags, n_ops; } nvb_read_hit;
+typedef struct { uint64_t seeds, seed_hits, candidates, aligned; } nvb_map_stats;
+
+/* 8-bit symbols (0..3) -> 2-bit big-endian words, 16 per uint32 (the layout of the reference's packed genome,
+ * nvbio/io/sequence: PackedStream<uint32,uint8,2,true>); words_d holds (n + 15) / 16 words */
+int nvb_pack_2bit(nvb_ctx* ctx, const uint8_t* symbols_d, uint32_t n, uint32_t* words_d, void* stream);
+
+/* reads: 8-bit device string set; genome_words_d: the indexed text, 2-bit packed (nvb_pack_2bit);
+ * hits_d[reads.count]; ops_d (may be NULL): ops_stride bytes per read (a multiple of 16, >= 2 * max_read_len + band),
+ * push order like nvb_batch_banded_traceback; stats_h (may be NULL). Scratch is owned by the context (grow-only);
+ * the call synchronises the stream a few times per batch of reads_per_batch reads (0 = default 2^20). */
+int nvb_map_reads(nvb_ctx* ctx, const nvb_fmindex* fmi_d, const uint32_t* genome_words_d, nvb_string_set reads,
+                  uint32_t max_read_len, const nvb_map_params* params, uint32_t reads_per_batch,
+                  nvb_read_hit* hits_d, uint8_t* ops_d, uint32_t ops_stride, nvb_map_stats* stats_h, void* stream);
+/* host buffers in / out (H2D of the reads, the pipeline, D2H of hits and ops; synchronous) */
+int nvb_map_reads_host(nvb_ctx* ctx, const nvb_fmindex* fmi_d, const uint32_t* genome_words_d,
+                       const uint8_t* reads_h, const uint32_t* read_off_h, uint32_t n_reads,
+                       const nvb_map_params* params, uint32_t reads_per_batch,
+                       nvb_read_hit* hits_h, uint8_t* ops_h, uint32_t ops_stride, nvb_map_stats* stats_h);
+
 #if defined(__GNUC__)
 #pragma GCC visibility pop
 #endif

@@ -17,3 +17,4 @@ from .alignment import (  # noqa: F401
     batch_alignment_traceback, batch_banded_alignment_traceback,
     batch_score_host, batch_traceback_host, ops_to_cigar, SINK_DT, ALN_DT,
 )
+from .pipeline import MapParams, map_reads, map_reads_host, pack_genome, ops_stride_for, HIT_DT, FLAG_REVERSE, FLAG_ALIGNED  # noqa: F401

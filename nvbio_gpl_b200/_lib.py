@@ -29,6 +29,15 @@ class AlignerC(C.Structure):
                 ("gap_a", C.c_int32), ("gap_b", C.c_int32)]
 
 
+class MapParamsC(C.Structure):
+    _fields_ = [("seed_len", C.c_uint32), ("seed_interval", C.c_uint32), ("max_hits", C.c_uint32), ("max_range", C.c_uint32),
+                ("band", C.c_uint32), ("both_strands", C.c_uint32), ("min_score", C.c_int32), ("aligner", AlignerC)]
+
+
+class MapStatsC(C.Structure):
+    _fields_ = [("seeds", C.c_uint64), ("seed_hits", C.c_uint64), ("candidates", C.c_uint64), ("aligned", C.c_uint64)]
+
+
 def build(verbose=False):
     """compile libnvbio_b200.so for sm_100a (nvcc cross-compiles without a GPU)"""
     cmd = ["make", "-C", os.path.join(HERE, "csrc"), "-j8"]
@@ -82,6 +91,11 @@ _PROTOS = {
     "nvb_ops_to_cigar": (_i, [_vp, _vp, _u32, _vp, _u32, _vp, _u32, _vp, _vp]),
     "nvb_batch_score_host": (_i, [_vp, AlignerC, _u32, _vp, _vp, _vp, _vp, _u32, _vp]),
     "nvb_batch_traceback_host": (_i, [_vp, AlignerC, _u32, _u32, _vp, _vp, _vp, _vp, _u32, _vp, _vp, _u32, _vp]),
+    "nvb_pack_2bit": (_i, [_vp, _vp, _u32, _vp, _vp]),
+    "nvb_map_reads": (_i, [_vp, C.POINTER(FMIndexC), _vp, StringSetC, _u32, C.POINTER(MapParamsC), _u32, _vp, _vp, _u32,
+                           C.POINTER(MapStatsC), _vp]),
+    "nvb_map_reads_host": (_i, [_vp, C.POINTER(FMIndexC), _vp, _vp, _vp, _u32, C.POINTER(MapParamsC), _u32, _vp, _vp, _u32,
+                                C.POINTER(MapStatsC)]),
     "nvb_last_paths": (_u32, [_vp]),
     "nvb_force_generic": (None, [_vp, _i]),
 }

@@ -47,7 +47,7 @@ extern "C" void nvb_ctx_destroy(nvb_ctx* c)
     if (!c) return;
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
-    for (int i = 0; i < 8; ++i) if (c->d_stage[i]) cudaFree(c->d_stage[i]);
+    for (int i = 0; i < NVB_STAGE_SLOTS; ++i) if (c->d_stage[i]) cudaFree(c->d_stage[i]);
     if (c->d_worklist) cudaFree(c->d_worklist);
     for (int i = 0; i < 2; ++i) if (c->aux[i]) { cudaStreamSynchronize(c->aux[i]); cudaStreamDestroy(c->aux[i]); }
     cudaStreamDestroy(c->stream);

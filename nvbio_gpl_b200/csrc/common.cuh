@@ -10,6 +10,7 @@
 #endif
 
 #define NVB_SM_COUNT 148
+#define NVB_STAGE_SLOTS 32
 
 struct nvb_ctx
 {
@@ -20,8 +21,8 @@ struct nvb_ctx
     uint32_t     last_paths;
     int          force_generic;
     // grow-only device/pinned staging owned by the *_host entry points
-    void*        d_stage[8];
-    size_t       d_stage_bytes[8];
+    void*        d_stage[NVB_STAGE_SLOTS];      // 0..7: *_host entry points, 8..: the seed-and-extend pipeline
+    size_t       d_stage_bytes[NVB_STAGE_SLOTS];
     // dirty-pair worklist of the packed DP kernels: [0] = count, [1..] = pair ids
     uint32_t*    d_worklist;
     size_t       d_worklist_cap;

@@ -107,30 +107,6 @@ fm_rank4_kernel(const FMView f, const uint32_t* __restrict__ k, uint32_t n, uint
     *(uint4*)(out + 4 * (size_t)tid) = r;
 }
 
-// LF-walk from SA row j to the nearest sampled row (j % 16 == 0). One block load per step: the
-// BWT symbol and its rank come from the same 32-byte block.
-__device__ __forceinline__ uint2 fm_locate_walk_one(const FMView& f, uint32_t j, const uint2* lut)
-{
-    uint32_t t = 0;
-    while (j & 15u)
-    {
-        if (j != f.primary)
-        {
-            const uint32_t jj = j < f.primary ? j : j - 1u;        // fmindex_inl.h:384
-            const FMBlock b = fm_load_block(f.blk, jj >> 6);
-            const uint32_t c = fm_bwt_symbol(b, jj & 63u);
-            // rank(fmi, j, c) with the FM special cases (fmindex_inl.h:31-47)
-            uint32_t r;
-            if (j == f.length) r = f.L2[c + 1] - f.L2[c];
-            else r = fm_block_rank(b, jj & 63u, c, lut);
-            j = f.L2[c] + r;
-        }
-        else j = 0;
-        ++t;
-    }
-    return make_uint2(j, t);
-}
-
 __global__ void __launch_bounds__(FM_THREADS)
 fm_locate_kernel(const FMView f, const uint32_t* __restrict__ rows, uint32_t n, uint32_t* __restrict__ pos)
 {

@@ -1,0 +1,438 @@
+// map_pipeline.cu -- seed -> locate -> extend -> reduce -> traceback over a batch of reads.
+//
+// The glue between the two halves of the hot path, as nvBowtie's driver arranges them:
+//   map_seed_kernel     exact backward search of every seed of every read, both strands
+//                       (nvBowtie/bowtie2/cuda/mapping_inl.h:73-86 -> match(fmi, seed, len), fmindex_inl.h:186-239)
+//   map_locate_kernel   one thread per selected SA row: locate (fmindex_inl.h:290-304), diagonal of the hit
+//                       g_pos = pos - pos_in_read (locate_inl.h:130-136), window begin g_pos - band/2 (score_inl.h:103-104)
+//   sort + unique       candidates = distinct (read, strand, window begin)
+//   map_extract_kernel  strand read and 2-bit genome window -> 8-bit string sets for the banded DP kernels
+//   nvb_batch_banded_score / nvb_batch_banded_traceback   the extension itself (dp_api.cu)
+//   map_reduce_kernel   best / second best window per read (reduce_inl.h), first maximum in (strand, begin) order
+//   map_finish_kernel   genome coordinates + op list of the best window
+// Everything a read needs stays on the device; the host only learns three counters per batch (seed hits,
+// candidates, aligned reads) to size the next launch.
+#include "fm_device.cuh"
+#include "dp_fast.h"
+#include <cub/device/device_scan.cuh>
+#include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_select.cuh>
+#include <thrust/iterator/counting_iterator.h>
+
+#define MAP_THREADS 256
+#define MAP_NONE    0xFFFFFFFFu
+#define MAP_INVALID (-(1 << 30))
+
+enum { S_SEED = 8, S_COUNT, S_SCAN, S_KEYS_A, S_KEYS_B, S_CUB, S_NUM, S_POFF, S_TOFF, S_PSYM, S_TSYM, S_SINKS,
+       S_BEST, S_SECOND, S_ALIST, S_ALN, S_TBOPS, S_TBNOPS, S_TBTEMP, S_HREADS, S_HOFF, S_HHITS, S_HOPS };
+
+struct MapGeom
+{
+    uint32_t r0, n_reads;            // the batch: reads [r0, r0 + n_reads)
+    uint32_t S, n_strands;           // seed slots per strand (for the longest read), strands
+    uint32_t seed_len, interval, max_hits, max_range, band;
+};
+
+__device__ __forceinline__ uint32_t map_strand_symbol(const uint8_t* read, uint32_t L, uint32_t strand, uint32_t i)
+{
+    if (!strand) return read[i];
+    const uint32_t c = read[L - 1u - i];
+    return c < 4u ? 3u - c : c;
+}
+
+__global__ void __launch_bounds__(MAP_THREADS)
+map_seed_kernel(const FMView f, const StrSet reads, const MapGeom g, uint2* __restrict__ seeds, uint32_t* __restrict__ counts)
+{
+    __shared__ uint2 s_lut[FM_LUT_ENTRIES];
+    fm_lut_init(s_lut);
+    const uint32_t per_read = g.S * g.n_strands;
+    const uint32_t t = blockIdx.x * MAP_THREADS + threadIdx.x;
+    if (t >= g.n_reads * per_read) return;
+    const uint32_t r = t / per_read, rem = t - r * per_read, strand = rem / g.S, k = rem - strand * g.S;
+    const uint32_t beg = reads.off[g.r0 + r], L = reads.off[g.r0 + r + 1] - beg;
+    const uint8_t* read = reads.sym + beg;
+    const uint32_t o = k * g.interval;
+    uint32_t x = 1, y = 0, cnt = 0;
+    if (o + g.seed_len <= L)
+    {
+        x = 0; y = f.length;
+        for (int32_t i = (int32_t)g.seed_len - 1; i >= 0 && x <= y; --i)
+        {
+            const uint32_t c = map_strand_symbol(read, L, strand, o + (uint32_t)i);
+            if (c > 3u) { x = 1; y = 0; break; }
+            const uint2 rk = fm_rank2(f, x - 1u, y, c, s_lut);
+            x = f.L2[c] + rk.x + 1u;
+            y = f.L2[c] + rk.y;
+        }
+        if (x <= y)
+        {
+            const uint32_t size = y - x + 1u;
+            if (!(g.max_range && size > g.max_range)) cnt = size < g.max_hits ? size : g.max_hits;
+        }
+    }
+    seeds[t] = make_uint2(x, cnt);
+    counts[t] = cnt;
+}
+
+__global__ void __launch_bounds__(MAP_THREADS)
+map_locate_kernel(const FMView f, const MapGeom g, const uint2* __restrict__ seeds, const uint32_t* __restrict__ scan,
+                  uint32_t n_slots, uint32_t n_hits, uint64_t* __restrict__ keys)
+{
+    __shared__ uint2 s_lut[FM_LUT_ENTRIES];
+    fm_lut_init(s_lut);
+    const uint32_t h = blockIdx.x * MAP_THREADS + threadIdx.x;
+    if (h >= n_hits) return;
+    uint32_t lo = 0, hi = n_slots - 1u;                     // last slot whose first hit is <= h
+    while (lo < hi) { const uint32_t mid = (lo + hi + 1u) >> 1; if (__ldg(scan + mid) <= h) lo = mid; else hi = mid - 1u; }
+    const uint32_t per_read = g.S * g.n_strands;
+    const uint32_t r = lo / per_read, rem = lo - r * per_read, strand = rem / g.S, k = rem - strand * g.S;
+    const uint32_t row = seeds[lo].x + (h - __ldg(scan + lo));
+    const uint2 w = fm_locate_walk_one(f, row, s_lut);
+    const uint32_t pos = __ldg(f.ssa + (w.x >> 4)) + w.y;
+    const uint32_t o = k * g.interval;
+    const uint32_t g_pos = pos > o ? pos - o : 0u;
+    const uint32_t gb = g_pos > g.band / 2u ? g_pos - g.band / 2u : 0u;
+    keys[h] = ((uint64_t)(r * 2u + strand) << 32) | gb;
+}
+
+// candidate j of a launch: a plain index into the sorted keys, or the best candidate of an aligned read
+__device__ __forceinline__ uint64_t map_key(const uint64_t* keys, const uint32_t* alist, const uint32_t* best, uint32_t j)
+{
+    return keys[alist ? best[alist[j]] : j];
+}
+
+__global__ void __launch_bounds__(MAP_THREADS)
+map_lengths_kernel(const uint64_t* __restrict__ keys, const uint32_t* __restrict__ alist, const uint32_t* __restrict__ best,
+                   uint32_t c0, uint32_t cnt, const StrSet reads, uint32_t r0, uint32_t band, uint32_t G,
+                   uint32_t* __restrict__ plen, uint32_t* __restrict__ tlen)
+{
+    const uint32_t j = blockIdx.x * MAP_THREADS + threadIdx.x;
+    if (j > cnt) return;
+    if (j == cnt) { plen[j] = 0; tlen[j] = 0; return; }
+    const uint64_t key = map_key(keys, alist, best, c0 + j);
+    const uint32_t r = (uint32_t)(key >> 33), gb = (uint32_t)key;
+    const uint32_t L = reads.off[r0 + r + 1] - reads.off[r0 + r];
+    const uint64_t ge = (uint64_t)gb + band + L;
+    plen[j] = L;
+    tlen[j] = (uint32_t)(ge < G ? ge : G) - gb;             // score_inl.h:105-106
+}
+
+// one warp per candidate
+__global__ void __launch_bounds__(MAP_THREADS)
+map_extract_kernel(const uint64_t* __restrict__ keys, const uint32_t* __restrict__ alist, const uint32_t* __restrict__ best,
+                   uint32_t c0, uint32_t cnt, const StrSet reads, uint32_t r0, const uint32_t* __restrict__ genome,
+                   const uint32_t* __restrict__ poff, const uint32_t* __restrict__ toff,
+                   uint8_t* __restrict__ psym, uint8_t* __restrict__ tsym)
+{
+    const uint32_t w = (blockIdx.x * MAP_THREADS + threadIdx.x) >> 5, lane = threadIdx.x & 31u;
+    if (w >= cnt) return;
+    const uint64_t key = map_key(keys, alist, best, c0 + w);
+    const uint32_t r = (uint32_t)(key >> 33), strand = (uint32_t)(key >> 32) & 1u, gb = (uint32_t)key;
+    const uint32_t p0 = poff[w], L = poff[w + 1] - p0, t0 = toff[w], N = toff[w + 1] - t0;
+    const uint8_t* read = reads.sym + reads.off[r0 + r];
+    for (uint32_t i = lane; i < L; i += 32u) psym[p0 + i] = (uint8_t)map_strand_symbol(read, L, strand, i);
+    for (uint32_t i = lane; i < N; i += 32u)
+    {
+        const uint32_t p = gb + i;
+        tsym[t0 + i] = (uint8_t)((__ldg(genome + (p >> 4)) >> (30u - 2u * (p & 15u))) & 3u);
+    }
+}
+
+__global__ void __launch_bounds__(MAP_THREADS)
+map_reduce_kernel(const uint64_t* __restrict__ keys, uint32_t n_cand, const nvb_best_sink* __restrict__ sinks, uint32_t n_reads,
+                  int32_t min_score, uint32_t* __restrict__ best, int32_t* __restrict__ second, nvb_read_hit* __restrict__ hits)
+{
+    const uint32_t r = blockIdx.x * MAP_THREADS + threadIdx.x;
+    if (r >= n_reads) return;
+    uint32_t range[2];
+    #pragma unroll
+    for (int e = 0; e < 2; ++e)
+    {
+        const uint64_t v = (uint64_t)(2u * r + 2u * e) << 32;   // lower_bound
+        uint32_t lo = 0, hi = n_cand;
+        while (lo < hi) { const uint32_t mid = lo + ((hi - lo) >> 1); if (keys[mid] < v) lo = mid + 1u; else hi = mid; }
+        range[e] = lo;
+    }
+    int32_t b = INT32_MIN, s2 = INT32_MIN; uint32_t bi = MAP_NONE;
+    for (uint32_t i = range[0]; i < range[1]; ++i)
+    {
+        const int32_t sc = sinks[i].score;
+        if (sc <= MAP_INVALID) continue;
+        if (sc > b) { if (b != INT32_MIN && b > s2) s2 = b; b = sc; bi = i; }
+        else if (sc > s2) s2 = sc;
+    }
+    if (bi != MAP_NONE && b < min_score) bi = MAP_NONE;
+    best[r] = bi; second[r] = s2;
+    nvb_read_hit h; h.score = h.second_score = INT32_MIN; h.begin = h.end = 0xFFFFFFFFu; h.flags = 0; h.n_ops = 0;
+    hits[r] = h;
+}
+
+struct MapAligned
+{
+    const uint32_t* best;
+    __host__ __device__ bool operator()(uint32_t r) const { return best[r] != MAP_NONE; }
+};
+
+// one warp per aligned read
+__global__ void __launch_bounds__(MAP_THREADS)
+map_finish_kernel(const uint64_t* __restrict__ keys, const uint32_t* __restrict__ alist, const uint32_t* __restrict__ best,
+                  const int32_t* __restrict__ second, uint32_t c0, uint32_t cnt, const nvb_alignment* __restrict__ aln,
+                  const uint8_t* __restrict__ tb_ops, uint32_t tb_stride, const uint32_t* __restrict__ tb_n_ops,
+                  nvb_read_hit* __restrict__ hits, uint8_t* __restrict__ ops, uint32_t ops_stride)
+{
+    const uint32_t w = (blockIdx.x * MAP_THREADS + threadIdx.x) >> 5, lane = threadIdx.x & 31u;
+    if (w >= cnt) return;
+    const uint32_t r = alist[c0 + w];
+    const uint64_t key = keys[best[r]];
+    const uint32_t gb = (uint32_t)key;
+    const uint32_t n = tb_n_ops[w];
+    if (lane == 0)
+    {
+        const nvb_alignment a = aln[w];
+        nvb_read_hit h;
+        h.score = a.score; h.second_score = second[r];
+        h.begin = gb + a.source_x; h.end = gb + a.sink_x;
+        h.flags = 2u | ((uint32_t)(key >> 32) & 1u); h.n_ops = n;
+        hits[r] = h;
+    }
+    if (ops)
+    {
+        const uint32_t bytes = n < ops_stride ? n : ops_stride;
+        const uint4* src = (const uint4*)(tb_ops + (size_t)w * tb_stride);
+        uint4* dst = (uint4*)(ops + (size_t)r * ops_stride);
+        for (uint32_t i = lane; i * 16u < bytes; i += 32u) dst[i] = src[i];
+    }
+}
+
+__global__ void __launch_bounds__(MAP_THREADS)
+pack_2bit_kernel(const uint8_t* __restrict__ sym, uint32_t n, uint32_t n_words, uint32_t* __restrict__ words)
+{
+    const uint32_t w = blockIdx.x * MAP_THREADS + threadIdx.x;
+    if (w >= n_words) return;
+    uint32_t v = 0;
+    const uint32_t base = w * 16u;
+    if (base + 16u <= n && (((uintptr_t)sym) & 15u) == 0)
+    {
+        const uint4 q = *(const uint4*)(sym + base);
+        const uint32_t qs[4] = { q.x, q.y, q.z, q.w };
+        #pragma unroll
+        for (int k = 0; k < 4; ++k)
+            #pragma unroll
+            for (int b = 0; b < 4; ++b) v |= ((qs[k] >> (8 * b)) & 3u) << (30 - 2 * (4 * k + b));
+    }
+    else
+        for (uint32_t i = 0; i < 16u && base + i < n; ++i) v |= (uint32_t)(sym[base + i] & 3u) << (30u - 2u * i);
+    words[w] = v;
+}
+
+extern "C" int nvb_pack_2bit(nvb_ctx* ctx, const uint8_t* symbols_d, uint32_t n, uint32_t* words_d, void* stream)
+{
+    if (!ctx) return NVB_ERR_ARG;
+    if (n == 0) return NVB_OK;
+    if (!symbols_d || !words_d) return NVB_ERR_ARG;
+    const uint32_t n_words = (uint32_t)(((uint64_t)n + 15u) / 16u);
+    pack_2bit_kernel<<<(n_words + MAP_THREADS - 1) / MAP_THREADS, MAP_THREADS, 0, (cudaStream_t)stream>>>(symbols_d, n, n_words, words_d);
+    NVB_LAUNCHED(ctx);
+    return NVB_OK;
+}
+
+static inline uint32_t map_grid(uint64_t threads) { return (uint32_t)((threads + MAP_THREADS - 1) / MAP_THREADS); }
+static inline uint32_t bits_for(uint64_t v) { uint32_t b = 0; while (b < 64 && (v >> b)) ++b; return b; }
+
+#define MAP_STAGE(slot, bytes, ptr) do { void* p_ = nullptr; if ((rc = nvb_stage(ctx, slot, (bytes), &p_))) return rc; ptr = (decltype(ptr))p_; } while (0)
+
+// string sets of `cnt` candidates starting at c0 (or of the best candidates of aligned reads alist[c0..]) into the slots
+static int map_build_sets(nvb_ctx* ctx, const uint64_t* keys, const uint32_t* alist, const uint32_t* best, uint32_t c0, uint32_t cnt,
+                          const StrSet& reads, uint32_t r0, const uint32_t* genome, uint32_t band, uint32_t G,
+                          uint32_t maxL, nvb_string_set* P, nvb_string_set* T, cudaStream_t s)
+{
+    int rc;
+    uint32_t *poff, *toff; uint8_t *psym, *tsym; void* tmp;
+    MAP_STAGE(S_POFF, sizeof(uint32_t) * ((size_t)cnt + 1), poff);
+    MAP_STAGE(S_TOFF, sizeof(uint32_t) * ((size_t)cnt + 1), toff);
+    MAP_STAGE(S_PSYM, (size_t)cnt * maxL + 128, psym);
+    MAP_STAGE(S_TSYM, (size_t)cnt * ((size_t)maxL + band) + 128, tsym);
+    psym += 64; tsym += 64;        // the banded kernels read whole 16-byte blocks around a string
+    map_lengths_kernel<<<map_grid((uint64_t)cnt + 1), MAP_THREADS, 0, s>>>(keys, alist, best, c0, cnt, reads, r0, band, G, poff, toff);
+    NVB_LAUNCHED(ctx);
+    size_t tmp_bytes = 0;
+    cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, poff, poff, (int)(cnt + 1), s);
+    MAP_STAGE(S_CUB, tmp_bytes, tmp);
+    NVB_CUDA(ctx, cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, poff, poff, (int)(cnt + 1), s));
+    NVB_CUDA(ctx, cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, toff, toff, (int)(cnt + 1), s));
+    ctx->launches += 2;
+    map_extract_kernel<<<map_grid((uint64_t)cnt * 32u), MAP_THREADS, 0, s>>>(keys, alist, best, c0, cnt, reads, r0, genome, poff, toff, psym, tsym);
+    NVB_LAUNCHED(ctx);
+    P->symbols = psym; P->offsets = poff; P->count = cnt; P->bits = 8;
+    T->symbols = tsym; T->offsets = toff; T->count = cnt; T->bits = 8;
+    return NVB_OK;
+}
+
+extern "C" int nvb_map_reads(nvb_ctx* ctx, const nvb_fmindex* fmi, const uint32_t* genome, nvb_string_set reads_set,
+                             uint32_t maxL, const nvb_map_params* mp, uint32_t reads_per_batch,
+                             nvb_read_hit* hits, uint8_t* ops, uint32_t ops_stride, nvb_map_stats* stats, void* stream)
+{
+    if (!ctx || !fmi || !mp) return NVB_ERR_ARG;
+    if (stats) { stats->seeds = stats->seed_hits = stats->candidates = stats->aligned = 0; }
+    const uint32_t n_total = reads_set.count;
+    if (n_total == 0) return NVB_OK;
+    if (!genome || !reads_set.symbols || !reads_set.offsets || !hits || !fmi->bwt_occ || !fmi->ssa) return NVB_ERR_ARG;
+    if (reads_set.bits != 8 || fmi->occ_int != 64 || fmi->sa_int != 16) return NVB_ERR_UNSUPPORTED;
+    if (mp->aligner.type != NVB_SEMI_GLOBAL || mp->seed_len == 0 || mp->seed_interval == 0 || mp->max_hits == 0) return NVB_ERR_UNSUPPORTED;
+    if (mp->band < 2 || mp->band > NVB_MAX_BAND_LEN || maxL == 0) return NVB_ERR_UNSUPPORTED;
+    const uint32_t tb_stride = ops ? ops_stride : ((2u * maxL + mp->band + 16u + 15u) & ~15u);
+    if ((tb_stride & 15u) || tb_stride < 2u * maxL + mp->band || (ops && (((uintptr_t)ops) & 15u))) return NVB_ERR_ARG;
+    cudaStream_t s = (cudaStream_t)stream;
+    const FMView f = make_view(fmi);
+    const StrSet reads = make_set(reads_set);
+    const uint32_t G = fmi->length;
+    int rc;
+
+    MapGeom g;
+    g.n_strands = mp->both_strands ? 2u : 1u;
+    g.S = maxL >= mp->seed_len ? (maxL - mp->seed_len) / mp->seed_interval + 1u : 0u;
+    g.seed_len = mp->seed_len; g.interval = mp->seed_interval; g.max_hits = mp->max_hits; g.max_range = mp->max_range; g.band = mp->band;
+    const uint32_t per_read = g.S * g.n_strands;
+    // batch: bounded so that seed slots and worst-case hits stay below 2^31
+    uint64_t rb = reads_per_batch ? reads_per_batch : (1u << 20);
+    if (per_read) { const uint64_t cap = 0x7FFFFFFFull / ((uint64_t)per_read * mp->max_hits); if (rb > cap) rb = cap; }
+    if (rb == 0) return NVB_ERR_UNSUPPORTED;
+    const uint32_t cand_chunk = 4u << 20, tb_chunk = 2u << 20;
+
+    uint32_t* d_num; MAP_STAGE(S_NUM, 64, d_num);
+    for (uint32_t r0 = 0; r0 < n_total; r0 += (uint32_t)rb)
+    {
+        const uint32_t nr = (uint32_t)(n_total - r0 < rb ? n_total - r0 : rb);
+        g.r0 = r0; g.n_reads = nr;
+        nvb_read_hit* bhits = hits + r0;
+        uint32_t* best; int32_t* second;
+        MAP_STAGE(S_BEST, sizeof(uint32_t) * (size_t)nr, best);
+        MAP_STAGE(S_SECOND, sizeof(int32_t) * (size_t)nr, second);
+        const uint32_t n_slots = nr * per_read;
+        uint32_t n_hits = 0, n_cand = 0, n_aligned = 0;
+        uint64_t *keys_a = nullptr, *keys_b = nullptr;
+        void* tmp; size_t tmp_bytes;
+        if (n_slots)
+        {
+            // ---- seeding
+            uint2* seeds; uint32_t *counts, *scan;
+            MAP_STAGE(S_SEED, sizeof(uint2) * (size_t)n_slots, seeds);
+            MAP_STAGE(S_COUNT, sizeof(uint32_t) * ((size_t)n_slots + 1), counts);
+            MAP_STAGE(S_SCAN, sizeof(uint32_t) * ((size_t)n_slots + 1), scan);
+            NVB_CUDA(ctx, cudaMemsetAsync(counts + n_slots, 0, sizeof(uint32_t), s));
+            map_seed_kernel<<<map_grid(n_slots), MAP_THREADS, 0, s>>>(f, reads, g, seeds, counts);
+            NVB_LAUNCHED(ctx);
+            tmp_bytes = 0;
+            cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, counts, scan, (int)(n_slots + 1), s);
+            MAP_STAGE(S_CUB, tmp_bytes, tmp);
+            NVB_CUDA(ctx, cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, counts, scan, (int)(n_slots + 1), s));
+            ctx->launches++;
+            NVB_CUDA(ctx, cudaMemcpyAsync(&n_hits, scan + n_slots, sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+            NVB_CUDA(ctx, cudaStreamSynchronize(s));
+            if (n_hits)
+            {
+                // ---- locate + candidate keys, sorted and de-duplicated
+                MAP_STAGE(S_KEYS_A, sizeof(uint64_t) * (size_t)n_hits, keys_a);
+                MAP_STAGE(S_KEYS_B, sizeof(uint64_t) * (size_t)n_hits, keys_b);
+                map_locate_kernel<<<map_grid(n_hits), MAP_THREADS, 0, s>>>(f, g, seeds, scan, n_slots, n_hits, keys_a);
+                NVB_LAUNCHED(ctx);
+                const int end_bit = (int)(32u + bits_for(2ull * nr));
+                size_t sort_bytes = 0, uniq_bytes = 0;
+                cub::DeviceRadixSort::SortKeys(nullptr, sort_bytes, keys_a, keys_b, (int)n_hits, 0, end_bit, s);
+                cub::DeviceSelect::Unique(nullptr, uniq_bytes, keys_b, keys_a, d_num, (int)n_hits, s);
+                tmp_bytes = sort_bytes > uniq_bytes ? sort_bytes : uniq_bytes;
+                MAP_STAGE(S_CUB, tmp_bytes, tmp);
+                NVB_CUDA(ctx, cub::DeviceRadixSort::SortKeys(tmp, sort_bytes, keys_a, keys_b, (int)n_hits, 0, end_bit, s));
+                NVB_CUDA(ctx, cub::DeviceSelect::Unique(tmp, uniq_bytes, keys_b, keys_a, d_num, (int)n_hits, s));
+                ctx->launches += 2;
+                NVB_CUDA(ctx, cudaMemcpyAsync(&n_cand, d_num, sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+                NVB_CUDA(ctx, cudaStreamSynchronize(s));
+            }
+        }
+        const uint64_t* keys = keys_a;
+        // ---- extension: banded scoring of every candidate
+        nvb_best_sink* sinks = nullptr;
+        if (n_cand)
+        {
+            MAP_STAGE(S_SINKS, sizeof(nvb_best_sink) * (size_t)n_cand, sinks);
+            for (uint32_t c0 = 0; c0 < n_cand; c0 += cand_chunk)
+            {
+                const uint32_t cnt = n_cand - c0 < cand_chunk ? n_cand - c0 : cand_chunk;
+                nvb_string_set P, T;
+                if ((rc = map_build_sets(ctx, keys, nullptr, nullptr, c0, cnt, reads, r0, genome, mp->band, G, maxL, &P, &T, s))) return rc;
+                if ((rc = nvb_batch_banded_score(ctx, mp->aligner, mp->band, P, T, sinks + c0, maxL, maxL + mp->band, nullptr, 0, s))) return rc;
+            }
+        }
+        // ---- best / second best per read, list of aligned reads
+        map_reduce_kernel<<<map_grid(nr), MAP_THREADS, 0, s>>>(keys, n_cand, sinks, nr, mp->min_score, best, second, bhits);
+        NVB_LAUNCHED(ctx);
+        if (n_cand)
+        {
+            uint32_t* alist;
+            MAP_STAGE(S_ALIST, sizeof(uint32_t) * (size_t)nr, alist);
+            MapAligned pred; pred.best = best;
+            thrust::counting_iterator<uint32_t> iota(0u);
+            tmp_bytes = 0;
+            cub::DeviceSelect::If(nullptr, tmp_bytes, iota, alist, d_num, (int)nr, pred, s);
+            MAP_STAGE(S_CUB, tmp_bytes, tmp);
+            NVB_CUDA(ctx, cub::DeviceSelect::If(tmp, tmp_bytes, iota, alist, d_num, (int)nr, pred, s));
+            ctx->launches++;
+            NVB_CUDA(ctx, cudaMemcpyAsync(&n_aligned, d_num, sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+            NVB_CUDA(ctx, cudaStreamSynchronize(s));
+            // ---- traceback of the best window of every aligned read
+            for (uint32_t c0 = 0; c0 < n_aligned; c0 += tb_chunk)
+            {
+                const uint32_t cnt = n_aligned - c0 < tb_chunk ? n_aligned - c0 : tb_chunk;
+                nvb_string_set P, T;
+                if ((rc = map_build_sets(ctx, keys, alist + c0, best, 0, cnt, reads, r0, genome, mp->band, G, maxL, &P, &T, s))) return rc;
+                nvb_alignment* aln; uint8_t* tb_ops; uint32_t* tb_n; void* tb_temp;
+                MAP_STAGE(S_ALN, sizeof(nvb_alignment) * (size_t)cnt, aln);
+                MAP_STAGE(S_TBOPS, (size_t)cnt * tb_stride + 16, tb_ops);
+                MAP_STAGE(S_TBNOPS, sizeof(uint32_t) * (size_t)cnt, tb_n);
+                size_t want = nvb_temp_bytes(NVB_OP_BANDED_TRACEBACK, mp->aligner, mp->band, 16, maxL, maxL + mp->band, cnt);
+                const size_t fast = (size_t)((cnt + 1u) / 2u) * 16u * maxL + 4096;   // flow words of the packed forward pass
+                if (want < fast) want = fast;
+                if (want > ((size_t)3 << 30)) want = (size_t)3 << 30;
+                MAP_STAGE(S_TBTEMP, want, tb_temp);
+                if ((rc = nvb_batch_banded_traceback(ctx, mp->aligner, mp->band, 16, P, T, aln, tb_ops, tb_stride, tb_n, maxL, maxL + mp->band,
+                                                     tb_temp, want, s))) return rc;
+                map_finish_kernel<<<map_grid((uint64_t)cnt * 32u), MAP_THREADS, 0, s>>>(keys, alist + c0, best, second, 0, cnt, aln, tb_ops, tb_stride, tb_n,
+                                                                                       bhits, ops ? ops + (size_t)r0 * ops_stride : nullptr, ops_stride);
+                NVB_LAUNCHED(ctx);
+            }
+        }
+        if (stats) { stats->seeds += n_slots; stats->seed_hits += n_hits; stats->candidates += n_cand; stats->aligned += n_aligned; }
+    }
+    return NVB_OK;
+}
+
+extern "C" int nvb_map_reads_host(nvb_ctx* ctx, const nvb_fmindex* fmi, const uint32_t* genome, const uint8_t* reads_h,
+                                  const uint32_t* off_h, uint32_t n, const nvb_map_params* mp, uint32_t reads_per_batch,
+                                  nvb_read_hit* hits_h, uint8_t* ops_h, uint32_t ops_stride, nvb_map_stats* stats)
+{
+    if (!ctx || !mp) return NVB_ERR_ARG;
+    if (stats) { stats->seeds = stats->seed_hits = stats->candidates = stats->aligned = 0; }
+    if (n == 0) return NVB_OK;
+    if (!reads_h || !off_h || !hits_h) return NVB_ERR_ARG;
+    NVB_CUDA(ctx, cudaSetDevice(ctx->device));
+    int rc;
+    uint32_t maxL = 0;
+    for (uint32_t i = 0; i < n; ++i) { const uint32_t l = off_h[i + 1] - off_h[i]; if (l > maxL) maxL = l; }
+    if (maxL == 0) return NVB_ERR_UNSUPPORTED;
+    const size_t b0 = off_h[0], nb = (size_t)off_h[n] - b0;
+    uint8_t *d_sym, *d_ops = nullptr; uint32_t* d_off; nvb_read_hit* d_hits;
+    MAP_STAGE(S_HREADS, nb + 64, d_sym);
+    MAP_STAGE(S_HOFF, sizeof(uint32_t) * ((size_t)n + 1), d_off);
+    MAP_STAGE(S_HHITS, sizeof(nvb_read_hit) * (size_t)n, d_hits);
+    if (ops_h) MAP_STAGE(S_HOPS, (size_t)n * ops_stride + 16, d_ops);
+    cudaStream_t s = ctx->stream;
+    if (ops_h) NVB_CUDA(ctx, cudaMemsetAsync(d_ops, 0, (size_t)n * ops_stride, s));
+    NVB_CUDA(ctx, cudaMemcpyAsync(d_sym, reads_h + b0, nb, cudaMemcpyHostToDevice, s));
+    NVB_CUDA(ctx, cudaMemcpyAsync(d_off, off_h, sizeof(uint32_t) * ((size_t)n + 1), cudaMemcpyHostToDevice, s));
+    nvb_string_set q; q.symbols = d_sym - b0; q.offsets = d_off; q.count = n; q.bits = 8;
+    if ((rc = nvb_map_reads(ctx, fmi, genome, q, maxL, mp, reads_per_batch, d_hits, d_ops, ops_stride, stats, s))) return rc;
+    NVB_CUDA(ctx, cudaMemcpyAsync(hits_h, d_hits, sizeof(nvb_read_hit) * (size_t)n, cudaMemcpyDeviceToHost, s));
+    if (ops_h) NVB_CUDA(ctx, cudaMemcpyAsync(ops_h, d_ops, (size_t)n * ops_stride, cudaMemcpyDeviceToHost, s));
+    NVB_CUDA(ctx, cudaStreamSynchronize(s));
+    return NVB_OK;
+}

@@ -1,0 +1,85 @@
+"""Host-side mirror of the seed -> locate -> extend -> reduce -> traceback call (``nvb_map_reads``).
+
+The steps are the ones nvBowtie's driver strings together (nvBowtie/bowtie2/cuda/mapping_inl.h:73-86 seed
+matching, locate_inl.h:115-200, score_inl.h:85-130 window placement and banded scoring, reduce_inl.h,
+traceback_inl.h:224-277), without its seed priorities, re-seeding, effort limits, MAPQ and mate pairing.
+All compute runs in libnvbio_b200.so; there is no CPU implementation here.
+"""
+import ctypes as C
+
+import numpy as np
+import torch
+
+from ._lib import lib, check, Context, MapParamsC, MapStatsC, StringSetC, current_stream_ptr
+from .alignment import Aligner, GotohAligner, SEMI_GLOBAL
+
+HIT_DT = np.dtype([("score", "<i4"), ("second_score", "<i4"), ("begin", "<u4"), ("end", "<u4"), ("flags", "<u4"), ("n_ops", "<u4")])
+FLAG_REVERSE, FLAG_ALIGNED = 1, 2
+
+
+class MapParams:
+    """seed_len / seed_interval / max_hits follow nvBowtie's ``ParamsPOD`` (params.h:124-163); the window is
+    ``[g - band/2, g - band/2 + band + read_len)`` (score_inl.h:103-106)"""
+
+    def __init__(self, aligner=None, seed_len=20, seed_interval=10, max_hits=4, max_range=0, band=15,
+                 both_strands=True, min_score=-(1 << 29)):
+        self.aligner = aligner if aligner is not None else GotohAligner(SEMI_GLOBAL, 0, -5, -8, -3)
+        assert isinstance(self.aligner, Aligner)
+        self.seed_len, self.seed_interval, self.max_hits, self.max_range = seed_len, seed_interval, max_hits, max_range
+        self.band, self.both_strands, self.min_score = band, both_strands, min_score
+
+    def c(self):
+        return MapParamsC(self.seed_len, self.seed_interval, self.max_hits, self.max_range, self.band,
+                          1 if self.both_strands else 0, self.min_score, self.aligner.c())
+
+
+def ops_stride_for(max_read_len, band):
+    return (2 * max_read_len + band + 16 + 15) // 16 * 16
+
+
+def pack_genome(symbols, ctx=None):
+    """uint8 device tensor of symbols 0..3 -> 2-bit big-endian words (int32 tensor, 16 symbols per word)"""
+    if not symbols.is_cuda:
+        raise RuntimeError("pack_genome needs a CUDA tensor; the hot path has no CPU fallback")
+    ctx = ctx or Context.default(symbols.device.index)
+    n = symbols.numel()
+    words = torch.empty((n + 15) // 16, dtype=torch.int32, device=symbols.device)
+    check(lib().nvb_pack_2bit(ctx.h, symbols.data_ptr(), n, words.data_ptr(), current_stream_ptr()), ctx.h)
+    return words
+
+
+def map_reads(fmi, genome_words, symbols, offsets, params, max_read_len=None, want_ops=True, reads_per_batch=0, ctx=None):
+    """device tensors in, device tensors out: (hits int32[n, 6] viewable as HIT_DT, ops uint8[n, stride] or None, stats dict)"""
+    if not symbols.is_cuda:
+        raise RuntimeError("map_reads needs CUDA tensors; the hot path has no CPU fallback")
+    dev = symbols.device
+    ctx = ctx or Context.default(dev.index)
+    n = offsets.numel() - 1
+    if max_read_len is None:
+        max_read_len = int((offsets[1:] - offsets[:-1]).max().item()) if n else 0
+    stride = ops_stride_for(max_read_len, params.band)
+    hits = torch.empty((n, 6), dtype=torch.int32, device=dev)
+    ops = torch.zeros((n, stride), dtype=torch.uint8, device=dev) if want_ops else None
+    stats = MapStatsC()
+    fc, pc = fmi.c(), params.c()
+    rs = StringSetC(symbols.data_ptr(), offsets.data_ptr(), n, 8)
+    check(lib().nvb_map_reads(ctx.h, C.byref(fc), genome_words.data_ptr(), rs, max_read_len, C.byref(pc), reads_per_batch,
+                              hits.data_ptr(), ops.data_ptr() if want_ops else None, stride, C.byref(stats),
+                              current_stream_ptr()), ctx.h)
+    return hits, ops, dict(seeds=stats.seeds, seed_hits=stats.seed_hits, candidates=stats.candidates, aligned=stats.aligned)
+
+
+def map_reads_host(fmi, genome_words, symbols_h, offsets_h, params, hits_h=None, ops_h=None, reads_per_batch=0, ctx=None):
+    """numpy (ideally pinned) buffers in and out through ``nvb_map_reads_host``: H2D, pipeline, D2H, synchronous"""
+    ctx = ctx or Context.default(genome_words.device.index)
+    n = len(offsets_h) - 1
+    L = int(np.max(np.diff(offsets_h.astype(np.int64)))) if n else 0
+    stride = ops_h.shape[1] if ops_h is not None else ops_stride_for(L, params.band)
+    if hits_h is None:
+        hits_h = np.zeros(n, dtype=HIT_DT)
+    stats = MapStatsC()
+    fc, pc = fmi.c(), params.c()
+    check(lib().nvb_map_reads_host(ctx.h, C.byref(fc), genome_words.data_ptr(), symbols_h.ctypes.data, offsets_h.ctypes.data, n,
+                                   C.byref(pc), reads_per_batch, hits_h.ctypes.data,
+                                   ops_h.ctypes.data if ops_h is not None else None, stride, C.byref(stats)), ctx.h)
+    return hits_h, ops_h, dict(seeds=stats.seeds, seed_hits=stats.seed_hits, candidates=stats.candidates, aligned=stats.aligned)

@@ -94,6 +94,15 @@ int ORC(banded_traceback)(orc_aligner a, uint32_t band, uint32_t checkpoints, co
                           uint32_t count, orc_alignment* out, uint8_t* ops, uint32_t ops_stride,
                           uint32_t* n_ops, int threads);
 
+/* seed-and-extend composition (oracle_map.c); flags: bit 0 = reverse-complement strand, bit 1 = aligned.
+ * begin/end = genome coordinates of the first aligned symbol / one past the last; ops in push order (end -> start). */
+typedef struct { uint32_t seed_len, seed_interval, max_hits, max_range, band, both_strands; int32_t min_score;
+                 orc_aligner aligner; } orc_map_params;
+typedef struct { int32_t score, second_score; uint32_t begin, end, flags, n_ops; } orc_read_hit;
+int ORC(map_reads)(const orc_fmindex* fmi, const uint8_t* genome, const uint8_t* reads, const uint32_t* read_off,
+                   uint32_t n_reads, const orc_map_params* p, orc_read_hit* hits, uint8_t* ops, uint32_t ops_stride,
+                   uint32_t* n_candidates, int threads);
+
 #ifdef __cplusplus
 }
 #endif

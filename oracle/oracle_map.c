@@ -1,0 +1,135 @@
+/*
+ * oracle_map.c -- TEST INFRASTRUCTURE ONLY (never linked into the product library).
+ *
+ * CPU composition of the seed-and-extend pipeline (SURVEY 8f row 4, 8d "C4/C5 inputs") out of the
+ * oracle's own entry points (oracle_abi.h): it is compiled twice, once over the plain-C restatement
+ * (prefix orc_) and once over the reference's own headers (prefix ref_, oracle/_ref), so the
+ * match / locate / banded score / banded traceback calls it makes are the pinned ones.
+ *
+ * The composition itself is OURS ("parity unpinned" for the glue): nvBowtie's driver
+ * (nvBowtie/bowtie2/cuda/mapping_inl.h, locate_inl.h, score_inl.h, reduce_inl.h, traceback_inl.h) adds
+ * seed-priority heuristics, re-seeding, effort limits and MAPQ that are out of scope.
+ * What is kept from it, with the reference lines each step follows:
+ *   - seeds: seed_len symbols every seed_interval symbols of the read and of its reverse complement,
+ *     exact backward search of each (mapping_inl.h:73-86 -> match(fmi, seed, len))
+ *   - hits: the first max_hits rows of every SA range (ranges wider than max_range are skipped),
+ *     located by locate(fmi, row); the hit's diagonal is g_pos = pos - pos_in_read
+ *     (locate_inl.h:130-136; clamped at 0 here where the reference lets the unsigned value wrap)
+ *   - extension window: genome_begin = g_pos > band/2 ? g_pos - band/2 : 0,
+ *     genome_end = min(genome_begin + band + read_len, genome_length)  (score_inl.h:103-106)
+ *   - banded SEMI_GLOBAL scoring of the (strand) read against the window (score_inl.h:482-583
+ *     -> batch_banded_alignment_score), candidates de-duplicated on (strand, genome_begin)
+ *   - best / second-best reduction per read (reduce_inl.h), best = first maximum in
+ *     (strand, genome_begin) order; reads whose best is below min_score stay unaligned
+ *   - banded traceback of the best with 16-row checkpoints (traceback_inl.h:224-277, defs.h:95)
+ */
+#include "oracle_abi.h"
+#include <stdlib.h>
+#include <string.h>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+
+#define MAP_INVALID (-(1 << 30))
+
+static int cmp_u64(const void* a, const void* b)
+{
+    const uint64_t x = *(const uint64_t*)a, y = *(const uint64_t*)b;
+    return x < y ? -1 : x > y ? 1 : 0;
+}
+
+int ORC(map_reads)(const orc_fmindex* fmi, const uint8_t* genome, const uint8_t* reads, const uint32_t* read_off,
+                   uint32_t n_reads, const orc_map_params* p, orc_read_hit* hits, uint8_t* ops, uint32_t ops_stride,
+                   uint32_t* n_candidates, int threads)
+{
+    if (!fmi || !genome || !read_off || !p || !hits) return -1;
+    if (p->seed_len == 0 || p->seed_interval == 0 || p->max_hits == 0 || p->band < 2) return -1;
+    const uint32_t G = fmi->length;
+    int failed = 0;
+    (void)threads;
+#ifdef _OPENMP
+    #pragma omp parallel num_threads(threads > 0 ? threads : omp_get_max_threads())
+#endif
+    {
+        uint8_t*  strand_read = NULL; size_t cap_read = 0;
+        uint64_t* keys = NULL;        size_t cap_keys = 0;
+        uint8_t*  tb_ops = NULL;      size_t cap_ops = 0;
+#ifdef _OPENMP
+        #pragma omp for schedule(dynamic, 64)
+#endif
+        for (uint32_t r = 0; r < n_reads; ++r)
+        {
+            const uint32_t L = read_off[r + 1] - read_off[r];
+            const uint8_t* fwd = reads + read_off[r];
+            orc_read_hit h; h.score = h.second_score = INT32_MIN; h.begin = h.end = 0xFFFFFFFFu; h.flags = 0; h.n_ops = 0;
+            if (n_candidates) n_candidates[r] = 0;
+            hits[r] = h;
+            if (L == 0) continue;
+            if (2 * (size_t)L > cap_read) { cap_read = 2 * (size_t)L; strand_read = (uint8_t*)realloc(strand_read, cap_read); }
+            memcpy(strand_read, fwd, L);
+            for (uint32_t i = 0; i < L; ++i) { const uint8_t c = fwd[L - 1 - i]; strand_read[L + i] = c < 4 ? (uint8_t)(3 - c) : c; }
+            const uint32_t n_strands = p->both_strands ? 2u : 1u;
+            const uint32_t n_seeds = L >= p->seed_len ? (L - p->seed_len) / p->seed_interval + 1 : 0;
+            const size_t need = (size_t)n_strands * n_seeds * p->max_hits;
+            if (need > cap_keys) { cap_keys = need; keys = (uint64_t*)realloc(keys, sizeof(uint64_t) * cap_keys); }
+            size_t nk = 0;
+            for (uint32_t s = 0; s < n_strands; ++s)
+                for (uint32_t k = 0; k < n_seeds; ++k)
+                {
+                    const uint32_t o = k * p->seed_interval;
+                    const uint32_t off[2] = { 0, p->seed_len };
+                    uint32_t range[2];
+                    if (ORC(fm_match)(fmi, strand_read + s * L + o, off, 1, range, NULL, 1)) { failed = 1; continue; }
+                    if (range[0] > range[1]) continue;
+                    const uint32_t size = range[1] - range[0] + 1;
+                    if (p->max_range && size > p->max_range) continue;
+                    const uint32_t cnt = size < p->max_hits ? size : p->max_hits;
+                    for (uint32_t t = 0; t < cnt; ++t)
+                    {
+                        const uint32_t row = range[0] + t;
+                        uint32_t pos;
+                        if (ORC(fm_locate)(fmi, &row, 1, &pos, NULL, 1)) { failed = 1; continue; }
+                        const uint32_t g_pos = pos > o ? pos - o : 0;
+                        const uint32_t gb = g_pos > p->band / 2 ? g_pos - p->band / 2 : 0;
+                        keys[nk++] = ((uint64_t)s << 32) | gb;
+                    }
+                }
+            if (nk == 0) continue;
+            qsort(keys, nk, sizeof(uint64_t), cmp_u64);
+            size_t nu = 1;
+            for (size_t i = 1; i < nk; ++i) if (keys[i] != keys[nu - 1]) keys[nu++] = keys[i];
+            if (n_candidates) n_candidates[r] = (uint32_t)nu;
+            int32_t best = INT32_MIN, second = INT32_MIN; size_t best_i = 0;
+            for (size_t i = 0; i < nu; ++i)
+            {
+                const uint32_t s = (uint32_t)(keys[i] >> 32), gb = (uint32_t)keys[i];
+                const uint64_t ge64 = (uint64_t)gb + p->band + L;
+                const uint32_t ge = ge64 < G ? (uint32_t)ge64 : G;
+                const uint32_t poff[2] = { 0, L }, toff[2] = { 0, ge - gb };
+                orc_sink sink;
+                if (ORC(banded_score)(p->aligner, p->band, strand_read + s * L, poff, genome + gb, toff, 1, &sink, 1)) { failed = 1; continue; }
+                if (sink.score <= MAP_INVALID) continue;
+                if (sink.score > best) { if (best != INT32_MIN) second = best > second ? best : second; best = sink.score; best_i = i; }
+                else if (sink.score > second) second = sink.score;
+            }
+            if (best == INT32_MIN || best < p->min_score) continue;
+            {
+                const uint32_t s = (uint32_t)(keys[best_i] >> 32), gb = (uint32_t)keys[best_i];
+                const uint64_t ge64 = (uint64_t)gb + p->band + L;
+                const uint32_t ge = ge64 < G ? (uint32_t)ge64 : G;
+                const uint32_t poff[2] = { 0, L }, toff[2] = { 0, ge - gb };
+                const uint32_t stride = 2 * L + p->band + 16;
+                if (stride > cap_ops) { cap_ops = stride; tb_ops = (uint8_t*)realloc(tb_ops, cap_ops); }
+                orc_alignment a; uint32_t n_ops = 0;
+                if (ORC(banded_traceback)(p->aligner, p->band, 16, strand_read + s * L, poff, genome + gb, toff, 1, &a, tb_ops, stride, &n_ops, 1)) { failed = 1; continue; }
+                h.score = a.score; h.second_score = second;
+                h.begin = gb + a.src_x; h.end = gb + a.sink_x;
+                h.flags = 2u | s; h.n_ops = n_ops;
+                hits[r] = h;
+                if (ops && ops_stride) memcpy(ops + (size_t)r * ops_stride, tb_ops, n_ops < ops_stride ? n_ops : ops_stride);
+            }
+        }
+        free(strand_read); free(keys); free(tb_ops);
+    }
+    return failed ? -2 : 0;
+}

@@ -27,6 +27,14 @@ class AlignerC(C.Structure):
                 ("p2", C.c_int32), ("p3", C.c_int32)]
 
 
+class MapParamsC(C.Structure):
+    _fields_ = [("seed_len", C.c_uint32), ("seed_interval", C.c_uint32), ("max_hits", C.c_uint32), ("max_range", C.c_uint32),
+                ("band", C.c_uint32), ("both_strands", C.c_uint32), ("min_score", C.c_int32), ("aligner", AlignerC)]
+
+
+HIT_DT = np.dtype([("score", "<i4"), ("second_score", "<i4"), ("begin", "<u4"), ("end", "<u4"), ("flags", "<u4"), ("n_ops", "<u4")])
+
+
 def aligner(kind, type_, p=(0, -1, -1, -1)):
     return AlignerC(kind, type_, *[int(v) for v in p])
 
@@ -210,3 +218,21 @@ class Oracle:
                                          C.c_uint32(n), _ptr(out), _ptr(ops), C.c_uint32(stride), _ptr(n_ops), C.c_int(threads))
         assert rc == 0, rc
         return out, ops, n_ops
+
+    # ---------------- seed-and-extend composition (oracle_map.c) ----------------
+    def map_reads(self, idx, genome, reads, read_off, params, ops_stride=None, threads=0):
+        """params: MapParamsC. Returns (hits[HIT_DT], ops[n, stride], n_candidates[n])."""
+        genome = np.ascontiguousarray(genome, dtype=np.uint8)
+        reads = np.ascontiguousarray(reads, dtype=np.uint8)
+        read_off = np.ascontiguousarray(read_off, dtype=np.uint32)
+        n = len(read_off) - 1
+        L = int(np.max(np.diff(read_off.astype(np.int64)))) if n else 0
+        stride = ops_stride if ops_stride is not None else (2 * L + params.band + 16 + 15) // 16 * 16
+        hits = np.zeros(n, dtype=HIT_DT)
+        ops = np.zeros((n, stride), dtype=np.uint8)
+        ncand = np.zeros(n, dtype=np.uint32)
+        f = idx.c()
+        rc = self._f("map_reads")(C.byref(f), _ptr(genome), _ptr(reads), _ptr(read_off), C.c_uint32(n), C.byref(params),
+                                  _ptr(hits), _ptr(ops), C.c_uint32(stride), _ptr(ncand), C.c_int(threads))
+        assert rc == 0, rc
+        return hits, ops, ncand

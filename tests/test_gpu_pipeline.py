@@ -1,0 +1,87 @@
+"""-m gpu: nvb_map_reads (seed -> locate -> extend -> reduce -> traceback on the device) vs the same composition
+of the oracle's pinned entry points (oracle/oracle_map.c): hits and op lists bit for bit."""
+import numpy as np
+import pytest
+import torch
+
+import nvbio_gpl_b200 as nvb
+import pyoracle as po
+import gpu_util as gu
+import map_util
+
+pytestmark = pytest.mark.gpu
+
+
+def hits_np(t):
+    return t.cpu().numpy().view(np.uint32).reshape(-1, 6).copy().view(nvb.HIT_DT).reshape(-1)
+
+
+def same(got_hits, got_ops, want_hits, want_ops):
+    if not (got_hits.view(np.uint32) == want_hits.view(np.uint32)).all():
+        bad = np.nonzero(got_hits != want_hits)[0][:5]
+        print("hit mismatch", bad, got_hits[bad], want_hits[bad])
+        return False
+    for i in range(len(got_hits)):
+        k = int(got_hits["n_ops"][i])
+        if not (got_ops[i, :k] == want_ops[i, :k]).all():
+            print("ops mismatch at", i)
+            return False
+    return True
+
+
+CASES = [
+    (po.GOTOH, (0, -5, -8, -3), 15, 4, 0, 1, -60),
+    (po.ED, (0, -1, -1, -1), 15, 4, 0, 1, -20),
+    (po.SW, (1, -2, -3, -3), 7, 2, 0, 1, -1000),
+    (po.GOTOH, (2, -3, -6, -2), 15, 8, 6, 0, 0),
+    (po.GOTOH, (0, -5, -8, -3), 12, 3, 0, 1, -60),      # a band only the int32 kernels take
+]
+
+
+@pytest.mark.parametrize("kind,scores,band,max_hits,max_range,both,min_score", CASES)
+def test_map_reads(oracle, kind, scores, band, max_hits, max_range, both, min_score):
+    rng = np.random.default_rng(band * 31 + kind + max_hits)
+    G = 60000
+    genome = rng.integers(0, 4, G).astype(np.uint8)
+    genome[7000:7600] = genome[21000:21600]
+    genome[30000:30300] = genome[21100:21400]
+    fmi, oidx = gu.fm_index_pair(oracle, genome)
+    words = nvb.pack_genome(torch.from_numpy(genome).to(gu.dev()))
+    sym, off = map_util.make_reads(rng, genome, 3000)
+    pc = map_util.map_params(band, kind, scores, 20, 10, max_hits, max_range, both, min_score)
+    want_hits, want_ops, want_nc = oracle.map_reads(oidx, genome, sym, off, pc)
+    params = nvb.MapParams(nvb.Aligner(kind, nvb.SEMI_GLOBAL, *scores), 20, 10, max_hits, max_range, band, bool(both), min_score)
+    rs = gu.sset(sym, off)
+    for rpb in (0, 700):                                  # one batch, several ragged batches
+        hits, ops, stats = nvb.map_reads(fmi, words, rs.symbols, rs.offsets, params, reads_per_batch=rpb)
+        assert same(hits_np(hits), ops.cpu().numpy(), want_hits, want_ops)
+        assert stats["candidates"] == int(want_nc.sum())
+        assert stats["aligned"] == int(((want_hits["flags"] & 2) != 0).sum())
+    # host entry point
+    h_hits, h_ops, _ = nvb.map_reads_host(fmi, words, sym, off, params,
+                                          ops_h=np.zeros((len(off) - 1, nvb.ops_stride_for(150, band)), np.uint8))
+    assert same(h_hits, h_ops, want_hits, want_ops)
+    assert (want_hits["flags"] & 2).astype(bool).sum() > 2000 or min_score >= 0
+
+
+def test_map_reads_edges(oracle):
+    rng = np.random.default_rng(3)
+    genome = rng.integers(0, 4, 5000).astype(np.uint8)
+    fmi, oidx = gu.fm_index_pair(oracle, genome)
+    words = nvb.pack_genome(torch.from_numpy(genome).to(gu.dev()))
+    params = nvb.MapParams()
+    # no reads
+    e = gu.sset(np.zeros(0, np.uint8), np.zeros(1, np.uint32))
+    hits, ops, stats = nvb.map_reads(fmi, words, e.symbols, e.offsets, params, max_read_len=10)
+    assert hits.shape[0] == 0 and stats["aligned"] == 0
+    # reads that cannot seed (too short, all N) and junk
+    reads = [genome[100:110], np.full(80, 4, np.uint8), rng.integers(0, 4, 100).astype(np.uint8), genome[4900:5000], genome[0:90]]
+    sym, off = po.concat(reads)
+    rs = gu.sset(sym, off)
+    hits, ops, stats = nvb.map_reads(fmi, words, rs.symbols, rs.offsets, params)
+    want_hits, want_ops, _ = oracle.map_reads(oidx, genome, sym, off, map_util.map_params(min_score=-(1 << 29)))
+    assert same(hits_np(hits), ops.cpu().numpy(), want_hits, want_ops)
+    assert (want_hits["flags"][:3] == 0).all() and (want_hits["flags"][3:] == 2).all()
+    # out-of-contract arguments fail loudly
+    with pytest.raises(nvb.NvbError):
+        nvb.map_reads(fmi, words, rs.symbols, rs.offsets, nvb.MapParams(nvb.GotohAligner(nvb.LOCAL, 2, -3, -6, -2)))
