@@ -35,9 +35,10 @@ def parse():
     ap.add_argument("--queries", type=int, default=10_000_000)
     ap.add_argument("--sw-pairs", type=int, default=100_000)
     ap.add_argument("--banded-pairs", type=int, default=10_000_000)
+    ap.add_argument("--reads", type=int, default=10_000_000, help="reads of the seed+extend leg (configs[3] shape, 150 bp)")
     ap.add_argument("--no-extra", action="store_true", help="skip the SW / banded secondary measurements")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
-    ap.add_argument("--only", default="", help="profiling aid: run only this leg (fm|sw|banded) with no cpu leg")
+    ap.add_argument("--only", default="", help="profiling aid: run only this leg (fm|sw|banded|map) with no cpu leg")
     return ap.parse_args()
 
 
@@ -163,6 +164,34 @@ def gen_pairs(n, M, N, seed, dev, sub=0.05, implant_frac=0.5, chunk=1_000_000):
     return P.reshape(-1).contiguous(), po_, T.reshape(-1).contiguous(), to_
 
 
+def gen_reads(genome, n, L, seed, dev, sub=0.01, indel=0.14, chunk=2_000_000):
+    """n reads of L symbols sampled from the genome: 1 % substitutions, one single-base indel in a fraction `indel` of
+    the reads (~0.1 % per base), every other read reverse-complemented (SURVEY 8d, C4 inputs)"""
+    import torch
+    out = torch.empty((n, L), dtype=torch.uint8, device=dev)
+    G = genome.numel()
+    for k, b in enumerate(range(0, n, chunk)):
+        e = min(n, b + chunk); m = e - b
+        g = torch.Generator(device=dev); g.manual_seed(seed * 1000 + k)
+        pos = torch.randint(0, G - L - 2, (m,), device=dev, generator=g)
+        cut = torch.randint(10, L - 10, (m,), device=dev, generator=g)
+        kind = torch.rand(m, device=dev, generator=g)
+        delta = torch.where(kind < indel / 2, 1, torch.where(kind < indel, -1, 0))     # +1: a genome base skipped, -1: a base inserted
+        ar = torch.arange(L, device=dev)
+        idx = pos[:, None] + ar[None, :] + (ar[None, :] >= cut[:, None]) * delta[:, None]
+        r = genome[idx.reshape(-1)].reshape(m, L)
+        ins = torch.nonzero(delta < 0)[:, 0]
+        r[ins, cut[ins]] = torch.randint(0, 4, (ins.numel(),), dtype=torch.uint8, device=dev, generator=g)
+        mm = torch.rand((m, L), device=dev, generator=g) < sub
+        r[mm] = (r[mm] + torch.randint(1, 4, (int(mm.sum().item()),), dtype=torch.uint8, device=dev, generator=g)) & 3
+        rc = torch.arange(m, device=dev) % 2 == 1
+        r[rc] = (3 - r[rc]).flip(1)
+        out[b:e] = r
+        del idx, r, mm
+    off = (torch.arange(n + 1, device=dev, dtype=torch.int64) * L).to(torch.int32)
+    return out.reshape(-1), off
+
+
 def time_steps(fn, steps, warmup, flush):
     """CUDA-event time of `steps` calls of fn on the current stream, L2 flushed between calls"""
     import torch
@@ -220,7 +249,7 @@ def run_b200(args):
     out = {}
     # ---------------- index: built once on rank 0, replicated over NVLink (outside the timed region)
     t0 = time.time()
-    if only in ("", "fm"):
+    if only in ("", "fm", "map"):
         if rank == 0:
             genome = gen_genome(args.genome, 2, dev)
             fmi = nvb.build_index(genome)
@@ -237,6 +266,7 @@ def run_b200(args):
                                   torch.empty(nvb.lib().nvb_ssa_words(n), dtype=torch.int32, device=dev))
             dist.broadcast(genome, 0); dist.broadcast(fmi.bwt_occ, 0); dist.broadcast(fmi.ssa, 0)
         build_s = time.time() - t0
+    if only in ("", "fm"):
         qsym, qoff = gen_queries(genome, args.queries, 100 + rank, dev)
         nq = args.queries
         ranges = torch.empty((nq, 2), dtype=torch.int32, device=dev)
@@ -256,6 +286,20 @@ def run_b200(args):
         step_ms = max_over_ranks(sum(times) / len(times))
         out["fm"] = dict(step_ms=step_ms, value=world * nq / (step_ms * 1e-3), launches=launches, clocks=clocks,
                          build_s=build_s, kernel_ms=sum(times) / len(times))
+
+        # ---- the same launch with the optional 10-mer jump table (8 MiB; identical ranges): reported beside `value`, not as it
+        fmi.build_ktab(10, ctx=ctx)
+        fck = fmi.c()
+        ranges_k = torch.empty((nq, 2), dtype=torch.int32, device=dev)
+        def _match_k():
+            check(L.nvb_fm_match(ctx.h, ctypes.byref(fck), qset, ranges_k.data_ptr(), current_stream_ptr()), ctx.h)
+        barrier()
+        tk = time_steps(_match_k, args.steps, args.warmup, flush)
+        k_ms = max_over_ranks(sum(tk) / len(tk))
+        assert bool((ranges_k == ranges).all().item()), "k-mer jump table changed a range"
+        out["fm"]["ktab10"] = dict(value=world * nq / (k_ms * 1e-3), ms_per_step=k_ms, table_bytes=int(fmi.ktab.numel() * 4))
+        del ranges_k
+        fmi.drop_ktab()
 
         # ---- e2e: host buffers (pinned) through the C-ABI *_host call: H2D + kernel + D2H per step
         hs = torch.empty(qsym.numel(), dtype=torch.uint8).pin_memory(); hs.copy_(qsym)
@@ -321,6 +365,65 @@ def run_b200(args):
             out["fm"]["parity"] = dict(checked=sample, mismatches=mism)
             out["fm"]["blocks_per_query"] = float(blocks.mean())
         del hs, ho, hr
+
+    # ---------------- seed -> locate -> extend -> traceback over 150-bp reads (configs[3] shape on this leg's genome)
+    if only == "map" or (only == "" and not args.no_extra):
+        RL, nr = 150, args.reads
+        words = nvb.pack_genome(genome, ctx=ctx)
+        fmi.build_ktab(10, ctx=ctx)          # seeding starts from the 10-mer jump table (identical ranges)
+        rsym, roff = gen_reads(genome, nr, RL, 7 + rank, dev)
+        mparams = nvb.MapParams(nvb.GotohAligner(nvb.SEMI_GLOBAL, 0, -5, -8, -3), seed_len=20, seed_interval=10, max_hits=4,
+                                max_range=0, band=15, both_strands=True, min_score=-90)
+        stride = nvb.ops_stride_for(RL, 15)
+        res = {}
+        def _map():
+            res["r"] = nvb.map_reads(fmi, words, rsym, roff, mparams, max_read_len=RL, ctx=ctx)
+        l0 = ctx.launches
+        _map()
+        per_call = ctx.launches - l0
+        barrier()
+        tms = time_steps(_map, max(2, args.steps // 3), 1, flush)
+        ms = max_over_ranks(sum(tms) / len(tms))
+        hits_d, ops_d, mstats = res["r"]
+        out["map"] = dict(reads_per_s=world * nr / (ms * 1e-3), ms=ms, reads=nr, read_len=RL, launches_per_call=per_call,
+                          seed_hits_per_read=mstats["seed_hits"] / nr, candidates_per_read=mstats["candidates"] / nr,
+                          aligned_frac=mstats["aligned"] / nr, genome=int(genome.numel()),
+                          params="20-mer seeds every 10 bp on both strands (10-mer jump table), <= 4 rows per seed, banded (15) Gotoh (0,-5,-8,-3) "
+                                 "SEMI_GLOBAL, min score -90, traceback of the best window")
+        # e2e: pinned host reads in, hits + op lists out
+        hr_sym = torch.empty(rsym.numel(), dtype=torch.uint8).pin_memory(); hr_sym.copy_(rsym)
+        hr_off = torch.empty(roff.numel(), dtype=torch.int32).pin_memory(); hr_off.copy_(roff)
+        hh = torch.empty((nr, 6), dtype=torch.int32).pin_memory()
+        hops = torch.empty((nr, stride), dtype=torch.uint8).pin_memory()
+        hh_n = hh.numpy().view(np.uint32).reshape(-1).view(nvb.HIT_DT)
+        args_h = (fmi, words, hr_sym.numpy(), hr_off.numpy().view(np.uint32), mparams)
+        nvb.map_reads_host(*args_h, hits_h=hh_n, ops_h=hops.numpy(), ctx=ctx)
+        barrier()
+        t_e = []
+        for _ in range(2):
+            t0_ = time.time(); nvb.map_reads_host(*args_h, hits_h=hh_n, ops_h=hops.numpy(), ctx=ctx); t_e.append(time.time() - t0_)
+        e_ms = max_over_ranks(min(t_e) * 1e3)
+        out["map"]["e2e"] = dict(reads_per_s=world * nr / (e_ms * 1e-3), ms=e_ms, h2d_bytes=int(hr_sym.numel() + hr_off.numel() * 4),
+                                 d2h_bytes=int(hh.numel() * 4 + hops.numel()))
+        assert (hh.numpy() == hits_d.cpu().numpy()).all(), "host and device pipeline entry points disagree"
+        if rank == 0 and world == 1 and not args.no_cpu and only in ("", "map"):
+            po, chk, kind = load_checker()
+            bwt_occ, ssa = fmi.host_arrays()
+            oidx = po.Index(fmi.length, fmi.primary, np.array(fmi.L2, dtype=np.uint32), bwt_occ, ssa)
+            gh = genome.cpu().numpy()
+            pc = po.MapParamsC(20, 10, 4, 0, 15, 1, -90, po.aligner(po.GOTOH, po.SEMI_GLOBAL, (0, -5, -8, -3)))
+            probe = 20000
+            t = time.time(); chk.map_reads(oidx, gh, hr_sym.numpy()[:probe * RL], hr_off.numpy().view(np.uint32)[:probe + 1], pc, ops_stride=stride, threads=host_threads()); dt = time.time() - t
+            k = int(min(nr, max(probe, 10.0 / max(dt, 1e-6) * probe)))
+            t = time.time(); wh, wo, _ = chk.map_reads(oidx, gh, hr_sym.numpy()[:k * RL], hr_off.numpy().view(np.uint32)[:k + 1], pc, ops_stride=stride, threads=host_threads()); dt = time.time() - t
+            got_h, got_o = hh_n[:k], hops.numpy()[:k]
+            mism = int((got_h.view(np.uint32).reshape(k, 6) != wh.view(np.uint32).reshape(k, 6)).any(axis=1).sum())
+            valid = np.arange(stride)[None, :] < wh["n_ops"][:, None]
+            mism_ops = int(((got_o != wo) & valid).any(axis=1).sum())
+            out["map"]["cpu"] = dict(reads_per_s=k / dt, cores=host_threads(), kind=kind, sample="first %d reads" % k)
+            out["map"]["parity"] = dict(checked=k, hit_mismatches=mism, ops_mismatches=mism_ops)
+            del gh
+        del hr_sym, hr_off, hh, hops, rsym, roff, words, res, hits_d, ops_d
 
     # ---------------- secondary: SW local scoring (configs[0]) and banded scoring/traceback (configs[2])
     if not args.no_extra or only in ("sw", "banded"):
@@ -408,7 +511,8 @@ def run_b200(args):
                             "index_bytes": int(fmi.bwt_occ.numel() * 4), "partition": "queries sharded, index replicated, no collective",
                             "l2": "flushed (256 MiB write) between timed steps, outside the event-timed region",
                             "index_build_s": round(fm["build_s"], 2),
-                            "e2e_packed4": fm.get("e2e_packed4")})
+                            "e2e_packed4": fm.get("e2e_packed4"),
+                            "value_with_kmer_jump_table": fm.get("ktab10")})
         if alg_per_q:
             ach = alg_per_q * args.queries / (fm["kernel_ms"] * 1e-3) / 1e9
             line["roofline"] = {"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
@@ -430,7 +534,7 @@ def run_b200(args):
         for k, kind in (("ed_semi", "ed"), ("gotoh_semi", "gotoh"), ("sw_local", "sw")):
             if k in out["banded"]:
                 out["banded"][k]["roofline"] = _roof(out["banded"][k]["gcups"], kind)
-    extra = {k: out[k] for k in ("sw", "banded") if k in out}
+    extra = {k: out[k] for k in ("sw", "banded", "map") if k in out}
     if extra:
         line["extra"] = extra
     print(json.dumps(line))

@@ -61,6 +61,8 @@ typedef struct {
     uint32_t        sa_int;     /* must be 16  (FMIndexDataCore::SA_INT)                        */
     const void*     bwt_occ;    /* fused array, 32 B per 64 symbols                             */
     const uint32_t* ssa;        /* (length+16)/16 entries, ssa[0] = 0xFFFFFFFF; may be NULL     */
+    const uint32_t* ktab;       /* optional k-mer jump table (nvb_fmindex_build_ktab), else NULL */
+    uint32_t        ktab_k;     /* symbols per table entry (0 = no table)                       */
 } nvb_fmindex;
 
 /* ConcatenatedStringSet<symbols, offsets> (nvbio/strings/string_set.h:405-492) */
@@ -128,6 +130,13 @@ int nvb_fmindex_save(nvb_ctx* ctx, const nvb_fmindex* fmi_d, const char* prefix,
 /* pin the first `bytes` of the fused array (the hot BWT prefix) in L2 for work on the ctx stream
  * (cudaAccessPolicyWindow); bytes = 0 removes the window. Replaces the reference's texture/__ldg
  * cache hint (nvbio/fmindex/fmindex.h:564-583). */
+/* Optional k-mer jump table: entry i = the raw (x, y) pair match() returns for the k-mer whose symbols are the
+ * base-4 digits of i (first symbol most significant), 2 uint32 per entry, 4^k entries (k <= 13). With fmi->ktab set,
+ * nvb_fm_match / nvb_fm_filter_rank / nvb_map_reads start a query of >= k symbols (none > 3 among its last k) from the
+ * entry of its last k symbols instead of walking the first k steps of fmindex_inl.h:186-239; results are identical,
+ * bit for bit (the loop would have stopped on the same pair). The table is the caller's memory, like the index. */
+size_t nvb_ktab_words(uint32_t k);
+int nvb_fmindex_build_ktab(nvb_ctx* ctx, const nvb_fmindex* fmi_d, uint32_t k, uint32_t* ktab_d, void* stream);
 int nvb_fmindex_pin_l2(nvb_ctx* ctx, const nvb_fmindex* fmi_d, size_t bytes);
 /* fuse a plain BWT (2-bit big-endian words, as in a .bwt file: nvBWT/nvBWT.cu:303-321) into the
  * interleaved bwt|occ image and compute L2; all pointers DEVICE; bwt_occ_out has

@@ -17,7 +17,7 @@ class NvbError(RuntimeError):
 class FMIndexC(C.Structure):
     _fields_ = [("length", C.c_uint32), ("primary", C.c_uint32), ("L2", C.c_uint32 * 5),
                 ("occ_int", C.c_uint32), ("sa_int", C.c_uint32),
-                ("bwt_occ", C.c_void_p), ("ssa", C.c_void_p)]
+                ("bwt_occ", C.c_void_p), ("ssa", C.c_void_p), ("ktab", C.c_void_p), ("ktab_k", C.c_uint32)]
 
 
 class StringSetC(C.Structure):
@@ -66,6 +66,8 @@ _PROTOS = {
     "nvb_fmindex_upload": (_i, [_vp, C.POINTER(FMIndexC), C.POINTER(FMIndexC)]),
     "nvb_fmindex_release": (_i, [_vp, C.POINTER(FMIndexC)]),
     "nvb_fmindex_pin_l2": (_i, [_vp, C.POINTER(FMIndexC), _sz]),
+    "nvb_ktab_words": (_sz, [_u32]),
+    "nvb_fmindex_build_ktab": (_i, [_vp, C.POINTER(FMIndexC), _u32, _vp, _vp]),
     "nvb_bwt_occ_words": (_sz, [_u32]),
     "nvb_ssa_words": (_sz, [_u32]),
     "nvb_fmindex_fuse": (_i, [_vp, _vp, _u32, _vp, _vp, _vp]),

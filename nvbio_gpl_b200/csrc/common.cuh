@@ -51,6 +51,8 @@ struct FMView
     uint32_t        L2[5];
     const uint4*    blk;      // 2 uint4 per 64 symbols: words, counters
     const uint32_t* ssa;
+    const uint2*    ktab;     // k-mer jump table (optional)
+    uint32_t        ktab_k;
 };
 
 static inline FMView make_view(const nvb_fmindex* f)
@@ -59,6 +61,7 @@ static inline FMView make_view(const nvb_fmindex* f)
     v.length = f->length; v.primary = f->primary;
     for (int i = 0; i < 5; ++i) v.L2[i] = f->L2[i];
     v.blk = (const uint4*)f->bwt_occ; v.ssa = f->ssa;
+    v.ktab = (const uint2*)f->ktab; v.ktab_k = f->ktab ? f->ktab_k : 0u;
     return v;
 }
 

@@ -19,7 +19,7 @@
 // The query symbols of a CTA are one contiguous span of the concatenated set: it is staged into
 // shared memory with coalesced 16-byte loads, so the dependent loop only touches the index.
 // ---------------------------------------------------------------------------------------------
-template <int BITS, bool FROM>
+template <int BITS, bool FROM, bool KTAB>
 __global__ void __launch_bounds__(FM_THREADS)
 fm_match_kernel(const FMView f, const StrSet q, uint32_t* __restrict__ ranges)
 {
@@ -56,7 +56,20 @@ fm_match_kernel(const FMView f, const StrSet q, uint32_t* __restrict__ ranges)
     if (FROM) { x = ranges[2 * tid]; y = ranges[2 * tid + 1]; }
     else      { x = 0; y = f.length; }
 
-    for (int32_t i = (int32_t)len - 1; i >= 0 && x <= y; --i)
+    int32_t i = (int32_t)len - 1;
+    if (KTAB && !FROM && len >= f.ktab_k)
+    {
+        // the last k symbols select a precomputed (x, y): the pair the loop below reaches after its first k steps
+        // (or the pair it stopped on); a symbol > 3 among them leaves the query to the loop
+        uint32_t idx = 0, bad = 0;
+        for (uint32_t j = len - f.ktab_k; j < len; ++j)
+        {
+            const uint32_t c = staged ? (uint32_t)s_sym[skew + (beg - span_begin) + j] : sym_at<BITS>(q.sym, beg + j);
+            bad |= c; idx = idx * 4u + (c & 3u);
+        }
+        if (bad <= 3u) { const uint2 r = __ldg(f.ktab + idx); x = r.x; y = r.y; i -= (int32_t)f.ktab_k; }
+    }
+    for (; i >= 0 && x <= y; --i)
     {
         const uint32_t c = staged ? (uint32_t)s_sym[skew + (beg - span_begin) + (uint32_t)i]
                                   : sym_at<BITS>(q.sym, beg + (uint32_t)i);
@@ -197,13 +210,50 @@ static int fm_match_launch(nvb_ctx* ctx, const nvb_fmindex* fmi, nvb_string_set 
     const StrSet q = make_set(queries);
     cudaStream_t s = (cudaStream_t)stream;
     const uint32_t grid = grid_for(q.count);
+    const bool kt = !FROM && f.ktab_k > 0;
+    if (f.ktab_k > 13u) return NVB_ERR_ARG;
     switch (queries.bits)
     {
-    case 8: fm_match_kernel<8, FROM><<<grid, FM_THREADS, 0, s>>>(f, q, ranges); break;
-    case 4: fm_match_kernel<4, FROM><<<grid, FM_THREADS, 0, s>>>(f, q, ranges); break;
-    case 2: fm_match_kernel<2, FROM><<<grid, FM_THREADS, 0, s>>>(f, q, ranges); break;
+    case 8: if (kt) fm_match_kernel<8, FROM, true><<<grid, FM_THREADS, 0, s>>>(f, q, ranges);
+            else    fm_match_kernel<8, FROM, false><<<grid, FM_THREADS, 0, s>>>(f, q, ranges); break;
+    case 4: if (kt) fm_match_kernel<4, FROM, true><<<grid, FM_THREADS, 0, s>>>(f, q, ranges);
+            else    fm_match_kernel<4, FROM, false><<<grid, FM_THREADS, 0, s>>>(f, q, ranges); break;
+    case 2: if (kt) fm_match_kernel<2, FROM, true><<<grid, FM_THREADS, 0, s>>>(f, q, ranges);
+            else    fm_match_kernel<2, FROM, false><<<grid, FM_THREADS, 0, s>>>(f, q, ranges); break;
     default: return NVB_ERR_ARG;
     }
+    NVB_LAUNCHED(ctx);
+    return NVB_OK;
+}
+
+// k-mer jump table: one thread per k-mer runs the plain backward search of its k symbols
+__global__ void __launch_bounds__(FM_THREADS)
+fm_ktab_kernel(const FMView f, uint32_t k, uint32_t n, uint2* __restrict__ tab)
+{
+    __shared__ uint2 s_lut[FM_LUT_ENTRIES];
+    fm_lut_init(s_lut);
+    const uint32_t idx = blockIdx.x * FM_THREADS + threadIdx.x;
+    if (idx >= n) return;
+    uint32_t x = 0, y = f.length;
+    for (uint32_t j = 0; j < k && x <= y; ++j)
+    {
+        const uint32_t c = (idx >> (2u * j)) & 3u;               // last symbol first
+        const uint2 r = fm_rank2(f, x - 1u, y, c, s_lut);
+        x = f.L2[c] + r.x + 1u;
+        y = f.L2[c] + r.y;
+    }
+    tab[idx] = make_uint2(x, y);
+}
+
+extern "C" size_t nvb_ktab_words(uint32_t k) { return k && k <= 13u ? (size_t)2 << (2u * k) : 0; }
+
+extern "C" int nvb_fmindex_build_ktab(nvb_ctx* ctx, const nvb_fmindex* fmi, uint32_t k, uint32_t* ktab, void* stream)
+{
+    if (!ctx || !ktab || k == 0 || k > 13u) return NVB_ERR_ARG;
+    int rc = check_fmi(fmi, false); if (rc) return rc;
+    FMView f = make_view(fmi); f.ktab = nullptr; f.ktab_k = 0;
+    const uint32_t n = 1u << (2u * k);
+    fm_ktab_kernel<<<grid_for(n), FM_THREADS, 0, (cudaStream_t)stream>>>(f, k, n, (uint2*)ktab);
     NVB_LAUNCHED(ctx);
     return NVB_OK;
 }

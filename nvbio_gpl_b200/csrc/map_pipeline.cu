@@ -18,6 +18,8 @@
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_select.cuh>
 #include <thrust/iterator/counting_iterator.h>
+#include <cstdio>
+#include <cstdlib>
 
 #define MAP_THREADS 256
 #define MAP_NONE    0xFFFFFFFFu
@@ -56,7 +58,18 @@ map_seed_kernel(const FMView f, const StrSet reads, const MapGeom g, uint2* __re
     if (o + g.seed_len <= L)
     {
         x = 0; y = f.length;
-        for (int32_t i = (int32_t)g.seed_len - 1; i >= 0 && x <= y; --i)
+        int32_t i = (int32_t)g.seed_len - 1;
+        if (f.ktab_k && g.seed_len >= f.ktab_k)
+        {
+            uint32_t idx = 0, bad = 0;
+            for (uint32_t j = g.seed_len - f.ktab_k; j < g.seed_len; ++j)
+            {
+                const uint32_t c = map_strand_symbol(read, L, strand, o + j);
+                bad |= c; idx = idx * 4u + (c & 3u);
+            }
+            if (bad <= 3u) { const uint2 r = __ldg(f.ktab + idx); x = r.x; y = r.y; i -= (int32_t)f.ktab_k; }
+        }
+        for (; i >= 0 && x <= y; --i)
         {
             const uint32_t c = map_strand_symbol(read, L, strand, o + (uint32_t)i);
             if (c > 3u) { x = 1; y = 0; break; }
@@ -236,6 +249,36 @@ extern "C" int nvb_pack_2bit(nvb_ctx* ctx, const uint8_t* symbols_d, uint32_t n,
     return NVB_OK;
 }
 
+// NVB_MAP_TRACE=1: per-phase device time of a call (CUDA events on the call's stream), printed to stderr
+struct MapTrace
+{
+    enum { SEED, LOCATE, SORT, EXTRACT, SCORE, REDUCE, TB_EXTRACT, TRACEBACK, FINISH, N_PHASES };
+    bool on; cudaStream_t s; cudaEvent_t ev[2]; float ms[N_PHASES]; int cur;
+    MapTrace(cudaStream_t st) : on(false), s(st), cur(0)
+    {
+        const char* e = getenv("NVB_MAP_TRACE");
+        on = e && e[0] == '1';
+        for (int i = 0; i < N_PHASES; ++i) ms[i] = 0.f;
+        if (on) { cudaEventCreate(&ev[0]); cudaEventCreate(&ev[1]); cudaEventRecord(ev[0], s); }
+    }
+    void mark(int phase)
+    {
+        if (!on) return;
+        cudaEventRecord(ev[cur ^ 1], s); cudaEventSynchronize(ev[cur ^ 1]);
+        float t = 0.f; cudaEventElapsedTime(&t, ev[cur], ev[cur ^ 1]); ms[phase] += t; cur ^= 1;
+    }
+    ~MapTrace()
+    {
+        if (!on) return;
+        static const char* names[N_PHASES] = { "seed+scan", "locate", "sort+unique", "extract", "score", "reduce+select", "tb extract", "traceback", "finish" };
+        float tot = 0.f; for (int i = 0; i < N_PHASES; ++i) tot += ms[i];
+        fprintf(stderr, "[nvb_map_reads] %.3f ms:", tot);
+        for (int i = 0; i < N_PHASES; ++i) fprintf(stderr, " %s %.3f |", names[i], ms[i]);
+        fprintf(stderr, "\n");
+        cudaEventDestroy(ev[0]); cudaEventDestroy(ev[1]);
+    }
+};
+
 static inline uint32_t map_grid(uint64_t threads) { return (uint32_t)((threads + MAP_THREADS - 1) / MAP_THREADS); }
 static inline uint32_t bits_for(uint64_t v) { uint32_t b = 0; while (b < 64 && (v >> b)) ++b; return b; }
 
@@ -300,6 +343,7 @@ extern "C" int nvb_map_reads(nvb_ctx* ctx, const nvb_fmindex* fmi, const uint32_
     const uint32_t cand_chunk = 4u << 20, tb_chunk = 2u << 20;
 
     uint32_t* d_num; MAP_STAGE(S_NUM, 64, d_num);
+    MapTrace trace(s);
     for (uint32_t r0 = 0; r0 < n_total; r0 += (uint32_t)rb)
     {
         const uint32_t nr = (uint32_t)(n_total - r0 < rb ? n_total - r0 : rb);
@@ -329,6 +373,7 @@ extern "C" int nvb_map_reads(nvb_ctx* ctx, const nvb_fmindex* fmi, const uint32_
             ctx->launches++;
             NVB_CUDA(ctx, cudaMemcpyAsync(&n_hits, scan + n_slots, sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
             NVB_CUDA(ctx, cudaStreamSynchronize(s));
+            trace.mark(MapTrace::SEED);
             if (n_hits)
             {
                 // ---- locate + candidate keys, sorted and de-duplicated
@@ -336,6 +381,7 @@ extern "C" int nvb_map_reads(nvb_ctx* ctx, const nvb_fmindex* fmi, const uint32_
                 MAP_STAGE(S_KEYS_B, sizeof(uint64_t) * (size_t)n_hits, keys_b);
                 map_locate_kernel<<<map_grid(n_hits), MAP_THREADS, 0, s>>>(f, g, seeds, scan, n_slots, n_hits, keys_a);
                 NVB_LAUNCHED(ctx);
+                trace.mark(MapTrace::LOCATE);
                 const int end_bit = (int)(32u + bits_for(2ull * nr));
                 size_t sort_bytes = 0, uniq_bytes = 0;
                 cub::DeviceRadixSort::SortKeys(nullptr, sort_bytes, keys_a, keys_b, (int)n_hits, 0, end_bit, s);
@@ -347,6 +393,7 @@ extern "C" int nvb_map_reads(nvb_ctx* ctx, const nvb_fmindex* fmi, const uint32_
                 ctx->launches += 2;
                 NVB_CUDA(ctx, cudaMemcpyAsync(&n_cand, d_num, sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
                 NVB_CUDA(ctx, cudaStreamSynchronize(s));
+                trace.mark(MapTrace::SORT);
             }
         }
         const uint64_t* keys = keys_a;
@@ -360,7 +407,9 @@ extern "C" int nvb_map_reads(nvb_ctx* ctx, const nvb_fmindex* fmi, const uint32_
                 const uint32_t cnt = n_cand - c0 < cand_chunk ? n_cand - c0 : cand_chunk;
                 nvb_string_set P, T;
                 if ((rc = map_build_sets(ctx, keys, nullptr, nullptr, c0, cnt, reads, r0, genome, mp->band, G, maxL, &P, &T, s))) return rc;
+                trace.mark(MapTrace::EXTRACT);
                 if ((rc = nvb_batch_banded_score(ctx, mp->aligner, mp->band, P, T, sinks + c0, maxL, maxL + mp->band, nullptr, 0, s))) return rc;
+                trace.mark(MapTrace::SCORE);
             }
         }
         // ---- best / second best per read, list of aligned reads
@@ -379,12 +428,14 @@ extern "C" int nvb_map_reads(nvb_ctx* ctx, const nvb_fmindex* fmi, const uint32_
             ctx->launches++;
             NVB_CUDA(ctx, cudaMemcpyAsync(&n_aligned, d_num, sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
             NVB_CUDA(ctx, cudaStreamSynchronize(s));
+            trace.mark(MapTrace::REDUCE);
             // ---- traceback of the best window of every aligned read
             for (uint32_t c0 = 0; c0 < n_aligned; c0 += tb_chunk)
             {
                 const uint32_t cnt = n_aligned - c0 < tb_chunk ? n_aligned - c0 : tb_chunk;
                 nvb_string_set P, T;
                 if ((rc = map_build_sets(ctx, keys, alist + c0, best, 0, cnt, reads, r0, genome, mp->band, G, maxL, &P, &T, s))) return rc;
+                trace.mark(MapTrace::TB_EXTRACT);
                 nvb_alignment* aln; uint8_t* tb_ops; uint32_t* tb_n; void* tb_temp;
                 MAP_STAGE(S_ALN, sizeof(nvb_alignment) * (size_t)cnt, aln);
                 MAP_STAGE(S_TBOPS, (size_t)cnt * tb_stride + 16, tb_ops);
@@ -396,9 +447,11 @@ extern "C" int nvb_map_reads(nvb_ctx* ctx, const nvb_fmindex* fmi, const uint32_
                 MAP_STAGE(S_TBTEMP, want, tb_temp);
                 if ((rc = nvb_batch_banded_traceback(ctx, mp->aligner, mp->band, 16, P, T, aln, tb_ops, tb_stride, tb_n, maxL, maxL + mp->band,
                                                      tb_temp, want, s))) return rc;
+                trace.mark(MapTrace::TRACEBACK);
                 map_finish_kernel<<<map_grid((uint64_t)cnt * 32u), MAP_THREADS, 0, s>>>(keys, alist + c0, best, second, 0, cnt, aln, tb_ops, tb_stride, tb_n,
                                                                                        bhits, ops ? ops + (size_t)r0 * ops_stride : nullptr, ops_stride);
                 NVB_LAUNCHED(ctx);
+                trace.mark(MapTrace::FINISH);
             }
         }
         if (stats) { stats->seeds += n_slots; stats->seed_hits += n_hits; stats->candidates += n_cand; stats->aligned += n_aligned; }

@@ -39,6 +39,7 @@ class FMIndex:
         self.L2 = [int(v) for v in L2]
         self.bwt_occ = bwt_occ      # torch.int32 [nvb_bwt_occ_words(length)]
         self.ssa = ssa              # torch.int32 [(length+16)//16] or None
+        self.ktab, self.ktab_k = None, 0   # optional k-mer jump table (build_ktab)
         assert bwt_occ.dtype == torch.int32 and bwt_occ.numel() == _words_for(self.length) * 2
 
     @property
@@ -63,7 +64,24 @@ class FMIndex:
         f.occ_int, f.sa_int = OCC_INT, SA_INT
         f.bwt_occ = self.bwt_occ.data_ptr()
         f.ssa = self.ssa.data_ptr() if self.ssa is not None else None
+        f.ktab = self.ktab.data_ptr() if self.ktab is not None else None
+        f.ktab_k = self.ktab_k if self.ktab is not None else 0
         return f
+
+    def build_ktab(self, k=10, ctx=None):
+        """k-mer jump table (nvb_fmindex_build_ktab): match() then starts from the precomputed range of a query's
+        last k symbols; identical results. 8 * 4**k bytes (k = 10: 8 MiB, L2-resident)."""
+        ctx = ctx or Context.default(self.device.index)
+        self.ktab, self.ktab_k = None, 0
+        tab = torch.empty(int(lib().nvb_ktab_words(k)), dtype=torch.int32, device=self.device)
+        f = self.c()
+        check(lib().nvb_fmindex_build_ktab(ctx.h, C.byref(f), int(k), tab.data_ptr(), _lib.current_stream_ptr()), ctx.h)
+        self.ktab, self.ktab_k = tab, int(k)
+        return self
+
+    def drop_ktab(self):
+        self.ktab, self.ktab_k = None, 0
+        return self
 
     def host_arrays(self):
         """(bwt_occ, ssa) as numpy uint32 -- what a host-side checker needs"""

@@ -186,3 +186,37 @@ def test_nvbwt_files_round_trip(oracle, tmp_path):
             pos = c.locate(torch.from_numpy(rows.view(np.int32)).to(gu.dev())).cpu().numpy().view(np.uint32)
             assert (pos == oracle.fm_locate(oidx, rows)).all()
         c.close()
+
+
+@pytest.mark.parametrize("k", [1, 3, 8, 10])
+def test_kmer_jump_table(oracle, k):
+    """match() through the k-mer jump table returns the raw ranges of the plain loop (fmindex_inl.h:186-239), also for
+    absent queries (the pair the loop stopped on), queries shorter than k and queries with an N in their last k symbols"""
+    rng = np.random.default_rng(100 + k)
+    for n, alpha in ((50000, 4), (3000, 2), (40, 4)):
+        text = rng.integers(0, alpha, n).astype(np.uint8)
+        fmi, oidx = gu.fm_index_pair(oracle, text)
+        Q, qo = util.rand_queries(rng, text, 30000, len_range=(0, 30), alpha=4, p_from_text=0.6, p_n=0.1)
+        qs = gu.sset(Q, qo)
+        want = oracle.fm_match(oidx, Q, qo)
+        plain = u32(nvb.match(fmi, qs.symbols, qs.offsets))
+        fmi.build_ktab(k)
+        tab = u32(fmi.ktab).reshape(-1, 2)
+        assert tab.shape[0] == 4 ** k
+        got = u32(nvb.match(fmi, qs.symbols, qs.offsets))
+        assert (plain == want).all() and (got == want).all()
+        # every table entry is match() of its k-mer
+        ids = rng.integers(0, 4 ** k, min(4 ** k, 2000))
+        kmers = ((ids[:, None] >> (2 * (k - 1 - np.arange(k)))[None, :]) & 3).astype(np.uint8)
+        assert (tab[ids] == oracle.fm_match(oidx, kmers.reshape(-1), (np.arange(len(ids) + 1) * k).astype(np.uint32))).all()
+        for bits in (4, 2):
+            if bits == 2 and (Q > 3).any():
+                Q2 = Q & 3
+                w = torch.from_numpy(nvb.pack_symbols(Q2, 2).view(np.int32)).to(gu.dev())
+                assert (u32(nvb.match(fmi, w, qs.offsets, bits=2)) == oracle.fm_match(oidx, Q2, qo)).all()
+            else:
+                w = torch.from_numpy(nvb.pack_symbols(Q, bits).view(np.int32)).to(gu.dev())
+                assert (u32(nvb.match(fmi, w, qs.offsets, bits=bits)) == want).all()
+        # the filter goes through the same kernel
+        flt = nvb.FMIndexFilter()
+        assert flt.rank(fmi, qs.symbols, qs.offsets) == int(((want[:, 1] + 1 - want[:, 0]).astype(np.uint32)).astype(np.uint64).sum())

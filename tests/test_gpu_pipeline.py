@@ -52,7 +52,9 @@ def test_map_reads(oracle, kind, scores, band, max_hits, max_range, both, min_sc
     want_hits, want_ops, want_nc = oracle.map_reads(oidx, genome, sym, off, pc)
     params = nvb.MapParams(nvb.Aligner(kind, nvb.SEMI_GLOBAL, *scores), 20, 10, max_hits, max_range, band, bool(both), min_score)
     rs = gu.sset(sym, off)
-    for rpb in (0, 700):                                  # one batch, several ragged batches
+    for rpb in (0, 700, 1100):                            # one batch, several ragged batches; the last with the k-mer jump table
+        if rpb == 1100:
+            fmi.build_ktab(8)
         hits, ops, stats = nvb.map_reads(fmi, words, rs.symbols, rs.offsets, params, reads_per_batch=rpb)
         assert same(hits_np(hits), ops.cpu().numpy(), want_hits, want_ops)
         assert stats["candidates"] == int(want_nc.sum())
