@@ -10,7 +10,7 @@
 #endif
 
 #define NVB_SM_COUNT 148
-#define NVB_STAGE_SLOTS 32
+#define NVB_STAGE_SLOTS 40
 
 struct nvb_ctx
 {

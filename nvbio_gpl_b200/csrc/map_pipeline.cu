@@ -26,7 +26,7 @@
 #define MAP_INVALID (-(1 << 30))
 
 enum { S_SEED = 8, S_COUNT, S_SCAN, S_KEYS_A, S_KEYS_B, S_CUB, S_NUM, S_POFF, S_TOFF, S_PSYM, S_TSYM, S_SINKS,
-       S_BEST, S_SECOND, S_ALIST, S_ALN, S_TBOPS, S_TBNOPS, S_TBTEMP, S_HREADS, S_HOFF, S_HHITS, S_HOPS };
+       S_BEST, S_SECOND, S_ALIST, S_ALN, S_TBOPS, S_TBNOPS, S_TBTEMP, S_HREADS, S_HOFF, S_HHITS, S_HOPS, S_ROWS, S_STEPS };
 
 struct MapGeom
 {
@@ -87,26 +87,143 @@ map_seed_kernel(const FMView f, const StrSet reads, const MapGeom g, uint2* __re
     counts[t] = cnt;
 }
 
+// one thread per seed slot: its selected SA rows go to their places in hit order (row, slot)
 __global__ void __launch_bounds__(MAP_THREADS)
-map_locate_kernel(const FMView f, const MapGeom g, const uint2* __restrict__ seeds, const uint32_t* __restrict__ scan,
-                  uint32_t n_slots, uint32_t n_hits, uint64_t* __restrict__ keys)
+map_expand_kernel(const uint2* __restrict__ seeds, const uint32_t* __restrict__ scan, uint32_t n_slots, uint2* __restrict__ rows)
+{
+    const uint32_t sl = blockIdx.x * MAP_THREADS + threadIdx.x;
+    if (sl >= n_slots) return;
+    const uint2 sd = seeds[sl];
+    const uint32_t base = scan[sl];
+    for (uint32_t t = 0; t < sd.y; ++t) rows[base + t] = make_uint2(sd.x + t, sl);
+}
+
+// LF-walk of every hit to its sampled SA row (locate_ssa_iterator, fmindex_inl.h:364-400). Walks take 0..15 steps:
+// each thread owns a strided list of hits and starts its next walk as soon as one ends, so the lanes of a warp do
+// not wait for the longest walk among them. rows[h].x becomes the sampled row, steps[h] the distance walked.
+__global__ void __launch_bounds__(MAP_THREADS)
+map_walk_kernel(const FMView f, uint32_t n_hits, uint2* __restrict__ rows, uint8_t* __restrict__ steps)
 {
     __shared__ uint2 s_lut[FM_LUT_ENTRIES];
     fm_lut_init(s_lut);
+    const uint32_t stride = gridDim.x * MAP_THREADS;
+    uint32_t h = blockIdx.x * MAP_THREADS + threadIdx.x;
+    bool alive = h < n_hits;                               // whole warps stay in the loop: it reconverges at the vote
+    uint32_t j = alive ? rows[h].x : 0u, t = 0;
+    uint32_t hn = h + stride;
+    uint32_t jn = hn < n_hits ? rows[hn].x : 0u;          // the next walk's row is fetched one walk ahead
+    while (__any_sync(0xFFFFFFFFu, alive))
+    {
+        if (alive && (j & 15u) == 0u)
+        {
+            rows[h].x = j; steps[h] = (uint8_t)t;
+            h = hn; j = jn; t = 0;
+            alive = h < n_hits;
+            hn = h + stride;
+            jn = hn < n_hits ? rows[hn].x : 0u;
+        }
+        if (alive && (j & 15u) != 0u)
+        {
+            uint32_t nj = 0;
+            if (j != f.primary)
+            {
+                const uint32_t jj = j < f.primary ? j : j - 1u;
+                const FMBlock b = fm_load_block(f.blk, jj >> 6);
+                const uint32_t c = fm_bwt_symbol(b, jj & 63u);
+                const uint32_t r = (j == f.length) ? f.L2[c + 1] - f.L2[c] : fm_block_rank(b, jj & 63u, c, s_lut);
+                nj = f.L2[c] + r;
+            }
+            j = nj; ++t;
+        }
+    }
+}
+
+// sampled row + steps -> text position -> candidate key ((read * 2 + strand) << 32 | window begin)
+__global__ void __launch_bounds__(MAP_THREADS)
+map_keys_kernel(const FMView f, const MapGeom g, const uint2* __restrict__ rows, const uint8_t* __restrict__ steps,
+                uint32_t n_hits, uint64_t* __restrict__ keys)
+{
     const uint32_t h = blockIdx.x * MAP_THREADS + threadIdx.x;
     if (h >= n_hits) return;
-    uint32_t lo = 0, hi = n_slots - 1u;                     // last slot whose first hit is <= h
-    while (lo < hi) { const uint32_t mid = (lo + hi + 1u) >> 1; if (__ldg(scan + mid) <= h) lo = mid; else hi = mid - 1u; }
+    const uint2 rec = rows[h];
+    const uint32_t pos = __ldg(f.ssa + (rec.x >> 4)) + steps[h];
     const uint32_t per_read = g.S * g.n_strands;
-    const uint32_t r = lo / per_read, rem = lo - r * per_read, strand = rem / g.S, k = rem - strand * g.S;
-    const uint32_t row = seeds[lo].x + (h - __ldg(scan + lo));
-    const uint2 w = fm_locate_walk_one(f, row, s_lut);
-    const uint32_t pos = __ldg(f.ssa + (w.x >> 4)) + w.y;
+    const uint32_t r = rec.y / per_read, rem = rec.y - r * per_read, strand = rem / g.S, k = rem - strand * g.S;
     const uint32_t o = k * g.interval;
     const uint32_t g_pos = pos > o ? pos - o : 0u;
     const uint32_t gb = g_pos > g.band / 2u ? g_pos - g.band / 2u : 0u;
     keys[h] = ((uint64_t)(r * 2u + strand) << 32) | gb;
 }
+
+// The hits of a read are contiguous (slots are in read order): one warp sorts them and keeps the distinct keys,
+// in place; the freed places are filled with MAP_DUP and dropped by the stream compaction that follows.
+#define MAP_DUP 0xFFFFFFFFFFFFFFFFull
+#define MAP_DEDUPE_WARPS 8
+__device__ __forceinline__ uint64_t map_shfl_xor64(uint64_t v, int m)
+{
+    return ((uint64_t)__shfl_xor_sync(0xFFFFFFFFu, (uint32_t)(v >> 32), m) << 32) | __shfl_xor_sync(0xFFFFFFFFu, (uint32_t)v, m);
+}
+__global__ void __launch_bounds__(MAP_DEDUPE_WARPS * 32)
+map_dedupe_kernel(const uint32_t* __restrict__ scan, uint32_t per_read, uint32_t n_reads, uint32_t cap, uint64_t* __restrict__ keys)
+{
+    extern __shared__ uint64_t s_keys[];                    // MAP_DEDUPE_WARPS * cap (only reads with more than 32 hits use it)
+    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
+    const uint32_t r = blockIdx.x * MAP_DEDUPE_WARPS + warp;
+    if (r >= n_reads) return;
+    const uint32_t lo = scan[r * per_read], cnt = scan[(r + 1u) * per_read] - lo;
+    if (cnt == 0) return;
+    if (cnt <= 32u)
+    {
+        uint64_t v = lane < cnt ? keys[lo + lane] : MAP_DUP;
+        #pragma unroll
+        for (int k = 2; k <= 32; k <<= 1)
+            #pragma unroll
+            for (int j = k >> 1; j > 0; j >>= 1)
+            {
+                const uint64_t o = map_shfl_xor64(v, j);
+                const bool keep_min = ((lane & k) == 0) == ((lane & j) == 0);
+                v = keep_min ? (v < o ? v : o) : (v > o ? v : o);
+            }
+        const uint32_t pl = __shfl_up_sync(0xFFFFFFFFu, (uint32_t)v, 1), ph = __shfl_up_sync(0xFFFFFFFFu, (uint32_t)(v >> 32), 1);
+        const bool keep = v != MAP_DUP && (lane == 0 || v != (((uint64_t)ph << 32) | pl));
+        const uint32_t m = __ballot_sync(0xFFFFFFFFu, keep);
+        const uint32_t kept = __popc(m);
+        if (keep) keys[lo + __popc(m & ((1u << lane) - 1u))] = v;
+        if (lane >= kept && lane < cnt) keys[lo + lane] = MAP_DUP;
+        return;
+    }
+    uint64_t* sk = s_keys + (size_t)warp * cap;
+    uint32_t N = 64; while (N < cnt) N <<= 1;                // cnt <= cap by construction
+    for (uint32_t i = lane; i < N; i += 32u) sk[i] = i < cnt ? keys[lo + i] : MAP_DUP;
+    __syncwarp();
+    for (uint32_t k = 2; k <= N; k <<= 1)
+        for (uint32_t j = k >> 1; j > 0; j >>= 1)
+        {
+            for (uint32_t i = lane; i < N; i += 32u)
+            {
+                const uint32_t p = i ^ j;
+                if (p > i)
+                {
+                    const uint64_t a = sk[i], b = sk[p];
+                    const bool up = (i & k) == 0;
+                    if ((a > b) == up) { sk[i] = b; sk[p] = a; }
+                }
+            }
+            __syncwarp();
+        }
+    uint32_t kept = 0;
+    for (uint32_t base = 0; base < N; base += 32u)
+    {
+        const uint32_t i = base + lane;
+        const uint64_t v = sk[i];
+        const bool keep = v != MAP_DUP && (i == 0 || v != sk[i - 1]);
+        const uint32_t m = __ballot_sync(0xFFFFFFFFu, keep);
+        if (keep) keys[lo + kept + __popc(m & ((1u << lane) - 1u))] = v;
+        kept += __popc(m);
+    }
+    for (uint32_t i = kept + lane; i < cnt; i += 32u) keys[lo + i] = MAP_DUP;
+}
+struct MapNotDup { __host__ __device__ bool operator()(uint64_t v) const { return v != MAP_DUP; } };
 
 // candidate j of a launch: a plain index into the sorted keys, or the best candidate of an aligned read
 __device__ __forceinline__ uint64_t map_key(const uint64_t* keys, const uint32_t* alist, const uint32_t* best, uint32_t j)
@@ -376,21 +493,48 @@ extern "C" int nvb_map_reads(nvb_ctx* ctx, const nvb_fmindex* fmi, const uint32_
             trace.mark(MapTrace::SEED);
             if (n_hits)
             {
-                // ---- locate + candidate keys, sorted and de-duplicated
+                // ---- locate + candidate keys, de-duplicated per read
+                uint2* rows; uint8_t* steps;
                 MAP_STAGE(S_KEYS_A, sizeof(uint64_t) * (size_t)n_hits, keys_a);
                 MAP_STAGE(S_KEYS_B, sizeof(uint64_t) * (size_t)n_hits, keys_b);
-                map_locate_kernel<<<map_grid(n_hits), MAP_THREADS, 0, s>>>(f, g, seeds, scan, n_slots, n_hits, keys_a);
+                MAP_STAGE(S_ROWS, sizeof(uint2) * (size_t)n_hits, rows);
+                MAP_STAGE(S_STEPS, (size_t)n_hits, steps);
+                map_expand_kernel<<<map_grid(n_slots), MAP_THREADS, 0, s>>>(seeds, scan, n_slots, rows);
+                NVB_LAUNCHED(ctx);
+                {
+                    const uint32_t want = map_grid(n_hits), persistent = (uint32_t)ctx->sm_count * 8u;
+                    map_walk_kernel<<<want < persistent ? want : persistent, MAP_THREADS, 0, s>>>(f, n_hits, rows, steps);
+                    NVB_LAUNCHED(ctx);
+                }
+                map_keys_kernel<<<map_grid(n_hits), MAP_THREADS, 0, s>>>(f, g, rows, steps, n_hits, keys_b);
                 NVB_LAUNCHED(ctx);
                 trace.mark(MapTrace::LOCATE);
-                const int end_bit = (int)(32u + bits_for(2ull * nr));
-                size_t sort_bytes = 0, uniq_bytes = 0;
-                cub::DeviceRadixSort::SortKeys(nullptr, sort_bytes, keys_a, keys_b, (int)n_hits, 0, end_bit, s);
-                cub::DeviceSelect::Unique(nullptr, uniq_bytes, keys_b, keys_a, d_num, (int)n_hits, s);
-                tmp_bytes = sort_bytes > uniq_bytes ? sort_bytes : uniq_bytes;
-                MAP_STAGE(S_CUB, tmp_bytes, tmp);
-                NVB_CUDA(ctx, cub::DeviceRadixSort::SortKeys(tmp, sort_bytes, keys_a, keys_b, (int)n_hits, 0, end_bit, s));
-                NVB_CUDA(ctx, cub::DeviceSelect::Unique(tmp, uniq_bytes, keys_b, keys_a, d_num, (int)n_hits, s));
-                ctx->launches += 2;
+                uint32_t cap = 64; while (cap < per_read * mp->max_hits) cap <<= 1;
+                size_t sel_bytes = 0;
+                if (cap <= 1024u)
+                {
+                    map_dedupe_kernel<<<(nr + MAP_DEDUPE_WARPS - 1) / MAP_DEDUPE_WARPS, MAP_DEDUPE_WARPS * 32, MAP_DEDUPE_WARPS * cap * sizeof(uint64_t), s>>>(
+                        scan, per_read, nr, cap, keys_b);
+                    NVB_LAUNCHED(ctx);
+                    cub::DeviceSelect::If(nullptr, sel_bytes, keys_b, keys_a, d_num, (int)n_hits, MapNotDup(), s);
+                    MAP_STAGE(S_CUB, sel_bytes, tmp);
+                    NVB_CUDA(ctx, cub::DeviceSelect::If(tmp, sel_bytes, keys_b, keys_a, d_num, (int)n_hits, MapNotDup(), s));
+                    ctx->launches++;
+                }
+                else
+                {
+                    // very many hits per read: global radix sort + unique
+                    const int end_bit = (int)(32u + bits_for(2ull * nr));
+                    size_t sort_bytes = 0, uniq_bytes = 0;
+                    uint64_t* keys_c = (uint64_t*)rows;          // rows are consumed
+                    cub::DeviceRadixSort::SortKeys(nullptr, sort_bytes, keys_b, keys_c, (int)n_hits, 0, end_bit, s);
+                    cub::DeviceSelect::Unique(nullptr, uniq_bytes, keys_c, keys_a, d_num, (int)n_hits, s);
+                    tmp_bytes = sort_bytes > uniq_bytes ? sort_bytes : uniq_bytes;
+                    MAP_STAGE(S_CUB, tmp_bytes, tmp);
+                    NVB_CUDA(ctx, cub::DeviceRadixSort::SortKeys(tmp, sort_bytes, keys_b, keys_c, (int)n_hits, 0, end_bit, s));
+                    NVB_CUDA(ctx, cub::DeviceSelect::Unique(tmp, uniq_bytes, keys_c, keys_a, d_num, (int)n_hits, s));
+                    ctx->launches += 2;
+                }
                 NVB_CUDA(ctx, cudaMemcpyAsync(&n_cand, d_num, sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
                 NVB_CUDA(ctx, cudaStreamSynchronize(s));
                 trace.mark(MapTrace::SORT);

@@ -35,6 +35,7 @@ CASES = [
     (po.SW, (1, -2, -3, -3), 7, 2, 0, 1, -1000),
     (po.GOTOH, (2, -3, -6, -2), 15, 8, 6, 0, 0),
     (po.GOTOH, (0, -5, -8, -3), 12, 3, 0, 1, -60),      # a band only the int32 kernels take
+    (po.ED, (0, -1, -1, -1), 15, 40, 0, 1, -20),         # more than 1024 possible hits per read: global sort path
 ]
 
 
