@@ -301,6 +301,16 @@ def run_b200(args):
         del ranges_k
         fmi.drop_ktab()
 
+        # ---- locate(fmi, row) of as many uniformly random SA rows (fmindex_inl.h:290-304): informational
+        lrows = torch.randint(0, fmi.length + 1, (nq,), device=dev, dtype=torch.int64).to(torch.int32)
+        lpos = torch.empty(nq, dtype=torch.int32, device=dev)
+        def _locate():
+            check(L.nvb_fm_locate(ctx.h, ctypes.byref(fc), lrows.data_ptr(), nq, lpos.data_ptr(), current_stream_ptr()), ctx.h)
+        tl = time_steps(_locate, max(3, args.steps // 2), 2, flush)
+        l_ms = max_over_ranks(sum(tl) / len(tl))
+        out["fm"]["locate"] = dict(value=world * nq / (l_ms * 1e-3), unit="locates/s", ms_per_step=l_ms, rows=nq)
+        del lrows, lpos
+
         # ---- e2e: host buffers (pinned) through the C-ABI *_host call: H2D + kernel + D2H per step
         hs = torch.empty(qsym.numel(), dtype=torch.uint8).pin_memory(); hs.copy_(qsym)
         ho = torch.empty(qoff.numel(), dtype=torch.int32).pin_memory(); ho.copy_(qoff)
@@ -512,7 +522,7 @@ def run_b200(args):
                             "l2": "flushed (256 MiB write) between timed steps, outside the event-timed region",
                             "index_build_s": round(fm["build_s"], 2),
                             "e2e_packed4": fm.get("e2e_packed4"),
-                            "value_with_kmer_jump_table": fm.get("ktab10")})
+                            "value_with_kmer_jump_table": fm.get("ktab10"), "locate": fm.get("locate")})
         if alg_per_q:
             ach = alg_per_q * args.queries / (fm["kernel_ms"] * 1e-3) / 1e9
             line["roofline"] = {"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,

@@ -142,3 +142,41 @@ __device__ __forceinline__ uint2 fm_locate_walk_one(const FMView& f, uint32_t j,
     }
     return make_uint2(j, t);
 }
+
+// Many LF-walks per thread, load-balanced: walks take 0..15 steps, so a thread owns the strided list of walks
+// first, first + stride, ... and starts its next one as soon as one ends; the warp vote keeps the loop converged.
+//   fetch(h) -> SA row of walk h ;  emit(h, sampled_row, steps)
+template <typename Fetch, typename Emit>
+__device__ __forceinline__ void fm_walk_balanced(const FMView& f, uint32_t n, uint32_t first, uint32_t stride, const uint2* lut,
+                                                 Fetch fetch, Emit emit)
+{
+    uint32_t h = first;
+    bool alive = h < n;
+    uint32_t j = alive ? fetch(h) : 0u, t = 0;
+    uint32_t hn = h + stride;
+    uint32_t jn = (alive && hn < n) ? fetch(hn) : 0u;          // the next walk's row is fetched one walk ahead
+    while (__any_sync(0xFFFFFFFFu, alive))
+    {
+        if (alive && (j & 15u) == 0u)
+        {
+            emit(h, j, t);
+            h = hn; j = jn; t = 0;
+            alive = h < n;
+            hn = h + stride;
+            jn = (alive && hn < n) ? fetch(hn) : 0u;
+        }
+        if (alive && (j & 15u) != 0u)
+        {
+            uint32_t nj = 0;                                    // j == primary -> 0 (fmindex_inl.h:380-383)
+            if (j != f.primary)
+            {
+                const uint32_t jj = j < f.primary ? j : j - 1u;             // fmindex_inl.h:384
+                const FMBlock b = fm_load_block(f.blk, jj >> 6);
+                const uint32_t c = fm_bwt_symbol(b, jj & 63u);
+                const uint32_t r = (j == f.length) ? f.L2[c + 1] - f.L2[c] : fm_block_rank(b, jj & 63u, c, lut);
+                nj = f.L2[c] + r;
+            }
+            j = nj; ++t;
+        }
+    }
+}

@@ -125,10 +125,9 @@ fm_locate_kernel(const FMView f, const uint32_t* __restrict__ rows, uint32_t n, 
 {
     __shared__ uint2 s_lut[FM_LUT_ENTRIES];
     fm_lut_init(s_lut);
-    const uint32_t tid = blockIdx.x * FM_THREADS + threadIdx.x;
-    if (tid >= n) return;
-    const uint2 w = fm_locate_walk_one(f, rows[tid], s_lut);
-    pos[tid] = __ldg(f.ssa + (w.x >> 4)) + w.y;
+    fm_walk_balanced(f, n, blockIdx.x * FM_THREADS + threadIdx.x, gridDim.x * FM_THREADS, s_lut,
+                     [&](uint32_t h) { return __ldg(rows + h); },
+                     [&](uint32_t h, uint32_t j, uint32_t t) { pos[h] = __ldg(f.ssa + (j >> 4)) + t; });
 }
 
 __global__ void __launch_bounds__(FM_THREADS)
@@ -136,9 +135,9 @@ fm_locate_walk_kernel(const FMView f, const uint32_t* __restrict__ rows, uint32_
 {
     __shared__ uint2 s_lut[FM_LUT_ENTRIES];
     fm_lut_init(s_lut);
-    const uint32_t tid = blockIdx.x * FM_THREADS + threadIdx.x;
-    if (tid >= n) return;
-    *(uint2*)(walk + 2 * (size_t)tid) = fm_locate_walk_one(f, rows[tid], s_lut);
+    fm_walk_balanced(f, n, blockIdx.x * FM_THREADS + threadIdx.x, gridDim.x * FM_THREADS, s_lut,
+                     [&](uint32_t h) { return __ldg(rows + h); },
+                     [&](uint32_t h, uint32_t j, uint32_t t) { *(uint2*)(walk + 2 * (size_t)h) = make_uint2(j, t); });
 }
 
 __global__ void __launch_bounds__(FM_THREADS)
@@ -197,6 +196,8 @@ static int check_fmi(const nvb_fmindex* f, bool need_ssa)
     return NVB_OK;
 }
 static inline uint32_t grid_for(uint32_t n) { return (n + FM_THREADS - 1) / FM_THREADS; }
+// the load-balanced walks run on a grid that just fills the device (8 CTAs of 256 threads per SM)
+static inline uint32_t walk_grid(const nvb_ctx* ctx, uint32_t n) { const uint32_t g = grid_for(n), p = (uint32_t)ctx->sm_count * 8u; return g < p ? g : p; }
 
 template <bool FROM>
 static int fm_match_launch(nvb_ctx* ctx, const nvb_fmindex* fmi, nvb_string_set queries, uint32_t* ranges,
@@ -293,7 +294,7 @@ extern "C" int nvb_fm_locate(nvb_ctx* ctx, const nvb_fmindex* fmi, const uint32_
     int rc = check_fmi(fmi, true); if (rc) return rc;
     if (n == 0) return NVB_OK;
     if (!rows || !pos) return NVB_ERR_ARG;
-    fm_locate_kernel<<<grid_for(n), FM_THREADS, 0, (cudaStream_t)stream>>>(make_view(fmi), rows, n, pos);
+    fm_locate_kernel<<<walk_grid(ctx, n), FM_THREADS, 0, (cudaStream_t)stream>>>(make_view(fmi), rows, n, pos);
     NVB_LAUNCHED(ctx);
     return NVB_OK;
 }
@@ -304,7 +305,7 @@ extern "C" int nvb_fm_locate_walk(nvb_ctx* ctx, const nvb_fmindex* fmi, const ui
     int rc = check_fmi(fmi, false); if (rc) return rc;
     if (n == 0) return NVB_OK;
     if (!rows || !walk) return NVB_ERR_ARG;
-    fm_locate_walk_kernel<<<grid_for(n), FM_THREADS, 0, (cudaStream_t)stream>>>(make_view(fmi), rows, n, walk);
+    fm_locate_walk_kernel<<<walk_grid(ctx, n), FM_THREADS, 0, (cudaStream_t)stream>>>(make_view(fmi), rows, n, walk);
     NVB_LAUNCHED(ctx);
     return NVB_OK;
 }

@@ -106,36 +106,9 @@ map_walk_kernel(const FMView f, uint32_t n_hits, uint2* __restrict__ rows, uint8
 {
     __shared__ uint2 s_lut[FM_LUT_ENTRIES];
     fm_lut_init(s_lut);
-    const uint32_t stride = gridDim.x * MAP_THREADS;
-    uint32_t h = blockIdx.x * MAP_THREADS + threadIdx.x;
-    bool alive = h < n_hits;                               // whole warps stay in the loop: it reconverges at the vote
-    uint32_t j = alive ? rows[h].x : 0u, t = 0;
-    uint32_t hn = h + stride;
-    uint32_t jn = hn < n_hits ? rows[hn].x : 0u;          // the next walk's row is fetched one walk ahead
-    while (__any_sync(0xFFFFFFFFu, alive))
-    {
-        if (alive && (j & 15u) == 0u)
-        {
-            rows[h].x = j; steps[h] = (uint8_t)t;
-            h = hn; j = jn; t = 0;
-            alive = h < n_hits;
-            hn = h + stride;
-            jn = hn < n_hits ? rows[hn].x : 0u;
-        }
-        if (alive && (j & 15u) != 0u)
-        {
-            uint32_t nj = 0;
-            if (j != f.primary)
-            {
-                const uint32_t jj = j < f.primary ? j : j - 1u;
-                const FMBlock b = fm_load_block(f.blk, jj >> 6);
-                const uint32_t c = fm_bwt_symbol(b, jj & 63u);
-                const uint32_t r = (j == f.length) ? f.L2[c + 1] - f.L2[c] : fm_block_rank(b, jj & 63u, c, s_lut);
-                nj = f.L2[c] + r;
-            }
-            j = nj; ++t;
-        }
-    }
+    fm_walk_balanced(f, n_hits, blockIdx.x * MAP_THREADS + threadIdx.x, gridDim.x * MAP_THREADS, s_lut,
+                     [&](uint32_t h) { return rows[h].x; },
+                     [&](uint32_t h, uint32_t j, uint32_t t) { rows[h].x = j; steps[h] = (uint8_t)t; });
 }
 
 // sampled row + steps -> text position -> candidate key ((read * 2 + strand) << 32 | window begin)
