@@ -194,6 +194,10 @@ int nvb_fm_filter_locate(nvb_ctx* ctx, const nvb_fmindex* fmi, const uint32_t* r
  * PackedStream<uint32*,uint8,BITS,true>: nvbio/io/sequence/sequence.h, nvbio/basic/packedstream.h) */
 int nvb_fm_match_host_packed(nvb_ctx* ctx, const nvb_fmindex* fmi_d, const void* words_h, uint32_t bits,
                              const uint32_t* offsets_h, uint32_t count, uint32_t* ranges_h);
+/* queries of one length (seeds): query i = symbols [i * query_len, (i + 1) * query_len) of the 8-bit or packed
+ * (4 / 2 bits, big-endian words) host stream; the offsets never cross PCIe */
+int nvb_fm_match_host_fixed(nvb_ctx* ctx, const nvb_fmindex* fmi_d, const void* symbols_h, uint32_t bits,
+                            uint32_t query_len, uint32_t count, uint32_t* ranges_h);
 int nvb_fm_locate_host(nvb_ctx* ctx, const nvb_fmindex* fmi_d, const uint32_t* rows_h, uint32_t n,
                        uint32_t* pos_h);
 

@@ -50,6 +50,7 @@ extern "C" void nvb_ctx_destroy(nvb_ctx* c)
     for (int i = 0; i < NVB_STAGE_SLOTS; ++i) if (c->d_stage[i]) cudaFree(c->d_stage[i]);
     if (c->d_worklist) cudaFree(c->d_worklist);
     for (int i = 0; i < 2; ++i) if (c->aux[i]) { cudaStreamSynchronize(c->aux[i]); cudaStreamDestroy(c->aux[i]); }
+    for (int i = 0; i < 12; ++i) if (c->host_ev[i]) cudaEventDestroy(c->host_ev[i]);
     cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -266,57 +267,104 @@ extern "C" int nvb_fmindex_pin_l2(nvb_ctx* ctx, const nvb_fmindex* d, size_t byt
 // host-buffer forms
 // ---------------------------------------------------------------------------------------------
 #define NVB_HOST_CHUNK (1u << 19)   // queries per pipelined chunk of the host entry points
+#define NVB_HOST_SETS  4            // buffer sets in flight
+#define NVB_HOST_SLOT0 33           // stage slots 33 .. 33 + 3 * NVB_HOST_SETS - 1
 
-// Host buffers in, host buffers out. Large batches are cut into chunks that alternate between two streams, so that
-// the H2D copy of one chunk, the kernel of another and the D2H copy of a third overlap (PCIe is full duplex):
-// the call costs about max(H2D, D2H) instead of their sum. Pinned host memory (nvb_host_alloc) is needed for that.
+__global__ void fixed_offsets_kernel(uint32_t* off, uint32_t first, uint32_t n, uint32_t len)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) off[i] = (first + i) * len;
+}
+
+// Host buffers in, host buffers out, as a three-stage pipeline over chunks of the batch: copy-in stream (H2D of the
+// symbols and offsets of chunk k), compute stream (the kernel), copy-out stream (D2H of the ranges), chained by
+// events, NVB_HOST_SETS buffer sets in flight. PCIe is full duplex, so the call costs about max(H2D, D2H) instead
+// of their sum (NVB_HOST_CHUNK / NVB_HOST_RAMPS in the environment tune the chunking). Pinned host
+// memory (nvb_host_alloc) is needed for the overlap. offsets_h == NULL means `fixed_len` symbols per query
+// (offsets are then generated on the device and never cross PCIe).
 static int fm_match_host_impl(nvb_ctx* ctx, const nvb_fmindex* fmi_d, const uint8_t* symbols_h, uint32_t bits,
-                              const uint32_t* offsets_h, uint32_t count, uint32_t* ranges_h)
+                              const uint32_t* offsets_h, uint32_t fixed_len, uint32_t count, uint32_t* ranges_h)
 {
     if (!ctx || !fmi_d) return NVB_ERR_ARG;
     if (count == 0) return NVB_OK;
-    if (!symbols_h || !offsets_h || !ranges_h) return NVB_ERR_ARG;
+    if (!symbols_h || !ranges_h || (!offsets_h && fixed_len == 0)) return NVB_ERR_ARG;
     if (bits != 8 && bits != 4 && bits != 2) return NVB_ERR_ARG;
+    if (!offsets_h && (uint64_t)count * fixed_len > 0xFFFFFFFFull) return NVB_ERR_ARG;
     NVB_CUDA(ctx, cudaSetDevice(ctx->device));
     int rc;
     const uint32_t spw = 32u / bits;                                  // symbols per 32-bit word of a packed stream
     // bytes [b0, b1) of the host symbol array that hold symbols [s0, s1) (whole words for packed streams)
     #define SPAN_BEGIN(s0) (bits == 8 ? (size_t)(s0) : (size_t)((s0) / spw) * 4u)
     #define SPAN_END(s1)   (bits == 8 ? (size_t)(s1) : (size_t)(((s1) + spw - 1) / spw) * 4u)
-    const uint32_t chunk = count > NVB_HOST_CHUNK ? NVB_HOST_CHUNK : count;
-    const uint32_t n_chunks = (count + chunk - 1) / chunk;
-    const int n_sets = n_chunks > 1 ? 2 : 1;
-    size_t max_bytes = 0;
+    #define OFFSET_OF(i)   (offsets_h ? offsets_h[i] : (uint32_t)(i) * fixed_len)
+    // chunk schedule: 1/4, 1/2, 1, 1, ..., 1, 1/2, 1/4 of NVB_HOST_CHUNK
+    std::vector<uint32_t> cut; cut.push_back(0);
+    {
+        static uint32_t env_chunk = 0, env_ramps = 0;   // ramped first/last chunks measured no gain on B200 + PCIe 5 (tools/host_probe.py)
+        if (!env_chunk)
+        {
+            const char* e = getenv("NVB_HOST_CHUNK"); env_chunk = e ? (uint32_t)atoi(e) : NVB_HOST_CHUNK;
+            if (env_chunk < 4096u) env_chunk = NVB_HOST_CHUNK;
+            const char* r = getenv("NVB_HOST_RAMPS"); if (r) env_ramps = (uint32_t)atoi(r);
+        }
+        const uint32_t C = env_chunk;
+        const bool ramps = env_ramps && count >= 4u * C;
+        uint32_t done = 0;
+        if (ramps) { done += C / 4; cut.push_back(done); done += C / 2; cut.push_back(done); }
+        const uint32_t mid = count - done - (ramps ? C / 2 + C / 4 : 0u);
+        const uint32_t n_mid = (mid + C - 1) / C, each = (mid + n_mid - 1) / n_mid;
+        for (uint32_t i = 0, left = mid; i < n_mid; ++i) { const uint32_t c = left < each ? left : each; done += c; left -= c; cut.push_back(done); }
+        if (ramps) { done += C / 2; cut.push_back(done); done += C / 4; cut.push_back(done); }
+    }
+    const uint32_t n_chunks = (uint32_t)cut.size() - 1;
+    size_t max_bytes = 0; uint32_t max_cnt = 0;
     for (uint32_t k = 0; k < n_chunks; ++k)
     {
-        const uint32_t c0 = k * chunk, c1 = c0 + chunk < count ? c0 + chunk : count;
-        const size_t nb = SPAN_END(offsets_h[c1]) - SPAN_BEGIN(offsets_h[c0]);
+        const size_t nb = SPAN_END(OFFSET_OF(cut[k + 1])) - SPAN_BEGIN(OFFSET_OF(cut[k]));
         if (nb > max_bytes) max_bytes = nb;
+        if (cut[k + 1] - cut[k] > max_cnt) max_cnt = cut[k + 1] - cut[k];
     }
-    void *d_sym[2], *d_off[2], *d_rng[2];
+    const int n_sets = n_chunks < NVB_HOST_SETS ? (int)n_chunks : NVB_HOST_SETS;
+    void *d_sym[NVB_HOST_SETS], *d_off[NVB_HOST_SETS], *d_rng[NVB_HOST_SETS];
     for (int b = 0; b < n_sets; ++b)
     {
-        if ((rc = nvb_stage(ctx, 3 * b + 0, max_bytes + 32, &d_sym[b]))) return rc;
-        if ((rc = nvb_stage(ctx, 3 * b + 1, sizeof(uint32_t) * ((size_t)chunk + 1), &d_off[b]))) return rc;
-        if ((rc = nvb_stage(ctx, 3 * b + 2, sizeof(uint32_t) * 2 * (size_t)chunk, &d_rng[b]))) return rc;
+        if ((rc = nvb_stage(ctx, NVB_HOST_SLOT0 + 3 * b + 0, max_bytes + 32, &d_sym[b]))) return rc;
+        if ((rc = nvb_stage(ctx, NVB_HOST_SLOT0 + 3 * b + 1, sizeof(uint32_t) * ((size_t)max_cnt + 1), &d_off[b]))) return rc;
+        if ((rc = nvb_stage(ctx, NVB_HOST_SLOT0 + 3 * b + 2, sizeof(uint32_t) * 2 * (size_t)max_cnt, &d_rng[b]))) return rc;
     }
+    if (!ctx->host_ev[0])
+        for (int i = 0; i < 3 * NVB_HOST_SETS; ++i) NVB_CUDA(ctx, cudaEventCreateWithFlags(&ctx->host_ev[i], cudaEventDisableTiming));
+    cudaStream_t s_in = ctx->aux[0], s_k = ctx->stream, s_out = ctx->aux[1];
     for (uint32_t k = 0; k < n_chunks; ++k)
     {
-        const int b = (int)(k & 1u) % n_sets;
-        cudaStream_t s = n_sets > 1 ? ctx->aux[b] : ctx->stream;
-        const uint32_t c0 = k * chunk, c1 = c0 + chunk < count ? c0 + chunk : count, cnt = c1 - c0;
-        const size_t b0 = SPAN_BEGIN(offsets_h[c0]), nb = SPAN_END(offsets_h[c1]) - b0;
-        NVB_CUDA(ctx, cudaMemcpyAsync(d_sym[b], symbols_h + b0, nb, cudaMemcpyHostToDevice, s));
-        NVB_CUDA(ctx, cudaMemcpyAsync(d_off[b], offsets_h + c0, sizeof(uint32_t) * ((size_t)cnt + 1), cudaMemcpyHostToDevice, s));
+        const int b = (int)(k % (uint32_t)n_sets);
+        cudaEvent_t ev_in = ctx->host_ev[3 * b], ev_k = ctx->host_ev[3 * b + 1], ev_out = ctx->host_ev[3 * b + 2];
+        const uint32_t c0 = cut[k], c1 = cut[k + 1], cnt = c1 - c0;
+        const size_t b0 = SPAN_BEGIN(OFFSET_OF(c0)), nb = SPAN_END(OFFSET_OF(c1)) - b0;
+        if (k >= (uint32_t)n_sets) NVB_CUDA(ctx, cudaStreamWaitEvent(s_in, ev_out, 0));       // the set's previous ranges have left
+        NVB_CUDA(ctx, cudaMemcpyAsync(d_sym[b], symbols_h + b0, nb, cudaMemcpyHostToDevice, s_in));
+        if (offsets_h) NVB_CUDA(ctx, cudaMemcpyAsync(d_off[b], offsets_h + c0, sizeof(uint32_t) * ((size_t)cnt + 1), cudaMemcpyHostToDevice, s_in));
+        NVB_CUDA(ctx, cudaEventRecord(ev_in, s_in));
+        NVB_CUDA(ctx, cudaStreamWaitEvent(s_k, ev_in, 0));
+        if (!offsets_h)
+        {
+            fixed_offsets_kernel<<<(cnt + 1 + 255) / 256, 256, 0, s_k>>>((uint32_t*)d_off[b], c0, cnt + 1, fixed_len);
+            NVB_LAUNCHED(ctx);
+        }
         // the chunk keeps its absolute offsets: rebase the symbol pointer instead
         nvb_string_set q; q.symbols = (const uint8_t*)d_sym[b] - b0; q.offsets = (const uint32_t*)d_off[b]; q.count = cnt; q.bits = bits;
-        if ((rc = nvb_fm_match(ctx, fmi_d, q, (uint32_t*)d_rng[b], s))) return rc;
-        NVB_CUDA(ctx, cudaMemcpyAsync(ranges_h + 2 * (size_t)c0, d_rng[b], sizeof(uint32_t) * 2 * (size_t)cnt, cudaMemcpyDeviceToHost, s));
+        if ((rc = nvb_fm_match(ctx, fmi_d, q, (uint32_t*)d_rng[b], s_k))) return rc;
+        NVB_CUDA(ctx, cudaEventRecord(ev_k, s_k));
+        NVB_CUDA(ctx, cudaStreamWaitEvent(s_out, ev_k, 0));
+        NVB_CUDA(ctx, cudaMemcpyAsync(ranges_h + 2 * (size_t)c0, d_rng[b], sizeof(uint32_t) * 2 * (size_t)cnt, cudaMemcpyDeviceToHost, s_out));
+        NVB_CUDA(ctx, cudaEventRecord(ev_out, s_out));
     }
     #undef SPAN_BEGIN
     #undef SPAN_END
-    if (n_sets > 1) { NVB_CUDA(ctx, cudaStreamSynchronize(ctx->aux[0])); NVB_CUDA(ctx, cudaStreamSynchronize(ctx->aux[1])); }
-    else NVB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    #undef OFFSET_OF
+    NVB_CUDA(ctx, cudaStreamSynchronize(s_out));
+    NVB_CUDA(ctx, cudaStreamSynchronize(s_in));
+    NVB_CUDA(ctx, cudaStreamSynchronize(s_k));
     return NVB_OK;
 }
 
@@ -325,13 +373,21 @@ static int fm_match_host_impl(nvb_ctx* ctx, const nvb_fmindex* fmi_d, const uint
 // the call costs about max(H2D, D2H) instead of their sum. Pinned host memory (nvb_host_alloc) is needed for that.
 extern "C" int nvb_fm_match_host(nvb_ctx* ctx, const nvb_fmindex* fmi_d, const uint8_t* symbols_h,
                                  const uint32_t* offsets_h, uint32_t count, uint32_t* ranges_h)
-{ return fm_match_host_impl(ctx, fmi_d, symbols_h, 8, offsets_h, count, ranges_h); }
+{ return fm_match_host_impl(ctx, fmi_d, symbols_h, 8, offsets_h, 0, count, ranges_h); }
 
 // the same over a packed host stream (bits = 4 or 2, big-endian 32-bit words: the layout of the reference's
 // io::SequenceData read streams, nvbio/io/sequence/sequence.h), which moves 2x / 4x fewer bytes over PCIe
 extern "C" int nvb_fm_match_host_packed(nvb_ctx* ctx, const nvb_fmindex* fmi_d, const void* words_h, uint32_t bits,
                                         const uint32_t* offsets_h, uint32_t count, uint32_t* ranges_h)
-{ return fm_match_host_impl(ctx, fmi_d, (const uint8_t*)words_h, bits, offsets_h, count, ranges_h); }
+{ return fm_match_host_impl(ctx, fmi_d, (const uint8_t*)words_h, bits, offsets_h, 0, count, ranges_h); }
+
+// queries of one length (seeds): no offsets cross PCIe. bits = 8, 4 or 2; query i = symbols [i * len, (i + 1) * len)
+extern "C" int nvb_fm_match_host_fixed(nvb_ctx* ctx, const nvb_fmindex* fmi_d, const void* symbols_h, uint32_t bits,
+                                       uint32_t query_len, uint32_t count, uint32_t* ranges_h)
+{
+    if (query_len == 0) return NVB_ERR_ARG;
+    return fm_match_host_impl(ctx, fmi_d, (const uint8_t*)symbols_h, bits, nullptr, query_len, count, ranges_h);
+}
 
 extern "C" int nvb_fm_locate_host(nvb_ctx* ctx, const nvb_fmindex* fmi_d, const uint32_t* rows_h, uint32_t n, uint32_t* pos_h)
 {

@@ -10,7 +10,7 @@
 #endif
 
 #define NVB_SM_COUNT 148
-#define NVB_STAGE_SLOTS 40
+#define NVB_STAGE_SLOTS 48
 
 struct nvb_ctx
 {
@@ -27,6 +27,7 @@ struct nvb_ctx
     uint32_t*    d_worklist;
     size_t       d_worklist_cap;
     int          sm_count;
+    cudaEvent_t  host_ev[12];  // event chain of the pipelined *_host entry points (3 per buffer set)
     cudaStream_t aux[2];       // the *_host entry points pipeline chunks over these (H2D of one chunk under the kernel / D2H of another)
 };
 

@@ -30,11 +30,12 @@ fm_match_kernel(const FMView f, const StrSet q, uint32_t* __restrict__ ranges)
     const uint32_t tid   = first + threadIdx.x;
     const uint32_t last  = min(first + FM_THREADS, q.count);
 
-    // stage the CTA's symbol span (bits == 8 only; packed sets are read in place)
-    const uint32_t span_begin = q.off[first];
-    const uint32_t span_end   = q.off[last];
+    // stage the CTA's symbol span: bytes for 8-bit sets, whole 32-bit words for packed sets
+    constexpr uint32_t SPW = 32u / BITS;                               // symbols per word of a packed stream
+    const uint32_t span_begin = BITS == 8 ? q.off[first] : (q.off[first] / SPW) * 4u;               // in bytes
+    const uint32_t span_end   = BITS == 8 ? q.off[last]  : ((q.off[last] + SPW - 1u) / SPW) * 4u;
     const uint32_t span_len   = span_end - span_begin;
-    const bool staged = (BITS == 8) && (span_len <= FM_STAGE_BYTES - 32u);
+    const bool staged = span_len <= FM_STAGE_BYTES - 32u;
     uint32_t skew = 0;
     if (staged)
     {
@@ -47,6 +48,14 @@ fm_match_kernel(const FMView f, const StrSet q, uint32_t* __restrict__ ranges)
         for (uint32_t i = threadIdx.x; i < n16; i += FM_THREADS) s[i] = __ldg(g + i);
         __syncthreads();
     }
+    // symbol at absolute symbol index a of the set
+    auto symbol = [&](uint32_t a) -> uint32_t
+    {
+        if (!staged) return sym_at<BITS>(q.sym, a);
+        if (BITS == 8) return (uint32_t)s_sym[skew + (a - span_begin)];
+        const uint32_t w = *(const uint32_t*)(s_sym + skew + ((a / SPW) * 4u - span_begin));
+        return BITS == 4 ? (w >> (28u - 4u * (a & 7u))) & 15u : (w >> (30u - 2u * (a & 15u))) & 3u;
+    };
     if (tid >= q.count) return;
 
     const uint32_t beg = q.off[tid];
@@ -64,15 +73,14 @@ fm_match_kernel(const FMView f, const StrSet q, uint32_t* __restrict__ ranges)
         uint32_t idx = 0, bad = 0;
         for (uint32_t j = len - f.ktab_k; j < len; ++j)
         {
-            const uint32_t c = staged ? (uint32_t)s_sym[skew + (beg - span_begin) + j] : sym_at<BITS>(q.sym, beg + j);
+            const uint32_t c = symbol(beg + j);
             bad |= c; idx = idx * 4u + (c & 3u);
         }
         if (bad <= 3u) { const uint2 r = __ldg(f.ktab + idx); x = r.x; y = r.y; i -= (int32_t)f.ktab_k; }
     }
     for (; i >= 0 && x <= y; --i)
     {
-        const uint32_t c = staged ? (uint32_t)s_sym[skew + (beg - span_begin) + (uint32_t)i]
-                                  : sym_at<BITS>(q.sym, beg + (uint32_t)i);
+        const uint32_t c = symbol(beg + (uint32_t)i);
         if (c > 3u) { x = 1; y = 0; break; }
         const uint2 r = fm_rank2(f, x - 1u, y, c, s_lut);
         x = f.L2[c] + r.x + 1u;

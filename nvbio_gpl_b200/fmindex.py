@@ -309,6 +309,16 @@ def match_host(fmi, symbols_h, offsets_h, ranges_h=None, ctx=None, bits=8):
     return ranges_h
 
 
+def match_host_fixed(fmi, symbols_h, query_len, count, ranges_h=None, ctx=None, bits=8):
+    """queries of one length (seeds): query i = symbols [i * query_len, (i + 1) * query_len); no offsets cross PCIe"""
+    ctx = _ctx(fmi.bwt_occ, ctx)
+    if ranges_h is None:
+        ranges_h = np.empty((count, 2), dtype=np.uint32)
+    f = fmi.c()
+    check(lib().nvb_fm_match_host_fixed(ctx.h, C.byref(f), symbols_h.ctypes.data, bits, query_len, count, ranges_h.ctypes.data), ctx.h)
+    return ranges_h
+
+
 def pack_symbols(symbols, bits):
     """uint8 symbols -> big-endian packed uint32 words (PackedStream<uint32*, uint8, BITS, true>: symbol 0 in the top bits)"""
     spw = 32 // bits

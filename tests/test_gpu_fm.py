@@ -130,6 +130,29 @@ def test_host_entry_packed_and_chunked(oracle):
     assert (nvb.match_host(fmi, nvb.pack_symbols(Q2, 2), qo, bits=2) == oracle.fm_match(oidx, Q2, qo)).all()
 
 
+def test_host_entry_fixed_length(oracle):
+    """queries of one length through nvb_fm_match_host_fixed (no offsets over PCIe), 8-bit and packed, batch long
+    enough for the ramped chunk schedule and every buffer set of the three-stage pipeline"""
+    rng = np.random.default_rng(32)
+    text = rng.integers(0, 4, 80000).astype(np.uint8)
+    fmi, oidx = gu.fm_index_pair(oracle, text)
+    n, L = 2_400_007, 20
+    pos = rng.integers(0, len(text) - L, n)
+    Q = text[(pos[:, None] + np.arange(L)[None, :])].copy()
+    junk = rng.random(n) < 0.2
+    Q[junk] = rng.integers(0, 4, (int(junk.sum()), L))
+    Q[rng.integers(0, n, 2000), rng.integers(0, L, 2000)] = 4
+    Q = Q.reshape(-1)
+    qo = (np.arange(n + 1, dtype=np.int64) * L).astype(np.uint32)
+    want = oracle.fm_match(oidx, Q, qo)
+    assert (nvb.match_host_fixed(fmi, Q, L, n) == want).all()
+    assert (nvb.match_host_fixed(fmi, nvb.pack_symbols(Q, 4), L, n, bits=4) == want).all()
+    assert (nvb.match_host(fmi, Q, qo) == want).all()
+    Q2 = Q & 3
+    assert (nvb.match_host_fixed(fmi, nvb.pack_symbols(Q2, 2), L, n, bits=2) == oracle.fm_match(oidx, Q2, qo)).all()
+    assert (nvb.match_host_fixed(fmi, Q[:L * 5], L, 5) == want[:5]).all()
+
+
 def test_fmindex_filter_rank_and_locate(oracle):
     """FMIndexFilter (filter_inl.h:75-110,261-393): scanned range sizes and (position, string id) hits, checked against the
     composition of the oracle's match / locate with the reference's slot arithmetic"""
