@@ -416,21 +416,24 @@ def run_b200(args):
                           aligned_frac=mstats["aligned"] / nr, genome=int(genome.numel()),
                           params="20-mer seeds every 10 bp on both strands (10-mer jump table), <= 4 rows per seed, banded (15) Gotoh (0,-5,-8,-3) "
                                  "SEMI_GLOBAL, min score -90, traceback of the best window")
-        # e2e: pinned host reads in, hits + op lists out
+        # e2e: pinned host reads in; hits + CIGARs out (the SAM-facing result), and once with the raw op lists for the parity check
         hr_sym = torch.empty(rsym.numel(), dtype=torch.uint8).pin_memory(); hr_sym.copy_(rsym)
         hr_off = torch.empty(roff.numel(), dtype=torch.int32).pin_memory(); hr_off.copy_(roff)
         hh = torch.empty((nr, 6), dtype=torch.int32).pin_memory()
         hops = torch.empty((nr, stride), dtype=torch.uint8).pin_memory()
+        hcig = torch.empty((nr, 16), dtype=torch.int16).pin_memory()
         hh_n = hh.numpy().view(np.uint32).reshape(-1).view(nvb.HIT_DT)
         args_h = (fmi, words, hr_sym.numpy(), hr_off.numpy().view(np.uint32), mparams)
-        nvb.map_reads_host(*args_h, hits_h=hh_n, ops_h=hops.numpy(), ctx=ctx)
+        nvb.map_reads_host(*args_h, hits_h=hh_n, cigar_h=hcig.numpy().view(np.uint16), max_read_len=RL, ctx=ctx)
         barrier()
         t_e = []
-        for _ in range(2):
-            t0_ = time.time(); nvb.map_reads_host(*args_h, hits_h=hh_n, ops_h=hops.numpy(), ctx=ctx); t_e.append(time.time() - t0_)
+        for _ in range(3):
+            t0_ = time.time(); nvb.map_reads_host(*args_h, hits_h=hh_n, cigar_h=hcig.numpy().view(np.uint16), max_read_len=RL, ctx=ctx); t_e.append(time.time() - t0_)
         e_ms = max_over_ranks(min(t_e) * 1e3)
         out["map"]["e2e"] = dict(reads_per_s=world * nr / (e_ms * 1e-3), ms=e_ms, h2d_bytes=int(hr_sym.numel() + hr_off.numel() * 4),
-                                 d2h_bytes=int(hh.numel() * 4 + hops.numel()))
+                                 d2h_bytes=int(hh.numel() * 4 + hcig.numel() * 2), result="hits + io::Cigar (16 entries per read)")
+        t0_ = time.time(); nvb.map_reads_host(*args_h, hits_h=hh_n, ops_h=hops.numpy(), max_read_len=RL, ctx=ctx); o_ms = (time.time() - t0_) * 1e3
+        out["map"]["e2e_op_lists"] = dict(reads_per_s=nr / (o_ms * 1e-3), ms=o_ms, d2h_bytes=int(hh.numel() * 4 + hops.numel()))
         assert (hh.numpy() == hits_d.cpu().numpy()).all(), "host and device pipeline entry points disagree"
         if rank == 0 and world == 1 and not args.no_cpu and only in ("", "map"):
             po, chk, kind = load_checker()
@@ -449,7 +452,7 @@ def run_b200(args):
             out["map"]["cpu"] = dict(reads_per_s=k / dt, cores=host_threads(), kind=kind, sample="first %d reads" % k)
             out["map"]["parity"] = dict(checked=k, hit_mismatches=mism, ops_mismatches=mism_ops)
             del gh
-        del hr_sym, hr_off, hh, hops, rsym, roff, words, res, hits_d, ops_d
+        del hr_sym, hr_off, hh, hops, hcig, rsym, roff, words, res, hits_d, ops_d
 
     # ---------------- secondary: SW local scoring (configs[0]) and banded scoring/traceback (configs[2])
     if not args.no_extra or only in ("sw", "banded"):

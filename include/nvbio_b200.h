@@ -301,11 +301,15 @@ int nvb_pack_2bit(nvb_ctx* ctx, const uint8_t* symbols_d, uint32_t n, uint32_t* 
 int nvb_map_reads(nvb_ctx* ctx, const nvb_fmindex* fmi_d, const uint32_t* genome_words_d, nvb_string_set reads,
                   uint32_t max_read_len, const nvb_map_params* params, uint32_t reads_per_batch,
                   nvb_read_hit* hits_d, uint8_t* ops_d, uint32_t ops_stride, nvb_map_stats* stats_h, void* stream);
-/* host buffers in / out (H2D of the reads, the pipeline, D2H of hits and ops; synchronous) */
+/* host buffers in / out, pipelined over read batches (reads of batch k+1 in, batch k mapped, results of batch k-1
+ * out); synchronous. ops_h and cigar_h are both optional: cigar_h receives cigar_stride uint16 entries per read in
+ * io::Cigar encoding (op | len << 2, forward order), the entry count in bits 8.. of the hit's flags; ops_stride is
+ * needed (scratch layout) whenever either is asked for. */
 int nvb_map_reads_host(nvb_ctx* ctx, const nvb_fmindex* fmi_d, const uint32_t* genome_words_d,
                        const uint8_t* reads_h, const uint32_t* read_off_h, uint32_t n_reads,
                        const nvb_map_params* params, uint32_t reads_per_batch,
-                       nvb_read_hit* hits_h, uint8_t* ops_h, uint32_t ops_stride, nvb_map_stats* stats_h);
+                       nvb_read_hit* hits_h, uint8_t* ops_h, uint32_t ops_stride,
+                       uint16_t* cigar_h, uint32_t cigar_stride, nvb_map_stats* stats_h);
 
 #if defined(__GNUC__)
 #pragma GCC visibility pop

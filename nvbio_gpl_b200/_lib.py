@@ -98,7 +98,7 @@ _PROTOS = {
     "nvb_map_reads": (_i, [_vp, C.POINTER(FMIndexC), _vp, StringSetC, _u32, C.POINTER(MapParamsC), _u32, _vp, _vp, _u32,
                            C.POINTER(MapStatsC), _vp]),
     "nvb_map_reads_host": (_i, [_vp, C.POINTER(FMIndexC), _vp, _vp, _vp, _u32, C.POINTER(MapParamsC), _u32, _vp, _vp, _u32,
-                                C.POINTER(MapStatsC)]),
+                                _vp, _u32, C.POINTER(MapStatsC)]),
     "nvb_last_paths": (_u32, [_vp]),
     "nvb_force_generic": (None, [_vp, _i]),
 }

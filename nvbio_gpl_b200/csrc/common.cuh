@@ -10,7 +10,7 @@
 #endif
 
 #define NVB_SM_COUNT 148
-#define NVB_STAGE_SLOTS 48
+#define NVB_STAGE_SLOTS 64
 
 struct nvb_ctx
 {

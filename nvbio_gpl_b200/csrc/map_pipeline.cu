@@ -20,6 +20,8 @@
 #include <thrust/iterator/counting_iterator.h>
 #include <cstdio>
 #include <cstdlib>
+#include <climits>
+#include <vector>
 
 #define MAP_THREADS 256
 #define MAP_NONE    0xFFFFFFFFu
@@ -576,33 +578,120 @@ extern "C" int nvb_map_reads(nvb_ctx* ctx, const nvb_fmindex* fmi, const uint32_
     return NVB_OK;
 }
 
+// op lists (push order) -> forward run-length CIGARs (io::Cigar: op | len << 2, nvbio/io/alignments.h:48-65);
+// the number of entries goes to bits 8.. of the hit's flags
+__global__ void __launch_bounds__(MAP_THREADS)
+map_cigar_kernel(nvb_read_hit* __restrict__ hits, const uint8_t* __restrict__ ops, uint32_t ops_stride, uint32_t n,
+                 uint16_t* __restrict__ cigar, uint32_t cigar_stride)
+{
+    const uint32_t r = blockIdx.x * MAP_THREADS + threadIdx.x;
+    if (r >= n) return;
+    const uint8_t* o = ops + (size_t)r * ops_stride;
+    uint16_t* c = cigar + (size_t)r * cigar_stride;
+    uint32_t len = hits[r].n_ops; if (len > ops_stride) len = ops_stride;
+    uint32_t out = 0, run = 0, prev = 0xFFu;
+    for (uint32_t k = len; k-- > 0;)
+    {
+        const uint32_t op = o[k] & 3u;
+        if (op == prev && run < 16383u) { ++run; continue; }
+        if (run) { if (out < cigar_stride) c[out] = (uint16_t)(prev | (run << 2)); ++out; }
+        prev = op; run = 1;
+    }
+    if (run) { if (out < cigar_stride) c[out] = (uint16_t)(prev | (run << 2)); ++out; }
+    hits[r].flags |= out << 8;
+}
+
+// Host buffers in and out, pipelined over batches of reads: the reads of batch k+1 cross PCIe while batch k is mapped,
+// and the results of batch k-1 leave (copy-in / compute / copy-out streams chained by events, two buffer sets).
+// cigar_h (optional): cigar_stride uint16 entries per read, io::Cigar encoding, entry count in flags >> 8; asking for
+// CIGARs instead of raw op lists (ops_h) cuts the D2H traffic from ~2 L to 2 * cigar_stride bytes per read.
+#define MAP_HOST_SLOT0 45
 extern "C" int nvb_map_reads_host(nvb_ctx* ctx, const nvb_fmindex* fmi, const uint32_t* genome, const uint8_t* reads_h,
                                   const uint32_t* off_h, uint32_t n, const nvb_map_params* mp, uint32_t reads_per_batch,
-                                  nvb_read_hit* hits_h, uint8_t* ops_h, uint32_t ops_stride, nvb_map_stats* stats)
+                                  nvb_read_hit* hits_h, uint8_t* ops_h, uint32_t ops_stride,
+                                  uint16_t* cigar_h, uint32_t cigar_stride, nvb_map_stats* stats)
 {
     if (!ctx || !mp) return NVB_ERR_ARG;
     if (stats) { stats->seeds = stats->seed_hits = stats->candidates = stats->aligned = 0; }
     if (n == 0) return NVB_OK;
-    if (!reads_h || !off_h || !hits_h) return NVB_ERR_ARG;
+    if (!reads_h || !off_h || !hits_h || (cigar_h && cigar_stride == 0)) return NVB_ERR_ARG;
     NVB_CUDA(ctx, cudaSetDevice(ctx->device));
     int rc;
-    uint32_t maxL = 0;
-    for (uint32_t i = 0; i < n; ++i) { const uint32_t l = off_h[i + 1] - off_h[i]; if (l > maxL) maxL = l; }
-    if (maxL == 0) return NVB_ERR_UNSUPPORTED;
-    const size_t b0 = off_h[0], nb = (size_t)off_h[n] - b0;
-    uint8_t *d_sym, *d_ops = nullptr; uint32_t* d_off; nvb_read_hit* d_hits;
-    MAP_STAGE(S_HREADS, nb + 64, d_sym);
-    MAP_STAGE(S_HOFF, sizeof(uint32_t) * ((size_t)n + 1), d_off);
-    MAP_STAGE(S_HHITS, sizeof(nvb_read_hit) * (size_t)n, d_hits);
-    if (ops_h) MAP_STAGE(S_HOPS, (size_t)n * ops_stride + 16, d_ops);
-    cudaStream_t s = ctx->stream;
-    if (ops_h) NVB_CUDA(ctx, cudaMemsetAsync(d_ops, 0, (size_t)n * ops_stride, s));
-    NVB_CUDA(ctx, cudaMemcpyAsync(d_sym, reads_h + b0, nb, cudaMemcpyHostToDevice, s));
-    NVB_CUDA(ctx, cudaMemcpyAsync(d_off, off_h, sizeof(uint32_t) * ((size_t)n + 1), cudaMemcpyHostToDevice, s));
-    nvb_string_set q; q.symbols = d_sym - b0; q.offsets = d_off; q.count = n; q.bits = 8;
-    if ((rc = nvb_map_reads(ctx, fmi, genome, q, maxL, mp, reads_per_batch, d_hits, d_ops, ops_stride, stats, s))) return rc;
-    NVB_CUDA(ctx, cudaMemcpyAsync(hits_h, d_hits, sizeof(nvb_read_hit) * (size_t)n, cudaMemcpyDeviceToHost, s));
-    if (ops_h) NVB_CUDA(ctx, cudaMemcpyAsync(ops_h, d_ops, (size_t)n * ops_stride, cudaMemcpyDeviceToHost, s));
-    NVB_CUDA(ctx, cudaStreamSynchronize(s));
+    const bool want_ops = ops_h || cigar_h;
+    const uint32_t rb = reads_per_batch ? reads_per_batch : (1u << 20);
+    const uint32_t n_batches = (n + rb - 1) / rb;
+    const int n_sets = n_batches > 1 ? 2 : 1;
+    size_t max_bytes = 0;
+    for (uint32_t k = 0; k < n_batches; ++k)
+    {
+        const uint32_t r0 = k * rb, r1 = r0 + rb < n ? r0 + rb : n;
+        const size_t nb = (size_t)off_h[r1] - off_h[r0];
+        if (nb > max_bytes) max_bytes = nb;
+    }
+    const uint32_t cap = n < rb ? n : rb;
+    uint8_t *d_sym[2], *d_ops[2] = { nullptr, nullptr }; uint32_t* d_off[2]; nvb_read_hit* d_hits[2]; uint16_t* d_cig[2] = { nullptr, nullptr };
+    for (int b = 0; b < n_sets; ++b)
+    {
+        MAP_STAGE(MAP_HOST_SLOT0 + 5 * b + 0, max_bytes + 64, d_sym[b]);
+        MAP_STAGE(MAP_HOST_SLOT0 + 5 * b + 1, sizeof(uint32_t) * ((size_t)cap + 1), d_off[b]);
+        MAP_STAGE(MAP_HOST_SLOT0 + 5 * b + 2, sizeof(nvb_read_hit) * (size_t)cap, d_hits[b]);
+        if (want_ops) MAP_STAGE(MAP_HOST_SLOT0 + 5 * b + 3, (size_t)cap * ops_stride + 16, d_ops[b]);
+        if (cigar_h)  MAP_STAGE(MAP_HOST_SLOT0 + 5 * b + 4, sizeof(uint16_t) * (size_t)cap * cigar_stride, d_cig[b]);
+    }
+    if (!ctx->host_ev[0])
+        for (int i = 0; i < 12; ++i) NVB_CUDA(ctx, cudaEventCreateWithFlags(&ctx->host_ev[i], cudaEventDisableTiming));
+    cudaStream_t s_in = ctx->aux[0], s_k = ctx->stream, s_out = ctx->aux[1];
+    auto copy_in = [&](uint32_t k) -> int
+    {
+        const int b = (int)(k & 1u) % n_sets;
+        const uint32_t r0 = k * rb, r1 = r0 + rb < n ? r0 + rb : n;
+        if (k >= (uint32_t)n_sets) NVB_CUDA(ctx, cudaStreamWaitEvent(s_in, ctx->host_ev[3 * b + 1], 0));   // batch k-2 has been mapped
+        NVB_CUDA(ctx, cudaMemcpyAsync(d_sym[b], reads_h + off_h[r0], (size_t)off_h[r1] - off_h[r0], cudaMemcpyHostToDevice, s_in));
+        NVB_CUDA(ctx, cudaMemcpyAsync(d_off[b], off_h + r0, sizeof(uint32_t) * ((size_t)(r1 - r0) + 1), cudaMemcpyHostToDevice, s_in));
+        NVB_CUDA(ctx, cudaEventRecord(ctx->host_ev[3 * b], s_in));
+        return NVB_OK;
+    };
+    if ((rc = copy_in(0))) return rc;
+    for (uint32_t k = 0; k < n_batches; ++k)
+    {
+        const int b = (int)(k & 1u) % n_sets;
+        const uint32_t r0 = k * rb, r1 = r0 + rb < n ? r0 + rb : n, nr = r1 - r0;
+        if (k + 1 < n_batches && (rc = copy_in(k + 1))) return rc;          // queued before this batch's compute blocks the host
+        uint32_t maxL = 0;
+        for (uint32_t i = r0; i < r1; ++i) { const uint32_t l = off_h[i + 1] - off_h[i]; if (l > maxL) maxL = l; }
+        NVB_CUDA(ctx, cudaStreamWaitEvent(s_k, ctx->host_ev[3 * b], 0));
+        if (k >= (uint32_t)n_sets) NVB_CUDA(ctx, cudaStreamWaitEvent(s_k, ctx->host_ev[3 * b + 2], 0));     // results of batch k-2 have left
+        if (want_ops) NVB_CUDA(ctx, cudaMemsetAsync(d_ops[b], 0, (size_t)nr * ops_stride, s_k));
+        nvb_map_stats st;
+        if (maxL == 0)
+        {
+            // nothing to map: every read of the batch is unaligned
+            std::vector<nvb_read_hit> none(nr);
+            for (uint32_t i = 0; i < nr; ++i) { none[i].score = none[i].second_score = INT32_MIN; none[i].begin = none[i].end = 0xFFFFFFFFu; none[i].flags = 0; none[i].n_ops = 0; }
+            NVB_CUDA(ctx, cudaMemcpyAsync(d_hits[b], none.data(), sizeof(nvb_read_hit) * nr, cudaMemcpyHostToDevice, s_k));
+            NVB_CUDA(ctx, cudaStreamSynchronize(s_k));
+            st.seeds = st.seed_hits = st.candidates = st.aligned = 0;
+        }
+        else
+        {
+            nvb_string_set q; q.symbols = d_sym[b] - off_h[r0]; q.offsets = d_off[b]; q.count = nr; q.bits = 8;
+            if ((rc = nvb_map_reads(ctx, fmi, genome, q, maxL, mp, nr, d_hits[b], d_ops[b], ops_stride, &st, s_k))) return rc;
+        }
+        if (cigar_h)
+        {
+            map_cigar_kernel<<<map_grid(nr), MAP_THREADS, 0, s_k>>>(d_hits[b], d_ops[b], ops_stride, nr, d_cig[b], cigar_stride);
+            NVB_LAUNCHED(ctx);
+        }
+        NVB_CUDA(ctx, cudaEventRecord(ctx->host_ev[3 * b + 1], s_k));
+        NVB_CUDA(ctx, cudaStreamWaitEvent(s_out, ctx->host_ev[3 * b + 1], 0));
+        NVB_CUDA(ctx, cudaMemcpyAsync(hits_h + r0, d_hits[b], sizeof(nvb_read_hit) * (size_t)nr, cudaMemcpyDeviceToHost, s_out));
+        if (ops_h)   NVB_CUDA(ctx, cudaMemcpyAsync(ops_h + (size_t)r0 * ops_stride, d_ops[b], (size_t)nr * ops_stride, cudaMemcpyDeviceToHost, s_out));
+        if (cigar_h) NVB_CUDA(ctx, cudaMemcpyAsync(cigar_h + (size_t)r0 * cigar_stride, d_cig[b], sizeof(uint16_t) * (size_t)nr * cigar_stride, cudaMemcpyDeviceToHost, s_out));
+        NVB_CUDA(ctx, cudaEventRecord(ctx->host_ev[3 * b + 2], s_out));
+        if (stats) { stats->seeds += st.seeds; stats->seed_hits += st.seed_hits; stats->candidates += st.candidates; stats->aligned += st.aligned; }
+    }
+    NVB_CUDA(ctx, cudaStreamSynchronize(s_out));
+    NVB_CUDA(ctx, cudaStreamSynchronize(s_k));
+    NVB_CUDA(ctx, cudaStreamSynchronize(s_in));
     return NVB_OK;
 }

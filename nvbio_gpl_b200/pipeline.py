@@ -69,17 +69,22 @@ def map_reads(fmi, genome_words, symbols, offsets, params, max_read_len=None, wa
     return hits, ops, dict(seeds=stats.seeds, seed_hits=stats.seed_hits, candidates=stats.candidates, aligned=stats.aligned)
 
 
-def map_reads_host(fmi, genome_words, symbols_h, offsets_h, params, hits_h=None, ops_h=None, reads_per_batch=0, ctx=None):
-    """numpy (ideally pinned) buffers in and out through ``nvb_map_reads_host``: H2D, pipeline, D2H, synchronous"""
+def map_reads_host(fmi, genome_words, symbols_h, offsets_h, params, hits_h=None, ops_h=None, cigar_h=None, reads_per_batch=0,
+                   max_read_len=None, ctx=None):
+    """numpy (ideally pinned) buffers in and out through ``nvb_map_reads_host``: batches pipelined over PCIe, synchronous.
+    ``cigar_h`` (uint16 [n, stride]) receives io::Cigar entries (op | len << 2); their count is ``flags >> 8``."""
     ctx = ctx or Context.default(genome_words.device.index)
     n = len(offsets_h) - 1
-    L = int(np.max(np.diff(offsets_h.astype(np.int64)))) if n else 0
-    stride = ops_h.shape[1] if ops_h is not None else ops_stride_for(L, params.band)
+    if max_read_len is None:
+        max_read_len = int(np.max(np.diff(offsets_h.astype(np.int64)))) if n else 0
+    stride = ops_h.shape[1] if ops_h is not None else ops_stride_for(max_read_len, params.band)
     if hits_h is None:
         hits_h = np.zeros(n, dtype=HIT_DT)
     stats = MapStatsC()
     fc, pc = fmi.c(), params.c()
     check(lib().nvb_map_reads_host(ctx.h, C.byref(fc), genome_words.data_ptr(), symbols_h.ctypes.data, offsets_h.ctypes.data, n,
                                    C.byref(pc), reads_per_batch, hits_h.ctypes.data,
-                                   ops_h.ctypes.data if ops_h is not None else None, stride, C.byref(stats)), ctx.h)
+                                   ops_h.ctypes.data if ops_h is not None else None, stride,
+                                   cigar_h.ctypes.data if cigar_h is not None else None,
+                                   cigar_h.shape[1] if cigar_h is not None else 0, C.byref(stats)), ctx.h)
     return hits_h, ops_h, dict(seeds=stats.seeds, seed_hits=stats.seed_hits, candidates=stats.candidates, aligned=stats.aligned)

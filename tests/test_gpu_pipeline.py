@@ -64,6 +64,17 @@ def test_map_reads(oracle, kind, scores, band, max_hits, max_range, both, min_sc
     h_hits, h_ops, _ = nvb.map_reads_host(fmi, words, sym, off, params,
                                           ops_h=np.zeros((len(off) - 1, nvb.ops_stride_for(150, band)), np.uint8))
     assert same(h_hits, h_ops, want_hits, want_ops)
+    # host entry point, several pipelined batches, CIGARs instead of op lists (io::Cigar: op | len << 2, forward order)
+    cig = np.zeros((len(off) - 1, 24), np.uint16)
+    c_hits, _, _ = nvb.map_reads_host(fmi, words, sym, off, params, cigar_h=cig, reads_per_batch=640)
+    n_cig = c_hits["flags"] >> 8
+    plain = c_hits.copy(); plain["flags"] &= 0xFF
+    assert (plain.view(np.uint32) == want_hits.view(np.uint32)).all()
+    for i in range(0, len(want_hits), 7):
+        k = int(want_hits["n_ops"][i])
+        fwd = want_ops[i, :k][::-1]
+        got = "".join("%d%s" % (int(e) >> 2, "MID"[int(e) & 3]) for e in cig[i, :int(n_cig[i])])
+        assert got == po.rle(fwd), (i, got, po.rle(fwd))
     assert (want_hits["flags"] & 2).astype(bool).sum() > 2000 or min_score >= 0
 
 
