@@ -94,6 +94,17 @@ int ORC(banded_traceback)(orc_aligner a, uint32_t band, uint32_t checkpoints, co
                           uint32_t count, orc_alignment* out, uint8_t* ops, uint32_t ops_stride,
                           uint32_t* n_ops, int threads);
 
+/* aln::Best2Sink<int32> (sink.h:99-123): best and runner-up whose text end is more than distinct_dist away */
+typedef struct { int32_t score1, score2; uint32_t x1, y1, x2, y2; } orc_sink2;
+/* scoring into a Best2Sink; band 0 = full matrix */
+int ORC(score_best2)(orc_aligner a, uint32_t band, uint32_t distinct_dist, const uint8_t* pat, const uint32_t* pat_off,
+                     const uint8_t* txt, const uint32_t* txt_off, uint32_t count, orc_sink2* sinks, int threads);
+/* EditDistanceAligner<type, MyersTag<alphabet>> banded scoring (myers/myers_banded_inl.h:183-296); min_score is
+ * truncated to int16 as the reference does; type 0 = GLOBAL, 2 = SEMI_GLOBAL (LOCAL reports nothing) */
+int ORC(banded_myers)(int32_t type, uint32_t alphabet, uint32_t band, int32_t min_score, const uint8_t* pat,
+                      const uint32_t* pat_off, const uint8_t* txt, const uint32_t* txt_off, uint32_t count,
+                      orc_sink* sinks, int threads);
+
 /* seed-and-extend composition (oracle_map.c); flags: bit 0 = reverse-complement strand, bit 1 = aligned.
  * begin/end = genome coordinates of the first aligned symbol / one past the last; ops in push order (end -> start). */
 typedef struct { uint32_t seed_len, seed_interval, max_hits, max_range, band, both_strands; int32_t min_score;

@@ -47,12 +47,17 @@ static scheme_t make_scheme(orc_aligner a)
     return s;
 }
 
-typedef struct { int32_t score; uint32_t x, y; } best_t;
+/* BestSink and, when `two` is set, Best2Sink (sink_inl.h:54-82): the runner-up must end more than `dd` text
+ * positions away from the current best */
+typedef struct { int32_t score; uint32_t x, y; int two; uint32_t dd; int32_t score2; uint32_t x2, y2; } best_t;
 /* Field_traits<int32>::min() is -(1<<30) in the reference (nvbio/basic/numbers.h:738-741) */
-static inline void best_init(best_t* b) { b->score = -(1 << 30); b->x = b->y = 0xFFFFFFFFu; }
+static inline void best_init(best_t* b)
+{ b->score = b->score2 = -(1 << 30); b->x = b->y = b->x2 = b->y2 = 0xFFFFFFFFu; b->two = 0; b->dd = 0; }
 static inline void best_report(best_t* b, int32_t s, uint32_t x, uint32_t y)
 {
     if (b->score <= s) { b->score = s; b->x = x; b->y = y; } /* sink_inl.h:44: last one wins */
+    else if (b->two && b->score2 <= s && (x + b->dd < b->x || x > b->x + b->dd)) /* sink_inl.h:77-81 (uint32 arithmetic) */
+    { b->score2 = s; b->x2 = x; b->y2 = y; }
 }
 static inline int32_t imax(int32_t a, int32_t b) { return a > b ? a : b; }
 
@@ -593,6 +598,121 @@ int orc_banded_traceback(orc_aligner a, uint32_t band, uint32_t checkpoints, con
         banded_traceback(&b, out + p, &tr);
         n_ops[p] = tr.n;
         free(mem); free(b.flow);
+    }
+    return 0;
+}
+
+/* ========================================================================================== */
+/*  Best2Sink scoring (sink.h:99-123, sink_inl.h:54-82) over the same sweeps; band 0 = full    */
+/* ========================================================================================== */
+int orc_score_best2(orc_aligner a, uint32_t band, uint32_t distinct_dist, const uint8_t* pat, const uint32_t* pat_off,
+                    const uint8_t* txt, const uint32_t* txt_off, uint32_t count, orc_sink2* sinks, int threads)
+{
+    if (band == 1 || band > MAX_BAND) return -2;
+    if (threads <= 0) threads = omp_get_max_threads();
+    #pragma omp parallel num_threads(threads)
+    {
+        int16_t* col = NULL; size_t cap = 0;
+        #pragma omp for schedule(dynamic,64)
+        for (int64_t p = 0; p < (int64_t)count; ++p)
+        {
+            best_t best; best_init(&best); best.two = 1; best.dd = distinct_dist;
+            const uint32_t M = pat_off[p + 1] - pat_off[p], N = txt_off[p + 1] - txt_off[p];
+            if (band == 0)
+            {
+                full_t f; memset(&f, 0, sizeof(f));
+                f.s = make_scheme(a);
+                f.pat = pat + pat_off[p]; f.M = M; f.txt = txt + txt_off[p]; f.N = N;
+                if (cap < (size_t)N + 1) { cap = (size_t)N + 1; free(col); col = (int16_t*)malloc(cap * 2 * sizeof(int16_t)); }
+                f.colH = col; f.colE = col + cap; f.CHK = 1u << 30; f.best = &best;
+                full_sweep(&f, 0, f.M, INIT_ZERO_COLUMN, 0, 0);
+            }
+            else
+            {
+                band_t b; memset(&b, 0, sizeof(b));
+                b.s = make_scheme(a); b.W = band; b.CHK = 1u << 30;
+                b.pat = pat + pat_off[p]; b.M = M; b.txt = txt + txt_off[p]; b.N = N; b.best = &best;
+                banded_sweep(&b, 0, b.M, 0, 0, 0);
+            }
+            sinks[p].score1 = best.score; sinks[p].score2 = best.score2;
+            sinks[p].x1 = best.x; sinks[p].y1 = best.y; sinks[p].x2 = best.x2; sinks[p].y2 = best.y2;
+        }
+        free(col);
+    }
+    return 0;
+}
+
+/* ========================================================================================== */
+/*  MyersTag<ALPHABET>: banded bit-vector edit distance (myers/myers_banded_inl.h:183-262)     */
+/* ========================================================================================== */
+/* One 32-bit column of vertical deltas slides down the diagonal: bit BAND-1 is the main diagonal's
+ * cell. `Peq[c]` holds, for the pattern symbols currently inside the window, the positions equal to c
+ * (loaded at bit BAND-1, shifted right once per text column). Phase 1 follows the diagonal while new
+ * pattern symbols enter, phase 2 walks right along the last pattern row; the running distance is the
+ * NEGATED edit distance. min_score is truncated to int16 exactly as banded_myers' parameter list does
+ * (:189), so the INT_MIN of the batch drivers becomes 0. */
+static inline uint32_t myers_peq(const uint32_t* B, uint32_t alphabet, uint8_t c)
+{
+    if (alphabet == 2) return B[c & 1u];       /* MyersBitVectors<2>::get (:85-90) */
+    if (alphabet == 4) return B[c & 3u];       /* MyersBitVectors<4>::get (:121-128) */
+    return B[c <= 4 ? c : 4];                  /* MyersBitVectors<5>::get (:160-166): anything above 3 reads B[4] */
+}
+static inline void myers_load(uint32_t* B, uint32_t alphabet, uint8_t c, uint32_t v)
+{
+    if (alphabet == 2) B[c & 1u] |= v;
+    else if (alphabet == 4) B[c & 3u] |= v;
+    else if (c <= 4) B[c] |= v;                /* MyersBitVectors<5>::load (:150-158): symbols above 4 load nothing */
+}
+static inline uint32_t myers_column(uint32_t eq, uint32_t* VP, uint32_t* VN, uint32_t* HPo, uint32_t* HNo)
+{
+    uint32_t X = eq | *VN;
+    const uint32_t D0 = ((*VP + (X & *VP)) ^ *VP) | X;
+    const uint32_t HN = *VP & D0;
+    const uint32_t HP = *VN | ~(*VP | D0);
+    X = D0 >> 1;
+    *VN = X & HP;
+    *VP = HN | ~(X | HP);
+    *HPo = HP; *HNo = HN;
+    return D0;
+}
+
+int orc_banded_myers(int32_t type, uint32_t alphabet, uint32_t band, int32_t min_score_in, const uint8_t* pat,
+                     const uint32_t* pat_off, const uint8_t* txt, const uint32_t* txt_off, uint32_t count,
+                     orc_sink* sinks, int threads)
+{
+    if (band < 1 || band > 32 || (alphabet != 2 && alphabet != 4 && alphabet != 5)) return -2;
+    if (threads <= 0) threads = omp_get_max_threads();
+    const int16_t min_score = (int16_t)min_score_in;                       /* :189 */
+    #pragma omp parallel for schedule(dynamic,64) num_threads(threads)
+    for (int64_t p = 0; p < (int64_t)count; ++p)
+    {
+        const uint8_t* P = pat + pat_off[p]; const uint32_t M = pat_off[p + 1] - pat_off[p];
+        const uint8_t* T = txt + txt_off[p]; const uint32_t N = txt_off[p + 1] - txt_off[p];
+        best_t best; best_init(&best);
+        if (N >= M)                                                        /* :195-196 */
+        {
+            uint32_t B[5] = { 0, 0, 0, 0, 0 }, VP = 0xFFFFFFFFu, VN = 0, HP, HN;
+            int dist = 0;                                                  /* -C with C = 0 (:203, :288) */
+            const uint32_t last = (N - 1u < M) ? N - 1u : M;               /* min(text_len-1, pattern_len-C), uint32 (:211) */
+            for (uint32_t i = 0; i < last; ++i)                            /* phase 1 (:212-219) */
+            {
+                for (uint32_t c = 0; c < 5; ++c) B[c] >>= 1;
+                myers_load(B, alphabet, P[i], 1u << (band - 1));
+                const uint32_t D0 = myers_column(myers_peq(B, alphabet, T[i]), &VP, &VN, &HP, &HN);
+                dist -= 1 - (int)((D0 >> (band - 1)) & 1u);
+            }
+            int s = (int)(band - 1u + M - last);                           /* :222 */
+            for (uint32_t i = last; i < N && s >= 0; ++i)                  /* phase 2 (:223-234) */
+            {
+                for (uint32_t c = 0; c < 5; ++c) B[c] >>= 1;
+                myers_column(myers_peq(B, alphabet, T[i]), &VP, &VN, &HP, &HN);
+                dist -= (int)((HP >> s) & 1u) - (int)((HN >> s) & 1u);
+                if (type == T_SEMI && dist >= min_score) best_report(&best, dist, i + 1, M);
+                --s;
+            }
+            if (type == T_GLOBAL && dist >= min_score) best_report(&best, dist, N, M);
+        }
+        sinks[p].score = best.score; sinks[p].x = best.x; sinks[p].y = best.y;
     }
     return 0;
 }

@@ -14,6 +14,7 @@ ED, SW, GOTOH = 0, 1, 2
 GLOBAL, LOCAL, SEMI_GLOBAL = 0, 1, 2
 
 SINK_DT = np.dtype([("score", "<i4"), ("x", "<u4"), ("y", "<u4")])
+SINK2_DT = np.dtype([("score1", "<i4"), ("score2", "<i4"), ("x1", "<u4"), ("y1", "<u4"), ("x2", "<u4"), ("y2", "<u4")])
 ALN_DT = np.dtype([("score", "<i4"), ("src_x", "<u4"), ("src_y", "<u4"), ("sink_x", "<u4"), ("sink_y", "<u4")])
 
 
@@ -218,6 +219,26 @@ class Oracle:
                                          C.c_uint32(n), _ptr(out), _ptr(ops), C.c_uint32(stride), _ptr(n_ops), C.c_int(threads))
         assert rc == 0, rc
         return out, ops, n_ops
+
+    def score_best2(self, a, band, distinct, pat, pat_off, txt, txt_off, threads=0):
+        """aln::Best2Sink<int32>(distinct) over the full (band = 0) or banded sweep"""
+        pat, pat_off, txt, txt_off = self._sets(pat, pat_off, txt, txt_off)
+        n = len(pat_off) - 1
+        sinks = np.zeros(n, dtype=SINK2_DT)
+        rc = self._f("score_best2")(a, C.c_uint32(band), C.c_uint32(distinct), _ptr(pat), _ptr(pat_off), _ptr(txt), _ptr(txt_off),
+                                    C.c_uint32(n), _ptr(sinks), C.c_int(threads))
+        assert rc == 0, rc
+        return sinks
+
+    def banded_myers(self, type_, alphabet, band, min_score, pat, pat_off, txt, txt_off, threads=0):
+        """EditDistanceAligner<type, MyersTag<alphabet>> banded scoring into a BestSink"""
+        pat, pat_off, txt, txt_off = self._sets(pat, pat_off, txt, txt_off)
+        n = len(pat_off) - 1
+        sinks = np.zeros(n, dtype=SINK_DT)
+        rc = self._f("banded_myers")(C.c_int32(type_), C.c_uint32(alphabet), C.c_uint32(band), C.c_int32(min_score), _ptr(pat), _ptr(pat_off),
+                                     _ptr(txt), _ptr(txt_off), C.c_uint32(n), _ptr(sinks), C.c_int(threads))
+        assert rc == 0, rc
+        return sinks
 
     # ---------------- seed-and-extend composition (oracle_map.c) ----------------
     def map_reads(self, idx, genome, reads, read_off, params, ops_stride=None, threads=0):

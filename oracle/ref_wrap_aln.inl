@@ -248,3 +248,129 @@ int ref_banded_traceback(orc_aligner a, uint32_t band, uint32_t checkpoints, con
 }
 
 } // extern "C"
+
+// ---- Best2Sink (nvbio/alignment/sink.h:99-123) and MyersTag (myers/myers_banded_inl.h) ----------------------
+namespace {
+
+inline void store_sink2(orc_sink2* out, const aln::Best2Sink<int32>& s)
+{
+    out->score1 = s.score1; out->score2 = s.score2;
+    out->x1 = s.sink1.x; out->y1 = s.sink1.y; out->x2 = s.sink2.x; out->y2 = s.sink2.y;
+}
+
+struct Args2
+{
+    const uint8_t* pat; const uint32_t* pat_off; const uint8_t* txt; const uint32_t* txt_off;
+    uint32_t count; uint32_t distinct; orc_sink2* sinks; int threads;
+};
+
+struct Score2F { Args2 g;
+    template <typename aligner_type> void operator()(const aligner_type aligner) const
+    {
+        typedef typename aln::column_storage_type<aligner_type>::type cell_type;
+        #pragma omp parallel num_threads(g.threads)
+        {
+            std::vector<cell_type> column;
+            #pragma omp for schedule(dynamic,64)
+            for (int64 i = 0; i < int64(g.count); ++i)
+            {
+                const uint32 M = g.pat_off[i+1] - g.pat_off[i];
+                const uint32 N = g.txt_off[i+1] - g.txt_off[i];
+                if (column.size() < N + 1u) column.resize( N + 1u );
+                aln::Best2Sink<int32> sink( g.distinct );
+                aln::alignment_score( aligner, sym_string( M, g.pat + g.pat_off[i] ), aln::trivial_quality_string(),
+                                      sym_string( N, g.txt + g.txt_off[i] ), MIN_SCORE, sink, &column[0] );
+                store_sink2( g.sinks + i, sink );
+            }
+        }
+    } };
+
+template <uint32 BAND> struct BandedScore2F { Args2 g;
+    template <typename aligner_type> void operator()(const aligner_type aligner) const
+    {
+        #pragma omp parallel for schedule(dynamic,64) num_threads(g.threads)
+        for (int64 i = 0; i < int64(g.count); ++i)
+        {
+            const uint32 M = g.pat_off[i+1] - g.pat_off[i];
+            const uint32 N = g.txt_off[i+1] - g.txt_off[i];
+            aln::Best2Sink<int32> sink( g.distinct );
+            aln::banded_alignment_score<BAND>( aligner, sym_string( M, g.pat + g.pat_off[i] ), aln::trivial_quality_string(),
+                                               sym_string( N, g.txt + g.txt_off[i] ), MIN_SCORE, sink );
+            store_sink2( g.sinks + i, sink );
+        }
+    } };
+
+template <uint32 BAND, aln::AlignmentType TYPE, uint32 ALPHABET>
+void myers_batch(const int32 min_score, const uint8_t* pat, const uint32_t* pat_off, const uint8_t* txt,
+                 const uint32_t* txt_off, uint32_t count, orc_sink* sinks, int threads)
+{
+    const aln::EditDistanceAligner<TYPE, aln::MyersTag<ALPHABET> > aligner =
+        aln::make_edit_distance_aligner<TYPE, aln::MyersTag<ALPHABET> >();
+    #pragma omp parallel for schedule(dynamic,64) num_threads(threads)
+    for (int64 i = 0; i < int64(count); ++i)
+    {
+        const uint32 M = pat_off[i+1] - pat_off[i];
+        const uint32 N = txt_off[i+1] - txt_off[i];
+        aln::BestSink<int32> sink;
+        aln::banded_alignment_score<BAND>( aligner, sym_string( M, pat + pat_off[i] ), aln::trivial_quality_string(),
+                                           sym_string( N, txt + txt_off[i] ), min_score, sink );
+        sinks[i].score = sink.score; sinks[i].x = sink.sink.x; sinks[i].y = sink.sink.y;
+    }
+}
+
+template <uint32 BAND, uint32 ALPHABET>
+int myers_type(const int32 type, const int32 min_score, const uint8_t* pat, const uint32_t* pat_off, const uint8_t* txt,
+               const uint32_t* txt_off, uint32_t count, orc_sink* sinks, int threads)
+{
+    switch (type) {
+    case 0: myers_batch<BAND,aln::GLOBAL,ALPHABET>( min_score, pat, pat_off, txt, txt_off, count, sinks, threads ); return 0;
+    case 1: myers_batch<BAND,aln::LOCAL,ALPHABET>( min_score, pat, pat_off, txt, txt_off, count, sinks, threads ); return 0;
+    case 2: myers_batch<BAND,aln::SEMI_GLOBAL,ALPHABET>( min_score, pat, pat_off, txt, txt_off, count, sinks, threads ); return 0;
+    default: return -1; }
+}
+
+template <uint32 BAND>
+int myers_alphabet(const uint32 alphabet, const int32 type, const int32 min_score, const uint8_t* pat, const uint32_t* pat_off,
+                   const uint8_t* txt, const uint32_t* txt_off, uint32_t count, orc_sink* sinks, int threads)
+{
+    switch (alphabet) {
+    case 2: return myers_type<BAND,2>( type, min_score, pat, pat_off, txt, txt_off, count, sinks, threads );
+    case 4: return myers_type<BAND,4>( type, min_score, pat, pat_off, txt, txt_off, count, sinks, threads );
+    case 5: return myers_type<BAND,5>( type, min_score, pat, pat_off, txt, txt_off, count, sinks, threads );
+    default: return -2; }
+}
+
+} // anonymous namespace
+
+extern "C" {
+
+int ref_score_best2(orc_aligner a, uint32_t band, uint32_t distinct_dist, const uint8_t* pat, const uint32_t* pat_off,
+                    const uint8_t* txt, const uint32_t* txt_off, uint32_t count, orc_sink2* sinks, int threads)
+{
+    if (threads <= 0) threads = omp_get_max_threads();
+    Args2 g = { pat, pat_off, txt, txt_off, count, distinct_dist, sinks, threads };
+    switch (band) {
+    case 0:  { Score2F f = { g }; return dispatch_aligner( a, f ); }
+    case 3:  { BandedScore2F<3>  f = { g }; return dispatch_aligner( a, f ); }
+    case 5:  { BandedScore2F<5>  f = { g }; return dispatch_aligner( a, f ); }
+    case 7:  { BandedScore2F<7>  f = { g }; return dispatch_aligner( a, f ); }
+    case 15: { BandedScore2F<15> f = { g }; return dispatch_aligner( a, f ); }
+    case 31: { BandedScore2F<31> f = { g }; return dispatch_aligner( a, f ); }
+    default: return -2; }
+}
+
+int ref_banded_myers(int32_t type, uint32_t alphabet, uint32_t band, int32_t min_score, const uint8_t* pat,
+                     const uint32_t* pat_off, const uint8_t* txt, const uint32_t* txt_off, uint32_t count,
+                     orc_sink* sinks, int threads)
+{
+    if (threads <= 0) threads = omp_get_max_threads();
+    switch (band) {
+    case 7:  return myers_alphabet<7>(  alphabet, type, min_score, pat, pat_off, txt, txt_off, count, sinks, threads );
+    case 15: return myers_alphabet<15>( alphabet, type, min_score, pat, pat_off, txt, txt_off, count, sinks, threads );
+    case 16: return myers_alphabet<16>( alphabet, type, min_score, pat, pat_off, txt, txt_off, count, sinks, threads );
+    case 31: return myers_alphabet<31>( alphabet, type, min_score, pat, pat_off, txt, txt_off, count, sinks, threads );
+    case 32: return myers_alphabet<32>( alphabet, type, min_score, pat, pat_off, txt, txt_off, count, sinks, threads );
+    default: return -2; }
+}
+
+} // extern "C"
