@@ -489,6 +489,7 @@ def run_b200(args):
             res = {}
             for name, a in (("ed_semi", nvb.EditDistanceAligner(nvb.SEMI_GLOBAL)),
                             ("gotoh_semi", nvb.GotohAligner(nvb.SEMI_GLOBAL, 0, -5, -8, -3)),
+                            ("sw_semi", nvb.SmithWatermanAligner(nvb.SEMI_GLOBAL, 2, -1, -1, -1)),
                             ("sw_local", nvb.SmithWatermanAligner(nvb.LOCAL, 2, -1, -1, -1))):
                 sinks = torch.empty((n, 3), dtype=torch.int32, device=dev)
                 fn = lambda: nvb.batch_banded_alignment_score(a, W, ps, ts, sinks=sinks, ctx=ctx)
@@ -496,6 +497,15 @@ def run_b200(args):
                 tms = time_steps(fn, max(3, args.steps // 2), 2, flush)
                 ms = max_over_ranks(sum(tms) / len(tms))
                 res[name] = dict(gcups=world * n * M * W / (ms * 1e-3) / 1e9, ms=ms, paths=ctx.last_paths)
+            # MyersTag<4> bit-vector edit distance over the 16-wide band the reference's fmmap example uses (fmmap.cu:347-358)
+            ma = nvb.MyersAligner(nvb.SEMI_GLOBAL, nvb.MyersTag(4))
+            msinks = torch.empty((n, 3), dtype=torch.int32, device=dev)
+            fn = lambda: nvb.batch_banded_myers_score(ma, 16, ps, ts, min_score=-1000, sinks=msinks, ctx=ctx)
+            barrier()
+            tms = time_steps(fn, max(3, args.steps // 2), 2, flush)
+            ms = max_over_ranks(sum(tms) / len(tms))
+            res["myers16_semi"] = dict(gcups=world * n * M * 16 / (ms * 1e-3) / 1e9, ms=ms, pairs_per_s=world * n / (ms * 1e-3),
+                                       note="bit-vector kernel: 1 thread per pair, band 16; GCUPS = n*M*16 / t")
             # traceback (CHK = 16 as nvBowtie, defs.h:95) on a slice that keeps scratch modest
             nt = min(n, 2_000_000)
             pt, tt = nvb.StringSet(P[:nt * M], Po[:nt + 1], 8, M), nvb.StringSet(T[:nt * N], To[:nt + 1], 8, N)
@@ -562,7 +572,7 @@ def run_b200(args):
     if "sw" in out:
         out["sw"]["roofline"] = _roof(out["sw"]["gcups"], "sw")
     if "banded" in out:
-        for k, kind in (("ed_semi", "ed"), ("gotoh_semi", "gotoh"), ("sw_local", "sw")):
+        for k, kind in (("ed_semi", "ed"), ("gotoh_semi", "gotoh"), ("sw_semi", "sw"), ("sw_local", "sw")):
             if k in out["banded"]:
                 out["banded"][k]["roofline"] = _roof(out["banded"][k]["gcups"], kind)
     extra = {k: out[k] for k in ("sw", "banded", "map") if k in out}

@@ -90,6 +90,10 @@ typedef struct {
  * 1-based; "no cell reported" = score -(1<<30), sink (0xFFFFFFFF,0xFFFFFFFF) */
 typedef struct { int32_t score; uint32_t sink_x, sink_y; } nvb_best_sink;
 
+/* aln::Best2Sink<int32> (nvbio/alignment/sink.h:99-123, sink_inl.h:54-82): the best cell and the best runner-up whose
+ * text end lies more than distinct_dist away from it; same "no cell reported" values as nvb_best_sink */
+typedef struct { int32_t score1, score2; uint32_t sink1_x, sink1_y, sink2_x, sink2_y; } nvb_best2_sink;
+
 /* aln::Alignment<int32> (nvbio/alignment/alignment.h:310-322) */
 typedef struct { int32_t score; uint32_t source_x, source_y, sink_x, sink_y; } nvb_alignment;
 
@@ -223,6 +227,22 @@ int nvb_batch_score(nvb_ctx* ctx, nvb_aligner aligner, nvb_string_set patterns, 
 int nvb_batch_banded_score(nvb_ctx* ctx, nvb_aligner aligner, uint32_t band, nvb_string_set patterns,
                            nvb_string_set texts, nvb_best_sink* sinks, uint32_t max_pattern_len,
                            uint32_t max_text_len, void* temp, size_t temp_bytes, void* stream);
+
+/* the same two calls with an aln::Best2Sink<int32>(distinct_dist) per pair instead of a BestSink (the sink nvBowtie's
+ * scoring uses to get a second-best score, nvBowtie/bowtie2/cuda/score_inl.h); band = 0: full matrix, else banded */
+int nvb_batch_score_best2(nvb_ctx* ctx, nvb_aligner aligner, uint32_t band, uint32_t distinct_dist,
+                          nvb_string_set patterns, nvb_string_set texts, nvb_best2_sink* sinks,
+                          uint32_t max_pattern_len, uint32_t max_text_len, void* temp, size_t temp_bytes, void* stream);
+
+/* batch_banded_alignment_score<BAND_LEN>(EditDistanceAligner<TYPE, MyersTag<ALPHABET>>, ...): Myers' bit-vector banded
+ * edit distance (nvbio/alignment/alignment.h:274-275, myers/myers_banded_inl.h:183-296; used by examples/fmmap/fmmap.cu:347-358).
+ * alphabet = 2, 4 or 5 (MyersTag's ALPHABET_SIZE), band = 1..32. Scores are negated distances; SEMI_GLOBAL reports every
+ * column of the last pattern row that lies in the band and scores >= min_score, GLOBAL the last one, LOCAL nothing.
+ * min_score is truncated to int16 as the reference's banded_myers does (:189) -- pass NVB_MYERS_BATCH_MIN_SCORE to get
+ * the value the reference's batch drivers end up with (Field_traits<int32>::min() -> 0: exact matches only). */
+#define NVB_MYERS_BATCH_MIN_SCORE (-(1 << 30))
+int nvb_batch_banded_myers_score(nvb_ctx* ctx, int32_t type, uint32_t alphabet, uint32_t band, nvb_string_set patterns,
+                                 nvb_string_set texts, int32_t min_score, nvb_best_sink* sinks, void* stream);
 
 /* BatchedAlignmentTraceback<CHECKPOINTS,...>::enact (nvbio/alignment/batched.h:335-380,
  * batched_inl.h:599-680,760-830; per pair aln::alignment_traceback, alignment_inl.h:355-455).

@@ -89,6 +89,8 @@ _PROTOS = {
     "nvb_temp_bytes": (_sz, [_i, AlignerC, _u32, _u32, _u32, _u32, _u32]),
     "nvb_batch_score": (_i, [_vp, AlignerC, StringSetC, StringSetC, _vp, _u32, _u32, _vp, _sz, _vp]),
     "nvb_batch_banded_score": (_i, [_vp, AlignerC, _u32, StringSetC, StringSetC, _vp, _u32, _u32, _vp, _sz, _vp]),
+    "nvb_batch_score_best2": (_i, [_vp, AlignerC, _u32, _u32, StringSetC, StringSetC, _vp, _u32, _u32, _vp, _sz, _vp]),
+    "nvb_batch_banded_myers_score": (_i, [_vp, C.c_int32, _u32, _u32, StringSetC, StringSetC, C.c_int32, _vp, _vp]),
     "nvb_batch_traceback": (_i, [_vp, AlignerC, _u32, StringSetC, StringSetC, _vp, _vp, _u32, _vp, _u32, _u32, _vp, _sz, _vp]),
     "nvb_batch_banded_traceback": (_i, [_vp, AlignerC, _u32, _u32, StringSetC, StringSetC, _vp, _vp, _u32, _vp, _u32, _u32, _vp, _sz, _vp]),
     "nvb_ops_to_cigar": (_i, [_vp, _vp, _u32, _vp, _u32, _vp, _u32, _vp, _vp]),

@@ -119,6 +119,52 @@ def batch_banded_alignment_score(aligner, band, patterns, texts, sinks=None, ctx
     return sinks
 
 
+class MyersTag:
+    """aln::MyersTag<ALPHABET_SIZE> (alignment.h:274-275): algorithm tag of the bit-vector edit distance"""
+
+    def __init__(self, alphabet_size):
+        self.alphabet_size = int(alphabet_size)
+
+
+class MyersAligner:
+    """aln::EditDistanceAligner<TYPE, MyersTag<ALPHABET>> (make_edit_distance_aligner<TYPE, MyersTag<A>>(), alignment.h:208)"""
+
+    def __init__(self, type_, tag):
+        self.type, self.alphabet = int(type_), int(tag.alphabet_size)
+
+
+MYERS_BATCH_MIN_SCORE = -(1 << 30)   # Field_traits<int32>::min(): what the reference's batch drivers pass (-> int16 0)
+
+
+def batch_banded_myers_score(aligner, band, patterns, texts, min_score=MYERS_BATCH_MIN_SCORE, sinks=None, ctx=None):
+    """aln::batch_banded_alignment_score<BAND_LEN>(EditDistanceAligner<TYPE, MyersTag<A>>, ...) (batched.h:142-192 over
+    myers/myers_banded_inl.h:183-296); min_score is truncated to int16 as the reference does"""
+    ctx = _ctx(patterns.offsets, ctx)
+    n = patterns.count
+    if sinks is None:
+        sinks = torch.empty((n, 3), dtype=torch.int32, device=patterns.offsets.device)
+    check(lib().nvb_batch_banded_myers_score(ctx.h, aligner.type, aligner.alphabet, band, patterns.c(), texts.c(), int(min_score),
+                                             sinks.data_ptr(), _lib.current_stream_ptr()), ctx.h)
+    return sinks
+
+
+def batch_alignment_score_best2(aligner, band, distinct_dist, patterns, texts, sinks=None, temp=None, ctx=None):
+    """batch_alignment_score / batch_banded_alignment_score<band> with aln::Best2Sink<int32>(distinct_dist) sinks
+    (sink.h:99-123). sinks: int32 [n,6] = (score1, score2, sink1.x, sink1.y, sink2.x, sink2.y); band 0 = full matrix"""
+    ctx = _ctx(patterns.offsets, ctx)
+    n = patterns.count
+    dev = patterns.offsets.device
+    if sinks is None:
+        sinks = torch.empty((n, 6), dtype=torch.int32, device=dev)
+    maxM, maxN = patterns.max_len, texts.max_len
+    if band == 0:
+        temp = _temp(_lib.OP_SCORE, aligner, 0, 0, maxM, maxN, n, dev, temp)
+    tp, tn = (temp.data_ptr(), temp.numel()) if temp is not None else (None, 0)
+    check(lib().nvb_batch_score_best2(ctx.h, aligner.c(), band, distinct_dist, patterns.c(), texts.c(), sinks.data_ptr(),
+                                      maxM, maxN, tp, tn, _lib.current_stream_ptr()), ctx.h)
+    return sinks
+
+
 def batch_alignment_traceback(aligner, checkpoints, patterns, texts, ops_stride=None, temp=None, ctx=None):
     """BatchedAlignmentTraceback<CHECKPOINTS,...>::enact (batched.h:335-380).
     Returns (alignments int32 [n,5], ops uint8 [n,ops_stride] in push order, n_ops int32 [n])"""

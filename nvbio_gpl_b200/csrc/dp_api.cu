@@ -148,6 +148,37 @@ extern "C" int nvb_batch_banded_score(nvb_ctx* ctx, nvb_aligner a, uint32_t band
     return dpg_banded_score(ctx, a, band, P, T, nullptr, nullptr, 0, n, sinks, s);
 }
 
+// aln::Best2Sink<int32>(distinct_dist) in place of BestSink (sink.h:99-123, sink_inl.h:54-82); band 0 = full matrix.
+// The sequential "else if" of Best2Sink::report is order-dependent, so this runs on the int32 one-pair-per-thread
+// kernels, which visit cells in the reference's order.
+extern "C" int nvb_batch_score_best2(nvb_ctx* ctx, nvb_aligner a, uint32_t band, uint32_t distinct_dist, nvb_string_set patterns,
+                                     nvb_string_set texts, nvb_best2_sink* sinks, uint32_t maxM, uint32_t maxN,
+                                     void* temp, size_t temp_bytes, void* stream)
+{
+    if (!ctx) return NVB_ERR_ARG;
+    int rc;
+    if ((rc = check_aligner(a)) || (rc = check_sets(patterns, texts))) return rc;
+    if (band == 1 || band > NVB_MAX_BAND_LEN) return NVB_ERR_UNSUPPORTED;
+    const uint32_t n = patterns.count;
+    if (n == 0) return NVB_OK;
+    if (!sinks) return NVB_ERR_ARG;
+    cudaStream_t s = (cudaStream_t)stream;
+    const StrSet P = make_set(patterns), T = make_set(texts);
+    const Sink2 s2 = { sinks, distinct_dist };
+    ctx->last_paths = 2u;
+    if (band) return dpg_banded_score(ctx, a, band, P, T, nullptr, nullptr, 0, n, nullptr, s, s2);
+    const TempPlan p = plan(NVB_OP_SCORE, a, 0, 0, maxM, maxN);
+    if (!temp && p.i16_per_pair) return NVB_ERR_TEMP;
+    const uint32_t bp = batch_pairs(p, temp_bytes, n);
+    if (bp == 0) return NVB_ERR_TEMP;
+    for (uint32_t first = 0; first < n; first += bp)
+    {
+        const uint32_t cnt = n - first < bp ? n - first : bp;
+        if ((rc = dpg_full_score(ctx, a, P, T, nullptr, nullptr, first, cnt, nullptr, (int16_t*)temp, maxN, s, s2))) return rc;
+    }
+    return NVB_OK;
+}
+
 extern "C" int nvb_batch_traceback(nvb_ctx* ctx, nvb_aligner a, uint32_t chk, nvb_string_set patterns,
                                    nvb_string_set texts, nvb_alignment* out, uint8_t* ops, uint32_t ops_stride,
                                    uint32_t* n_ops, uint32_t maxM, uint32_t maxN, void* temp, size_t temp_bytes, void* stream)

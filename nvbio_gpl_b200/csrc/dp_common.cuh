@@ -17,16 +17,25 @@ static inline Scheme make_scheme(const nvb_aligner& a)
     return s;
 }
 
+// optional Best2Sink output of the int32 scoring kernels (out == NULL: plain BestSink into `sinks`)
+struct Sink2 { nvb_best2_sink* out; uint32_t distinct; };
+
 #define NVB_SINK_MIN (-(1 << 30))   // Field_traits<int32>::min(), nvbio/basic/numbers.h:738-741
 
 #ifdef __CUDACC__
+// BestSink, and with `two` set Best2Sink (sink_inl.h:54-82): the runner-up must end more than `dd` text positions
+// away from the current best (uint32 arithmetic, as the reference)
 struct Best
 {
     int32_t score; uint32_t x, y;
-    __device__ __forceinline__ void init() { score = NVB_SINK_MIN; x = y = 0xFFFFFFFFu; }
+    int32_t score2; uint32_t x2, y2, dd; bool two;
+    __device__ __forceinline__ void init() { score = score2 = NVB_SINK_MIN; x = y = x2 = y2 = 0xFFFFFFFFu; dd = 0; two = false; }
     // BestSink::report uses '<=': the last visited maximal cell wins (sink_inl.h:40-48)
     __device__ __forceinline__ void report(int32_t s, uint32_t xx, uint32_t yy)
-    { if (score <= s) { score = s; x = xx; y = yy; } }
+    {
+        if (score <= s) { score = s; x = xx; y = yy; }
+        else if (two && score2 <= s && (xx + dd < x || xx > x + dd)) { score2 = s; x2 = xx; y2 = yy; }
+    }
 };
 
 struct PairView

@@ -6,34 +6,34 @@
 
 template <bool GOTOH, int TYPE, int WT>
 static int score_w(nvb_ctx* ctx, Scheme sc, uint32_t band, StrSet P, StrSet T, const uint32_t* list, const uint32_t* d_count, uint32_t first,
-                   uint32_t n, nvb_best_sink* sinks, cudaStream_t s)
+                   uint32_t n, nvb_best_sink* sinks, cudaStream_t s, Sink2 s2)
 {
-    dpg_banded_score_kernel<GOTOH, TYPE, WT><<<(n + 127) / 128, 128, 0, s>>>(sc, band, P, T, list, d_count, first, n, sinks);
+    dpg_banded_score_kernel<GOTOH, TYPE, WT><<<(n + 127) / 128, 128, 0, s>>>(sc, band, P, T, list, d_count, first, n, sinks, s2);
     NVB_LAUNCHED(ctx);
     return NVB_OK;
 }
 template <bool GOTOH, int TYPE>
 static int score_t(nvb_ctx* ctx, Scheme sc, uint32_t band, StrSet P, StrSet T, const uint32_t* list, const uint32_t* d_count, uint32_t first,
-                   uint32_t n, nvb_best_sink* sinks, cudaStream_t s)
+                   uint32_t n, nvb_best_sink* sinks, cudaStream_t s, Sink2 s2)
 {
     switch (band)
     {
-    case 3:  return score_w<GOTOH, TYPE, 3>(ctx, sc, band, P, T, list, d_count, first, n, sinks, s);
-    case 5:  return score_w<GOTOH, TYPE, 5>(ctx, sc, band, P, T, list, d_count, first, n, sinks, s);
-    case 7:  return score_w<GOTOH, TYPE, 7>(ctx, sc, band, P, T, list, d_count, first, n, sinks, s);
-    case 15: return score_w<GOTOH, TYPE, 15>(ctx, sc, band, P, T, list, d_count, first, n, sinks, s);
-    case 31: return score_w<GOTOH, TYPE, 31>(ctx, sc, band, P, T, list, d_count, first, n, sinks, s);
-    default: return score_w<GOTOH, TYPE, 0>(ctx, sc, band, P, T, list, d_count, first, n, sinks, s);
+    case 3:  return score_w<GOTOH, TYPE, 3>(ctx, sc, band, P, T, list, d_count, first, n, sinks, s, s2);
+    case 5:  return score_w<GOTOH, TYPE, 5>(ctx, sc, band, P, T, list, d_count, first, n, sinks, s, s2);
+    case 7:  return score_w<GOTOH, TYPE, 7>(ctx, sc, band, P, T, list, d_count, first, n, sinks, s, s2);
+    case 15: return score_w<GOTOH, TYPE, 15>(ctx, sc, band, P, T, list, d_count, first, n, sinks, s, s2);
+    case 31: return score_w<GOTOH, TYPE, 31>(ctx, sc, band, P, T, list, d_count, first, n, sinks, s, s2);
+    default: return score_w<GOTOH, TYPE, 0>(ctx, sc, band, P, T, list, d_count, first, n, sinks, s, s2);
     }
 }
 
 int dpg_banded_score(nvb_ctx* ctx, const nvb_aligner& a, uint32_t band, StrSet P, StrSet T, const uint32_t* list,
-                     const uint32_t* d_count, uint32_t first, uint32_t n, nvb_best_sink* sinks, cudaStream_t s)
+                     const uint32_t* d_count, uint32_t first, uint32_t n, nvb_best_sink* sinks, cudaStream_t s, Sink2 s2)
 {
     if (n == 0) return NVB_OK;
     const Scheme sc = make_scheme(a);
     const bool g = a.kind == NVB_GOTOH;
-    #define GO(G, TY) return score_t<G, TY>(ctx, sc, band, P, T, list, d_count, first, n, sinks, s)
+    #define GO(G, TY) return score_t<G, TY>(ctx, sc, band, P, T, list, d_count, first, n, sinks, s, s2)
     switch (a.type)
     {
     case NVB_GLOBAL:      if (g) GO(true, T_GLOBAL); else GO(false, T_GLOBAL);

@@ -237,7 +237,7 @@ struct BandDP
 template <bool GOTOH, int TYPE, int WT>
 __global__ void __launch_bounds__(128)
 dpg_banded_score_kernel(Scheme s, uint32_t W, StrSet P, StrSet T, const uint32_t* __restrict__ list, const uint32_t* __restrict__ d_count, uint32_t first,
-                        uint32_t n, nvb_best_sink* __restrict__ sinks)
+                        uint32_t n, nvb_best_sink* __restrict__ sinks, Sink2 s2)
 {
     const uint32_t lp = blockIdx.x * 128 + threadIdx.x;
     if (lp >= n) return;
@@ -247,8 +247,10 @@ dpg_banded_score_kernel(Scheme s, uint32_t W, StrSet P, StrSet T, const uint32_t
     dp.s = s; dp.v = make_pair_view(P, T, id); dp.Wrt = W; dp.cs = 1;
     dp.chkH = dp.chkF = nullptr; dp.flow = nullptr; dp.CHK = 1u << 30;
     Best b; b.init(); dp.best = &b;
+    if (s2.out) { b.two = true; b.dd = s2.distinct; }
     dp.sweep(0, dp.v.M, false, false, 0);
-    sinks[id].score = b.score; sinks[id].sink_x = b.x; sinks[id].sink_y = b.y;
+    if (s2.out) { nvb_best2_sink o; o.score1 = b.score; o.score2 = b.score2; o.sink1_x = b.x; o.sink1_y = b.y; o.sink2_x = b.x2; o.sink2_y = b.y2; s2.out[id] = o; }
+    else { sinks[id].score = b.score; sinks[id].sink_x = b.x; sinks[id].sink_y = b.y; }
 }
 
 template <bool GOTOH, int TYPE, int WT>

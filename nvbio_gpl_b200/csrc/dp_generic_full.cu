@@ -4,21 +4,21 @@
 
 template <bool GOTOH, int TYPE>
 static int score_t(nvb_ctx* ctx, Scheme sc, StrSet P, StrSet T, const uint32_t* list, const uint32_t* d_count, uint32_t first, uint32_t n,
-                   nvb_best_sink* sinks, int16_t* temp, uint32_t maxN, cudaStream_t s)
+                   nvb_best_sink* sinks, int16_t* temp, uint32_t maxN, cudaStream_t s, Sink2 s2)
 {
     dpg_full_score_kernel<GOTOH, TYPE><<<(n + DPG_THREADS - 1) / DPG_THREADS, DPG_THREADS, 0, s>>>(
-        sc, P, T, list, d_count, first, n, sinks, temp, maxN);
+        sc, P, T, list, d_count, first, n, sinks, temp, maxN, s2);
     NVB_LAUNCHED(ctx);
     return NVB_OK;
 }
 
 int dpg_full_score(nvb_ctx* ctx, const nvb_aligner& a, StrSet P, StrSet T, const uint32_t* list, const uint32_t* d_count, uint32_t first,
-                   uint32_t n, nvb_best_sink* sinks, int16_t* temp, uint32_t maxN, cudaStream_t s)
+                   uint32_t n, nvb_best_sink* sinks, int16_t* temp, uint32_t maxN, cudaStream_t s, Sink2 s2)
 {
     if (n == 0) return NVB_OK;
     const Scheme sc = make_scheme(a);
     const bool g = a.kind == NVB_GOTOH;
-    #define GO(G, TY) return score_t<G, TY>(ctx, sc, P, T, list, d_count, first, n, sinks, temp, maxN, s)
+    #define GO(G, TY) return score_t<G, TY>(ctx, sc, P, T, list, d_count, first, n, sinks, temp, maxN, s, s2)
     switch (a.type)
     {
     case NVB_GLOBAL:      if (g) GO(true, T_GLOBAL); else GO(false, T_GLOBAL);

@@ -234,7 +234,7 @@ struct FullDP
 template <bool GOTOH, int TYPE>
 __global__ void __launch_bounds__(DPG_THREADS)
 dpg_full_score_kernel(Scheme s, StrSet P, StrSet T, const uint32_t* __restrict__ list, const uint32_t* __restrict__ d_count, uint32_t first,
-                      uint32_t n, nvb_best_sink* __restrict__ sinks, int16_t* __restrict__ temp, uint32_t maxN)
+                      uint32_t n, nvb_best_sink* __restrict__ sinks, int16_t* __restrict__ temp, uint32_t maxN, Sink2 s2)
 {
     const uint32_t lp = blockIdx.x * DPG_THREADS + threadIdx.x;
     if (lp >= n) return;
@@ -247,8 +247,10 @@ dpg_full_score_kernel(Scheme s, StrSet P, StrSet T, const uint32_t* __restrict__
     dp.colE = temp + (size_t)maxN * n + lp;
     dp.chkH = dp.chkE = nullptr; dp.flow = nullptr; dp.CHK = 1u << 30;
     Best b; b.init(); dp.best = &b;
+    if (s2.out) { b.two = true; b.dd = s2.distinct; }
     if (dp.v.N <= maxN) dp.sweep(0, dp.v.M, false, false, 0);
-    sinks[id].score = b.score; sinks[id].sink_x = b.x; sinks[id].sink_y = b.y;
+    if (s2.out) { nvb_best2_sink o; o.score1 = b.score; o.score2 = b.score2; o.sink1_x = b.x; o.sink1_y = b.y; o.sink2_x = b.x2; o.sink2_y = b.y2; s2.out[id] = o; }
+    else { sinks[id].score = b.score; sinks[id].sink_x = b.x; sinks[id].sink_y = b.y; }
 }
 
 // traceback: scratch per pair = 2 columns + 2*nchk*N checkpoints (int16) + N*CHK flow bytes

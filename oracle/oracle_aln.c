@@ -706,7 +706,8 @@ int orc_banded_myers(int32_t type, uint32_t alphabet, uint32_t band, int32_t min
             {
                 for (uint32_t c = 0; c < 5; ++c) B[c] >>= 1;
                 myers_column(myers_peq(B, alphabet, T[i]), &VP, &VN, &HP, &HN);
-                dist -= (int)((HP >> s) & 1u) - (int)((HN >> s) & 1u);
+                /* s == 32 (band 32, N == M) is an undefined shift in the reference (:179); its x86 host build shifts by s mod 32 */
+                dist -= (int)((HP >> (s & 31)) & 1u) - (int)((HN >> (s & 31)) & 1u);
                 if (type == T_SEMI && dist >= min_score) best_report(&best, dist, i + 1, M);
                 --s;
             }
