@@ -43,6 +43,9 @@ struct FullFastParams
     uint32_t       tstride;    // shared-memory words per couple = ceil(maxN / 8)
     int32_t        match, mismatch, G, I, B;
     uint32_t       one, sixteen;   // runtime 1 and 16: keep the IMADs IMADs
+    uint32_t       unshear;        // fix2(-16 b): the value handed to the next lane leaves the stripe's shear
+    uint32_t       FL[16];         // LOCAL floor of stripe column j in sheared coordinates: pack2(B + b j)
+    uint32_t       CJ[16];         // key addend: (h' << 4) + CJ[j] = (H + B) << 4 | j
 };
 
 __device__ __forceinline__ uint32_t pack2(int32_t v) { return ((uint32_t)v & 0xFFFFu) * 0x00010001u; }
@@ -53,15 +56,33 @@ __device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t s)
 __device__ __forceinline__ uint32_t imad(uint32_t a, uint32_t b, uint32_t c)
 { uint32_t d; asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c)); return d; }
 
+// 4 bytes holding 2-bit symbols -> 4 nibbles in the low half
+__device__ __forceinline__ uint32_t squeeze4(uint32_t x)
+{
+    x &= 0x03030303u; x = (x | (x >> 4)) & 0x00FF00FFu; x = (x | (x >> 8)) & 0x0000FFFFu;
+    return x;
+}
+
 __device__ __forceinline__ void mark_dirty(uint32_t* wl, uint32_t id)
 {
     const uint32_t slot = atomicAdd(wl, 1u);
     wl[1 + slot] = id;
 }
 
-__global__ void __launch_bounds__(DPF_THREADS)
+// BT > 0: b = -I = BT and the bias B = DPF_BIAS are compile-time, so the per-column floors FL[j] and key addends CJ[j]
+// are immediates; BT = 0 reads them from the parameter block (any I in -64..-1).
+#define DPF_BIAS 64
+template <int BT>
+__global__ void __launch_bounds__(DPF_THREADS, 5)
 dpf_full_sw_local_kernel(const FullFastParams p)
 {
+    auto FLc = [&](const int j) -> uint32_t { return BT ? (uint32_t)(DPF_BIAS + BT * j) * 0x00010001u : p.FL[j]; };
+    auto CJc = [&](const int j) -> uint32_t
+    {
+        if (!BT) return p.CJ[j];
+        const int32_t cj = j - 16 * BT * j;
+        return cj < 0 ? ((((uint32_t)(cj - 1) & 0xFFFFu) << 16) | ((uint32_t)cj & 0xFFFFu)) : 0u;
+    };
     extern __shared__ uint32_t s_text[];   // [warp][couple slot][tstride]: 8 rows per word, nibble = rA | rB << 2
     const uint32_t lane = threadIdx.x & 31u, wib = threadIdx.x >> 5;
     const uint32_t warp = blockIdx.x * DPF_WARPS + wib;
@@ -87,85 +108,153 @@ dpf_full_sw_local_kernel(const FullFastParams p)
     {
         for (uint32_t w = k; w * 8 < Nmax; w += p.lanes)
         {
-            uint32_t word = 0;
-            #pragma unroll
-            for (uint32_t e = 0; e < 8; ++e)
+            // 8 rows of one text as 8 nibbles; whole aligned words of an 8-bit set are fetched with two 32-bit loads
+            auto rows8 = [&](const uint32_t tb, const uint32_t N, bool& dirty) -> uint32_t
             {
-                const uint32_t i = w * 8 + e;
-                const uint32_t rA = i < NA ? sym_at_rt(p.T.sym, p.T.bits, tbA + i) : 0u;
-                const uint32_t rB = i < NB ? sym_at_rt(p.T.sym, p.T.bits, tbB + i) : 0u;
-                dirtyA |= rA > 3u; dirtyB |= rB > 3u;
-                word |= ((rA & 3u) | ((rB & 3u) << 2)) << (4 * e);
-            }
-            my_text[w] = word;
+                const uint32_t i0 = w * 8;
+                const uint8_t* src = p.T.sym + tb + i0;
+                if (p.T.bits == 8 && i0 + 8 <= N && ((uintptr_t)src & 3u) == 0)
+                {
+                    const uint32_t x0 = __ldg((const uint32_t*)src), x1 = __ldg((const uint32_t*)src + 1);
+                    dirty |= ((x0 | x1) & 0xFCFCFCFCu) != 0;
+                    return squeeze4(x0) | (squeeze4(x1) << 16);
+                }
+                uint32_t word = 0;
+                #pragma unroll
+                for (uint32_t e = 0; e < 8; ++e)
+                {
+                    const uint32_t r = i0 + e < N ? sym_at_rt(p.T.sym, p.T.bits, tb + i0 + e) : 0u;
+                    dirty |= r > 3u;
+                    word |= (r & 3u) << (4 * e);
+                }
+                return word;
+            };
+            my_text[w] = rows8(tbA, NA, dirtyA) | (rows8(tbB, NB, dirtyB) << 2);
         }
     }
     __syncwarp();
 
     // ---- this lane's stripe: substitution profiles of 16 pattern columns of both pairs
     const uint32_t B2 = pack2(p.B), Gf = fix2(p.G), If = fix2(p.I);
-    const uint32_t base  = ((uint32_t)p.mismatch & 0xFFu) * 0x01010101u;     // 4 x mismatch
-    const uint32_t delta = ((uint32_t)(p.mismatch ^ p.match)) & 0xFFu;       // flips one byte to match
+    const uint32_t base  = ((uint32_t)(p.mismatch - p.I) & 0xFFu) * 0x01010101u;            // 4 x (mismatch + b)
+    const uint32_t delta = ((uint32_t)((p.mismatch - p.I) ^ (p.match - p.I))) & 0xFFu;       // flips one byte to match + b
     const uint32_t block = k * 16u;
     uint32_t TA[16], TB[16], H[16];
-    #pragma unroll
-    for (int j = 0; j < 16; ++j)
     {
-        const uint32_t c = block + j;
-        uint32_t wa = 0x80808080u, wb = 0x80808080u;       // columns past the pattern: S = -128
-        if (live && c < MA) { const uint32_t q = sym_at_rt(p.P.sym, p.P.bits, pbA + c); dirtyA |= q > 3u; wa = base ^ (delta << (8u * (q & 3u))); }
-        if (live && c < MB) { const uint32_t q = sym_at_rt(p.P.sym, p.P.bits, pbB + c); dirtyB |= q > 3u; wb = base ^ (delta << (8u * (q & 3u))); }
-        TA[j] = wa; TB[j] = wb; H[j] = B2;
+        // the stripe's 16 pattern symbols of one pair: four aligned 32-bit loads when the stripe is whole, else bytes
+        auto stripe16 = [&](const uint32_t pb, const uint32_t M, bool& dirty, uint32_t* q4)
+        {
+            const uint8_t* src = p.P.sym + pb + block;
+            if (p.P.bits == 8 && block + 16u <= M && ((uintptr_t)src & 3u) == 0)
+            {
+                #pragma unroll
+                for (int w = 0; w < 4; ++w) q4[w] = __ldg((const uint32_t*)src + w);
+            }
+            else
+            {
+                #pragma unroll
+                for (int w = 0; w < 4; ++w)
+                {
+                    uint32_t x = 0;
+                    #pragma unroll
+                    for (int e = 0; e < 4; ++e)
+                    {
+                        const uint32_t c = block + 4 * w + e;
+                        x |= (c < M ? sym_at_rt(p.P.sym, p.P.bits, pb + c) : 0xFFu) << (8 * e);   // 0xFF = past the pattern
+                    }
+                    q4[w] = x;
+                }
+            }
+        };
+        uint32_t qa[4] = { 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu }, qb[4] = { 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu };
+        if (live) { stripe16(pbA, MA, dirtyA, qa); stripe16(pbB, MB, dirtyB, qb); }
+        #pragma unroll
+        for (int j = 0; j < 16; ++j)
+        {
+            const uint32_t c = block + j;
+            const uint32_t a = (qa[j >> 2] >> (8 * (j & 3))) & 255u, b = (qb[j >> 2] >> (8 * (j & 3))) & 255u;
+            uint32_t wa = 0x80808080u, wb = 0x80808080u;       // columns past the pattern: S = -128
+            if (live && c < MA) { dirtyA |= a > 3u; wa = base ^ (delta << (8u * (a & 3u))); }
+            if (live && c < MB) { dirtyB |= b > 3u; wb = base ^ (delta << (8u * (b & 3u))); }
+            TA[j] = wa; TB[j] = wb; H[j] = FLc(j);
+        }
     }
     // halves that own cells in this stripe
     const uint32_t smask = (block < MA ? 0x0000FFFFu : 0u) | (block < MB ? 0xFFFF0000u : 0u);
 
     uint32_t bestkey = B2 << 4;          // packed (biased score << 4 | column in stripe)
     uint32_t bestrow = 0;                // packed text rows of the best
-    uint32_t carry = B2, send = B2, tw = 0;
+    // Rows are kept SHEARED along the stripe: stored h'[j] = H + B + b*j (b = -I), so the move from the left costs
+    // nothing (h'[j-1] already equals H[j-1] + I + B + b*j), the diagonal's +b sits in the profile bytes and the LOCAL
+    // floor of column j is the constant FL[j] = B + b*j. Only the value handed to the next lane is un-sheared (-16 b).
+    uint32_t r_one, r_sixteen;          // in registers: an instruction takes one constant-bank operand, FL[] / CJ[] / Gf use it
+    asm volatile("mov.u32 %0, %1;" : "=r"(r_one) : "r"(p.one));
+    asm volatile("mov.u32 %0, %1;" : "=r"(r_sixteen) : "r"(p.sixteen));
+    const uint32_t zero_in = pack2(p.B + p.I);                  // H = 0 of the column left of the stripe (local j = -1)
+    uint32_t carry = zero_in, send = FLc(15), tw = 0;
 
-    const uint32_t steps = __reduce_max_sync(0xFFFFFFFFu, live ? Nmax + p.lanes - 1 : 0u);
-    for (uint32_t t = 0; t < steps; ++t)
+    // one text row of the stripe. MASKED = false: every lane of the warp is on a row that exists in both of its pairs.
+    auto row_step = [&](const uint32_t t, const bool masked)
     {
-        uint32_t cin = __shfl_up_sync(0xFFFFFFFFu, send, 1);
-        if (k == 0) cin = B2;                                   // column 0 of a LOCAL matrix is all zeros
-        const uint32_t i = t - k;                               // this lane's text row
-        if (live && i < Nmax)                                   // (unsigned: also false while t < k)
+        uint32_t cin = imad(__shfl_up_sync(0xFFFFFFFFu, send, 1), r_one, p.unshear);
+        if (k == 0) cin = zero_in;                              // column 0 of a LOCAL matrix is all zeros
+        const uint32_t i = t - k;                               // this lane's text row (wraps while t < k: a dummy row)
+        if (t == k)                                             // first real row: the dummy rows above left garbage behind
         {
-            if ((i & 7u) == 0) tw = my_text[i >> 3];
-            const uint32_t nib = tw & 15u; tw >>= 4;
-            // selector: byte rA of profA -> byte 0, its sign -> byte 1; byte rB of profB -> byte 2, sign -> byte 3
-            const uint32_t sel = imad((nib & 3u) | ((nib & 12u) << 6), 0x11u, 0xC480u);
+            #pragma unroll
+            for (int j = 0; j < 16; ++j) H[j] = FLc(j);
+            carry = zero_in;
+        }
+        if ((i & 7u) == 0 && i < Nmax) tw = my_text[i >> 3];
+        const uint32_t nib = tw & 15u; tw >>= 4;
+        // selector: byte rA of profA -> byte 0, its sign -> byte 1; byte rB of profB -> byte 2, sign -> byte 3
+        const uint32_t sel = imad((nib & 3u) | ((nib & 12u) << 6), 0x11u, 0xC480u);
 
-            uint32_t diag = carry, left = cin;
-            carry = cin;
-            // running best with its column bits cleared, minus one: a cell of equal score compares greater
-            const uint32_t kb = __vadd2(bestkey & 0xFFF0FFF0u, 0xFFFFFFFFu);
-            uint32_t acc = kb;
-            uint32_t key[16];
+        // phase A: everything that only needs the previous row
+        uint32_t v[16];
+        {
+            uint32_t diag = carry;
             #pragma unroll
             for (int j = 0; j < 16; ++j)
             {
                 const uint32_t S = prmt(TA[j], TB[j], sel);
-                const uint32_t u = imad(H[j], p.one, Gf);
-                const uint32_t v = __viaddmax_s16x2(diag, S, u);
-                const uint32_t l = imad(left, p.one, If);
-                const uint32_t h = __vimax3_s16x2(l, v, B2);
-                diag = H[j]; H[j] = h; left = h;
-                key[j] = imad(h, p.sixteen, (uint32_t)j * 0x00010001u);
+                const uint32_t u = imad(H[j], r_one, Gf);
+                v[j] = __viaddmax_s16x2(diag, S, u);
+                diag = H[j];
             }
-            #pragma unroll
-            for (int j = 0; j < 16; j += 2) acc = __vimax3_s16x2(acc, key[j], key[j + 1]);
-            send = left;
-
-            // halves whose row holds a score >= the best so far take the row (later rows win ties)
-            const uint32_t rmask = smask & ((i < NA ? 0x0000FFFFu : 0u) | (i < NB ? 0xFFFF0000u : 0u));
-            const uint32_t d = __vsub2(kb, acc);                          // < 0 in a half that improved
-            const uint32_t m = prmt(d, d, 0xBB99u) & rmask;               // 0xFFFF per improved, valid half
-            bestkey = (acc & m) | (bestkey & ~m);
-            bestrow = ((i * 0x00010001u) & m) | (bestrow & ~m);
         }
-    }
+        carry = cin;
+        // phase B: the serial chain along the row, keys reduced pairwise on the fly
+        // running best with its column bits cleared, minus one: a cell of equal score compares greater
+        const uint32_t kb = __vadd2(bestkey & 0xFFF0FFF0u, 0xFFFFFFFFu);
+        uint32_t acc = kb, left = cin;
+        #pragma unroll
+        for (int j = 0; j < 16; j += 2)
+        {
+            const uint32_t h0 = __vimax3_s16x2(left, v[j], FLc(j));
+            const uint32_t h1 = __vimax3_s16x2(h0, v[j + 1], FLc(j + 1));
+            H[j] = h0; H[j + 1] = h1; left = h1;
+            acc = __vimax3_s16x2(acc, imad(h0, r_sixteen, CJc(j)), imad(h1, r_sixteen, CJc(j + 1)));
+        }
+        send = left;
+
+        // halves whose row holds a score >= the best so far take the row (later rows win ties)
+        const uint32_t d = __vsub2(kb, acc);                          // < 0 in a half that improved
+        uint32_t m = prmt(d, d, 0xBB99u) & smask;                     // 0xFFFF per improved half that owns cells here
+        if (masked) m &= (i < NA ? 0x0000FFFFu : 0u) | (i < NB ? 0xFFFF0000u : 0u);
+        bestkey = (acc & m) | (bestkey & ~m);
+        bestrow = ((i * 0x00010001u) & m) | (bestrow & ~m);
+    };
+
+    const uint32_t steps = __reduce_max_sync(0xFFFFFFFFu, live ? Nmax + p.lanes - 1 : 0u);
+    // rows [t_lo, t_hi): all lanes on existing rows of both pairs (dead lanes never report: their smask is 0)
+    const uint32_t Nmin  = __reduce_min_sync(0xFFFFFFFFu, live ? min(NA, hasB ? NB : NA) : 0xFFFFFFFFu);
+    const uint32_t t_lo  = min(p.lanes - 1u, steps);
+    const uint32_t t_hi  = max(t_lo, min(Nmin, steps));
+    uint32_t t = 0;
+    for (; t < t_lo; ++t)  row_step(t, true);
+    for (; t < t_hi; ++t)  row_step(t, false);
+    for (; t < steps; ++t) row_step(t, true);
 
     // ---- epilogue: the highest stripe among those with the best score wins (stripes are visited in order)
     const uint32_t dmaskA = __ballot_sync(0xFFFFFFFFu, dirtyA), dmaskB = __ballot_sync(0xFFFFFFFFu, dirtyB);
@@ -191,7 +280,7 @@ dpf_full_sw_local_kernel(const FullFastParams p)
         const uint32_t M = h ? MB : MA, N = h ? NB : NA;
         bool dirty = ((h ? dmaskB : dmaskA) & gmask) != 0;
         // key overflow; the other pair's rows are swept too, hence the couple's longer text in the bound
-        if (p.match > 0 && (uint64_t)p.match * min(M, Nmax) + (uint32_t)p.B >= 2047u) dirty = true;
+        if (p.match > 0 && (uint64_t)p.match * min(M, Nmax) + (uint32_t)p.B + 15u * (uint32_t)(-p.I) >= 2047u) dirty = true;
         if (dirty) { mark_dirty(p.worklist, id); continue; }
         const uint32_t wk = h ? wkB : wkA;
         const uint32_t stripe = h ? wlaneB : wlaneA;
@@ -220,7 +309,7 @@ bool dpf_full_score_supported(const nvb_aligner& a, const StrSet& P, const StrSe
     if (a.type != NVB_LOCAL) return false;
     if (a.kind != NVB_SMITH_WATERMAN && a.kind != NVB_EDIT_DISTANCE) return false;
     const Scheme s = make_scheme(a);
-    if (s.match < -127 || s.match > 127 || s.mismatch < -127 || s.mismatch > 127) return false;
+    if (s.match - s.gb < -127 || s.match - s.gb > 127 || s.mismatch - s.gb < -127 || s.mismatch - s.gb > 127) return false;   // profile bytes hold S + b
     if (s.ga >= 0 || s.gb >= 0 || s.ga < -64 || s.gb < -64) return false;
     if (maxN == 0 || maxM == 0 || maxN > 65535u) return false;
     uint32_t lanes, tpw, tstride; size_t smem;
@@ -238,17 +327,39 @@ int dpf_full_score(nvb_ctx* ctx, const nvb_aligner& a, StrSet P, StrSet T, nvb_b
     p.P = P; p.T = T; p.sinks = sinks; p.worklist = worklist;
     p.n_pairs = P.count; p.n_tasks = (P.count + 1) / 2;
     p.match = s.match; p.mismatch = s.mismatch; p.G = s.ga; p.I = s.gb;
-    p.B = -(s.ga < s.gb ? s.ga : s.gb);
+    const int bt = (-s.gb >= 1 && -s.gb <= 4) ? -s.gb : 0;      // instantiated immediates
+    p.B = bt ? DPF_BIAS : -(s.ga < s.gb ? s.ga : s.gb);
     p.one = 1; p.sixteen = 16;
+    {
+        const int32_t b = -s.gb;
+        p.unshear = (((uint32_t)(-16 * b - 1) & 0xFFFFu) << 16) | ((uint32_t)(-16 * b) & 0xFFFFu);
+        for (int j = 0; j < 16; ++j)
+        {
+            p.FL[j] = ((uint32_t)(p.B + b * j) & 0xFFFFu) * 0x00010001u;
+            const int32_t cj = j - 16 * b * j;                 // <= 0; a negative addend borrows one from the upper half
+            p.CJ[j] = cj < 0 ? ((((uint32_t)(cj - 1) & 0xFFFFu) << 16) | ((uint32_t)cj & 0xFFFFu)) : 0u;
+        }
+    }
     static bool attr_set = false;
     if (!attr_set)
     {
-        NVB_CUDA(ctx, cudaFuncSetAttribute(dpf_full_sw_local_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+        NVB_CUDA(ctx, cudaFuncSetAttribute(dpf_full_sw_local_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+        NVB_CUDA(ctx, cudaFuncSetAttribute(dpf_full_sw_local_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+        NVB_CUDA(ctx, cudaFuncSetAttribute(dpf_full_sw_local_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+        NVB_CUDA(ctx, cudaFuncSetAttribute(dpf_full_sw_local_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+        NVB_CUDA(ctx, cudaFuncSetAttribute(dpf_full_sw_local_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
         attr_set = true;
     }
     const uint32_t n_warps = (p.n_tasks + p.tpw - 1) / p.tpw;
     const uint32_t grid = (n_warps + DPF_WARPS - 1) / DPF_WARPS;
-    dpf_full_sw_local_kernel<<<grid, DPF_THREADS, smem, st>>>(p);
+    switch (bt)
+    {
+    case 1:  dpf_full_sw_local_kernel<1><<<grid, DPF_THREADS, smem, st>>>(p); break;
+    case 2:  dpf_full_sw_local_kernel<2><<<grid, DPF_THREADS, smem, st>>>(p); break;
+    case 3:  dpf_full_sw_local_kernel<3><<<grid, DPF_THREADS, smem, st>>>(p); break;
+    case 4:  dpf_full_sw_local_kernel<4><<<grid, DPF_THREADS, smem, st>>>(p); break;
+    default: dpf_full_sw_local_kernel<0><<<grid, DPF_THREADS, smem, st>>>(p); break;
+    }
     NVB_LAUNCHED(ctx);
     return NVB_OK;
 }
