@@ -194,12 +194,17 @@ dpf_full_sw_local_kernel(const FullFastParams p)
     uint32_t carry = zero_in, send = FLc(15), tw = 0;
 
     // one text row of the stripe. MASKED = false: every lane of the warp is on a row that exists in both of its pairs.
-    auto row_step = [&](const uint32_t t, const bool masked)
+    // lane 0 of a couple has no left neighbour: column 0 of a LOCAL matrix is all zeros. Folded into the un-shear IMAD.
+    const uint32_t cin_mul = k == 0 ? 0u : r_one, cin_add = k == 0 ? zero_in : p.unshear;
+    uint32_t r_m1; asm volatile("mov.u32 %0, %1;" : "=r"(r_m1) : "r"(0u - p.one));
+
+    // one text row of the stripe. masked = false: every lane of the warp is on a row that exists in both of its pairs;
+    // first = true: some lane may still be on the dummy rows above its first row (they leave garbage that is reset here)
+    auto row_step = [&](const uint32_t t, const bool masked, const bool first)
     {
-        uint32_t cin = imad(__shfl_up_sync(0xFFFFFFFFu, send, 1), r_one, p.unshear);
-        if (k == 0) cin = zero_in;                              // column 0 of a LOCAL matrix is all zeros
+        const uint32_t cin = imad(__shfl_up_sync(0xFFFFFFFFu, send, 1), cin_mul, cin_add);
         const uint32_t i = t - k;                               // this lane's text row (wraps while t < k: a dummy row)
-        if (t == k)                                             // first real row: the dummy rows above left garbage behind
+        if (first && t == k)
         {
             #pragma unroll
             for (int j = 0; j < 16; ++j) H[j] = FLc(j);
@@ -224,9 +229,11 @@ dpf_full_sw_local_kernel(const FullFastParams p)
             }
         }
         carry = cin;
-        // phase B: the serial chain along the row, keys reduced pairwise on the fly
-        // running best with its column bits cleared, minus one: a cell of equal score compares greater
-        const uint32_t kb = __vadd2(bestkey & 0xFFF0FFF0u, 0xFFFFFFFFu);
+        // phase B: the serial chain along the row, keys reduced pairwise on the fly.
+        // kb = running best with its column bits cleared, minus one: a cell of equal score compares greater. Both halves
+        // of every operand below are non-negative and the differences too, so plain 32-bit IMADs (FMA pipe) do the
+        // packed arithmetic without borrows.
+        const uint32_t kb = imad(bestkey & 0xFFF0FFF0u, r_one, 0xFFFEFFFFu);          // - 0x00010001
         uint32_t acc = kb, left = cin;
         #pragma unroll
         for (int j = 0; j < 16; j += 2)
@@ -238,23 +245,24 @@ dpf_full_sw_local_kernel(const FullFastParams p)
         }
         send = left;
 
-        // halves whose row holds a score >= the best so far take the row (later rows win ties)
-        const uint32_t d = __vsub2(kb, acc);                          // < 0 in a half that improved
-        uint32_t m = prmt(d, d, 0xBB99u) & smask;                     // 0xFFFF per improved half that owns cells here
+        // halves whose row holds a score >= the best so far take the row (later rows win ties): acc - kb > 0 there
+        const uint32_t d = imad(kb, r_m1, acc);                        // acc - kb, >= 0 in both halves
+        const uint32_t sgn = imad(d, r_one, 0x7FFF7FFFu);              // bit 15 of a half set iff its difference is > 0
+        uint32_t m = prmt(sgn, sgn, 0xBB99u) & smask;                  // 0xFFFF per improved half that owns cells here
         if (masked) m &= (i < NA ? 0x0000FFFFu : 0u) | (i < NB ? 0xFFFF0000u : 0u);
         bestkey = (acc & m) | (bestkey & ~m);
-        bestrow = ((i * 0x00010001u) & m) | (bestrow & ~m);
+        bestrow = (imad(i, 0x00010001u, 0u) & m) | (bestrow & ~m);
     };
 
     const uint32_t steps = __reduce_max_sync(0xFFFFFFFFu, live ? Nmax + p.lanes - 1 : 0u);
     // rows [t_lo, t_hi): all lanes on existing rows of both pairs (dead lanes never report: their smask is 0)
     const uint32_t Nmin  = __reduce_min_sync(0xFFFFFFFFu, live ? min(NA, hasB ? NB : NA) : 0xFFFFFFFFu);
-    const uint32_t t_lo  = min(p.lanes - 1u, steps);
+    const uint32_t t_lo  = min(p.lanes, steps);
     const uint32_t t_hi  = max(t_lo, min(Nmin, steps));
     uint32_t t = 0;
-    for (; t < t_lo; ++t)  row_step(t, true);
-    for (; t < t_hi; ++t)  row_step(t, false);
-    for (; t < steps; ++t) row_step(t, true);
+    for (; t < t_lo; ++t)  row_step(t, true, true);
+    for (; t < t_hi; ++t)  row_step(t, false, false);
+    for (; t < steps; ++t) row_step(t, true, false);
 
     // ---- epilogue: the highest stripe among those with the best score wins (stripes are visited in order)
     const uint32_t dmaskA = __ballot_sync(0xFFFFFFFFu, dirtyA), dmaskB = __ballot_sync(0xFFFFFFFFu, dirtyB);
