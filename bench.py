@@ -36,6 +36,7 @@ def parse():
     ap.add_argument("--sw-pairs", type=int, default=100_000)
     ap.add_argument("--banded-pairs", type=int, default=10_000_000)
     ap.add_argument("--reads", type=int, default=10_000_000, help="reads of the seed+extend leg (configs[3] shape, 150 bp)")
+    ap.add_argument("--pairs", type=int, default=5_000_000, help="read pairs of the paired-end leg (configs[4] shape, 2 x 150 bp)")
     ap.add_argument("--no-extra", action="store_true", help="skip the SW / banded secondary measurements")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
     ap.add_argument("--only", default="", help="profiling aid: run only this leg (fm|sw|banded|map) with no cpu leg")
@@ -189,6 +190,31 @@ def gen_reads(genome, n, L, seed, dev, sub=0.01, indel=0.14, chunk=2_000_000):
         out[b:e] = r
         del idx, r, mm
     off = (torch.arange(n + 1, device=dev, dtype=torch.int64) * L).to(torch.int32)
+    return out.reshape(-1), off
+
+
+def gen_mates(genome, n_pairs, L, seed, dev, frag=(250, 500), sub=0.01, chunk=1_000_000):
+    """n_pairs fragments of 250..499 bp: mate 1 = its first L symbols, mate 2 = the reverse complement of its last L, 1 %
+    substitutions each; every other pair comes from the reverse strand (mates swapped). Laid out pair by pair (configs[4])."""
+    import torch
+    out = torch.empty((n_pairs, 2, L), dtype=torch.uint8, device=dev)
+    G = genome.numel()
+    ar = torch.arange(L, device=dev)
+    for k, b in enumerate(range(0, n_pairs, chunk)):
+        e = min(n_pairs, b + chunk); m = e - b
+        g = torch.Generator(device=dev); g.manual_seed(seed * 1000 + k)
+        F = torch.randint(frag[0], frag[1], (m,), device=dev, generator=g)
+        pos = torch.randint(0, G - frag[1] - 2, (m,), device=dev, generator=g)
+        m1 = genome[(pos[:, None] + ar[None, :]).reshape(-1)].reshape(m, L)
+        m2 = (3 - genome[((pos + F - L)[:, None] + ar[None, :]).reshape(-1)].reshape(m, L)).flip(1)
+        r = torch.stack([m1, m2], dim=1)
+        mm = torch.rand((m, 2, L), device=dev, generator=g) < sub
+        r[mm] = (r[mm] + torch.randint(1, 4, (int(mm.sum().item()),), dtype=torch.uint8, device=dev, generator=g)) & 3
+        sw = torch.arange(m, device=dev) % 2 == 1
+        r[sw] = r[sw].flip(1)
+        out[b:e] = r
+        del m1, m2, r, mm
+    off = (torch.arange(2 * n_pairs + 1, device=dev, dtype=torch.int64) * L).to(torch.int32)
     return out.reshape(-1), off
 
 
@@ -452,7 +478,27 @@ def run_b200(args):
             out["map"]["cpu"] = dict(reads_per_s=k / dt, cores=host_threads(), kind=kind, sample="first %d reads" % k)
             out["map"]["parity"] = dict(checked=k, hit_mismatches=mism, ops_mismatches=mism_ops)
             del gh
-        del hr_sym, hr_off, hh, hops, hcig, rsym, roff, words, res, hits_d, ops_d
+        del hr_sym, hr_off, hh, hops, hcig, rsym, roff, res, hits_d, ops_d
+
+        # ---- paired-end (configs[4] shape): both mates mapped independently (2 x pairs reads), then nvb_pair_hits
+        if args.pairs > 0:
+            npairs = args.pairs
+            msym, moff = gen_mates(genome, npairs, RL, 11 + rank, dev)
+            pres = {}
+            def _pairs():
+                h, _, st = nvb.map_reads(fmi, words, msym, moff, mparams, max_read_len=RL, want_ops=False, ctx=ctx)
+                pres["p"] = nvb.pair_hits(h, 0, 500, ctx=ctx); pres["st"] = st
+            _pairs()
+            barrier()
+            tms = time_steps(_pairs, max(2, args.steps // 3), 1, flush)
+            ms = max_over_ranks(sum(tms) / len(tms))
+            fl = pres["p"][:, 3]
+            out["pairs"] = dict(pairs_per_s=world * npairs / (ms * 1e-3), ms=ms, pairs=npairs, read_len=RL, fragment="250..499 bp, FR",
+                                concordant_frac=float(((fl & 4) != 0).float().mean().item()),
+                                both_aligned_frac=float(((fl & 3) == 3).float().mean().item()),
+                                note="mates mapped independently (seed, locate, banded Gotoh, traceback for the coordinates; op lists not kept), then nvb_pair_hits (FR, fragment <= 500)")
+            del msym, moff, pres
+        del words
 
     # ---------------- secondary: SW local scoring (configs[0]) and banded scoring/traceback (configs[2])
     if not args.no_extra or only in ("sw", "banded"):
@@ -575,7 +621,7 @@ def run_b200(args):
         for k, kind in (("ed_semi", "ed"), ("gotoh_semi", "gotoh"), ("sw_semi", "sw"), ("sw_local", "sw")):
             if k in out["banded"]:
                 out["banded"][k]["roofline"] = _roof(out["banded"][k]["gcups"], kind)
-    extra = {k: out[k] for k in ("sw", "banded", "map") if k in out}
+    extra = {k: out[k] for k in ("sw", "banded", "map", "pairs") if k in out}
     if extra:
         line["extra"] = extra
     print(json.dumps(line))

@@ -331,6 +331,16 @@ int nvb_map_reads_host(nvb_ctx* ctx, const nvb_fmindex* fmi_d, const uint32_t* g
                        nvb_read_hit* hits_h, uint8_t* ops_h, uint32_t ops_stride,
                        uint16_t* cigar_h, uint32_t cigar_stride, nvb_map_stats* stats_h);
 
+/* Mate pairing over the hits of 2 n reads laid out pair by pair (read 2 i = mate 1, 2 i + 1 = mate 2), both mapped
+ * independently by nvb_map_reads: forward-reverse policy with a fragment-length window (nvBowtie's pe_policy = PE_POLICY_FR,
+ * min_frag_len / max_frag_len, nvBowtie/bowtie2/cuda/params.h:147-152). flags: bit 0 = mate 1 aligned, bit 1 = mate 2
+ * aligned, bit 2 = concordant (opposite strands, the forward mate starts and the reverse mate ends a fragment of
+ * min_frag_len..max_frag_len). score = sum of the aligned mates' scores (INT32_MIN if none); frag_begin/frag_end = the hull
+ * of the aligned mates. nvBowtie's anchor + opposite-mate window search (score_inl.h:385-411) is NOT part of it. */
+typedef struct { int32_t score; uint32_t frag_begin, frag_end, flags; } nvb_pair_hit;
+int nvb_pair_hits(nvb_ctx* ctx, const nvb_read_hit* hits_d, uint32_t n_pairs, uint32_t min_frag_len, uint32_t max_frag_len,
+                  nvb_pair_hit* pairs_d, void* stream);
+
 #if defined(__GNUC__)
 #pragma GCC visibility pop
 #endif

@@ -403,6 +403,51 @@ static int map_build_sets(nvb_ctx* ctx, const uint64_t* keys, const uint32_t* al
     return NVB_OK;
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// mate pairing over the hits of 2 n reads (read 2 i = mate 1, read 2 i + 1 = mate 2 of pair i): classifies each pair
+// as concordant / discordant / single / unaligned under the forward-reverse policy with a fragment-length window
+// (nvBowtie's ParamsPOD::pe_policy = PE_POLICY_FR, min_frag_len / max_frag_len: params.h:147-152; its anchor + opposite-
+// mate window search, score_inl.h:385-411, is replaced by the independent mapping of both mates).
+// ---------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+map_pair_kernel(const nvb_read_hit* __restrict__ hits, uint32_t n_pairs, uint32_t min_frag, uint32_t max_frag,
+                nvb_pair_hit* __restrict__ out)
+{
+    const uint32_t i = blockIdx.x * 256u + threadIdx.x;
+    if (i >= n_pairs) return;
+    // 24-byte records: 8-byte aligned loads
+    const uint2* h2 = (const uint2*)(hits + 2 * (size_t)i);
+    const uint2 pa = __ldg(h2), qa = __ldg(h2 + 1), a1 = __ldg(h2 + 2);      // (score, second), (begin, end), (flags, n_ops) of mate 1
+    const uint2 pb = __ldg(h2 + 3), qb = __ldg(h2 + 4), b1 = __ldg(h2 + 5);
+    const uint4 a0 = make_uint4(pa.x, pa.y, qa.x, qa.y), b0 = make_uint4(pb.x, pb.y, qb.x, qb.y);
+    const bool al1 = (a1.x & 2u) != 0, al2 = (b1.x & 2u) != 0;
+    nvb_pair_hit o; o.score = INT32_MIN; o.frag_begin = o.frag_end = 0xFFFFFFFFu; o.flags = (al1 ? 1u : 0u) | (al2 ? 2u : 0u);
+    if (al1 && al2)
+    {
+        o.score = (int32_t)a0.x + (int32_t)b0.x;
+        const bool r1 = (a1.x & 1u) != 0, r2 = (b1.x & 1u) != 0;
+        // the forward mate starts the fragment, the reverse-complemented mate ends it
+        const uint32_t fb = r1 ? b0.z : a0.z, fe = r1 ? b0.w : a0.w, rb = r1 ? a0.z : b0.z, re = r1 ? a0.w : b0.w;
+        o.frag_begin = min(a0.z, b0.z); o.frag_end = max(a0.w, b0.w);
+        const uint32_t frag = re >= fb ? re - fb : 0u;
+        if (r1 != r2 && fb <= rb && fe <= re && frag >= min_frag && frag <= max_frag) o.flags |= 4u;   // concordant
+    }
+    else if (al1) { o.score = (int32_t)a0.x; o.frag_begin = a0.z; o.frag_end = a0.w; }
+    else if (al2) { o.score = (int32_t)b0.x; o.frag_begin = b0.z; o.frag_end = b0.w; }
+    out[i] = o;
+}
+
+extern "C" int nvb_pair_hits(nvb_ctx* ctx, const nvb_read_hit* hits_d, uint32_t n_pairs, uint32_t min_frag_len, uint32_t max_frag_len,
+                             nvb_pair_hit* pairs_d, void* stream)
+{
+    if (!ctx) return NVB_ERR_ARG;
+    if (n_pairs == 0) return NVB_OK;
+    if (!hits_d || !pairs_d || min_frag_len > max_frag_len) return NVB_ERR_ARG;
+    map_pair_kernel<<<(n_pairs + 255u) / 256u, 256, 0, (cudaStream_t)stream>>>(hits_d, n_pairs, min_frag_len, max_frag_len, pairs_d);
+    NVB_LAUNCHED(ctx);
+    return NVB_OK;
+}
+
 extern "C" int nvb_map_reads(nvb_ctx* ctx, const nvb_fmindex* fmi, const uint32_t* genome, nvb_string_set reads_set,
                              uint32_t maxL, const nvb_map_params* mp, uint32_t reads_per_batch,
                              nvb_read_hit* hits, uint8_t* ops, uint32_t ops_stride, nvb_map_stats* stats, void* stream)

@@ -15,6 +15,8 @@ from .alignment import Aligner, GotohAligner, SEMI_GLOBAL
 
 HIT_DT = np.dtype([("score", "<i4"), ("second_score", "<i4"), ("begin", "<u4"), ("end", "<u4"), ("flags", "<u4"), ("n_ops", "<u4")])
 FLAG_REVERSE, FLAG_ALIGNED = 1, 2
+PAIR_DT = np.dtype([("score", "<i4"), ("frag_begin", "<u4"), ("frag_end", "<u4"), ("flags", "<u4")])
+PAIR_MATE1, PAIR_MATE2, PAIR_CONCORDANT = 1, 2, 4
 
 
 class MapParams:
@@ -88,3 +90,15 @@ def map_reads_host(fmi, genome_words, symbols_h, offsets_h, params, hits_h=None,
                                    cigar_h.ctypes.data if cigar_h is not None else None,
                                    cigar_h.shape[1] if cigar_h is not None else 0, C.byref(stats)), ctx.h)
     return hits_h, ops_h, dict(seeds=stats.seeds, seed_hits=stats.seed_hits, candidates=stats.candidates, aligned=stats.aligned)
+
+
+def pair_hits(hits, min_frag_len=0, max_frag_len=500, ctx=None):
+    """mate pairing (``nvb_pair_hits``) over the device hits of 2 n independently mapped mates laid out pair by pair; forward-reverse
+    policy with nvBowtie's fragment window (params.h:147-152). Returns int32 [n, 4] viewable as PAIR_DT."""
+    if not hits.is_cuda:
+        raise RuntimeError("pair_hits needs CUDA tensors; the hot path has no CPU fallback")
+    ctx = ctx or Context.default(hits.device.index)
+    n = hits.shape[0] // 2
+    out = torch.empty((n, 4), dtype=torch.int32, device=hits.device)
+    check(lib().nvb_pair_hits(ctx.h, hits.data_ptr(), n, int(min_frag_len), int(max_frag_len), out.data_ptr(), current_stream_ptr()), ctx.h)
+    return out

@@ -133,3 +133,29 @@ int ORC(map_reads)(const orc_fmindex* fmi, const uint8_t* genome, const uint8_t*
     }
     return failed ? -2 : 0;
 }
+
+/* mate pairing over independently mapped mates (read 2 i / 2 i + 1): forward-reverse policy with a fragment-length window
+ * (nvBowtie/bowtie2/cuda/params.h:147-152); the composition is ours, see the header */
+int ORC(pair_hits)(const orc_read_hit* hits, uint32_t n_pairs, uint32_t min_frag, uint32_t max_frag, orc_pair_hit* out)
+{
+    for (uint32_t i = 0; i < n_pairs; ++i)
+    {
+        const orc_read_hit a = hits[2 * (size_t)i], b = hits[2 * (size_t)i + 1];
+        const int al1 = (a.flags & 2u) != 0, al2 = (b.flags & 2u) != 0;
+        orc_pair_hit o; o.score = INT32_MIN; o.frag_begin = o.frag_end = 0xFFFFFFFFu; o.flags = (al1 ? 1u : 0u) | (al2 ? 2u : 0u);
+        if (al1 && al2)
+        {
+            const int r1 = (a.flags & 1u) != 0, r2 = (b.flags & 1u) != 0;
+            const orc_read_hit* f = r1 ? &b : &a; const orc_read_hit* r = r1 ? &a : &b;
+            o.score = a.score + b.score;
+            o.frag_begin = a.begin < b.begin ? a.begin : b.begin;
+            o.frag_end = a.end > b.end ? a.end : b.end;
+            const uint32_t frag = r->end >= f->begin ? r->end - f->begin : 0u;
+            if (r1 != r2 && f->begin <= r->begin && f->end <= r->end && frag >= min_frag && frag <= max_frag) o.flags |= 4u;
+        }
+        else if (al1) { o.score = a.score; o.frag_begin = a.begin; o.frag_end = a.end; }
+        else if (al2) { o.score = b.score; o.frag_begin = b.begin; o.frag_end = b.end; }
+        out[i] = o;
+    }
+    return 0;
+}

@@ -14,6 +14,7 @@ ED, SW, GOTOH = 0, 1, 2
 GLOBAL, LOCAL, SEMI_GLOBAL = 0, 1, 2
 
 SINK_DT = np.dtype([("score", "<i4"), ("x", "<u4"), ("y", "<u4")])
+PAIR_DT = np.dtype([("score", "<i4"), ("frag_begin", "<u4"), ("frag_end", "<u4"), ("flags", "<u4")])
 SINK2_DT = np.dtype([("score1", "<i4"), ("score2", "<i4"), ("x1", "<u4"), ("y1", "<u4"), ("x2", "<u4"), ("y2", "<u4")])
 ALN_DT = np.dtype([("score", "<i4"), ("src_x", "<u4"), ("src_y", "<u4"), ("sink_x", "<u4"), ("sink_y", "<u4")])
 
@@ -257,3 +258,12 @@ class Oracle:
                                   _ptr(hits), _ptr(ops), C.c_uint32(stride), _ptr(ncand), C.c_int(threads))
         assert rc == 0, rc
         return hits, ops, ncand
+
+    def pair_hits(self, hits, min_frag, max_frag):
+        """mate pairing over independently mapped mates (hits[2 i], hits[2 i + 1]) -> PAIR_DT records"""
+        hits = np.ascontiguousarray(hits)
+        n = len(hits) // 2
+        out = np.zeros(n, dtype=PAIR_DT)
+        rc = self._f("pair_hits")(_ptr(hits), C.c_uint32(n), C.c_uint32(min_frag), C.c_uint32(max_frag), _ptr(out))
+        assert rc == 0, rc
+        return out

@@ -99,3 +99,47 @@ def test_map_reads_edges(oracle):
     # out-of-contract arguments fail loudly
     with pytest.raises(nvb.NvbError):
         nvb.map_reads(fmi, words, rs.symbols, rs.offsets, nvb.MapParams(nvb.GotohAligner(nvb.LOCAL, 2, -3, -6, -2)))
+
+
+def make_pairs(rng, genome, n, L=100, frag=(180, 420)):
+    """mate 1 = forward prefix, mate 2 = reverse complement of the suffix of a fragment; every 8th pair swaps the strands,
+    every 11th has an unrelated mate 2, every 13th a fragment longer than the window"""
+    G = len(genome)
+    reads = []
+    for i in range(n):
+        F = int(rng.integers(*frag)) if i % 13 else 900
+        p = int(rng.integers(0, G - F))
+        m1 = genome[p:p + L].copy()
+        m2 = (3 - genome[p + F - L:p + F])[::-1].copy()
+        if i % 11 == 10:
+            m2 = rng.integers(0, 4, L).astype(np.uint8)
+        for m in (m1, m2):
+            k = rng.random(L) < 0.01
+            m[k] = (m[k] + 1) % 4
+        if i % 8 == 7:
+            m1, m2 = m2, m1
+        reads += [np.ascontiguousarray(m1, dtype=np.uint8), np.ascontiguousarray(m2, dtype=np.uint8)]
+    return po.concat(reads)
+
+
+def test_pair_hits(oracle):
+    """nvb_pair_hits over independently mapped mates vs the oracle's pairing of the oracle's hits"""
+    rng = np.random.default_rng(99)
+    G = 80000
+    genome = rng.integers(0, 4, G).astype(np.uint8)
+    fmi, oidx = gu.fm_index_pair(oracle, genome)
+    words = nvb.pack_genome(torch.from_numpy(genome).to(gu.dev()))
+    R, Ro = make_pairs(rng, genome, 1500)
+    mp = nvb.MapParams(nvb.GotohAligner(nvb.SEMI_GLOBAL, 0, -5, -8, -3), max_hits=4, band=15, min_score=-60)
+    hits, _, _ = nvb.map_reads(fmi, words, torch.from_numpy(R).to(gu.dev()), torch.from_numpy(Ro.view(np.int32)).to(gu.dev()), mp)
+    want_hits, _, _ = oracle.map_reads(oidx, genome, R, Ro, map_util.map_params(min_score=-60))
+    assert (hits_np(hits).view(np.uint32) == want_hits.view(np.uint32)).all()
+    for lo, hi in ((0, 500), (200, 400), (0, 1000)):
+        got = nvb.pair_hits(hits, lo, hi).cpu().numpy().view(np.uint32).reshape(-1, 4).copy().view(nvb.PAIR_DT).reshape(-1)
+        want = oracle.pair_hits(want_hits, lo, hi)
+        assert (got.view(np.uint32) == want.view(np.uint32)).all()
+    got = oracle.pair_hits(want_hits, 0, 500)
+    conc = (got["flags"] & 4) != 0
+    idx = np.arange(len(got))
+    assert conc[(idx % 11 != 10) & (idx % 13 != 0)].mean() > 0.97       # sampled fragments pair up, whichever mate is forward
+    assert not conc[idx % 13 == 0].any()                                  # 900-bp fragments fall outside the window

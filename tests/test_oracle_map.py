@@ -39,3 +39,21 @@ def test_oracle_map_strands_and_limits(oracle):
     assert (both[f]["begin"] == fwd[f]["begin"]).all() and (both[f]["score"] == fwd[f]["score"]).all()
     none = oracle.map_reads(idx, genome, sym, off, map_util.map_params(min_score=1))[0]
     assert ((none["flags"] & 2) == 0).all()
+
+
+def test_pair_hits_rules(oracle):
+    """forward-reverse policy and fragment window of the pairing step on hand-made hits"""
+    H = np.zeros(12, dtype=po.HIT_DT)
+    def hit(i, begin, end, rev, score=-5, aligned=True):
+        H[i] = (score, -(1 << 30), begin, end, (2 if aligned else 0) | (1 if rev else 0), 0)
+    hit(0, 100, 200, False); hit(1, 300, 400, True)            # FR, fragment 300: concordant
+    hit(2, 300, 400, True);  hit(3, 100, 200, False)           # mates swapped: still concordant
+    hit(4, 100, 200, False); hit(5, 300, 400, False)           # same strand
+    hit(6, 300, 400, False); hit(7, 100, 200, True)            # RF (reverse mate upstream)
+    hit(8, 100, 200, False); hit(9, 0, 0, False, aligned=False)   # single
+    hit(10, 100, 200, False); hit(11, 900, 1000, True)         # fragment 900 > window
+    out = oracle.pair_hits(H, 0, 500)
+    assert list(out["flags"]) == [7, 7, 3, 3, 1, 3]
+    assert list(out["score"][:4]) == [-10, -10, -10, -10] and out["score"][4] == -5
+    assert (out["frag_begin"][0], out["frag_end"][0]) == (100, 400)
+    assert list(oracle.pair_hits(H, 350, 500)["flags"]) == [3, 3, 3, 3, 1, 3]
