@@ -143,7 +143,7 @@ __device__ __forceinline__ uint2 fm_locate_walk_one(const FMView& f, uint32_t j,
     return make_uint2(j, t);
 }
 
-// Many LF-walks per thread, load-balanced: walks take 0..15 steps, so a thread owns the strided list of walks
+// Many LF-walks per thread, load-balanced: walk lengths vary (geometric, 15 steps on average), so a thread owns the strided list of walks
 // first, first + stride, ... and starts its next one as soon as one ends; the warp vote keeps the loop converged.
 //   fetch(h) -> SA row of walk h ;  emit(h, sampled_row, steps)
 template <typename Fetch, typename Emit>

@@ -100,22 +100,24 @@ map_expand_kernel(const uint2* __restrict__ seeds, const uint32_t* __restrict__ 
     for (uint32_t t = 0; t < sd.y; ++t) rows[base + t] = make_uint2(sd.x + t, sl);
 }
 
-// LF-walk of every hit to its sampled SA row (locate_ssa_iterator, fmindex_inl.h:364-400). Walks take 0..15 steps:
+// LF-walk of every hit to its sampled SA row (locate_ssa_iterator, fmindex_inl.h:364-400). The sampled rows are every
+// 16th ROW of the suffix array, so a walk is a geometric trial: 15 steps on average, unbounded in principle (one in
+// 10^7 hits walks more than 255 steps -- seen on the 3.1 Gbp genome), hence 32-bit step counts:
 // each thread owns a strided list of hits and starts its next walk as soon as one ends, so the lanes of a warp do
 // not wait for the longest walk among them. rows[h].x becomes the sampled row, steps[h] the distance walked.
 __global__ void __launch_bounds__(MAP_THREADS)
-map_walk_kernel(const FMView f, uint32_t n_hits, uint2* __restrict__ rows, uint8_t* __restrict__ steps)
+map_walk_kernel(const FMView f, uint32_t n_hits, uint2* __restrict__ rows, uint32_t* __restrict__ steps)
 {
     __shared__ uint2 s_lut[FM_LUT_ENTRIES];
     fm_lut_init(s_lut);
     fm_walk_balanced(f, n_hits, blockIdx.x * MAP_THREADS + threadIdx.x, gridDim.x * MAP_THREADS, s_lut,
                      [&](uint32_t h) { return rows[h].x; },
-                     [&](uint32_t h, uint32_t j, uint32_t t) { rows[h].x = j; steps[h] = (uint8_t)t; });
+                     [&](uint32_t h, uint32_t j, uint32_t t) { rows[h].x = j; steps[h] = t; });
 }
 
 // sampled row + steps -> text position -> candidate key ((read * 2 + strand) << 32 | window begin)
 __global__ void __launch_bounds__(MAP_THREADS)
-map_keys_kernel(const FMView f, const MapGeom g, const uint2* __restrict__ rows, const uint8_t* __restrict__ steps,
+map_keys_kernel(const FMView f, const MapGeom g, const uint2* __restrict__ rows, const uint32_t* __restrict__ steps,
                 uint32_t n_hits, uint64_t* __restrict__ keys)
 {
     const uint32_t h = blockIdx.x * MAP_THREADS + threadIdx.x;
@@ -514,11 +516,11 @@ extern "C" int nvb_map_reads(nvb_ctx* ctx, const nvb_fmindex* fmi, const uint32_
             if (n_hits)
             {
                 // ---- locate + candidate keys, de-duplicated per read
-                uint2* rows; uint8_t* steps;
+                uint2* rows; uint32_t* steps;
                 MAP_STAGE(S_KEYS_A, sizeof(uint64_t) * (size_t)n_hits, keys_a);
                 MAP_STAGE(S_KEYS_B, sizeof(uint64_t) * (size_t)n_hits, keys_b);
                 MAP_STAGE(S_ROWS, sizeof(uint2) * (size_t)n_hits, rows);
-                MAP_STAGE(S_STEPS, (size_t)n_hits, steps);
+                MAP_STAGE(S_STEPS, sizeof(uint32_t) * (size_t)n_hits, steps);
                 map_expand_kernel<<<map_grid(n_slots), MAP_THREADS, 0, s>>>(seeds, scan, n_slots, rows);
                 NVB_LAUNCHED(ctx);
                 {

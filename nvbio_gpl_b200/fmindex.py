@@ -97,6 +97,30 @@ class FMIndex:
 # ------------------------------------------------------------------------------------------------
 # synthetic index construction (not on the hot path)
 # ------------------------------------------------------------------------------------------------
+_SORT_MAX = (1 << 31) - 2      # torch.sort refuses dimensions above INT_MAX
+
+
+def _sort_with_index(key):
+    """(sorted keys, permutation) of an int64 key vector of any length: torch.sort where it applies, else the two halves are
+    sorted separately and merged by rank (searchsorted); equal keys keep their original order"""
+    m = key.numel()
+    if m <= _SORT_MAX:
+        return torch.sort(key, stable=True)
+    h = m // 2
+    ka, ia = torch.sort(key[:h], stable=True)
+    kb, ib = torch.sort(key[h:], stable=True)
+    ib += h
+    del key
+    pa = torch.searchsorted(kb, ka, right=False); pa += torch.arange(h, device=ka.device)
+    ks = torch.empty(m, dtype=torch.int64, device=ka.device); idx = torch.empty(m, dtype=torch.int64, device=ka.device)
+    ks[pa] = ka; idx[pa] = ia
+    del pa, ia
+    pb = torch.searchsorted(ka, kb, right=True); pb += torch.arange(m - h, device=kb.device)
+    del ka
+    ks[pb] = kb; idx[pb] = ib
+    return ks, idx
+
+
 def suffix_array(text):
     """suffix array of the n+1 suffixes of ``text`` (the empty suffix sorts first), prefix doubling"""
     dev = text.device
@@ -107,13 +131,14 @@ def suffix_array(text):
     K = 21
     pad = torch.zeros(K, dtype=torch.int64, device=dev)
     tp = torch.cat([t + 1, pad])
+    del t
     key = torch.zeros(m, dtype=torch.int64, device=dev)
     for k in range(K):
         key = key * 8 + tp[k:k + m]
     del tp
     h = K
     while True:
-        ks, idx = torch.sort(key)
+        ks, idx = _sort_with_index(key)
         del key
         flag = torch.ones(m, dtype=torch.int64, device=dev)
         flag[1:] = (ks[1:] != ks[:-1]).to(torch.int64)
@@ -128,7 +153,7 @@ def suffix_array(text):
         nxt = torch.zeros(m, dtype=torch.int64, device=dev)
         if h < m:
             nxt[:m - h] = rank[h:]
-        key = rank * (m + 1) + nxt
+        key = ((rank - (1 << 31)) << 32) + nxt      # (rank, next rank) as one signed key; both fit 32 bits for any uint32 text length
         del rank, nxt
         h *= 2
 
