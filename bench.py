@@ -37,9 +37,10 @@ def parse():
     ap.add_argument("--banded-pairs", type=int, default=10_000_000)
     ap.add_argument("--reads", type=int, default=10_000_000, help="reads of the seed+extend leg (configs[3] shape, 150 bp)")
     ap.add_argument("--pairs", type=int, default=5_000_000, help="read pairs of the paired-end leg (configs[4] shape, 2 x 150 bp)")
+    ap.add_argument("--c4-genome", type=int, default=3_100_000_000, help="genome of the configs[3]/[4] leg at its named size (0 = skip)")
     ap.add_argument("--no-extra", action="store_true", help="skip the SW / banded secondary measurements")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
-    ap.add_argument("--only", default="", help="profiling aid: run only this leg (fm|sw|banded|map) with no cpu leg")
+    ap.add_argument("--only", default="", help="profiling aid: run only this leg (fm|sw|banded|map|c4) with no cpu leg")
     return ap.parse_args()
 
 
@@ -274,14 +275,27 @@ def run_b200(args):
     only = args.only
     out = {}
     # ---------------- index: built once on rank 0, replicated over NVLink (outside the timed region)
-    t0 = time.time()
-    if only in ("", "fm", "map"):
+    def make_index(n_symbols):
+        """(genome, fmi, seconds); raises on every rank if rank 0 could not build it"""
+        t0 = time.time()
+        genome = fmi = None
+        ok = torch.ones(1, dtype=torch.int64, device=dev)
+        err = None
         if rank == 0:
-            genome = gen_genome(args.genome, 2, dev)
-            fmi = nvb.build_index(genome)
-            meta = torch.tensor([fmi.length, fmi.primary] + fmi.L2, dtype=torch.int64, device=dev)
+            try:
+                genome = gen_genome(n_symbols, 2, dev)
+                fmi = nvb.build_index(genome)
+                meta = torch.tensor([fmi.length, fmi.primary] + fmi.L2, dtype=torch.int64, device=dev)
+            except Exception as e:          # noqa: BLE001 -- e.g. out of memory on the 3.1 Gbp suffix sort
+                err = e; ok[0] = 0; genome = fmi = None
+                torch.cuda.empty_cache()
+                meta = torch.zeros(7, dtype=torch.int64, device=dev)
         else:
             meta = torch.zeros(7, dtype=torch.int64, device=dev)
+        if world > 1:
+            dist.broadcast(ok, 0)
+        if int(ok.item()) == 0:
+            raise RuntimeError("index build failed on rank 0: %s" % (str(err)[:200] if err else "see rank 0"))
         if world > 1:
             dist.broadcast(meta, 0)
             if rank != 0:
@@ -291,7 +305,14 @@ def run_b200(args):
                                   torch.empty(nvb.lib().nvb_bwt_occ_words(n), dtype=torch.int32, device=dev),
                                   torch.empty(nvb.lib().nvb_ssa_words(n), dtype=torch.int32, device=dev))
             dist.broadcast(genome, 0); dist.broadcast(fmi.bwt_occ, 0); dist.broadcast(fmi.ssa, 0)
-        build_s = time.time() - t0
+        torch.cuda.synchronize()
+        return genome, fmi, time.time() - t0
+
+    genome = fmi = None
+    index_bytes = 0
+    if only in ("", "fm", "map"):
+        genome, fmi, build_s = make_index(args.genome)
+        index_bytes = int(fmi.bwt_occ.numel() * 4)
     if only in ("", "fm"):
         qsym, qoff = gen_queries(genome, args.queries, 100 + rank, dev)
         nq = args.queries
@@ -419,8 +440,8 @@ def run_b200(args):
         del hs, ho, hr
 
     # ---------------- seed -> locate -> extend -> traceback over 150-bp reads (configs[3] shape on this leg's genome)
-    if only == "map" or (only == "" and not args.no_extra):
-        RL, nr = 150, args.reads
+    def map_leg(genome, fmi, nr, npairs, tag, ptag):
+        RL = 150
         words = nvb.pack_genome(genome, ctx=ctx)
         fmi.build_ktab(10, ctx=ctx)          # seeding starts from the 10-mer jump table (identical ranges)
         rsym, roff = gen_reads(genome, nr, RL, 7 + rank, dev)
@@ -437,7 +458,7 @@ def run_b200(args):
         tms = time_steps(_map, max(2, args.steps // 3), 1, flush)
         ms = max_over_ranks(sum(tms) / len(tms))
         hits_d, ops_d, mstats = res["r"]
-        out["map"] = dict(reads_per_s=world * nr / (ms * 1e-3), ms=ms, reads=nr, read_len=RL, launches_per_call=per_call,
+        out[tag] = dict(reads_per_s=world * nr / (ms * 1e-3), ms=ms, reads=nr, read_len=RL, launches_per_call=per_call,
                           seed_hits_per_read=mstats["seed_hits"] / nr, candidates_per_read=mstats["candidates"] / nr,
                           aligned_frac=mstats["aligned"] / nr, genome=int(genome.numel()),
                           params="20-mer seeds every 10 bp on both strands (10-mer jump table), <= 4 rows per seed, banded (15) Gotoh (0,-5,-8,-3) "
@@ -456,12 +477,12 @@ def run_b200(args):
         for _ in range(3):
             t0_ = time.time(); nvb.map_reads_host(*args_h, hits_h=hh_n, cigar_h=hcig.numpy().view(np.uint16), max_read_len=RL, ctx=ctx); t_e.append(time.time() - t0_)
         e_ms = max_over_ranks(min(t_e) * 1e3)
-        out["map"]["e2e"] = dict(reads_per_s=world * nr / (e_ms * 1e-3), ms=e_ms, h2d_bytes=int(hr_sym.numel() + hr_off.numel() * 4),
+        out[tag]["e2e"] = dict(reads_per_s=world * nr / (e_ms * 1e-3), ms=e_ms, h2d_bytes=int(hr_sym.numel() + hr_off.numel() * 4),
                                  d2h_bytes=int(hh.numel() * 4 + hcig.numel() * 2), result="hits + io::Cigar (16 entries per read)")
         t0_ = time.time(); nvb.map_reads_host(*args_h, hits_h=hh_n, ops_h=hops.numpy(), max_read_len=RL, ctx=ctx); o_ms = (time.time() - t0_) * 1e3
-        out["map"]["e2e_op_lists"] = dict(reads_per_s=nr / (o_ms * 1e-3), ms=o_ms, d2h_bytes=int(hh.numel() * 4 + hops.numel()))
+        out[tag]["e2e_op_lists"] = dict(reads_per_s=nr / (o_ms * 1e-3), ms=o_ms, d2h_bytes=int(hh.numel() * 4 + hops.numel()))
         assert (hh.numpy() == hits_d.cpu().numpy()).all(), "host and device pipeline entry points disagree"
-        if rank == 0 and world == 1 and not args.no_cpu and only in ("", "map"):
+        if rank == 0 and world == 1 and not args.no_cpu and only in ("", "map", "c4"):
             po, chk, kind = load_checker()
             bwt_occ, ssa = fmi.host_arrays()
             oidx = po.Index(fmi.length, fmi.primary, np.array(fmi.L2, dtype=np.uint32), bwt_occ, ssa)
@@ -475,14 +496,13 @@ def run_b200(args):
             mism = int((got_h.view(np.uint32).reshape(k, 6) != wh.view(np.uint32).reshape(k, 6)).any(axis=1).sum())
             valid = np.arange(stride)[None, :] < wh["n_ops"][:, None]
             mism_ops = int(((got_o != wo) & valid).any(axis=1).sum())
-            out["map"]["cpu"] = dict(reads_per_s=k / dt, cores=host_threads(), kind=kind, sample="first %d reads" % k)
-            out["map"]["parity"] = dict(checked=k, hit_mismatches=mism, ops_mismatches=mism_ops)
+            out[tag]["cpu"] = dict(reads_per_s=k / dt, cores=host_threads(), kind=kind, sample="first %d reads" % k)
+            out[tag]["parity"] = dict(checked=k, hit_mismatches=mism, ops_mismatches=mism_ops)
             del gh
         del hr_sym, hr_off, hh, hops, hcig, rsym, roff, res, hits_d, ops_d
 
         # ---- paired-end (configs[4] shape): both mates mapped independently (2 x pairs reads), then nvb_pair_hits
-        if args.pairs > 0:
-            npairs = args.pairs
+        if npairs > 0:
             msym, moff = gen_mates(genome, npairs, RL, 11 + rank, dev)
             pres = {}
             def _pairs():
@@ -493,12 +513,16 @@ def run_b200(args):
             tms = time_steps(_pairs, max(2, args.steps // 3), 1, flush)
             ms = max_over_ranks(sum(tms) / len(tms))
             fl = pres["p"][:, 3]
-            out["pairs"] = dict(pairs_per_s=world * npairs / (ms * 1e-3), ms=ms, pairs=npairs, read_len=RL, fragment="250..499 bp, FR",
+            out[ptag] = dict(pairs_per_s=world * npairs / (ms * 1e-3), ms=ms, pairs=npairs, read_len=RL, fragment="250..499 bp, FR",
                                 concordant_frac=float(((fl & 4) != 0).float().mean().item()),
                                 both_aligned_frac=float(((fl & 3) == 3).float().mean().item()),
                                 note="mates mapped independently (seed, locate, banded Gotoh, traceback for the coordinates; op lists not kept), then nvb_pair_hits (FR, fragment <= 500)")
             del msym, moff, pres
         del words
+        fmi.drop_ktab()
+
+    if only == "map" or (only == "" and not args.no_extra):
+        map_leg(genome, fmi, args.reads, args.pairs, "map", "pairs")
 
     # ---------------- secondary: SW local scoring (configs[0]) and banded scoring/traceback (configs[2])
     if not args.no_extra or only in ("sw", "banded"):
@@ -567,6 +591,19 @@ def run_b200(args):
                 del ttemp, bufs
             out["banded"] = dict(pairs=n, M=M, N=N, band=W, **res)
 
+    # ---------------- configs[3] / configs[4] at their named genome size (3.1 Gbp): a second index, built after everything
+    # else has been measured and freed; a failure (memory) is recorded instead of ending the run
+    if only == "c4" or (only == "" and not args.no_extra and args.c4_genome > 0):
+        genome = fmi = None
+        torch.cuda.empty_cache()
+        try:
+            genome, fmi, c4_build_s = make_index(args.c4_genome)
+            map_leg(genome, fmi, args.reads, args.pairs, "map_c4", "pairs_c4")
+            out["map_c4"]["index_build_s"] = round(c4_build_s, 2)
+        except Exception as e:              # noqa: BLE001
+            out["map_c4"] = {"error": str(e)[:300], "genome": args.c4_genome}
+        genome = fmi = None
+
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -595,7 +632,7 @@ def run_b200(args):
                     config={"workload": "configs[1]: FM-index exact 20-mer backward search, %d queries per GPU on a synthetic %d bp 2-bit genome"
                                         % (args.queries, args.genome),
                             "queries": "90% cut from the genome, 10% random, 0.1% with an N, unsorted",
-                            "index_bytes": int(fmi.bwt_occ.numel() * 4), "partition": "queries sharded, index replicated, no collective",
+                            "index_bytes": index_bytes, "partition": "queries sharded, index replicated, no collective",
                             "l2": "flushed (256 MiB write) between timed steps, outside the event-timed region",
                             "index_build_s": round(fm["build_s"], 2),
                             "e2e_8bit_symbols_with_offsets": fm.get("e2e"), "e2e_packed4_with_offsets": fm.get("e2e_packed4"),
@@ -621,7 +658,7 @@ def run_b200(args):
         for k, kind in (("ed_semi", "ed"), ("gotoh_semi", "gotoh"), ("sw_semi", "sw"), ("sw_local", "sw")):
             if k in out["banded"]:
                 out["banded"][k]["roofline"] = _roof(out["banded"][k]["gcups"], kind)
-    extra = {k: out[k] for k in ("sw", "banded", "map", "pairs") if k in out}
+    extra = {k: out[k] for k in ("sw", "banded", "map", "pairs", "map_c4", "pairs_c4") if k in out}
     if extra:
         line["extra"] = extra
     print(json.dumps(line))
