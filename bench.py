@@ -640,7 +640,10 @@ def run_b200(args):
         if alg_per_q:
             ach = alg_per_q * args.queries / (fm["kernel_ms"] * 1e-3) / 1e9
             line["roofline"] = {"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
-                                "traffic": None, "kernel": "fm_match_kernel<8,false>", "peak_source": peak_src,
+                                # dram__bytes_read.sum + dram__bytes_write.sum of one fm_match launch of THIS workload under ncu --set full
+                                # (profiles/r1h_fm_match_ncu_full.csv; the 50 MB index is L2-resident, so it is far below the algorithmic bytes)
+                                "traffic": 902.7e6 if (args.genome == 100_000_000 and args.queries == 10_000_000) else None,
+                                "kernel": "fm_match_kernel<8,false,false>", "peak_source": peak_src,
                                 "algorithmic_bytes_per_query": alg_per_q, "blocks_per_query": bpq}
         if "cpu" in fm:
             line["cpu_baseline"] = fm["cpu"]
