@@ -356,7 +356,18 @@ def run_b200(args):
         tl = time_steps(_locate, max(3, args.steps // 2), 2, flush)
         l_ms = max_over_ranks(sum(tl) / len(tl))
         out["fm"]["locate"] = dict(value=world * nq / (l_ms * 1e-3), unit="locates/s", ms_per_step=l_ms, rows=nq)
-        del lrows, lpos
+        # the same rows through the optional 4-row sampled SA (identical positions, a quarter of the walk)
+        lpos0 = lpos.clone()
+        fmi.build_dssa(4, ctx=ctx)
+        fcd = fmi.c()
+        def _locate_d():
+            check(L.nvb_fm_locate(ctx.h, ctypes.byref(fcd), lrows.data_ptr(), nq, lpos.data_ptr(), current_stream_ptr()), ctx.h)
+        tl = time_steps(_locate_d, max(3, args.steps // 2), 2, flush)
+        l_ms = max_over_ranks(sum(tl) / len(tl))
+        assert bool((lpos == lpos0).all().item()), "the denser sampled SA changed a position"
+        out["fm"]["locate"]["with_4_row_ssa"] = dict(value=world * nq / (l_ms * 1e-3), ms_per_step=l_ms, table_bytes=int(fmi.dssa.numel() * 4))
+        fmi.drop_dssa()
+        del lrows, lpos, lpos0
 
         # ---- e2e: host buffers (pinned) through the C-ABI *_host call: H2D + kernel + D2H per step
         hs = torch.empty(qsym.numel(), dtype=torch.uint8).pin_memory(); hs.copy_(qsym)
@@ -443,7 +454,11 @@ def run_b200(args):
     def map_leg(genome, fmi, nr, npairs, tag, ptag):
         RL = 150
         words = nvb.pack_genome(genome, ctx=ctx)
-        fmi.build_ktab(10, ctx=ctx)          # seeding starts from the 10-mer jump table (identical ranges)
+        # index-side optional structures (identical results): k-mer jump table for seeding (k = 10 while index + table fit L2,
+        # 13 on a DRAM-resident index) and a 4-row sampled SA for the locate walks
+        kk = int(os.environ.get("KTAB_K", 10 if genome.numel() <= 400_000_000 else 13))
+        fmi.build_ktab(kk, ctx=ctx)
+        fmi.build_dssa(4, ctx=ctx)
         rsym, roff = gen_reads(genome, nr, RL, 7 + rank, dev)
         mparams = nvb.MapParams(nvb.GotohAligner(nvb.SEMI_GLOBAL, 0, -5, -8, -3), seed_len=20, seed_interval=10, max_hits=4,
                                 max_range=0, band=15, both_strands=True, min_score=-90)
@@ -461,8 +476,9 @@ def run_b200(args):
         out[tag] = dict(reads_per_s=world * nr / (ms * 1e-3), ms=ms, reads=nr, read_len=RL, launches_per_call=per_call,
                           seed_hits_per_read=mstats["seed_hits"] / nr, candidates_per_read=mstats["candidates"] / nr,
                           aligned_frac=mstats["aligned"] / nr, genome=int(genome.numel()),
-                          params="20-mer seeds every 10 bp on both strands (10-mer jump table), <= 4 rows per seed, banded (15) Gotoh (0,-5,-8,-3) "
-                                 "SEMI_GLOBAL, min score -90, traceback of the best window")
+                          params="20-mer seeds every 10 bp on both strands (%d-mer jump table, %d MB; 4-row sampled SA, %d MB), <= 4 rows per seed, "
+                                 "banded (15) Gotoh (0,-5,-8,-3) SEMI_GLOBAL, min score -90, traceback of the best window"
+                                 % (kk, fmi.ktab.numel() * 4 >> 20, fmi.dssa.numel() * 4 >> 20))
         # e2e: pinned host reads in; hits + CIGARs out (the SAM-facing result), and once with the raw op lists for the parity check
         hr_sym = torch.empty(rsym.numel(), dtype=torch.uint8).pin_memory(); hr_sym.copy_(rsym)
         hr_off = torch.empty(roff.numel(), dtype=torch.int32).pin_memory(); hr_off.copy_(roff)
@@ -519,7 +535,7 @@ def run_b200(args):
                                 note="mates mapped independently (seed, locate, banded Gotoh, traceback for the coordinates; op lists not kept), then nvb_pair_hits (FR, fragment <= 500)")
             del msym, moff, pres
         del words
-        fmi.drop_ktab()
+        fmi.drop_ktab(); fmi.drop_dssa()
 
     if only == "map" or (only == "" and not args.no_extra):
         map_leg(genome, fmi, args.reads, args.pairs, "map", "pairs")

@@ -63,6 +63,8 @@ typedef struct {
     const uint32_t* ssa;        /* (length+16)/16 entries, ssa[0] = 0xFFFFFFFF; may be NULL     */
     const uint32_t* ktab;       /* optional k-mer jump table (nvb_fmindex_build_ktab), else NULL */
     uint32_t        ktab_k;     /* symbols per table entry (0 = no table)                       */
+    const uint32_t* dssa;       /* optional denser sampled SA (nvb_fmindex_build_dssa), else NULL */
+    uint32_t        dssa_int;   /* its row interval: 2, 4 or 8 (0 = none)                       */
 } nvb_fmindex;
 
 /* ConcatenatedStringSet<symbols, offsets> (nvbio/strings/string_set.h:405-492) */
@@ -142,6 +144,13 @@ int nvb_fmindex_save(nvb_ctx* ctx, const nvb_fmindex* fmi_d, const char* prefix,
 size_t nvb_ktab_words(uint32_t k);
 int nvb_fmindex_build_ktab(nvb_ctx* ctx, const nvb_fmindex* fmi_d, uint32_t k, uint32_t* ktab_d, void* stream);
 int nvb_fmindex_pin_l2(nvb_ctx* ctx, const nvb_fmindex* fmi_d, size_t bytes);
+/* Optional denser sampled suffix array: entry i = locate(fmi, i * sa_int) computed once through the index's own SSA
+ * (sa_int = 2, 4 or 8; (length + sa_int) / sa_int entries). With fmi->dssa set, every locate (nvb_fm_locate[_walk/_lookup],
+ * nvb_fm_filter_locate, nvb_map_reads) stops its LF walk at the first row that is a multiple of sa_int instead of 16 and
+ * reads the position there: the same positions, bit for bit, after a quarter (sa_int = 4) of the walk. Like the k-mer
+ * table it is an index-side structure in the caller's memory; the nvBWT files and the reference layout are unchanged. */
+size_t nvb_dssa_words(uint32_t length, uint32_t sa_int);
+int nvb_fmindex_build_dssa(nvb_ctx* ctx, const nvb_fmindex* fmi_d, uint32_t sa_int, uint32_t* dssa_d, void* stream);
 /* fuse a plain BWT (2-bit big-endian words, as in a .bwt file: nvBWT/nvBWT.cu:303-321) into the
  * interleaved bwt|occ image and compute L2; all pointers DEVICE; bwt_occ_out has
  * nvb_bwt_occ_words(length) words. Replaces nvbio/io/fmindex/fmindex_impl.cu:283-318 +

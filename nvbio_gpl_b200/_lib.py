@@ -17,7 +17,8 @@ class NvbError(RuntimeError):
 class FMIndexC(C.Structure):
     _fields_ = [("length", C.c_uint32), ("primary", C.c_uint32), ("L2", C.c_uint32 * 5),
                 ("occ_int", C.c_uint32), ("sa_int", C.c_uint32),
-                ("bwt_occ", C.c_void_p), ("ssa", C.c_void_p), ("ktab", C.c_void_p), ("ktab_k", C.c_uint32)]
+                ("bwt_occ", C.c_void_p), ("ssa", C.c_void_p), ("ktab", C.c_void_p), ("ktab_k", C.c_uint32),
+                ("dssa", C.c_void_p), ("dssa_int", C.c_uint32)]
 
 
 class StringSetC(C.Structure):
@@ -68,6 +69,8 @@ _PROTOS = {
     "nvb_fmindex_pin_l2": (_i, [_vp, C.POINTER(FMIndexC), _sz]),
     "nvb_ktab_words": (_sz, [_u32]),
     "nvb_fmindex_build_ktab": (_i, [_vp, C.POINTER(FMIndexC), _u32, _vp, _vp]),
+    "nvb_dssa_words": (_sz, [_u32, _u32]),
+    "nvb_fmindex_build_dssa": (_i, [_vp, C.POINTER(FMIndexC), _u32, _vp, _vp]),
     "nvb_bwt_occ_words": (_sz, [_u32]),
     "nvb_ssa_words": (_sz, [_u32]),
     "nvb_fmindex_fuse": (_i, [_vp, _vp, _u32, _vp, _vp, _vp]),

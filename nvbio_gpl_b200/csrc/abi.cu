@@ -109,7 +109,7 @@ extern "C" int nvb_fmindex_upload(nvb_ctx* ctx, const nvb_fmindex* h, nvb_fminde
 {
     if (!ctx || !h || !d || !h->bwt_occ) return NVB_ERR_ARG;
     if (h->occ_int != 64u || h->sa_int != 16u) return NVB_ERR_UNSUPPORTED;
-    *d = *h; d->bwt_occ = nullptr; d->ssa = nullptr; d->ktab = nullptr; d->ktab_k = 0;
+    *d = *h; d->bwt_occ = nullptr; d->ssa = nullptr; d->ktab = nullptr; d->ktab_k = 0; d->dssa = nullptr; d->dssa_int = 0;
     const size_t bw = nvb_bwt_occ_words(h->length) * sizeof(uint32_t);
     void* p = nullptr;
     NVB_CUDA(ctx, cudaMalloc(&p, bw ? bw : 32));

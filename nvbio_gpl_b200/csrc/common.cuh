@@ -54,6 +54,8 @@ struct FMView
     const uint32_t* ssa;
     const uint2*    ktab;     // k-mer jump table (optional)
     uint32_t        ktab_k;
+    const uint32_t* sa_tab;   // the sampled SA the walks end on: ssa (rows % 16 == 0) or the optional denser one
+    uint32_t        sa_mask, sa_shift;
 };
 
 static inline FMView make_view(const nvb_fmindex* f)
@@ -63,6 +65,9 @@ static inline FMView make_view(const nvb_fmindex* f)
     for (int i = 0; i < 5; ++i) v.L2[i] = f->L2[i];
     v.blk = (const uint4*)f->bwt_occ; v.ssa = f->ssa;
     v.ktab = (const uint2*)f->ktab; v.ktab_k = f->ktab ? f->ktab_k : 0u;
+    v.sa_tab = f->ssa; v.sa_mask = 15u; v.sa_shift = 4u;
+    if (f->dssa && (f->dssa_int == 2u || f->dssa_int == 4u || f->dssa_int == 8u))
+    { v.sa_tab = f->dssa; v.sa_mask = f->dssa_int - 1u; v.sa_shift = f->dssa_int == 2u ? 1u : f->dssa_int == 4u ? 2u : 3u; }
     return v;
 }
 

@@ -124,7 +124,7 @@ __device__ __forceinline__ uint32_t fm_bwt_symbol(const FMBlock& b, uint32_t pos
 __device__ __forceinline__ uint2 fm_locate_walk_one(const FMView& f, uint32_t j, const uint2* lut)
 {
     uint32_t t = 0;
-    while (j & 15u)
+    while (j & f.sa_mask)
     {
         if (j != f.primary)
         {
@@ -157,7 +157,7 @@ __device__ __forceinline__ void fm_walk_balanced(const FMView& f, uint32_t n, ui
     uint32_t jn = (alive && hn < n) ? fetch(hn) : 0u;          // the next walk's row is fetched one walk ahead
     while (__any_sync(0xFFFFFFFFu, alive))
     {
-        if (alive && (j & 15u) == 0u)
+        if (alive && (j & f.sa_mask) == 0u)
         {
             emit(h, j, t);
             h = hn; j = jn; t = 0;
@@ -165,7 +165,7 @@ __device__ __forceinline__ void fm_walk_balanced(const FMView& f, uint32_t n, ui
             hn = h + stride;
             jn = (alive && hn < n) ? fetch(hn) : 0u;
         }
-        if (alive && (j & 15u) != 0u)
+        if (alive && (j & f.sa_mask) != 0u)
         {
             uint32_t nj = 0;                                    // j == primary -> 0 (fmindex_inl.h:380-383)
             if (j != f.primary)

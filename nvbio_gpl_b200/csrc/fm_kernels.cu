@@ -135,7 +135,7 @@ fm_locate_kernel(const FMView f, const uint32_t* __restrict__ rows, uint32_t n, 
     fm_lut_init(s_lut);
     fm_walk_balanced(f, n, blockIdx.x * FM_THREADS + threadIdx.x, gridDim.x * FM_THREADS, s_lut,
                      [&](uint32_t h) { return __ldg(rows + h); },
-                     [&](uint32_t h, uint32_t j, uint32_t t) { pos[h] = __ldg(f.ssa + (j >> 4)) + t; });
+                     [&](uint32_t h, uint32_t j, uint32_t t) { pos[h] = __ldg(f.sa_tab + (j >> f.sa_shift)) + t; });
 }
 
 __global__ void __launch_bounds__(FM_THREADS)
@@ -154,7 +154,7 @@ fm_locate_lookup_kernel(const FMView f, const uint32_t* __restrict__ walk, uint3
     const uint32_t tid = blockIdx.x * FM_THREADS + threadIdx.x;
     if (tid >= n) return;
     const uint2 w = *(const uint2*)(walk + 2 * (size_t)tid);
-    pos[tid] = __ldg(f.ssa + (w.x >> 4)) + w.y;
+    pos[tid] = __ldg(f.sa_tab + (w.x >> f.sa_shift)) + w.y;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -267,6 +267,32 @@ extern "C" int nvb_fmindex_build_ktab(nvb_ctx* ctx, const nvb_fmindex* fmi, uint
     return NVB_OK;
 }
 
+// denser sampled SA: entry i = locate(fmi, i * sa_int) through the index's own SSA (rows are generated on the fly)
+__global__ void __launch_bounds__(FM_THREADS)
+fm_dssa_kernel(const FMView f, uint32_t shift, uint32_t n, uint32_t* __restrict__ out)
+{
+    __shared__ uint2 s_lut[FM_LUT_ENTRIES];
+    fm_lut_init(s_lut);
+    fm_walk_balanced(f, n, blockIdx.x * FM_THREADS + threadIdx.x, gridDim.x * FM_THREADS, s_lut,
+                     [&](uint32_t h) { return h << shift; },
+                     [&](uint32_t h, uint32_t j, uint32_t t) { out[h] = __ldg(f.sa_tab + (j >> f.sa_shift)) + t; });
+}
+
+extern "C" size_t nvb_dssa_words(uint32_t length, uint32_t sa_int)
+{ return (sa_int == 2u || sa_int == 4u || sa_int == 8u) ? ((size_t)length + sa_int) / sa_int : 0; }
+
+extern "C" int nvb_fmindex_build_dssa(nvb_ctx* ctx, const nvb_fmindex* fmi, uint32_t sa_int, uint32_t* dssa, void* stream)
+{
+    if (!ctx || !dssa || !(sa_int == 2u || sa_int == 4u || sa_int == 8u)) return NVB_ERR_ARG;
+    int rc = check_fmi(fmi, true); if (rc) return rc;
+    nvb_fmindex plain = *fmi; plain.dssa = nullptr; plain.dssa_int = 0;      // always derived from the 16-row SSA
+    const FMView f = make_view(&plain);
+    const uint32_t n = (uint32_t)nvb_dssa_words(fmi->length, sa_int);
+    fm_dssa_kernel<<<walk_grid(ctx, n), FM_THREADS, 0, (cudaStream_t)stream>>>(f, sa_int == 2u ? 1u : sa_int == 4u ? 2u : 3u, n, dssa);
+    NVB_LAUNCHED(ctx);
+    return NVB_OK;
+}
+
 extern "C" int nvb_fm_match(nvb_ctx* ctx, const nvb_fmindex* fmi, nvb_string_set queries, uint32_t* ranges, void* stream)
 { return fm_match_launch<false>(ctx, fmi, queries, ranges, stream); }
 
@@ -367,7 +393,7 @@ fm_filter_locate_kernel(const FMView f, const uint32_t* __restrict__ ranges, con
         const uint64_t base = slot ? __ldg(slots + slot - 1) : 0ull;
         const uint32_t row = __ldg(ranges + 2 * (size_t)slot) + (uint32_t)(out - base);
         const uint2 w = fm_locate_walk_one(f, row, s_lut);
-        pos = __ldg(f.ssa + (w.x >> 4)) + w.y;
+        pos = __ldg(f.sa_tab + (w.x >> f.sa_shift)) + w.y;
     }
     *(uint2*)(hits + 2 * tid) = make_uint2(pos, slot);
 }

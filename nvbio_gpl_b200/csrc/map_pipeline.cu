@@ -21,6 +21,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <climits>
+#include <chrono>
 #include <vector>
 
 #define MAP_THREADS 256
@@ -123,7 +124,7 @@ map_keys_kernel(const FMView f, const MapGeom g, const uint2* __restrict__ rows,
     const uint32_t h = blockIdx.x * MAP_THREADS + threadIdx.x;
     if (h >= n_hits) return;
     const uint2 rec = rows[h];
-    const uint32_t pos = __ldg(f.ssa + (rec.x >> 4)) + steps[h];
+    const uint32_t pos = __ldg(f.sa_tab + (rec.x >> f.sa_shift)) + steps[h];
     const uint32_t per_read = g.S * g.n_strands;
     const uint32_t r = rec.y / per_read, rem = rec.y - r * per_read, strand = rem / g.S, k = rem - strand * g.S;
     const uint32_t o = k * g.interval;
@@ -347,9 +348,10 @@ extern "C" int nvb_pack_2bit(nvb_ctx* ctx, const uint8_t* symbols_d, uint32_t n,
 struct MapTrace
 {
     enum { SEED, LOCATE, SORT, EXTRACT, SCORE, REDUCE, TB_EXTRACT, TRACEBACK, FINISH, N_PHASES };
-    bool on; cudaStream_t s; cudaEvent_t ev[2]; float ms[N_PHASES]; int cur;
+    bool on; cudaStream_t s; cudaEvent_t ev[2]; float ms[N_PHASES]; int cur; std::chrono::steady_clock::time_point t0;
     MapTrace(cudaStream_t st) : on(false), s(st), cur(0)
     {
+        t0 = std::chrono::steady_clock::now();
         const char* e = getenv("NVB_MAP_TRACE");
         on = e && e[0] == '1';
         for (int i = 0; i < N_PHASES; ++i) ms[i] = 0.f;
@@ -366,7 +368,9 @@ struct MapTrace
         if (!on) return;
         static const char* names[N_PHASES] = { "seed+scan", "locate", "sort+unique", "extract", "score", "reduce+select", "tb extract", "traceback", "finish" };
         float tot = 0.f; for (int i = 0; i < N_PHASES; ++i) tot += ms[i];
-        fprintf(stderr, "[nvb_map_reads] %.3f ms:", tot);
+        cudaStreamSynchronize(s);
+        const double wall = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+        fprintf(stderr, "[nvb_map_reads] wall %.3f ms, phases %.3f ms:", wall, tot);
         for (int i = 0; i < N_PHASES; ++i) fprintf(stderr, " %s %.3f |", names[i], ms[i]);
         fprintf(stderr, "\n");
         cudaEventDestroy(ev[0]); cudaEventDestroy(ev[1]);

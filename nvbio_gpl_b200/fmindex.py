@@ -40,6 +40,7 @@ class FMIndex:
         self.bwt_occ = bwt_occ      # torch.int32 [nvb_bwt_occ_words(length)]
         self.ssa = ssa              # torch.int32 [(length+16)//16] or None
         self.ktab, self.ktab_k = None, 0   # optional k-mer jump table (build_ktab)
+        self.dssa, self.dssa_int = None, 0 # optional denser sampled SA (build_dssa)
         assert bwt_occ.dtype == torch.int32 and bwt_occ.numel() == _words_for(self.length) * 2
 
     @property
@@ -66,6 +67,8 @@ class FMIndex:
         f.ssa = self.ssa.data_ptr() if self.ssa is not None else None
         f.ktab = self.ktab.data_ptr() if self.ktab is not None else None
         f.ktab_k = self.ktab_k if self.ktab is not None else 0
+        f.dssa = self.dssa.data_ptr() if self.dssa is not None else None
+        f.dssa_int = self.dssa_int if self.dssa is not None else 0
         return f
 
     def build_ktab(self, k=10, ctx=None):
@@ -77,6 +80,21 @@ class FMIndex:
         f = self.c()
         check(lib().nvb_fmindex_build_ktab(ctx.h, C.byref(f), int(k), tab.data_ptr(), _lib.current_stream_ptr()), ctx.h)
         self.ktab, self.ktab_k = tab, int(k)
+        return self
+
+    def build_dssa(self, sa_int=4, ctx=None):
+        """denser sampled SA (nvb_fmindex_build_dssa): entry i = locate(i * sa_int) through the 16-row SSA; every locate then walks
+        to the nearest multiple of sa_int instead of 16. Identical positions; 4 * (length + sa_int) / sa_int bytes."""
+        ctx = ctx or Context.default(self.device.index)
+        self.dssa, self.dssa_int = None, 0
+        tab = torch.empty(int(lib().nvb_dssa_words(self.length, sa_int)), dtype=torch.int32, device=self.device)
+        f = self.c()
+        check(lib().nvb_fmindex_build_dssa(ctx.h, C.byref(f), int(sa_int), tab.data_ptr(), _lib.current_stream_ptr()), ctx.h)
+        self.dssa, self.dssa_int = tab, int(sa_int)
+        return self
+
+    def drop_dssa(self):
+        self.dssa, self.dssa_int = None, 0
         return self
 
     def drop_ktab(self):

@@ -243,3 +243,32 @@ def test_kmer_jump_table(oracle, k):
         # the filter goes through the same kernel
         flt = nvb.FMIndexFilter()
         assert flt.rank(fmi, qs.symbols, qs.offsets) == int(((want[:, 1] + 1 - want[:, 0]).astype(np.uint32)).astype(np.uint64).sum())
+
+
+@pytest.mark.parametrize("sa_int", [2, 4, 8])
+def test_dense_ssa(oracle, sa_int):
+    """locate through the optional denser sampled SA returns the positions of the plain walk (fmindex_inl.h:364-394): one-phase,
+    two-phase and the FMIndexFilter form; every table entry is locate() of its row"""
+    rng = np.random.default_rng(200 + sa_int)
+    for n, alpha in ((60000, 4), (3000, 2), (41, 4), (16, 4)):
+        text = rng.integers(0, alpha, n).astype(np.uint8)
+        fmi, oidx = gu.fm_index_pair(oracle, text)
+        rows = np.concatenate([rng.integers(0, n + 1, 20000), np.arange(min(n + 1, 200)), [n, fmi.primary]]).astype(np.uint32)
+        want = oracle.fm_locate(oidx, rows)
+        rd = torch.from_numpy(rows.view(np.int32)).to(gu.dev())
+        assert (u32(nvb.locate(fmi, rd)) == want).all()
+        fmi.build_dssa(sa_int)
+        tab = u32(fmi.dssa)
+        assert len(tab) == (n + sa_int) // sa_int
+        assert (tab == oracle.fm_locate(oidx, (np.arange(len(tab)) * sa_int).astype(np.uint32))).all()
+        assert (u32(nvb.locate(fmi, rd)) == want).all()
+        assert (u32(nvb.locate(fmi, rd, two_phase=True)) == want).all()
+        Q, qo = util.rand_queries(rng, text, 3000, len_range=(6, 20), alpha=alpha, p_from_text=0.9, p_n=0.0)
+        qs = gu.sset(Q, qo)
+        flt = nvb.FMIndexFilter()
+        nh = flt.rank(fmi, qs.symbols, qs.offsets)
+        hits_dense = u32(flt.locate(0, nh))
+        fmi.drop_dssa()
+        flt2 = nvb.FMIndexFilter()
+        assert flt2.rank(fmi, qs.symbols, qs.offsets) == nh
+        assert (hits_dense == u32(flt2.locate(0, nh))).all()
