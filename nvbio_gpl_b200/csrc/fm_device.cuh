@@ -146,10 +146,12 @@ __device__ __forceinline__ uint2 fm_locate_walk_one(const FMView& f, uint32_t j,
 // Many LF-walks per thread, load-balanced: walk lengths vary (geometric, 15 steps on average), so a thread owns the strided list of walks
 // first, first + stride, ... and starts its next one as soon as one ends; the warp vote keeps the loop converged.
 //   fetch(h) -> SA row of walk h ;  emit(h, sampled_row, steps)
-template <typename Fetch, typename Emit>
+// DENSE = false: the 16-row SSA of the nvBWT layout (mask known at compile time); true: the optional denser table
+template <bool DENSE, typename Fetch, typename Emit>
 __device__ __forceinline__ void fm_walk_balanced(const FMView& f, uint32_t n, uint32_t first, uint32_t stride, const uint2* lut,
                                                  Fetch fetch, Emit emit)
 {
+    const uint32_t sa_mask = DENSE ? f.sa_mask : 15u;
     uint32_t h = first;
     bool alive = h < n;
     uint32_t j = alive ? fetch(h) : 0u, t = 0;
@@ -157,7 +159,7 @@ __device__ __forceinline__ void fm_walk_balanced(const FMView& f, uint32_t n, ui
     uint32_t jn = (alive && hn < n) ? fetch(hn) : 0u;          // the next walk's row is fetched one walk ahead
     while (__any_sync(0xFFFFFFFFu, alive))
     {
-        if (alive && (j & f.sa_mask) == 0u)
+        if (alive && (j & sa_mask) == 0u)
         {
             emit(h, j, t);
             h = hn; j = jn; t = 0;
@@ -165,7 +167,7 @@ __device__ __forceinline__ void fm_walk_balanced(const FMView& f, uint32_t n, ui
             hn = h + stride;
             jn = (alive && hn < n) ? fetch(hn) : 0u;
         }
-        if (alive && (j & f.sa_mask) != 0u)
+        if (alive && (j & sa_mask) != 0u)
         {
             uint32_t nj = 0;                                    // j == primary -> 0 (fmindex_inl.h:380-383)
             if (j != f.primary)

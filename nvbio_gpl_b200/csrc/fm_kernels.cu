@@ -128,22 +128,24 @@ fm_rank4_kernel(const FMView f, const uint32_t* __restrict__ k, uint32_t n, uint
     *(uint4*)(out + 4 * (size_t)tid) = r;
 }
 
+template <bool DENSE>
 __global__ void __launch_bounds__(FM_THREADS)
 fm_locate_kernel(const FMView f, const uint32_t* __restrict__ rows, uint32_t n, uint32_t* __restrict__ pos)
 {
     __shared__ uint2 s_lut[FM_LUT_ENTRIES];
     fm_lut_init(s_lut);
-    fm_walk_balanced(f, n, blockIdx.x * FM_THREADS + threadIdx.x, gridDim.x * FM_THREADS, s_lut,
+    fm_walk_balanced<DENSE>(f, n, blockIdx.x * FM_THREADS + threadIdx.x, gridDim.x * FM_THREADS, s_lut,
                      [&](uint32_t h) { return __ldg(rows + h); },
                      [&](uint32_t h, uint32_t j, uint32_t t) { pos[h] = __ldg(f.sa_tab + (j >> f.sa_shift)) + t; });
 }
 
+template <bool DENSE>
 __global__ void __launch_bounds__(FM_THREADS)
 fm_locate_walk_kernel(const FMView f, const uint32_t* __restrict__ rows, uint32_t n, uint32_t* __restrict__ walk)
 {
     __shared__ uint2 s_lut[FM_LUT_ENTRIES];
     fm_lut_init(s_lut);
-    fm_walk_balanced(f, n, blockIdx.x * FM_THREADS + threadIdx.x, gridDim.x * FM_THREADS, s_lut,
+    fm_walk_balanced<DENSE>(f, n, blockIdx.x * FM_THREADS + threadIdx.x, gridDim.x * FM_THREADS, s_lut,
                      [&](uint32_t h) { return __ldg(rows + h); },
                      [&](uint32_t h, uint32_t j, uint32_t t) { *(uint2*)(walk + 2 * (size_t)h) = make_uint2(j, t); });
 }
@@ -273,7 +275,7 @@ fm_dssa_kernel(const FMView f, uint32_t shift, uint32_t n, uint32_t* __restrict_
 {
     __shared__ uint2 s_lut[FM_LUT_ENTRIES];
     fm_lut_init(s_lut);
-    fm_walk_balanced(f, n, blockIdx.x * FM_THREADS + threadIdx.x, gridDim.x * FM_THREADS, s_lut,
+    fm_walk_balanced<false>(f, n, blockIdx.x * FM_THREADS + threadIdx.x, gridDim.x * FM_THREADS, s_lut,
                      [&](uint32_t h) { return h << shift; },
                      [&](uint32_t h, uint32_t j, uint32_t t) { out[h] = __ldg(f.sa_tab + (j >> f.sa_shift)) + t; });
 }
@@ -328,7 +330,9 @@ extern "C" int nvb_fm_locate(nvb_ctx* ctx, const nvb_fmindex* fmi, const uint32_
     int rc = check_fmi(fmi, true); if (rc) return rc;
     if (n == 0) return NVB_OK;
     if (!rows || !pos) return NVB_ERR_ARG;
-    fm_locate_kernel<<<walk_grid(ctx, n), FM_THREADS, 0, (cudaStream_t)stream>>>(make_view(fmi), rows, n, pos);
+    const FMView f = make_view(fmi);
+    if (f.sa_mask != 15u) fm_locate_kernel<true><<<walk_grid(ctx, n), FM_THREADS, 0, (cudaStream_t)stream>>>(f, rows, n, pos);
+    else                  fm_locate_kernel<false><<<walk_grid(ctx, n), FM_THREADS, 0, (cudaStream_t)stream>>>(f, rows, n, pos);
     NVB_LAUNCHED(ctx);
     return NVB_OK;
 }
@@ -339,7 +343,9 @@ extern "C" int nvb_fm_locate_walk(nvb_ctx* ctx, const nvb_fmindex* fmi, const ui
     int rc = check_fmi(fmi, false); if (rc) return rc;
     if (n == 0) return NVB_OK;
     if (!rows || !walk) return NVB_ERR_ARG;
-    fm_locate_walk_kernel<<<walk_grid(ctx, n), FM_THREADS, 0, (cudaStream_t)stream>>>(make_view(fmi), rows, n, walk);
+    const FMView f = make_view(fmi);
+    if (f.sa_mask != 15u) fm_locate_walk_kernel<true><<<walk_grid(ctx, n), FM_THREADS, 0, (cudaStream_t)stream>>>(f, rows, n, walk);
+    else                  fm_locate_walk_kernel<false><<<walk_grid(ctx, n), FM_THREADS, 0, (cudaStream_t)stream>>>(f, rows, n, walk);
     NVB_LAUNCHED(ctx);
     return NVB_OK;
 }

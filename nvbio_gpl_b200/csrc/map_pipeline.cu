@@ -106,12 +106,13 @@ map_expand_kernel(const uint2* __restrict__ seeds, const uint32_t* __restrict__ 
 // 10^7 hits walks more than 255 steps -- seen on the 3.1 Gbp genome), hence 32-bit step counts:
 // each thread owns a strided list of hits and starts its next walk as soon as one ends, so the lanes of a warp do
 // not wait for the longest walk among them. rows[h].x becomes the sampled row, steps[h] the distance walked.
+template <bool DENSE>
 __global__ void __launch_bounds__(MAP_THREADS)
 map_walk_kernel(const FMView f, uint32_t n_hits, uint2* __restrict__ rows, uint32_t* __restrict__ steps)
 {
     __shared__ uint2 s_lut[FM_LUT_ENTRIES];
     fm_lut_init(s_lut);
-    fm_walk_balanced(f, n_hits, blockIdx.x * MAP_THREADS + threadIdx.x, gridDim.x * MAP_THREADS, s_lut,
+    fm_walk_balanced<DENSE>(f, n_hits, blockIdx.x * MAP_THREADS + threadIdx.x, gridDim.x * MAP_THREADS, s_lut,
                      [&](uint32_t h) { return rows[h].x; },
                      [&](uint32_t h, uint32_t j, uint32_t t) { rows[h].x = j; steps[h] = t; });
 }
@@ -529,7 +530,8 @@ extern "C" int nvb_map_reads(nvb_ctx* ctx, const nvb_fmindex* fmi, const uint32_
                 NVB_LAUNCHED(ctx);
                 {
                     const uint32_t want = map_grid(n_hits), persistent = (uint32_t)ctx->sm_count * 8u;
-                    map_walk_kernel<<<want < persistent ? want : persistent, MAP_THREADS, 0, s>>>(f, n_hits, rows, steps);
+                    if (f.sa_mask != 15u) map_walk_kernel<true><<<want < persistent ? want : persistent, MAP_THREADS, 0, s>>>(f, n_hits, rows, steps);
+                    else                  map_walk_kernel<false><<<want < persistent ? want : persistent, MAP_THREADS, 0, s>>>(f, n_hits, rows, steps);
                     NVB_LAUNCHED(ctx);
                 }
                 map_keys_kernel<<<map_grid(n_hits), MAP_THREADS, 0, s>>>(f, g, rows, steps, n_hits, keys_b);
