@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stddef.h>
+#include <stdlib.h>
 #include "../../include/nvbio_b200.h"
 
 #if defined(__CUDA_ARCH__) && (__CUDA_ARCH__ < 1000)
@@ -56,6 +57,7 @@ struct FMView
     uint32_t        ktab_k;
     const uint32_t* sa_tab;   // the sampled SA the walks end on: ssa (rows % 16 == 0) or the optional denser one
     uint32_t        sa_mask, sa_shift;
+    uint32_t        hot_range; // backward-search steps whose range is wider than this load their blocks through L1
 };
 
 static inline FMView make_view(const nvb_fmindex* f)
@@ -66,6 +68,13 @@ static inline FMView make_view(const nvb_fmindex* f)
     v.blk = (const uint4*)f->bwt_occ; v.ssa = f->ssa;
     v.ktab = (const uint2*)f->ktab; v.ktab_k = f->ktab ? f->ktab_k : 0u;
     v.sa_tab = f->ssa; v.sa_mask = 15u; v.sa_shift = 4u;
+    {
+        // ranges wider than length / 4^k belong to the first k steps of every query: about 2.7 * 4^k distinct blocks
+        static int shift = -1;
+        if (shift < 0) { const char* e = getenv("NVB_FM_HOT_SHIFT"); shift = e ? atoi(e) : 10; }
+        v.hot_range = shift >= 32 ? 0xFFFFFFFFu : (f->length >> shift);
+        if (v.hot_range < 64u) v.hot_range = 64u;
+    }
     if (f->dssa && (f->dssa_int == 2u || f->dssa_int == 4u || f->dssa_int == 8u))
     { v.sa_tab = f->dssa; v.sa_mask = f->dssa_int - 1u; v.sa_shift = f->dssa_int == 2u ? 1u : f->dssa_int == 4u ? 2u : 3u; }
     return v;

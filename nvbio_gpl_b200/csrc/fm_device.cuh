@@ -12,6 +12,18 @@
 
 struct FMBlock { uint32_t w0, w1, w2, w3; uint32_t o0, o1, o2, o3; };
 
+// the few thousand blocks under the top of the search tree (range still wider than FMView::hot_range rows: every query
+// of a batch walks through them) are kept in L1; everything below is a one-off and bypasses it
+__device__ __forceinline__ FMBlock fm_load_block_hot(const uint4* blk, uint32_t b)
+{
+    FMBlock r;
+    const void* p = (const void*)(blk + 2ull * b);
+    asm volatile("ld.global.nc.L1::evict_last.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(r.w0), "=r"(r.w1), "=r"(r.w2), "=r"(r.w3), "=r"(r.o0), "=r"(r.o1), "=r"(r.o2), "=r"(r.o3)
+                 : "l"(p));
+    return r;
+}
+
 __device__ __forceinline__ FMBlock fm_load_block(const uint4* blk, uint32_t b)
 {
     FMBlock r;
@@ -109,6 +121,33 @@ __device__ __forceinline__ uint2 fm_rank2(const FMView& f, uint32_t x, uint32_t 
     uint2 r;
     r.y = qy.load ? fm_block_rank(by, qy.k & 63u, c, lut) : qy.value;
     r.x = qx.load ? fm_block_rank(bx, qx.k & 63u, c, lut) : qx.value;
+    return r;
+}
+
+// rank(fmi, (x, y), c) inside the backward-search loop, after its first step: there x = previous x - 1 >= 0 and
+// y <= length, so of the FM special cases (fmindex_inl.h:31-47) only "k >= primary -> k - 1" is left (k == length falls
+// under it: BWT[0..length-1] holds every occurrence), and with primary > 0 the adjusted index cannot underflow. When both
+// indices fall into one block (the common case once the range is narrow) the block is fetched once and its match flags
+// are computed once for both ranks (rank_dictionary_inl.h:425-448 fetches it once, too).
+__device__ __forceinline__ uint2 fm_rank2_inner(const FMView& f, uint32_t x, uint32_t y, uint32_t c, const uint2* lut)
+{
+    const uint32_t kx = x - (x >= f.primary ? 1u : 0u), ky = y - (y >= f.primary ? 1u : 0u);
+    const uint32_t bxi = kx >> 6, byi = ky >> 6;
+    const uint32_t cpat = c * 0x55555555u;
+    const bool hot = y - x > f.hot_range;
+    const FMBlock by = hot ? fm_load_block_hot(f.blk, byi) : fm_load_block(f.blk, byi);
+    uint32_t f01 = fm_eq_pair(by.w0, by.w1, cpat), f23 = fm_eq_pair(by.w2, by.w3, cpat);
+    uint32_t base = (c & 2u) ? ((c & 1u) ? by.o3 : by.o2) : ((c & 1u) ? by.o1 : by.o0);
+    const uint2 my = lut[ky & 63u], mx = lut[kx & 63u];
+    uint2 r;
+    r.y = base + __popc(f01 & my.x) + __popc(f23 & my.y);
+    if (bxi != byi)
+    {
+        const FMBlock bx = hot ? fm_load_block_hot(f.blk, bxi) : fm_load_block(f.blk, bxi);
+        f01 = fm_eq_pair(bx.w0, bx.w1, cpat); f23 = fm_eq_pair(bx.w2, bx.w3, cpat);
+        base = (c & 2u) ? ((c & 1u) ? bx.o3 : bx.o2) : ((c & 1u) ? bx.o1 : bx.o0);
+    }
+    r.x = base + __popc(f01 & mx.x) + __popc(f23 & mx.y);
     return r;
 }
 

@@ -25,6 +25,8 @@ fm_match_kernel(const FMView f, const StrSet q, uint32_t* __restrict__ ranges)
 {
     __shared__ __align__(16) uint8_t s_sym[FM_STAGE_BYTES];
     __shared__ uint2 s_lut[FM_LUT_ENTRIES];
+    __shared__ uint32_t s_L2[8];             // L2[c] by a shared-memory load: indexing the parameter struct would go through local memory
+    if (threadIdx.x < 5) s_L2[threadIdx.x] = f.L2[threadIdx.x];
     fm_lut_init(s_lut);
     const uint32_t first = blockIdx.x * FM_THREADS;
     const uint32_t tid   = first + threadIdx.x;
@@ -78,13 +80,41 @@ fm_match_kernel(const FMView f, const StrSet q, uint32_t* __restrict__ ranges)
         }
         if (bad <= 3u) { const uint2 r = __ldg(f.ktab + idx); x = r.x; y = r.y; i -= (int32_t)f.ktab_k; }
     }
-    for (; i >= 0 && x <= y; --i)
+    // first step: x - 1 may be -1 and y may be length (from [0, length] the reference's shortcuts touch no block at all)
+    if (i >= 0 && x <= y)
     {
         const uint32_t c = symbol(beg + (uint32_t)i);
-        if (c > 3u) { x = 1; y = 0; break; }
-        const uint2 r = fm_rank2(f, x - 1u, y, c, s_lut);
-        x = f.L2[c] + r.x + 1u;
-        y = f.L2[c] + r.y;
+        if (c > 3u) { x = 1; y = 0; i = -1; }
+        else
+        {
+            const uint2 r = fm_rank2(f, x - 1u, y, c, s_lut);
+            x = s_L2[c] + r.x + 1u;
+            y = s_L2[c] + r.y;
+            --i;
+        }
+    }
+    // every later step has x >= 1: the lean form (an index whose primary row is 0 keeps the general one)
+    if (f.primary != 0u)
+    {
+        for (; i >= 0 && x <= y; --i)
+        {
+            const uint32_t c = symbol(beg + (uint32_t)i);
+            if (c > 3u) { x = 1; y = 0; break; }
+            const uint2 r = fm_rank2_inner(f, x - 1u, y, c, s_lut);
+            x = s_L2[c] + r.x + 1u;
+            y = s_L2[c] + r.y;
+        }
+    }
+    else
+    {
+        for (; i >= 0 && x <= y; --i)
+        {
+            const uint32_t c = symbol(beg + (uint32_t)i);
+            if (c > 3u) { x = 1; y = 0; break; }
+            const uint2 r = fm_rank2(f, x - 1u, y, c, s_lut);
+            x = s_L2[c] + r.x + 1u;
+            y = s_L2[c] + r.y;
+        }
     }
     *(uint2*)(ranges + 2 * (size_t)tid) = make_uint2(x, y);
 }
