@@ -49,6 +49,8 @@ __global__ void __launch_bounds__(MAP_THREADS)
 map_seed_kernel(const FMView f, const StrSet reads, const MapGeom g, uint2* __restrict__ seeds, uint32_t* __restrict__ counts)
 {
     __shared__ uint2 s_lut[FM_LUT_ENTRIES];
+    __shared__ uint32_t s_L2[8];
+    if (threadIdx.x < 5) s_L2[threadIdx.x] = f.L2[threadIdx.x];
     fm_lut_init(s_lut);
     const uint32_t per_read = g.S * g.n_strands;
     const uint32_t t = blockIdx.x * MAP_THREADS + threadIdx.x;
@@ -76,9 +78,10 @@ map_seed_kernel(const FMView f, const StrSet reads, const MapGeom g, uint2* __re
         {
             const uint32_t c = map_strand_symbol(read, L, strand, o + (uint32_t)i);
             if (c > 3u) { x = 1; y = 0; break; }
-            const uint2 rk = fm_rank2(f, x - 1u, y, c, s_lut);
-            x = f.L2[c] + rk.x + 1u;
-            y = f.L2[c] + rk.y;
+            // x >= 1 after any step (and from the table): the lean form without the FM special cases applies
+            const uint2 rk = (x != 0u && f.primary != 0u) ? fm_rank2_inner(f, x - 1u, y, c, s_lut) : fm_rank2(f, x - 1u, y, c, s_lut);
+            x = s_L2[c] + rk.x + 1u;
+            y = s_L2[c] + rk.y;
         }
         if (x <= y)
         {
