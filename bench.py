@@ -657,8 +657,9 @@ def run_b200(args):
             ach = alg_per_q * args.queries / (fm["kernel_ms"] * 1e-3) / 1e9
             line["roofline"] = {"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
                                 # dram__bytes_read.sum + dram__bytes_write.sum of one fm_match launch of THIS workload under ncu --set full
-                                # (profiles/r1h_fm_match_ncu_full.csv; the 50 MB index is L2-resident, so it is far below the algorithmic bytes)
-                                "traffic": 902.7e6 if (args.genome == 100_000_000 and args.queries == 10_000_000) else None,
+                                # (profiles/r1j_fm_match_ncu_full.csv: 607.5 MB read + 598.7 MB written, the writes mostly the L2 flush buffer's dirty
+                                # lines leaving during the launch; the 50 MB index is L2-resident, so traffic is far below the algorithmic bytes)
+                                "traffic": 1206.2e6 if (args.genome == 100_000_000 and args.queries == 10_000_000) else None,
                                 "kernel": "fm_match_kernel<8,false,false>", "peak_source": peak_src,
                                 "algorithmic_bytes_per_query": alg_per_q, "blocks_per_query": bpq}
         if "cpu" in fm:
