@@ -172,6 +172,15 @@ int nvb_fm_match(nvb_ctx* ctx, const nvb_fmindex* fmi, nvb_string_set queries, u
  * ranges is in/out */
 int nvb_fm_match_from(nvb_ctx* ctx, const nvb_fmindex* fmi, nvb_string_set queries, uint32_t* ranges,
                       void* stream);
+/* nvBowtie's approximate seed mapping, map<find_exact>(query, len1, len2 = length, ...) (nvBowtie/bowtie2/cuda/mapping_inl.h:114-184,
+ * driven by seed_mapper<APPROX_MAPPING>): the query is matched exactly over its first len1 search steps and with at most one
+ * substitution over the remaining ones (rank4 at every such step, :146). Search order is match()'s: step t consumes symbol
+ * length - 1 - t (the reference iterates a reversed seed stream). Every non-empty raw SA range is emitted in the reference's
+ * push order -- substitutions by step then by symbol, the exact range last when find_exact != 0: counts[q] ranges were found,
+ * the first min(counts[q], cap) of them are at ranges[2 * (q * cap + k)]. The priority deque the reference pushes them into
+ * (seed_hit_deque_array.h) is the caller's. */
+int nvb_fm_match_approx(nvb_ctx* ctx, const nvb_fmindex* fmi, nvb_string_set queries, uint32_t len1, int find_exact,
+                        uint32_t cap, uint32_t* ranges, uint32_t* counts, void* stream);
 /* rank(fmi, range, c) (fmindex_inl.h:60-88): out[2i],out[2i+1] = occurrences of c[i] in
  * BWT[0..ranges[2i]] and BWT[0..ranges[2i+1]] (0xFFFFFFFF = -1 -> 0) */
 int nvb_fm_rank(nvb_ctx* ctx, const nvb_fmindex* fmi, const uint32_t* ranges, const uint8_t* c,

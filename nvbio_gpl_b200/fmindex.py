@@ -252,6 +252,19 @@ def match(fmi, symbols, offsets, ranges=None, bits=8, ctx=None):
     return ranges
 
 
+def match_approx(fmi, symbols, offsets, len1, find_exact=True, cap=64, bits=8, ctx=None):
+    """nvBowtie's map<find_exact> (mapping_inl.h:114-184): exact over the first len1 search steps, one substitution allowed in the
+    rest. Returns (ranges int32 [n, cap, 2] holding raw uint32 SA ranges in the reference's push order, counts int32 [n])."""
+    ctx = _ctx(fmi.bwt_occ, ctx)
+    n = offsets.numel() - 1
+    ranges = torch.zeros((n, cap, 2), dtype=torch.int32, device=fmi.device)
+    counts = torch.empty(n, dtype=torch.int32, device=fmi.device)
+    f = fmi.c()
+    check(lib().nvb_fm_match_approx(ctx.h, C.byref(f), _set_c(symbols, offsets, bits), int(len1), 1 if find_exact else 0, int(cap),
+                                    ranges.data_ptr(), counts.data_ptr(), _lib.current_stream_ptr()), ctx.h)
+    return ranges, counts
+
+
 def rank(fmi, ranges, c, ctx=None):
     """rank(fmi, range, c) (fmindex_inl.h:60-88): int32 [n,2]"""
     ctx = _ctx(fmi.bwt_occ, ctx)

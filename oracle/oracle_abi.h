@@ -114,6 +114,9 @@ int ORC(map_reads)(const orc_fmindex* fmi, const uint8_t* genome, const uint8_t*
                    uint32_t n_reads, const orc_map_params* p, orc_read_hit* hits, uint8_t* ops, uint32_t ops_stride,
                    uint32_t* n_candidates, int threads);
 
+/* nvBowtie's approximate seed mapping map<find_exact> (mapping_inl.h:114-184); see oracle_map.c */
+int ORC(fm_match_approx)(const orc_fmindex* fmi, const uint8_t* symbols, const uint32_t* offsets, uint32_t count, uint32_t len1,
+                         int find_exact, uint32_t cap, uint32_t* ranges, uint32_t* counts, int threads);
 typedef struct { int32_t score; uint32_t frag_begin, frag_end, flags; } orc_pair_hit;
 int ORC(pair_hits)(const orc_read_hit* hits, uint32_t n_pairs, uint32_t min_frag, uint32_t max_frag, orc_pair_hit* out);
 

@@ -159,3 +159,58 @@ int ORC(pair_hits)(const orc_read_hit* hits, uint32_t n_pairs, uint32_t min_frag
     }
     return 0;
 }
+
+/* nvBowtie's approximate seed mapping, `map<find_exact>` (nvBowtie/bowtie2/cuda/mapping_inl.h:114-184): the seed is matched
+ * exactly over its first len1 search steps and with at most one substitution in the remaining ones, using rank4 for the four
+ * candidate symbols of a step (:146) and match_range (:74-86) for the tail behind a substitution. Search order here is the order
+ * of nvb_fm_match / match(): step t consumes symbol q[len - 1 - t] (the reference iterates a reversed seed stream). Every
+ * non-empty SA range is emitted in the reference's push order (substitutions by step, then by symbol; the exact range last when
+ * find_exact); counts[q] = ranges found, of which the first min(counts, cap) are stored. Composed of the pinned entry points
+ * ORC(fm_rank4) / ORC(fm_rank), compiled over the C restatement and over the reference's own headers. */
+static void ORC(approx_tail)(const orc_fmindex* fmi, const uint8_t* q, uint32_t len, uint32_t t0, uint32_t* x, uint32_t* y)
+{
+    for (uint32_t t = t0; t < len && *x <= *y; ++t)                                    /* match_range, :74-86 */
+    {
+        const uint8_t c = q[len - 1 - t];
+        if (c > 3) { *x = 1; *y = 0; return; }
+        const uint32_t rg[2] = { *x - 1u, *y }; uint32_t r[2];
+        ORC(fm_rank)(fmi, rg, &c, 1, r, 1);
+        *x = fmi->L2[c] + r[0] + 1u; *y = fmi->L2[c] + r[1];
+    }
+}
+
+int ORC(fm_match_approx)(const orc_fmindex* fmi, const uint8_t* symbols, const uint32_t* offsets, uint32_t count, uint32_t len1,
+                         int find_exact, uint32_t cap, uint32_t* ranges, uint32_t* counts, int threads)
+{
+    if (!fmi || !offsets || !counts || (cap && !ranges)) return -1;
+    (void)threads;
+#ifdef _OPENMP
+    #pragma omp parallel for schedule(dynamic, 64) num_threads(threads > 0 ? threads : omp_get_max_threads())
+#endif
+    for (int64_t qi = 0; qi < (int64_t)count; ++qi)
+    {
+        const uint8_t* q = symbols + offsets[qi]; const uint32_t len = offsets[qi + 1] - offsets[qi];
+        const uint32_t l1 = len1 < len ? len1 : len;
+        uint32_t* out = ranges + 2 * (size_t)qi * cap; uint32_t n = 0;
+        uint32_t bx = 0, by = fmi->length;
+        ORC(approx_tail)(fmi, q + (len - l1), l1, 0, &bx, &by);                         /* exact over the first len1 steps, :136-137 */
+        for (uint32_t t = l1; t < len && bx <= by; ++t)                                /* :140-173 */
+        {
+            const uint8_t c = q[len - 1 - t];
+            const uint32_t k[2] = { bx - 1u, by }; uint32_t occ[8];
+            ORC(fm_rank4)(fmi, k, 2, occ, 1);                                          /* :146 */
+            for (uint32_t sub = 0; sub < 4; ++sub)
+                if (sub != c && occ[4 + sub] > occ[sub])
+                {
+                    uint32_t x = fmi->L2[sub] + occ[sub] + 1u, y = fmi->L2[sub] + occ[4 + sub];
+                    ORC(approx_tail)(fmi, q, len, t + 1, &x, &y);
+                    if (x <= y) { if (n < cap) { out[2 * n] = x; out[2 * n + 1] = y; } ++n; }
+                }
+            if (c < 4) { bx = fmi->L2[c] + occ[c] + 1u; by = fmi->L2[c] + occ[4 + c]; }
+            else { bx = 1; by = 0; break; }
+        }
+        if (find_exact && bx <= by) { if (n < cap) { out[2 * n] = bx; out[2 * n + 1] = by; } ++n; }
+        counts[qi] = n;
+    }
+    return 0;
+}

@@ -267,3 +267,16 @@ class Oracle:
         rc = self._f("pair_hits")(_ptr(hits), C.c_uint32(n), C.c_uint32(min_frag), C.c_uint32(max_frag), _ptr(out))
         assert rc == 0, rc
         return out
+
+    def fm_match_approx(self, idx, symbols, offsets, len1, find_exact=True, cap=64, threads=0):
+        """nvBowtie's map<find_exact> (mapping_inl.h:114-184): (ranges[n, cap, 2], counts[n])"""
+        symbols = np.ascontiguousarray(symbols, dtype=np.uint8)
+        offsets = np.ascontiguousarray(offsets, dtype=np.uint32)
+        n = len(offsets) - 1
+        ranges = np.zeros((n, cap, 2), dtype=np.uint32)
+        counts = np.zeros(n, dtype=np.uint32)
+        f = idx.c()
+        rc = self._f("fm_match_approx")(C.byref(f), _ptr(symbols), _ptr(offsets), C.c_uint32(n), C.c_uint32(len1), C.c_int(1 if find_exact else 0),
+                                        C.c_uint32(cap), _ptr(ranges), _ptr(counts), C.c_int(threads))
+        assert rc == 0, rc
+        return ranges, counts

@@ -272,3 +272,24 @@ def test_dense_ssa(oracle, sa_int):
         flt2 = nvb.FMIndexFilter()
         assert flt2.rank(fmi, qs.symbols, qs.offsets) == nh
         assert (hits_dense == u32(flt2.locate(0, nh))).all()
+
+
+def test_match_approx(oracle):
+    """nvb_fm_match_approx (nvBowtie's map<find_exact>, mapping_inl.h:114-184) vs the oracle composition: ranges in push order,
+    counts, truncation at cap, N symbols, empty and short queries, packed sets"""
+    rng = np.random.default_rng(31)
+    for n, alpha in ((50000, 4), (3000, 2), (33, 4)):
+        text = rng.integers(0, alpha, n).astype(np.uint8)
+        fmi, oidx = gu.fm_index_pair(oracle, text)
+        Q, qo = util.rand_queries(rng, text, 8000, len_range=(0, 30), alpha=alpha, p_from_text=0.8, p_n=0.05)
+        qs = gu.sset(Q, qo)
+        for len1, cap in ((0, 96), (10, 64), (14, 4), (40, 8)):
+            for fe in (True, False):
+                want_r, want_c = oracle.fm_match_approx(oidx, Q, qo, len1, fe, cap=cap)
+                got_r, got_c = nvb.match_approx(fmi, qs.symbols, qs.offsets, len1, fe, cap=cap)
+                assert (u32(got_c) == want_c).all(), (len1, fe)
+                assert (u32(got_r).reshape(-1, cap, 2) == want_r).all(), (len1, fe)
+        w = torch.from_numpy(nvb.pack_symbols(Q, 4).view(np.int32)).to(gu.dev())
+        want_r, want_c = oracle.fm_match_approx(oidx, Q, qo, 10, True, cap=64)
+        got_r, got_c = nvb.match_approx(fmi, w, qs.offsets, 10, True, cap=64, bits=4)
+        assert (u32(got_c) == want_c).all() and (u32(got_r).reshape(-1, 64, 2) == want_r).all()

@@ -93,3 +93,54 @@ def test_locate_every_row(oracle):
     pos, steps = oracle.fm_locate(idx, np.arange(1, n + 1, dtype=np.uint32), want_steps=True)
     assert (pos.astype(np.int64) == idx.sa[1:]).all()
     assert steps.max() < 16 * 8 and (steps[15::16] == 0).all()
+
+
+def test_match_approx_semantics(oracle):
+    """nvBowtie's map<find_exact> (mapping_inl.h:114-184) restated over the pinned rank/rank4 entry points: every emitted range is
+    the SA range of the query with exactly one substitution at a step >= len1 (or of the query itself), in push order, and the
+    C-restatement and reference-header compositions agree"""
+    rng = np.random.default_rng(12)
+    text = rng.integers(0, 4, 3000).astype(np.uint8)
+    idx = oracle.build_index(text)
+    Q, qo = util.rand_queries(rng, text, 300, len_range=(4, 14), alpha=4, p_from_text=0.8, p_n=0.05)
+    for len1 in (0, 3, 6, 20):
+        for fe in (True, False):
+            ranges, counts = oracle.fm_match_approx(idx, Q, qo, len1, fe, cap=64)
+            for i in range(len(counts)):
+                q = Q[qo[i]:qo[i + 1]]; L = len(q); want = []
+                # exact prefix of the search (the LAST len1 symbols) must match somewhere, and the base range must stay non-empty up to step t
+                for t in range(min(len1, L), L):
+                    base = q[L - t:]                      # symbols consumed before step t
+                    if (base > 3).any() or (len(base) and oracle.fm_match(idx, base, np.array([0, len(base)], np.uint32))[0][0] >
+                                            oracle.fm_match(idx, base, np.array([0, len(base)], np.uint32))[0][1]):
+                        break
+                    for sub in range(4):
+                        if sub == q[L - 1 - t]:
+                            continue
+                        m = q.copy(); m[L - 1 - t] = sub
+                        r = oracle.fm_match(idx, m, np.array([0, L], np.uint32))[0]
+                        if (m > 3).any():
+                            continue
+                        if r[0] <= r[1]:
+                            want.append((int(r[0]), int(r[1])))
+                    if q[L - 1 - t] > 3:
+                        break
+                if fe and not (q > 3).any():
+                    r = oracle.fm_match(idx, q, np.array([0, L], np.uint32))[0]
+                    if r[0] <= r[1]:
+                        want.append((int(r[0]), int(r[1])))
+                got = [(int(a), int(b)) for a, b in ranges[i, :counts[i]]]
+                assert got == want, (len1, fe, i, got, want)
+
+
+def test_match_approx_oracle_vs_reference_composition(oracle, ref):
+    rng = np.random.default_rng(13)
+    for n, alpha in ((20000, 4), (2000, 2)):
+        text = rng.integers(0, alpha, n).astype(np.uint8)
+        idx = oracle.build_index(text)
+        Q, qo = util.rand_queries(rng, text, 2000, len_range=(0, 26), alpha=alpha, p_from_text=0.8, p_n=0.05)
+        for len1 in (0, 10, 16):
+            for fe in (True, False):
+                a = oracle.fm_match_approx(idx, Q, qo, len1, fe, cap=80)
+                b = ref.fm_match_approx(idx, Q, qo, len1, fe, cap=80)
+                assert (a[1] == b[1]).all() and (a[0] == b[0]).all()
