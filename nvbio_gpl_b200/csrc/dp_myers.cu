@@ -122,6 +122,82 @@ myers_banded_kernel(const StrSet P, const StrSet T, const int32_t type, const ui
     sinks[id].score = best.score; sinks[id].sink_x = best.x; sinks[id].sink_y = best.y;
 }
 
+// four consecutive symbols of an 8-bit stream per call, from aligned 32-bit words joined by a funnel shift (one LDG per call);
+// words past the end of the symbol array are not touched
+struct Sym4Reader
+{
+    const uint32_t* w; uint32_t sh, w0, w1, left;      // left = aligned words still readable after w1
+    __device__ __forceinline__ void init(const uint8_t* base, uint32_t beg, uint32_t total)
+    {
+        const uint32_t words = (total + 3u) >> 2, wi = beg >> 2;
+        w = (const uint32_t*)base + wi; sh = (beg & 3u) * 8u;
+        w0 = wi < words ? __ldg(w) : 0u;
+        w1 = wi + 1u < words ? __ldg(w + 1) : 0u;
+        left = wi + 2u < words ? words - (wi + 2u) : 0u;
+    }
+    __device__ __forceinline__ uint32_t next4()
+    {
+        const uint32_t r = __funnelshift_r(w0, w1, sh);
+        w0 = w1; ++w;
+        if (left) { w1 = __ldg(w + 1); --left; } else w1 = 0u;
+        return r;
+    }
+};
+
+// the same algorithm over 8-bit string sets, four text columns per loop iteration: symbols arrive as whole words and both phases
+// share one column loop (column i is on the diagonal while i < last, then slides along the last pattern row until the band's
+// bottom leaves it: i < min(N, M + band), i.e. s = band - 1 + M - i >= 0)
+template <int ALPHABET>
+__global__ void __launch_bounds__(128)
+myers_banded_kernel8(const StrSet P, const StrSet T, const int32_t type, const uint32_t band, const int32_t min_score,
+                     nvb_best_sink* __restrict__ sinks)
+{
+    const uint32_t id = blockIdx.x * blockDim.x + threadIdx.x;
+    if (id >= P.count) return;
+    const uint32_t pb = P.off[id], M = P.off[id + 1] - pb;
+    const uint32_t tb = T.off[id], N = T.off[id + 1] - tb;
+    Best best; best.init();
+    if (N >= M)
+    {
+        Sym4Reader pr, tr; pr.init(P.sym, pb, P.off[P.count]); tr.init(T.sym, tb, T.off[T.count]);
+        Planes<ALPHABET> B; B.init();
+        uint32_t VP = 0xFFFFFFFFu, VN = 0u;
+        int32_t dist = 0;
+        const uint32_t top = 1u << (band - 1u);
+        const uint32_t last = min(N - 1u, M);
+        const uint32_t ncols = (uint32_t)min((uint64_t)N, (uint64_t)M + band);
+        for (uint32_t i0 = 0; i0 < ncols; i0 += 4u)
+        {
+            const uint32_t p4 = i0 < last ? pr.next4() : 0u;
+            const uint32_t t4 = tr.next4();
+            #pragma unroll
+            for (uint32_t k = 0; k < 4u; ++k)
+            {
+                const uint32_t i = i0 + k;
+                if (i >= ncols) break;
+                B.shift();
+                if (i < last) B.load((p4 >> (8u * k)) & 255u, top);
+                uint32_t X = B.eq((t4 >> (8u * k)) & 255u) | VN;
+                const uint32_t D0 = ((VP + (X & VP)) ^ VP) | X;
+                const uint32_t HN = VP & D0;
+                const uint32_t HP = VN | ~(VP | D0);
+                X = D0 >> 1;
+                VN = X & HP;
+                VP = HN | ~(X | HP);
+                if (i < last) dist -= 1 - (int32_t)((D0 >> (band - 1u)) & 1u);
+                else
+                {
+                    const uint32_t s = (band - 1u + M - i) & 31u;          // (s == 32 behaves as on the reference's x86 host build)
+                    dist -= (int32_t)((HP >> s) & 1u) - (int32_t)((HN >> s) & 1u);
+                    if (type == T_SEMI && dist >= min_score) best.report(dist, i + 1u, M);
+                }
+            }
+        }
+        if (type == T_GLOBAL && dist >= min_score) best.report(dist, N, M);
+    }
+    sinks[id].score = best.score; sinks[id].sink_x = best.x; sinks[id].sink_y = best.y;
+}
+
 } // namespace
 
 extern "C" int nvb_batch_banded_myers_score(nvb_ctx* ctx, int32_t type, uint32_t alphabet, uint32_t band, nvb_string_set patterns,
@@ -141,12 +217,16 @@ extern "C" int nvb_batch_banded_myers_score(nvb_ctx* ctx, int32_t type, uint32_t
     const int32_t ms = (int32_t)(int16_t)min_score;                        // myers_banded_inl.h:189
     cudaStream_t s = (cudaStream_t)stream;
     const uint32_t grid = (n + 127u) / 128u;
+    const bool fast8 = patterns.bits == 8 && texts.bits == 8;
+    #define NVB_MYERS_GO(A) do { if (fast8) myers_banded_kernel8<A><<<grid, 128, 0, s>>>(P, T, type, band, ms, sinks); \
+                                 else myers_banded_kernel<A><<<grid, 128, 0, s>>>(P, T, type, band, ms, sinks); } while (0)
     switch (alphabet)
     {
-    case 2: myers_banded_kernel<2><<<grid, 128, 0, s>>>(P, T, type, band, ms, sinks); break;
-    case 4: myers_banded_kernel<4><<<grid, 128, 0, s>>>(P, T, type, band, ms, sinks); break;
-    default: myers_banded_kernel<5><<<grid, 128, 0, s>>>(P, T, type, band, ms, sinks); break;
+    case 2:  NVB_MYERS_GO(2); break;
+    case 4:  NVB_MYERS_GO(4); break;
+    default: NVB_MYERS_GO(5); break;
     }
+    #undef NVB_MYERS_GO
     ctx->last_paths = 1;
     NVB_LAUNCHED(ctx);
     return NVB_OK;
