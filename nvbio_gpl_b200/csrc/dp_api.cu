@@ -65,6 +65,73 @@ static uint32_t batch_pairs(const TempPlan& p, size_t temp_bytes, uint32_t n)
     return (uint32_t)fit;
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Packed (4 / 2 bit) string sets -- the layout of the reference's read and genome streams -- are expanded to one byte per
+// symbol into context-owned scratch so that the banded fast kernels (which stream 16-byte blocks of 8-bit symbols) take
+// them too; the symbol index space, hence the offsets, is unchanged. max_len must be a true maximum (the reference sizes
+// its own scratch from it as well): the expansion covers count * max_len symbols.
+// ---------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+dp_unpack_kernel(const uint32_t* __restrict__ words, uint32_t bits, const uint32_t* __restrict__ total_d, uint64_t cap, uint8_t* __restrict__ out)
+{
+    const uint64_t g = (uint64_t)blockIdx.x * 256u + threadIdx.x;        // one group of 16 symbols per thread
+    const uint64_t total = min((uint64_t)*total_d, cap);
+    const uint64_t i0 = g * 16u;
+    if (i0 >= total) return;
+    uint32_t b[4];
+    if (bits == 4)
+    {
+        const uint32_t w0 = __ldg(words + 2 * g), w1 = (i0 + 8u < total) ? __ldg(words + 2 * g + 1) : 0u;
+        #pragma unroll
+        for (int k = 0; k < 4; ++k)
+        {
+            const uint32_t w = k < 2 ? w0 : w1; const int base = 28 - 16 * (k & 1);
+            b[k] = ((w >> base) & 15u) | (((w >> (base - 4)) & 15u) << 8) | (((w >> (base - 8)) & 15u) << 16) | (((w >> (base - 12)) & 15u) << 24);
+        }
+    }
+    else
+    {
+        const uint32_t w = __ldg(words + g);
+        #pragma unroll
+        for (int k = 0; k < 4; ++k)
+        {
+            const int base = 30 - 8 * k;
+            b[k] = ((w >> base) & 3u) | (((w >> (base - 2)) & 3u) << 8) | (((w >> (base - 4)) & 3u) << 16) | (((w >> (base - 6)) & 3u) << 24);
+        }
+    }
+    *(uint4*)(out + i0) = make_uint4(b[0], b[1], b[2], b[3]);          // the scratch is padded to whole groups
+}
+
+enum { DP_STAGE_UNPACK_P = 40, DP_STAGE_UNPACK_T = 41 };
+
+static int unpack_set(nvb_ctx* ctx, StrSet& S, uint32_t max_len, int slot, cudaStream_t s)
+{
+    if (S.bits == 8) return NVB_OK;
+    const uint64_t cap = (uint64_t)S.count * max_len;
+    if (cap == 0 || cap > 0xFFFFFFF0ull) return NVB_ERR_UNSUPPORTED;
+    void* out = nullptr;
+    int rc = nvb_stage(ctx, slot, (size_t)((cap + 15u) & ~15ull) + 64, &out);
+    if (rc) return rc;
+    const uint64_t groups = (cap + 15u) / 16u;
+    dp_unpack_kernel<<<(uint32_t)((groups + 255u) / 256u), 256, 0, s>>>((const uint32_t*)S.sym, S.bits, S.off + S.count, cap, (uint8_t*)out);
+    NVB_LAUNCHED(ctx);
+    S.sym = (const uint8_t*)out; S.bits = 8;
+    return NVB_OK;
+}
+
+// expands packed sets when that opens a fast path the 8-bit form would take
+template <typename Supported>
+static int unpack_for_fast_path(nvb_ctx* ctx, StrSet& P, StrSet& T, uint32_t maxM, uint32_t maxN, cudaStream_t s, Supported supported)
+{
+    if ((P.bits == 8 && T.bits == 8) || ctx->force_generic == 1) return NVB_OK;
+    StrSet P8 = P, T8 = T; P8.bits = T8.bits = 8;
+    if (!supported(P8, T8)) return NVB_OK;
+    if ((uint64_t)P.count * maxM > 0xFFFFFFF0ull || (uint64_t)T.count * maxN > 0xFFFFFFF0ull) return NVB_OK;
+    int rc;
+    if ((rc = unpack_set(ctx, P, maxM, DP_STAGE_UNPACK_P, s)) || (rc = unpack_set(ctx, T, maxN, DP_STAGE_UNPACK_T, s))) return rc;
+    return NVB_OK;
+}
+
 extern "C" int nvb_batch_score(nvb_ctx* ctx, nvb_aligner a, nvb_string_set patterns, nvb_string_set texts,
                                nvb_best_sink* sinks, uint32_t maxM, uint32_t maxN, void* temp, size_t temp_bytes, void* stream)
 {
@@ -131,7 +198,9 @@ extern "C" int nvb_batch_banded_score(nvb_ctx* ctx, nvb_aligner a, uint32_t band
     if (n == 0) return NVB_OK;
     if (!sinks) return NVB_ERR_ARG;
     cudaStream_t s = (cudaStream_t)stream;
-    const StrSet P = make_set(patterns), T = make_set(texts);
+    StrSet P = make_set(patterns), T = make_set(texts);
+    if ((rc = unpack_for_fast_path(ctx, P, T, maxM, maxN, s, [&](const StrSet& p8, const StrSet& t8)
+             { return (ctx->force_generic == 0 && dpb2_score_supported(a, band, p8, t8, maxM, maxN)) || dpf_banded_score_supported(a, band, p8, t8, maxM, maxN); }))) return rc;
     ctx->last_paths = 0;
     const bool use_b2 = ctx->force_generic == 0 && dpb2_score_supported(a, band, P, T, maxM, maxN);
     if (use_b2 || (ctx->force_generic != 1 && dpf_banded_score_supported(a, band, P, T, maxM, maxN)))   // force_generic: 1 = int32 kernels only, 2 = no sheared-coordinate kernels
@@ -212,7 +281,6 @@ extern "C" int nvb_batch_banded_traceback(nvb_ctx* ctx, nvb_aligner a, uint32_t 
                                           uint8_t* ops, uint32_t ops_stride, uint32_t* n_ops, uint32_t maxM,
                                           uint32_t maxN, void* temp, size_t temp_bytes, void* stream)
 {
-    (void)maxN;
     if (!ctx) return NVB_ERR_ARG;
     int rc;
     if ((rc = check_aligner(a)) || (rc = check_sets(patterns, texts))) return rc;
@@ -221,7 +289,9 @@ extern "C" int nvb_batch_banded_traceback(nvb_ctx* ctx, nvb_aligner a, uint32_t 
     if (n == 0) return NVB_OK;
     if (!out || !ops || !n_ops || !temp) return NVB_ERR_ARG;
     cudaStream_t s = (cudaStream_t)stream;
-    const StrSet P = make_set(patterns), T = make_set(texts);
+    StrSet P = make_set(patterns), T = make_set(texts);
+    if ((rc = unpack_for_fast_path(ctx, P, T, maxM, maxN, s, [&](const StrSet& p8, const StrSet& t8)
+             { return ctx->force_generic == 0 && dpb2_traceback_supported(a, band, p8, t8, maxM); }))) return rc;
     const TempPlan p = plan(NVB_OP_BANDED_TRACEBACK, a, band, chk, maxM, maxN);
     const uint32_t bp = batch_pairs(p, temp_bytes, n);
     if (bp == 0) return NVB_ERR_TEMP;

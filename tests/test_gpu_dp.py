@@ -166,3 +166,29 @@ def test_host_entry_points_and_cigar(oracle, ctx):
     for i in range(50):
         s = "".join("%d%s" % (w >> 2, "MID"[w & 3]) for w in cig[i, :ncig[i]])
         assert s == po.rle(tb[1][i, :tb[2][i]][::-1])
+
+
+@pytest.mark.parametrize("bits", [4, 2])
+def test_banded_packed_string_sets(oracle, ctx, bits):
+    """4- and 2-bit packed string sets (the reference's read / genome streams) through the banded entry points: expanded to
+    bytes in context scratch for the fast kernels, read directly by the int32 ones; same sinks and op lists either way"""
+    rng = np.random.default_rng(40 + bits)
+    for kind, scheme in ((po.ED, (0, 0, 0, 0)), (po.GOTOH, (0, -5, -8, -3)), (po.SW, (2, -1, -1, -1))):
+        for ty in (po.GLOBAL, po.LOCAL, po.SEMI_GLOBAL):
+            for band in (15, 7, 12):
+                a, oa = gu.aligner(kind, ty, scheme), po.aligner(kind, ty, scheme)
+                P, Po, T, To = util.rand_pairs(rng, 600, (1, 120), util.banded_text_len(rng, ty, band), 4)
+                if bits == 4:
+                    P = P.copy(); T = T.copy()
+                    P[rng.random(len(P)) < 0.003] = 4; T[rng.random(len(T)) < 0.003] = 9
+                dev = gu.dev()
+                pk = torch.from_numpy(nvb.pack_symbols(P, bits).view(np.int32)).to(dev)
+                tk = torch.from_numpy(nvb.pack_symbols(T, bits).view(np.int32)).to(dev)
+                po_d = torch.from_numpy(Po.view(np.int32)).to(dev); to_d = torch.from_numpy(To.view(np.int32)).to(dev)
+                maxM = int(np.diff(Po.astype(np.int64)).max()); maxN = int(np.diff(To.astype(np.int64)).max())
+                ps, ts = nvb.StringSet(pk, po_d, bits, maxM), nvb.StringSet(tk, to_d, bits, maxN)
+                got = gu.sinks_np(nvb.batch_banded_alignment_score(a, band, ps, ts))
+                want = oracle.banded_score(oa, band, P, Po, T, To)
+                assert (got == want).all(), (kind, ty, band, np.nonzero(got != want)[0][:5])
+                got = gu.tb_np(nvb.batch_banded_alignment_traceback(a, band, 16, ps, ts))
+                assert gu.tb_equal(got, oracle.banded_traceback(oa, band, 16, P, Po, T, To)), (kind, ty, band)
