@@ -328,8 +328,9 @@ static bool band_geometry(uint32_t band, uint32_t maxM, uint32_t* rows_cap, uint
 bool dpf_banded_score_supported(const nvb_aligner& a, uint32_t band, const StrSet& P, const StrSet& T, uint32_t maxM, uint32_t maxN)
 {
     (void)maxN;
-    if (band != 7 && band != 15) return false;
-    if (P.bits != 8 || T.bits != 8) return false;       // packed sets take the int32 kernels
+    if (band != 7 && band != 15 && band != 31) return false;
+    if (band == 31 && a.type == NVB_LOCAL) return false;  // the arg-max key has 4 bits for the band cell
+    if (P.bits != 8 || T.bits != 8) return false;       // packed sets are expanded by the caller (dp_api.cu)
     const Scheme s = make_scheme(a);
     if (s.match < -127 || s.match > 127 || s.mismatch < -127 || s.mismatch > 127) return false;
     if (s.ga >= 0 || s.gb >= 0 || s.ga < -512 || s.gb < -512) return false;
@@ -363,10 +364,11 @@ template <int W>
 static int band_dispatch(nvb_ctx* ctx, const nvb_aligner& a, const BandFastParams& p, size_t smem, cudaStream_t st)
 {
     const bool g = a.kind == NVB_GOTOH;
+    if (W > 16 && a.type == NVB_LOCAL) return NVB_ERR_UNSUPPORTED;
     switch (a.type)
     {
     case NVB_GLOBAL:      return g ? band_launch<W, T_GLOBAL, true>(ctx, p, smem, st) : band_launch<W, T_GLOBAL, false>(ctx, p, smem, st);
-    case NVB_LOCAL:       return g ? band_launch<W, T_LOCAL, true>(ctx, p, smem, st)  : band_launch<W, T_LOCAL, false>(ctx, p, smem, st);
+    case NVB_LOCAL:       return g ? band_launch<(W > 16 ? 15 : W), T_LOCAL, true>(ctx, p, smem, st)  : band_launch<(W > 16 ? 15 : W), T_LOCAL, false>(ctx, p, smem, st);
     case NVB_SEMI_GLOBAL: return g ? band_launch<W, T_SEMI, true>(ctx, p, smem, st)   : band_launch<W, T_SEMI, false>(ctx, p, smem, st);
     }
     return NVB_ERR_ARG;
@@ -387,5 +389,6 @@ int dpf_banded_score(nvb_ctx* ctx, const nvb_aligner& a, uint32_t band, StrSet P
     p.one = 1; p.sixteen = 16;
     if (band == 7)  return band_dispatch<7>(ctx, a, p, smem, st);
     if (band == 15) return band_dispatch<15>(ctx, a, p, smem, st);
+    if (band == 31) return band_dispatch<31>(ctx, a, p, smem, st);
     return NVB_ERR_UNSUPPORTED;
 }
