@@ -177,7 +177,9 @@ dpf_banded_kernel(const BandFastParams p)
         const uint2 pr = lut_prof[my_txt[j]];
         TA[j] = pr.x; TB[j] = pr.y;
     }
-    uint32_t bestkey = B2 << 4, bestrow = 0;
+    constexpr uint32_t KB = W > 16 ? 5u : 4u;                    // bits of the band cell in the arg-max key (score << KB | cell)
+    constexpr uint32_t KMASK = ~(((1u << KB) - 1u) * 0x00010001u);
+    uint32_t bestkey = B2 << KB, bestrow = 0;
 
     for (uint32_t i0 = 0; i0 < rows; i0 += RU)
     {
@@ -247,7 +249,7 @@ dpf_banded_kernel(const BandFastParams p)
                 if (LOCAL)
                 {
                     // later rows win ties: compare against the best with its column bits cleared, minus one
-                    const uint32_t kb = __vadd2(bestkey & 0xFFF0FFF0u, 0xFFFFFFFFu);
+                    const uint32_t kb = __vadd2(bestkey & KMASK, 0xFFFFFFFFu);
                     uint32_t acc = kb;
                     #pragma unroll
                     for (int j = 0; j + 1 < W; j += 2) acc = __vimax3_s16x2(acc, key[j], key[j + 1]);
@@ -291,8 +293,8 @@ dpf_banded_kernel(const BandFastParams p)
             {
                 const uint32_t k = h ? (bestkey >> 16) : (bestkey & 0xFFFFu);
                 const uint32_t row = h ? (bestrow >> 16) : (bestrow & 0xFFFFu);
-                out.score = (int32_t)(k >> 4) - p.bias;
-                out.sink_x = row + (k & 15u) + 1u; out.sink_y = row + 1u;
+                out.score = (int32_t)(k >> KB) - p.bias;
+                out.sink_x = row + (k & ((1u << KB) - 1u)) + 1u; out.sink_y = row + 1u;
             }
             else if (TYPE == T_GLOBAL)
             {
@@ -329,7 +331,6 @@ bool dpf_banded_score_supported(const nvb_aligner& a, uint32_t band, const StrSe
 {
     (void)maxN;
     if (band != 7 && band != 15 && band != 31) return false;
-    if (band == 31 && a.type == NVB_LOCAL) return false;  // the arg-max key has 4 bits for the band cell
     if (P.bits != 8 || T.bits != 8) return false;       // packed sets are expanded by the caller (dp_api.cu)
     const Scheme s = make_scheme(a);
     if (s.match < -127 || s.match > 127 || s.mismatch < -127 || s.mismatch > 127) return false;
@@ -339,7 +340,7 @@ bool dpf_banded_score_supported(const nvb_aligner& a, uint32_t band, const StrSe
     if (a.type == NVB_LOCAL)
     {
         if (max(iabs32(s.ga), iabs32(s.gb)) > 64) return false;
-        if ((uint64_t)max(s.match, 0) * maxM + 64u >= 2047u) return false;        // 11 score bits in the arg-max key
+        if ((uint64_t)max(s.match, 0) * maxM + 64u >= (band > 16 ? 1023u : 2047u)) return false;   // 11 (10 for band 31) score bits in the arg-max key
     }
     else if ((uint64_t)big * ((uint64_t)maxM + band + 2) >= 15000u) return false;  // bias 0x4000 keeps both halves positive
     uint32_t rc, tc; size_t smem;
@@ -364,11 +365,10 @@ template <int W>
 static int band_dispatch(nvb_ctx* ctx, const nvb_aligner& a, const BandFastParams& p, size_t smem, cudaStream_t st)
 {
     const bool g = a.kind == NVB_GOTOH;
-    if (W > 16 && a.type == NVB_LOCAL) return NVB_ERR_UNSUPPORTED;
     switch (a.type)
     {
     case NVB_GLOBAL:      return g ? band_launch<W, T_GLOBAL, true>(ctx, p, smem, st) : band_launch<W, T_GLOBAL, false>(ctx, p, smem, st);
-    case NVB_LOCAL:       return g ? band_launch<(W > 16 ? 15 : W), T_LOCAL, true>(ctx, p, smem, st)  : band_launch<(W > 16 ? 15 : W), T_LOCAL, false>(ctx, p, smem, st);
+    case NVB_LOCAL:       return g ? band_launch<W, T_LOCAL, true>(ctx, p, smem, st)  : band_launch<W, T_LOCAL, false>(ctx, p, smem, st);
     case NVB_SEMI_GLOBAL: return g ? band_launch<W, T_SEMI, true>(ctx, p, smem, st)   : band_launch<W, T_SEMI, false>(ctx, p, smem, st);
     }
     return NVB_ERR_ARG;
@@ -386,7 +386,7 @@ int dpf_banded_score(nvb_ctx* ctx, const nvb_aligner& a, uint32_t band, StrSet P
     p.n_pairs = P.count; p.n_threads = (P.count + 1) / 2;
     p.match = s.match; p.mismatch = s.mismatch; p.ga = s.ga; p.gb = s.gb;
     p.bias = a.type == NVB_LOCAL ? max(iabs32(s.ga), iabs32(s.gb)) : 0x4000;
-    p.one = 1; p.sixteen = 16;
+    p.one = 1; p.sixteen = band > 16 ? 32 : 16;           // the key multiplier: 1 << (bits of the band cell)
     if (band == 7)  return band_dispatch<7>(ctx, a, p, smem, st);
     if (band == 15) return band_dispatch<15>(ctx, a, p, smem, st);
     if (band == 31) return band_dispatch<31>(ctx, a, p, smem, st);
