@@ -330,7 +330,7 @@ static bool band_geometry(uint32_t band, uint32_t maxM, uint32_t* rows_cap, uint
 bool dpf_banded_score_supported(const nvb_aligner& a, uint32_t band, const StrSet& P, const StrSet& T, uint32_t maxM, uint32_t maxN)
 {
     (void)maxN;
-    if (band != 7 && band != 15 && band != 31) return false;
+    if (band != 3 && band != 5 && band != 7 && band != 15 && band != 31) return false;
     if (P.bits != 8 || T.bits != 8) return false;       // packed sets are expanded by the caller (dp_api.cu)
     const Scheme s = make_scheme(a);
     if (s.match < -127 || s.match > 127 || s.mismatch < -127 || s.mismatch > 127) return false;
@@ -387,6 +387,8 @@ int dpf_banded_score(nvb_ctx* ctx, const nvb_aligner& a, uint32_t band, StrSet P
     p.match = s.match; p.mismatch = s.mismatch; p.ga = s.ga; p.gb = s.gb;
     p.bias = a.type == NVB_LOCAL ? max(iabs32(s.ga), iabs32(s.gb)) : 0x4000;
     p.one = 1; p.sixteen = band > 16 ? 32 : 16;           // the key multiplier: 1 << (bits of the band cell)
+    if (band == 3)  return band_dispatch<3>(ctx, a, p, smem, st);
+    if (band == 5)  return band_dispatch<5>(ctx, a, p, smem, st);
     if (band == 7)  return band_dispatch<7>(ctx, a, p, smem, st);
     if (band == 15) return band_dispatch<15>(ctx, a, p, smem, st);
     if (band == 31) return band_dispatch<31>(ctx, a, p, smem, st);
