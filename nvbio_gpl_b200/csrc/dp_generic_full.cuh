@@ -61,9 +61,14 @@ struct FullDP
         for (int j = 0; j <= BL; ++j) if ((uint32_t)j == ncols) hlast = H[j];
 
         const uint32_t fbase = block - chk_id * CHK;
+        // BestSink over a LOCAL stripe row: cells are visited left to right and the last maximum wins, i.e. the maximum of
+        // (score << 5 | column) -- one IMNMX per cell instead of a compare and three selects; the row then reports once.
+        // (Best2Sink needs every cell in order, so it keeps the per-cell report.)
+        const bool keyed = local && best && !best->two;
         for (uint32_t i = 0; i < N; ++i)
         {
             const uint32_t r = v.t(i);
+            int32_t rk = -1;
             int32_t diag = carry;
             H[0] = carry = colH[i * cs];
             int32_t E = GOTOH ? (int32_t)colE[i * cs] : 0;
@@ -101,10 +106,12 @@ struct FullDP
                     }
                     diag = H[j];
                     H[j] = hi;
-                    if (local && best) best->report(hi, i + 1, block + j);
+                    if (keyed) rk = max(rk, (hi << 5) | j);
+                    else if (local && best) best->report(hi, i + 1, block + j);
                     if ((uint32_t)j == ncols) hlast = hi;
                 }
             }
+            if (keyed && rk >= 0) best->report(rk >> 5, i + 1, block + (uint32_t)(rk & 31));
             if (ncols == 0) hlast = H[0];
             colH[i * cs] = (int16_t)hlast;
             if (GOTOH) colE[i * cs] = (int16_t)Eout;
