@@ -21,7 +21,7 @@
 
 namespace {
 
-// byte i of an 8-bit symbol stream through a cached aligned word; packed streams go through sym_at_rt
+// symbol i of an 8-bit or packed (4 / 2 bit, big-endian words) stream through a cached aligned word
 struct SymReader
 {
     const uint8_t* base; uint32_t bits; uint32_t beg; uint32_t word; uint32_t have;   // have = index of cached word + 1
@@ -29,10 +29,12 @@ struct SymReader
     __device__ __forceinline__ uint32_t get(uint32_t i)
     {
         const uint32_t a = beg + i;
-        if (bits != 8) return sym_at_rt(base, bits, a);
-        const uint32_t w = a >> 2;
+        const uint32_t lg = bits == 8 ? 2u : bits == 4 ? 3u : 4u;          // log2(symbols per 32-bit word)
+        const uint32_t w = a >> lg;
         if (have != w + 1u) { word = __ldg((const uint32_t*)base + w); have = w + 1u; }
-        return (word >> (8u * (a & 3u))) & 255u;
+        if (bits == 8) return (word >> (8u * (a & 3u))) & 255u;
+        if (bits == 4) return (word >> (28u - 4u * (a & 7u))) & 15u;        // big-endian packed streams (packedstream_inl.h:30-52)
+        return (word >> (30u - 2u * (a & 15u))) & 3u;
     }
 };
 
