@@ -566,6 +566,17 @@ def run_b200(args):
                 out["sw"]["cpu_gcups"] = k * M * N / dt / 1e9
                 out["sw"]["cpu_kind"] = kind
                 out["sw"]["parity"] = dict(checked=k, mismatches=mism)
+            # the other full-matrix aligners of batch_alignment_score at the same shape (int32 one-pair-per-thread kernels): informational
+            others = {}
+            for oname, oa_ in (("sw_global", nvb.SmithWatermanAligner(nvb.GLOBAL, 2, -1, -1, -1)), ("sw_semi_global", nvb.SmithWatermanAligner(nvb.SEMI_GLOBAL, 2, -1, -1, -1)),
+                               ("gotoh_local", nvb.GotohAligner(nvb.LOCAL, 2, -2, -5, -3)), ("gotoh_semi_global", nvb.GotohAligner(nvb.SEMI_GLOBAL, 2, -2, -5, -3))):
+                otemp = torch.empty(int(nvb.lib().nvb_temp_bytes(0, oa_.c(), 0, 0, M, N, n)), dtype=torch.uint8, device=dev)
+                ofn = lambda: nvb.batch_alignment_score(oa_, ps, ts, sinks=sinks, temp=otemp, ctx=ctx)
+                otms = time_steps(ofn, 2, 1, flush)
+                oms = max_over_ranks(sum(otms) / len(otms))
+                others[oname] = dict(gcups=world * n * M * N / (oms * 1e-3) / 1e9, ms=oms, paths=ctx.last_paths)
+                del otemp
+            out["sw"]["other_aligners"] = others
             del P, T, temp
         if only in ("", "banded"):
             M, W, n = 250, 15, args.banded_pairs
