@@ -455,10 +455,11 @@ def run_b200(args):
         RL = 150
         words = nvb.pack_genome(genome, ctx=ctx)
         # index-side optional structures (identical results): k-mer jump table for seeding (k = 10 while index + table fit L2,
-        # 13 on a DRAM-resident index) and a 4-row sampled SA for the locate walks
+        # 13 on a DRAM-resident index) and a 2-row sampled SA for the locate walks (4 bytes per 2 genome symbols)
         kk = int(os.environ.get("KTAB_K", 10 if genome.numel() <= 400_000_000 else 13))
         fmi.build_ktab(kk, ctx=ctx)
-        fmi.build_dssa(4, ctx=ctx)
+        dd = int(os.environ.get("DSSA_INT", 2))
+        fmi.build_dssa(dd, ctx=ctx)
         rsym, roff = gen_reads(genome, nr, RL, 7 + rank, dev)
         mparams = nvb.MapParams(nvb.GotohAligner(nvb.SEMI_GLOBAL, 0, -5, -8, -3), seed_len=20, seed_interval=10, max_hits=4,
                                 max_range=0, band=15, both_strands=True, min_score=-90)
@@ -476,9 +477,9 @@ def run_b200(args):
         out[tag] = dict(reads_per_s=world * nr / (ms * 1e-3), ms=ms, reads=nr, read_len=RL, launches_per_call=per_call,
                           seed_hits_per_read=mstats["seed_hits"] / nr, candidates_per_read=mstats["candidates"] / nr,
                           aligned_frac=mstats["aligned"] / nr, genome=int(genome.numel()),
-                          params="20-mer seeds every 10 bp on both strands (%d-mer jump table, %d MB; 4-row sampled SA, %d MB), <= 4 rows per seed, "
+                          params="20-mer seeds every 10 bp on both strands (%d-mer jump table, %d MB; %d-row sampled SA, %d MB), <= 4 rows per seed, "
                                  "banded (15) Gotoh (0,-5,-8,-3) SEMI_GLOBAL, min score -90, traceback of the best window"
-                                 % (kk, fmi.ktab.numel() * 4 >> 20, fmi.dssa.numel() * 4 >> 20))
+                                 % (kk, fmi.ktab.numel() * 4 >> 20, dd, fmi.dssa.numel() * 4 >> 20))
         # e2e: pinned host reads in; hits + CIGARs out (the SAM-facing result), and once with the raw op lists for the parity check
         hr_sym = torch.empty(rsym.numel(), dtype=torch.uint8).pin_memory(); hr_sym.copy_(rsym)
         hr_off = torch.empty(roff.numel(), dtype=torch.int32).pin_memory(); hr_off.copy_(roff)
