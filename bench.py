@@ -455,8 +455,8 @@ def run_b200(args):
         RL = 150
         words = nvb.pack_genome(genome, ctx=ctx)
         # index-side optional structures (identical results): k-mer jump table for seeding (k = 10 while index + table fit L2,
-        # 13 on a DRAM-resident index) and a 2-row sampled SA for the locate walks (4 bytes per 2 genome symbols)
-        kk = int(os.environ.get("KTAB_K", 10 if genome.numel() <= 400_000_000 else 13))
+        # 15 = 8 GiB on a DRAM-resident index) and a 2-row sampled SA for the locate walks (4 bytes per 2 genome symbols)
+        kk = int(os.environ.get("KTAB_K", 10 if genome.numel() <= 400_000_000 else 15))
         fmi.build_ktab(kk, ctx=ctx)
         dd = int(os.environ.get("DSSA_INT", 2))
         fmi.build_dssa(dd, ctx=ctx)

@@ -137,7 +137,7 @@ int nvb_fmindex_save(nvb_ctx* ctx, const nvb_fmindex* fmi_d, const char* prefix,
  * (cudaAccessPolicyWindow); bytes = 0 removes the window. Replaces the reference's texture/__ldg
  * cache hint (nvbio/fmindex/fmindex.h:564-583). */
 /* Optional k-mer jump table: entry i = the raw (x, y) pair match() returns for the k-mer whose symbols are the
- * base-4 digits of i (first symbol most significant), 2 uint32 per entry, 4^k entries (k <= 13). With fmi->ktab set,
+ * base-4 digits of i (first symbol most significant), 2 uint32 per entry, 4^k entries (k <= 15: 8 GiB). With fmi->ktab set,
  * nvb_fm_match / nvb_fm_filter_rank / nvb_map_reads start a query of >= k symbols (none > 3 among its last k) from the
  * entry of its last k symbols instead of walking the first k steps of fmindex_inl.h:186-239; results are identical,
  * bit for bit (the loop would have stopped on the same pair). The table is the caller's memory, like the index. */

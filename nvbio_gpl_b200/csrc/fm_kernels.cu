@@ -319,7 +319,7 @@ static int fm_match_launch(nvb_ctx* ctx, const nvb_fmindex* fmi, nvb_string_set 
     cudaStream_t s = (cudaStream_t)stream;
     const uint32_t grid = grid_for(q.count);
     const bool kt = !FROM && f.ktab_k > 0;
-    if (f.ktab_k > 13u) return NVB_ERR_ARG;
+    if (f.ktab_k > 15u) return NVB_ERR_ARG;
     switch (queries.bits)
     {
     case 8: if (kt) fm_match_kernel<8, FROM, true><<<grid, FM_THREADS, 0, s>>>(f, q, ranges);
@@ -353,11 +353,11 @@ fm_ktab_kernel(const FMView f, uint32_t k, uint32_t n, uint2* __restrict__ tab)
     tab[idx] = make_uint2(x, y);
 }
 
-extern "C" size_t nvb_ktab_words(uint32_t k) { return k && k <= 13u ? (size_t)2 << (2u * k) : 0; }
+extern "C" size_t nvb_ktab_words(uint32_t k) { return k && k <= 15u ? (size_t)2 << (2u * k) : 0; }
 
 extern "C" int nvb_fmindex_build_ktab(nvb_ctx* ctx, const nvb_fmindex* fmi, uint32_t k, uint32_t* ktab, void* stream)
 {
-    if (!ctx || !ktab || k == 0 || k > 13u) return NVB_ERR_ARG;
+    if (!ctx || !ktab || k == 0 || k > 15u) return NVB_ERR_ARG;
     int rc = check_fmi(fmi, false); if (rc) return rc;
     FMView f = make_view(fmi); f.ktab = nullptr; f.ktab_k = 0;
     const uint32_t n = 1u << (2u * k);
