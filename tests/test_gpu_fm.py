@@ -211,7 +211,7 @@ def test_nvbwt_files_round_trip(oracle, tmp_path):
         c.close()
 
 
-@pytest.mark.parametrize("k", [1, 3, 8, 10])
+@pytest.mark.parametrize("k", [1, 3, 8, 10, 12])
 def test_kmer_jump_table(oracle, k):
     """match() through the k-mer jump table returns the raw ranges of the plain loop (fmindex_inl.h:186-239), also for
     absent queries (the pair the loop stopped on), queries shorter than k and queries with an N in their last k symbols"""
