@@ -41,7 +41,8 @@ typedef enum {
     NVB_ERR_ARG       = -1,  /* NULL / out-of-contract argument                         */
     NVB_ERR_CUDA      = -2,  /* a CUDA runtime call failed (see nvb_last_cuda_error)    */
     NVB_ERR_TEMP      = -3,  /* temp buffer smaller than nvb_temp_bytes(...)            */
-    NVB_ERR_UNSUPPORTED = -4 /* combination outside the contract        */
+    NVB_ERR_UNSUPPORTED = -4,/* combination outside the contract        */
+    NVB_ERR_TOO_LARGE = -5   /* problem larger than a fixed built-in limit (nvb_batch_score_noalloc) */
 } nvb_status;
 
 typedef struct nvb_ctx nvb_ctx;
@@ -238,6 +239,19 @@ size_t nvb_temp_bytes(int op, nvb_aligner aligner, uint32_t band, uint32_t check
 int nvb_batch_score(nvb_ctx* ctx, nvb_aligner aligner, nvb_string_set patterns, nvb_string_set texts,
                     nvb_best_sink* sinks, uint32_t max_pattern_len, uint32_t max_text_len,
                     void* temp, size_t temp_bytes, void* stream);
+
+/* nvb_batch_score without any allocation. NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same inputs, outputs and results as nvb_batch_score; the scratch (one int16 score column of max_text_len cells per pair,
+ * two for Gotoh) is a static device array of NVB_NOALLOC_SCRATCH_BYTES inside the library, held by every GPU that loads it
+ * until exit. Problems needing more -- nvb_batch_score_noalloc_bytes(aligner, max_text_len, n) > NVB_NOALLOC_SCRATCH_BYTES,
+ * i.e. more than 16 Mi cells (8 Mi for Gotoh) -- are rejected with NVB_ERR_TOO_LARGE: split the batch. The call makes no
+ * cudaMalloc / cudaFree and touches no context-owned buffer; it runs the int32 one-pair-per-thread kernels. All calls share
+ * the array: calls that overlap on the GPU (other streams, other host threads, other contexts on the same device) race. */
+#define NVB_NOALLOC_SCRATCH_BYTES (32u << 20)
+size_t nvb_batch_score_noalloc_bytes(nvb_aligner aligner, uint32_t max_text_len, uint32_t n);
+int nvb_batch_score_noalloc(nvb_ctx* ctx, nvb_aligner aligner, nvb_string_set patterns, nvb_string_set texts,
+                            nvb_best_sink* sinks, uint32_t max_pattern_len, uint32_t max_text_len, void* stream);
 
 /* aln::batch_banded_alignment_score<BAND_LEN>(...) (nvbio/alignment/batched.h:142-192,
  * batched_banded_inl.h:34-81,152-157). band in 2..64; pairs with text shorter than the pattern

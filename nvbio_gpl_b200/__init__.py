@@ -13,7 +13,7 @@ from .io import load_index, save_index, CLoadedIndex  # noqa: F401
 from .alignment import (  # noqa: F401
     EDIT_DISTANCE, SMITH_WATERMAN, GOTOH, GLOBAL, LOCAL, SEMI_GLOBAL,
     Aligner, EditDistanceAligner, SmithWatermanAligner, GotohAligner, StringSet,
-    batch_alignment_score, batch_banded_alignment_score,
+    batch_alignment_score, batch_banded_alignment_score, batch_alignment_score_noalloc, NOALLOC_SCRATCH_BYTES,
     MyersTag, MyersAligner, batch_banded_myers_score, batch_alignment_score_best2, MYERS_BATCH_MIN_SCORE,
     batch_alignment_traceback, batch_banded_alignment_traceback,
     batch_score_host, batch_traceback_host, ops_to_cigar, SINK_DT, ALN_DT,

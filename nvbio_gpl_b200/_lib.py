@@ -92,6 +92,8 @@ _PROTOS = {
     "nvb_fm_locate_host": (_i, [_vp, C.POINTER(FMIndexC), _vp, _u32, _vp]),
     "nvb_temp_bytes": (_sz, [_i, AlignerC, _u32, _u32, _u32, _u32, _u32]),
     "nvb_batch_score": (_i, [_vp, AlignerC, StringSetC, StringSetC, _vp, _u32, _u32, _vp, _sz, _vp]),
+    "nvb_batch_score_noalloc_bytes": (_sz, [AlignerC, _u32, _u32]),
+    "nvb_batch_score_noalloc": (_i, [_vp, AlignerC, StringSetC, StringSetC, _vp, _u32, _u32, _vp]),
     "nvb_batch_banded_score": (_i, [_vp, AlignerC, _u32, StringSetC, StringSetC, _vp, _u32, _u32, _vp, _sz, _vp]),
     "nvb_batch_score_best2": (_i, [_vp, AlignerC, _u32, _u32, StringSetC, StringSetC, _vp, _u32, _u32, _vp, _sz, _vp]),
     "nvb_batch_banded_myers_score": (_i, [_vp, C.c_int32, _u32, _u32, StringSetC, StringSetC, C.c_int32, _vp, _vp]),

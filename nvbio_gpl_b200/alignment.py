@@ -107,6 +107,18 @@ def batch_alignment_score(aligner, patterns, texts, sinks=None, temp=None, ctx=N
     return sinks
 
 
+NOALLOC_SCRATCH_BYTES = 32 << 20
+
+
+def batch_alignment_score_noalloc(aligner, patterns, texts, sinks, ctx=None):
+    """nvb_batch_score_noalloc: batch_alignment_score with its scratch in a static device array of the library (no allocation in
+    the call; `sinks` is the caller's int32 [n,3] tensor). Raises NvbError (status -5) beyond NOALLOC_SCRATCH_BYTES."""
+    ctx = _ctx(patterns.offsets, ctx)
+    check(lib().nvb_batch_score_noalloc(ctx.h, aligner.c(), patterns.c(), texts.c(), sinks.data_ptr(), patterns.max_len, texts.max_len,
+                                        _lib.current_stream_ptr()), ctx.h)
+    return sinks
+
+
 def batch_banded_alignment_score(aligner, band, patterns, texts, sinks=None, ctx=None):
     """aln::batch_banded_alignment_score<BAND_LEN>(...) (batched.h:142-192)"""
     ctx = _ctx(patterns.offsets, ctx)

@@ -16,6 +16,7 @@ extern "C" const char* nvb_status_string(int status)
     case NVB_ERR_CUDA:        return "CUDA error (no CPU fallback exists)";
     case NVB_ERR_TEMP:        return "temp buffer too small";
     case NVB_ERR_UNSUPPORTED: return "combination outside the contract";
+    case NVB_ERR_TOO_LARGE:   return "problem larger than the built-in limit of a no-allocation entry point (split the batch)";
     default:                  return "unknown status";
     }
 }

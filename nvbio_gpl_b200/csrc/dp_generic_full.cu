@@ -57,3 +57,60 @@ int dpg_full_traceback(nvb_ctx* ctx, const nvb_aligner& a, StrSet P, StrSet T, u
     #undef GO
     return NVB_ERR_ARG;
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// nvb_batch_score_noalloc -- full-matrix scoring that allocates NOTHING (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: CUDA graph capture, tight serving loops,
+// harnesses that forbid it). The score columns (one int16 column of max_text_len cells per pair, two for Gotoh) live in
+// a file-scope device array of NVB_NOALLOC_SCRATCH_BYTES that every GPU loading the library holds until exit. It runs the
+// int32 one-pair-per-thread kernels above (dpg_full_score_kernel), which initialise their columns themselves, so nothing
+// in the array has to start at zero; every call shares the array, so calls that overlap on the GPU (different streams,
+// different host threads) race on it.
+// ---------------------------------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NVB_NOALLOC_SCRATCH_BYTES];
+
+#include <mutex>
+// In host code g_noalloc_scratch is only a stand-in for the symbol: its device address is asked for once per device, with
+// that device current, and cached.
+static int noalloc_scratch_ptr(nvb_ctx* ctx, void** out)
+{
+    enum { MAX_DEVICES = 64 };
+    static void* ptrs[MAX_DEVICES] = { nullptr };
+    static std::mutex mtx;
+    int dev = -1;
+    NVB_CUDA(ctx, cudaGetDevice(&dev));
+    if (dev < 0 || dev >= MAX_DEVICES) return NVB_ERR_UNSUPPORTED;
+    std::lock_guard<std::mutex> lock(mtx);
+    if (!ptrs[dev])
+    {
+        void* p = nullptr;
+        NVB_CUDA(ctx, cudaGetSymbolAddress(&p, g_noalloc_scratch));
+        if (!p) return NVB_ERR_CUDA;
+        ptrs[dev] = p;
+    }
+    *out = ptrs[dev];
+    return NVB_OK;
+}
+
+extern "C" size_t nvb_batch_score_noalloc_bytes(nvb_aligner a, uint32_t max_text_len, uint32_t n)
+{ return (size_t)(a.kind == NVB_GOTOH ? 2 : 1) * max_text_len * (size_t)n * sizeof(int16_t); }
+
+extern "C" int nvb_batch_score_noalloc(nvb_ctx* ctx, nvb_aligner a, nvb_string_set patterns, nvb_string_set texts,
+                                       nvb_best_sink* sinks, uint32_t max_pattern_len, uint32_t max_text_len, void* stream)
+{
+    (void)max_pattern_len;
+    if (!ctx) return NVB_ERR_ARG;
+    if (a.kind < NVB_EDIT_DISTANCE || a.kind > NVB_GOTOH || a.type < NVB_GLOBAL || a.type > NVB_SEMI_GLOBAL) return NVB_ERR_ARG;
+    if (patterns.count != texts.count) return NVB_ERR_ARG;
+    const uint32_t n = patterns.count;
+    if (n == 0) return NVB_OK;
+    if (!sinks || !patterns.symbols || !patterns.offsets || !texts.symbols || !texts.offsets) return NVB_ERR_ARG;
+    if (!(patterns.bits == 8 || patterns.bits == 4 || patterns.bits == 2) || !(texts.bits == 8 || texts.bits == 4 || texts.bits == 2)) return NVB_ERR_ARG;
+    if (nvb_batch_score_noalloc_bytes(a, max_text_len, n) > (size_t)NVB_NOALLOC_SCRATCH_BYTES) return NVB_ERR_TOO_LARGE;
+    void* scratch = nullptr;
+    int rc = noalloc_scratch_ptr(ctx, &scratch);
+    if (rc) return rc;
+    ctx->last_paths = 2u;
+    return dpg_full_score(ctx, a, make_set(patterns), make_set(texts), nullptr, nullptr, 0, n, sinks, (int16_t*)scratch, max_text_len,
+                          (cudaStream_t)stream);
+}
