@@ -169,6 +169,11 @@ int nvb_fmindex_fuse(nvb_ctx* ctx, const uint32_t* bwt_words, uint32_t length, u
  * ranges: 2 uint32 per query = the raw inclusive SA interval (x,y); empty iff x > y. */
 int nvb_fm_match(nvb_ctx* ctx, const nvb_fmindex* fmi, nvb_string_set queries, uint32_t* ranges,
                  void* stream);
+/* match_reverse(fmi, pattern, len) (nvbio/fmindex/fmindex_inl.h:252-278): the same search consuming the pattern front to
+ * back, i.e. match() of the reversed pattern -- what nvBowtie runs against the index of the REVERSED text (.rbwt/.rsa,
+ * nvb_fmindex_load(reverse = 1); nvBowtie/bowtie2/cuda/mapping_inl.h:71-86) */
+int nvb_fm_match_reverse(nvb_ctx* ctx, const nvb_fmindex* fmi, nvb_string_set queries, uint32_t* ranges,
+                         void* stream);
 /* match continued from given ranges: match(fmi, pattern, len, range) (fmindex_inl.h:212-239);
  * ranges is in/out */
 int nvb_fm_match_from(nvb_ctx* ctx, const nvb_fmindex* fmi, nvb_string_set queries, uint32_t* ranges,

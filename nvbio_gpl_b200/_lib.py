@@ -76,6 +76,7 @@ _PROTOS = {
     "nvb_fmindex_fuse": (_i, [_vp, _vp, _u32, _vp, _vp, _vp]),
     "nvb_fm_match": (_i, [_vp, C.POINTER(FMIndexC), StringSetC, _vp, _vp]),
     "nvb_fm_match_from": (_i, [_vp, C.POINTER(FMIndexC), StringSetC, _vp, _vp]),
+    "nvb_fm_match_reverse": (_i, [_vp, C.POINTER(FMIndexC), StringSetC, _vp, _vp]),
     "nvb_fm_match_approx": (_i, [_vp, C.POINTER(FMIndexC), StringSetC, _u32, _i, _u32, _vp, _vp, _vp]),
     "nvb_fm_rank": (_i, [_vp, C.POINTER(FMIndexC), _vp, _vp, _u32, _vp, _vp]),
     "nvb_fm_rank4": (_i, [_vp, C.POINTER(FMIndexC), _vp, _u32, _vp, _vp]),

@@ -110,11 +110,24 @@ def batch_alignment_score(aligner, patterns, texts, sinks=None, temp=None, ctx=N
 NOALLOC_SCRATCH_BYTES = 32 << 20
 
 
-def batch_alignment_score_noalloc(aligner, patterns, texts, sinks, ctx=None):
-    """nvb_batch_score_noalloc: batch_alignment_score with its scratch in a static device array of the library (no allocation in
-    the call; `sinks` is the caller's int32 [n,3] tensor). Raises NvbError (status -5) beyond NOALLOC_SCRATCH_BYTES."""
+def batch_alignment_score_noalloc(aligner, patterns, texts, sinks, max_pattern_len=None, max_text_len=None, ctx=None):
+    """nvb_batch_score_noalloc: batch_alignment_score with its scratch in a static device array of the library (no allocation and
+    no synchronisation in the call, so it can run under CUDA graph capture once a Context exists). `sinks` is the caller's int32
+    [n,3] tensor on the sets' device. The maximum lengths must be known without touching the device: pass them, or build the
+    StringSets with max_len (from_numpy does). Raises NvbError (status -5) beyond NOALLOC_SCRATCH_BYTES."""
     ctx = _ctx(patterns.offsets, ctx)
-    check(lib().nvb_batch_score_noalloc(ctx.h, aligner.c(), patterns.c(), texts.c(), sinks.data_ptr(), patterns.max_len, texts.max_len,
+    maxM = patterns._max_len if max_pattern_len is None else int(max_pattern_len)
+    maxN = texts._max_len if max_text_len is None else int(max_text_len)
+    if maxM is None or maxN is None:
+        raise _lib.NvbError("batch_alignment_score_noalloc: maximum string lengths unknown; computing them would allocate and "
+                            "synchronise -- pass max_pattern_len / max_text_len or construct the StringSets with max_len")
+    n = patterns.count
+    if texts.count != n:
+        raise _lib.NvbError("batch_alignment_score_noalloc: %d patterns but %d texts" % (n, texts.count))
+    if not (isinstance(sinks, torch.Tensor) and sinks.is_cuda and sinks.device == patterns.offsets.device and sinks.dtype == torch.int32
+            and sinks.is_contiguous() and tuple(sinks.shape) == (n, 3)):
+        raise _lib.NvbError("batch_alignment_score_noalloc: sinks must be a contiguous int32 [%d, 3] tensor on %s" % (n, patterns.offsets.device))
+    check(lib().nvb_batch_score_noalloc(ctx.h, aligner.c(), patterns.c(), texts.c(), sinks.data_ptr(), maxM, maxN,
                                         _lib.current_stream_ptr()), ctx.h)
     return sinks
 

@@ -39,6 +39,10 @@ extern "C" int nvb_ctx_create(int device, nvb_ctx** out)
     if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return NVB_ERR_CUDA; }
     for (int i = 0; i < 2; ++i)
         if (cudaStreamCreateWithFlags(&c->aux[i], cudaStreamNonBlocking) != cudaSuccess) { delete c; return NVB_ERR_CUDA; }
+    // nvb_batch_score_noalloc: the address of its static scratch array is resolved here, once per device, so that the entry
+    // point itself can be the first thing a caller runs under CUDA graph capture (a failure only surfaces there)
+    (void)nvb_noalloc_warmup(c);
+    c->last_err = cudaSuccess; cudaGetLastError();
     *out = c;
     return NVB_OK;
 }

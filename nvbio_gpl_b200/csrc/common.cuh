@@ -43,6 +43,7 @@ struct nvb_ctx
 
 int   nvb_stage(nvb_ctx* ctx, int slot, size_t bytes, void** out);
 int   nvb_worklist(nvb_ctx* ctx, size_t entries, uint32_t** out);
+int   nvb_noalloc_warmup(nvb_ctx* ctx);   // dp_generic_full.cu: resolves the static scratch array's device address for ctx->device
 
 // ---------------------------------------------------------------------------------------------
 // device-side view of the fused nvBWT index

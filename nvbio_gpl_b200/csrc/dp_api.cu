@@ -60,8 +60,15 @@ static uint32_t batch_pairs(const TempPlan& p, size_t temp_bytes, uint32_t n)
     if (per == 0) return n;
     if (temp_bytes < 256) return 0;
     size_t fit = (temp_bytes - 256) / per;
-    if (fit >= n) return n;
+    // the tracebacks place their flow region behind the int16 region of the batch rounded up to 128 pairs: "everything
+    // fits" must hold for that rounded layout too, or a buffer sized per * n + 256 with n % 128 != 0 would be overrun
+    if (fit >= n)
+    {
+        const size_t n128 = ((size_t)n + 127) & ~(size_t)127;
+        if (p.flow_per_pair == 0 || p.i16_per_pair * 2 * n128 + p.flow_per_pair * (size_t)n + 256 <= temp_bytes) return n;
+    }
     fit &= ~(size_t)127;
+    if (fit > n) fit = n & ~(size_t)127;
     return (uint32_t)fit;
 }
 

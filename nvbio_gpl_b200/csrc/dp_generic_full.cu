@@ -71,20 +71,27 @@ static __device__ __align__(256) unsigned char g_noalloc_scratch[NVB_NOALLOC_SCR
 
 #include <mutex>
 // In host code g_noalloc_scratch is only a stand-in for the symbol: its device address is asked for once per device, with
-// that device current, and cached.
+// THAT device current (the context's device, whatever the caller's current device is), and cached for the life of the
+// process (cudaDeviceReset invalidates it, like every other device pointer the process holds). The first use per device
+// must happen outside CUDA graph capture: nvb_ctx_create does it (nvb_noalloc_warmup), so a context created before
+// capture begins is enough.
 static int noalloc_scratch_ptr(nvb_ctx* ctx, void** out)
 {
     enum { MAX_DEVICES = 64 };
     static void* ptrs[MAX_DEVICES] = { nullptr };
     static std::mutex mtx;
-    int dev = -1;
-    NVB_CUDA(ctx, cudaGetDevice(&dev));
+    const int dev = ctx->device;
     if (dev < 0 || dev >= MAX_DEVICES) return NVB_ERR_UNSUPPORTED;
     std::lock_guard<std::mutex> lock(mtx);
     if (!ptrs[dev])
     {
+        int cur = -1;
+        NVB_CUDA(ctx, cudaGetDevice(&cur));
+        if (cur != dev) NVB_CUDA(ctx, cudaSetDevice(dev));
         void* p = nullptr;
-        NVB_CUDA(ctx, cudaGetSymbolAddress(&p, g_noalloc_scratch));
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (cur != dev && cur >= 0) cudaSetDevice(cur);
+        if (e != cudaSuccess) { ctx->last_err = e; return NVB_ERR_CUDA; }
         if (!p) return NVB_ERR_CUDA;
         ptrs[dev] = p;
     }
@@ -92,8 +99,15 @@ static int noalloc_scratch_ptr(nvb_ctx* ctx, void** out)
     return NVB_OK;
 }
 
+// resolves the static array's address for ctx's device (called by nvb_ctx_create; harmless to call again)
+int nvb_noalloc_warmup(nvb_ctx* ctx) { void* p = nullptr; return noalloc_scratch_ptr(ctx, &p); }
+
+// saturating: a product that does not fit size_t reads as SIZE_MAX (> any limit)
 extern "C" size_t nvb_batch_score_noalloc_bytes(nvb_aligner a, uint32_t max_text_len, uint32_t n)
-{ return (size_t)(a.kind == NVB_GOTOH ? 2 : 1) * max_text_len * (size_t)n * sizeof(int16_t); }
+{
+    const unsigned __int128 b = (unsigned __int128)(a.kind == NVB_GOTOH ? 2u : 1u) * max_text_len * n * sizeof(int16_t);
+    return b > (unsigned __int128)SIZE_MAX ? SIZE_MAX : (size_t)b;
+}
 
 extern "C" int nvb_batch_score_noalloc(nvb_ctx* ctx, nvb_aligner a, nvb_string_set patterns, nvb_string_set texts,
                                        nvb_best_sink* sinks, uint32_t max_pattern_len, uint32_t max_text_len, void* stream)

@@ -19,7 +19,8 @@
 // The query symbols of a CTA are one contiguous span of the concatenated set: it is staged into
 // shared memory with coalesced 16-byte loads, so the dependent loop only touches the index.
 // ---------------------------------------------------------------------------------------------
-template <int BITS, bool FROM, bool KTAB>
+// REV: match_reverse (fmindex_inl.h:252-278) -- the same loop consuming the pattern front to back.
+template <int BITS, bool FROM, bool KTAB, bool REV>
 __global__ void __launch_bounds__(FM_THREADS)
 fm_match_kernel(const FMView f, const StrSet q, uint32_t* __restrict__ ranges)
 {
@@ -67,38 +68,40 @@ fm_match_kernel(const FMView f, const StrSet q, uint32_t* __restrict__ ranges)
     if (FROM) { x = ranges[2 * tid]; y = ranges[2 * tid + 1]; }
     else      { x = 0; y = f.length; }
 
-    int32_t i = (int32_t)len - 1;
+    // search step t consumes symbol len - 1 - t (match) or t (match_reverse)
+    auto consumed = [&](uint32_t t) -> uint32_t { return symbol(beg + (REV ? t : len - 1u - t)); };
+    uint32_t t = 0;
     if (KTAB && !FROM && len >= f.ktab_k)
     {
-        // the last k symbols select a precomputed (x, y): the pair the loop below reaches after its first k steps
+        // the first k consumed symbols select a precomputed (x, y): the pair the loop below reaches after its first k steps
         // (or the pair it stopped on); a symbol > 3 among them leaves the query to the loop
         uint32_t idx = 0, bad = 0;
-        for (uint32_t j = len - f.ktab_k; j < len; ++j)
+        for (uint32_t j = 0; j < f.ktab_k; ++j)
         {
-            const uint32_t c = symbol(beg + j);
-            bad |= c; idx = idx * 4u + (c & 3u);
+            const uint32_t c = consumed(j);
+            bad |= c; idx |= (c & 3u) << (2u * j);
         }
-        if (bad <= 3u) { const uint2 r = __ldg(f.ktab + idx); x = r.x; y = r.y; i -= (int32_t)f.ktab_k; }
+        if (bad <= 3u) { const uint2 r = __ldg(f.ktab + idx); x = r.x; y = r.y; t = f.ktab_k; }
     }
     // first step: x - 1 may be -1 and y may be length (from [0, length] the reference's shortcuts touch no block at all)
-    if (i >= 0 && x <= y)
+    if (t < len && x <= y)
     {
-        const uint32_t c = symbol(beg + (uint32_t)i);
-        if (c > 3u) { x = 1; y = 0; i = -1; }
+        const uint32_t c = consumed(t);
+        if (c > 3u) { x = 1; y = 0; t = len; }
         else
         {
             const uint2 r = fm_rank2(f, x - 1u, y, c, s_lut);
             x = s_L2[c] + r.x + 1u;
             y = s_L2[c] + r.y;
-            --i;
+            ++t;
         }
     }
     // every later step has x >= 1: the lean form (an index whose primary row is 0 keeps the general one)
     if (f.primary != 0u)
     {
-        for (; i >= 0 && x <= y; --i)
+        for (; t < len && x <= y; ++t)
         {
-            const uint32_t c = symbol(beg + (uint32_t)i);
+            const uint32_t c = consumed(t);
             if (c > 3u) { x = 1; y = 0; break; }
             const uint2 r = fm_rank2_inner(f, x - 1u, y, c, s_lut);
             x = s_L2[c] + r.x + 1u;
@@ -107,9 +110,9 @@ fm_match_kernel(const FMView f, const StrSet q, uint32_t* __restrict__ ranges)
     }
     else
     {
-        for (; i >= 0 && x <= y; --i)
+        for (; t < len && x <= y; ++t)
         {
-            const uint32_t c = symbol(beg + (uint32_t)i);
+            const uint32_t c = consumed(t);
             if (c > 3u) { x = 1; y = 0; break; }
             const uint2 r = fm_rank2(f, x - 1u, y, c, s_lut);
             x = s_L2[c] + r.x + 1u;
@@ -306,7 +309,7 @@ static inline uint32_t grid_for(uint32_t n) { return (n + FM_THREADS - 1) / FM_T
 // the load-balanced walks run on a grid that just fills the device (8 CTAs of 256 threads per SM)
 static inline uint32_t walk_grid(const nvb_ctx* ctx, uint32_t n) { const uint32_t g = grid_for(n), p = (uint32_t)ctx->sm_count * 8u; return g < p ? g : p; }
 
-template <bool FROM>
+template <bool FROM, bool REV>
 static int fm_match_launch(nvb_ctx* ctx, const nvb_fmindex* fmi, nvb_string_set queries, uint32_t* ranges,
                            void* stream)
 {
@@ -322,12 +325,12 @@ static int fm_match_launch(nvb_ctx* ctx, const nvb_fmindex* fmi, nvb_string_set 
     if (f.ktab_k > 15u) return NVB_ERR_ARG;
     switch (queries.bits)
     {
-    case 8: if (kt) fm_match_kernel<8, FROM, true><<<grid, FM_THREADS, 0, s>>>(f, q, ranges);
-            else    fm_match_kernel<8, FROM, false><<<grid, FM_THREADS, 0, s>>>(f, q, ranges); break;
-    case 4: if (kt) fm_match_kernel<4, FROM, true><<<grid, FM_THREADS, 0, s>>>(f, q, ranges);
-            else    fm_match_kernel<4, FROM, false><<<grid, FM_THREADS, 0, s>>>(f, q, ranges); break;
-    case 2: if (kt) fm_match_kernel<2, FROM, true><<<grid, FM_THREADS, 0, s>>>(f, q, ranges);
-            else    fm_match_kernel<2, FROM, false><<<grid, FM_THREADS, 0, s>>>(f, q, ranges); break;
+    case 8: if (kt) fm_match_kernel<8, FROM, true, REV><<<grid, FM_THREADS, 0, s>>>(f, q, ranges);
+            else    fm_match_kernel<8, FROM, false, REV><<<grid, FM_THREADS, 0, s>>>(f, q, ranges); break;
+    case 4: if (kt) fm_match_kernel<4, FROM, true, REV><<<grid, FM_THREADS, 0, s>>>(f, q, ranges);
+            else    fm_match_kernel<4, FROM, false, REV><<<grid, FM_THREADS, 0, s>>>(f, q, ranges); break;
+    case 2: if (kt) fm_match_kernel<2, FROM, true, REV><<<grid, FM_THREADS, 0, s>>>(f, q, ranges);
+            else    fm_match_kernel<2, FROM, false, REV><<<grid, FM_THREADS, 0, s>>>(f, q, ranges); break;
     default: return NVB_ERR_ARG;
     }
     NVB_LAUNCHED(ctx);
@@ -393,10 +396,13 @@ extern "C" int nvb_fmindex_build_dssa(nvb_ctx* ctx, const nvb_fmindex* fmi, uint
 }
 
 extern "C" int nvb_fm_match(nvb_ctx* ctx, const nvb_fmindex* fmi, nvb_string_set queries, uint32_t* ranges, void* stream)
-{ return fm_match_launch<false>(ctx, fmi, queries, ranges, stream); }
+{ return fm_match_launch<false, false>(ctx, fmi, queries, ranges, stream); }
+
+extern "C" int nvb_fm_match_reverse(nvb_ctx* ctx, const nvb_fmindex* fmi, nvb_string_set queries, uint32_t* ranges, void* stream)
+{ return fm_match_launch<false, true>(ctx, fmi, queries, ranges, stream); }
 
 extern "C" int nvb_fm_match_from(nvb_ctx* ctx, const nvb_fmindex* fmi, nvb_string_set queries, uint32_t* ranges, void* stream)
-{ return fm_match_launch<true>(ctx, fmi, queries, ranges, stream); }
+{ return fm_match_launch<true, false>(ctx, fmi, queries, ranges, stream); }
 
 extern "C" int nvb_fm_match_approx(nvb_ctx* ctx, const nvb_fmindex* fmi, nvb_string_set queries, uint32_t len1, int find_exact,
                                    uint32_t cap, uint32_t* ranges, uint32_t* counts, void* stream)
@@ -521,7 +527,7 @@ extern "C" int nvb_fm_filter_rank(nvb_ctx* ctx, const nvb_fmindex* fmi, nvb_stri
 {
     if (!ctx || !ranges || !slots) return NVB_ERR_ARG;
     if (n_hits_h) *n_hits_h = 0;
-    int rc = fm_match_launch<false>(ctx, fmi, queries, ranges, stream); if (rc) return rc;
+    int rc = fm_match_launch<false, false>(ctx, fmi, queries, ranges, stream); if (rc) return rc;
     const uint32_t n = queries.count;
     if (n == 0) return NVB_OK;
     cudaStream_t s = (cudaStream_t)stream;

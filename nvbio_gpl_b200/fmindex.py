@@ -252,6 +252,17 @@ def match(fmi, symbols, offsets, ranges=None, bits=8, ctx=None):
     return ranges
 
 
+def match_reverse(fmi, symbols, offsets, bits=8, ctx=None):
+    """match_reverse(fmi, pattern, len) for every string (fmindex_inl.h:252-278): the pattern is consumed front to back, so on
+    the index of the reversed text (nvBWT's .rbwt/.rsa) it finds the occurrences of the pattern itself. int32 [n,2] raw ranges."""
+    ctx = _ctx(fmi.bwt_occ, ctx)
+    n = offsets.numel() - 1
+    ranges = torch.empty((n, 2), dtype=torch.int32, device=fmi.device)
+    f = fmi.c()
+    check(lib().nvb_fm_match_reverse(ctx.h, C.byref(f), _set_c(symbols, offsets, bits), ranges.data_ptr(), _lib.current_stream_ptr()), ctx.h)
+    return ranges
+
+
 def match_approx(fmi, symbols, offsets, len1, find_exact=True, cap=64, bits=8, ctx=None):
     """nvBowtie's map<find_exact> (mapping_inl.h:114-184): exact over the first len1 search steps, one substitution allowed in the
     rest. Returns (ranges int32 [n, cap, 2] holding raw uint32 SA ranges in the reference's push order, counts int32 [n])."""

@@ -54,11 +54,12 @@ class CLoadedIndex:
         self.f = FMIndexC()
         check(lib().nvb_fmindex_load(self.ctx.h, prefix.encode(), 1 if reverse else 0, C.byref(self.f)), self.ctx.h)
 
-    def match(self, symbols, offsets, bits=8):
+    def match(self, symbols, offsets, bits=8, reverse=False):
         from .fmindex import _set_c
         n = offsets.numel() - 1
         ranges = torch.empty((n, 2), dtype=torch.int32, device=offsets.device)
-        check(lib().nvb_fm_match(self.ctx.h, C.byref(self.f), _set_c(symbols, offsets, bits), ranges.data_ptr(), _lib.current_stream_ptr()), self.ctx.h)
+        fn = lib().nvb_fm_match_reverse if reverse else lib().nvb_fm_match
+        check(fn(self.ctx.h, C.byref(self.f), _set_c(symbols, offsets, bits), ranges.data_ptr(), _lib.current_stream_ptr()), self.ctx.h)
         return ranges
 
     def locate(self, rows):

@@ -63,6 +63,10 @@ int ORC(build_index)(const uint8_t* text, uint32_t n, uint32_t* primary, uint32_
 int ORC(fm_match)(const orc_fmindex* fmi, const uint8_t* symbols, const uint32_t* offsets,
                   uint32_t count, uint32_t* ranges, uint32_t* blocks, int threads);
 
+/* match_reverse (fmindex_inl.h:252-278): the pattern consumed front to back */
+int ORC(fm_match_reverse)(const orc_fmindex* fmi, const uint8_t* symbols, const uint32_t* offsets,
+                          uint32_t count, uint32_t* ranges, int threads);
+
 /* rank of symbol c[i] over the range pairs (x,y); out = 2 uint32 per query */
 int ORC(fm_rank)(const orc_fmindex* fmi, const uint32_t* ranges, const uint8_t* c,
                  uint32_t count, uint32_t* out, int threads);

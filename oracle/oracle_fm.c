@@ -224,6 +224,31 @@ int orc_fm_match(const orc_fmindex* f, const uint8_t* symbols, const uint32_t* o
     return 0;
 }
 
+/* forward search over the pattern = backward search of the reversed pattern: nvbio/fmindex/fmindex_inl.h:252-278 */
+int orc_fm_match_reverse(const orc_fmindex* f, const uint8_t* symbols, const uint32_t* offsets,
+                         uint32_t count, uint32_t* ranges, int threads)
+{
+    if (threads <= 0) threads = omp_get_max_threads();
+    #pragma omp parallel for schedule(dynamic,256) num_threads(threads)
+    for (int64_t q = 0; q < (int64_t)count; ++q)
+    {
+        const uint8_t* p = symbols + offsets[q];
+        const uint32_t len = offsets[q + 1] - offsets[q];
+        uint32_t x = 0, y = f->length;
+        for (uint32_t i = 0; i < len && x <= y; ++i)
+        {
+            const uint32_t c = p[i];
+            if (c > 3) { x = 1; y = 0; break; }
+            uint32_t rx, ry;
+            fm_rank2(f, x - 1u, y, c, &rx, &ry, NULL);
+            x = f->L2[c] + rx + 1u;
+            y = f->L2[c] + ry;
+        }
+        ranges[2 * q] = x; ranges[2 * q + 1] = y;
+    }
+    return 0;
+}
+
 int orc_fm_rank(const orc_fmindex* f, const uint32_t* ranges, const uint8_t* c, uint32_t count,
                 uint32_t* out, int threads)
 {

@@ -146,6 +146,16 @@ class Oracle:
         assert rc == 0, rc
         return (ranges, blocks) if want_blocks else ranges
 
+    def fm_match_reverse(self, idx, symbols, offsets, threads=0):
+        n = len(offsets) - 1
+        symbols = np.ascontiguousarray(symbols, dtype=np.uint8)
+        offsets = np.ascontiguousarray(offsets, dtype=np.uint32)
+        ranges = np.zeros((n, 2), dtype=np.uint32)
+        f = idx.c()
+        rc = self._f("fm_match_reverse")(C.byref(f), _ptr(symbols), _ptr(offsets), C.c_uint32(n), _ptr(ranges), C.c_int(threads))
+        assert rc == 0, rc
+        return ranges
+
     def fm_rank(self, idx, ranges, c, threads=0):
         ranges = np.ascontiguousarray(ranges, dtype=np.uint32)
         c = np.ascontiguousarray(c, dtype=np.uint8)

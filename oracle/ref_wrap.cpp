@@ -126,6 +126,20 @@ int ref_fm_match(const orc_fmindex* f, const uint8_t* symbols, const uint32_t* o
     return 0;
 }
 
+int ref_fm_match_reverse(const orc_fmindex* f, const uint8_t* symbols, const uint32_t* offsets,
+                         uint32_t count, uint32_t* ranges, int threads)
+{
+    const fm_index_type fmi = make_fmi( f );
+    if (threads <= 0) threads = omp_get_max_threads();
+    #pragma omp parallel for schedule(dynamic,256) num_threads(threads)
+    for (int64 q = 0; q < int64(count); ++q)
+    {
+        const uint2 r = match_reverse( fmi, symbols + offsets[q], offsets[q+1] - offsets[q] );
+        ranges[2*q] = r.x; ranges[2*q+1] = r.y;
+    }
+    return 0;
+}
+
 int ref_fm_rank(const orc_fmindex* f, const uint32_t* ranges, const uint8_t* c, uint32_t count,
                 uint32_t* out, int threads)
 {

@@ -293,3 +293,46 @@ def test_match_approx(oracle):
         want_r, want_c = oracle.fm_match_approx(oidx, Q, qo, 10, True, cap=64)
         got_r, got_c = nvb.match_approx(fmi, w, qs.offsets, 10, True, cap=64, bits=4)
         assert (u32(got_c) == want_c).all() and (u32(got_r).reshape(-1, 64, 2) == want_r).all()
+
+
+def test_match_reverse_and_reverse_index_files(oracle, tmp_path):
+    """nvb_fm_match_reverse (fmindex_inl.h:252-278) vs the oracle (raw ranges, N symbols, empty patterns, packed sets, with
+    and without the k-mer table), and nvBowtie's use of it: the reverse index written to / read from .rbwt + .rsa
+    (nvb_fmindex_save/load with reverse = 1) finds as many occurrences as match() on the forward index"""
+    rng = np.random.default_rng(61)
+    for n, alpha in ((60000, 4), (3000, 2), (65, 4), (1, 4)):
+        text = rng.integers(0, alpha, n).astype(np.uint8)
+        fmi, oidx = gu.fm_index_pair(oracle, text)
+        Q, qo = util.rand_queries(rng, text, 20000, len_range=(0, 36), alpha=alpha)
+        qs = gu.sset(Q, qo)
+        want = oracle.fm_match_reverse(oidx, Q, qo)
+        assert (u32(nvb.match_reverse(fmi, qs.symbols, qs.offsets)) == want).all()
+        w4 = torch.from_numpy(nvb.pack_symbols(Q, 4).view(np.int32)).to(gu.dev())
+        assert (u32(nvb.match_reverse(fmi, w4, qs.offsets, bits=4)) == want).all()
+        fmi.build_ktab(6)
+        assert (u32(nvb.match_reverse(fmi, qs.symbols, qs.offsets)) == want).all()
+        fmi.drop_ktab()
+        # the reverse index through the nvBWT files
+        rtext = text[::-1].copy()
+        rfmi, ridx = gu.fm_index_pair(oracle, rtext)
+        prefix = str(tmp_path / ("r%d" % n))
+        nvb.save_index(rfmi, prefix, reverse=True)
+        import os
+        assert os.path.exists(prefix + ".rbwt") and os.path.exists(prefix + ".rsa") and not os.path.exists(prefix + ".bwt")
+        back = nvb.load_index(prefix, gu.dev(), reverse=True)
+        b2, s2 = back.host_arrays()
+        assert back.primary == ridx.primary and (b2 == ridx.bwt_occ).all() and (s2 == ridx.ssa).all()
+        c = nvb.CLoadedIndex(prefix, reverse=True)
+        got_r = c.match(qs.symbols, qs.offsets, reverse=True).cpu().numpy().view(np.uint32)
+        assert (got_r == oracle.fm_match_reverse(ridx, Q, qo)).all()
+        fw = oracle.fm_match(oidx, Q, qo)
+        cnt = lambda r: np.where(r[:, 0] <= r[:, 1], r[:, 1].astype(np.int64) - r[:, 0] + 1, 0)
+        assert (cnt(got_r) == cnt(fw)).all()
+        # a located row of the reverse index is an occurrence in the reversed text: position p <-> n - p - len in the forward text
+        ok = np.nonzero((got_r[:, 0] <= got_r[:, 1]) & (np.diff(qo.astype(np.int64)) >= 8))[0][:300]
+        if len(ok):
+            pos = c.locate(torch.from_numpy(got_r[ok, 0].copy().view(np.int32)).to(gu.dev())).cpu().numpy().view(np.uint32)
+            for p, i in zip(pos, ok):
+                L = int(qo[i + 1] - qo[i])
+                assert (rtext[p:p + L][::-1] == Q[qo[i]:qo[i + 1]]).all()
+        c.close()

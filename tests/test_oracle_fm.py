@@ -144,3 +144,18 @@ def test_match_approx_oracle_vs_reference_composition(oracle, ref):
                 a = oracle.fm_match_approx(idx, Q, qo, len1, fe, cap=80)
                 b = ref.fm_match_approx(idx, Q, qo, len1, fe, cap=80)
                 assert (a[1] == b[1]).all() and (a[0] == b[0]).all()
+
+
+def test_match_reverse_on_the_reverse_index_counts_forward_occurrences(oracle):
+    """how nvBowtie uses it (mapping_inl.h:71-86): match_reverse over the index of the REVERSED text finds the pattern's own
+    occurrences -- the range sizes equal those of match() over the forward index, and match_reverse(q) == match(reversed q)"""
+    rng = np.random.default_rng(77)
+    for n, alpha in ((5000, 4), (700, 2)):
+        text = rng.integers(0, alpha, n).astype(np.uint8)
+        fwd, rev = oracle.build_index(text), oracle.build_index(text[::-1].copy())
+        Q, qo = util.rand_queries(rng, text, 3000, len_range=(0, 16), alpha=alpha)
+        a, b = oracle.fm_match(fwd, Q, qo), oracle.fm_match_reverse(rev, Q, qo)
+        cnt = lambda r: np.where(r[:, 0] <= r[:, 1], r[:, 1].astype(np.int64) - r[:, 0] + 1, 0)
+        assert (cnt(a) == cnt(b)).all()
+        Qr, _ = po.concat([Q[qo[i]:qo[i + 1]][::-1] for i in range(len(qo) - 1)])
+        assert (oracle.fm_match_reverse(fwd, Q, qo) == oracle.fm_match(fwd, Qr, qo)).all()

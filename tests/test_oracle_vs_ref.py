@@ -17,6 +17,7 @@ def test_fm_index_build_and_queries(oracle, ref, n, alpha):
     Q, qo = util.rand_queries(rng, text, 3000, alpha=alpha)
     ra, rb = ref.fm_match(a, Q, qo), oracle.fm_match(b, Q, qo)
     assert (ra == rb).all()
+    assert (ref.fm_match_reverse(a, Q, qo) == oracle.fm_match_reverse(b, Q, qo)).all()      # fmindex_inl.h:252-278
     ok = ra[:, 0] <= ra[:, 1]
     rows = np.concatenate([ra[ok, 0], ra[ok, 1], rng.integers(0, n + 1, 500).astype(np.uint32)])
     pa, sa = ref.fm_locate(a, rows, True)

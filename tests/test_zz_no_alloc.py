@@ -32,9 +32,13 @@ def test_noalloc_score_equals_batch_score_twice_in_a_row(oracle):
             want = gu.sinks_np(nvb.batch_alignment_score(a, ps, ts, ctx=ctx))
             sinks = torch.full((ps.count, 3), 7, dtype=torch.int32, device=gu.dev())
             torch.cuda.synchronize()
-            mem0 = torch.cuda.memory_allocated()
-            got = gu.sinks_np(nvb.batch_alignment_score_noalloc(a, ps, ts, sinks, ctx=ctx))
-            assert torch.cuda.memory_allocated() == mem0
+            # driver-level free memory (cudaMemGetInfo): a cudaMalloc inside the library would show here, torch's own
+            # allocator statistics would not see it
+            free0, mem0 = torch.cuda.mem_get_info()[0], torch.cuda.memory_allocated()
+            nvb.batch_alignment_score_noalloc(a, ps, ts, sinks, ctx=ctx)
+            torch.cuda.synchronize()
+            assert torch.cuda.mem_get_info()[0] == free0 and torch.cuda.memory_allocated() == mem0
+            got = gu.sinks_np(sinks)
             assert ctx.last_paths == 2
             assert (got == want).all(), (kind, ty, np.nonzero(got != want)[0][:5])
             assert (got == oracle.score(oa, P, Po, T, To)).all()
@@ -62,4 +66,46 @@ def test_noalloc_limit_is_enforced():
     ps2 = nvb.StringSet(ps.symbols[:k * 10], off_p[:k + 1].contiguous(), 8, 10)
     ts2 = nvb.StringSet(ts.symbols[:k * N], off_t[:k + 1].contiguous(), 8, N)
     nvb.batch_alignment_score_noalloc(a, ps2, ts2, sinks[:k], ctx=ctx)
+    torch.cuda.synchronize()
+
+
+def test_noalloc_runs_under_cuda_graph_capture(oracle):
+    """the advertised use: captured in a CUDA graph (where cudaMalloc is illegal) and replayed on new inputs in the same buffers"""
+    rng = np.random.default_rng(77)
+    ctx = nvb.Context.default(0)           # created outside capture: resolves the static array's address for this device
+    a, oa = nvb.GotohAligner(nvb.LOCAL, 2, -2, -5, -3), po.aligner(po.GOTOH, po.LOCAL, (2, -2, -5, -3))
+    n, M, N = 2000, 60, 120
+    batches = [util.rand_pairs(rng, n, (M, M + 1), lambda m: N, 4) for _ in range(2)]
+    P, Po, T, To = batches[0]
+    ps, ts = gu.sset(P, Po), gu.sset(T, To)
+    sinks = torch.zeros((n, 3), dtype=torch.int32, device=gu.dev())
+    nvb.batch_alignment_score_noalloc(a, ps, ts, sinks, ctx=ctx)          # warm: module load, lazy kernel load
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        nvb.batch_alignment_score_noalloc(a, ps, ts, sinks, max_pattern_len=M, max_text_len=N, ctx=ctx)
+    for P, Po, T, To in batches[::-1]:     # replay on other symbols written into the captured buffers (same offsets: fixed lengths)
+        ps.symbols.copy_(torch.from_numpy(P)); ts.symbols.copy_(torch.from_numpy(T))
+        sinks.fill_(9)
+        g.replay()
+        torch.cuda.synchronize()
+        assert (gu.sinks_np(sinks) == oracle.score(oa, P, Po, T, To)).all()
+
+
+def test_noalloc_python_wrapper_validates_arguments():
+    dev = gu.dev()
+    a = nvb.SmithWatermanAligner(nvb.LOCAL, 2, -1, -1, -1)
+    off = (torch.arange(5, device=dev, dtype=torch.int64) * 4).to(torch.int32)
+    ps = nvb.StringSet(torch.zeros(16, dtype=torch.uint8, device=dev), off, 8)        # no max_len given
+    ts = nvb.StringSet(torch.zeros(16, dtype=torch.uint8, device=dev), off, 8, 4)
+    good = torch.zeros((4, 3), dtype=torch.int32, device=dev)
+    with pytest.raises(nvb.NvbError):      # would need a device reduction + .item() to learn max_len
+        nvb.batch_alignment_score_noalloc(a, ps, ts, good)
+    nvb.batch_alignment_score_noalloc(a, ps, ts, good, max_pattern_len=4)
+    for bad in (torch.zeros((3, 3), dtype=torch.int32, device=dev), torch.zeros((4, 3), dtype=torch.int64, device=dev),
+                torch.zeros((4, 3), dtype=torch.int32), torch.zeros((3, 4), dtype=torch.int32, device=dev).t()):
+        with pytest.raises(nvb.NvbError):
+            nvb.batch_alignment_score_noalloc(a, ps, ts, bad, max_pattern_len=4)
+    # the byte count saturates instead of wrapping (2^31 x 2^31 x 2 x 2 B does not fit 64 bits)
+    assert nvb.lib().nvb_batch_score_noalloc_bytes(nvb.GotohAligner(nvb.LOCAL, 2, -2, -5, -3).c(), 1 << 31, 1 << 31) > nvb.NOALLOC_SCRATCH_BYTES
     torch.cuda.synchronize()
