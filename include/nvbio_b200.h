@@ -169,6 +169,16 @@ int nvb_fmindex_fuse(nvb_ctx* ctx, const uint32_t* bwt_words, uint32_t length, u
  * ranges: 2 uint32 per query = the raw inclusive SA interval (x,y); empty iff x > y. */
 int nvb_fm_match(nvb_ctx* ctx, const nvb_fmindex* fmi, nvb_string_set queries, uint32_t* ranges,
                  void* stream);
+/* Batches of at least min_batch queries run nvb_fm_match / nvb_fm_match_reverse / nvb_fm_filter_rank with their search
+ * prefixes SHARED across the batch: the state after k steps depends only on the first k symbols consumed (fmindex_inl.h:186-239),
+ * and among n queries the first K = log4(n / 2) of them take at most 4^K <= n / 2 distinct values. Each call first computes the
+ * states of all 4^K K-mers (4^8 eight-step searches, then 4^K entries extended from those) into context-owned scratch and
+ * starts every query from its entry -- the mechanism of nvb_fmindex_build_ktab, but rebuilt per call, sized by the batch
+ * (8 * 4^K <= 4 bytes per query) and charged to the call. The ranges are identical bit for bit. Calls through one ctx must be
+ * stream-ordered, and the first call at a larger batch size allocates (grow-only). Default 65536 (NVB_FM_SHARE_MIN in the
+ * environment); 0xFFFFFFFF = always the plain loop. Continued ranges (nvb_fm_match_from) and smaller batches stay plain; a
+ * caller's own table (fmi->ktab) is used instead when it is at least as deep. */
+void nvb_fm_batch_sharing(nvb_ctx* ctx, uint32_t min_batch);
 /* match_reverse(fmi, pattern, len) (nvbio/fmindex/fmindex_inl.h:252-278): the same search consuming the pattern front to
  * back, i.e. match() of the reversed pattern -- what nvBowtie runs against the index of the REVERSED text (.rbwt/.rsa,
  * nvb_fmindex_load(reverse = 1); nvBowtie/bowtie2/cuda/mapping_inl.h:71-86) */

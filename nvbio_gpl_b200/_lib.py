@@ -111,6 +111,7 @@ _PROTOS = {
     "nvb_pair_hits": (_i, [_vp, _vp, _u32, _u32, _u32, _vp, _vp]),
     "nvb_last_paths": (_u32, [_vp]),
     "nvb_force_generic": (None, [_vp, _i]),
+    "nvb_fm_batch_sharing": (None, [_vp, _u32]),
 }
 EXPORTS = sorted(_PROTOS)
 
@@ -170,6 +171,10 @@ class Context:
 
     def force_generic(self, on):
         lib().nvb_force_generic(self.h, int(on))
+
+    def fm_batch_sharing(self, min_batch):
+        """batches of at least min_batch queries share search prefixes in match() (0xFFFFFFFF = never)"""
+        lib().nvb_fm_batch_sharing(self.h, int(min_batch))
 
     def synchronize(self):
         check(lib().nvb_ctx_synchronize(self.h), self.h)

@@ -36,6 +36,7 @@ extern "C" int nvb_ctx_create(int device, nvb_ctx** out)
     memset(c, 0, sizeof(*c));
     c->device = device;
     c->sm_count = prop.multiProcessorCount;
+    { const char* e = getenv("NVB_FM_SHARE_MIN"); c->fm_share_min = e ? (uint32_t)strtoul(e, nullptr, 10) : (1u << 16); }
     if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return NVB_ERR_CUDA; }
     for (int i = 0; i < 2; ++i)
         if (cudaStreamCreateWithFlags(&c->aux[i], cudaStreamNonBlocking) != cudaSuccess) { delete c; return NVB_ERR_CUDA; }
@@ -60,6 +61,7 @@ extern "C" void nvb_ctx_destroy(nvb_ctx* c)
     delete c;
 }
 
+extern "C" void nvb_fm_batch_sharing(nvb_ctx* c, uint32_t min_batch) { if (c) c->fm_share_min = min_batch; }
 extern "C" void* nvb_ctx_stream(nvb_ctx* c) { return c ? (void*)c->stream : nullptr; }
 extern "C" int nvb_ctx_synchronize(nvb_ctx* c)
 {

@@ -12,6 +12,9 @@
 
 #define NVB_SM_COUNT 148
 #define NVB_STAGE_SLOTS 64
+// stage slot map (nvb_ctx::d_stage): 0-7 *_host DP/locate entry points and FMIndexFilter | 8-32 the seed-and-extend pipeline
+// (map_pipeline.cu S_*) | 33-44 nvb_fm_match_host* (4 buffer sets x 3) | 40-41 are NOT free: they belong to that range; the
+// packed-set expansion of dp_api.cu uses 60-61 | 45-54 nvb_map_reads_host (2 sets x 5) | 62-63 per-batch k-mer table (fm_kernels.cu)
 
 struct nvb_ctx
 {
@@ -21,6 +24,7 @@ struct nvb_ctx
     uint64_t     launches;
     uint32_t     last_paths;
     int          force_generic;
+    uint32_t     fm_share_min;  // nvb_fm_match batches of at least this many queries share search prefixes through a per-batch k-mer table (fm_kernels.cu)
     // grow-only device/pinned staging owned by the *_host entry points
     void*        d_stage[NVB_STAGE_SLOTS];      // 0..7: *_host entry points, 8..: the seed-and-extend pipeline
     size_t       d_stage_bytes[NVB_STAGE_SLOTS];

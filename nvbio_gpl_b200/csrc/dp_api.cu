@@ -109,7 +109,7 @@ dp_unpack_kernel(const uint32_t* __restrict__ words, uint32_t bits, const uint32
     *(uint4*)(out + i0) = make_uint4(b[0], b[1], b[2], b[3]);          // the scratch is padded to whole groups
 }
 
-enum { DP_STAGE_UNPACK_P = 40, DP_STAGE_UNPACK_T = 41 };
+enum { DP_STAGE_UNPACK_P = 60, DP_STAGE_UNPACK_T = 61 };   // slot map in common.cuh (40/41 collided with nvb_fm_match_host's 4th buffer set)
 
 static int unpack_set(nvb_ctx* ctx, StrSet& S, uint32_t max_len, int slot, cudaStream_t s)
 {

@@ -309,6 +309,8 @@ static inline uint32_t grid_for(uint32_t n) { return (n + FM_THREADS - 1) / FM_T
 // the load-balanced walks run on a grid that just fills the device (8 CTAs of 256 threads per SM)
 static inline uint32_t walk_grid(const nvb_ctx* ctx, uint32_t n) { const uint32_t g = grid_for(n), p = (uint32_t)ctx->sm_count * 8u; return g < p ? g : p; }
 
+static int fm_batch_table(nvb_ctx* ctx, FMView& f, uint32_t n, cudaStream_t s);
+
 template <bool FROM, bool REV>
 static int fm_match_launch(nvb_ctx* ctx, const nvb_fmindex* fmi, nvb_string_set queries, uint32_t* ranges,
                            void* stream)
@@ -317,12 +319,17 @@ static int fm_match_launch(nvb_ctx* ctx, const nvb_fmindex* fmi, nvb_string_set 
     int rc = check_fmi(fmi, false); if (rc) return rc;
     if (queries.count == 0) return NVB_OK;
     if (!queries.symbols || !queries.offsets) return NVB_ERR_ARG;
-    const FMView f = make_view(fmi);
+    FMView f = make_view(fmi);
     const StrSet q = make_set(queries);
     cudaStream_t s = (cudaStream_t)stream;
     const uint32_t grid = grid_for(q.count);
-    const bool kt = !FROM && f.ktab_k > 0;
     if (f.ktab_k > 15u) return NVB_ERR_ARG;
+    if (!(queries.bits == 8 || queries.bits == 4 || queries.bits == 2)) return NVB_ERR_ARG;
+    // large batches share their search prefixes through a per-batch k-mer table (context-owned scratch, fm_batch_table);
+    // continued ranges and small batches stay plain
+    if (!FROM && q.count >= ctx->fm_share_min)
+        if ((rc = fm_batch_table(ctx, f, q.count, s))) return rc;
+    const bool kt = !FROM && f.ktab_k > 0;
     switch (queries.bits)
     {
     case 8: if (kt) fm_match_kernel<8, FROM, true, REV><<<grid, FM_THREADS, 0, s>>>(f, q, ranges);
@@ -354,6 +361,54 @@ fm_ktab_kernel(const FMView f, uint32_t k, uint32_t n, uint2* __restrict__ tab)
         y = f.L2[c] + r.y;
     }
     tab[idx] = make_uint2(x, y);
+}
+
+// entries of a k_to-mer table from a k_from-mer table: the state after the first k_from consumed symbols is entry
+// (idx mod 4^k_from); k_to - k_from more steps of the plain loop follow
+__global__ void __launch_bounds__(FM_THREADS)
+fm_ktab_extend_kernel(const FMView f, const uint2* __restrict__ from, uint32_t k_from, uint32_t k_to, uint32_t n, uint2* __restrict__ tab)
+{
+    __shared__ uint2 s_lut[FM_LUT_ENTRIES];
+    fm_lut_init(s_lut);
+    const uint32_t idx = blockIdx.x * FM_THREADS + threadIdx.x;
+    if (idx >= n) return;
+    const uint2 st = __ldg(from + (idx & ((1u << (2u * k_from)) - 1u)));
+    uint32_t x = st.x, y = st.y;
+    for (uint32_t j = k_from; j < k_to && x <= y; ++j)
+    {
+        const uint32_t c = (idx >> (2u * j)) & 3u;
+        const uint2 r = fm_rank2(f, x - 1u, y, c, s_lut);
+        x = f.L2[c] + r.x + 1u;
+        y = f.L2[c] + r.y;
+    }
+    tab[idx] = make_uint2(x, y);
+}
+
+// Per-batch k-mer table (batch sharing): among n queries the first K = log4(n / 2) consumed symbols take at most 4^K <= n / 2
+// distinct values, so the states after K steps are computed once per value -- 4^8 eight-step searches, then 4^K entries
+// extended from them -- into context-owned scratch, and every query starts from its entry exactly as it would from a
+// caller-provided table (nvb_fmindex_build_ktab). It is rebuilt on EVERY call: per-batch work inside the call, not an index-side
+// structure. Cost: 4^K (K - 8) + 8 * 4^8 rank steps (6 % of the 20 n steps of 10 M 20-mers); saves K steps per query.
+enum { FM_SLOT_BT8 = 62, FM_SLOT_BTK = 63 };        // slot map in common.cuh
+static int fm_batch_table(nvb_ctx* ctx, FMView& f, uint32_t n, cudaStream_t s)
+{
+    uint32_t K = 8;
+    while (K < 15u && (4ull << (2u * K)) <= (uint64_t)n / 2u) ++K;      // largest K with 4^K <= n / 2
+    if (f.ktab_k >= K) return NVB_OK;                                    // the caller's table is at least as deep
+    int rc; void *t8 = nullptr, *tk = nullptr;
+    if ((rc = nvb_stage(ctx, FM_SLOT_BT8, sizeof(uint2) << 16, &t8))) return rc;
+    FMView plain = f; plain.ktab = nullptr; plain.ktab_k = 0;
+    fm_ktab_kernel<<<(1u << 16) / FM_THREADS, FM_THREADS, 0, s>>>(plain, 8u, 1u << 16, (uint2*)t8);
+    NVB_LAUNCHED(ctx);
+    if (K > 8u)
+    {
+        const uint32_t m = 1u << (2u * K);
+        if ((rc = nvb_stage(ctx, FM_SLOT_BTK, sizeof(uint2) * (size_t)m, &tk))) return rc;
+        fm_ktab_extend_kernel<<<m / FM_THREADS, FM_THREADS, 0, s>>>(plain, (const uint2*)t8, 8u, K, m, (uint2*)tk);
+        NVB_LAUNCHED(ctx);
+    }
+    f.ktab = (const uint2*)(K > 8u ? tk : t8); f.ktab_k = K;
+    return NVB_OK;
 }
 
 extern "C" size_t nvb_ktab_words(uint32_t k) { return k && k <= 15u ? (size_t)2 << (2u * k) : 0; }

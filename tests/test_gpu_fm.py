@@ -18,6 +18,16 @@ def u32(t):
     return t.cpu().numpy().view(np.uint32)
 
 
+@pytest.fixture(autouse=True, params=["default", "share_all"])
+def sharing_mode(request):
+    """every test of this file runs twice: with the library's default choice between the plain one-query-per-thread kernel
+    and the per-batch k-mer table (fm_batch_table in fm_kernels.cu), and with EVERY match() batch forced through the table"""
+    ctx = nvb.Context.default(0)
+    ctx.fm_batch_sharing(1 if request.param == "share_all" else 1 << 16)
+    yield request.param
+    ctx.fm_batch_sharing(1 << 16)
+
+
 @pytest.mark.parametrize("n,alpha", [(1, 4), (2, 4), (63, 4), (64, 4), (65, 4), (1000, 2), (4096, 4), (300000, 4), (5000, 1)])
 def test_match_rank_locate(oracle, n, alpha):
     rng = np.random.default_rng(n * 7 + alpha)
@@ -336,3 +346,51 @@ def test_match_reverse_and_reverse_index_files(oracle, tmp_path):
                 L = int(qo[i + 1] - qo[i])
                 assert (rtext[p:p + L][::-1] == Q[qo[i]:qo[i + 1]]).all()
         c.close()
+
+
+def test_batch_sharing_adversarial(oracle):
+    """the per-batch k-mer table on batches large enough for every table depth the test can afford (K = 8, 9, 10), built to
+    stress its entry rules: exact duplicates, queries that extend / truncate one another, absent k-mers repeated with different
+    tails (dead table entries), N symbols at every position (inside and behind the first K consumed symbols), queries shorter
+    than K, empty queries, a binary alphabet; match and match_reverse; 8-bit and packed sets"""
+    rng = np.random.default_rng(909)
+    ctx = nvb.Context.default(0)
+    ctx.fm_batch_sharing(1)
+    try:
+        for n, alpha, lens, nq in ((200000, 4, (0, 34), 60000), (5000, 2, (0, 90), 400000), (70000, 4, (18, 23), 1500000)):
+            text = rng.integers(0, alpha, n).astype(np.uint8)
+            fmi, oidx = gu.fm_index_pair(oracle, text)
+            base_n = min(nq, 60000)
+            Q, qo = util.rand_queries(rng, text, base_n, len_range=lens, alpha=alpha, p_from_text=0.7, p_n=0.08)
+            qs = [Q[qo[i]:qo[i + 1]] for i in range(len(qo) - 1)]
+            extra = []
+            for i in rng.integers(0, len(qs), 30000):
+                q = qs[i]
+                r = rng.random()
+                if r < 0.3:
+                    extra.append(q.copy())                                              # duplicate
+                elif r < 0.5:
+                    extra.append(np.concatenate([rng.integers(0, alpha, int(rng.integers(1, 40))).astype(np.uint8), q]))   # extends (match order)
+                elif r < 0.7:
+                    extra.append(np.concatenate([q, rng.integers(0, alpha, int(rng.integers(1, 40))).astype(np.uint8)]))   # extends (reverse order)
+                elif r < 0.85:
+                    extra.append(q[len(q) // 3:].copy())
+                else:
+                    extra.append(q[:len(q) // 2].copy())
+            allq = qs + extra
+            reps = max(1, nq // len(allq))                 # repeated to reach the batch size of the deeper tables
+            perm = np.concatenate([rng.permutation(len(allq)) for _ in range(reps)])
+            Q2, q2o = po.concat([allq[i] for i in perm])
+            s2 = gu.sset(Q2, q2o)
+            want_f, want_r = oracle.fm_match(oidx, Q2, q2o), oracle.fm_match_reverse(oidx, Q2, q2o)
+            got = u32(nvb.match(fmi, s2.symbols, s2.offsets))
+            bad = np.nonzero((got != want_f).any(axis=1))[0]
+            assert len(bad) == 0, (n, bad[:5], got[bad[:5]], want_f[bad[:5]])
+            assert (u32(nvb.match_reverse(fmi, s2.symbols, s2.offsets)) == want_r).all(), n
+            w4 = torch.from_numpy(nvb.pack_symbols(Q2, 4).view(np.int32)).to(gu.dev())
+            assert (u32(nvb.match(fmi, w4, s2.offsets, bits=4)) == want_f).all()
+            Q3 = Q2 & 3
+            w2 = torch.from_numpy(nvb.pack_symbols(Q3, 2).view(np.int32)).to(gu.dev())
+            assert (u32(nvb.match_reverse(fmi, w2, s2.offsets, bits=2)) == oracle.fm_match_reverse(oidx, Q3, q2o)).all()
+    finally:
+        ctx.fm_batch_sharing(1 << 16)
