@@ -40,7 +40,8 @@ def parse():
     ap.add_argument("--c4-genome", type=int, default=3_100_000_000, help="genome of the configs[3]/[4] leg at its named size (0 = skip)")
     ap.add_argument("--no-extra", action="store_true", help="skip the SW / banded secondary measurements")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
-    ap.add_argument("--only", default="", help="profiling aid: run only this leg (fm|sw|banded|map|c4) with no cpu leg")
+    ap.add_argument("--only", default="", help="profiling aid: run only this leg (fm|sw|banded|map|c4|fm_c4) with no cpu leg")
+    ap.add_argument("--traffic-child", default="", help="internal: the short run bench.py puts under ncu to measure DRAM traffic (fm|fm_c4)")
     return ap.parse_args()
 
 
@@ -116,6 +117,30 @@ class ClockSampler:
 # ------------------------------------------------------------------------------------------------
 # synthetic workloads
 # ------------------------------------------------------------------------------------------------
+def c1_workload_name(args):
+    """the configs[1] workload, spelled identically by both arms"""
+    return ("configs[1]: FM-index exact 20-mer backward search, %d queries per GPU on a synthetic %d bp 2-bit genome"
+            % (args.queries, args.genome))
+
+
+def host_genome(n, seed=2):
+    """the configs[1] genome: generated on the host with numpy so that BOTH arms (--impl b200 / reference) index the same text"""
+    return np.random.default_rng(seed).integers(0, 4, n, dtype=np.uint8)
+
+
+def host_queries(text, k, seed):
+    """the configs[1] queries (both arms): 90 % 20-mers cut from the genome, 10 % random, 0.1 % with an N; unsorted"""
+    r = np.random.default_rng(seed)
+    n = len(text)
+    pos = r.integers(0, n - QLEN, k)
+    q = text[(pos[:, None] + np.arange(QLEN)[None, :]).reshape(-1)].reshape(k, QLEN).copy()
+    rnd = r.random(k) < 0.10
+    q[rnd] = r.integers(0, 4, (int(rnd.sum()), QLEN), dtype=np.uint8)
+    hasn = np.nonzero(r.random(k) < 0.001)[0]
+    q[hasn, r.integers(0, QLEN, len(hasn))] = 4
+    return q.reshape(-1), (np.arange(k + 1, dtype=np.int64) * QLEN).astype(np.uint32)
+
+
 def gen_genome(n, seed, dev):
     import torch
     g = torch.Generator(device=dev); g.manual_seed(seed)
@@ -236,6 +261,87 @@ def time_steps(fn, steps, warmup, flush):
 
 
 # ------------------------------------------------------------------------------------------------
+# DRAM traffic of one nvb_fm_match call, measured under ncu on a short child run of this script
+# ------------------------------------------------------------------------------------------------
+TRAFFIC_FILE = os.path.join(ROOT, "profiles", "r2_fm_traffic.json")
+
+
+def traffic_child(args):
+    """what ncu profiles: the leg's index and queries (same seeds as the bench), then TWO nvb_fm_match calls; the parent reads
+    the kernels of the second one"""
+    import ctypes
+    import torch
+    import nvbio_gpl_b200 as nvb
+    from nvbio_gpl_b200._lib import check, current_stream_ptr
+    from nvbio_gpl_b200.fmindex import _set_c
+    dev = torch.device("cuda", 0)
+    ctx = nvb.Context.default(0)
+    if args.traffic_child == "fm":
+        text = host_genome(args.genome)
+        fmi = nvb.build_index(torch.from_numpy(text).to(dev))
+        hq, hqo = host_queries(text, args.queries, 100)
+        qsym, qoff = torch.from_numpy(hq).to(dev), torch.from_numpy(hqo.view(np.int32)).to(dev)
+    else:
+        genome = gen_genome(args.c4_genome, 2, dev)
+        fmi = nvb.build_index(genome)
+        qsym, qoff = gen_queries(genome, args.queries, 300, dev)
+        del genome
+    torch.cuda.empty_cache()
+    ranges = torch.empty((args.queries, 2), dtype=torch.int32, device=dev)
+    fc, qset = fmi.c(), _set_c(qsym, qoff)
+    for _ in range(2):
+        check(nvb.lib().nvb_fm_match(ctx.h, ctypes.byref(fc), qset, ranges.data_ptr(), current_stream_ptr()), ctx.h)
+    torch.cuda.synchronize()
+
+
+def parse_ncu_launches(path):
+    """[(kernel name, {metric: value})] in launch order from an ncu --csv log"""
+    import csv
+    rows = [ln for ln in open(path) if ln.startswith('"')]
+    launches, last_id = [], None
+    for r in csv.DictReader(rows):
+        if r["ID"] != last_id:
+            launches.append((r["Kernel Name"], {}))
+            last_id = r["ID"]
+        v = float(r["Metric Value"].replace(",", ""))
+        u = r["Metric Unit"].lower()
+        scale = {"byte": 1.0, "kbyte": 1e3, "mbyte": 1e6, "gbyte": 1e9, "ns": 1e-6, "us": 1e-3, "usecond": 1e-3, "ms": 1.0, "msecond": 1.0, "nsecond": 1e-6, "second": 1e3}.get(u, 1.0)
+        launches[-1][1][r["Metric Name"]] = v * scale
+    return launches
+
+
+def measure_traffic(tag, args):
+    import shutil
+    key = "%s/%d/%d" % (tag, args.genome if tag == "fm" else args.c4_genome, args.queries)
+    ncu = shutil.which("ncu")
+    if ncu and not os.environ.get("BENCH_NO_NCU"):
+        log = os.path.join(tempfile.gettempdir(), "bench_traffic_%s_%d.csv" % (tag, os.getpid()))
+        cmd = [ncu, "--metrics", "dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum", "--clock-control", "none",
+               "-k", "regex:fm_", "--csv", "--log-file", log, sys.executable, os.path.abspath(__file__), "--traffic-child", tag,
+               "--genome", str(args.genome), "--c4-genome", str(args.c4_genome), "--queries", str(args.queries)]
+        try:
+            r = subprocess.run(cmd, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL, timeout=420)
+            launches = parse_ncu_launches(log) if r.returncode == 0 else []
+            os.remove(log)
+        except Exception:          # noqa: BLE001 -- ncu closed on this pool, timed out, or produced nothing
+            launches = []
+        if launches and len(launches) % 2 == 0:
+            call = launches[len(launches) // 2:]
+            kernels = [dict(kernel=k.split("(")[0], dram_read=m.get("dram__bytes_read.sum"), dram_write=m.get("dram__bytes_write.sum"),
+                            ms=m.get("gpu__time_duration.sum")) for k, m in call]
+            total = sum((k["dram_read"] or 0) + (k["dram_write"] or 0) for k in kernels)
+            return {"bytes": total, "kernels": kernels, "key": key,
+                    "source": "measured in this run: ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum on the second nvb_fm_match call of bench.py --traffic-child %s" % tag}
+    try:
+        rec = json.load(open(TRAFFIC_FILE)).get(key)
+        if rec:
+            return {"bytes": rec["bytes"], "kernels": rec.get("kernels"), "key": key, "source": "profiles/r2_fm_traffic.json (ncu was not available in this run)"}
+    except (OSError, ValueError):
+        pass
+    return None
+
+
+# ------------------------------------------------------------------------------------------------
 def run_b200(args):
     import torch
     import torch.distributed as dist
@@ -275,15 +381,16 @@ def run_b200(args):
     only = args.only
     out = {}
     # ---------------- index: built once on rank 0, replicated over NVLink (outside the timed region)
-    def make_index(n_symbols):
-        """(genome, fmi, seconds); raises on every rank if rank 0 could not build it"""
+    def make_index(n_symbols, host_text=None):
+        """(genome, fmi, seconds); raises on every rank if rank 0 could not build it. host_text: the text to index (configs[1]:
+        generated on the host so that both arms use the same one), else a device-generated random genome"""
         t0 = time.time()
         genome = fmi = None
         ok = torch.ones(1, dtype=torch.int64, device=dev)
         err = None
         if rank == 0:
             try:
-                genome = gen_genome(n_symbols, 2, dev)
+                genome = torch.from_numpy(host_text).to(dev) if host_text is not None else gen_genome(n_symbols, 2, dev)
                 fmi = nvb.build_index(genome)
                 meta = torch.tensor([fmi.length, fmi.primary] + fmi.L2, dtype=torch.int64, device=dev)
             except Exception as e:          # noqa: BLE001 -- e.g. out of memory on the 3.1 Gbp suffix sort
@@ -310,29 +417,74 @@ def run_b200(args):
 
     genome = fmi = None
     index_bytes = 0
-    if only in ("", "fm", "map"):
-        genome, fmi, build_s = make_index(args.genome)
-        index_bytes = int(fmi.bwt_occ.numel() * 4)
-    if only in ("", "fm"):
-        qsym, qoff = gen_queries(genome, args.queries, 100 + rank, dev)
-        nq = args.queries
+    host_text = None
+
+    def fm_core(tag, fmi, qsym, qoff, nq, build_s):
+        """device-resident timing of nvb_fm_match over one batch: the library's default path (large batches share their search
+        prefixes through a per-batch k-mer table, rebuilt inside every timed call) and the plain loop beside it"""
         ranges = torch.empty((nq, 2), dtype=torch.int32, device=dev)
-
-        def _match():   # resident inputs, resident output: exactly one nvb_fm_match launch
-            check(L.nvb_fm_match(ctx.h, ctypes.byref(fc), qset, ranges.data_ptr(), current_stream_ptr()), ctx.h)
-
         fc = fmi.c()
         qset = _set_c(qsym, qoff)
+
+        def _match():   # resident inputs, resident output: one nvb_fm_match call
+            check(L.nvb_fm_match(ctx.h, ctypes.byref(fc), qset, ranges.data_ptr(), current_stream_ptr()), ctx.h)
+
+        ctx.fm_batch_sharing(1 << 16)
         l0 = ctx.launches
         barrier()
         sampler = ClockSampler(local) if rank == 0 else None
         times = time_steps(_match, args.steps, args.warmup, flush)
         barrier()
         clocks = sampler.stop() if sampler else None
-        launches = (ctx.launches - l0) - args.warmup
+        launches = ((ctx.launches - l0) * args.steps) // (args.steps + args.warmup)
         step_ms = max_over_ranks(sum(times) / len(times))
-        out["fm"] = dict(step_ms=step_ms, value=world * nq / (step_ms * 1e-3), launches=launches, clocks=clocks,
-                         build_s=build_s, kernel_ms=sum(times) / len(times))
+        out[tag] = dict(step_ms=step_ms, value=world * nq / (step_ms * 1e-3), launches=launches, clocks=clocks,
+                        build_s=build_s, kernel_ms=sum(times) / len(times), queries=nq, index_bytes=int(fmi.bwt_occ.numel() * 4))
+        got = ranges.clone()
+        # the reference's loop as is: every query walks all of its steps (batch sharing switched off)
+        ctx.fm_batch_sharing(0xFFFFFFFF)
+        barrier()
+        tp = time_steps(_match, args.steps, args.warmup, flush)
+        ctx.fm_batch_sharing(1 << 16)
+        p_ms = max_over_ranks(sum(tp) / len(tp))
+        assert bool((ranges == got).all().item()), "batch sharing changed a range"
+        out[tag]["plain_loop"] = dict(value=world * nq / (p_ms * 1e-3), ms_per_step=p_ms,
+                                      note="nvb_fm_batch_sharing(ctx, 0xFFFFFFFF): one query per thread, all 20 steps")
+        return ranges, fc, qset
+
+    def fm_check(tag, fmi, hs_n, ho_n, got_n, nq):
+        """cpu_baseline + parity + algorithmic bytes (rank 0, N == 1 only): the ONLY use of oracle/ on this leg"""
+        po, chk, kind = load_checker()
+        bwt_occ, ssa = fmi.host_arrays()
+        oidx = po.Index(fmi.length, fmi.primary, np.array(fmi.L2, dtype=np.uint32), bwt_occ, ssa)
+        threads = host_threads()
+        probe = 100_000
+        t = time.time(); chk.fm_match(oidx, hs_n[:probe * QLEN], ho_n[:probe + 1], threads=threads); dt = time.time() - t
+        sample = int(min(nq, max(probe, 12.0 / max(dt, 1e-6) * probe)))
+        best = 1e30
+        for _ in range(2):
+            t = time.time(); want = chk.fm_match(oidx, hs_n[:sample * QLEN], ho_n[:sample + 1], threads=threads)
+            best = min(best, time.time() - t)
+        mism = int((want != got_n[:sample]).any(axis=1).sum())
+        # distinct 32-byte blocks the reference algorithm touches (counted by the C restatement)
+        orc = po.Oracle("oracle")
+        nb = min(sample, 1_000_000)
+        _, blocks = orc.fm_match(oidx, hs_n[:nb * QLEN], ho_n[:nb + 1], want_blocks=True, threads=threads)
+        out[tag]["cpu"] = dict(value=sample / best, unit="lookups/s", cores=threads, kind=kind,
+                               sample="first %d of the %d queries, best of 2, extrapolation-free rate" % (sample, nq))
+        out[tag]["parity"] = dict(checked=sample, mismatches=mism)
+        out[tag]["blocks_per_query"] = float(blocks.mean())
+
+    if only in ("", "fm", "map"):
+        host_text = host_genome(args.genome)
+        genome, fmi, build_s = make_index(args.genome, host_text)
+        index_bytes = int(fmi.bwt_occ.numel() * 4)
+    if only in ("", "fm"):
+        nq = args.queries
+        hq, hqo = host_queries(host_text, nq, 100 + rank)
+        qsym, qoff = torch.from_numpy(hq).to(dev), torch.from_numpy(hqo.view(np.int32)).to(dev)
+        ranges, fc, qset = fm_core("fm", fmi, qsym, qoff, nq, build_s)
+        del hq, hqo
 
         # ---- the same launch with the optional 10-mer jump table (8 MiB; identical ranges): reported beside `value`, not as it
         fmi.build_ktab(10, ctx=ctx)
@@ -426,28 +578,8 @@ def run_b200(args):
                                        h2d_bytes_per_step=int(hp.numel() * 4), d2h_bytes_per_step=int(hr.numel() * 4))
         del hp
 
-        # ---- cpu_baseline + parity + algorithmic bytes (rank 0, N == 1 only): the ONLY use of oracle/
         if rank == 0 and world == 1 and not args.no_cpu and only == "":
-            po, chk, kind = load_checker()
-            bwt_occ, ssa = fmi.host_arrays()
-            oidx = po.Index(fmi.length, fmi.primary, np.array(fmi.L2, dtype=np.uint32), bwt_occ, ssa)
-            threads = host_threads()
-            probe = 100_000
-            t = time.time(); chk.fm_match(oidx, hs_n[:probe * QLEN], ho_n[:probe + 1], threads=threads); dt = time.time() - t
-            sample = int(min(nq, max(probe, 12.0 / max(dt, 1e-6) * probe)))
-            best = 1e30
-            for _ in range(2):
-                t = time.time(); want = chk.fm_match(oidx, hs_n[:sample * QLEN], ho_n[:sample + 1], threads=threads)
-                best = min(best, time.time() - t)
-            mism = int((want != hr_n[:sample]).any(axis=1).sum())
-            # distinct 32-byte blocks the reference algorithm touches (counted by the C restatement)
-            _, orc, _ = (po, po.Oracle("oracle"), None)
-            nb = min(sample, 1_000_000)
-            _, blocks = orc.fm_match(oidx, hs_n[:nb * QLEN], ho_n[:nb + 1], want_blocks=True, threads=threads)
-            out["fm"]["cpu"] = dict(value=sample / best, unit="lookups/s", cores=threads, kind=kind,
-                                    sample="first %d of the %d queries, best of 2, extrapolation-free rate" % (sample, nq))
-            out["fm"]["parity"] = dict(checked=sample, mismatches=mism)
-            out["fm"]["blocks_per_query"] = float(blocks.mean())
+            fm_check("fm", fmi, hs_n, ho_n, hr_n, nq)
         del hs, ho, hr
 
     # ---------------- seed -> locate -> extend -> traceback over 150-bp reads (configs[3] shape on this leg's genome)
@@ -621,15 +753,23 @@ def run_b200(args):
 
     # ---------------- configs[3] / configs[4] at their named genome size (3.1 Gbp): a second index, built after everything
     # else has been measured and freed; a failure (memory) is recorded instead of ending the run
-    if only == "c4" or (only == "" and not args.no_extra and args.c4_genome > 0):
+    if only in ("c4", "fm_c4") or (only == "" and not args.no_extra and args.c4_genome > 0):
         genome = fmi = None
         torch.cuda.empty_cache()
         try:
             genome, fmi, c4_build_s = make_index(args.c4_genome)
-            map_leg(genome, fmi, args.reads, args.pairs, "map_c4", "pairs_c4")
-            out["map_c4"]["index_build_s"] = round(c4_build_s, 2)
+            # exact 20-mer seeding on the DRAM-resident index (1.55 GB fused image): where HBM actually binds
+            nq = args.queries
+            qsym, qoff = gen_queries(genome, nq, 300 + rank, dev)
+            ranges, _, _ = fm_core("fm_c4", fmi, qsym, qoff, nq, c4_build_s)
+            if rank == 0 and world == 1 and not args.no_cpu and only == "":
+                fm_check("fm_c4", fmi, qsym.cpu().numpy(), qoff.cpu().numpy().view(np.uint32), ranges.cpu().numpy().view(np.uint32), nq)
+            del qsym, qoff, ranges
+            if only != "fm_c4":
+                map_leg(genome, fmi, args.reads, args.pairs, "map_c4", "pairs_c4")
+                out["map_c4"]["index_build_s"] = round(c4_build_s, 2)
         except Exception as e:              # noqa: BLE001
-            out["map_c4"] = {"error": str(e)[:300], "genome": args.c4_genome}
+            out["map_c4" if "fm_c4" in out else "fm_c4"] = {"error": str(e)[:300], "genome": args.c4_genome}
         genome = fmi = None
 
     if world > 1:
@@ -645,35 +785,58 @@ def run_b200(args):
         pass
     hbm_peak, peak_src = (peaks["hbm_gbs"], "measured") if "hbm_gbs" in peaks else (6650.0, "fallback")
 
+    # DRAM traffic of one nvb_fm_match call (dram__bytes_read.sum + dram__bytes_write.sum over its kernels): measured live by
+    # putting a short child run of this script under ncu, now that this process has released the GPU memory; when ncu is
+    # not available the committed capture of the same child is named instead
+    torch.cuda.empty_cache()
+    traffic = {}
+    for tag in ("fm", "fm_c4"):
+        if tag in out and "value" in out[tag] and world == 1 and only in ("", "fm", "fm_c4", "c4"):
+            traffic[tag] = measure_traffic(tag, args)
+
+    def fm_roofline(tag):
+        fm = out[tag]
+        bpq = fm.get("blocks_per_query")
+        if not bpq:
+            return None
+        # algorithmic bytes per query: 32 B x distinct blocks the reference's loop touches + symbols + offset + result
+        alg_per_q = 32.0 * bpq + QLEN + 4 + 8
+        ach = alg_per_q * fm["queries"] / (fm["kernel_ms"] * 1e-3) / 1e9
+        tr = traffic.get(tag) or {}
+        r = {"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
+             "traffic": tr.get("bytes"), "traffic_source": tr.get("source"), "traffic_per_kernel": tr.get("kernels"),
+             "kernel": "one nvb_fm_match call = fm_ktab_kernel + fm_ktab_extend_kernel (per-batch k-mer table) + fm_match_kernel<8,0,1,0>; "
+                       "duration = CUDA events around the call on its stream, average of the timed steps",
+             "peak_source": peak_src, "algorithmic_bytes_per_query": alg_per_q, "blocks_per_query": bpq,
+             "index_bytes": fm["index_bytes"]}
+        if tr.get("bytes"):
+            r["dram_gbs"] = tr["bytes"] / (fm["kernel_ms"] * 1e-3) / 1e9
+            r["dram_frac_of_peak"] = r["dram_gbs"] / hbm_peak
+        return r
+
     line = {"metric": "fm_index_seed_lookups_per_s", "unit": "lookups/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u32",
             "data": "synthetic", "impl": "b200"}
     if "fm" in out:
         fm = out["fm"]
-        bpq = fm.get("blocks_per_query")
-        # algorithmic bytes per query: 32 B x distinct blocks + query symbols + offset + 8 B result
-        alg_per_q = (32.0 * bpq + QLEN + 4 + 8) if bpq else None
         line.update(value=fm["value"], ms_per_step=fm["step_ms"], gpu_launches=fm["launches"], clocks=fm["clocks"],
                     e2e=dict({k: fm["e2e_fixed4"][k] for k in ("value", "unit", "h2d_bytes_per_step", "d2h_bytes_per_step")},
                              call="nvb_fm_match_host_fixed: pinned host buffers, 4-bit packed 20-mers (the reference's read-stream "
                                   "layout, N representable), no offsets on the bus; H2D + kernels + D2H of the raw ranges inside the timed region"),
-                    config={"workload": "configs[1]: FM-index exact 20-mer backward search, %d queries per GPU on a synthetic %d bp 2-bit genome"
-                                        % (args.queries, args.genome),
-                            "queries": "90% cut from the genome, 10% random, 0.1% with an N, unsorted",
+                    config={"workload": c1_workload_name(args),
+                            "queries": "90% cut from the genome, 10% random, 0.1% with an N, unsorted; genome and queries generated on the host "
+                                       "with numpy (seeds 2 / 100 + rank), the same arrays --impl reference uses",
                             "index_bytes": index_bytes, "partition": "queries sharded, index replicated, no collective",
                             "l2": "flushed (256 MiB write) between timed steps, outside the event-timed region",
-                            "index_build_s": round(fm["build_s"], 2),
+                            "path": "library default: batches >= 65536 queries share their search prefixes through a per-batch k-mer table "
+                                    "rebuilt inside every timed call (no index-side structure beyond the reference's nvBWT image)",
+                            "index_build_s": round(fm["build_s"], 2), "value_plain_loop": fm.get("plain_loop"),
                             "e2e_8bit_symbols_with_offsets": fm.get("e2e"), "e2e_packed4_with_offsets": fm.get("e2e_packed4"),
-                            "value_with_kmer_jump_table": fm.get("ktab10"), "locate": fm.get("locate")})
-        if alg_per_q:
-            ach = alg_per_q * args.queries / (fm["kernel_ms"] * 1e-3) / 1e9
-            line["roofline"] = {"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
-                                # dram__bytes_read.sum + dram__bytes_write.sum of one fm_match launch of THIS workload under ncu --set full
-                                # (profiles/r1j_fm_match_ncu_full.csv: 607.5 MB read + 598.7 MB written, the writes mostly the L2 flush buffer's dirty
-                                # lines leaving during the launch; the 50 MB index is L2-resident, so traffic is far below the algorithmic bytes)
-                                "traffic": 1206.2e6 if (args.genome == 100_000_000 and args.queries == 10_000_000) else None,
-                                "kernel": "fm_match_kernel<8,false,false>", "peak_source": peak_src,
-                                "algorithmic_bytes_per_query": alg_per_q, "blocks_per_query": bpq}
+                            "value_with_prebuilt_kmer_jump_table": fm.get("ktab10"), "locate": fm.get("locate")})
+        rl = fm_roofline("fm")
+        if rl:
+            rl["note"] = "the 50 MB index is L2-resident: DRAM traffic is far below the algorithmic bytes and frac is not an HBM measurement; see extra.fm_c4 for the DRAM-resident index"
+            line["roofline"] = rl
         if "cpu" in fm:
             line["cpu_baseline"] = fm["cpu"]
             line["parity"] = fm["parity"]
@@ -690,7 +853,14 @@ def run_b200(args):
         for k, kind in (("ed_semi", "ed"), ("gotoh_semi", "gotoh"), ("sw_semi", "sw"), ("sw_local", "sw")):
             if k in out["banded"]:
                 out["banded"][k]["roofline"] = _roof(out["banded"][k]["gcups"], kind)
-    extra = {k: out[k] for k in ("sw", "banded", "map", "pairs", "map_c4", "pairs_c4") if k in out}
+    if "fm_c4" in out and "value" in out["fm_c4"]:
+        rl = fm_roofline("fm_c4")
+        if rl:
+            out["fm_c4"]["roofline"] = rl
+        out["fm_c4"]["workload"] = ("configs[3] index: FM-index exact 20-mer backward search, %d queries per GPU on a synthetic %d bp genome "
+                                    "(1.55 GB fused nvBWT image, DRAM-resident)" % (out["fm_c4"]["queries"], args.c4_genome))
+        out["fm_c4"]["cpu_baseline"] = out["fm_c4"].pop("cpu", None)
+    extra = {k: out[k] for k in ("fm_c4", "sw", "banded", "map", "pairs", "map_c4", "pairs_c4") if k in out}
     if extra:
         line["extra"] = extra
     print(json.dumps(line))
@@ -705,29 +875,17 @@ def run_reference(args):
         return
     po, chk, kind = load_checker()
     threads = host_threads()
-    rng = np.random.default_rng(2)
     n = args.genome
-    text = rng.integers(0, 4, n, dtype=np.uint8)
+    text = host_genome(n)                                  # the same text the b200 arm indexes
     t0 = time.time()
     idx = chk.build_index(text)
     build_s = time.time() - t0
     probe = 100_000
-
-    def queries(k, seed):
-        r = np.random.default_rng(seed)
-        pos = r.integers(0, n - QLEN, k)
-        q = text[(pos[:, None] + np.arange(QLEN)[None, :]).reshape(-1)].reshape(k, QLEN).copy()
-        rnd = r.random(k) < 0.10
-        q[rnd] = r.integers(0, 4, (int(rnd.sum()), QLEN), dtype=np.uint8)
-        hasn = np.nonzero(r.random(k) < 0.001)[0]
-        q[hasn, r.integers(0, QLEN, len(hasn))] = 4
-        return q.reshape(-1), (np.arange(k + 1) * QLEN).astype(np.uint32)
-
-    Q, qo = queries(probe, 100)
-    t = time.time(); chk.fm_match(idx, Q, qo, threads=threads); dt = time.time() - t
+    Qall, qoall = host_queries(text, args.queries, 100)    # the same queries as the b200 arm's rank 0; a step runs a prefix of them
+    t = time.time(); chk.fm_match(idx, Qall[:probe * QLEN], qoall[:probe + 1], threads=threads); dt = time.time() - t
     total = max(1, args.steps + args.warmup)
     sample = int(min(args.queries, max(probe, (120.0 / total) / max(dt, 1e-6) * probe)))
-    Q, qo = queries(sample, 100)
+    Q, qo = Qall[:sample * QLEN], qoall[:sample + 1]
     for _ in range(args.warmup):
         chk.fm_match(idx, Q, qo, threads=threads)
     t = time.time()
@@ -739,16 +897,17 @@ def run_reference(args):
         "impl": "reference", "metric": "fm_index_seed_lookups_per_s", "value": v, "unit": "lookups/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u32", "data": "synthetic",
-        "config": {"workload": "configs[1]: FM-index exact 20-mer backward search on a synthetic %d bp 2-bit genome" % n,
-                   "index_build_s": round(build_s, 2)},
+        "config": {"workload": c1_workload_name(args), "index_build_s": round(build_s, 2)},
         "cpu_baseline": {"value": v, "unit": "lookups/s", "cores": threads, "kind": kind,
-                         "sample": "%d queries per step (bounded sample of the 10 M-query workload)" % sample},
+                         "sample": "the first %d of the %d queries per step (bounded sample of the same seeded workload)" % (sample, args.queries)},
         "e2e": {"value": v, "unit": "lookups/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}))
 
 
 if __name__ == "__main__":
     a = parse()
-    if a.impl == "reference":
+    if a.traffic_child:
+        traffic_child(a)
+    elif a.impl == "reference":
         run_reference(a)
     else:
         run_b200(a)

@@ -32,6 +32,7 @@ struct nvb_ctx
     uint32_t*    d_worklist;
     size_t       d_worklist_cap;
     int          sm_count;
+    size_t       l2_bytes;
     cudaEvent_t  host_ev[12];  // event chain of the pipelined *_host entry points (3 per buffer set)
     cudaStream_t aux[2];       // the *_host entry points pipeline chunks over these (H2D of one chunk under the kernel / D2H of another)
 };

@@ -394,6 +394,12 @@ static int fm_batch_table(nvb_ctx* ctx, FMView& f, uint32_t n, cudaStream_t s)
 {
     uint32_t K = 8;
     while (K < 15u && (4ull << (2u * K)) <= (uint64_t)n / 2u) ++K;      // largest K with 4^K <= n / 2
+    // an index that would stay L2-resident must not be pushed out by its own table: index + table within half of L2
+    // (each die keeps its own copy of what its SMs read). configs[1] (50 MB): K = 10 -> 12.4 G lookups/s, K = 11 -> 11.5
+    const size_t idx_bytes = nvb_bwt_occ_words(f.length) * sizeof(uint32_t);
+    if (idx_bytes <= ctx->l2_bytes * 3 / 4)
+        while (K > 8u && idx_bytes + (sizeof(uint2) << (2u * K)) > ctx->l2_bytes / 2) --K;
+    { const char* e = getenv("NVB_FM_TABLE_K"); if (e) { const uint32_t k = (uint32_t)atoi(e); if (k >= 8u && k <= 15u) K = k; } }   // tuning aid (tools/fm_probe.py)
     if (f.ktab_k >= K) return NVB_OK;                                    // the caller's table is at least as deep
     int rc; void *t8 = nullptr, *tk = nullptr;
     if ((rc = nvb_stage(ctx, FM_SLOT_BT8, sizeof(uint2) << 16, &t8))) return rc;

@@ -44,13 +44,20 @@ def main():
             ms = sum(ts) / len(ts)
             print(json.dumps(dict(genome=G, queries=nq, tag=tag, ms=round(ms, 4), glookups_s=round(nq / ms / 1e6, 3), min_ms=round(min(ts), 4), build_s=round(build_s, 1), **kw)), flush=True)
 
+        if os.environ.get("PROBE_ONLY") == "table":      # profiling aid: two calls of the default path, nothing else
+            run(); run(); torch.cuda.synchronize()
+            continue
         ctx.fm_batch_sharing(0xFFFFFFFF)
         timed("plain")
         want = ranges.clone()
         ctx.fm_batch_sharing(1 << 16)
-        ranges.zero_()
-        timed("batch_table")
-        assert bool((ranges == want).all().item()), "batch table changed a range"
+        for k in os.environ.get("PROBE_K", "0").split(","):
+            if k != "0":
+                os.environ["NVB_FM_TABLE_K"] = k
+            ranges.zero_()
+            timed("batch_table", table_k=int(k))
+            assert bool((ranges == want).all().item()), "batch table changed a range"
+        os.environ.pop("NVB_FM_TABLE_K", None)
         if os.environ.get("PROBE_SORTED"):
             os.environ["NVB_FM_SHARE"] = "sort"
             for bits, r in ((24, 8), (24, 4), (32, 8)):
