@@ -679,38 +679,66 @@ def run_b200(args):
             M, N, n = 150, 500, args.sw_pairs
             P, Po, T, To = gen_pairs(n, M, N, 1 + rank, dev)
             ps, ts = nvb.StringSet(P, Po, 8, M), nvb.StringSet(T, To, 8, N)
-            a = nvb.SmithWatermanAligner(nvb.LOCAL, 2, -1, -1, -1)
             sinks = torch.empty((n, 3), dtype=torch.int32, device=dev)
-            temp = torch.empty(int(nvb.lib().nvb_temp_bytes(0, a.c(), 0, 0, M, N, n)), dtype=torch.uint8, device=dev)
-            fn = lambda: nvb.batch_alignment_score(a, ps, ts, sinks=sinks, temp=temp, ctx=ctx)
-            barrier()
-            tms = time_steps(fn, max(3, args.steps // 2), 2, flush)
-            ms = max_over_ranks(sum(tms) / len(tms))
-            out["sw"] = dict(gcups=world * n * M * N / (ms * 1e-3) / 1e9, ms=ms, pairs=n, M=M, N=N, paths=ctx.last_paths)
-            if rank == 0 and world == 1 and not args.no_cpu and only == "":
+            do_cpu = rank == 0 and world == 1 and not args.no_cpu and only == ""
+            if do_cpu:
                 po, chk, kind = load_checker()
-                k = min(n, 20000)
-                Ph, Th = P[:k * M].cpu().numpy(), T[:k * N].cpu().numpy()
-                Poh, Toh = (np.arange(k + 1) * M).astype(np.uint32), (np.arange(k + 1) * N).astype(np.uint32)
-                oa = po.aligner(po.SW, po.LOCAL, (2, -1, -1, -1))
-                t = time.time(); want = chk.score(oa, Ph, Poh, Th, Toh, threads=host_threads()); dt = time.time() - t
-                got = sinks[:k].cpu().numpy()
-                mism = int(((got[:, 0] != want["score"]) | (got[:, 1].view(np.uint32) != want["x"]) | (got[:, 2].view(np.uint32) != want["y"])).sum())
-                out["sw"]["cpu_gcups"] = k * M * N / dt / 1e9
-                out["sw"]["cpu_kind"] = kind
-                out["sw"]["parity"] = dict(checked=k, mismatches=mism)
-            # the other full-matrix aligners of batch_alignment_score at the same shape (int32 one-pair-per-thread kernels): informational
+                Ph, Th = P.cpu().numpy(), T.cpu().numpy()
+                Poh, Toh = Po.cpu().numpy().view(np.uint32), To.cpu().numpy().view(np.uint32)
+            # pinned host copies for the end-to-end form (nvb_batch_score_host: H2D of both string sets + kernels + D2H of the sinks)
+            hP = torch.empty(P.numel(), dtype=torch.uint8).pin_memory(); hP.copy_(P)
+            hT = torch.empty(T.numel(), dtype=torch.uint8).pin_memory(); hT.copy_(T)
+            hPo = torch.empty(Po.numel(), dtype=torch.int32).pin_memory(); hPo.copy_(Po)
+            hTo = torch.empty(To.numel(), dtype=torch.int32).pin_memory(); hTo.copy_(To)
+            hS = torch.empty((n, 3), dtype=torch.int32).pin_memory()
+            hS_n = hS.numpy().reshape(-1).view(nvb.SINK_DT)
+            cstream = torch.cuda.ExternalStream(ctx.stream, device=dev)
+
+            def full_leg(a, oa, steps, check_pairs):
+                """device-resident GCUPS, end-to-end GCUPS through the host entry point, parity + CPU rate on the first check_pairs pairs"""
+                temp = torch.empty(int(nvb.lib().nvb_temp_bytes(0, a.c(), 0, 0, M, N, n)), dtype=torch.uint8, device=dev)
+                fn = lambda: nvb.batch_alignment_score(a, ps, ts, sinks=sinks, temp=temp, ctx=ctx)
+                barrier()
+                tms = time_steps(fn, steps, 2, flush)
+                ms = max_over_ranks(sum(tms) / len(tms))
+                r = dict(gcups=world * n * M * N / (ms * 1e-3) / 1e9, ms=ms, paths=ctx.last_paths)
+                del temp
+                args_h = (a, 0, hP.numpy(), hPo.numpy().view(np.uint32), hT.numpy(), hTo.numpy().view(np.uint32))
+                nvb.batch_score_host(*args_h, sinks_h=hS_n, ctx=ctx)
+                et = []
+                for _ in range(2):
+                    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    e0.record(cstream); nvb.batch_score_host(*args_h, sinks_h=hS_n, ctx=ctx); e1.record(cstream); e1.synchronize()
+                    et.append(e0.elapsed_time(e1))
+                e_ms = max_over_ranks(min(et))
+                r["e2e"] = dict(gcups=world * n * M * N / (e_ms * 1e-3) / 1e9, ms=e_ms, h2d_bytes=int(hP.numel() + hT.numel() + 4 * (hPo.numel() + hTo.numel())),
+                                d2h_bytes=int(hS.numel() * 4), call="nvb_batch_score_host, pinned host buffers")
+                assert (hS.numpy() == sinks.cpu().numpy()).all(), "host and device scoring entry points disagree"
+                if do_cpu:
+                    k = min(n, check_pairs)
+                    t = time.time(); want = chk.score(oa, Ph[:k * M], Poh[:k + 1], Th[:k * N], Toh[:k + 1], threads=host_threads()); dt = time.time() - t
+                    got = sinks[:k].cpu().numpy()
+                    mism = int(((got[:, 0] != want["score"]) | (got[:, 1].view(np.uint32) != want["x"]) | (got[:, 2].view(np.uint32) != want["y"])).sum())
+                    r["cpu_gcups"] = k * M * N / dt / 1e9
+                    r["cpu_kind"] = kind
+                    r["cpu_cores"] = host_threads()
+                    r["parity"] = dict(checked=k, mismatches=mism)
+                return r
+
+            out["sw"] = dict(pairs=n, M=M, N=N, **full_leg(nvb.SmithWatermanAligner(nvb.LOCAL, 2, -1, -1, -1),
+                                                           po.aligner(po.SW, po.LOCAL, (2, -1, -1, -1)) if do_cpu else None, max(3, args.steps // 2), n))
+            # the other full-matrix aligners of batch_alignment_score at the same shape
             others = {}
-            for oname, oa_ in (("sw_global", nvb.SmithWatermanAligner(nvb.GLOBAL, 2, -1, -1, -1)), ("sw_semi_global", nvb.SmithWatermanAligner(nvb.SEMI_GLOBAL, 2, -1, -1, -1)),
-                               ("gotoh_local", nvb.GotohAligner(nvb.LOCAL, 2, -2, -5, -3)), ("gotoh_semi_global", nvb.GotohAligner(nvb.SEMI_GLOBAL, 2, -2, -5, -3))):
-                otemp = torch.empty(int(nvb.lib().nvb_temp_bytes(0, oa_.c(), 0, 0, M, N, n)), dtype=torch.uint8, device=dev)
-                ofn = lambda: nvb.batch_alignment_score(oa_, ps, ts, sinks=sinks, temp=otemp, ctx=ctx)
-                otms = time_steps(ofn, 2, 1, flush)
-                oms = max_over_ranks(sum(otms) / len(otms))
-                others[oname] = dict(gcups=world * n * M * N / (oms * 1e-3) / 1e9, ms=oms, paths=ctx.last_paths)
-                del otemp
+            for oname, kind_, ty_, sc_ in (("sw_global", "SW", nvb.GLOBAL, (2, -1, -1, -1)), ("sw_semi_global", "SW", nvb.SEMI_GLOBAL, (2, -1, -1, -1)),
+                                          ("ed_semi_global", "ED", nvb.SEMI_GLOBAL, (0, -1, -1, -1)), ("ed_global", "ED", nvb.GLOBAL, (0, -1, -1, -1)),
+                                          ("gotoh_local", "GOTOH", nvb.LOCAL, (2, -2, -5, -3)), ("gotoh_semi_global", "GOTOH", nvb.SEMI_GLOBAL, (2, -2, -5, -3)),
+                                          ("gotoh_global", "GOTOH", nvb.GLOBAL, (2, -2, -5, -3))):
+                a_ = nvb.EditDistanceAligner(ty_) if kind_ == "ED" else (nvb.SmithWatermanAligner(ty_, *sc_) if kind_ == "SW" else nvb.GotohAligner(ty_, *sc_))
+                oa_ = po.aligner(getattr(po, kind_), ty_, sc_) if do_cpu else None
+                others[oname] = full_leg(a_, oa_, 3, 20000)
+                others[oname]["scheme"] = list(sc_)
             out["sw"]["other_aligners"] = others
-            del P, T, temp
+            del P, T, hP, hT, hS
         if only in ("", "banded"):
             M, W, n = 250, 15, args.banded_pairs
             N = M + W
@@ -844,15 +872,24 @@ def run_b200(args):
     # B200s, profiles/r1b_pipe_peak.jsonl) x 2 cells / DPX instructions per packed cell of the textbook recurrence
     dpx = 1.8306e13
     peak = {"sw": dpx * 2 / 2 / 1e9, "ed": dpx * 2 / 2 / 1e9, "gotoh": dpx * 2 / 5 / 1e9}
-    def _roof(gcups, kind):
+    def _roof(gcups, kind, own):
+        """frac: against the textbook recurrence's DPX count (2 per packed cell for SW/ED, 5 for Gotoh); frac_own: against the ALU-pipe
+        instructions the kernel itself issues per packed cell (PRMT, min/max and logic ops share that 64-lane pipe)"""
         return {"bound": "dpx", "achieved": gcups, "peak": peak[kind] * world, "unit": "GCUPS", "frac": gcups / (peak[kind] * world),
+                "own_alu_instr_per_packed_cell": own, "peak_own": dpx * 2 / own / 1e9 * world, "frac_own": gcups / (dpx * 2 / own / 1e9 * world),
                 "peak_source": "measured DPX issue rate (profiles/r1b_pipe_peak.jsonl) x 2 cells / %d DPX per packed cell" % (5 if kind == "gotoh" else 2)}
     if "sw" in out:
-        out["sw"]["roofline"] = _roof(out["sw"]["gcups"], "sw")
+        out["sw"]["roofline"] = _roof(out["sw"]["gcups"], "sw", 3.5)
+        own_full = {"sw_global": ("sw", 2.0), "sw_semi_global": ("sw", 2.0), "ed_semi_global": ("ed", 2.0), "ed_global": ("ed", 2.0),
+                    "gotoh_local": ("gotoh", 5.5), "gotoh_semi_global": ("gotoh", 4.0), "gotoh_global": ("gotoh", 4.0)}
+        for k, (kind, own) in own_full.items():
+            o = out["sw"].get("other_aligners", {}).get(k)
+            if o and o.get("paths", 2) & 1:
+                o["roofline"] = _roof(o["gcups"], kind, own)
     if "banded" in out:
-        for k, kind in (("ed_semi", "ed"), ("gotoh_semi", "gotoh"), ("sw_semi", "sw"), ("sw_local", "sw")):
+        for k, kind, own in (("ed_semi", "ed", 2.0), ("gotoh_semi", "gotoh", 4.0), ("sw_semi", "sw", 2.0), ("sw_local", "sw", 3.5)):
             if k in out["banded"]:
-                out["banded"][k]["roofline"] = _roof(out["banded"][k]["gcups"], kind)
+                out["banded"][k]["roofline"] = _roof(out["banded"][k]["gcups"], kind, own)
     if "fm_c4" in out and "value" in out["fm_c4"]:
         rl = fm_roofline("fm_c4")
         if rl:

@@ -153,14 +153,17 @@ extern "C" int nvb_batch_score(nvb_ctx* ctx, nvb_aligner a, nvb_string_set patte
     const TempPlan p = plan(NVB_OP_SCORE, a, 0, 0, maxM, maxN);
     ctx->last_paths = 0;
 
-    if (ctx->force_generic != 1 && temp && batch_pairs(p, temp_bytes, n) >= n && dpf_full_score_supported(a, P, T, maxM, maxN))
+    const bool fast_local = dpf_full_score_supported(a, P, T, maxM, maxN);
+    const bool fast_sheared = !fast_local && ctx->force_generic == 0 && dpf2_full_score_supported(a, maxM, maxN);   // force_generic 2: no sheared-coordinate kernels
+    if (ctx->force_generic != 1 && temp && batch_pairs(p, temp_bytes, n) >= n && (fast_local || fast_sheared))
     {
         // packed DPX kernel; pairs it cannot represent exactly are appended to the ctx worklist and
         // re-scored by the int32 kernel, which reads the count on the device (no host sync)
         uint32_t* wl = nullptr;
         if ((rc = nvb_worklist(ctx, n, &wl))) return rc;
         NVB_CUDA(ctx, cudaMemsetAsync(wl, 0, sizeof(uint32_t), s));
-        if ((rc = dpf_full_score(ctx, a, P, T, sinks, maxM, maxN, wl, temp, s))) return rc;
+        if (fast_local) { if ((rc = dpf_full_score(ctx, a, P, T, sinks, maxM, maxN, wl, temp, s))) return rc; }
+        else { if ((rc = dpf2_full_score(ctx, a, P, T, sinks, maxM, maxN, wl, s))) return rc; ctx->last_paths |= 4u; }
         ctx->last_paths |= 1u;
         if (!temp && p.i16_per_pair) return NVB_ERR_TEMP;
         uint32_t n_dirty = n;

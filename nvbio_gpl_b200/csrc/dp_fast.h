@@ -11,6 +11,10 @@
 bool dpf_full_score_supported(const nvb_aligner& a, const StrSet& P, const StrSet& T, uint32_t maxM, uint32_t maxN);
 int  dpf_full_score(nvb_ctx* ctx, const nvb_aligner& a, StrSet P, StrSet T, nvb_best_sink* sinks, uint32_t maxM,
                     uint32_t maxN, uint32_t* worklist, void* temp, cudaStream_t s);
+// full-matrix SW / ED GLOBAL + SEMI_GLOBAL and Gotoh, sheared coordinates (dp_fast_full2.cu)
+bool dpf2_full_score_supported(const nvb_aligner& a, uint32_t maxM, uint32_t maxN);
+int  dpf2_full_score(nvb_ctx* ctx, const nvb_aligner& a, StrSet P, StrSet T, nvb_best_sink* sinks, uint32_t maxM,
+                     uint32_t maxN, uint32_t* worklist, cudaStream_t s);
 bool dpf_banded_score_supported(const nvb_aligner& a, uint32_t band, const StrSet& P, const StrSet& T, uint32_t maxM, uint32_t maxN);
 int  dpf_banded_score(nvb_ctx* ctx, const nvb_aligner& a, uint32_t band, StrSet P, StrSet T, nvb_best_sink* sinks,
                       uint32_t maxM, uint32_t maxN, uint32_t* worklist, cudaStream_t s);

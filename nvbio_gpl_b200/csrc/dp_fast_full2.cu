@@ -1,0 +1,312 @@
+// dp_fast_full2.cu -- packed s16x2 DPX wavefront kernels for the full-matrix aligners the LOCAL Smith-Waterman kernel
+// (dp_fast_full.cu) does not cover: Smith-Waterman / edit distance GLOBAL and SEMI_GLOBAL (this file, part 1) and Gotoh
+// (part 2). They replace the reference's one-thread-per-pair sweeps (nvbio/alignment/batched_inl.h:79-128 over
+// sw/sw_inl.h:419-749 and gotoh/gotoh_inl.h:458-840) for pairs of 2-bit symbols whose scores fit 15 bits; everything else
+// goes to the int32 kernels through the worklist, bit for bit as before.
+//
+// Layout as in dp_fast_full.cu: two pairs per 32-bit register (a "couple"), the pattern cut into stripes of 16 columns
+// spread over adjacent lanes, lane k one text row behind lane k-1 (anti-diagonal wavefront, boundary cells by warp
+// shuffle), the couple's two texts as a nibble stream in shared memory.
+//
+// SW / ED, GLOBAL and SEMI_GLOBAL: SHEARED in both directions. With r text rows and j pattern columns consumed,
+//   h[r][j] = H[r][j] - G r - I j          (G = deletion, I = insertion, both <= 0)
+// turns the recurrence of sw_inl.h:470-486 into
+//   h[r][j] = max3( h[r-1][j-1] + S', h[r-1][j], h[r][j-1] ),   S' = S - G - I >= 0
+// so both gap moves are free, every stored value is >= 0 (the packed addition is a plain 32-bit IMAD on the FMA pipe:
+// no carry between the halves) and a cell costs PRMT + VIMNMX3 on the ALU pipe. The boundaries become constants:
+// row 0 (I j, sw_inl.h:655) -> 0; column 0 of GLOBAL (G r) -> 0, of SEMI_GLOBAL (0) -> -G r.
+// Pattern columns past M get S' = 0: there the free move from the left makes h[r][j] = h[r][M] exactly (the diagonal and
+// top candidates are older values of the same non-decreasing column), so the LAST lane of a couple always ends its row on
+// h[r][M] of both pairs, whatever their lengths. That value, un-sheared along the rows, goes to a per-couple array in
+// shared memory (one IMAD + one STS per row, nothing on the ALU pipe); the sinks are taken from it after the sweep:
+// GLOBAL = row N (sw_inl.h:745-746), SEMI_GLOBAL = the maximum over the rows, the last one among equals (sw_inl.h:518-524
+// with BestSink's <=, sink_inl.h:44).
+#include "dp_fast.h"
+
+#define DF2_WARPS   4
+#define DF2_THREADS (DF2_WARPS * 32)
+
+struct Full2Params
+{
+    StrSet         P, T;
+    nvb_best_sink* sinks;
+    uint32_t*      worklist;   // [0] = count, [1..] = pair ids
+    uint32_t       n_pairs, n_tasks;
+    uint32_t       lanes, tpw;     // stripes per couple, couples per warp
+    uint32_t       tstride;        // text words per couple = ceil(maxN / 8)
+    uint32_t       cstride;        // candidate words per couple = maxN
+    int32_t        match, mismatch, ga, gb;
+    int32_t        semi;           // 1 = SEMI_GLOBAL, 0 = GLOBAL
+    uint32_t       one;
+};
+
+__device__ __forceinline__ uint32_t f2_pack2(int32_t v) { return ((uint32_t)v & 0xFFFFu) * 0x00010001u; }
+__device__ __forceinline__ uint32_t f2_prmt(uint32_t a, uint32_t b, uint32_t s)
+{ uint32_t d; asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(s)); return d; }
+__device__ __forceinline__ uint32_t f2_imad(uint32_t a, uint32_t b, uint32_t c)
+{ uint32_t d; asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c)); return d; }
+__device__ __forceinline__ uint32_t f2_squeeze4(uint32_t x)
+{
+    x &= 0x03030303u; x = (x | (x >> 4)) & 0x00FF00FFu; x = (x | (x >> 8)) & 0x0000FFFFu;
+    return x;
+}
+__device__ __forceinline__ void f2_mark_dirty(uint32_t* wl, uint32_t id)
+{
+    const uint32_t slot = atomicAdd(wl, 1u);
+    wl[1 + slot] = id;
+}
+
+// the couple's two texts as a nibble stream (8 rows per word, nibble = rA | rB << 2), written by the couple's lanes
+__device__ __forceinline__ void f2_pack_text(const StrSet& T, uint32_t* my_text, uint32_t k, uint32_t lanes, uint32_t tbA, uint32_t NA,
+                                             uint32_t tbB, uint32_t NB, uint32_t Nmax, bool& dirtyA, bool& dirtyB)
+{
+    for (uint32_t w = k; w * 8 < Nmax; w += lanes)
+    {
+        auto rows8 = [&](const uint32_t tb, const uint32_t N, bool& dirty) -> uint32_t
+        {
+            const uint32_t i0 = w * 8;
+            const uint8_t* src = T.sym + tb + i0;
+            if (T.bits == 8 && i0 + 8 <= N && ((uintptr_t)src & 3u) == 0)
+            {
+                const uint32_t x0 = __ldg((const uint32_t*)src), x1 = __ldg((const uint32_t*)src + 1);
+                dirty |= ((x0 | x1) & 0xFCFCFCFCu) != 0;
+                return f2_squeeze4(x0) | (f2_squeeze4(x1) << 16);
+            }
+            uint32_t word = 0;
+            #pragma unroll
+            for (uint32_t e = 0; e < 8; ++e)
+            {
+                const uint32_t r = i0 + e < N ? sym_at_rt(T.sym, T.bits, tb + i0 + e) : 0u;
+                dirty |= r > 3u;
+                word |= (r & 3u) << (4 * e);
+            }
+            return word;
+        };
+        my_text[w] = rows8(tbA, NA, dirtyA) | (rows8(tbB, NB, dirtyB) << 2);
+    }
+}
+
+// the stripe's 16 pattern symbols of one pair as 4 words of bytes (0xFF past the pattern)
+__device__ __forceinline__ void f2_stripe16(const StrSet& P, uint32_t pb, uint32_t M, uint32_t block, uint32_t* q4)
+{
+    const uint8_t* src = P.sym + pb + block;
+    if (P.bits == 8 && block + 16u <= M && ((uintptr_t)src & 3u) == 0)
+    {
+        #pragma unroll
+        for (int w = 0; w < 4; ++w) q4[w] = __ldg((const uint32_t*)src + w);
+    }
+    else
+    {
+        #pragma unroll
+        for (int w = 0; w < 4; ++w)
+        {
+            uint32_t x = 0;
+            #pragma unroll
+            for (int e = 0; e < 4; ++e)
+            {
+                const uint32_t c = block + 4 * w + e;
+                x |= (c < M ? sym_at_rt(P.sym, P.bits, pb + c) : 0xFFu) << (8 * e);
+            }
+            q4[w] = x;
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// part 1: Smith-Waterman / edit distance, GLOBAL and SEMI_GLOBAL
+// ---------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(DF2_THREADS, 5)
+dpf2_sw_kernel(const Full2Params p)
+{
+    extern __shared__ uint32_t s_mem[];    // per warp and couple slot: tstride text words, then cstride candidate words
+    const uint32_t lane = threadIdx.x & 31u, wib = threadIdx.x >> 5;
+    const uint32_t warp = blockIdx.x * DF2_WARPS + wib;
+    const uint32_t g = lane / p.lanes, k = lane - g * p.lanes;       // couple slot, stripe
+    const uint32_t task = warp * p.tpw + g;
+    const bool live = g < p.tpw && task < p.n_tasks;
+    const uint32_t gbase = g * p.lanes;
+
+    uint32_t idA = 0, idB = 0, pbA = 0, pbB = 0, tbA = 0, tbB = 0, MA = 0, MB = 0, NA = 0, NB = 0;
+    bool hasB = false;
+    if (live)
+    {
+        idA = 2 * task; hasB = idA + 1 < p.n_pairs; idB = hasB ? idA + 1 : idA;
+        pbA = p.P.off[idA]; MA = p.P.off[idA + 1] - pbA; pbB = p.P.off[idB]; MB = p.P.off[idB + 1] - pbB;
+        tbA = p.T.off[idA]; NA = p.T.off[idA + 1] - tbA; tbB = p.T.off[idB]; NB = p.T.off[idB + 1] - tbB;
+    }
+    const uint32_t Nmax = max(NA, NB);
+    bool dirtyA = false, dirtyB = false;
+
+    uint32_t* my_text = s_mem + ((size_t)wib * p.tpw + (live ? g : 0)) * (p.tstride + p.cstride);
+    uint32_t* my_cand = my_text + p.tstride;
+    if (live) f2_pack_text(p.T, my_text, k, p.lanes, tbA, NA, tbB, NB, Nmax, dirtyA, dirtyB);
+    __syncwarp();
+
+    // substitution profiles in sheared scores: S' = S - G - I (0 past the pattern)
+    const int32_t sm = p.match - p.ga - p.gb, sx = p.mismatch - p.ga - p.gb;
+    const uint32_t base  = ((uint32_t)sx & 0xFFu) * 0x01010101u;
+    const uint32_t delta = ((uint32_t)(sx ^ sm)) & 0xFFu;
+    const uint32_t block = k * 16u;
+    uint32_t TA[16], TB[16], H[16];
+    {
+        uint32_t qa[4] = { 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu }, qb[4] = { 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu };
+        if (live) { f2_stripe16(p.P, pbA, MA, block, qa); f2_stripe16(p.P, pbB, MB, block, qb); }
+        #pragma unroll
+        for (int j = 0; j < 16; ++j)
+        {
+            const uint32_t c = block + j;
+            const uint32_t a = (qa[j >> 2] >> (8 * (j & 3))) & 255u, b = (qb[j >> 2] >> (8 * (j & 3))) & 255u;
+            uint32_t wa = 0u, wb = 0u;
+            if (live && c < MA) { dirtyA |= a > 3u; wa = base ^ (delta << (8u * (a & 3u))); }
+            if (live && c < MB) { dirtyB |= b > 3u; wb = base ^ (delta << (8u * (b & 3u))); }
+            TA[j] = wa; TB[j] = wb; H[j] = 0u;
+        }
+    }
+    uint32_t r_one; asm volatile("mov.u32 %0, %1;" : "=r"(r_one) : "r"(p.one));
+    const uint32_t g2 = f2_pack2(-p.ga);                                   // -G in both halves
+    // column 0 of the matrix, the left input of lane 0: GLOBAL 0, SEMI_GLOBAL -G r; other lanes take their neighbour's last cell
+    const uint32_t cin_mul = k == 0 ? 0u : r_one, col_mul = (k == 0 && p.semi) ? g2 : 0u;
+    const bool last_lane = live && k == p.lanes - 1u;
+    uint32_t carry = 0u, send = 0u, tw = 0u;
+
+    auto row_step = [&](const uint32_t t, const bool first)
+    {
+        const uint32_t i = t - k;                               // this lane's text row (wraps while t < k: a dummy row)
+        const uint32_t cin = f2_imad(__shfl_up_sync(0xFFFFFFFFu, send, 1), cin_mul, f2_imad(i + 1u, col_mul, 0u));
+        if (first && t == k)
+        {
+            #pragma unroll
+            for (int j = 0; j < 16; ++j) H[j] = 0u;
+            carry = 0u;
+        }
+        if ((i & 7u) == 0 && i < Nmax) tw = my_text[i >> 3];
+        const uint32_t nib = tw & 15u; tw >>= 4;
+        const uint32_t sel = f2_imad((nib & 3u) | ((nib & 12u) << 6), 0x11u, 0xC480u);
+        // phase A: diagonal candidates from the previous row (FMA pipe)
+        uint32_t d[16];
+        {
+            uint32_t diag = carry;
+            #pragma unroll
+            for (int j = 0; j < 16; ++j)
+            {
+                d[j] = f2_imad(diag, r_one, f2_prmt(TA[j], TB[j], sel));
+                diag = H[j];
+            }
+        }
+        carry = cin;
+        // phase B: one VIMNMX3 per packed cell along the row
+        uint32_t left = cin;
+        #pragma unroll
+        for (int j = 0; j < 16; ++j)
+        {
+            left = __vimax3_s16x2(d[j], H[j], left);
+            H[j] = left;
+        }
+        send = left;
+        // h[r][M] of both pairs, un-sheared along the rows: + G r + const (const = -G Nmax keeps it >= 0)
+        if (last_lane && i < Nmax) my_cand[i] = f2_imad(Nmax - 1u - i, g2, send);
+    };
+
+    const uint32_t steps = __reduce_max_sync(0xFFFFFFFFu, live ? Nmax + p.lanes - 1 : 0u);
+    const uint32_t t_lo  = min(p.lanes, steps);
+    uint32_t t = 0;
+    for (; t < t_lo; ++t)  row_step(t, true);
+    for (; t < steps; ++t) row_step(t, false);
+    __syncwarp();
+
+    // ---- sinks from the candidate column: key = value << 16 | row, so the last row wins among equal values
+    uint32_t bA = 0u, bB = 0u;
+    if (live)
+    {
+        if (p.semi)
+        {
+            for (uint32_t r = k; r < Nmax; r += p.lanes)
+            {
+                const uint32_t c = my_cand[r];
+                if (r < NA) bA = max(bA, ((c & 0xFFFFu) << 16) | r);
+                if (r < NB) bB = max(bB, (c & 0xFFFF0000u) | r);
+            }
+        }
+        else if (k == 0)
+        {
+            if (NA) bA = ((my_cand[NA - 1u] & 0xFFFFu) << 16) | (NA - 1u);
+            if (NB) bB = (my_cand[NB - 1u] & 0xFFFF0000u) | (NB - 1u);
+        }
+    }
+    const uint32_t dmaskA = __ballot_sync(0xFFFFFFFFu, dirtyA), dmaskB = __ballot_sync(0xFFFFFFFFu, dirtyB);
+    const uint32_t gmask = (p.lanes >= 32 ? 0xFFFFFFFFu : ((1u << p.lanes) - 1u)) << gbase;
+    uint32_t wA = 0u, wB = 0u;
+    for (uint32_t dd = 0; dd < p.lanes; ++dd)
+    {
+        const uint32_t src = min(gbase + dd, 31u);
+        wA = max(wA, __shfl_sync(0xFFFFFFFFu, bA, src));
+        wB = max(wB, __shfl_sync(0xFFFFFFFFu, bB, src));
+    }
+    if (!live || k != 0) return;
+
+    #pragma unroll
+    for (int h = 0; h < 2; ++h)
+    {
+        if (h == 1 && !hasB) break;
+        const uint32_t id = h ? idB : idA;
+        const uint32_t M = h ? MB : MA, N = h ? NB : NA;
+        bool dirty = ((h ? dmaskB : dmaskA) & gmask) != 0;
+        if (M == 0 || N == 0) dirty = true;                                 // degenerate shapes: the int32 kernel knows the reference's answers
+        // 15-bit range of everything stored: the other pair's rows and the padded columns are swept too
+        const uint32_t pos = p.match > 0 ? (uint32_t)p.match : 0u;
+        if ((uint64_t)pos * min(max(MA, MB), Nmax) + 2ull * (uint32_t)(-p.ga) * Nmax + (uint64_t)(uint32_t)(-p.gb) * (16u * p.lanes) >= 32000ull) dirty = true;
+        if (dirty) { f2_mark_dirty(p.worklist, id); continue; }
+        const uint32_t w = h ? wB : wA;
+        nvb_best_sink out;
+        out.score  = (int32_t)(w >> 16) + p.ga * (int32_t)Nmax + p.gb * (int32_t)M;
+        out.sink_x = (w & 0xFFFFu) + 1u;
+        out.sink_y = M;
+        p.sinks[id] = out;
+    }
+}
+
+static bool full2_geometry(uint32_t maxM, uint32_t maxN, uint32_t* lanes, uint32_t* tpw, uint32_t* tstride, uint32_t* cstride, size_t* smem)
+{
+    const uint32_t stripes = (maxM + 15u) / 16u;
+    if (stripes == 0 || stripes > 32u) return false;
+    *lanes = stripes; *tpw = 32u / stripes; *tstride = (maxN + 7u) / 8u; *cstride = maxN;
+    *smem = (size_t)DF2_WARPS * *tpw * (*tstride + *cstride) * sizeof(uint32_t);
+    return *smem <= 160u * 1024u;
+}
+
+bool dpf2_full_score_supported(const nvb_aligner& a, uint32_t maxM, uint32_t maxN)
+{
+    if (a.type != NVB_GLOBAL && a.type != NVB_SEMI_GLOBAL) return false;
+    if (a.kind != NVB_SMITH_WATERMAN && a.kind != NVB_EDIT_DISTANCE) return false;
+    const Scheme s = make_scheme(a);
+    if (s.ga > 0 || s.gb > 0 || s.ga < -255 || s.gb < -255) return false;
+    const int32_t sm = s.match - s.ga - s.gb, sx = s.mismatch - s.ga - s.gb;     // sheared substitution scores: bytes 0..127
+    if (sm < 0 || sm > 127 || sx < 0 || sx > 127) return false;
+    if (maxN == 0 || maxM == 0 || maxN > 65535u) return false;
+    uint32_t lanes, tpw, tstride, cstride; size_t smem;
+    return full2_geometry(maxM, maxN, &lanes, &tpw, &tstride, &cstride, &smem);
+}
+
+int dpf2_full_score(nvb_ctx* ctx, const nvb_aligner& a, StrSet P, StrSet T, nvb_best_sink* sinks, uint32_t maxM,
+                    uint32_t maxN, uint32_t* worklist, cudaStream_t st)
+{
+    const Scheme s = make_scheme(a);
+    Full2Params p;
+    size_t smem;
+    if (!full2_geometry(maxM, maxN, &p.lanes, &p.tpw, &p.tstride, &p.cstride, &smem)) return NVB_ERR_UNSUPPORTED;
+    p.P = P; p.T = T; p.sinks = sinks; p.worklist = worklist;
+    p.n_pairs = P.count; p.n_tasks = (P.count + 1) / 2;
+    p.match = s.match; p.mismatch = s.mismatch; p.ga = s.ga; p.gb = s.gb;
+    p.semi = a.type == NVB_SEMI_GLOBAL ? 1 : 0;
+    p.one = 1;
+    if (!(ctx->attr_done & NVB_ATTR_FULL2))
+    {
+        NVB_CUDA(ctx, cudaFuncSetAttribute(dpf2_sw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+        ctx->attr_done |= NVB_ATTR_FULL2;
+    }
+    const uint32_t n_warps = (p.n_tasks + p.tpw - 1) / p.tpw;
+    const uint32_t grid = (n_warps + DF2_WARPS - 1) / DF2_WARPS;
+    dpf2_sw_kernel<<<grid, DF2_THREADS, smem, st>>>(p);
+    NVB_LAUNCHED(ctx);
+    return NVB_OK;
+}

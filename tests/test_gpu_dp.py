@@ -40,6 +40,22 @@ def test_full_score_and_traceback(oracle, ctx, kind, scheme, ty):
 
 
 @pytest.mark.parametrize("kind,scheme,ty", CASES)
+def test_full_score_wide_shapes(oracle, ctx, kind, scheme, ty):
+    """full-matrix scoring at the shapes the wavefront kernels spread over many lanes (configs[0]: 150 x 500) and at ragged
+    ones: couples of unequal pattern and text lengths, patterns of 1..16 stripes, texts shorter than patterns"""
+    rng = np.random.default_rng(hash((kind, scheme, ty, 3)) & 0xFFFF)
+    a, oa = gu.aligner(kind, ty, scheme), po.aligner(kind, ty, scheme)
+    for alpha, m_range, n_of_m in ((4, (140, 151), lambda M: 500), (2, (1, 260), lambda M: int(rng.integers(1, 420))),
+                                   (4, (150, 151), lambda M: int(rng.integers(100, 300)))):
+        P, Po, T, To = util.rand_pairs(rng, 401, m_range, n_of_m, alpha)
+        ps, ts = gu.sset(P, Po), gu.sset(T, To)
+        got = gu.sinks_np(nvb.batch_alignment_score(a, ps, ts))
+        want = oracle.score(oa, P, Po, T, To)
+        bad = np.nonzero(got != want)[0]
+        assert len(bad) == 0, (bad[:5], got[bad[:5]], want[bad[:5]], np.diff(Po.astype(np.int64))[bad[:5]], np.diff(To.astype(np.int64))[bad[:5]])
+
+
+@pytest.mark.parametrize("kind,scheme,ty", CASES)
 def test_banded_score_and_traceback(oracle, ctx, kind, scheme, ty):
     rng = np.random.default_rng(hash((kind, scheme, ty, 1)) & 0xFFFF)
     a, oa = gu.aligner(kind, ty, scheme), po.aligner(kind, ty, scheme)
