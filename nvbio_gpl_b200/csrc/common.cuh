@@ -33,10 +33,15 @@ struct nvb_ctx
     size_t       d_worklist_cap;
     int          sm_count;
     size_t       l2_bytes;
-    uint32_t     attr_done;     // kernel families whose cudaFuncSetAttribute calls have been made ON THIS CONTEXT'S DEVICE (they are per device)
     cudaEvent_t  host_ev[12];  // event chain of the pipelined *_host entry points (3 per buffer set)
     cudaStream_t aux[2];       // the *_host entry points pipeline chunks over these (H2D of one chunk under the kernel / D2H of another)
 };
+
+// true the first time it is evaluated AT THIS PLACE for the context's device: cudaFuncSetAttribute is per device and, inside a
+// template launcher, per instantiation (the static lives in the lambda of each instantiation)
+#include <atomic>
+#define NVB_FIRST_ON_DEVICE(ctx) ([&]() -> bool { static std::atomic<unsigned long long> m_{0}; const unsigned long long b_ = 1ull << ((ctx)->device & 63); \
+                                                return !(m_.fetch_or(b_) & b_); }())
 
 #define NVB_CUDA(ctx, call)                                                 \
     do { cudaError_t e_ = (call);                                           \
@@ -49,7 +54,6 @@ struct nvb_ctx
 
 int   nvb_stage(nvb_ctx* ctx, int slot, size_t bytes, void** out);
 int   nvb_worklist(nvb_ctx* ctx, size_t entries, uint32_t** out);
-enum { NVB_ATTR_FULL = 1u, NVB_ATTR_FULL2 = 2u, NVB_ATTR_BANDED = 4u, NVB_ATTR_BAND2 = 8u, NVB_ATTR_BAND2_TB = 16u };
 int   nvb_noalloc_warmup(nvb_ctx* ctx);   // dp_generic_full.cu: resolves the static scratch array's device address for ctx->device
 
 // ---------------------------------------------------------------------------------------------

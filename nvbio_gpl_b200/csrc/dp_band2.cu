@@ -336,10 +336,9 @@ template <int W, int TYPE, bool GOTOH, int MINB>
 static int band2_launch_as(nvb_ctx* ctx, const Band2Params& p, cudaStream_t st)
 {
     constexpr size_t smem = 128 + (size_t)B2_THREADS * (4 * 64 + 4);
-    if (!(ctx->attr_done & NVB_ATTR_BAND2))
+    if (NVB_FIRST_ON_DEVICE(ctx))
     {
         NVB_CUDA(ctx, cudaFuncSetAttribute(band2_kernel<W, TYPE, GOTOH, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        ctx->attr_done |= NVB_ATTR_BAND2;
     }
     band2_kernel<W, TYPE, GOTOH, MINB><<<(p.n_threads + B2_THREADS - 1) / B2_THREADS, B2_THREADS, smem, st>>>(p);
     NVB_LAUNCHED(ctx);

@@ -427,10 +427,9 @@ template <int W, int TYPE, bool GOTOH>
 static int band2_tb_launch(nvb_ctx* ctx, const Band2TbParams& q, cudaStream_t st)
 {
     constexpr size_t smem = 128 + (size_t)B2_THREADS * (4 * 64 + 4);
-    if (!(ctx->attr_done & NVB_ATTR_BAND2_TB))
+    if (NVB_FIRST_ON_DEVICE(ctx))
     {
         NVB_CUDA(ctx, cudaFuncSetAttribute(band2_tb_forward_kernel<W, TYPE, GOTOH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        ctx->attr_done |= NVB_ATTR_BAND2_TB;
     }
     band2_tb_forward_kernel<W, TYPE, GOTOH><<<(q.threads + B2_THREADS - 1) / B2_THREADS, B2_THREADS, smem, st>>>(q);
     NVB_LAUNCHED(ctx);

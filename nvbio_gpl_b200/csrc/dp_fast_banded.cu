@@ -350,10 +350,9 @@ bool dpf_banded_score_supported(const nvb_aligner& a, uint32_t band, const StrSe
 template <int W, int TYPE, bool GOTOH>
 static int band_launch(nvb_ctx* ctx, const BandFastParams& p, size_t smem, cudaStream_t st)
 {
-    if (!(ctx->attr_done & NVB_ATTR_BANDED))
+    if (NVB_FIRST_ON_DEVICE(ctx))
     {
         NVB_CUDA(ctx, cudaFuncSetAttribute(dpf_banded_kernel<W, TYPE, GOTOH>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        ctx->attr_done |= NVB_ATTR_BANDED;
     }
     dpf_banded_kernel<W, TYPE, GOTOH><<<(p.n_threads + DPB_THREADS - 1) / DPB_THREADS, DPB_THREADS, smem, st>>>(p);
     NVB_LAUNCHED(ctx);

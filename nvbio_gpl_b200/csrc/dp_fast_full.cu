@@ -348,14 +348,13 @@ int dpf_full_score(nvb_ctx* ctx, const nvb_aligner& a, StrSet P, StrSet T, nvb_b
             p.CJ[j] = cj < 0 ? ((((uint32_t)(cj - 1) & 0xFFFFu) << 16) | ((uint32_t)cj & 0xFFFFu)) : 0u;
         }
     }
-    if (!(ctx->attr_done & NVB_ATTR_FULL))
+    if (NVB_FIRST_ON_DEVICE(ctx))
     {
         NVB_CUDA(ctx, cudaFuncSetAttribute(dpf_full_sw_local_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
         NVB_CUDA(ctx, cudaFuncSetAttribute(dpf_full_sw_local_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
         NVB_CUDA(ctx, cudaFuncSetAttribute(dpf_full_sw_local_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
         NVB_CUDA(ctx, cudaFuncSetAttribute(dpf_full_sw_local_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
         NVB_CUDA(ctx, cudaFuncSetAttribute(dpf_full_sw_local_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
-        ctx->attr_done |= NVB_ATTR_FULL;
     }
     const uint32_t n_warps = (p.n_tasks + p.tpw - 1) / p.tpw;
     const uint32_t grid = (n_warps + DPF_WARPS - 1) / DPF_WARPS;

@@ -1,6 +1,6 @@
 // dp_fast_full2.cu -- packed s16x2 DPX wavefront kernels for the full-matrix aligners the LOCAL Smith-Waterman kernel
 // (dp_fast_full.cu) does not cover: Smith-Waterman / edit distance GLOBAL and SEMI_GLOBAL (this file, part 1) and Gotoh
-// (part 2). They replace the reference's one-thread-per-pair sweeps (nvbio/alignment/batched_inl.h:79-128 over
+// (part 2: LOCAL, and GLOBAL / SEMI_GLOBAL). They replace the reference's one-thread-per-pair sweeps (nvbio/alignment/batched_inl.h:79-128 over
 // sw/sw_inl.h:419-749 and gotoh/gotoh_inl.h:458-840) for pairs of 2-bit symbols whose scores fit 15 bits; everything else
 // goes to the int32 kernels through the worklist, bit for bit as before.
 //
@@ -265,6 +265,362 @@ dpf2_sw_kernel(const Full2Params p)
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// part 2: Gotoh. Reference recurrence (gotoh_inl.h:458-575), go = gap open, ge = gap extension, d = go - ge <= 0:
+//   F[r][c] = max(F[r-1][c] + ge, H[r-1][c] + go)      E[r][c] = max(E[r][c-1] + ge, H[r][c-1] + go)
+//   H[r][c] = max(E[r][c], F[r][c], H[r-1][c-1] + S)   (LOCAL: and 0)
+// Both kernels keep HO = H + d (H with the opening surcharge already applied) so that extension and opening become one
+// maximum each, and shear the coordinates by ge so that extending costs nothing.
+// ---------------------------------------------------------------------------------------------------------------
+// addend that adds g <= 0 to both halves of a register whose low half is >= -g (the low half's carry completes the high half's g - 1)
+__device__ __forceinline__ uint32_t f2_fix2(int32_t g) { return g == 0 ? 0u : ((((uint32_t)(g - 1) & 0xFFFFu) << 16) | ((uint32_t)g & 0xFFFFu)); }
+
+struct Gotoh2Params
+{
+    Full2Params f;
+    uint32_t    sixteen;
+    uint32_t    unshear;        // LOCAL: fix2(-16 b), the shear step between neighbouring lanes
+    uint32_t    FL[16];         // LOCAL floor of local column j: pack2(B + b j)
+    uint32_t    CJ[16];         // LOCAL key addend: (h' << 4) + CJ[j] = (H + B) << 4 | j
+    int32_t     B;              // bias
+};
+
+#define DF2_BIAS 64
+
+// ---- Gotoh LOCAL: sheared along the columns of a stripe only (the floor of local column j is the constant B + b j, b = -ge):
+//   x'[j] = x + B + b j  for x = H, E, F;   HO' = H' + d
+//   F'  = max(F', HO'top) + ge          E' = max(E'left, HO'left)
+//   h'  = max3( max(HO'diag + (S - go), floor_j), F', E' )              HO' = h' + d
+// per packed cell: PRMT + VIMNMX (F) + VIMNMX (E) + VIADDMNMX (diagonal with the floor folded in) + VIMNMX3 + 1/2 VIMNMX3 (key)
+// on the ALU pipe; the three additions are IMADs. BestSink's order: the reference sweeps Gotoh in stripes of EIGHT columns
+// (gotoh_inl.h:1259-1262), so inside a lane's 16 columns the upper half belongs to a later stripe: among equal scores the
+// running best is replaced when (score, column >> 3) is >= -- keys compared with their low 3 bits cleared.
+template <int BT>
+__global__ void __launch_bounds__(DF2_THREADS, 4)
+dpf2_gotoh_local_kernel(const Gotoh2Params q)
+{
+    const Full2Params& p = q.f;
+    auto FLc = [&](const int j) -> uint32_t { return BT ? (uint32_t)(DF2_BIAS + BT * j) * 0x00010001u : q.FL[j]; };
+    auto CJc = [&](const int j) -> uint32_t
+    {
+        if (!BT) return q.CJ[j];
+        const int32_t cj = j - 16 * BT * j;
+        return cj < 0 ? ((((uint32_t)(cj - 1) & 0xFFFFu) << 16) | ((uint32_t)cj & 0xFFFFu)) : 0u;
+    };
+    extern __shared__ uint32_t s_mem[];
+    const uint32_t lane = threadIdx.x & 31u, wib = threadIdx.x >> 5;
+    const uint32_t warp = blockIdx.x * DF2_WARPS + wib;
+    const uint32_t g = lane / p.lanes, k = lane - g * p.lanes;
+    const uint32_t task = warp * p.tpw + g;
+    const bool live = g < p.tpw && task < p.n_tasks;
+    const uint32_t gbase = g * p.lanes;
+
+    uint32_t idA = 0, idB = 0, pbA = 0, pbB = 0, tbA = 0, tbB = 0, MA = 0, MB = 0, NA = 0, NB = 0;
+    bool hasB = false;
+    if (live)
+    {
+        idA = 2 * task; hasB = idA + 1 < p.n_pairs; idB = hasB ? idA + 1 : idA;
+        pbA = p.P.off[idA]; MA = p.P.off[idA + 1] - pbA; pbB = p.P.off[idB]; MB = p.P.off[idB + 1] - pbB;
+        tbA = p.T.off[idA]; NA = p.T.off[idA + 1] - tbA; tbB = p.T.off[idB]; NB = p.T.off[idB + 1] - tbB;
+    }
+    const uint32_t Nmax = max(NA, NB);
+    bool dirtyA = false, dirtyB = false;
+    uint32_t* my_text = s_mem + ((size_t)wib * p.tpw + (live ? g : 0)) * p.tstride;
+    if (live) f2_pack_text(p.T, my_text, k, p.lanes, tbA, NA, tbB, NB, Nmax, dirtyA, dirtyB);
+    __syncwarp();
+
+    const int32_t go = p.ga, ge = p.gb, b = -ge, dd = go - ge, B = q.B;
+    // profile bytes: S - go (the diagonal reads HO' = H' + d of the previous column: -d + b = -go)
+    const uint32_t base  = ((uint32_t)(p.mismatch - go) & 0xFFu) * 0x01010101u;
+    const uint32_t delta = ((uint32_t)((p.mismatch - go) ^ (p.match - go))) & 0xFFu;
+    const uint32_t block = k * 16u;
+    uint32_t TA[16], TB[16], HO[16], F[16];
+    const uint32_t d2 = f2_fix2(dd), ge2 = f2_fix2(ge);
+    {
+        uint32_t qa[4] = { 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu }, qb[4] = { 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu };
+        if (live) { f2_stripe16(p.P, pbA, MA, block, qa); f2_stripe16(p.P, pbB, MB, block, qb); }
+        #pragma unroll
+        for (int j = 0; j < 16; ++j)
+        {
+            const uint32_t c = block + j;
+            const uint32_t a = (qa[j >> 2] >> (8 * (j & 3))) & 255u, bb = (qb[j >> 2] >> (8 * (j & 3))) & 255u;
+            uint32_t wa = 0x80808080u, wb = 0x80808080u;       // columns past the pattern: S = -128
+            if (live && c < MA) { dirtyA |= a > 3u; wa = base ^ (delta << (8u * (a & 3u))); }
+            if (live && c < MB) { dirtyB |= bb > 3u; wb = base ^ (delta << (8u * (bb & 3u))); }
+            TA[j] = wa; TB[j] = wb;
+        }
+    }
+    const uint32_t smask = (block < MA ? 0x0000FFFFu : 0u) | (block < MB ? 0xFFFF0000u : 0u);
+    uint32_t r_one, r_sixteen, r_m1;
+    asm volatile("mov.u32 %0, %1;" : "=r"(r_one) : "r"(p.one));
+    asm volatile("mov.u32 %0, %1;" : "=r"(r_sixteen) : "r"(q.sixteen));
+    asm volatile("mov.u32 %0, %1;" : "=r"(r_m1) : "r"(0u - p.one));
+    // column 0 of the matrix in the shear of local column -1: H = 0 -> HO' = B - b + d; E = 0 (gotoh_inl.h:68-71) -> B - b
+    const uint32_t ho_zero = f2_pack2(B - b + dd), e_zero = f2_pack2(B - b);
+    // lane 0 has no left neighbour; other lanes take (HO', E') of their neighbour's column 15 out of its shear (-16 b)
+    const uint32_t cin_mul = k == 0 ? 0u : r_one;
+    const uint32_t ho_add = k == 0 ? ho_zero : q.unshear, e_add = k == 0 ? e_zero : q.unshear;
+    uint32_t bestkey = f2_pack2(B) << 4, bestrow = 0u;
+    uint32_t carry = ho_zero, send_h = ho_zero, send_e = e_zero, tw = 0u;
+
+    auto reset = [&]()
+    {
+        #pragma unroll
+        for (int j = 0; j < 16; ++j) { HO[j] = f2_imad(FLc(j), r_one, d2); F[j] = 0u; }     // row 0: H = 0, F = -inf
+        carry = ho_zero;
+    };
+    reset();
+
+    auto row_step = [&](const uint32_t t, const bool masked, const bool first)
+    {
+        const uint32_t hin = f2_imad(__shfl_up_sync(0xFFFFFFFFu, send_h, 1), cin_mul, ho_add);
+        const uint32_t ein = f2_imad(__shfl_up_sync(0xFFFFFFFFu, send_e, 1), cin_mul, e_add);
+        const uint32_t i = t - k;
+        if (first && t == k) reset();
+        if ((i & 7u) == 0 && i < Nmax) tw = my_text[i >> 3];
+        const uint32_t nib = tw & 15u; tw >>= 4;
+        const uint32_t sel = f2_imad((nib & 3u) | ((nib & 12u) << 6), 0x11u, 0xC480u);
+
+        const uint32_t kb = f2_imad(bestkey & 0xFFF8FFF8u, r_one, 0xFFFEFFFFu);
+        uint32_t acc = kb, left = hin, e = ein, diag = carry;
+        carry = hin;
+        #pragma unroll
+        for (int j = 0; j < 16; j += 2)
+        {
+            uint32_t hh[2];
+            #pragma unroll
+            for (int u = 0; u < 2; ++u)
+            {
+                const int jj = j + u;
+                const uint32_t S = f2_prmt(TA[jj], TB[jj], sel);
+                const uint32_t top = HO[jj];
+                const uint32_t fn = f2_imad(__vmaxs2(F[jj], top), r_one, ge2);     // max(F, HO top) + ge
+                const uint32_t dg = __viaddmax_s16x2(diag, S, FLc(jj));                   // max(diagonal, floor)
+                e = __vmaxs2(e, left);                                               // E' of this column
+                const uint32_t h = __vimax3_s16x2(dg, fn, e);
+                F[jj] = fn; diag = top;
+                left = f2_imad(h, r_one, d2);                                             // HO' = h' + d
+                HO[jj] = left;
+                hh[u] = h;
+            }
+            acc = __vimax3_s16x2(acc, f2_imad(hh[0], r_sixteen, CJc(j)), f2_imad(hh[1], r_sixteen, CJc(j + 1)));
+        }
+        send_h = left; send_e = e;
+
+        const uint32_t df = f2_imad(kb, r_m1, acc);
+        const uint32_t sgn = f2_imad(df, r_one, 0x7FFF7FFFu);
+        uint32_t m = f2_prmt(sgn, sgn, 0xBB99u) & smask;
+        if (masked) m &= (i < NA ? 0x0000FFFFu : 0u) | (i < NB ? 0xFFFF0000u : 0u);
+        bestkey = (acc & m) | (bestkey & ~m);
+        bestrow = (f2_imad(i, 0x00010001u, 0u) & m) | (bestrow & ~m);
+    };
+
+    const uint32_t steps = __reduce_max_sync(0xFFFFFFFFu, live ? Nmax + p.lanes - 1 : 0u);
+    const uint32_t Nmin  = __reduce_min_sync(0xFFFFFFFFu, live ? min(NA, hasB ? NB : NA) : 0xFFFFFFFFu);
+    const uint32_t t_lo  = min(p.lanes, steps);
+    const uint32_t t_hi  = max(t_lo, min(Nmin, steps));
+    uint32_t t = 0;
+    for (; t < t_lo; ++t)  row_step(t, true, true);
+    for (; t < t_hi; ++t)  row_step(t, false, false);
+    for (; t < steps; ++t) row_step(t, true, false);
+
+    const uint32_t dmaskA = __ballot_sync(0xFFFFFFFFu, dirtyA), dmaskB = __ballot_sync(0xFFFFFFFFu, dirtyB);
+    const uint32_t gmask = (p.lanes >= 32 ? 0xFFFFFFFFu : ((1u << p.lanes) - 1u)) << gbase;
+    uint32_t wkA = 0, wkB = 0, wlaneA = 0, wlaneB = 0;
+    for (uint32_t l = 0; l < p.lanes; ++l)
+    {
+        const uint32_t src = min(gbase + l, 31u);
+        const uint32_t ok = __shfl_sync(0xFFFFFFFFu, bestkey, src);
+        const uint32_t sA = (ok & 0xFFFFu) >> 4, sB = ok >> 20;
+        if (sA >= (wkA >> 4)) { wkA = ok & 0xFFFFu; wlaneA = l; }
+        if (sB >= (wkB >> 4)) { wkB = ok >> 16; wlaneB = l; }
+    }
+    const uint32_t rowsA = __shfl_sync(0xFFFFFFFFu, bestrow, min(gbase + wlaneA, 31u));
+    const uint32_t rowsB = __shfl_sync(0xFFFFFFFFu, bestrow, min(gbase + wlaneB, 31u));
+    if (!live || k != 0) return;
+
+    #pragma unroll
+    for (int h = 0; h < 2; ++h)
+    {
+        if (h == 1 && !hasB) break;
+        const uint32_t id = h ? idB : idA;
+        const uint32_t M = h ? MB : MA, N = h ? NB : NA;
+        bool dirty = ((h ? dmaskB : dmaskA) & gmask) != 0;
+        if (p.match > 0 && (uint64_t)p.match * min(max(MA, MB), Nmax) + (uint32_t)B + 15u * (uint32_t)b >= 2047u) dirty = true;
+        if (dirty) { f2_mark_dirty(p.worklist, id); continue; }
+        const uint32_t wk = h ? wkB : wkA;
+        const uint32_t stripe = h ? wlaneB : wlaneA;
+        const uint32_t row = h ? (rowsB >> 16) : (rowsA & 0xFFFFu);
+        const int32_t score = (int32_t)(wk >> 4) - B;
+        nvb_best_sink out;
+        if (M == 0 || N == 0) { out.score = NVB_SINK_MIN; out.sink_x = out.sink_y = 0xFFFFFFFFu; }
+        else if (score <= 0) { out.score = 0; out.sink_x = N; out.sink_y = M; }   // all cells tie at 0: the last one visited
+        else { out.score = score; out.sink_x = row + 1u; out.sink_y = stripe * 16u + (wk & 15u) + 1u; }
+        p.sinks[id] = out;
+    }
+}
+
+// ---- Gotoh GLOBAL / SEMI_GLOBAL: sheared by ge in BOTH directions, x''[r][c] = x[r][c] - ge (r + c) + bias:
+//   F''  = max(F'', HO''top)          E'' = max(E''left, HO''left)
+//   h''  = max3( HO''diag + (S - ge - go), F'', E'' )                   HO'' = h'' + d
+// per packed cell PRMT + 2 VIMNMX + VIMNMX3 on the ALU pipe, two IMADs. Boundaries: row 0 (go + ge (c - 1),
+// gotoh_inl.h:675) and column 0 of GLOBAL become the constant d, column 0 of SEMI_GLOBAL (0) becomes -ge r; E of column 0
+// and F of row 0 are -infinity = 0 below every biased value. The opening surcharge is paid on every move to the right, so
+// columns past M do NOT carry h[r][M] along (as they do in part 1): the lane holding column M picks it out of its 16
+// registers with a one-hot multiply-add chain on the FMA pipe, which needs both pairs of a couple to have the same M --
+// couples that do not go to the int32 kernel.
+__global__ void __launch_bounds__(DF2_THREADS, 4)
+dpf2_gotoh_kernel(const Gotoh2Params q)
+{
+    const Full2Params& p = q.f;
+    extern __shared__ uint32_t s_mem[];
+    const uint32_t lane = threadIdx.x & 31u, wib = threadIdx.x >> 5;
+    const uint32_t warp = blockIdx.x * DF2_WARPS + wib;
+    const uint32_t g = lane / p.lanes, k = lane - g * p.lanes;
+    const uint32_t task = warp * p.tpw + g;
+    const bool live = g < p.tpw && task < p.n_tasks;
+    const uint32_t gbase = g * p.lanes;
+
+    uint32_t idA = 0, idB = 0, pbA = 0, pbB = 0, tbA = 0, tbB = 0, MA = 0, MB = 0, NA = 0, NB = 0;
+    bool hasB = false;
+    if (live)
+    {
+        idA = 2 * task; hasB = idA + 1 < p.n_pairs; idB = hasB ? idA + 1 : idA;
+        pbA = p.P.off[idA]; MA = p.P.off[idA + 1] - pbA; pbB = p.P.off[idB]; MB = p.P.off[idB + 1] - pbB;
+        tbA = p.T.off[idA]; NA = p.T.off[idA + 1] - tbA; tbB = p.T.off[idB]; NB = p.T.off[idB + 1] - tbB;
+    }
+    const uint32_t Nmax = max(NA, NB);
+    bool dirtyA = false, dirtyB = false;
+    uint32_t* my_text = s_mem + ((size_t)wib * p.tpw + (live ? g : 0)) * (p.tstride + p.cstride);
+    uint32_t* my_cand = my_text + p.tstride;
+    if (live) f2_pack_text(p.T, my_text, k, p.lanes, tbA, NA, tbB, NB, Nmax, dirtyA, dirtyB);
+    __syncwarp();
+
+    const int32_t go = p.ga, ge = p.gb, b = -ge, dd = go - ge, B = q.B;
+    const int32_t sm = p.match - ge - go, sx = p.mismatch - ge - go;       // >= 0
+    const uint32_t base  = ((uint32_t)sx & 0xFFu) * 0x01010101u;
+    const uint32_t delta = ((uint32_t)(sx ^ sm)) & 0xFFu;
+    const uint32_t block = k * 16u;
+    uint32_t TA[16], TB[16], HO[16], F[16], OH[16];
+    const uint32_t d2 = f2_fix2(dd), b2 = f2_pack2(b);
+    const bool capture = live && MA > 0 && k == (MA - 1u) / 16u;          // this lane holds column M (MA == MB, else the couple is dirty)
+    {
+        uint32_t qa[4] = { 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu }, qb[4] = { 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu };
+        if (live) { f2_stripe16(p.P, pbA, MA, block, qa); f2_stripe16(p.P, pbB, MB, block, qb); }
+        #pragma unroll
+        for (int j = 0; j < 16; ++j)
+        {
+            const uint32_t c = block + j;
+            const uint32_t a = (qa[j >> 2] >> (8 * (j & 3))) & 255u, bb = (qb[j >> 2] >> (8 * (j & 3))) & 255u;
+            uint32_t wa = 0u, wb = 0u;
+            if (live && c < MA) { dirtyA |= a > 3u; wa = base ^ (delta << (8u * (a & 3u))); }
+            if (live && c < MB) { dirtyB |= bb > 3u; wb = base ^ (delta << (8u * (bb & 3u))); }
+            TA[j] = wa; TB[j] = wb;
+            OH[j] = (capture && (uint32_t)j == ((MA - 1u) & 15u)) ? 1u : 0u;
+        }
+    }
+    uint32_t r_one; asm volatile("mov.u32 %0, %1;" : "=r"(r_one) : "r"(p.one));
+    // row 0 and column 0 in sheared, biased form
+    const uint32_t ho_row0 = f2_pack2(2 * dd + B), ho_origin = f2_pack2(dd + B);
+    const uint32_t cin_mul = k == 0 ? 0u : r_one;
+    const uint32_t col_mul = (k == 0 && p.semi) ? b2 : 0u;                 // SEMI_GLOBAL: H[r][0] = 0 -> -ge r
+    const uint32_t col_add = k == 0 ? (p.semi ? ho_origin : ho_row0) : 0u; // GLOBAL: H[r][0] = go + ge (r - 1) -> d, like row 0
+    uint32_t carry = 0u, send_h = 0u, send_e = 0u, tw = 0u;
+
+    auto reset = [&]()
+    {
+        #pragma unroll
+        for (int j = 0; j < 16; ++j) { HO[j] = ho_row0; F[j] = 0u; }
+        carry = k == 0 ? ho_origin : ho_row0;                               // H[0][0] = 0, H[0][c > 0] = go + ge (c - 1)
+    };
+    reset();
+
+    auto row_step = [&](const uint32_t t, const bool first)
+    {
+        const uint32_t i = t - k;
+        const uint32_t hin = f2_imad(__shfl_up_sync(0xFFFFFFFFu, send_h, 1), cin_mul, f2_imad(i + 1u, col_mul, col_add));
+        const uint32_t ein = f2_imad(__shfl_up_sync(0xFFFFFFFFu, send_e, 1), cin_mul, 0u);        // column 0: E = -infinity
+        if (first && t == k) reset();
+        if ((i & 7u) == 0 && i < Nmax) tw = my_text[i >> 3];
+        const uint32_t nib = tw & 15u; tw >>= 4;
+        const uint32_t sel = f2_imad((nib & 3u) | ((nib & 12u) << 6), 0x11u, 0xC480u);
+        uint32_t left = hin, e = ein, diag = carry, cap = 0u;
+        carry = hin;
+        #pragma unroll
+        for (int j = 0; j < 16; ++j)
+        {
+            const uint32_t top = HO[j];
+            const uint32_t fn = __vmaxs2(F[j], top);
+            const uint32_t dg = f2_imad(diag, r_one, f2_prmt(TA[j], TB[j], sel));
+            e = __vmaxs2(e, left);
+            const uint32_t h = __vimax3_s16x2(dg, fn, e);
+            F[j] = fn; diag = top;
+            left = f2_imad(h, r_one, d2);
+            HO[j] = left;
+            cap = f2_imad(left, OH[j], cap);
+        }
+        send_h = left; send_e = e;
+        // HO''[r][M] un-sheared along the rows: + ge r, shifted by -ge Nmax to stay >= 0
+        if (capture && i < Nmax) my_cand[i] = f2_imad(Nmax - 1u - i, b2, cap);
+    };
+
+    const uint32_t steps = __reduce_max_sync(0xFFFFFFFFu, live ? Nmax + p.lanes - 1 : 0u);
+    const uint32_t t_lo  = min(p.lanes, steps);
+    uint32_t t = 0;
+    for (; t < t_lo; ++t)  row_step(t, true);
+    for (; t < steps; ++t) row_step(t, false);
+    __syncwarp();
+
+    uint32_t bA = 0u, bB = 0u;
+    if (live)
+    {
+        if (p.semi)
+        {
+            for (uint32_t r = k; r < Nmax; r += p.lanes)
+            {
+                const uint32_t c = my_cand[r];
+                if (r < NA) bA = max(bA, ((c & 0xFFFFu) << 16) | r);
+                if (r < NB) bB = max(bB, (c & 0xFFFF0000u) | r);
+            }
+        }
+        else if (k == 0)
+        {
+            if (NA) bA = ((my_cand[NA - 1u] & 0xFFFFu) << 16) | (NA - 1u);
+            if (NB) bB = (my_cand[NB - 1u] & 0xFFFF0000u) | (NB - 1u);
+        }
+    }
+    const uint32_t dmaskA = __ballot_sync(0xFFFFFFFFu, dirtyA), dmaskB = __ballot_sync(0xFFFFFFFFu, dirtyB);
+    const uint32_t gmask = (p.lanes >= 32 ? 0xFFFFFFFFu : ((1u << p.lanes) - 1u)) << gbase;
+    uint32_t wA = 0u, wB = 0u;
+    for (uint32_t l = 0; l < p.lanes; ++l)
+    {
+        const uint32_t src = min(gbase + l, 31u);
+        wA = max(wA, __shfl_sync(0xFFFFFFFFu, bA, src));
+        wB = max(wB, __shfl_sync(0xFFFFFFFFu, bB, src));
+    }
+    if (!live || k != 0) return;
+
+    #pragma unroll
+    for (int h = 0; h < 2; ++h)
+    {
+        if (h == 1 && !hasB) break;
+        const uint32_t id = h ? idB : idA;
+        const uint32_t M = h ? MB : MA, N = h ? NB : NA;
+        bool dirty = ((h ? dmaskB : dmaskA) & gmask) != 0;
+        if (M == 0 || N == 0 || (hasB && MA != MB)) dirty = true;
+        const uint32_t pos = p.match > 0 ? (uint32_t)p.match : 0u;
+        if ((uint64_t)pos * min(M, Nmax) + (uint64_t)(uint32_t)b * (2ull * Nmax + 16u * p.lanes) + (uint32_t)B >= 32000ull) dirty = true;
+        if (dirty) { f2_mark_dirty(p.worklist, id); continue; }
+        const uint32_t w = h ? wB : wA;
+        nvb_best_sink out;
+        // value = H''[r][M] + d + B - ge (Nmax - r)  ->  H = value - d - B + ge (Nmax + M)
+        out.score  = (int32_t)(w >> 16) - dd - B + ge * (int32_t)(Nmax + M);
+        out.sink_x = (w & 0xFFFFu) + 1u;
+        out.sink_y = M;
+        p.sinks[id] = out;
+    }
+}
+
 static bool full2_geometry(uint32_t maxM, uint32_t maxN, uint32_t* lanes, uint32_t* tpw, uint32_t* tstride, uint32_t* cstride, size_t* smem)
 {
     const uint32_t stripes = (maxM + 15u) / 16u;
@@ -274,14 +630,30 @@ static bool full2_geometry(uint32_t maxM, uint32_t maxN, uint32_t* lanes, uint32
     return *smem <= 160u * 1024u;
 }
 
-bool dpf2_full_score_supported(const nvb_aligner& a, uint32_t maxM, uint32_t maxN)
+static bool sw_supported(const nvb_aligner& a)
 {
     if (a.type != NVB_GLOBAL && a.type != NVB_SEMI_GLOBAL) return false;
     if (a.kind != NVB_SMITH_WATERMAN && a.kind != NVB_EDIT_DISTANCE) return false;
     const Scheme s = make_scheme(a);
     if (s.ga > 0 || s.gb > 0 || s.ga < -255 || s.gb < -255) return false;
     const int32_t sm = s.match - s.ga - s.gb, sx = s.mismatch - s.ga - s.gb;     // sheared substitution scores: bytes 0..127
-    if (sm < 0 || sm > 127 || sx < 0 || sx > 127) return false;
+    return !(sm < 0 || sm > 127 || sx < 0 || sx > 127);
+}
+static bool gotoh_supported(const nvb_aligner& a)
+{
+    if (a.kind != NVB_GOTOH) return false;
+    const Scheme s = make_scheme(a);
+    const int32_t go = s.ga, ge = s.gb;
+    if (ge > 0 || go > ge || go < -64) return false;            // d = go - ge <= 0: opening never cheaper than extending
+    if (a.type == NVB_LOCAL)
+        return s.match - go <= 127 && s.match - go >= -127 && s.mismatch - go <= 127 && s.mismatch - go >= -127;
+    const int32_t sm = s.match - ge - go, sx = s.mismatch - ge - go;
+    return !(sm < 0 || sm > 127 || sx < 0 || sx > 127);
+}
+
+bool dpf2_full_score_supported(const nvb_aligner& a, uint32_t maxM, uint32_t maxN)
+{
+    if (!sw_supported(a) && !gotoh_supported(a)) return false;
     if (maxN == 0 || maxM == 0 || maxN > 65535u) return false;
     uint32_t lanes, tpw, tstride, cstride; size_t smem;
     return full2_geometry(maxM, maxN, &lanes, &tpw, &tstride, &cstride, &smem);
@@ -291,7 +663,8 @@ int dpf2_full_score(nvb_ctx* ctx, const nvb_aligner& a, StrSet P, StrSet T, nvb_
                     uint32_t maxN, uint32_t* worklist, cudaStream_t st)
 {
     const Scheme s = make_scheme(a);
-    Full2Params p;
+    Gotoh2Params q;
+    Full2Params& p = q.f;
     size_t smem;
     if (!full2_geometry(maxM, maxN, &p.lanes, &p.tpw, &p.tstride, &p.cstride, &smem)) return NVB_ERR_UNSUPPORTED;
     p.P = P; p.T = T; p.sinks = sinks; p.worklist = worklist;
@@ -299,14 +672,49 @@ int dpf2_full_score(nvb_ctx* ctx, const nvb_aligner& a, StrSet P, StrSet T, nvb_
     p.match = s.match; p.mismatch = s.mismatch; p.ga = s.ga; p.gb = s.gb;
     p.semi = a.type == NVB_SEMI_GLOBAL ? 1 : 0;
     p.one = 1;
-    if (!(ctx->attr_done & NVB_ATTR_FULL2))
+    if (NVB_FIRST_ON_DEVICE(ctx))
     {
         NVB_CUDA(ctx, cudaFuncSetAttribute(dpf2_sw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
-        ctx->attr_done |= NVB_ATTR_FULL2;
+        NVB_CUDA(ctx, cudaFuncSetAttribute(dpf2_gotoh_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+        NVB_CUDA(ctx, cudaFuncSetAttribute(dpf2_gotoh_local_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+        NVB_CUDA(ctx, cudaFuncSetAttribute(dpf2_gotoh_local_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+        NVB_CUDA(ctx, cudaFuncSetAttribute(dpf2_gotoh_local_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+        NVB_CUDA(ctx, cudaFuncSetAttribute(dpf2_gotoh_local_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
     }
     const uint32_t n_warps = (p.n_tasks + p.tpw - 1) / p.tpw;
     const uint32_t grid = (n_warps + DF2_WARPS - 1) / DF2_WARPS;
-    dpf2_sw_kernel<<<grid, DF2_THREADS, smem, st>>>(p);
+    if (a.kind != NVB_GOTOH)
+        dpf2_sw_kernel<<<grid, DF2_THREADS, smem, st>>>(p);
+    else if (a.type == NVB_LOCAL)
+    {
+        const int32_t b = -s.gb;
+        const int bt = (b >= 1 && b <= 3) ? b : 0;
+        q.B = DF2_BIAS;
+        q.sixteen = 16;
+        q.unshear = (((uint32_t)(-16 * b - 1) & 0xFFFFu) << 16) | ((uint32_t)(-16 * b) & 0xFFFFu);
+        if (b == 0) q.unshear = 0u;
+        for (int j = 0; j < 16; ++j)
+        {
+            q.FL[j] = ((uint32_t)(q.B + b * j) & 0xFFFFu) * 0x00010001u;
+            const int32_t cj = j - 16 * b * j;
+            q.CJ[j] = cj < 0 ? ((((uint32_t)(cj - 1) & 0xFFFFu) << 16) | ((uint32_t)cj & 0xFFFFu)) : (uint32_t)cj * 0x00010001u;
+        }
+        const size_t smem_l = (size_t)DF2_WARPS * p.tpw * p.tstride * sizeof(uint32_t);
+        switch (bt)
+        {
+        case 1:  dpf2_gotoh_local_kernel<1><<<grid, DF2_THREADS, smem_l, st>>>(q); break;
+        case 2:  dpf2_gotoh_local_kernel<2><<<grid, DF2_THREADS, smem_l, st>>>(q); break;
+        case 3:  dpf2_gotoh_local_kernel<3><<<grid, DF2_THREADS, smem_l, st>>>(q); break;
+        default: dpf2_gotoh_local_kernel<0><<<grid, DF2_THREADS, smem_l, st>>>(q); break;
+        }
+    }
+    else
+    {
+        const int32_t dd = s.ga - s.gb;
+        q.B = 3 * (-dd) + 4;
+        q.sixteen = 16; q.unshear = 0;
+        dpf2_gotoh_kernel<<<grid, DF2_THREADS, smem, st>>>(q);
+    }
     NVB_LAUNCHED(ctx);
     return NVB_OK;
 }
