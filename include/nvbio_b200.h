@@ -286,7 +286,8 @@ int nvb_batch_score_best2(nvb_ctx* ctx, nvb_aligner aligner, uint32_t band, uint
  * alphabet = 2, 4 or 5 (MyersTag's ALPHABET_SIZE), band = 1..32. Scores are negated distances; SEMI_GLOBAL reports every
  * column of the last pattern row that lies in the band and scores >= min_score, GLOBAL the last one, LOCAL nothing.
  * min_score is truncated to int16 as the reference's banded_myers does (:189) -- pass NVB_MYERS_BATCH_MIN_SCORE to get
- * the value the reference's batch drivers end up with (Field_traits<int32>::min() -> 0: exact matches only). */
+ * the value the reference's batch drivers end up with (Field_traits<int32>::min() -> 0: exact matches only).
+ * 8-bit symbol arrays must be 4-byte aligned (the kernel reads them as aligned words; NVB_ERR_ARG otherwise). */
 #define NVB_MYERS_BATCH_MIN_SCORE (-(1 << 30))
 int nvb_batch_banded_myers_score(nvb_ctx* ctx, int32_t type, uint32_t alphabet, uint32_t band, nvb_string_set patterns,
                                  nvb_string_set texts, int32_t min_score, nvb_best_sink* sinks, void* stream);

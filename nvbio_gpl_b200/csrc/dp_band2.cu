@@ -187,10 +187,11 @@ band2_kernel(const Band2Params p)
 
     uint32_t seen = 0;
     Stream sPA, sPB, sTA, sTB;
-    c_open(sPA, p.P.sym, pbA, MA, 0, slot, seen);
-    c_open(sPB, p.P.sym, pbB, MB, 0, slot + 64, seen);
-    c_open(sTA, p.T.sym, tbA, NA, W - 1, slot + 128, seen);
-    c_open(sTB, p.T.sym, tbB, NB, W - 1, slot + 192, seen);
+    const uint32_t Ptot = __ldg(p.P.off + p.P.count), Ttot = __ldg(p.T.off + p.T.count);
+    bool edge = c_open(sPA, p.P.sym, Ptot, pbA, MA, 0, slot, seen);
+    edge |= c_open(sPB, p.P.sym, Ptot, pbB, MB, 0, slot + 64, seen);
+    edge |= c_open(sTA, p.T.sym, Ttot, tbA, NA, W - 1, slot + 128, seen);
+    edge |= c_open(sTB, p.T.sym, Ttot, tbB, NB, W - 1, slot + 192, seen);
 
     uint32_t X[W], F[W], win[WS];
     #pragma unroll
@@ -299,7 +300,7 @@ band2_kernel(const Band2Params p)
     }
 
     // ---- epilogue
-    bool dirty = MA == 0 || MB == 0;
+    bool dirty = MA == 0 || MB == 0 || edge;     // edge: a string at the end of an unaligned symbol array (c_open)
     // GLOBAL reports the band's last cell; when that lies right of the text the reference's score depends on the 255s it
     // reads there (sw_banded_inl.h:444), which this kernel's text stream does not reproduce
     // LOCAL reports every band cell, the ones right of the text included (where the reference reads 255s as well)

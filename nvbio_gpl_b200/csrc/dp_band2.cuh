@@ -90,18 +90,25 @@ __device__ __forceinline__ void c_put(uint8_t* ring, uint32_t slot_off, const ui
     d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
     if (slot_off == 0u) { d[12] = v.x; d[13] = v.y; d[14] = v.z; d[15] = v.w; }
 }
-// skip = bytes of the string that are not streamed (the text positions the window starts with)
-__device__ __forceinline__ void c_open(Stream& s, const uint8_t* sym, uint32_t beg, uint32_t L, uint32_t skip, uint8_t* ring, uint32_t& seen)
+// skip = bytes of the string that are not streamed (the text positions the window starts with); total = symbols in the whole
+// set. The streams fetch ALIGNED 16-byte blocks: a string whose first or last block sticks out of the symbol array
+// [sym, sym + total) -- only the strings at the two ends of a set whose array is not 16-byte aligned there -- is not streamed
+// at all (every load predicated off); the function then returns true and the caller hands the pair to the int32 kernel. No byte
+// outside the caller's array is ever read.
+__device__ __forceinline__ bool c_open(Stream& s, const uint8_t* sym, uint32_t total, uint32_t beg, uint32_t L, uint32_t skip, uint8_t* ring, uint32_t& seen)
 {
     const uint32_t delta = (uint32_t)((uintptr_t)sym & 15u);
     s.base = sym - delta;
     const uint32_t pos = delta + beg + skip, b0 = pos & ~15u;
     s.end = delta + beg + L; s.nb = b0 + 32u;
     s.ring = ring; s.ptr = ring + (pos & 15u);
+    const bool edge = L > skip && (b0 < delta || ((s.end + 15u) & ~15u) > delta + total);
+    if (edge) s.end = 0u;
     const uint4 v0 = c_load(s, b0), v1 = c_load(s, b0 + 16u);
     seen |= v0.x | v0.y | v0.z | v0.w | v1.x | v1.y | v1.z | v1.w;      // neighbours' bytes included: a filter, confirmed exactly later
     c_put(ring, 0u, c_clip(s, b0, v0));
     c_put(ring, 16u, c_clip(s, b0 + 16u, v1));
+    return edge;
 }
 // one byte on (single rows): fetches synchronously when the stream enters its next block
 __device__ __forceinline__ void c_step(Stream& s, uint32_t& seen)

@@ -161,10 +161,11 @@ band2_tb_forward_kernel(const Band2TbParams q)
 
     uint32_t seen = 0;
     Stream sPA, sPB, sTA, sTB;
-    c_open(sPA, p.P.sym, pbA, MA, 0, slot, seen);
-    c_open(sPB, p.P.sym, pbB, MB, 0, slot + 64, seen);
-    c_open(sTA, p.T.sym, tbA, NA, W - 1, slot + 128, seen);
-    c_open(sTB, p.T.sym, tbB, NB, W - 1, slot + 192, seen);
+    const uint32_t Ptot = __ldg(p.P.off + p.P.count), Ttot = __ldg(p.T.off + p.T.count);
+    bool edge = c_open(sPA, p.P.sym, Ptot, pbA, MA, 0, slot, seen);
+    edge |= c_open(sPB, p.P.sym, Ptot, pbB, MB, 0, slot + 64, seen);
+    edge |= c_open(sTA, p.T.sym, Ttot, tbA, NA, W - 1, slot + 128, seen);
+    edge |= c_open(sTB, p.T.sym, Ttot, tbB, NB, W - 1, slot + 192, seen);
 
     uint32_t X[W], F[W], win[WS];
     #pragma unroll
@@ -259,7 +260,7 @@ band2_tb_forward_kernel(const Band2TbParams q)
         }
     }
 
-    bool dirty = MA == 0 || MB == 0;
+    bool dirty = MA == 0 || MB == 0 || edge;     // edge: a string at the end of an unaligned symbol array (c_open)
     if (TYPE == T_GLOBAL) dirty = dirty || NA < MA + W - 1 || NB < MB + W - 1;
     if (seen & 0xFCFCFCFCu)
         dirty = dirty || c_has_high_symbol(p.P.sym, pbA, MA) || c_has_high_symbol(p.P.sym, pbB, MB) ||
