@@ -318,6 +318,40 @@ int nvb_ops_to_cigar(nvb_ctx* ctx, const uint8_t* ops, uint32_t ops_stride, cons
                      uint32_t n, uint16_t* cigar, uint32_t cigar_stride, uint32_t* n_cigar,
                      void* stream);
 
+/* Quality-aware scoring schemes: the scheme interfaces of nvbio/alignment/alignment.h:411-436 (GotohScoringScheme) and :488-505
+ * (SmithWatermanScoringScheme) evaluate match(q) and mismatch(a, b, q) at the quality q of each PATTERN position
+ * (sw_inl.h:470-472, gotoh_inl.h:666,729, sw_banded_inl.h:391, gotoh_banded_inl.h:461); nvBowtie's scheme is one
+ * (nvBowtie/bowtie2/cuda/scoring.h:206-301: constant match bonus, quality-scaled mismatch penalty, separate read and reference gap
+ * penalties). Across the C ABI the two functors are 256-entry HOST tables indexed by q (schemes whose mismatch also depends on
+ * the two symbols stay out of contract); aligner.match / .mismatch are ignored, aligner.gap_a / gap_b stay deletion / insertion
+ * (SW) or pattern_gap_open / pattern_gap_extension (Gotoh: the reference runs the whole recurrence on the PATTERN gap
+ * penalties, gotoh_inl.h:641-642); text_gap_open / text_gap_ext are Gotoh's text_gap_open() / text_gap_extension(), which the
+ * reference reads only to initialise GLOBAL first columns / band rows and in the banded infimum (gotoh_inl.h:69-70,
+ * gotoh_banded_inl.h:48,437-439). quals (DEVICE) holds one byte per pattern symbol, addressed by the patterns' offsets; NULL =
+ * aln::trivial_quality_string (q = 0 everywhere). Edit distance has no scheme: qualities do not enter. These calls run the
+ * int32 one-pair-per-thread kernels and copy the tables (2 KB) to a context-owned buffer first; otherwise they behave exactly
+ * like the entry points without _q (same scratch, results, refusal rules). */
+typedef struct {
+    const int32_t* match_h;        /* 256 entries: scheme.match(q)                                  */
+    const int32_t* mismatch_h;     /* 256 entries: scheme.mismatch(a, b, q), a != b                 */
+    int32_t        text_gap_open;  /* Gotoh: scheme.text_gap_open()                                 */
+    int32_t        text_gap_ext;   /* Gotoh: scheme.text_gap_extension()                            */
+} nvb_quality_scheme;
+int nvb_batch_score_q(nvb_ctx* ctx, nvb_aligner aligner, const nvb_quality_scheme* scheme, nvb_string_set patterns, const uint8_t* quals,
+                      nvb_string_set texts, nvb_best_sink* sinks, uint32_t max_pattern_len, uint32_t max_text_len,
+                      void* temp, size_t temp_bytes, void* stream);
+int nvb_batch_banded_score_q(nvb_ctx* ctx, nvb_aligner aligner, const nvb_quality_scheme* scheme, uint32_t band, nvb_string_set patterns,
+                             const uint8_t* quals, nvb_string_set texts, nvb_best_sink* sinks, uint32_t max_pattern_len,
+                             uint32_t max_text_len, void* temp, size_t temp_bytes, void* stream);
+int nvb_batch_traceback_q(nvb_ctx* ctx, nvb_aligner aligner, const nvb_quality_scheme* scheme, uint32_t checkpoints,
+                          nvb_string_set patterns, const uint8_t* quals, nvb_string_set texts, nvb_alignment* out,
+                          uint8_t* ops, uint32_t ops_stride, uint32_t* n_ops, uint32_t max_pattern_len, uint32_t max_text_len,
+                          void* temp, size_t temp_bytes, void* stream);
+int nvb_batch_banded_traceback_q(nvb_ctx* ctx, nvb_aligner aligner, const nvb_quality_scheme* scheme, uint32_t band, uint32_t checkpoints,
+                                 nvb_string_set patterns, const uint8_t* quals, nvb_string_set texts, nvb_alignment* out,
+                                 uint8_t* ops, uint32_t ops_stride, uint32_t* n_ops, uint32_t max_pattern_len, uint32_t max_text_len,
+                                 void* temp, size_t temp_bytes, void* stream);
+
 /* host-buffer forms (H2D of both string sets, kernel(s), D2H of the results; synchronous) */
 int nvb_batch_score_host(nvb_ctx* ctx, nvb_aligner aligner, uint32_t band /* 0 = full matrix */,
                          const uint8_t* pat_h, const uint32_t* pat_off_h, const uint8_t* txt_h,

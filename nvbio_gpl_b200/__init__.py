@@ -12,7 +12,7 @@ from .fmindex import FMIndex, FMIndexFilter, match, match_reverse, match_approx,
 from .io import load_index, save_index, CLoadedIndex  # noqa: F401
 from .alignment import (  # noqa: F401
     EDIT_DISTANCE, SMITH_WATERMAN, GOTOH, GLOBAL, LOCAL, SEMI_GLOBAL,
-    Aligner, EditDistanceAligner, SmithWatermanAligner, GotohAligner, StringSet,
+    Aligner, EditDistanceAligner, SmithWatermanAligner, GotohAligner, QualityScheme, StringSet,
     batch_alignment_score, batch_banded_alignment_score, batch_alignment_score_noalloc, NOALLOC_SCRATCH_BYTES,
     MyersTag, MyersAligner, batch_banded_myers_score, batch_alignment_score_best2, MYERS_BATCH_MIN_SCORE,
     batch_alignment_traceback, batch_banded_alignment_traceback,

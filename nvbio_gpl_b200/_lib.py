@@ -30,6 +30,10 @@ class AlignerC(C.Structure):
                 ("gap_a", C.c_int32), ("gap_b", C.c_int32)]
 
 
+class QualitySchemeC(C.Structure):
+    _fields_ = [("match_h", C.c_void_p), ("mismatch_h", C.c_void_p), ("text_gap_open", C.c_int32), ("text_gap_ext", C.c_int32)]
+
+
 class MapParamsC(C.Structure):
     _fields_ = [("seed_len", C.c_uint32), ("seed_interval", C.c_uint32), ("max_hits", C.c_uint32), ("max_range", C.c_uint32),
                 ("band", C.c_uint32), ("both_strands", C.c_uint32), ("min_score", C.c_int32), ("aligner", AlignerC)]
@@ -95,6 +99,10 @@ _PROTOS = {
     "nvb_batch_score": (_i, [_vp, AlignerC, StringSetC, StringSetC, _vp, _u32, _u32, _vp, _sz, _vp]),
     "nvb_batch_score_noalloc_bytes": (_sz, [AlignerC, _u32, _u32]),
     "nvb_batch_score_noalloc": (_i, [_vp, AlignerC, StringSetC, StringSetC, _vp, _u32, _u32, _vp]),
+    "nvb_batch_score_q": (_i, [_vp, AlignerC, C.POINTER(QualitySchemeC), StringSetC, _vp, StringSetC, _vp, _u32, _u32, _vp, _sz, _vp]),
+    "nvb_batch_banded_score_q": (_i, [_vp, AlignerC, C.POINTER(QualitySchemeC), _u32, StringSetC, _vp, StringSetC, _vp, _u32, _u32, _vp, _sz, _vp]),
+    "nvb_batch_traceback_q": (_i, [_vp, AlignerC, C.POINTER(QualitySchemeC), _u32, StringSetC, _vp, StringSetC, _vp, _vp, _u32, _vp, _u32, _u32, _vp, _sz, _vp]),
+    "nvb_batch_banded_traceback_q": (_i, [_vp, AlignerC, C.POINTER(QualitySchemeC), _u32, _u32, StringSetC, _vp, StringSetC, _vp, _vp, _u32, _vp, _u32, _u32, _vp, _sz, _vp]),
     "nvb_batch_banded_score": (_i, [_vp, AlignerC, _u32, StringSetC, StringSetC, _vp, _u32, _u32, _vp, _sz, _vp]),
     "nvb_batch_score_best2": (_i, [_vp, AlignerC, _u32, _u32, StringSetC, StringSetC, _vp, _u32, _u32, _vp, _sz, _vp]),
     "nvb_batch_banded_myers_score": (_i, [_vp, C.c_int32, _u32, _u32, StringSetC, StringSetC, C.c_int32, _vp, _vp]),

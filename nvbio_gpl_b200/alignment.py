@@ -47,6 +47,26 @@ def GotohAligner(type_, match, mismatch, gap_open, gap_ext):
     return Aligner(GOTOH, type_, match, mismatch, gap_open, gap_ext)
 
 
+class QualityScheme:
+    """the quality-aware half of a SmithWatermanScoringScheme / GotohScoringScheme (alignment.h:411-436, 488-505): match(q) and
+    mismatch(a, b, q) as 256-entry tables over the pattern quality, plus Gotoh's text gap penalties (the aligner's gap_a / gap_b are
+    the pattern gap penalties). Pass it as ``scheme=`` together with ``quals=`` (uint8 device tensor, one per pattern symbol)."""
+
+    def __init__(self, match, mismatch, text_gap_open=0, text_gap_ext=0):
+        self.match = np.ascontiguousarray(match, dtype=np.int32)
+        self.mismatch = np.ascontiguousarray(mismatch, dtype=np.int32)
+        if len(self.match) != 256 or len(self.mismatch) != 256:
+            raise _lib.NvbError("QualityScheme: the match and mismatch tables need 256 entries each")
+        self.text_gap_open, self.text_gap_ext = int(text_gap_open), int(text_gap_ext)
+
+    def c(self):
+        return _lib.QualitySchemeC(self.match.ctypes.data, self.mismatch.ctypes.data, self.text_gap_open, self.text_gap_ext)
+
+
+def _qptr(quals):
+    return quals.data_ptr() if quals is not None else None
+
+
 class StringSet:
     """ConcatenatedStringSet (nvbio/strings/string_set.h:405-492): symbols + count+1 offsets, on a CUDA device"""
 
@@ -92,9 +112,10 @@ def _temp(op, aligner, band, chk, maxM, maxN, n, device, temp):
     return temp
 
 
-def batch_alignment_score(aligner, patterns, texts, sinks=None, temp=None, ctx=None):
-    """aln::batch_alignment_score(aligner, patterns, texts, sinks, scheduler, maxM, maxN) (batched.h:98-140).
-    sinks: int32 [n,3] = (score, sink.x = text end, sink.y = pattern end)"""
+def batch_alignment_score(aligner, patterns, texts, sinks=None, temp=None, ctx=None, scheme=None, quals=None):
+    """aln::batch_alignment_score(aligner, patterns, [quals,] texts, sinks, scheduler, maxM, maxN) (batched.h:98-192).
+    sinks: int32 [n,3] = (score, sink.x = text end, sink.y = pattern end). scheme / quals: a QualityScheme and the pattern
+    qualities (the reference's quals overload, batched.h:126-148)"""
     ctx = _ctx(patterns.offsets, ctx)
     n = patterns.count
     dev = patterns.offsets.device
@@ -102,6 +123,11 @@ def batch_alignment_score(aligner, patterns, texts, sinks=None, temp=None, ctx=N
         sinks = torch.empty((n, 3), dtype=torch.int32, device=dev)
     maxM, maxN = patterns.max_len, texts.max_len
     temp = _temp(_lib.OP_SCORE, aligner, 0, 0, maxM, maxN, n, dev, temp)
+    if scheme is not None:
+        qs = scheme.c()
+        check(lib().nvb_batch_score_q(ctx.h, aligner.c(), C.byref(qs), patterns.c(), _qptr(quals), texts.c(), sinks.data_ptr(), maxM, maxN,
+                                      temp.data_ptr(), temp.numel(), _lib.current_stream_ptr()), ctx.h)
+        return sinks
     check(lib().nvb_batch_score(ctx.h, aligner.c(), patterns.c(), texts.c(), sinks.data_ptr(), maxM, maxN,
                                 temp.data_ptr(), temp.numel(), _lib.current_stream_ptr()), ctx.h)
     return sinks
@@ -132,13 +158,18 @@ def batch_alignment_score_noalloc(aligner, patterns, texts, sinks, max_pattern_l
     return sinks
 
 
-def batch_banded_alignment_score(aligner, band, patterns, texts, sinks=None, ctx=None):
+def batch_banded_alignment_score(aligner, band, patterns, texts, sinks=None, ctx=None, scheme=None, quals=None):
     """aln::batch_banded_alignment_score<BAND_LEN>(...) (batched.h:142-192)"""
     ctx = _ctx(patterns.offsets, ctx)
     n = patterns.count
     dev = patterns.offsets.device
     if sinks is None:
         sinks = torch.empty((n, 3), dtype=torch.int32, device=dev)
+    if scheme is not None:
+        qs = scheme.c()
+        check(lib().nvb_batch_banded_score_q(ctx.h, aligner.c(), C.byref(qs), band, patterns.c(), _qptr(quals), texts.c(), sinks.data_ptr(),
+                                             patterns.max_len, texts.max_len, None, 0, _lib.current_stream_ptr()), ctx.h)
+        return sinks
     check(lib().nvb_batch_banded_score(ctx.h, aligner.c(), band, patterns.c(), texts.c(), sinks.data_ptr(),
                                        patterns.max_len, texts.max_len, None, 0, _lib.current_stream_ptr()), ctx.h)
     return sinks
@@ -190,7 +221,7 @@ def batch_alignment_score_best2(aligner, band, distinct_dist, patterns, texts, s
     return sinks
 
 
-def batch_alignment_traceback(aligner, checkpoints, patterns, texts, ops_stride=None, temp=None, ctx=None):
+def batch_alignment_traceback(aligner, checkpoints, patterns, texts, ops_stride=None, temp=None, ctx=None, scheme=None, quals=None):
     """BatchedAlignmentTraceback<CHECKPOINTS,...>::enact (batched.h:335-380).
     Returns (alignments int32 [n,5], ops uint8 [n,ops_stride] in push order, n_ops int32 [n])"""
     ctx = _ctx(patterns.offsets, ctx)
@@ -203,13 +234,19 @@ def batch_alignment_traceback(aligner, checkpoints, patterns, texts, ops_stride=
     ops = torch.zeros((n, ops_stride), dtype=torch.uint8, device=dev)
     n_ops = torch.empty(n, dtype=torch.int32, device=dev)
     temp = _temp(_lib.OP_TRACEBACK, aligner, 0, checkpoints, maxM, maxN, n, dev, temp)
+    if scheme is not None:
+        qs = scheme.c()
+        check(lib().nvb_batch_traceback_q(ctx.h, aligner.c(), C.byref(qs), checkpoints, patterns.c(), _qptr(quals), texts.c(), out.data_ptr(),
+                                          ops.data_ptr(), ops_stride, n_ops.data_ptr(), maxM, maxN, temp.data_ptr(), temp.numel(),
+                                          _lib.current_stream_ptr()), ctx.h)
+        return out, ops, n_ops
     check(lib().nvb_batch_traceback(ctx.h, aligner.c(), checkpoints, patterns.c(), texts.c(), out.data_ptr(), ops.data_ptr(),
                                     ops_stride, n_ops.data_ptr(), maxM, maxN, temp.data_ptr(), temp.numel(),
                                     _lib.current_stream_ptr()), ctx.h)
     return out, ops, n_ops
 
 
-def batch_banded_alignment_traceback(aligner, band, checkpoints, patterns, texts, ops_stride=None, temp=None, ctx=None, bufs=None):
+def batch_banded_alignment_traceback(aligner, band, checkpoints, patterns, texts, ops_stride=None, temp=None, ctx=None, bufs=None, scheme=None, quals=None):
     """BatchedBandedAlignmentTraceback<BAND_LEN,CHECKPOINTS,...>::enact (batched.h:382-438)"""
     ctx = _ctx(patterns.offsets, ctx)
     n = patterns.count
@@ -225,6 +262,12 @@ def batch_banded_alignment_traceback(aligner, band, checkpoints, patterns, texts
         ops = torch.zeros((n, ops_stride), dtype=torch.uint8, device=dev)
         n_ops = torch.empty(n, dtype=torch.int32, device=dev)
     temp = _temp(_lib.OP_BANDED_TRACEBACK, aligner, band, checkpoints, maxM, maxN, n, dev, temp)
+    if scheme is not None:
+        qs = scheme.c()
+        check(lib().nvb_batch_banded_traceback_q(ctx.h, aligner.c(), C.byref(qs), band, checkpoints, patterns.c(), _qptr(quals), texts.c(),
+                                                 out.data_ptr(), ops.data_ptr(), ops_stride, n_ops.data_ptr(), maxM, maxN, temp.data_ptr(),
+                                                 temp.numel(), _lib.current_stream_ptr()), ctx.h)
+        return out, ops, n_ops
     check(lib().nvb_batch_banded_traceback(ctx.h, aligner.c(), band, checkpoints, patterns.c(), texts.c(), out.data_ptr(),
                                            ops.data_ptr(), ops_stride, n_ops.data_ptr(), maxM, maxN, temp.data_ptr(),
                                            temp.numel(), _lib.current_stream_ptr()), ctx.h)

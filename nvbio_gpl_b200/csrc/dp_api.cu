@@ -139,7 +139,31 @@ static int unpack_for_fast_path(nvb_ctx* ctx, StrSet& P, StrSet& T, uint32_t max
     return NVB_OK;
 }
 
-extern "C" int nvb_batch_score(nvb_ctx* ctx, nvb_aligner a, nvb_string_set patterns, nvb_string_set texts,
+
+// ---------------------------------------------------------------------------------------------------------------
+// Quality-aware scoring schemes (nvbio/alignment/alignment.h:411-436,488-505; nvBowtie's is bowtie2/cuda/scoring.h:206-301): the
+// host tables go to a small context-owned device buffer, the calls then run the int32 kernels, which read match(q) /
+// mismatch(a, b, q) at the quality of each pattern position.
+// ---------------------------------------------------------------------------------------------------------------
+enum { DP_STAGE_QTABLES = 55 };   // slot map in common.cuh
+static int quality_tables(nvb_ctx* ctx, const nvb_aligner& a, const nvb_quality_scheme* qs, const uint8_t* quals, cudaStream_t s, QualDev* qd, const QualDev** out)
+{
+    *out = nullptr;
+    if (!qs) return quals ? NVB_ERR_ARG : NVB_OK;
+    if (!qs->match_h || !qs->mismatch_h) return NVB_ERR_ARG;
+    if (a.kind == NVB_EDIT_DISTANCE) return NVB_OK;                       // EditDistanceAligner has no scheme: qualities do not enter
+    void* d = nullptr;
+    int rc = nvb_stage(ctx, DP_STAGE_QTABLES, 512 * sizeof(int32_t), &d);
+    if (rc) return rc;
+    NVB_CUDA(ctx, cudaMemcpyAsync(d, qs->match_h, 256 * sizeof(int32_t), cudaMemcpyHostToDevice, s));
+    NVB_CUDA(ctx, cudaMemcpyAsync((int32_t*)d + 256, qs->mismatch_h, 256 * sizeof(int32_t), cudaMemcpyHostToDevice, s));
+    qd->qm = (const int32_t*)d; qd->qx = (const int32_t*)d + 256; qd->quals = quals;
+    qd->tga = qs->text_gap_open; qd->tgb = qs->text_gap_ext;
+    *out = qd;
+    return NVB_OK;
+}
+
+static int batch_score_impl(nvb_ctx* ctx, nvb_aligner a, const nvb_quality_scheme* qs, const uint8_t* quals, nvb_string_set patterns, nvb_string_set texts,
                                nvb_best_sink* sinks, uint32_t maxM, uint32_t maxN, void* temp, size_t temp_bytes, void* stream)
 {
     if (!ctx) return NVB_ERR_ARG;
@@ -152,10 +176,13 @@ extern "C" int nvb_batch_score(nvb_ctx* ctx, nvb_aligner a, nvb_string_set patte
     const StrSet P = make_set(patterns), T = make_set(texts);
     const TempPlan p = plan(NVB_OP_SCORE, a, 0, 0, maxM, maxN);
     ctx->last_paths = 0;
+    QualDev qdev; const QualDev* qd = nullptr;
+    if ((rc = quality_tables(ctx, a, qs, quals, s, &qdev, &qd))) return rc;
 
     const bool fast_local = dpf_full_score_supported(a, P, T, maxM, maxN);
-    const bool fast_sheared = !fast_local && ctx->force_generic == 0 && dpf2_full_score_supported(a, maxM, maxN);   // force_generic 2: no sheared-coordinate kernels
-    if (ctx->force_generic != 1 && temp && batch_pairs(p, temp_bytes, n) >= n && (fast_local || fast_sheared))
+    const bool fast_sheared = !fast_local && ctx->force_generic == 0 && dpf2_full_score_supported(a, maxM, maxN);
+    const bool use_fast = !qd;                                                   // quality-aware schemes: int32 kernels   // force_generic 2: no sheared-coordinate kernels
+    if (use_fast && ctx->force_generic != 1 && temp && batch_pairs(p, temp_bytes, n) >= n && (fast_local || fast_sheared))
     {
         // packed DPX kernel; pairs it cannot represent exactly are appended to the ctx worklist and
         // re-scored by the int32 kernel, which reads the count on the device (no host sync)
@@ -190,12 +217,20 @@ extern "C" int nvb_batch_score(nvb_ctx* ctx, nvb_aligner a, nvb_string_set patte
     for (uint32_t first = 0; first < n; first += bp)
     {
         const uint32_t cnt = n - first < bp ? n - first : bp;
-        if ((rc = dpg_full_score(ctx, a, P, T, nullptr, nullptr, first, cnt, sinks, (int16_t*)temp, maxN, s))) return rc;
+        if ((rc = dpg_full_score(ctx, a, P, T, nullptr, nullptr, first, cnt, sinks, (int16_t*)temp, maxN, s, Sink2{nullptr, 0}, qd))) return rc;
     }
     return NVB_OK;
 }
 
-extern "C" int nvb_batch_banded_score(nvb_ctx* ctx, nvb_aligner a, uint32_t band, nvb_string_set patterns,
+extern "C" int nvb_batch_score(nvb_ctx* ctx, nvb_aligner a, nvb_string_set patterns, nvb_string_set texts,
+                               nvb_best_sink* sinks, uint32_t maxM, uint32_t maxN, void* temp, size_t temp_bytes, void* stream)
+{ return batch_score_impl(ctx, a, nullptr, nullptr, patterns, texts, sinks, maxM, maxN, temp, temp_bytes, stream); }
+
+extern "C" int nvb_batch_score_q(nvb_ctx* ctx, nvb_aligner a, const nvb_quality_scheme* qs, nvb_string_set patterns, const uint8_t* quals,
+                                 nvb_string_set texts, nvb_best_sink* sinks, uint32_t maxM, uint32_t maxN, void* temp, size_t temp_bytes, void* stream)
+{ if (!qs) return NVB_ERR_ARG; return batch_score_impl(ctx, a, qs, quals, patterns, texts, sinks, maxM, maxN, temp, temp_bytes, stream); }
+
+static int batch_banded_score_impl(nvb_ctx* ctx, nvb_aligner a, const nvb_quality_scheme* qs, const uint8_t* quals, uint32_t band, nvb_string_set patterns,
                                       nvb_string_set texts, nvb_best_sink* sinks, uint32_t maxM, uint32_t maxN,
                                       void* temp, size_t temp_bytes, void* stream)
 {
@@ -209,6 +244,9 @@ extern "C" int nvb_batch_banded_score(nvb_ctx* ctx, nvb_aligner a, uint32_t band
     if (!sinks) return NVB_ERR_ARG;
     cudaStream_t s = (cudaStream_t)stream;
     StrSet P = make_set(patterns), T = make_set(texts);
+    QualDev qdev; const QualDev* qd = nullptr;
+    if ((rc = quality_tables(ctx, a, qs, quals, s, &qdev, &qd))) return rc;
+    if (qd) { ctx->last_paths = 2u; return dpg_banded_score(ctx, a, band, P, T, nullptr, nullptr, 0, n, sinks, s, Sink2{nullptr, 0}, qd); }
     if ((rc = unpack_for_fast_path(ctx, P, T, maxM, maxN, s, [&](const StrSet& p8, const StrSet& t8)
              { return (ctx->force_generic == 0 && dpb2_score_supported(a, band, p8, t8, maxM, maxN)) || dpf_banded_score_supported(a, band, p8, t8, maxM, maxN); }))) return rc;
     ctx->last_paths = 0;
@@ -226,6 +264,16 @@ extern "C" int nvb_batch_banded_score(nvb_ctx* ctx, nvb_aligner a, uint32_t band
     ctx->last_paths |= 2u;
     return dpg_banded_score(ctx, a, band, P, T, nullptr, nullptr, 0, n, sinks, s);
 }
+
+extern "C" int nvb_batch_banded_score(nvb_ctx* ctx, nvb_aligner a, uint32_t band, nvb_string_set patterns,
+                                      nvb_string_set texts, nvb_best_sink* sinks, uint32_t maxM, uint32_t maxN,
+                                      void* temp, size_t temp_bytes, void* stream)
+{ return batch_banded_score_impl(ctx, a, nullptr, nullptr, band, patterns, texts, sinks, maxM, maxN, temp, temp_bytes, stream); }
+
+extern "C" int nvb_batch_banded_score_q(nvb_ctx* ctx, nvb_aligner a, const nvb_quality_scheme* qs, uint32_t band, nvb_string_set patterns,
+                                        const uint8_t* quals, nvb_string_set texts, nvb_best_sink* sinks, uint32_t maxM, uint32_t maxN,
+                                        void* temp, size_t temp_bytes, void* stream)
+{ if (!qs) return NVB_ERR_ARG; return batch_banded_score_impl(ctx, a, qs, quals, band, patterns, texts, sinks, maxM, maxN, temp, temp_bytes, stream); }
 
 // aln::Best2Sink<int32>(distinct_dist) in place of BestSink (sink.h:99-123, sink_inl.h:54-82); band 0 = full matrix.
 // The sequential "else if" of Best2Sink::report is order-dependent, so this runs on the int32 one-pair-per-thread
@@ -258,7 +306,7 @@ extern "C" int nvb_batch_score_best2(nvb_ctx* ctx, nvb_aligner a, uint32_t band,
     return NVB_OK;
 }
 
-extern "C" int nvb_batch_traceback(nvb_ctx* ctx, nvb_aligner a, uint32_t chk, nvb_string_set patterns,
+static int batch_traceback_impl(nvb_ctx* ctx, nvb_aligner a, const nvb_quality_scheme* qs, const uint8_t* quals, uint32_t chk, nvb_string_set patterns,
                                    nvb_string_set texts, nvb_alignment* out, uint8_t* ops, uint32_t ops_stride,
                                    uint32_t* n_ops, uint32_t maxM, uint32_t maxN, void* temp, size_t temp_bytes, void* stream)
 {
@@ -271,6 +319,8 @@ extern "C" int nvb_batch_traceback(nvb_ctx* ctx, nvb_aligner a, uint32_t chk, nv
     if (!out || !ops || !n_ops || !temp) return NVB_ERR_ARG;
     cudaStream_t s = (cudaStream_t)stream;
     const StrSet P = make_set(patterns), T = make_set(texts);
+    QualDev qdev; const QualDev* qd = nullptr;
+    if ((rc = quality_tables(ctx, a, qs, quals, s, &qdev, &qd))) return rc;
     const TempPlan p = plan(NVB_OP_TRACEBACK, a, 0, chk, maxM, maxN);
     const uint32_t bp = batch_pairs(p, temp_bytes, n);
     if (bp == 0) return NVB_ERR_TEMP;
@@ -281,12 +331,22 @@ extern "C" int nvb_batch_traceback(nvb_ctx* ctx, nvb_aligner a, uint32_t chk, nv
         const uint32_t cnt = n - first < bp ? n - first : bp;
         int16_t* t16 = (int16_t*)temp;
         uint8_t* flow = (uint8_t*)temp + p.i16_per_pair * 2 * (size_t)bp128;
-        if ((rc = dpg_full_traceback(ctx, a, P, T, first, cnt, chk, out, ops, ops_stride, n_ops, t16, flow, maxM, maxN, s))) return rc;
+        if ((rc = dpg_full_traceback(ctx, a, P, T, first, cnt, chk, out, ops, ops_stride, n_ops, t16, flow, maxM, maxN, s, qd))) return rc;
     }
     return NVB_OK;
 }
 
-extern "C" int nvb_batch_banded_traceback(nvb_ctx* ctx, nvb_aligner a, uint32_t band, uint32_t chk,
+extern "C" int nvb_batch_traceback(nvb_ctx* ctx, nvb_aligner a, uint32_t chk, nvb_string_set patterns,
+                                   nvb_string_set texts, nvb_alignment* out, uint8_t* ops, uint32_t ops_stride,
+                                   uint32_t* n_ops, uint32_t maxM, uint32_t maxN, void* temp, size_t temp_bytes, void* stream)
+{ return batch_traceback_impl(ctx, a, nullptr, nullptr, chk, patterns, texts, out, ops, ops_stride, n_ops, maxM, maxN, temp, temp_bytes, stream); }
+
+extern "C" int nvb_batch_traceback_q(nvb_ctx* ctx, nvb_aligner a, const nvb_quality_scheme* qs, uint32_t chk, nvb_string_set patterns,
+                                     const uint8_t* quals, nvb_string_set texts, nvb_alignment* out, uint8_t* ops, uint32_t ops_stride,
+                                     uint32_t* n_ops, uint32_t maxM, uint32_t maxN, void* temp, size_t temp_bytes, void* stream)
+{ if (!qs) return NVB_ERR_ARG; return batch_traceback_impl(ctx, a, qs, quals, chk, patterns, texts, out, ops, ops_stride, n_ops, maxM, maxN, temp, temp_bytes, stream); }
+
+static int batch_banded_traceback_impl(nvb_ctx* ctx, nvb_aligner a, const nvb_quality_scheme* qs, const uint8_t* quals, uint32_t band, uint32_t chk,
                                           nvb_string_set patterns, nvb_string_set texts, nvb_alignment* out,
                                           uint8_t* ops, uint32_t ops_stride, uint32_t* n_ops, uint32_t maxM,
                                           uint32_t maxN, void* temp, size_t temp_bytes, void* stream)
@@ -300,15 +360,17 @@ extern "C" int nvb_batch_banded_traceback(nvb_ctx* ctx, nvb_aligner a, uint32_t 
     if (!out || !ops || !n_ops || !temp) return NVB_ERR_ARG;
     cudaStream_t s = (cudaStream_t)stream;
     StrSet P = make_set(patterns), T = make_set(texts);
+    QualDev qdev; const QualDev* qd = nullptr;
+    if ((rc = quality_tables(ctx, a, qs, quals, s, &qdev, &qd))) return rc;
     if ((rc = unpack_for_fast_path(ctx, P, T, maxM, maxN, s, [&](const StrSet& p8, const StrSet& t8)
-             { return ctx->force_generic == 0 && dpb2_traceback_supported(a, band, p8, t8, maxM); }))) return rc;
+             { return !qd && ctx->force_generic == 0 && dpb2_traceback_supported(a, band, p8, t8, maxM); }))) return rc;
     const TempPlan p = plan(NVB_OP_BANDED_TRACEBACK, a, band, chk, maxM, maxN);
     const uint32_t bp = batch_pairs(p, temp_bytes, n);
     if (bp == 0) return NVB_ERR_TEMP;
     const uint32_t bp128 = (bp + 127u) & ~127u;
     ctx->last_paths = 0;
     const uint32_t* list = nullptr; const uint32_t* d_count = nullptr;
-    if (ctx->force_generic == 0 && dpb2_traceback_supported(a, band, P, T, maxM))
+    if (!qd && ctx->force_generic == 0 && dpb2_traceback_supported(a, band, P, T, maxM))
     {
         // one tagged forward pass + a walk per pair; the flow of a launch lives in temp ([row][couple]).
         // Pairs the packed kernel cannot represent (a symbol > 3, ...) are re-done below by the int32 kernel.
@@ -337,10 +399,22 @@ extern "C" int nvb_batch_banded_traceback(nvb_ctx* ctx, nvb_aligner a, uint32_t 
         const uint32_t cnt = n - first < bp ? n - first : bp;
         int16_t* t16 = (int16_t*)temp;
         uint8_t* flow = (uint8_t*)temp + p.i16_per_pair * 2 * (size_t)bp128;
-        if ((rc = dpg_banded_traceback(ctx, a, band, P, T, list, d_count, first, cnt, chk, out, ops, ops_stride, n_ops, t16, flow, maxM, s))) return rc;
+        if ((rc = dpg_banded_traceback(ctx, a, band, P, T, list, d_count, first, cnt, chk, out, ops, ops_stride, n_ops, t16, flow, maxM, s, qd))) return rc;
     }
     return NVB_OK;
 }
+
+extern "C" int nvb_batch_banded_traceback(nvb_ctx* ctx, nvb_aligner a, uint32_t band, uint32_t chk,
+                                          nvb_string_set patterns, nvb_string_set texts, nvb_alignment* out,
+                                          uint8_t* ops, uint32_t ops_stride, uint32_t* n_ops, uint32_t maxM,
+                                          uint32_t maxN, void* temp, size_t temp_bytes, void* stream)
+{ return batch_banded_traceback_impl(ctx, a, nullptr, nullptr, band, chk, patterns, texts, out, ops, ops_stride, n_ops, maxM, maxN, temp, temp_bytes, stream); }
+
+extern "C" int nvb_batch_banded_traceback_q(nvb_ctx* ctx, nvb_aligner a, const nvb_quality_scheme* qs, uint32_t band, uint32_t chk,
+                                            nvb_string_set patterns, const uint8_t* quals, nvb_string_set texts, nvb_alignment* out,
+                                            uint8_t* ops, uint32_t ops_stride, uint32_t* n_ops, uint32_t maxM,
+                                            uint32_t maxN, void* temp, size_t temp_bytes, void* stream)
+{ if (!qs) return NVB_ERR_ARG; return batch_banded_traceback_impl(ctx, a, qs, quals, band, chk, patterns, texts, out, ops, ops_stride, n_ops, maxM, maxN, temp, temp_bytes, stream); }
 
 // ---------------------------------------------------------------------------------------------
 // push-order ops -> forward run-length CIGAR (io::Cigar, nvbio/io/alignments.h:48-65)

@@ -7,13 +7,25 @@ enum { OP_SUB = 0, OP_INS = 1, OP_DEL = 2, OP_SINK = 3, OP_INS_EXT = 4, OP_DEL_E
 enum { ST_H = 0, ST_E = 1, ST_F = 2 };                                                      // alignment.h:341-346
 
 // SW/ED: ga = deletion (consumes text), gb = insertion (consumes pattern); Gotoh: ga = open, gb = ext
-struct Scheme { int32_t match, mismatch, ga, gb; };
+// Quality-aware schemes (alignment.h:411-436, 488-505): qm/qx = match(q) / mismatch(a, b, q) tables in device memory (NULL: the
+// constants), quals = one byte per pattern symbol addressed by the patterns' offsets (NULL: all 0); tga/tgb = Gotoh's
+// text_gap_open/extension, which the reference uses only for GLOBAL first columns / band rows and the banded infimum.
+struct Scheme { int32_t match, mismatch, ga, gb; int32_t tga, tgb; const int32_t* qm; const int32_t* qx; const uint8_t* quals; };
+struct QualDev { const int32_t* qm; const int32_t* qx; const uint8_t* quals; int32_t tga, tgb; };
 
+static inline Scheme make_scheme(const nvb_aligner& a);
+static inline Scheme make_scheme_q(const nvb_aligner& a, const QualDev* q)
+{
+    Scheme s = make_scheme(a);
+    if (q && a.kind != NVB_EDIT_DISTANCE) { s.qm = q->qm; s.qx = q->qx; s.quals = q->quals; if (a.kind == NVB_GOTOH) { s.tga = q->tga; s.tgb = q->tgb; } }
+    return s;
+}
 static inline Scheme make_scheme(const nvb_aligner& a)
 {
     Scheme s;
     if (a.kind == NVB_EDIT_DISTANCE) { s.match = 0; s.mismatch = -1; s.ga = -1; s.gb = -1; }   // ed_utils.h:36-43
     else { s.match = a.match; s.mismatch = a.mismatch; s.ga = a.gap_a; s.gb = a.gap_b; }
+    s.tga = s.ga; s.tgb = s.gb; s.qm = s.qx = nullptr; s.quals = nullptr;
     return s;
 }
 
@@ -42,15 +54,18 @@ struct PairView
 {
     const uint8_t* pat; uint32_t pbits; uint32_t pbeg; uint32_t M;
     const uint8_t* txt; uint32_t tbits; uint32_t tbeg; uint32_t N;
+    const uint8_t* qual;                                   // pattern qualities of this pair (NULL: all 0)
+    __device__ __forceinline__ uint32_t pq(uint32_t j) const { return qual ? (uint32_t)__ldg(qual + j) : 0u; }
     __device__ __forceinline__ uint32_t p(uint32_t j) const { return sym_at_rt(pat, pbits, pbeg + j); }
     __device__ __forceinline__ uint32_t t(uint32_t i) const { return sym_at_rt(txt, tbits, tbeg + i); }
 };
 
-__device__ __forceinline__ PairView make_pair_view(const StrSet& P, const StrSet& T, uint32_t id)
+__device__ __forceinline__ PairView make_pair_view(const StrSet& P, const StrSet& T, uint32_t id, const uint8_t* quals = nullptr)
 {
     PairView v;
     v.pat = P.sym; v.pbits = P.bits; v.pbeg = P.off[id]; v.M = P.off[id + 1] - v.pbeg;
     v.txt = T.sym; v.tbits = T.bits; v.tbeg = T.off[id]; v.N = T.off[id + 1] - v.tbeg;
+    v.qual = quals ? quals + v.pbeg : nullptr;
     return v;
 }
 #endif

@@ -28,10 +28,10 @@ static int score_t(nvb_ctx* ctx, Scheme sc, uint32_t band, StrSet P, StrSet T, c
 }
 
 int dpg_banded_score(nvb_ctx* ctx, const nvb_aligner& a, uint32_t band, StrSet P, StrSet T, const uint32_t* list,
-                     const uint32_t* d_count, uint32_t first, uint32_t n, nvb_best_sink* sinks, cudaStream_t s, Sink2 s2)
+                     const uint32_t* d_count, uint32_t first, uint32_t n, nvb_best_sink* sinks, cudaStream_t s, Sink2 s2, const QualDev* qd)
 {
     if (n == 0) return NVB_OK;
-    const Scheme sc = make_scheme(a);
+    const Scheme sc = make_scheme_q(a, qd);
     const bool g = a.kind == NVB_GOTOH;
     #define GO(G, TY) return score_t<G, TY>(ctx, sc, band, P, T, list, d_count, first, n, sinks, s, s2)
     switch (a.type)
@@ -74,10 +74,10 @@ static int tb_t(nvb_ctx* ctx, Scheme sc, uint32_t band, StrSet P, StrSet T, cons
 
 int dpg_banded_traceback(nvb_ctx* ctx, const nvb_aligner& a, uint32_t band, StrSet P, StrSet T, const uint32_t* list, const uint32_t* d_count, uint32_t first, uint32_t n,
                          uint32_t chk, nvb_alignment* out, uint8_t* ops, uint32_t ops_stride, uint32_t* n_ops,
-                         int16_t* temp16, uint8_t* flow, uint32_t maxM, cudaStream_t s)
+                         int16_t* temp16, uint8_t* flow, uint32_t maxM, cudaStream_t s, const QualDev* qd)
 {
     if (n == 0) return NVB_OK;
-    const Scheme sc = make_scheme(a);
+    const Scheme sc = make_scheme_q(a, qd);
     const bool g = a.kind == NVB_GOTOH;
     #define GO(G, TY) return tb_t<G, TY>(ctx, sc, band, P, T, list, d_count, first, n, chk, out, ops, ops_stride, n_ops, temp16, flow, maxM, s)
     switch (a.type)

@@ -41,8 +41,9 @@ struct BandDP
         int32_t H[WA], F[WA];
         const bool packed_cache = !(Wd == 3 || Wd == 5 || Wd == 7 || Wd == 15);   // alignment_base_inl.h:66-90
         const int32_t G = s.ga, I = s.gb;
-        const int32_t gmax = s.ga > s.gb ? s.ga : s.gb;
-        const int32_t inf = GOTOH ? -32768 - gmax : -32768 + gmax;               // gotoh_banded_inl.h:437-439
+        int32_t gmax = s.ga > s.gb ? s.ga : s.gb;
+        if (GOTOH) gmax = max(gmax, max(s.tga, s.tgb));                          // the text gaps count too: gotoh_banded_inl.h:437-439
+        const int32_t inf = GOTOH ? -32768 - gmax : -32768 + gmax;
 
         if (from_chk)
         {
@@ -59,7 +60,7 @@ struct BandDP
             for (uint32_t j = 0; j < (uint32_t)WA; ++j) if (j < Wd)
             {
                 if (!GOTOH) H[j] = (TYPE == T_GLOBAL) ? (int32_t)j * s.ga : 0;                         // sw_banded_inl.h:35-45
-                else H[j] = (TYPE == T_GLOBAL && j > 0) ? s.ga + (int32_t)(j - 1) * s.gb : 0;          // gotoh_banded_inl.h:37-68
+                else H[j] = (TYPE == T_GLOBAL && j > 0) ? s.tga + (int32_t)(j - 1) * s.tgb : 0;        // text gaps: gotoh_banded_inl.h:37-68
                 F[j] = inf;
             }
         }
@@ -76,13 +77,15 @@ struct BandDP
                 }
             }
             const uint32_t q = v.p(i);
+            // match(qq) / mismatch(g, q, qq) at this pattern row's quality (sw_banded_inl.h:391, gotoh_banded_inl.h:461)
+            const int32_t s_match = s.qm ? __ldg(s.qm + v.pq(i)) : s.match, s_mis = s.qx ? __ldg(s.qx + v.pq(i)) : s.mismatch;
             int32_t E = 0; uint32_t edir = 0;
             #pragma unroll UN
             for (uint32_t j = 0; j < (uint32_t)WA; ++j) if (j < Wd)
             {
                 uint32_t g = text_at(i + j);
                 if (packed_cache && j < Wd - 1) g &= 3u;
-                const int32_t S = (g == q) ? s.match : s.mismatch;
+                const int32_t S = (g == q) ? s_match : s_mis;
                 const int32_t dg = H[j] + S;
                 int32_t hi; uint32_t dir, cell;
                 if (!GOTOH)
@@ -244,7 +247,7 @@ dpg_banded_score_kernel(Scheme s, uint32_t W, StrSet P, StrSet T, const uint32_t
     if (d_count && first + lp >= *d_count) return;
     const uint32_t id = list ? list[first + lp] : first + lp;
     BandDP<GOTOH, TYPE, WT> dp;
-    dp.s = s; dp.v = make_pair_view(P, T, id); dp.Wrt = W; dp.cs = 1;
+    dp.s = s; dp.v = make_pair_view(P, T, id, s.quals); dp.Wrt = W; dp.cs = 1;
     dp.chkH = dp.chkF = nullptr; dp.flow = nullptr; dp.CHK = 1u << 30;
     Best b; b.init(); dp.best = &b;
     if (s2.out) { b.two = true; b.dd = s2.distinct; }
@@ -267,7 +270,7 @@ dpg_banded_traceback_kernel(Scheme s, uint32_t W, StrSet P, StrSet T, const uint
     const uint32_t id = list ? list[first + lp] : first + lp;
     const uint32_t nrows = 2u + (maxM + CHK - 1) / CHK;
     BandDP<GOTOH, TYPE, WT> dp;
-    dp.s = s; dp.v = make_pair_view(P, T, id); dp.Wrt = W; dp.cs = n;
+    dp.s = s; dp.v = make_pair_view(P, T, id, s.quals); dp.Wrt = W; dp.cs = n;
     dp.chkH = temp16 + lp;
     dp.chkF = temp16 + (size_t)nrows * W * n + lp;
     dp.flow = flow + lp; dp.CHK = CHK; dp.best = nullptr;

@@ -6,17 +6,19 @@ template <bool GOTOH, int TYPE>
 static int score_t(nvb_ctx* ctx, Scheme sc, StrSet P, StrSet T, const uint32_t* list, const uint32_t* d_count, uint32_t first, uint32_t n,
                    nvb_best_sink* sinks, int16_t* temp, uint32_t maxN, cudaStream_t s, Sink2 s2)
 {
-    dpg_full_score_kernel<GOTOH, TYPE><<<(n + DPG_THREADS - 1) / DPG_THREADS, DPG_THREADS, 0, s>>>(
+    if (sc.qm) dpg_full_score_kernel<GOTOH, TYPE, true><<<(n + DPG_THREADS - 1) / DPG_THREADS, DPG_THREADS, 0, s>>>(
+        sc, P, T, list, d_count, first, n, sinks, temp, maxN, s2);
+    else dpg_full_score_kernel<GOTOH, TYPE, false><<<(n + DPG_THREADS - 1) / DPG_THREADS, DPG_THREADS, 0, s>>>(
         sc, P, T, list, d_count, first, n, sinks, temp, maxN, s2);
     NVB_LAUNCHED(ctx);
     return NVB_OK;
 }
 
 int dpg_full_score(nvb_ctx* ctx, const nvb_aligner& a, StrSet P, StrSet T, const uint32_t* list, const uint32_t* d_count, uint32_t first,
-                   uint32_t n, nvb_best_sink* sinks, int16_t* temp, uint32_t maxN, cudaStream_t s, Sink2 s2)
+                   uint32_t n, nvb_best_sink* sinks, int16_t* temp, uint32_t maxN, cudaStream_t s, Sink2 s2, const QualDev* qd)
 {
     if (n == 0) return NVB_OK;
-    const Scheme sc = make_scheme(a);
+    const Scheme sc = make_scheme_q(a, qd);
     const bool g = a.kind == NVB_GOTOH;
     #define GO(G, TY) return score_t<G, TY>(ctx, sc, P, T, list, d_count, first, n, sinks, temp, maxN, s, s2)
     switch (a.type)
@@ -34,7 +36,9 @@ static int tb_t(nvb_ctx* ctx, Scheme sc, StrSet P, StrSet T, uint32_t first, uin
                 nvb_alignment* out, uint8_t* ops, uint32_t ops_stride, uint32_t* n_ops, int16_t* temp16,
                 uint8_t* flow, uint32_t maxM, uint32_t maxN, cudaStream_t s)
 {
-    dpg_full_traceback_kernel<GOTOH, TYPE><<<(n + DPG_THREADS - 1) / DPG_THREADS, DPG_THREADS, 0, s>>>(
+    if (sc.qm) dpg_full_traceback_kernel<GOTOH, TYPE, true><<<(n + DPG_THREADS - 1) / DPG_THREADS, DPG_THREADS, 0, s>>>(
+        sc, P, T, first, n, chk, out, ops, ops_stride, n_ops, temp16, flow, maxM, maxN);
+    else dpg_full_traceback_kernel<GOTOH, TYPE, false><<<(n + DPG_THREADS - 1) / DPG_THREADS, DPG_THREADS, 0, s>>>(
         sc, P, T, first, n, chk, out, ops, ops_stride, n_ops, temp16, flow, maxM, maxN);
     NVB_LAUNCHED(ctx);
     return NVB_OK;
@@ -42,10 +46,10 @@ static int tb_t(nvb_ctx* ctx, Scheme sc, StrSet P, StrSet T, uint32_t first, uin
 
 int dpg_full_traceback(nvb_ctx* ctx, const nvb_aligner& a, StrSet P, StrSet T, uint32_t first, uint32_t n, uint32_t chk,
                        nvb_alignment* out, uint8_t* ops, uint32_t ops_stride, uint32_t* n_ops, int16_t* temp16,
-                       uint8_t* flow, uint32_t maxM, uint32_t maxN, cudaStream_t s)
+                       uint8_t* flow, uint32_t maxM, uint32_t maxN, cudaStream_t s, const QualDev* qd)
 {
     if (n == 0) return NVB_OK;
-    const Scheme sc = make_scheme(a);
+    const Scheme sc = make_scheme_q(a, qd);
     const bool g = a.kind == NVB_GOTOH;
     #define GO(G, TY) return tb_t<G, TY>(ctx, sc, P, T, first, n, chk, out, ops, ops_stride, n_ops, temp16, flow, maxM, maxN, s)
     switch (a.type)

@@ -10,7 +10,7 @@
 #pragma once
 #include "dp_common.cuh"
 
-template <bool GOTOH, int TYPE>
+template <bool GOTOH, int TYPE, bool QUAL = false>
 struct FullDP
 {
     static const int BL = GOTOH ? 8 : 16;
@@ -36,6 +36,7 @@ struct FullDP
         const int32_t inf = infimum();
         int32_t H[BL + 1], F[BL + 1];
         uint32_t q[BL + 1];
+        int32_t sm[QUAL ? BL + 1 : 1], sx[QUAL ? BL + 1 : 1];       // match(qq) / mismatch(r, q, qq) of the stripe's columns (sw_inl.h:470-472)
 
         if (save_chk && (block % CHK) == 0)
         {
@@ -54,6 +55,11 @@ struct FullDP
             else H[j] = (block + j > 0) ? s.ga + s.gb * (int32_t)(block + j - 1u) : 0;             // gotoh_inl.h:675
             F[j] = inf;
             q[j] = (j >= 1 && (uint32_t)j <= ncols) ? v.p(block + j - 1) : 0x100u;
+            if (QUAL)
+            {
+                const uint32_t qq = (j >= 1 && (uint32_t)j <= ncols) ? v.pq(block + j - 1) : 0u;
+                sm[j] = __ldg(s.qm + qq); sx[j] = __ldg(s.qx + qq);
+            }
         }
         int32_t carry = H[0];
         int32_t hlast = 0;
@@ -78,7 +84,7 @@ struct FullDP
             {
                 if ((uint32_t)j <= ncols)
                 {
-                    const int32_t S = (r == q[j]) ? s.match : s.mismatch;
+                    const int32_t S = QUAL ? ((r == q[j]) ? sm[j] : sx[j]) : ((r == q[j]) ? s.match : s.mismatch);
                     int32_t hi; uint32_t dir;
                     if (!GOTOH)
                     {
@@ -140,7 +146,7 @@ struct FullDP
                 if (!GOTOH) colH[i * cs] = (int16_t)(TYPE == T_GLOBAL ? s.ga * (int32_t)(i + 1) : 0);   // sw_inl.h:68-70
                 else
                 {
-                    colH[i * cs] = (int16_t)(TYPE == T_GLOBAL ? s.ga + s.gb * (int32_t)i : 0);        // gotoh_inl.h:68-71
+                    colH[i * cs] = (int16_t)(TYPE == T_GLOBAL ? s.tga + s.tgb * (int32_t)i : 0);      // text gaps: gotoh_inl.h:68-71
                     colE[i * cs] = (int16_t)(TYPE == T_LOCAL ? 0 : inf);
                 }
             }
@@ -238,7 +244,7 @@ struct FullDP
 #define DPG_THREADS 128
 
 // scoring: scratch = colH[,colE], strided by the pairs of the launch
-template <bool GOTOH, int TYPE>
+template <bool GOTOH, int TYPE, bool QUAL>
 __global__ void __launch_bounds__(DPG_THREADS)
 dpg_full_score_kernel(Scheme s, StrSet P, StrSet T, const uint32_t* __restrict__ list, const uint32_t* __restrict__ d_count, uint32_t first,
                       uint32_t n, nvb_best_sink* __restrict__ sinks, int16_t* __restrict__ temp, uint32_t maxN, Sink2 s2)
@@ -247,8 +253,8 @@ dpg_full_score_kernel(Scheme s, StrSet P, StrSet T, const uint32_t* __restrict__
     if (lp >= n) return;
     if (d_count && first + lp >= *d_count) return;
     const uint32_t id = list ? list[first + lp] : first + lp;
-    FullDP<GOTOH, TYPE> dp;
-    dp.s = s; dp.v = make_pair_view(P, T, id);
+    FullDP<GOTOH, TYPE, QUAL> dp;
+    dp.s = s; dp.v = make_pair_view(P, T, id, s.quals);
     dp.cs = n;
     dp.colH = temp + lp;
     dp.colE = temp + (size_t)maxN * n + lp;
@@ -261,7 +267,7 @@ dpg_full_score_kernel(Scheme s, StrSet P, StrSet T, const uint32_t* __restrict__
 }
 
 // traceback: scratch per pair = 2 columns + 2*nchk*N checkpoints (int16) + N*CHK flow bytes
-template <bool GOTOH, int TYPE>
+template <bool GOTOH, int TYPE, bool QUAL>
 __global__ void __launch_bounds__(DPG_THREADS)
 dpg_full_traceback_kernel(Scheme s, StrSet P, StrSet T, uint32_t first, uint32_t n, uint32_t CHK,
                           nvb_alignment* __restrict__ out, uint8_t* __restrict__ ops, uint32_t ops_stride,
@@ -272,8 +278,8 @@ dpg_full_traceback_kernel(Scheme s, StrSet P, StrSet T, uint32_t first, uint32_t
     if (lp >= n) return;
     const uint32_t id = first + lp;
     const uint32_t nchk = (maxM + CHK - 1) / CHK + 1;
-    FullDP<GOTOH, TYPE> dp;
-    dp.s = s; dp.v = make_pair_view(P, T, id);
+    FullDP<GOTOH, TYPE, QUAL> dp;
+    dp.s = s; dp.v = make_pair_view(P, T, id, s.quals);
     dp.cs = n;
     dp.colH = temp16 + lp;
     dp.colE = temp16 + (size_t)maxN * n + lp;

@@ -98,6 +98,24 @@ int ORC(banded_traceback)(orc_aligner a, uint32_t band, uint32_t checkpoints, co
                           uint32_t count, orc_alignment* out, uint8_t* ops, uint32_t ops_stride,
                           uint32_t* n_ops, int threads);
 
+/* Quality-aware scoring schemes (alignment.h:411-436 GotohScoringScheme, :488-505 SmithWatermanScoringScheme; nvBowtie's is
+ * nvBowtie/bowtie2/cuda/scoring.h:206-301): match(q) and mismatch(a, b, q) as 256-entry tables indexed by the quality of the
+ * PATTERN position; the aligner's p2/p3 stay deletion/insertion (SW) or pattern_gap_open/extension (Gotoh); text_gap_* are
+ * what the reference uses to initialise GLOBAL first columns / band rows and the banded infimum. quals = one uint8 per
+ * pattern symbol, addressed by the patterns' offsets (NULL = trivial_quality_string: all 0). */
+typedef struct { const int32_t* match; const int32_t* mismatch; int32_t text_gap_open, text_gap_ext; } orc_qscheme;
+int ORC(score_q)(orc_aligner a, const orc_qscheme* qs, const uint8_t* quals, const uint8_t* pat, const uint32_t* pat_off, const uint8_t* txt,
+                 const uint32_t* txt_off, uint32_t count, orc_sink* sinks, int threads);
+int ORC(banded_score_q)(orc_aligner a, const orc_qscheme* qs, const uint8_t* quals, uint32_t band, const uint8_t* pat, const uint32_t* pat_off,
+                        const uint8_t* txt, const uint32_t* txt_off, uint32_t count, orc_sink* sinks, int threads);
+int ORC(traceback_q)(orc_aligner a, const orc_qscheme* qs, const uint8_t* quals, uint32_t checkpoints, const uint8_t* pat, const uint32_t* pat_off,
+                     const uint8_t* txt, const uint32_t* txt_off, uint32_t count, orc_alignment* out,
+                     uint8_t* ops, uint32_t ops_stride, uint32_t* n_ops, int threads);
+int ORC(banded_traceback_q)(orc_aligner a, const orc_qscheme* qs, const uint8_t* quals, uint32_t band, uint32_t checkpoints, const uint8_t* pat,
+                            const uint32_t* pat_off, const uint8_t* txt, const uint32_t* txt_off,
+                            uint32_t count, orc_alignment* out, uint8_t* ops, uint32_t ops_stride,
+                            uint32_t* n_ops, int threads);
+
 /* aln::Best2Sink<int32> (sink.h:99-123): best and runner-up whose text end is more than distinct_dist away */
 typedef struct { int32_t score1, score2; uint32_t x1, y1, x2, y2; } orc_sink2;
 /* scoring into a Best2Sink; band 0 = full matrix */

@@ -33,7 +33,11 @@ enum { K_ED = 0, K_SW = 1, K_GOTOH = 2 };
 enum { OP_SUB = 0, OP_INS = 1, OP_DEL = 2, OP_SINK = 3, OP_INS_EXT = 4, OP_DEL_EXT = 8 };
 enum { ST_H = 0, ST_E = 1, ST_F = 2 };
 
-typedef struct { int gotoh, type, match, mismatch, ga, gb; } scheme_t;
+typedef struct { int gotoh, type, match, mismatch, ga, gb;
+                 int tga, tgb;                  /* Gotoh: text_gap_open / text_gap_extension, used ONLY to initialise the first text column (full) /
+                                                   band row (banded) of GLOBAL alignments and in the banded infimum (gotoh_inl.h:69-70, gotoh_banded_inl.h:48,437-439) */
+                 const int32_t* qm; const int32_t* qx; /* quality-aware schemes: match(q) / mismatch(a,b,q) tables (alignment.h:411-436,488-505), NULL = constants */
+               } scheme_t;
 /* SW/ED: ga = deletion (vertical move, consumes text), gb = insertion (consumes pattern)
  * Gotoh: ga = gap open, gb = gap extension */
 
@@ -44,8 +48,23 @@ static scheme_t make_scheme(orc_aligner a)
     s.type = a.type;
     if (a.kind == K_ED) { s.match = 0; s.mismatch = -1; s.ga = -1; s.gb = -1; } /* ed_utils.h:36-43 */
     else { s.match = a.p0; s.mismatch = a.p1; s.ga = a.p2; s.gb = a.p3; }
+    s.tga = s.ga; s.tgb = s.gb; s.qm = s.qx = NULL;
     return s;
 }
+
+static scheme_t make_scheme_q(orc_aligner a, const orc_qscheme* q)
+{
+    scheme_t s = make_scheme(a);
+    if (q && a.kind != K_ED)
+    {
+        s.qm = q->match; s.qx = q->mismatch;
+        if (s.gotoh) { s.tga = q->text_gap_open; s.tgb = q->text_gap_ext; }
+    }
+    return s;
+}
+/* substitution score at pattern quality qq: scoring.match(qq) / scoring.mismatch(r, q, qq) (sw_inl.h:470-472, gotoh_inl.h:506-508) */
+static inline int32_t subst(const scheme_t* s, int equal, uint8_t qq)
+{ return equal ? (s->qm ? s->qm[qq] : s->match) : (s->qx ? s->qx[qq] : s->mismatch); }
 
 /* BestSink and, when `two` is set, Best2Sink (sink_inl.h:54-82): the runner-up must end more than `dd` text
  * positions away from the current best */
@@ -70,6 +89,7 @@ static inline void push(tracer_t* t, uint8_t op) { if (t->n < t->cap) t->ops[t->
 typedef struct {
     scheme_t       s;
     const uint8_t* pat; uint32_t M;
+    const uint8_t* qual;   /* pattern qualities (NULL = all 0: trivial_quality_string) */
     const uint8_t* txt; uint32_t N;
     int16_t*       colH;   /* stripe boundary column (H) : N cells                       */
     int16_t*       colE;   /* Gotoh only: E of the boundary column                        */
@@ -120,7 +140,7 @@ static void full_stripe(full_t* f, uint32_t block, uint32_t ncols, int last, int
         for (uint32_t j = 1; j <= ncols; ++j)
         {
             const uint8_t q = f->pat[block + j - 1];
-            const int32_t S = (r == q) ? s->match : s->mismatch;
+            const int32_t S = subst(s, r == q, f->qual ? f->qual[block + j - 1] : 0);
             int32_t hi; uint8_t dir;
             if (!s->gotoh)
             {
@@ -190,7 +210,7 @@ static void full_sweep(full_t* f, uint32_t wb, uint32_t we, int init, int save_c
             if (!s->gotoh) f->colH[i] = (int16_t)(s->type == T_GLOBAL ? s->ga * (int32_t)(i + 1) : 0);
             else
             {
-                f->colH[i] = (int16_t)(s->type == T_GLOBAL ? s->ga + s->gb * (int32_t)i : 0);
+                f->colH[i] = (int16_t)(s->type == T_GLOBAL ? s->tga + s->tgb * (int32_t)i : 0);
                 f->colE[i] = (int16_t)(s->type == T_LOCAL ? 0 : infimum);
             }
         }
@@ -291,8 +311,8 @@ static void full_traceback(full_t* f, orc_alignment* res, tracer_t* out)
     res->src_x = sx; res->src_y = sy;
 }
 
-int orc_score(orc_aligner a, const uint8_t* pat, const uint32_t* pat_off, const uint8_t* txt,
-              const uint32_t* txt_off, uint32_t count, orc_sink* sinks, int threads)
+int orc_score_q(orc_aligner a, const orc_qscheme* qs, const uint8_t* quals, const uint8_t* pat, const uint32_t* pat_off, const uint8_t* txt,
+                const uint32_t* txt_off, uint32_t count, orc_sink* sinks, int threads)
 {
     if (threads <= 0) threads = omp_get_max_threads();
     #pragma omp parallel num_threads(threads)
@@ -302,7 +322,8 @@ int orc_score(orc_aligner a, const uint8_t* pat, const uint32_t* pat_off, const 
         for (int64_t p = 0; p < (int64_t)count; ++p)
         {
             full_t f; memset(&f, 0, sizeof(f));
-            f.s = make_scheme(a);
+            f.s = make_scheme_q(a, qs);
+            f.qual = quals ? quals + pat_off[p] : NULL;
             f.pat = pat + pat_off[p]; f.M = pat_off[p + 1] - pat_off[p];
             f.txt = txt + txt_off[p]; f.N = txt_off[p + 1] - txt_off[p];
             if (cap < (size_t)f.N + 1) { cap = (size_t)f.N + 1; free(col); col = (int16_t*)malloc(cap * 2 * sizeof(int16_t)); }
@@ -316,9 +337,13 @@ int orc_score(orc_aligner a, const uint8_t* pat, const uint32_t* pat_off, const 
     return 0;
 }
 
-int orc_traceback(orc_aligner a, uint32_t checkpoints, const uint8_t* pat, const uint32_t* pat_off,
-                  const uint8_t* txt, const uint32_t* txt_off, uint32_t count, orc_alignment* out,
-                  uint8_t* ops, uint32_t ops_stride, uint32_t* n_ops, int threads)
+int orc_score(orc_aligner a, const uint8_t* pat, const uint32_t* pat_off, const uint8_t* txt,
+              const uint32_t* txt_off, uint32_t count, orc_sink* sinks, int threads)
+{ return orc_score_q(a, NULL, NULL, pat, pat_off, txt, txt_off, count, sinks, threads); }
+
+int orc_traceback_q(orc_aligner a, const orc_qscheme* qs, const uint8_t* quals, uint32_t checkpoints, const uint8_t* pat, const uint32_t* pat_off,
+                    const uint8_t* txt, const uint32_t* txt_off, uint32_t count, orc_alignment* out,
+                    uint8_t* ops, uint32_t ops_stride, uint32_t* n_ops, int threads)
 {
     if (checkpoints == 0 || (checkpoints & 15u)) return -2;
     if (threads <= 0) threads = omp_get_max_threads();
@@ -326,7 +351,8 @@ int orc_traceback(orc_aligner a, uint32_t checkpoints, const uint8_t* pat, const
     for (int64_t p = 0; p < (int64_t)count; ++p)
     {
         full_t f; memset(&f, 0, sizeof(f));
-        f.s = make_scheme(a);
+        f.s = make_scheme_q(a, qs);
+        f.qual = quals ? quals + pat_off[p] : NULL;
         f.pat = pat + pat_off[p]; f.M = pat_off[p + 1] - pat_off[p];
         f.txt = txt + txt_off[p]; f.N = txt_off[p + 1] - txt_off[p];
         f.CHK = checkpoints;
@@ -342,6 +368,11 @@ int orc_traceback(orc_aligner a, uint32_t checkpoints, const uint8_t* pat, const
     return 0;
 }
 
+int orc_traceback(orc_aligner a, uint32_t checkpoints, const uint8_t* pat, const uint32_t* pat_off,
+                  const uint8_t* txt, const uint32_t* txt_off, uint32_t count, orc_alignment* out,
+                  uint8_t* ops, uint32_t ops_stride, uint32_t* n_ops, int threads)
+{ return orc_traceback_q(a, NULL, NULL, checkpoints, pat, pat_off, txt, txt_off, count, out, ops, ops_stride, n_ops, threads); }
+
 /* ========================================================================================== */
 /*  BANDED                                                                                    */
 /* ========================================================================================== */
@@ -350,6 +381,7 @@ typedef struct {
     scheme_t       s;
     uint32_t       W;      /* band length */
     const uint8_t* pat; uint32_t M;
+    const uint8_t* qual;   /* pattern qualities (NULL = all 0) */
     const uint8_t* txt; uint32_t N;
     best_t*        best;   /* NULL = null sink */
     int16_t*       chkH;   /* [W*row_id + j], clamped to INT16_MIN+32 */
@@ -376,6 +408,7 @@ static int banded_sweep(band_t* b, uint32_t wb, uint32_t we, int from_chk, int s
      * the move from the previous text position (sw_banded_inl.h:365-366,399,417-418) */
     const int32_t G = s->ga, I = s->gb;
     int32_t gmax = s->ga > s->gb ? s->ga : s->gb;
+    if (s->gotoh) { const int32_t t = s->tga > s->tgb ? s->tga : s->tgb; if (t > gmax) gmax = t; }   /* gotoh_banded_inl.h:437-439 */
     const int32_t infimum = s->gotoh ? INT16_MIN - gmax : INT16_MIN + gmax;
 
     if (from_chk)
@@ -388,7 +421,7 @@ static int banded_sweep(band_t* b, uint32_t wb, uint32_t we, int from_chk, int s
         for (uint32_t j = 0; j < W; ++j)
         {
             if (!s->gotoh) H[j] = (s->type == T_GLOBAL) ? (int32_t)j * s->ga : 0;
-            else H[j] = (s->type == T_GLOBAL && j > 0) ? s->ga + (int32_t)(j - 1) * s->gb : 0;
+            else H[j] = (s->type == T_GLOBAL && j > 0) ? s->tga + (int32_t)(j - 1) * s->tgb : 0;   /* text gaps: gotoh_banded_inl.h:48 */
             F[j] = infimum;
         }
 
@@ -409,7 +442,7 @@ static int banded_sweep(band_t* b, uint32_t wb, uint32_t we, int from_chk, int s
              * symbols are truncated to 2 bits there (N -> A, the 255 past-the-end marker -> T) */
             uint8_t g = text_at(b, i + j);
             if (packed_cache && j < W - 1) g &= 3u;
-            const int32_t S = (g == q) ? s->match : s->mismatch;
+            const int32_t S = subst(s, g == q, b->qual ? b->qual[i] : 0);
             const int32_t dg = H[j] + S;
             int32_t hi; uint8_t dir, cell;
             if (!s->gotoh)
@@ -557,8 +590,8 @@ static void banded_traceback(band_t* b, orc_alignment* res, tracer_t* out)
     res->src_x = sx; res->src_y = sy;
 }
 
-int orc_banded_score(orc_aligner a, uint32_t band, const uint8_t* pat, const uint32_t* pat_off,
-                     const uint8_t* txt, const uint32_t* txt_off, uint32_t count, orc_sink* sinks, int threads)
+int orc_banded_score_q(orc_aligner a, const orc_qscheme* qs, const uint8_t* quals, uint32_t band, const uint8_t* pat, const uint32_t* pat_off,
+                       const uint8_t* txt, const uint32_t* txt_off, uint32_t count, orc_sink* sinks, int threads)
 {
     if (band < 2 || band > MAX_BAND) return -2;
     if (threads <= 0) threads = omp_get_max_threads();
@@ -566,7 +599,8 @@ int orc_banded_score(orc_aligner a, uint32_t band, const uint8_t* pat, const uin
     for (int64_t p = 0; p < (int64_t)count; ++p)
     {
         band_t b; memset(&b, 0, sizeof(b));
-        b.s = make_scheme(a); b.W = band; b.CHK = 1u << 30;
+        b.s = make_scheme_q(a, qs); b.W = band; b.CHK = 1u << 30;
+        b.qual = quals ? quals + pat_off[p] : NULL;
         b.pat = pat + pat_off[p]; b.M = pat_off[p + 1] - pat_off[p];
         b.txt = txt + txt_off[p]; b.N = txt_off[p + 1] - txt_off[p];
         best_t best; best_init(&best); b.best = &best;
@@ -576,10 +610,14 @@ int orc_banded_score(orc_aligner a, uint32_t band, const uint8_t* pat, const uin
     return 0;
 }
 
-int orc_banded_traceback(orc_aligner a, uint32_t band, uint32_t checkpoints, const uint8_t* pat,
-                         const uint32_t* pat_off, const uint8_t* txt, const uint32_t* txt_off,
-                         uint32_t count, orc_alignment* out, uint8_t* ops, uint32_t ops_stride,
-                         uint32_t* n_ops, int threads)
+int orc_banded_score(orc_aligner a, uint32_t band, const uint8_t* pat, const uint32_t* pat_off,
+                     const uint8_t* txt, const uint32_t* txt_off, uint32_t count, orc_sink* sinks, int threads)
+{ return orc_banded_score_q(a, NULL, NULL, band, pat, pat_off, txt, txt_off, count, sinks, threads); }
+
+int orc_banded_traceback_q(orc_aligner a, const orc_qscheme* qs, const uint8_t* quals, uint32_t band, uint32_t checkpoints, const uint8_t* pat,
+                           const uint32_t* pat_off, const uint8_t* txt, const uint32_t* txt_off,
+                           uint32_t count, orc_alignment* out, uint8_t* ops, uint32_t ops_stride,
+                           uint32_t* n_ops, int threads)
 {
     if (band < 2 || band > MAX_BAND || checkpoints == 0) return -2;
     if (threads <= 0) threads = omp_get_max_threads();
@@ -587,7 +625,8 @@ int orc_banded_traceback(orc_aligner a, uint32_t band, uint32_t checkpoints, con
     for (int64_t p = 0; p < (int64_t)count; ++p)
     {
         band_t b; memset(&b, 0, sizeof(b));
-        b.s = make_scheme(a); b.W = band; b.CHK = checkpoints;
+        b.s = make_scheme_q(a, qs); b.W = band; b.CHK = checkpoints;
+        b.qual = quals ? quals + pat_off[p] : NULL;
         b.pat = pat + pat_off[p]; b.M = pat_off[p + 1] - pat_off[p];
         b.txt = txt + txt_off[p]; b.N = txt_off[p + 1] - txt_off[p];
         const size_t nchk = (size_t)band * (2u + (b.M + checkpoints - 1) / checkpoints);
@@ -601,6 +640,12 @@ int orc_banded_traceback(orc_aligner a, uint32_t band, uint32_t checkpoints, con
     }
     return 0;
 }
+
+int orc_banded_traceback(orc_aligner a, uint32_t band, uint32_t checkpoints, const uint8_t* pat,
+                         const uint32_t* pat_off, const uint8_t* txt, const uint32_t* txt_off,
+                         uint32_t count, orc_alignment* out, uint8_t* ops, uint32_t ops_stride,
+                         uint32_t* n_ops, int threads)
+{ return orc_banded_traceback_q(a, NULL, NULL, band, checkpoints, pat, pat_off, txt, txt_off, count, out, ops, ops_stride, n_ops, threads); }
 
 /* ========================================================================================== */
 /*  Best2Sink scoring (sink.h:99-123, sink_inl.h:54-82) over the same sweeps; band 0 = full    */

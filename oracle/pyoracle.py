@@ -29,6 +29,33 @@ class AlignerC(C.Structure):
                 ("p2", C.c_int32), ("p3", C.c_int32)]
 
 
+class QSchemeC(C.Structure):
+    _fields_ = [("match", C.c_void_p), ("mismatch", C.c_void_p), ("text_gap_open", C.c_int32), ("text_gap_ext", C.c_int32)]
+
+
+class QScheme:
+    """quality-aware scheme tables (alignment.h:411-436, 488-505): match(q), mismatch(a, b, q) for q = 0..255 and, for Gotoh, the
+    text gap penalties; the aligner's p2/p3 are deletion/insertion (SW) or pattern_gap_open/extension (Gotoh)"""
+
+    def __init__(self, match, mismatch, text_gap_open=0, text_gap_ext=0):
+        self.match = np.ascontiguousarray(match, dtype=np.int32)
+        self.mismatch = np.ascontiguousarray(mismatch, dtype=np.int32)
+        assert len(self.match) == 256 and len(self.mismatch) == 256
+        self.tgo, self.tge = int(text_gap_open), int(text_gap_ext)
+
+    def c(self):
+        return QSchemeC(self.match.ctypes.data, self.mismatch.ctypes.data, self.tgo, self.tge)
+
+    @staticmethod
+    def bowtie2(match=2, mm_min=2, mm_max=6):
+        """nvBowtie's SmithWatermanScoringScheme<QualCost, ...> (nvBowtie/bowtie2/cuda/scoring.h:73-92,279-281): constant match bonus,
+        mismatch = -(min + int(min(q, 40) / 40 * (max - min)))"""
+        q = np.arange(256)
+        frac = (np.minimum(q, 40) / np.float32(40.0)).astype(np.float32)
+        mmp = mm_min + (frac * np.float32(mm_max - mm_min)).astype(np.int32)
+        return np.full(256, match, np.int32), (-mmp).astype(np.int32)
+
+
 class MapParamsC(C.Structure):
     _fields_ = [("seed_len", C.c_uint32), ("seed_interval", C.c_uint32), ("max_hits", C.c_uint32), ("max_range", C.c_uint32),
                 ("band", C.c_uint32), ("both_strands", C.c_uint32), ("min_score", C.c_int32), ("aligner", AlignerC)]
@@ -188,23 +215,32 @@ class Oracle:
         return (np.ascontiguousarray(pat, dtype=np.uint8), np.ascontiguousarray(pat_off, dtype=np.uint32),
                 np.ascontiguousarray(txt, dtype=np.uint8), np.ascontiguousarray(txt_off, dtype=np.uint32))
 
-    def score(self, a, pat, pat_off, txt, txt_off, threads=0):
+    @staticmethod
+    def _q(qs, quals):
+        """(pointer to the scheme struct or NULL, quality bytes or NULL); the struct is kept alive by the caller's frame"""
+        qc = qs.c() if qs is not None else None
+        qb = np.ascontiguousarray(quals, dtype=np.uint8) if quals is not None else None
+        return qc, (C.byref(qc) if qc is not None else None), qb
+
+    def score(self, a, pat, pat_off, txt, txt_off, threads=0, qs=None, quals=None):
         pat, pat_off, txt, txt_off = self._sets(pat, pat_off, txt, txt_off)
         n = len(pat_off) - 1
         sinks = np.zeros(n, dtype=SINK_DT)
-        rc = self._f("score")(a, _ptr(pat), _ptr(pat_off), _ptr(txt), _ptr(txt_off), C.c_uint32(n), _ptr(sinks), C.c_int(threads))
+        qc, qp, qb = self._q(qs, quals)
+        rc = self._f("score_q")(a, qp, _ptr(qb), _ptr(pat), _ptr(pat_off), _ptr(txt), _ptr(txt_off), C.c_uint32(n), _ptr(sinks), C.c_int(threads))
         assert rc == 0, rc
         return sinks
 
-    def banded_score(self, a, band, pat, pat_off, txt, txt_off, threads=0):
+    def banded_score(self, a, band, pat, pat_off, txt, txt_off, threads=0, qs=None, quals=None):
         pat, pat_off, txt, txt_off = self._sets(pat, pat_off, txt, txt_off)
         n = len(pat_off) - 1
         sinks = np.zeros(n, dtype=SINK_DT)
-        rc = self._f("banded_score")(a, C.c_uint32(band), _ptr(pat), _ptr(pat_off), _ptr(txt), _ptr(txt_off), C.c_uint32(n), _ptr(sinks), C.c_int(threads))
+        qc, qp, qb = self._q(qs, quals)
+        rc = self._f("banded_score_q")(a, qp, _ptr(qb), C.c_uint32(band), _ptr(pat), _ptr(pat_off), _ptr(txt), _ptr(txt_off), C.c_uint32(n), _ptr(sinks), C.c_int(threads))
         assert rc == 0, rc
         return sinks
 
-    def traceback(self, a, chk, pat, pat_off, txt, txt_off, threads=0):
+    def traceback(self, a, chk, pat, pat_off, txt, txt_off, threads=0, qs=None, quals=None):
         pat, pat_off, txt, txt_off = self._sets(pat, pat_off, txt, txt_off)
         n = len(pat_off) - 1
         M = int(np.max(np.diff(pat_off.astype(np.int64)))) if n else 0
@@ -213,12 +249,13 @@ class Oracle:
         out = np.zeros(n, dtype=ALN_DT)
         ops = np.zeros((n, stride), dtype=np.uint8)
         n_ops = np.zeros(n, dtype=np.uint32)
-        rc = self._f("traceback")(a, C.c_uint32(chk), _ptr(pat), _ptr(pat_off), _ptr(txt), _ptr(txt_off), C.c_uint32(n),
+        qc, qp, qb = self._q(qs, quals)
+        rc = self._f("traceback_q")(a, qp, _ptr(qb), C.c_uint32(chk), _ptr(pat), _ptr(pat_off), _ptr(txt), _ptr(txt_off), C.c_uint32(n),
                                   _ptr(out), _ptr(ops), C.c_uint32(stride), _ptr(n_ops), C.c_int(threads))
         assert rc == 0, rc
         return out, ops, n_ops
 
-    def banded_traceback(self, a, band, chk, pat, pat_off, txt, txt_off, threads=0):
+    def banded_traceback(self, a, band, chk, pat, pat_off, txt, txt_off, threads=0, qs=None, quals=None):
         pat, pat_off, txt, txt_off = self._sets(pat, pat_off, txt, txt_off)
         n = len(pat_off) - 1
         M = int(np.max(np.diff(pat_off.astype(np.int64)))) if n else 0
@@ -226,7 +263,8 @@ class Oracle:
         out = np.zeros(n, dtype=ALN_DT)
         ops = np.zeros((n, stride), dtype=np.uint8)
         n_ops = np.zeros(n, dtype=np.uint32)
-        rc = self._f("banded_traceback")(a, C.c_uint32(band), C.c_uint32(chk), _ptr(pat), _ptr(pat_off), _ptr(txt), _ptr(txt_off),
+        qc, qp, qb = self._q(qs, quals)
+        rc = self._f("banded_traceback_q")(a, qp, _ptr(qb), C.c_uint32(band), C.c_uint32(chk), _ptr(pat), _ptr(pat_off), _ptr(txt), _ptr(txt_off),
                                          C.c_uint32(n), _ptr(out), _ptr(ops), C.c_uint32(stride), _ptr(n_ops), C.c_int(threads))
         assert rc == 0, rc
         return out, ops, n_ops

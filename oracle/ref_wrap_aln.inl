@@ -20,8 +20,35 @@ struct RecBacktracer
 
 const int32 MIN_SCORE = Field_traits<int32>::min();
 
-template <typename aligner_type>
-void score_batch(const aligner_type aligner, const uint8_t* pat, const uint32_t* pat_off,
+// pattern qualities of pair i: trivial_quality_string (all 0) or a view of the caller's bytes
+struct NoQuals   { typedef aln::trivial_quality_string type; type get(int64, uint32) const { return type(); } };
+struct ByteQuals { typedef sym_string type; const uint8_t* q; const uint32_t* off; type get(int64 i, uint32 M) const { return sym_string( M, q + off[i] ); } };
+
+// table-driven models of the reference's quality-aware scheme interfaces (alignment.h:411-436, 488-505): what nvBowtie's
+// SmithWatermanScoringScheme (nvBowtie/bowtie2/cuda/scoring.h:279-286) evaluates, with the functors tabulated over q
+struct TableSWScheme
+{
+    const int32* m; const int32* x; int32 del, ins;
+    int32 match(const uint8 q = 0) const { return m[q]; }
+    int32 mismatch(const uint8 q = 0) const { return x[q]; }
+    int32 mismatch(const uint8 a, const uint8 b, const uint8 q = 0) const { return x[q]; }
+    int32 deletion()  const { return del; }
+    int32 insertion() const { return ins; }
+};
+struct TableGotohScheme
+{
+    const int32* m; const int32* x; int32 pgo, pge, tgo, tge;
+    int32 match(const uint8 q = 0) const { return m[q]; }
+    int32 mismatch(const uint8 q = 0) const { return x[q]; }
+    int32 mismatch(const uint8 a, const uint8 b, const uint8 q = 0) const { return x[q]; }
+    int32 pattern_gap_open()      const { return pgo; }
+    int32 pattern_gap_extension() const { return pge; }
+    int32 text_gap_open()         const { return tgo; }
+    int32 text_gap_extension()    const { return tge; }
+};
+
+template <typename aligner_type, typename quals_type>
+void score_batch(const aligner_type aligner, const quals_type quals, const uint8_t* pat, const uint32_t* pat_off,
                  const uint8_t* txt, const uint32_t* txt_off, uint32_t count, orc_sink* sinks, int threads)
 {
     typedef typename aln::column_storage_type<aligner_type>::type cell_type;
@@ -35,15 +62,15 @@ void score_batch(const aligner_type aligner, const uint8_t* pat, const uint32_t*
             const uint32 N = txt_off[i+1] - txt_off[i];
             if (column.size() < N + 1u) column.resize( N + 1u );
             aln::BestSink<int32> sink;
-            aln::alignment_score( aligner, sym_string( M, pat + pat_off[i] ), aln::trivial_quality_string(),
+            aln::alignment_score( aligner, sym_string( M, pat + pat_off[i] ), quals.get( i, M ),
                                   sym_string( N, txt + txt_off[i] ), MIN_SCORE, sink, &column[0] );
             sinks[i].score = sink.score; sinks[i].x = sink.sink.x; sinks[i].y = sink.sink.y;
         }
     }
 }
 
-template <uint32 BAND, typename aligner_type>
-void banded_score_batch(const aligner_type aligner, const uint8_t* pat, const uint32_t* pat_off,
+template <uint32 BAND, typename aligner_type, typename quals_type>
+void banded_score_batch(const aligner_type aligner, const quals_type quals, const uint8_t* pat, const uint32_t* pat_off,
                         const uint8_t* txt, const uint32_t* txt_off, uint32_t count, orc_sink* sinks, int threads)
 {
     #pragma omp parallel for schedule(dynamic,64) num_threads(threads)
@@ -52,7 +79,7 @@ void banded_score_batch(const aligner_type aligner, const uint8_t* pat, const ui
         const uint32 M = pat_off[i+1] - pat_off[i];
         const uint32 N = txt_off[i+1] - txt_off[i];
         aln::BestSink<int32> sink;
-        aln::banded_alignment_score<BAND>( aligner, sym_string( M, pat + pat_off[i] ), aln::trivial_quality_string(),
+        aln::banded_alignment_score<BAND>( aligner, sym_string( M, pat + pat_off[i] ), quals.get( i, M ),
                                            sym_string( N, txt + txt_off[i] ), MIN_SCORE, sink );
         sinks[i].score = sink.score; sinks[i].x = sink.sink.x; sinks[i].y = sink.sink.y;
     }
@@ -65,8 +92,8 @@ inline void store_aln(orc_alignment* out, const aln::Alignment<int32>& a)
     out->sink_x = a.sink.x;  out->sink_y = a.sink.y;
 }
 
-template <uint32 CHK, typename aligner_type>
-void traceback_batch(const aligner_type aligner, const uint8_t* pat, const uint32_t* pat_off,
+template <uint32 CHK, typename aligner_type, typename quals_type>
+void traceback_batch(const aligner_type aligner, const quals_type quals, const uint8_t* pat, const uint32_t* pat_off,
                      const uint8_t* txt, const uint32_t* txt_off, uint32_t count, orc_alignment* out,
                      uint8_t* ops, uint32_t ops_stride, uint32_t* n_ops, int threads)
 {
@@ -89,7 +116,7 @@ void traceback_batch(const aligner_type aligner, const uint8_t* pat, const uint3
             PackedStream<uint32*,uint8,BITS,false> submatrix( &submatrix_words[0] );
             RecBacktracer bt = { ops + size_t(i) * ops_stride, 0u, ops_stride };
             const aln::Alignment<int32> a = aln::alignment_traceback<CHK>(
-                aligner, sym_string( M, pat + pat_off[i] ), aln::trivial_quality_string(),
+                aligner, sym_string( M, pat + pat_off[i] ), quals.get( i, M ),
                 sym_string( N, txt + txt_off[i] ), MIN_SCORE, bt, &checkpoints[0], submatrix, &column[0] );
             store_aln( out + i, a );
             n_ops[i] = bt.n;
@@ -97,8 +124,8 @@ void traceback_batch(const aligner_type aligner, const uint8_t* pat, const uint3
     }
 }
 
-template <uint32 BAND, uint32 CHK, typename aligner_type>
-void banded_traceback_batch(const aligner_type aligner, const uint8_t* pat, const uint32_t* pat_off,
+template <uint32 BAND, uint32 CHK, typename aligner_type, typename quals_type>
+void banded_traceback_batch(const aligner_type aligner, const quals_type quals, const uint8_t* pat, const uint32_t* pat_off,
                             const uint8_t* txt, const uint32_t* txt_off, uint32_t count, orc_alignment* out,
                             uint8_t* ops, uint32_t ops_stride, uint32_t* n_ops, int threads)
 {
@@ -118,7 +145,7 @@ void banded_traceback_batch(const aligner_type aligner, const uint8_t* pat, cons
             PackedStream<uint32*,uint8,BITS,false> submatrix( &submatrix_words[0] );
             RecBacktracer bt = { ops + size_t(i) * ops_stride, 0u, ops_stride };
             const aln::Alignment<int32> a = aln::banded_alignment_traceback<BAND,CHK>(
-                aligner, sym_string( M, pat + pat_off[i] ), aln::trivial_quality_string(),
+                aligner, sym_string( M, pat + pat_off[i] ), quals.get( i, M ),
                 sym_string( N, txt + txt_off[i] ), MIN_SCORE, bt, &checkpoints[0], submatrix );
             store_aln( out + i, a );
             n_ops[i] = bt.n;
@@ -129,7 +156,7 @@ void banded_traceback_batch(const aligner_type aligner, const uint8_t* pat, cons
 // ---- runtime -> compile-time dispatch ---------------------------------------------------------
 
 template <typename F>
-int dispatch_aligner(const orc_aligner a, F f)
+int dispatch_aligner(const orc_aligner a, F f, const orc_qscheme* qs = 0)
 {
     using namespace aln;
     #define NVB_TYPES(MAKE) \
@@ -142,6 +169,18 @@ int dispatch_aligner(const orc_aligner a, F f)
     {
         #define NVB_MK_ED(T) make_edit_distance_aligner<T>()
         NVB_TYPES(NVB_MK_ED)
+    }
+    else if (a.kind == 1 && qs)
+    {
+        const TableSWScheme s = { qs->match, qs->mismatch, a.p2, a.p3 };
+        #define NVB_MK_SWQ(T) make_smith_waterman_aligner<T>( s )
+        NVB_TYPES(NVB_MK_SWQ)
+    }
+    else if (a.kind == 2 && qs)
+    {
+        const TableGotohScheme s = { qs->match, qs->mismatch, a.p2, a.p3, qs->text_gap_open, qs->text_gap_ext };
+        #define NVB_MK_GTQ(T) make_gotoh_aligner<T>( s )
+        NVB_TYPES(NVB_MK_GTQ)
     }
     else if (a.kind == 1)
     {
@@ -163,31 +202,36 @@ struct Args
     const uint8_t* pat; const uint32_t* pat_off; const uint8_t* txt; const uint32_t* txt_off;
     uint32_t count; orc_sink* sinks; orc_alignment* out; uint8_t* ops; uint32_t ops_stride; uint32_t* n_ops;
     int threads;
+    const uint8_t* quals;   // NULL: trivial_quality_string
 };
 
 struct ScoreF { Args g;
     template <typename A> void operator()(const A a) const
-    { score_batch( a, g.pat, g.pat_off, g.txt, g.txt_off, g.count, g.sinks, g.threads ); } };
+    { if (g.quals) { const ByteQuals q = { g.quals, g.pat_off }; score_batch( a, q, g.pat, g.pat_off, g.txt, g.txt_off, g.count, g.sinks, g.threads ); }
+      else score_batch( a, NoQuals(), g.pat, g.pat_off, g.txt, g.txt_off, g.count, g.sinks, g.threads ); } };
 
 template <uint32 BAND> struct BandedScoreF { Args g;
     template <typename A> void operator()(const A a) const
-    { banded_score_batch<BAND>( a, g.pat, g.pat_off, g.txt, g.txt_off, g.count, g.sinks, g.threads ); } };
+    { if (g.quals) { const ByteQuals q = { g.quals, g.pat_off }; banded_score_batch<BAND>( a, q, g.pat, g.pat_off, g.txt, g.txt_off, g.count, g.sinks, g.threads ); }
+      else banded_score_batch<BAND>( a, NoQuals(), g.pat, g.pat_off, g.txt, g.txt_off, g.count, g.sinks, g.threads ); } };
 
 template <uint32 CHK> struct TracebackF { Args g;
     template <typename A> void operator()(const A a) const
-    { traceback_batch<CHK>( a, g.pat, g.pat_off, g.txt, g.txt_off, g.count, g.out, g.ops, g.ops_stride, g.n_ops, g.threads ); } };
+    { if (g.quals) { const ByteQuals q = { g.quals, g.pat_off }; traceback_batch<CHK>( a, q, g.pat, g.pat_off, g.txt, g.txt_off, g.count, g.out, g.ops, g.ops_stride, g.n_ops, g.threads ); }
+      else traceback_batch<CHK>( a, NoQuals(), g.pat, g.pat_off, g.txt, g.txt_off, g.count, g.out, g.ops, g.ops_stride, g.n_ops, g.threads ); } };
 
 template <uint32 BAND, uint32 CHK> struct BandedTracebackF { Args g;
     template <typename A> void operator()(const A a) const
-    { banded_traceback_batch<BAND,CHK>( a, g.pat, g.pat_off, g.txt, g.txt_off, g.count, g.out, g.ops, g.ops_stride, g.n_ops, g.threads ); } };
+    { if (g.quals) { const ByteQuals q = { g.quals, g.pat_off }; banded_traceback_batch<BAND,CHK>( a, q, g.pat, g.pat_off, g.txt, g.txt_off, g.count, g.out, g.ops, g.ops_stride, g.n_ops, g.threads ); }
+      else banded_traceback_batch<BAND,CHK>( a, NoQuals(), g.pat, g.pat_off, g.txt, g.txt_off, g.count, g.out, g.ops, g.ops_stride, g.n_ops, g.threads ); } };
 
 template <uint32 BAND>
-int banded_traceback_chk(const orc_aligner a, const uint32 chk, const Args& g)
+int banded_traceback_chk(const orc_aligner a, const uint32 chk, const Args& g, const orc_qscheme* qs)
 {
     switch (chk) {
-    case 16: { BandedTracebackF<BAND,16> f = { g }; return dispatch_aligner( a, f ); }
-    case 32: { BandedTracebackF<BAND,32> f = { g }; return dispatch_aligner( a, f ); }
-    case 64: { BandedTracebackF<BAND,64> f = { g }; return dispatch_aligner( a, f ); }
+    case 16: { BandedTracebackF<BAND,16> f = { g }; return dispatch_aligner( a, f, qs ); }
+    case 32: { BandedTracebackF<BAND,32> f = { g }; return dispatch_aligner( a, f, qs ); }
+    case 64: { BandedTracebackF<BAND,64> f = { g }; return dispatch_aligner( a, f, qs ); }
     default: return -2; }
 }
 
@@ -195,57 +239,72 @@ int banded_traceback_chk(const orc_aligner a, const uint32 chk, const Args& g)
 
 extern "C" {
 
+int ref_score_q(orc_aligner a, const orc_qscheme* qs, const uint8_t* quals, const uint8_t* pat, const uint32_t* pat_off, const uint8_t* txt,
+                const uint32_t* txt_off, uint32_t count, orc_sink* sinks, int threads)
+{
+    if (threads <= 0) threads = omp_get_max_threads();
+    Args g = { pat, pat_off, txt, txt_off, count, sinks, 0, 0, 0, 0, threads, quals };
+    ScoreF f = { g };
+    return dispatch_aligner( a, f, qs );
+}
 int ref_score(orc_aligner a, const uint8_t* pat, const uint32_t* pat_off, const uint8_t* txt,
               const uint32_t* txt_off, uint32_t count, orc_sink* sinks, int threads)
-{
-    if (threads <= 0) threads = omp_get_max_threads();
-    Args g = { pat, pat_off, txt, txt_off, count, sinks, 0, 0, 0, 0, threads };
-    ScoreF f = { g };
-    return dispatch_aligner( a, f );
-}
+{ return ref_score_q( a, 0, 0, pat, pat_off, txt, txt_off, count, sinks, threads ); }
 
-int ref_banded_score(orc_aligner a, uint32_t band, const uint8_t* pat, const uint32_t* pat_off,
-                     const uint8_t* txt, const uint32_t* txt_off, uint32_t count, orc_sink* sinks, int threads)
+int ref_banded_score_q(orc_aligner a, const orc_qscheme* qs, const uint8_t* quals, uint32_t band, const uint8_t* pat, const uint32_t* pat_off,
+                       const uint8_t* txt, const uint32_t* txt_off, uint32_t count, orc_sink* sinks, int threads)
 {
     if (threads <= 0) threads = omp_get_max_threads();
-    Args g = { pat, pat_off, txt, txt_off, count, sinks, 0, 0, 0, 0, threads };
+    Args g = { pat, pat_off, txt, txt_off, count, sinks, 0, 0, 0, 0, threads, quals };
     switch (band) {
-    case 3:  { BandedScoreF<3>  f = { g }; return dispatch_aligner( a, f ); }
-    case 5:  { BandedScoreF<5>  f = { g }; return dispatch_aligner( a, f ); }
-    case 7:  { BandedScoreF<7>  f = { g }; return dispatch_aligner( a, f ); }
-    case 15: { BandedScoreF<15> f = { g }; return dispatch_aligner( a, f ); }
-    case 31: { BandedScoreF<31> f = { g }; return dispatch_aligner( a, f ); }
+    case 3:  { BandedScoreF<3>  f = { g }; return dispatch_aligner( a, f, qs ); }
+    case 5:  { BandedScoreF<5>  f = { g }; return dispatch_aligner( a, f, qs ); }
+    case 7:  { BandedScoreF<7>  f = { g }; return dispatch_aligner( a, f, qs ); }
+    case 15: { BandedScoreF<15> f = { g }; return dispatch_aligner( a, f, qs ); }
+    case 31: { BandedScoreF<31> f = { g }; return dispatch_aligner( a, f, qs ); }
     default: return -2; }
 }
+int ref_banded_score(orc_aligner a, uint32_t band, const uint8_t* pat, const uint32_t* pat_off,
+                     const uint8_t* txt, const uint32_t* txt_off, uint32_t count, orc_sink* sinks, int threads)
+{ return ref_banded_score_q( a, 0, 0, band, pat, pat_off, txt, txt_off, count, sinks, threads ); }
 
+int ref_traceback_q(orc_aligner a, const orc_qscheme* qs, const uint8_t* quals, uint32_t checkpoints, const uint8_t* pat, const uint32_t* pat_off,
+                    const uint8_t* txt, const uint32_t* txt_off, uint32_t count, orc_alignment* out,
+                    uint8_t* ops, uint32_t ops_stride, uint32_t* n_ops, int threads)
+{
+    if (threads <= 0) threads = omp_get_max_threads();
+    Args g = { pat, pat_off, txt, txt_off, count, 0, out, ops, ops_stride, n_ops, threads, quals };
+    switch (checkpoints) {
+    case 16: { TracebackF<16> f = { g }; return dispatch_aligner( a, f, qs ); }
+    case 32: { TracebackF<32> f = { g }; return dispatch_aligner( a, f, qs ); }
+    case 64: { TracebackF<64> f = { g }; return dispatch_aligner( a, f, qs ); }
+    default: return -2; }
+}
 int ref_traceback(orc_aligner a, uint32_t checkpoints, const uint8_t* pat, const uint32_t* pat_off,
                   const uint8_t* txt, const uint32_t* txt_off, uint32_t count, orc_alignment* out,
                   uint8_t* ops, uint32_t ops_stride, uint32_t* n_ops, int threads)
+{ return ref_traceback_q( a, 0, 0, checkpoints, pat, pat_off, txt, txt_off, count, out, ops, ops_stride, n_ops, threads ); }
+
+int ref_banded_traceback_q(orc_aligner a, const orc_qscheme* qs, const uint8_t* quals, uint32_t band, uint32_t checkpoints, const uint8_t* pat,
+                           const uint32_t* pat_off, const uint8_t* txt, const uint32_t* txt_off,
+                           uint32_t count, orc_alignment* out, uint8_t* ops, uint32_t ops_stride,
+                           uint32_t* n_ops, int threads)
 {
     if (threads <= 0) threads = omp_get_max_threads();
-    Args g = { pat, pat_off, txt, txt_off, count, 0, out, ops, ops_stride, n_ops, threads };
-    switch (checkpoints) {
-    case 16: { TracebackF<16> f = { g }; return dispatch_aligner( a, f ); }
-    case 32: { TracebackF<32> f = { g }; return dispatch_aligner( a, f ); }
-    case 64: { TracebackF<64> f = { g }; return dispatch_aligner( a, f ); }
+    Args g = { pat, pat_off, txt, txt_off, count, 0, out, ops, ops_stride, n_ops, threads, quals };
+    switch (band) {
+    case 3:  return banded_traceback_chk<3>( a, checkpoints, g, qs );
+    case 5:  return banded_traceback_chk<5>( a, checkpoints, g, qs );
+    case 7:  return banded_traceback_chk<7>( a, checkpoints, g, qs );
+    case 15: return banded_traceback_chk<15>( a, checkpoints, g, qs );
+    case 31: return banded_traceback_chk<31>( a, checkpoints, g, qs );
     default: return -2; }
 }
-
 int ref_banded_traceback(orc_aligner a, uint32_t band, uint32_t checkpoints, const uint8_t* pat,
                          const uint32_t* pat_off, const uint8_t* txt, const uint32_t* txt_off,
                          uint32_t count, orc_alignment* out, uint8_t* ops, uint32_t ops_stride,
                          uint32_t* n_ops, int threads)
-{
-    if (threads <= 0) threads = omp_get_max_threads();
-    Args g = { pat, pat_off, txt, txt_off, count, 0, out, ops, ops_stride, n_ops, threads };
-    switch (band) {
-    case 3:  return banded_traceback_chk<3>( a, checkpoints, g );
-    case 5:  return banded_traceback_chk<5>( a, checkpoints, g );
-    case 7:  return banded_traceback_chk<7>( a, checkpoints, g );
-    case 15: return banded_traceback_chk<15>( a, checkpoints, g );
-    case 31: return banded_traceback_chk<31>( a, checkpoints, g );
-    default: return -2; }
-}
+{ return ref_banded_traceback_q( a, 0, 0, band, checkpoints, pat, pat_off, txt, txt_off, count, out, ops, ops_stride, n_ops, threads ); }
 
 } // extern "C"
 

@@ -208,3 +208,43 @@ def test_banded_packed_string_sets(oracle, ctx, bits):
                 assert (got == want).all(), (kind, ty, band, np.nonzero(got != want)[0][:5])
                 got = gu.tb_np(nvb.batch_banded_alignment_traceback(a, band, 16, ps, ts))
                 assert gu.tb_equal(got, oracle.banded_traceback(oa, band, 16, P, Po, T, To)), (kind, ty, band)
+
+
+@pytest.mark.parametrize("kind", [po.SW, po.GOTOH])
+@pytest.mark.parametrize("ty", [0, 1, 2])
+def test_quality_aware_schemes(oracle, kind, ty):
+    """nvb_batch_*_q: quality-aware scoring schemes (alignment.h:411-436, 488-505) through the C ABI vs the oracle (itself pinned on
+    the reference's quality overloads, tests/test_oracle_vs_ref.py): nvBowtie's scheme (scoring.h:279-286) and an arbitrary table,
+    full and banded, scoring and traceback, packed pattern sets, and the NULL quality string"""
+    rng = np.random.default_rng(2000 + 10 * kind + ty)
+    bt_m, bt_x = po.QScheme.bowtie2(2 if ty == 1 else 0, 2, 6)
+    schemes = [((0, 0, -8, -3) if kind == po.GOTOH else (0, 0, -3, -4), bt_m, bt_x, -7, -2),
+               ((0, 0, -4, -2) if kind == po.GOTOH else (0, 0, -2, -2), rng.integers(0, 5, 256), -rng.integers(0, 7, 256), -3, -3)]
+    for params, tm, tx, tgo, tge in schemes:
+        a, oa = gu.aligner(kind, ty, params), po.aligner(kind, ty, params)
+        qs, oqs = nvb.QualityScheme(tm, tx, tgo, tge), po.QScheme(tm, tx, tgo, tge)
+        for alpha in (4, 2):
+            P, Po, T, To = util.rand_pairs(rng, 300, (1, 70), lambda M: int(rng.integers(0, 120)), alpha)
+            Q = rng.integers(0, 60, len(P)).astype(np.uint8)
+            Q[rng.integers(0, len(P), 40)] = 255
+            ps, ts = gu.sset(P, Po), gu.sset(T, To)
+            qd = torch.from_numpy(Q).to(gu.dev())
+            got = gu.sinks_np(nvb.batch_alignment_score(a, ps, ts, scheme=qs, quals=qd))
+            assert (got == oracle.score(oa, P, Po, T, To, qs=oqs, quals=Q)).all()
+            got = gu.sinks_np(nvb.batch_alignment_score(a, ps, ts, scheme=qs))
+            assert (got == oracle.score(oa, P, Po, T, To, qs=oqs)).all()
+            got = gu.tb_np(nvb.batch_alignment_traceback(a, 16, ps, ts, scheme=qs, quals=qd))
+            assert gu.tb_equal(got, oracle.traceback(oa, 16, P, Po, T, To, qs=oqs, quals=Q))
+            if alpha == 4:      # 4-bit packed patterns: the qualities stay one byte per symbol
+                p4 = nvb.StringSet(torch.from_numpy(nvb.pack_symbols(P, 4).view(np.int32)).to(gu.dev()), ps.offsets, 4, ps.max_len)
+                got = gu.sinks_np(nvb.batch_alignment_score(a, p4, ts, scheme=qs, quals=qd))
+                assert (got == oracle.score(oa, P, Po, T, To, qs=oqs, quals=Q)).all()
+            for band in (7, 15, 31, 12):
+                P, Po, T, To = util.rand_pairs(rng, 300, (1, 80), util.banded_text_len(rng, ty, band), alpha)
+                Q = rng.integers(0, 60, len(P)).astype(np.uint8)
+                ps, ts = gu.sset(P, Po), gu.sset(T, To)
+                qd = torch.from_numpy(Q).to(gu.dev())
+                got = gu.sinks_np(nvb.batch_banded_alignment_score(a, band, ps, ts, scheme=qs, quals=qd))
+                assert (got == oracle.banded_score(oa, band, P, Po, T, To, qs=oqs, quals=Q)).all(), band
+                got = gu.tb_np(nvb.batch_banded_alignment_traceback(a, band, 16, ps, ts, scheme=qs, quals=qd))
+                assert gu.tb_equal(got, oracle.banded_traceback(oa, band, 16, P, Po, T, To, qs=oqs, quals=Q)), band

@@ -71,3 +71,32 @@ def test_config_shapes(oracle, ref):
     for a in (po.aligner(po.ED, po.SEMI_GLOBAL), po.aligner(po.GOTOH, po.SEMI_GLOBAL, (0, -5, -8, -3))):
         assert (ref.banded_score(a, 15, P, Po, T, To) == oracle.banded_score(a, 15, P, Po, T, To)).all()
         assert util.ops_equal(ref.banded_traceback(a, 15, 16, P, Po, T, To), oracle.banded_traceback(a, 15, 16, P, Po, T, To))
+
+
+@pytest.mark.parametrize("kind", [po.SW, po.GOTOH])
+@pytest.mark.parametrize("ty", [0, 1, 2])
+def test_quality_aware_schemes(oracle, ref, kind, ty):
+    """quality-aware scoring schemes (alignment.h:411-436, 488-505): the restatement with match(q) / mismatch(a, b, q) tables and
+    per-position pattern qualities against the reference's own quality overloads instantiated with table-driven schemes -- nvBowtie's
+    (scoring.h:279-286: constant match, quality-scaled mismatch, distinct read/reference gap penalties) and an arbitrary one;
+    full and banded, scoring and traceback"""
+    rng = np.random.default_rng(1000 + 10 * kind + ty)
+    bt_m, bt_x = po.QScheme.bowtie2(2 if ty == 1 else 0, 2, 6)
+    schemes = [((0, 0, -8, -3) if kind == po.GOTOH else (0, 0, -3, -4), po.QScheme(bt_m, bt_x, -7, -2)),
+               ((0, 0, -4, -2) if kind == po.GOTOH else (0, 0, -2, -2), po.QScheme(rng.integers(0, 5, 256), -rng.integers(0, 7, 256), -3, -3))]
+    for params, qs in schemes:
+        a = po.aligner(kind, ty, params)
+        for alpha in (4, 2):
+            P, Po, T, To = util.rand_pairs(rng, 120, (1, 60), lambda M: int(rng.integers(0, 100)), alpha)
+            Q = rng.integers(0, 60, len(P)).astype(np.uint8)
+            Q[rng.integers(0, max(1, len(P)), 40) % max(1, len(P))] = 255
+            assert (ref.score(a, P, Po, T, To, qs=qs, quals=Q) == oracle.score(a, P, Po, T, To, qs=qs, quals=Q)).all()
+            # the tables at quality 0 are what a NULL quality string reads
+            assert (ref.score(a, P, Po, T, To, qs=qs) == oracle.score(a, P, Po, T, To, qs=qs)).all()
+            assert util.ops_equal(ref.traceback(a, 16, P, Po, T, To, qs=qs, quals=Q), oracle.traceback(a, 16, P, Po, T, To, qs=qs, quals=Q))
+            for band in (7, 15, 31):
+                P, Po, T, To = util.rand_pairs(rng, 120, (1, 60), util.banded_text_len(rng, ty, band), alpha)
+                Q = rng.integers(0, 60, len(P)).astype(np.uint8)
+                assert (ref.banded_score(a, band, P, Po, T, To, qs=qs, quals=Q) == oracle.banded_score(a, band, P, Po, T, To, qs=qs, quals=Q)).all(), band
+                assert util.ops_equal(ref.banded_traceback(a, band, 16, P, Po, T, To, qs=qs, quals=Q),
+                                      oracle.banded_traceback(a, band, 16, P, Po, T, To, qs=qs, quals=Q)), band
