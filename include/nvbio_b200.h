@@ -89,15 +89,16 @@ typedef struct {
     int32_t gap_b;     /* SW: m_insertion  ; Gotoh: m_gap_ext                                   */
 } nvb_aligner;         /* kind == ED ignores the four scores: (0,-1,-1,-1)                      */
 
-/* aln::BestSink<int32> (nvbio/alignment/sink.h, sink_inl.h:31-48): sink = (text end, pattern end),
- * 1-based; "no cell reported" = score -(1<<30), sink (0xFFFFFFFF,0xFFFFFFFF) */
+/* the fields of aln::BestSink<int32> (nvbio/alignment/sink.h, sink_inl.h:31-48), PACKED (12 bytes; the reference's struct is 16:
+ * see nvb_sinks_to_reference_layout): sink = (text end, pattern end), 1-based; "no cell reported" = score -(1<<30), sink
+ * (0xFFFFFFFF,0xFFFFFFFF) */
 typedef struct { int32_t score; uint32_t sink_x, sink_y; } nvb_best_sink;
 
 /* aln::Best2Sink<int32> (nvbio/alignment/sink.h:99-123, sink_inl.h:54-82): the best cell and the best runner-up whose
  * text end lies more than distinct_dist away from it; same "no cell reported" values as nvb_best_sink */
 typedef struct { int32_t score1, score2; uint32_t sink1_x, sink1_y, sink2_x, sink2_y; } nvb_best2_sink;
 
-/* aln::Alignment<int32> (nvbio/alignment/alignment.h:310-322) */
+/* the fields of aln::Alignment<int32> (nvbio/alignment/alignment.h:310-322), packed (20 bytes; the reference's struct is 24) */
 typedef struct { int32_t score; uint32_t source_x, source_y, sink_x, sink_y; } nvb_alignment;
 
 /* traceback ops, one uint8 per op in PUSH order (end -> start), as a Backtracer receives them
@@ -351,6 +352,14 @@ int nvb_batch_banded_traceback_q(nvb_ctx* ctx, nvb_aligner aligner, const nvb_qu
                                  nvb_string_set patterns, const uint8_t* quals, nvb_string_set texts, nvb_alignment* out,
                                  uint8_t* ops, uint32_t ops_stride, uint32_t* n_ops, uint32_t max_pattern_len, uint32_t max_text_len,
                                  void* temp, size_t temp_bytes, void* stream);
+
+/* The reference's own records are padded: CUDA aligns uint2 to 8 bytes, so aln::BestSink<int32> { int32 score; uint2 sink; }
+ * (nvbio/alignment/sink.h:60-75) occupies 16 bytes (score, 4 bytes of padding, sink.x, sink.y) and aln::Alignment<int32>
+ * { int32 score; uint2 source, sink; } (alignment.h:310-322) 24 bytes -- nvb_best_sink / nvb_alignment are the packed 12 / 20-byte
+ * forms. These calls write n results in the reference's layout (best_sinks_out: 16-byte aligned, 16 n bytes; alignments_out:
+ * 8-byte aligned, 24 n bytes); include/nvbio_b200_adaptor.h uses them to fill the caller's BestSink<int32>* / Alignment<int32>*. */
+int nvb_sinks_to_reference_layout(nvb_ctx* ctx, const nvb_best_sink* sinks, uint32_t n, void* best_sinks_out, void* stream);
+int nvb_alignments_to_reference_layout(nvb_ctx* ctx, const nvb_alignment* alignments, uint32_t n, void* alignments_out, void* stream);
 
 /* host-buffer forms (H2D of both string sets, kernel(s), D2H of the results; synchronous) */
 int nvb_batch_score_host(nvb_ctx* ctx, nvb_aligner aligner, uint32_t band /* 0 = full matrix */,

@@ -449,3 +449,44 @@ extern "C" int nvb_ops_to_cigar(nvb_ctx* ctx, const uint8_t* ops, uint32_t ops_s
     NVB_LAUNCHED(ctx);
     return NVB_OK;
 }
+
+// ---------------------------------------------------------------------------------------------
+// The reference's in-memory records: CUDA's uint2 is 8-byte aligned, so aln::BestSink<int32> { int32 score; uint2 sink; } is
+// 16 bytes (score, 4 bytes of padding, sink.x, sink.y) and aln::Alignment<int32> { int32 score; uint2 source, sink; } 24 --
+// not the packed 12 / 20-byte records of this ABI. These two calls write an array of results in the reference's layout
+// (what include/nvbio_b200_adaptor.h hands back to the reference's callers).
+// ---------------------------------------------------------------------------------------------
+__global__ void sinks_to_ref_kernel(const nvb_best_sink* __restrict__ in, uint32_t n, uint4* __restrict__ out)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) { const nvb_best_sink v = in[i]; out[i] = make_uint4((uint32_t)v.score, 0u, v.sink_x, v.sink_y); }
+}
+__global__ void alignments_to_ref_kernel(const nvb_alignment* __restrict__ in, uint32_t n, uint2* __restrict__ out)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n)
+    {
+        const nvb_alignment v = in[i];
+        out[3 * (size_t)i]     = make_uint2((uint32_t)v.score, 0u);
+        out[3 * (size_t)i + 1] = make_uint2(v.source_x, v.source_y);
+        out[3 * (size_t)i + 2] = make_uint2(v.sink_x, v.sink_y);
+    }
+}
+extern "C" int nvb_sinks_to_reference_layout(nvb_ctx* ctx, const nvb_best_sink* sinks, uint32_t n, void* best_sinks_out, void* stream)
+{
+    if (!ctx) return NVB_ERR_ARG;
+    if (n == 0) return NVB_OK;
+    if (!sinks || !best_sinks_out || ((uintptr_t)best_sinks_out & 15u)) return NVB_ERR_ARG;
+    sinks_to_ref_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(sinks, n, (uint4*)best_sinks_out);
+    NVB_LAUNCHED(ctx);
+    return NVB_OK;
+}
+extern "C" int nvb_alignments_to_reference_layout(nvb_ctx* ctx, const nvb_alignment* alignments, uint32_t n, void* alignments_out, void* stream)
+{
+    if (!ctx) return NVB_ERR_ARG;
+    if (n == 0) return NVB_OK;
+    if (!alignments || !alignments_out || ((uintptr_t)alignments_out & 7u)) return NVB_ERR_ARG;
+    alignments_to_ref_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(alignments, n, (uint2*)alignments_out);
+    NVB_LAUNCHED(ctx);
+    return NVB_OK;
+}
