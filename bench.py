@@ -40,7 +40,7 @@ def parse():
     ap.add_argument("--c4-genome", type=int, default=3_100_000_000, help="genome of the configs[3]/[4] leg at its named size (0 = skip)")
     ap.add_argument("--no-extra", action="store_true", help="skip the SW / banded secondary measurements")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
-    ap.add_argument("--only", default="", help="profiling aid: run only this leg (fm|sw|banded|map|c4|fm_c4) with no cpu leg")
+    ap.add_argument("--only", default="", help="profiling aid: run only this leg (fm|sw|banded|traceback|map|c4|fm_c4) with no cpu leg")
     ap.add_argument("--traffic-child", default="", help="internal: the short run bench.py puts under ncu to measure DRAM traffic (fm|fm_c4)")
     return ap.parse_args()
 
@@ -674,7 +674,7 @@ def run_b200(args):
         map_leg(genome, fmi, args.reads, args.pairs, "map", "pairs")
 
     # ---------------- secondary: SW local scoring (configs[0]) and banded scoring/traceback (configs[2])
-    if not args.no_extra or only in ("sw", "banded"):
+    if not args.no_extra or only in ("sw", "banded", "traceback"):
         if only in ("", "sw"):
             M, N, n = 150, 500, args.sw_pairs
             P, Po, T, To = gen_pairs(n, M, N, 1 + rank, dev)
@@ -745,16 +745,51 @@ def run_b200(args):
             P, Po, T, To = gen_pairs(n, M, N, 3 + rank, dev, sub=0.04, implant_frac=1.0)
             ps, ts = nvb.StringSet(P, Po, 8, M), nvb.StringSet(T, To, 8, N)
             res = {}
-            for name, a in (("ed_semi", nvb.EditDistanceAligner(nvb.SEMI_GLOBAL)),
-                            ("gotoh_semi", nvb.GotohAligner(nvb.SEMI_GLOBAL, 0, -5, -8, -3)),
-                            ("sw_semi", nvb.SmithWatermanAligner(nvb.SEMI_GLOBAL, 2, -1, -1, -1)),
-                            ("sw_local", nvb.SmithWatermanAligner(nvb.LOCAL, 2, -1, -1, -1))):
+            do_cpu = rank == 0 and world == 1 and not args.no_cpu and only == ""
+            k_chk = min(n, 1_000_000)              # parity gate + CPU rate on the first million pairs (the whole batch shares one generator)
+            k_e2e = min(n, 2_000_000)              # end-to-end legs on a prefix: 1 GB of pinned host strings
+            if do_cpu:
+                po, chk, kind = load_checker()
+                Ph, Th = P[:k_chk * M].cpu().numpy(), T[:k_chk * N].cpu().numpy()
+                Poh, Toh = (np.arange(k_chk + 1, dtype=np.int64) * M).astype(np.uint32), (np.arange(k_chk + 1, dtype=np.int64) * N).astype(np.uint32)
+            hP = torch.empty(k_e2e * M, dtype=torch.uint8).pin_memory(); hP.copy_(P[:k_e2e * M])
+            hT = torch.empty(k_e2e * N, dtype=torch.uint8).pin_memory(); hT.copy_(T[:k_e2e * N])
+            hPo = torch.empty(k_e2e + 1, dtype=torch.int32).pin_memory(); hPo.copy_(Po[:k_e2e + 1])
+            hTo = torch.empty(k_e2e + 1, dtype=torch.int32).pin_memory(); hTo.copy_(To[:k_e2e + 1])
+            hS = torch.empty((k_e2e, 3), dtype=torch.int32).pin_memory()
+            hS_n = hS.numpy().reshape(-1).view(nvb.SINK_DT)
+            cstream = torch.cuda.ExternalStream(ctx.stream, device=dev)
+
+            def sinks_mismatches(got, want):
+                return int(((got[:, 0] != want["score"]) | (got[:, 1].view(np.uint32) != want["x"]) | (got[:, 2].view(np.uint32) != want["y"])).sum())
+
+            for name, a, okind, osc in (("ed_semi", nvb.EditDistanceAligner(nvb.SEMI_GLOBAL), "ED", (0, -1, -1, -1)),
+                                        ("gotoh_semi", nvb.GotohAligner(nvb.SEMI_GLOBAL, 0, -5, -8, -3), "GOTOH", (0, -5, -8, -3)),
+                                        ("sw_semi", nvb.SmithWatermanAligner(nvb.SEMI_GLOBAL, 2, -1, -1, -1), "SW", (2, -1, -1, -1)),
+                                        ("sw_local", nvb.SmithWatermanAligner(nvb.LOCAL, 2, -1, -1, -1), "SW", (2, -1, -1, -1))):
                 sinks = torch.empty((n, 3), dtype=torch.int32, device=dev)
                 fn = lambda: nvb.batch_banded_alignment_score(a, W, ps, ts, sinks=sinks, ctx=ctx)
                 barrier()
                 tms = time_steps(fn, max(3, args.steps // 2), 2, flush)
                 ms = max_over_ranks(sum(tms) / len(tms))
                 res[name] = dict(gcups=world * n * M * W / (ms * 1e-3) / 1e9, ms=ms, paths=ctx.last_paths)
+                # end to end through nvb_batch_score_host(band): pinned host strings in, sinks out
+                args_h = (a, W, hP.numpy(), hPo.numpy().view(np.uint32), hT.numpy(), hTo.numpy().view(np.uint32))
+                nvb.batch_score_host(*args_h, sinks_h=hS_n, ctx=ctx)
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(cstream); nvb.batch_score_host(*args_h, sinks_h=hS_n, ctx=ctx); e1.record(cstream); e1.synchronize()
+                e_ms = max_over_ranks(e0.elapsed_time(e1))
+                res[name]["e2e"] = dict(gcups=world * k_e2e * M * W / (e_ms * 1e-3) / 1e9, ms=e_ms, pairs=k_e2e,
+                                        h2d_bytes=int(hP.numel() + hT.numel() + 4 * (hPo.numel() + hTo.numel())), d2h_bytes=int(hS.numel() * 4),
+                                        call="nvb_batch_score_host(band = 15), pinned host buffers")
+                assert (hS.numpy() == sinks[:k_e2e].cpu().numpy()).all(), "host and device banded scoring disagree"
+                if do_cpu:
+                    oa = po.aligner(getattr(po, okind), a.type, osc)
+                    t = time.time(); want = chk.banded_score(oa, W, Ph, Poh, Th, Toh, threads=host_threads()); dt = time.time() - t
+                    res[name]["cpu_gcups"] = k_chk * M * W / dt / 1e9
+                    res[name]["cpu_kind"] = kind; res[name]["cpu_cores"] = host_threads()
+                    res[name]["parity"] = dict(checked=k_chk, mismatches=sinks_mismatches(sinks[:k_chk].cpu().numpy(), want))
+                del sinks
             # MyersTag<4> bit-vector edit distance over the 16-wide band the reference's fmmap example uses (fmmap.cu:347-358)
             ma = nvb.MyersAligner(nvb.SEMI_GLOBAL, nvb.MyersTag(4))
             msinks = torch.empty((n, 3), dtype=torch.int32, device=dev)
@@ -764,11 +799,18 @@ def run_b200(args):
             ms = max_over_ranks(sum(tms) / len(tms))
             res["myers16_semi"] = dict(gcups=world * n * M * 16 / (ms * 1e-3) / 1e9, ms=ms, pairs_per_s=world * n / (ms * 1e-3),
                                        note="bit-vector kernel: 1 thread per pair, band 16; GCUPS = n*M*16 / t")
+            if do_cpu:
+                t = time.time(); want = chk.banded_myers(nvb.SEMI_GLOBAL, 4, 16, -1000, Ph, Poh, Th, Toh, threads=host_threads()); dt = time.time() - t
+                res["myers16_semi"]["cpu_pairs_per_s"] = k_chk / dt
+                res["myers16_semi"]["cpu_kind"] = kind; res["myers16_semi"]["cpu_cores"] = host_threads()
+                res["myers16_semi"]["parity"] = dict(checked=k_chk, mismatches=sinks_mismatches(msinks[:k_chk].cpu().numpy(), want))
+            del msinks
             # traceback (CHK = 16 as nvBowtie, defs.h:95) on a slice that keeps scratch modest
             nt = min(n, 2_000_000)
+            kt = min(nt, 200_000)                  # parity gate + CPU rate of the tracebacks
             pt, tt = nvb.StringSet(P[:nt * M], Po[:nt + 1], 8, M), nvb.StringSet(T[:nt * N], To[:nt + 1], 8, N)
-            for name, a in (("ed_semi_traceback", nvb.EditDistanceAligner(nvb.SEMI_GLOBAL)),
-                            ("gotoh_semi_traceback", nvb.GotohAligner(nvb.SEMI_GLOBAL, 0, -5, -8, -3))):
+            for name, a, okind, osc in (("ed_semi_traceback", nvb.EditDistanceAligner(nvb.SEMI_GLOBAL), "ED", (0, -1, -1, -1)),
+                                        ("gotoh_semi_traceback", nvb.GotohAligner(nvb.SEMI_GLOBAL, 0, -5, -8, -3), "GOTOH", (0, -5, -8, -3))):
                 ttemp = torch.empty(int(nvb.lib().nvb_temp_bytes(3, a.c(), W, 16, M, N, nt)), dtype=torch.uint8, device=dev)
                 bufs = nvb.batch_banded_alignment_traceback(a, W, 16, pt, tt, temp=ttemp, ctx=ctx)
                 fn = lambda: nvb.batch_banded_alignment_traceback(a, W, 16, pt, tt, temp=ttemp, ctx=ctx, bufs=bufs)
@@ -776,8 +818,64 @@ def run_b200(args):
                 ms = max_over_ranks(sum(tms) / len(tms))
                 res[name] = dict(pairs_per_s=world * nt / (ms * 1e-3), ms=ms, pairs=nt, paths=ctx.last_paths,
                                  gcups_equiv=world * nt * M * W / (ms * 1e-3) / 1e9)
+                # end to end: nvb_batch_traceback_host(band) on the checked prefix (alignments + op lists back on the host)
+                stride = int(bufs[1].shape[1])
+                t0_ = time.time()
+                h_out, h_ops, h_nops = nvb.batch_traceback_host(a, W, 16, hP.numpy()[:kt * M], hPo.numpy().view(np.uint32)[:kt + 1], hT.numpy()[:kt * N],
+                                                                hTo.numpy().view(np.uint32)[:kt + 1], stride, ctx=ctx)
+                e_ms = (time.time() - t0_) * 1e3
+                res[name]["e2e"] = dict(pairs_per_s=kt / (e_ms * 1e-3), ms=e_ms, pairs=kt, d2h_bytes=int(kt * (20 + 4 + stride)),
+                                        call="nvb_batch_traceback_host(band = 15, checkpoints = 16), pageable result arrays, wall clock")
+                if do_cpu:
+                    oa = po.aligner(getattr(po, okind), a.type, osc)
+                    t = time.time(); w_out, w_ops, w_n = chk.banded_traceback(oa, W, 16, Ph[:kt * M], Poh[:kt + 1], Th[:kt * N], Toh[:kt + 1], threads=host_threads()); dt = time.time() - t
+                    g_out, g_ops, g_n = bufs[0][:kt].cpu().numpy(), bufs[1][:kt].cpu().numpy(), bufs[2][:kt].cpu().numpy().view(np.uint32)
+                    bad = (g_out[:, 0] != w_out["score"]) | (g_out[:, 1].view(np.uint32) != w_out["src_x"]) | (g_out[:, 2].view(np.uint32) != w_out["src_y"]) | \
+                          (g_out[:, 3].view(np.uint32) != w_out["sink_x"]) | (g_out[:, 4].view(np.uint32) != w_out["sink_y"]) | (g_n != w_n)
+                    wcol = min(g_ops.shape[1], w_ops.shape[1])
+                    valid = np.arange(wcol)[None, :] < w_n[:, None]
+                    bad |= ((g_ops[:, :wcol] != w_ops[:, :wcol]) & valid).any(axis=1)
+                    bad_h = (h_out["score"] != w_out["score"]) | (h_nops != w_n) | ((h_ops[:, :wcol] != w_ops[:, :wcol]) & valid).any(axis=1)
+                    res[name]["cpu_pairs_per_s"] = kt / dt
+                    res[name]["cpu_kind"] = kind; res[name]["cpu_cores"] = host_threads()
+                    res[name]["parity"] = dict(checked=kt, mismatches=int(bad.sum()), host_entry_mismatches=int(bad_h.sum()))
                 del ttemp, bufs
             out["banded"] = dict(pairs=n, M=M, N=N, band=W, **res)
+            del P, T, hP, hT, hS
+
+        # ---------------- full-matrix checkpointed traceback (A9: alignment_inl.h:355-455; CHECKPOINTS = 64 as nvBowtie's defs.h:96) at configs[0]'s shape
+        if only in ("", "sw", "traceback"):
+            M, N, nt = 150, 500, min(args.sw_pairs, 50_000)
+            P, Po, T, To = gen_pairs(nt, M, N, 5 + rank, dev)
+            pt, tt = nvb.StringSet(P, Po, 8, M), nvb.StringSet(T, To, 8, N)
+            res = {}
+            for name, a, okind, osc in (("sw_local", nvb.SmithWatermanAligner(nvb.LOCAL, 2, -1, -1, -1), "SW", (2, -1, -1, -1)),
+                                        ("gotoh_semi_global", nvb.GotohAligner(nvb.SEMI_GLOBAL, 2, -2, -5, -3), "GOTOH", (2, -2, -5, -3))):
+                ttemp = torch.empty(int(nvb.lib().nvb_temp_bytes(2, a.c(), 0, 64, M, N, nt)), dtype=torch.uint8, device=dev)
+                bufs = {}
+                def fn():
+                    bufs["r"] = nvb.batch_alignment_traceback(a, 64, pt, tt, temp=ttemp, ctx=ctx)
+                tms = time_steps(fn, 2, 1, flush)
+                ms = max_over_ranks(sum(tms) / len(tms))
+                res[name] = dict(pairs_per_s=world * nt / (ms * 1e-3), ms=ms, pairs=nt, paths=ctx.last_paths, gcups_equiv=world * nt * M * N / (ms * 1e-3) / 1e9,
+                                 note="int32 one-pair-per-thread kernels (score pass + per-checkpoint recomputation); no packed kernel yet")
+                if rank == 0 and world == 1 and not args.no_cpu and only == "":
+                    po, chk, kind = load_checker()
+                    kt = min(nt, 5000)
+                    oa = po.aligner(getattr(po, okind), a.type, osc)
+                    Ph, Th = P[:kt * M].cpu().numpy(), T[:kt * N].cpu().numpy()
+                    Poh, Toh = (np.arange(kt + 1) * M).astype(np.uint32), (np.arange(kt + 1) * N).astype(np.uint32)
+                    t = time.time(); w_out, w_ops, w_n = chk.traceback(oa, 64, Ph, Poh, Th, Toh, threads=host_threads()); dt = time.time() - t
+                    g_out, g_ops, g_n = bufs["r"][0][:kt].cpu().numpy(), bufs["r"][1][:kt].cpu().numpy(), bufs["r"][2][:kt].cpu().numpy().view(np.uint32)
+                    wcol = min(g_ops.shape[1], w_ops.shape[1])
+                    valid = np.arange(wcol)[None, :] < w_n[:, None]
+                    bad = (g_out[:, 0] != w_out["score"]) | (g_n != w_n) | ((g_ops[:, :wcol] != w_ops[:, :wcol]) & valid).any(axis=1)
+                    res[name]["cpu_pairs_per_s"] = kt / dt
+                    res[name]["cpu_kind"] = kind; res[name]["cpu_cores"] = host_threads()
+                    res[name]["parity"] = dict(checked=kt, mismatches=int(bad.sum()))
+                del ttemp, bufs
+            out["full_traceback"] = dict(M=M, N=N, checkpoints=64, **res)
+            del P, T
 
     # ---------------- configs[3] / configs[4] at their named genome size (3.1 Gbp): a second index, built after everything
     # else has been measured and freed; a failure (memory) is recorded instead of ending the run
@@ -897,7 +995,7 @@ def run_b200(args):
         out["fm_c4"]["workload"] = ("configs[3] index: FM-index exact 20-mer backward search, %d queries per GPU on a synthetic %d bp genome "
                                     "(1.55 GB fused nvBWT image, DRAM-resident)" % (out["fm_c4"]["queries"], args.c4_genome))
         out["fm_c4"]["cpu_baseline"] = out["fm_c4"].pop("cpu", None)
-    extra = {k: out[k] for k in ("fm_c4", "sw", "banded", "map", "pairs", "map_c4", "pairs_c4") if k in out}
+    extra = {k: out[k] for k in ("fm_c4", "sw", "full_traceback", "banded", "map", "pairs", "map_c4", "pairs_c4") if k in out}
     if extra:
         line["extra"] = extra
     print(json.dumps(line))
