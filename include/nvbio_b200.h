@@ -432,6 +432,21 @@ typedef struct { int32_t score; uint32_t frag_begin, frag_end, flags; } nvb_pair
 int nvb_pair_hits(nvb_ctx* ctx, const nvb_read_hit* hits_d, uint32_t n_pairs, uint32_t min_frag_len, uint32_t max_frag_len,
                   nvb_pair_hit* pairs_d, void* stream);
 
+/* ----------------------------------------------------------------------------------------- */
+/* One process, several contexts: the batch is cut into n_ctx contiguous slices, one host thread per context runs the   */
+/* single-context host entry point on its slice against ITS index (fmis_d[i], genome_words_d[i]: a replica per device, or the same */
+/* pointers for contexts that share a device), and every slice writes its own range of the caller's result arrays. No collective,  */
+/* no counterpart in the reference's library (nvBowtie runs one thread per GPU the same way). Slices start on multiples of 32       */
+/* queries / 2 reads (packed fixed-length streams stay word-aligned, mates stay together). stats_h receives the sums.               */
+/* ----------------------------------------------------------------------------------------- */
+int nvb_fm_match_host_multi(nvb_ctx* const* ctxs, const nvb_fmindex* fmis_d, uint32_t n_ctx, const void* symbols_h, uint32_t bits,
+                            const uint32_t* offsets_h /* NULL: queries of fixed_len symbols */, uint32_t fixed_len, uint32_t count,
+                            uint32_t* ranges_h);
+int nvb_map_reads_host_multi(nvb_ctx* const* ctxs, const nvb_fmindex* fmis_d, const uint32_t* const* genome_words_d, uint32_t n_ctx,
+                             const uint8_t* reads_h, const uint32_t* read_off_h, uint32_t n_reads, const nvb_map_params* params,
+                             uint32_t reads_per_batch, nvb_read_hit* hits_h, uint8_t* ops_h, uint32_t ops_stride,
+                             uint16_t* cigar_h, uint32_t cigar_stride, nvb_map_stats* stats_h);
+
 #if defined(__GNUC__)
 #pragma GCC visibility pop
 #endif

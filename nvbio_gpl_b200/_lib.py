@@ -118,6 +118,8 @@ _PROTOS = {
                            C.POINTER(MapStatsC), _vp]),
     "nvb_map_reads_host": (_i, [_vp, C.POINTER(FMIndexC), _vp, _vp, _vp, _u32, C.POINTER(MapParamsC), _u32, _vp, _vp, _u32,
                                 _vp, _u32, C.POINTER(MapStatsC)]),
+    "nvb_fm_match_host_multi": (_i, [_vp, _vp, _u32, _vp, _u32, _vp, _u32, _u32, _vp]),
+    "nvb_map_reads_host_multi": (_i, [_vp, _vp, _vp, _u32, _vp, _vp, _u32, C.POINTER(MapParamsC), _u32, _vp, _vp, _u32, _vp, _u32, C.POINTER(MapStatsC)]),
     "nvb_pair_hits": (_i, [_vp, _vp, _u32, _u32, _u32, _vp, _vp]),
     "nvb_last_paths": (_u32, [_vp]),
     "nvb_force_generic": (None, [_vp, _i]),

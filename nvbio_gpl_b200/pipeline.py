@@ -92,6 +92,48 @@ def map_reads_host(fmi, genome_words, symbols_h, offsets_h, params, hits_h=None,
     return hits_h, ops_h, dict(seeds=stats.seeds, seed_hits=stats.seed_hits, candidates=stats.candidates, aligned=stats.aligned)
 
 
+def _ctx_array(ctxs):
+    arr = (C.c_void_p * len(ctxs))(*[c.h for c in ctxs])
+    return arr
+
+
+def map_reads_host_multi(ctxs, fmis, genome_words, symbols_h, offsets_h, params, hits_h=None, ops_h=None, cigar_h=None,
+                         reads_per_batch=0, max_read_len=None):
+    """``nvb_map_reads_host_multi``: one host thread per context, contiguous slices of one host batch, every slice writing its own
+    range of the result arrays. ctxs / fmis / genome_words: one per context (index replicas on the contexts' devices)."""
+    from ._lib import FMIndexC
+    n = len(offsets_h) - 1
+    if max_read_len is None:
+        max_read_len = int(np.max(np.diff(offsets_h.astype(np.int64)))) if n else 0
+    stride = ops_h.shape[1] if ops_h is not None else ops_stride_for(max_read_len, params.band)
+    if hits_h is None:
+        hits_h = np.zeros(n, dtype=HIT_DT)
+    k = len(ctxs)
+    fcs = (FMIndexC * k)(*[f.c() for f in fmis])
+    gws = (C.c_void_p * k)(*[g.data_ptr() for g in genome_words])
+    stats = MapStatsC()
+    pc = params.c()
+    check(lib().nvb_map_reads_host_multi(_ctx_array(ctxs), fcs, gws, k, symbols_h.ctypes.data, offsets_h.ctypes.data, n, C.byref(pc),
+                                         reads_per_batch, hits_h.ctypes.data, ops_h.ctypes.data if ops_h is not None else None, stride,
+                                         cigar_h.ctypes.data if cigar_h is not None else None,
+                                         cigar_h.shape[1] if cigar_h is not None else 0, C.byref(stats)), ctxs[0].h)
+    return hits_h, ops_h, dict(seeds=stats.seeds, seed_hits=stats.seed_hits, candidates=stats.candidates, aligned=stats.aligned)
+
+
+def match_host_multi(ctxs, fmis, symbols_h, offsets_h=None, query_len=0, count=None, ranges_h=None, bits=8):
+    """``nvb_fm_match_host_multi``: the query batch cut into one contiguous slice per context (offsets_h = None: queries of
+    query_len symbols each)"""
+    from ._lib import FMIndexC
+    k = len(ctxs)
+    n = (len(offsets_h) - 1) if offsets_h is not None else int(count)
+    if ranges_h is None:
+        ranges_h = np.empty((n, 2), dtype=np.uint32)
+    fcs = (FMIndexC * k)(*[f.c() for f in fmis])
+    check(lib().nvb_fm_match_host_multi(_ctx_array(ctxs), fcs, k, symbols_h.ctypes.data, bits,
+                                        offsets_h.ctypes.data if offsets_h is not None else None, int(query_len), n, ranges_h.ctypes.data), ctxs[0].h)
+    return ranges_h
+
+
 def pair_hits(hits, min_frag_len=0, max_frag_len=500, ctx=None):
     """mate pairing (``nvb_pair_hits``) over the device hits of 2 n independently mapped mates laid out pair by pair; forward-reverse
     policy with nvBowtie's fragment window (params.h:147-152). Returns int32 [n, 4] viewable as PAIR_DT."""

@@ -143,3 +143,45 @@ def test_pair_hits(oracle):
     idx = np.arange(len(got))
     assert conc[(idx % 11 != 10) & (idx % 13 != 0)].mean() > 0.97       # sampled fragments pair up, whichever mate is forward
     assert not conc[idx % 13 == 0].any()                                  # 900-bp fragments fall outside the window
+
+
+def test_multi_context_host_entries(oracle):
+    """nvb_map_reads_host_multi / nvb_fm_match_host_multi (one host thread per context, contiguous slices of one host
+    batch, disjoint ranges of one result array): three contexts -- on this box all on device 0, each with its own stream and
+    scratch -- give the results of the single-context calls and of the oracle, for slice counts that do and do not divide the batch"""
+    rng = np.random.default_rng(808)
+    G = 50000
+    genome = rng.integers(0, 4, G).astype(np.uint8)
+    fmi, oidx = gu.fm_index_pair(oracle, genome)
+    words = nvb.pack_genome(torch.from_numpy(genome).to(gu.dev()))
+    sym, off = map_util.make_reads(rng, genome, 2501)
+    pc = map_util.map_params(15, po.GOTOH, (0, -5, -8, -3), 20, 10, 4, 0, 1, -60)
+    params = nvb.MapParams(nvb.GotohAligner(nvb.SEMI_GLOBAL, 0, -5, -8, -3), 20, 10, 4, 0, 15, True, -60)
+    want_hits, want_ops, _ = oracle.map_reads(oidx, genome, sym, off, pc)
+    L = int(np.max(np.diff(off.astype(np.int64))))
+    stride = nvb.ops_stride_for(L, 15)
+    ctxs = [nvb.Context(0) for _ in range(3)]
+    try:
+        for k in (1, 2, 3):
+            ops_h = np.zeros((len(off) - 1, stride), dtype=np.uint8)
+            hits_h, _, st = nvb.map_reads_host_multi(ctxs[:k], [fmi] * k, [words] * k, sym, off, params, ops_h=ops_h, reads_per_batch=500)
+            assert same(hits_h, ops_h, want_hits, want_ops), k
+            assert st["aligned"] == int((want_hits["flags"] & 2 != 0).sum())
+        # seeding: ragged 8-bit queries, and fixed-length 4-bit packed seeds
+        import util
+        Q, qo = util.rand_queries(rng, genome, 70001, len_range=(0, 30))
+        want = oracle.fm_match(oidx, Q, qo)
+        for k in (1, 2, 3):
+            assert (nvb.match_host_multi(ctxs[:k], [fmi] * k, Q, qo) == want).all(), k
+        n, Lq = 100003, 20
+        pos = rng.integers(0, G - Lq, n)
+        F = genome[(pos[:, None] + np.arange(Lq)[None, :])].reshape(-1).copy()
+        F[rng.integers(0, len(F), 500)] = 4
+        fo = (np.arange(n + 1, dtype=np.int64) * Lq).astype(np.uint32)
+        wantf = oracle.fm_match(oidx, F, fo)
+        for k in (2, 3):
+            got = nvb.match_host_multi(ctxs[:k], [fmi] * k, nvb.pack_symbols(F, 4), None, query_len=Lq, count=n, bits=4)
+            assert (got == wantf).all(), k
+    finally:
+        for c in ctxs:
+            c.close()
