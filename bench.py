@@ -576,22 +576,34 @@ def run_b200(args):
         f4_ms = max_over_ranks(sum(f4_t) / len(f4_t))
         out["fm"]["e2e_fixed4"] = dict(value=world * nq / (f4_ms * 1e-3), unit="lookups/s", ms_per_step=f4_ms,
                                        h2d_bytes_per_step=int(hp.numel() * 4), d2h_bytes_per_step=int(hr.numel() * 4))
-        del hp
+        # what the bus alone allows for that call: the same pinned buffers copied with no kernel in between (the call's
+        # chunks overlap the two directions, so the bound is the slower direction; the serial sum is printed beside it)
+        dq = torch.empty(hp.numel(), dtype=torch.int32, device=dev)
+        dr = torch.empty((nq, 2), dtype=torch.int32, device=dev)
+        hr2 = torch.empty((nq, 2), dtype=torch.int32).pin_memory()
+        def _copy_ms(fn):
+            ts = []
+            for _ in range(3):
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(); fn(); e1.record(); e1.synchronize(); ts.append(e0.elapsed_time(e1))
+            return max_over_ranks(min(ts))
+        h2d_ms = _copy_ms(lambda: dq.copy_(hp, non_blocking=True))
+        d2h_ms = _copy_ms(lambda: hr2.copy_(dr, non_blocking=True))
+        out["fm"]["e2e_fixed4"]["copy_ceiling"] = dict(h2d_ms=h2d_ms, d2h_ms=d2h_ms, h2d_gbs=hp.numel() * 4 / h2d_ms / 1e6, d2h_gbs=hr.numel() * 4 / d2h_ms / 1e6,
+                                                       lookups_per_s_overlapped=world * nq / (max(h2d_ms, d2h_ms) * 1e-3),
+                                                       lookups_per_s_serial=world * nq / ((h2d_ms + d2h_ms) * 1e-3),
+                                                       frac_of_overlapped=(world * nq / (f4_ms * 1e-3)) / (world * nq / (max(h2d_ms, d2h_ms) * 1e-3)))
+        del hp, dq, dr, hr2
 
         if rank == 0 and world == 1 and not args.no_cpu and only == "":
             fm_check("fm", fmi, hs_n, ho_n, hr_n, nq)
         del hs, ho, hr
 
     # ---------------- seed -> locate -> extend -> traceback over 150-bp reads (configs[3] shape on this leg's genome)
-    def map_leg(genome, fmi, nr, npairs, tag, ptag):
+    def map_leg(genome, fmi, nr, npairs, tag, ptag, strong=None):
+        """strong = (reads_total, pairs_total): the configs[3] / configs[4] totals split over the ranks (strong scaling)"""
         RL = 150
         words = nvb.pack_genome(genome, ctx=ctx)
-        # index-side optional structures (identical results): k-mer jump table for seeding (k = 10 while index + table fit L2,
-        # 15 = 8 GiB on a DRAM-resident index) and a 2-row sampled SA for the locate walks (4 bytes per 2 genome symbols)
-        kk = int(os.environ.get("KTAB_K", 10 if genome.numel() <= 400_000_000 else 15))
-        fmi.build_ktab(kk, ctx=ctx)
-        dd = int(os.environ.get("DSSA_INT", 2))
-        fmi.build_dssa(dd, ctx=ctx)
         rsym, roff = gen_reads(genome, nr, RL, 7 + rank, dev)
         mparams = nvb.MapParams(nvb.GotohAligner(nvb.SEMI_GLOBAL, 0, -5, -8, -3), seed_len=20, seed_interval=10, max_hits=4,
                                 max_range=0, band=15, both_strands=True, min_score=-90)
@@ -599,19 +611,51 @@ def run_b200(args):
         res = {}
         def _map():
             res["r"] = nvb.map_reads(fmi, words, rsym, roff, mparams, max_read_len=RL, ctx=ctx)
+        steps_m = max(2, args.steps // 3)
+        # (1) the reference's own index layout (BWT + occurrence counters + 16-row sampled SA, nothing else index-side);
+        # the call builds its per-call k-mer table for the seeds itself
+        _map()
+        barrier()
+        tms = time_steps(_map, steps_m, 1, flush)
+        ms_plain = max_over_ranks(sum(tms) / len(tms))
+        plain_hits = res["r"][0].clone()
+        # (2) index-side optional structures (identical results): k-mer jump table for seeding (k = 10 while index + table fit
+        # L2, 15 = 8 GiB on a DRAM-resident index) and a 2-row sampled SA for the locate walks (4 bytes per 2 genome symbols)
+        kk = int(os.environ.get("KTAB_K", 10 if genome.numel() <= 400_000_000 else 15))
+        fmi.build_ktab(kk, ctx=ctx)
+        dd = int(os.environ.get("DSSA_INT", 2))
+        fmi.build_dssa(dd, ctx=ctx)
         l0 = ctx.launches
         _map()
         per_call = ctx.launches - l0
         barrier()
-        tms = time_steps(_map, max(2, args.steps // 3), 1, flush)
+        tms = time_steps(_map, steps_m, 1, flush)
         ms = max_over_ranks(sum(tms) / len(tms))
         hits_d, ops_d, mstats = res["r"]
+        assert bool((plain_hits == hits_d).all().item()), "index-side tables changed the mapping result"
+        del plain_hits
         out[tag] = dict(reads_per_s=world * nr / (ms * 1e-3), ms=ms, reads=nr, read_len=RL, launches_per_call=per_call,
                           seed_hits_per_read=mstats["seed_hits"] / nr, candidates_per_read=mstats["candidates"] / nr,
                           aligned_frac=mstats["aligned"] / nr, genome=int(genome.numel()),
                           params="20-mer seeds every 10 bp on both strands (%d-mer jump table, %d MB; %d-row sampled SA, %d MB), <= 4 rows per seed, "
                                  "banded (15) Gotoh (0,-5,-8,-3) SEMI_GLOBAL, min score -90, traceback of the best window"
-                                 % (kk, fmi.ktab.numel() * 4 >> 20, dd, fmi.dssa.numel() * 4 >> 20))
+                                 % (kk, fmi.ktab.numel() * 4 >> 20, dd, fmi.dssa.numel() * 4 >> 20),
+                          plain_layout=dict(reads_per_s=world * nr / (ms_plain * 1e-3), ms=ms_plain,
+                                            note="the reference's index layout only (16-row sampled SA, no index-side tables); "
+                                                 "per-call k-mer table built inside the call; identical hits"))
+        if strong is not None:
+            # strong scaling on the config's total: each rank maps total / world reads
+            nr_s = min(nr, max(1, strong[0] // world))
+            if nr_s == nr:
+                ms_s = ms
+            else:
+                rs_sym, rs_off = rsym[:nr_s * RL], roff[:nr_s + 1]
+                fn_s = lambda: nvb.map_reads(fmi, words, rs_sym, rs_off, mparams, max_read_len=RL, ctx=ctx)
+                fn_s(); barrier()
+                tms = time_steps(fn_s, steps_m, 1, flush)
+                ms_s = max_over_ranks(sum(tms) / len(tms))
+            out[tag + "_strong"] = dict(reads_per_s=world * nr_s / (ms_s * 1e-3), ms=ms_s, reads_total=world * nr_s, reads_per_rank=nr_s,
+                                        scaling="strong", n_gpus=world)
         # e2e: pinned host reads in; hits + CIGARs out (the SAM-facing result), and once with the raw op lists for the parity check
         hr_sym = torch.empty(rsym.numel(), dtype=torch.uint8).pin_memory(); hr_sym.copy_(rsym)
         hr_off = torch.empty(roff.numel(), dtype=torch.int32).pin_memory(); hr_off.copy_(roff)
@@ -631,7 +675,8 @@ def run_b200(args):
         t0_ = time.time(); nvb.map_reads_host(*args_h, hits_h=hh_n, ops_h=hops.numpy(), max_read_len=RL, ctx=ctx); o_ms = (time.time() - t0_) * 1e3
         out[tag]["e2e_op_lists"] = dict(reads_per_s=nr / (o_ms * 1e-3), ms=o_ms, d2h_bytes=int(hh.numel() * 4 + hops.numel()))
         assert (hh.numpy() == hits_d.cpu().numpy()).all(), "host and device pipeline entry points disagree"
-        if rank == 0 and world == 1 and not args.no_cpu and only in ("", "map", "c4"):
+        do_cpu = rank == 0 and world == 1 and not args.no_cpu and only in ("", "map", "c4")
+        if do_cpu:
             po, chk, kind = load_checker()
             bwt_occ, ssa = fmi.host_arrays()
             oidx = po.Index(fmi.length, fmi.primary, np.array(fmi.L2, dtype=np.uint32), bwt_occ, ssa)
@@ -647,26 +692,53 @@ def run_b200(args):
             mism_ops = int(((got_o != wo) & valid).any(axis=1).sum())
             out[tag]["cpu"] = dict(reads_per_s=k / dt, cores=host_threads(), kind=kind, sample="first %d reads" % k)
             out[tag]["parity"] = dict(checked=k, hit_mismatches=mism, ops_mismatches=mism_ops)
-            del gh
+            cpu_reads_per_s = k / dt
         del hr_sym, hr_off, hh, hops, hcig, rsym, roff, res, hits_d, ops_d
 
         # ---- paired-end (configs[4] shape): both mates mapped independently (2 x pairs reads), then nvb_pair_hits
         if npairs > 0:
             msym, moff = gen_mates(genome, npairs, RL, 11 + rank, dev)
             pres = {}
-            def _pairs():
-                h, _, st = nvb.map_reads(fmi, words, msym, moff, mparams, max_read_len=RL, want_ops=False, ctx=ctx)
-                pres["p"] = nvb.pair_hits(h, 0, 500, ctx=ctx); pres["st"] = st
+            def _pairs(sym=msym, off=moff):
+                h, _, st = nvb.map_reads(fmi, words, sym, off, mparams, max_read_len=RL, want_ops=False, ctx=ctx)
+                pres["h"] = h; pres["p"] = nvb.pair_hits(h, 0, 500, ctx=ctx); pres["st"] = st
             _pairs()
             barrier()
-            tms = time_steps(_pairs, max(2, args.steps // 3), 1, flush)
+            tms = time_steps(_pairs, steps_m, 1, flush)
             ms = max_over_ranks(sum(tms) / len(tms))
             fl = pres["p"][:, 3]
             out[ptag] = dict(pairs_per_s=world * npairs / (ms * 1e-3), ms=ms, pairs=npairs, read_len=RL, fragment="250..499 bp, FR",
                                 concordant_frac=float(((fl & 4) != 0).float().mean().item()),
                                 both_aligned_frac=float(((fl & 3) == 3).float().mean().item()),
                                 note="mates mapped independently (seed, locate, banded Gotoh, traceback for the coordinates; op lists not kept), then nvb_pair_hits (FR, fragment <= 500)")
+            if do_cpu:
+                # parity of the paired path: the first kp pairs through the checker's mapper and mate pairing
+                kp = int(min(npairs, max(10000, 5.0 * cpu_reads_per_s / 2)))
+                mh, mo = msym[:2 * kp * RL].cpu().numpy(), moff[:2 * kp + 1].cpu().numpy().view(np.uint32)
+                t = time.time(); wh, _, _ = chk.map_reads(oidx, gh, mh, mo, pc, ops_stride=stride, threads=host_threads())
+                wp = chk.pair_hits(wh, 0, 500); dt = time.time() - t
+                got_h = pres["h"][:2 * kp].cpu().numpy().view(np.uint32).reshape(2 * kp, 6)
+                got_p = pres["p"][:kp].cpu().numpy().view(np.uint32).reshape(kp, 4)
+                out[ptag]["parity"] = dict(checked=kp, mate_hit_mismatches=int((got_h != wh.view(np.uint32).reshape(2 * kp, 6)).any(axis=1).sum()),
+                                           pair_mismatches=int((got_p != wp.view(np.uint32).reshape(kp, 4)).any(axis=1).sum()))
+                out[ptag]["cpu"] = dict(pairs_per_s=kp / dt, cores=host_threads(), kind=kind, sample="first %d pairs" % kp)
+                del mh, mo
+            if strong is not None:
+                np_s = max(1, strong[1] // world)
+                if np_s == npairs:
+                    ms_s = ms
+                else:
+                    del msym, moff; pres.clear()
+                    msym, moff = gen_mates(genome, np_s, RL, 13 + rank, dev)
+                    fn_s = lambda: _pairs(msym, moff)
+                    fn_s(); barrier()
+                    tms = time_steps(fn_s, 2, 1, flush)
+                    ms_s = max_over_ranks(sum(tms) / len(tms))
+                out[ptag + "_strong"] = dict(pairs_per_s=world * np_s / (ms_s * 1e-3), ms=ms_s, pairs_total=world * np_s, pairs_per_rank=np_s,
+                                             scaling="strong", n_gpus=world)
             del msym, moff, pres
+        if do_cpu:
+            del gh
         del words
         fmi.drop_ktab(); fmi.drop_dssa()
 
@@ -892,7 +964,7 @@ def run_b200(args):
                 fm_check("fm_c4", fmi, qsym.cpu().numpy(), qoff.cpu().numpy().view(np.uint32), ranges.cpu().numpy().view(np.uint32), nq)
             del qsym, qoff, ranges
             if only != "fm_c4":
-                map_leg(genome, fmi, args.reads, args.pairs, "map_c4", "pairs_c4")
+                map_leg(genome, fmi, args.reads, args.pairs, "map_c4", "pairs_c4", strong=(10_000_000, 50_000_000))
                 out["map_c4"]["index_build_s"] = round(c4_build_s, 2)
         except Exception as e:              # noqa: BLE001
             out["map_c4" if "fm_c4" in out else "fm_c4"] = {"error": str(e)[:300], "genome": args.c4_genome}
@@ -957,7 +1029,7 @@ def run_b200(args):
                             "path": "library default: batches >= 65536 queries share their search prefixes through a per-batch k-mer table "
                                     "rebuilt inside every timed call (no index-side structure beyond the reference's nvBWT image)",
                             "index_build_s": round(fm["build_s"], 2), "value_plain_loop": fm.get("plain_loop"),
-                            "e2e_8bit_symbols_with_offsets": fm.get("e2e"), "e2e_packed4_with_offsets": fm.get("e2e_packed4"),
+                            "e2e_copy_ceiling": fm["e2e_fixed4"].get("copy_ceiling"), "e2e_8bit_symbols_with_offsets": fm.get("e2e"), "e2e_packed4_with_offsets": fm.get("e2e_packed4"),
                             "value_with_prebuilt_kmer_jump_table": fm.get("ktab10"), "locate": fm.get("locate")})
         rl = fm_roofline("fm")
         if rl:
@@ -995,7 +1067,7 @@ def run_b200(args):
         out["fm_c4"]["workload"] = ("configs[3] index: FM-index exact 20-mer backward search, %d queries per GPU on a synthetic %d bp genome "
                                     "(1.55 GB fused nvBWT image, DRAM-resident)" % (out["fm_c4"]["queries"], args.c4_genome))
         out["fm_c4"]["cpu_baseline"] = out["fm_c4"].pop("cpu", None)
-    extra = {k: out[k] for k in ("fm_c4", "sw", "full_traceback", "banded", "map", "pairs", "map_c4", "pairs_c4") if k in out}
+    extra = {k: out[k] for k in ("fm_c4", "sw", "full_traceback", "banded", "map", "pairs", "map_c4", "pairs_c4", "map_c4_strong", "pairs_c4_strong") if k in out}
     if extra:
         line["extra"] = extra
     print(json.dumps(line))

@@ -92,6 +92,10 @@ static inline FMView make_view(const nvb_fmindex* f)
     return v;
 }
 
+// per-batch k-mer table (fm_kernels.cu): replaces f.ktab by a table built in context scratch for a batch of n strings
+// of at least max_k symbols each, when that is deeper than the caller's
+int nvb_fm_batch_table(nvb_ctx* ctx, FMView& f, uint64_t n, uint32_t max_k, cudaStream_t s);
+
 // string-set view passed by value to kernels
 struct StrSet
 {

@@ -309,7 +309,6 @@ static inline uint32_t grid_for(uint32_t n) { return (n + FM_THREADS - 1) / FM_T
 // the load-balanced walks run on a grid that just fills the device (8 CTAs of 256 threads per SM)
 static inline uint32_t walk_grid(const nvb_ctx* ctx, uint32_t n) { const uint32_t g = grid_for(n), p = (uint32_t)ctx->sm_count * 8u; return g < p ? g : p; }
 
-static int fm_batch_table(nvb_ctx* ctx, FMView& f, uint32_t n, cudaStream_t s);
 
 template <bool FROM, bool REV>
 static int fm_match_launch(nvb_ctx* ctx, const nvb_fmindex* fmi, nvb_string_set queries, uint32_t* ranges,
@@ -328,7 +327,7 @@ static int fm_match_launch(nvb_ctx* ctx, const nvb_fmindex* fmi, nvb_string_set 
     // large batches share their search prefixes through a per-batch k-mer table (context-owned scratch, fm_batch_table);
     // continued ranges and small batches stay plain
     if (!FROM && q.count >= ctx->fm_share_min)
-        if ((rc = fm_batch_table(ctx, f, q.count, s))) return rc;
+        if ((rc = nvb_fm_batch_table(ctx, f, q.count, 15u, s))) return rc;
     const bool kt = !FROM && f.ktab_k > 0;
     switch (queries.bits)
     {
@@ -390,16 +389,17 @@ fm_ktab_extend_kernel(const FMView f, const uint2* __restrict__ from, uint32_t k
 // caller-provided table (nvb_fmindex_build_ktab). It is rebuilt on EVERY call: per-batch work inside the call, not an index-side
 // structure. Cost: 4^K (K - 8) + 8 * 4^8 rank steps (6 % of the 20 n steps of 10 M 20-mers); saves K steps per query.
 enum { FM_SLOT_BT8 = 62, FM_SLOT_BTK = 63 };        // slot map in common.cuh
-static int fm_batch_table(nvb_ctx* ctx, FMView& f, uint32_t n, cudaStream_t s)
+int nvb_fm_batch_table(nvb_ctx* ctx, FMView& f, uint64_t n, uint32_t max_k, cudaStream_t s)
 {
+    if (max_k < 8u) return NVB_OK;                                       // strings shorter than the smallest table
     uint32_t K = 8;
-    while (K < 15u && (4ull << (2u * K)) <= (uint64_t)n / 2u) ++K;      // largest K with 4^K <= n / 2
+    while (K < 15u && K < max_k && (4ull << (2u * K)) <= n / 2u) ++K;    // largest K with 4^K <= n / 2
     // an index that would stay L2-resident must not be pushed out by its own table: index + table within half of L2
     // (each die keeps its own copy of what its SMs read). configs[1] (50 MB): K = 10 -> 12.4 G lookups/s, K = 11 -> 11.5
     const size_t idx_bytes = nvb_bwt_occ_words(f.length) * sizeof(uint32_t);
     if (idx_bytes <= ctx->l2_bytes * 3 / 4)
         while (K > 8u && idx_bytes + (sizeof(uint2) << (2u * K)) > ctx->l2_bytes / 2) --K;
-    { const char* e = getenv("NVB_FM_TABLE_K"); if (e) { const uint32_t k = (uint32_t)atoi(e); if (k >= 8u && k <= 15u) K = k; } }   // tuning aid (tools/fm_probe.py)
+    { const char* e = getenv("NVB_FM_TABLE_K"); if (e) { const uint32_t k = (uint32_t)atoi(e); if (k >= 8u && k <= 15u && k <= max_k) K = k; } }   // tuning aid (tools/fm_probe.py)
     if (f.ktab_k >= K) return NVB_OK;                                    // the caller's table is at least as deep
     int rc; void *t8 = nullptr, *tk = nullptr;
     if ((rc = nvb_stage(ctx, FM_SLOT_BT8, sizeof(uint2) << 16, &t8))) return rc;

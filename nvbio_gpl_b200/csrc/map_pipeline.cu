@@ -473,7 +473,7 @@ extern "C" int nvb_map_reads(nvb_ctx* ctx, const nvb_fmindex* fmi, const uint32_
     const uint32_t tb_stride = ops ? ops_stride : ((2u * maxL + mp->band + 16u + 15u) & ~15u);
     if ((tb_stride & 15u) || tb_stride < 2u * maxL + mp->band || (ops && (((uintptr_t)ops) & 15u))) return NVB_ERR_ARG;
     cudaStream_t s = (cudaStream_t)stream;
-    const FMView f = make_view(fmi);
+    FMView f = make_view(fmi);
     const StrSet reads = make_set(reads_set);
     const uint32_t G = fmi->length;
     int rc;
@@ -490,6 +490,11 @@ extern "C" int nvb_map_reads(nvb_ctx* ctx, const nvb_fmindex* fmi, const uint32_
     const uint32_t cand_chunk = 4u << 20, tb_chunk = 2u << 20;
 
     uint32_t* d_num; MAP_STAGE(S_NUM, 64, d_num);
+    // the seeds of the whole call share their first steps through one per-call k-mer table (as nvb_fm_match does per batch)
+    {
+        const uint64_t seeds = (uint64_t)n_total * ((uint64_t)(maxL >= mp->seed_len ? (maxL - mp->seed_len) / mp->seed_interval + 1u : 0u) * (mp->both_strands ? 2u : 1u));
+        if (seeds >= ctx->fm_share_min && (rc = nvb_fm_batch_table(ctx, f, seeds, mp->seed_len, s))) return rc;
+    }
     MapTrace trace(s);
     for (uint32_t r0 = 0; r0 < n_total; r0 += (uint32_t)rb)
     {

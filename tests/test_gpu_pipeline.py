@@ -12,6 +12,16 @@ import map_util
 pytestmark = pytest.mark.gpu
 
 
+@pytest.fixture(autouse=True, params=["default", "share_all"])
+def sharing_mode(request):
+    """every test of this file runs twice: with the library's default (the per-call k-mer table of nvb_map_reads only for
+    calls of >= 65536 seeds) and with the table forced for every call"""
+    ctx = nvb.Context.default(0)
+    ctx.fm_batch_sharing(1 if request.param == "share_all" else 1 << 16)
+    yield request.param
+    ctx.fm_batch_sharing(1 << 16)
+
+
 def hits_np(t):
     return t.cpu().numpy().view(np.uint32).reshape(-1, 6).copy().view(nvb.HIT_DT).reshape(-1)
 
@@ -76,6 +86,23 @@ def test_map_reads(oracle, kind, scores, band, max_hits, max_range, both, min_sc
         got = "".join("%d%s" % (int(e) >> 2, "MID"[int(e) & 3]) for e in cig[i, :int(n_cig[i])])
         assert got == po.rle(fwd), (i, got, po.rle(fwd))
     assert (want_hits["flags"] & 2).astype(bool).sum() > 2000 or min_score >= 0
+
+
+@pytest.mark.parametrize("seed_len,interval", [(6, 12), (9, 7), (12, 10), (31, 16)])
+def test_map_reads_seed_lengths(oracle, seed_len, interval):
+    """seeds shorter than, equal to and longer than the depth of the per-call k-mer table (no table below 8 symbols)"""
+    rng = np.random.default_rng(seed_len)
+    genome = rng.integers(0, 4, 20000).astype(np.uint8)
+    fmi, oidx = gu.fm_index_pair(oracle, genome)
+    words = nvb.pack_genome(torch.from_numpy(genome).to(gu.dev()))
+    sym, off = map_util.make_reads(rng, genome, 1500)
+    pc = map_util.map_params(15, po.GOTOH, (0, -5, -8, -3), seed_len, interval, 3, 0, 1, -60)
+    want_hits, want_ops, want_nc = oracle.map_reads(oidx, genome, sym, off, pc)
+    params = nvb.MapParams(nvb.GotohAligner(nvb.SEMI_GLOBAL, 0, -5, -8, -3), seed_len, interval, 3, 0, 15, True, -60)
+    rs = gu.sset(sym, off)
+    hits, ops, stats = nvb.map_reads(fmi, words, rs.symbols, rs.offsets, params)
+    assert same(hits_np(hits), ops.cpu().numpy(), want_hits, want_ops)
+    assert stats["candidates"] == int(want_nc.sum())
 
 
 def test_map_reads_edges(oracle):
