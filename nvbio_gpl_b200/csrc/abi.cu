@@ -343,6 +343,18 @@ static int fm_match_host_impl(nvb_ctx* ctx, const nvb_fmindex* fmi_d, const uint
     if (!ctx->host_ev[0])
         for (int i = 0; i < 3 * NVB_HOST_SETS; ++i) NVB_CUDA(ctx, cudaEventCreateWithFlags(&ctx->host_ev[i], cudaEventDisableTiming));
     cudaStream_t s_in = ctx->aux[0], s_k = ctx->stream, s_out = ctx->aux[1];
+    // each chunk's nvb_fm_match builds its own k-mer table. One table for the whole call was measured and is SLOWER end to
+    // end (2.85 vs 2.3-2.5 ms for 10 M 20-mers, tools/host_probe2.py): the call is bound by the two copy directions sharing
+    // the bus, not by the kernels, and shorter kernels only move the D2H copies to where they collide more with the H2D ones
+    // NVB_HOST_TRACE=1: per-chunk completion times of the three stages on stderr (tuning aid, tools/host_probe2.py)
+    const bool trace = getenv("NVB_HOST_TRACE") != nullptr;
+    std::vector<cudaEvent_t> tev;
+    if (trace)
+    {
+        tev.resize(1 + 3 * (size_t)n_chunks);
+        for (auto& e : tev) cudaEventCreate(&e);
+        cudaEventRecord(tev[0], s_in);
+    }
     for (uint32_t k = 0; k < n_chunks; ++k)
     {
         const int b = (int)(k % (uint32_t)n_sets);
@@ -366,6 +378,7 @@ static int fm_match_host_impl(nvb_ctx* ctx, const nvb_fmindex* fmi_d, const uint
         NVB_CUDA(ctx, cudaStreamWaitEvent(s_out, ev_k, 0));
         NVB_CUDA(ctx, cudaMemcpyAsync(ranges_h + 2 * (size_t)c0, d_rng[b], sizeof(uint32_t) * 2 * (size_t)cnt, cudaMemcpyDeviceToHost, s_out));
         NVB_CUDA(ctx, cudaEventRecord(ev_out, s_out));
+        if (trace) { cudaEventRecord(tev[1 + 3 * k], s_in); cudaEventRecord(tev[2 + 3 * k], s_k); cudaEventRecord(tev[3 + 3 * k], s_out); }
     }
     #undef SPAN_BEGIN
     #undef SPAN_END
@@ -373,6 +386,16 @@ static int fm_match_host_impl(nvb_ctx* ctx, const nvb_fmindex* fmi_d, const uint
     NVB_CUDA(ctx, cudaStreamSynchronize(s_out));
     NVB_CUDA(ctx, cudaStreamSynchronize(s_in));
     NVB_CUDA(ctx, cudaStreamSynchronize(s_k));
+    if (trace)
+    {
+        for (uint32_t k = 0; k < n_chunks; ++k)
+        {
+            float a = 0, b = 0, c = 0;
+            cudaEventElapsedTime(&a, tev[0], tev[1 + 3 * k]); cudaEventElapsedTime(&b, tev[0], tev[2 + 3 * k]); cudaEventElapsedTime(&c, tev[0], tev[3 + 3 * k]);
+            fprintf(stderr, "[nvb host trace] chunk %2u: in %.3f  kernel %.3f  out %.3f ms\n", k, a, b, c);
+        }
+        for (auto& e : tev) cudaEventDestroy(e);
+    }
     return NVB_OK;
 }
 

@@ -96,6 +96,20 @@ static inline FMView make_view(const nvb_fmindex* f)
 // of at least max_k symbols each, when that is deeper than the caller's
 int nvb_fm_batch_table(nvb_ctx* ctx, FMView& f, uint64_t n, uint32_t max_k, cudaStream_t s);
 
+// the host entry points cut one batch into chunks: the table is built once for the whole batch and handed to the chunks
+// as the k-mer table of a local copy of the caller's descriptor
+static inline int nvb_with_batch_table(nvb_ctx* ctx, const nvb_fmindex* fmi, uint64_t n, uint32_t max_k, cudaStream_t s, nvb_fmindex* local)
+{
+    *local = *fmi;
+    // (a descriptor the entry points would refuse is left to them)
+    if (n < ctx->fm_share_min || !fmi->bwt_occ || fmi->occ_int != 64u || (((uintptr_t)fmi->bwt_occ) & 31u)) return NVB_OK;
+    FMView v = make_view(fmi);
+    const int rc = nvb_fm_batch_table(ctx, v, n, max_k, s);
+    if (rc) return rc;
+    local->ktab = (const uint32_t*)v.ktab; local->ktab_k = v.ktab_k;
+    return NVB_OK;
+}
+
 // string-set view passed by value to kernels
 struct StrSet
 {

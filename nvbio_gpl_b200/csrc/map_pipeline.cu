@@ -672,7 +672,7 @@ extern "C" int nvb_map_reads_host(nvb_ctx* ctx, const nvb_fmindex* fmi, const ui
                                   nvb_read_hit* hits_h, uint8_t* ops_h, uint32_t ops_stride,
                                   uint16_t* cigar_h, uint32_t cigar_stride, nvb_map_stats* stats)
 {
-    if (!ctx || !mp) return NVB_ERR_ARG;
+    if (!ctx || !mp || !fmi) return NVB_ERR_ARG;
     if (stats) { stats->seeds = stats->seed_hits = stats->candidates = stats->aligned = 0; }
     if (n == 0) return NVB_OK;
     if (!reads_h || !off_h || !hits_h || (cigar_h && cigar_stride == 0)) return NVB_ERR_ARG;
@@ -713,6 +713,15 @@ extern "C" int nvb_map_reads_host(nvb_ctx* ctx, const nvb_fmindex* fmi, const ui
         return NVB_OK;
     };
     if ((rc = copy_in(0))) return rc;
+    // one k-mer table for the seeds of the whole call, sized on the longest read of the first batch
+    nvb_fmindex fmi_call;
+    {
+        uint32_t maxL0 = 0;
+        for (uint32_t i = 0; i < cap; ++i) { const uint32_t l = off_h[i + 1] - off_h[i]; if (l > maxL0) maxL0 = l; }
+        const uint64_t per_read = (mp->seed_len && mp->seed_interval && maxL0 >= mp->seed_len ? (maxL0 - mp->seed_len) / mp->seed_interval + 1u : 0u) * (mp->both_strands ? 2u : 1u);
+        if ((rc = nvb_with_batch_table(ctx, fmi, (uint64_t)n * per_read, mp->seed_len, s_k, &fmi_call))) return rc;
+        fmi = &fmi_call;
+    }
     for (uint32_t k = 0; k < n_batches; ++k)
     {
         const int b = (int)(k & 1u) % n_sets;
