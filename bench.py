@@ -903,12 +903,19 @@ def run_b200(args):
                                  gcups_equiv=world * nt * M * W / (ms * 1e-3) / 1e9)
                 # end to end: nvb_batch_traceback_host(band) on the checked prefix (alignments + op lists back on the host)
                 stride = int(bufs[1].shape[1])
-                t0_ = time.time()
-                h_out, h_ops, h_nops = nvb.batch_traceback_host(a, W, 16, hP.numpy()[:kt * M], hPo.numpy().view(np.uint32)[:kt + 1], hT.numpy()[:kt * N],
-                                                                hTo.numpy().view(np.uint32)[:kt + 1], stride, ctx=ctx)
-                e_ms = (time.time() - t0_) * 1e3
-                res[name]["e2e"] = dict(pairs_per_s=kt / (e_ms * 1e-3), ms=e_ms, pairs=kt, d2h_bytes=int(kt * (20 + 4 + stride)),
-                                        call="nvb_batch_traceback_host(band = 15, checkpoints = 16), pageable result arrays, wall clock")
+                ph_out = torch.empty(kt * 20, dtype=torch.uint8).pin_memory()
+                ph_ops = torch.empty((kt, stride), dtype=torch.uint8).pin_memory()
+                ph_n = torch.empty(kt, dtype=torch.int32).pin_memory()
+                tb_h = lambda: nvb.batch_traceback_host(a, W, 16, hP.numpy()[:kt * M], hPo.numpy().view(np.uint32)[:kt + 1], hT.numpy()[:kt * N],
+                                                        hTo.numpy().view(np.uint32)[:kt + 1], stride, ctx=ctx, out=ph_out.numpy().view(nvb.ALN_DT),
+                                                        ops=ph_ops.numpy(), n_ops=ph_n.numpy().view(np.uint32))
+                tb_h()
+                et = []
+                for _ in range(3):
+                    t0_ = time.time(); h_out, h_ops, h_nops = tb_h(); et.append((time.time() - t0_) * 1e3)
+                e_ms = min(et)
+                res[name]["e2e"] = dict(pairs_per_s=kt / (e_ms * 1e-3), ms=e_ms, pairs=kt, h2d_bytes=int(kt * (M + N + 8)), d2h_bytes=int(kt * (20 + 4 + stride)),
+                                        call="nvb_batch_traceback_host(band = 15, checkpoints = 16), pinned host buffers, wall clock, best of 3 after one warm-up call")
                 if do_cpu:
                     oa = po.aligner(getattr(po, okind), a.type, osc)
                     t = time.time(); w_out, w_ops, w_n = chk.banded_traceback(oa, W, 16, Ph[:kt * M], Poh[:kt + 1], Th[:kt * N], Toh[:kt + 1], threads=host_threads()); dt = time.time() - t

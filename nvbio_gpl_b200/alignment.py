@@ -298,12 +298,17 @@ def batch_score_host(aligner, band, pat, pat_off, txt, txt_off, sinks_h=None, de
     return sinks_h
 
 
-def batch_traceback_host(aligner, band, checkpoints, pat, pat_off, txt, txt_off, ops_stride, device=0, ctx=None):
+def batch_traceback_host(aligner, band, checkpoints, pat, pat_off, txt, txt_off, ops_stride, device=0, ctx=None,
+                         out=None, ops=None, n_ops=None):
+    """host arrays in, host arrays out (``nvb_batch_traceback_host``). out / ops / n_ops: caller-owned result arrays (ALN_DT [n],
+    uint8 [n, ops_stride], uint32 [n]); pinned ones (``nvb_host_alloc`` / ``torch.Tensor.pin_memory``) avoid the bounce copy"""
     ctx = ctx or Context.default(device)
     n = len(pat_off) - 1
-    out = np.empty(n, dtype=ALN_DT)
-    ops = np.zeros((n, ops_stride), dtype=np.uint8)
-    n_ops = np.empty(n, dtype=np.uint32)
+    out = np.empty(n, dtype=ALN_DT) if out is None else out
+    ops = np.zeros((n, ops_stride), dtype=np.uint8) if ops is None else ops
+    n_ops = np.empty(n, dtype=np.uint32) if n_ops is None else n_ops
+    if len(out) < n or ops.shape[0] < n or ops.shape[1] != ops_stride or len(n_ops) < n:
+        raise ValueError("result arrays too small for %d pairs" % n)
     check(lib().nvb_batch_traceback_host(ctx.h, aligner.c(), band, checkpoints, pat.ctypes.data, pat_off.ctypes.data,
                                          txt.ctypes.data, txt_off.ctypes.data, n, out.ctypes.data, ops.ctypes.data,
                                          ops_stride, n_ops.ctypes.data), ctx.h)

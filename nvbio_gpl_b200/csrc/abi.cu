@@ -37,6 +37,7 @@ extern "C" int nvb_ctx_create(int device, nvb_ctx** out)
     c->device = device;
     c->sm_count = prop.multiProcessorCount;
     c->l2_bytes = (size_t)prop.l2CacheSize;
+    { const char* e = getenv("NVB_FM_TMA"); c->fm_tma = e ? atoi(e) != 0 : 1; }
     { const char* e = getenv("NVB_FM_SHARE_MIN"); c->fm_share_min = e ? (uint32_t)strtoul(e, nullptr, 10) : (1u << 16); }
     if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return NVB_ERR_CUDA; }
     for (int i = 0; i < 2; ++i)

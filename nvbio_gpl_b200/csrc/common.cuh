@@ -33,6 +33,7 @@ struct nvb_ctx
     size_t       d_worklist_cap;
     int          sm_count;
     size_t       l2_bytes;
+    int          fm_tma;       // fm_match stages its queries by TMA bulk copy (NVB_FM_TMA, default 1)
     cudaEvent_t  host_ev[12];  // event chain of the pipelined *_host entry points (3 per buffer set)
     cudaStream_t aux[2];       // the *_host entry points pipeline chunks over these (H2D of one chunk under the kernel / D2H of another)
 };

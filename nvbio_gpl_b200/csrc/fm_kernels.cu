@@ -20,7 +20,7 @@
 // shared memory with coalesced 16-byte loads, so the dependent loop only touches the index.
 // ---------------------------------------------------------------------------------------------
 // REV: match_reverse (fmindex_inl.h:252-278) -- the same loop consuming the pattern front to back.
-template <int BITS, bool FROM, bool KTAB, bool REV>
+template <int BITS, bool FROM, bool KTAB, bool REV, bool TMA>
 __global__ void __launch_bounds__(FM_THREADS)
 fm_match_kernel(const FMView f, const StrSet q, uint32_t* __restrict__ ranges)
 {
@@ -47,9 +47,33 @@ fm_match_kernel(const FMView f, const StrSet q, uint32_t* __restrict__ ranges)
         skew = (uint32_t)(gaddr & 15u);
         const uint4* g = (const uint4*)(gaddr - skew);
         const uint32_t n16 = (span_len + skew + 15u) >> 4;
-        uint4* s = (uint4*)s_sym;
-        for (uint32_t i = threadIdx.x; i < n16; i += FM_THREADS) s[i] = __ldg(g + i);
-        __syncthreads();
+        if (TMA && n16)
+        {
+            // one bulk copy (TMA, cp.async.bulk -> UBLKCP) of the CTA's span, issued by one thread and awaited on an mbarrier
+            // by all: the span is contiguous, 16-byte aligned on both sides and a multiple of 16 bytes long
+            __shared__ __align__(8) uint64_t s_bar;
+            const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&s_bar);
+            if (threadIdx.x == 0)
+            {
+                asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"(bar));
+                asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+                const uint32_t bytes = n16 << 4;
+                asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar), "r"(bytes) : "memory");
+                asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                             :: "r"((uint32_t)__cvta_generic_to_shared(s_sym)), "l"(g), "r"(bytes), "r"(bar) : "memory");
+            }
+            __syncthreads();                                  // the barrier is initialised (and the LUT / L2 tables written)
+            uint32_t done = 0;
+            while (!done)
+                asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0; selp.u32 %0, 1, 0, p; }"
+                             : "=r"(done) : "r"(bar) : "memory");
+        }
+        else if (!TMA)
+        {
+            uint4* s = (uint4*)s_sym;
+            for (uint32_t i = threadIdx.x; i < n16; i += FM_THREADS) s[i] = __ldg(g + i);
+            __syncthreads();
+        }
     }
     // symbol at absolute symbol index a of the set
     auto symbol = [&](uint32_t a) -> uint32_t
@@ -329,16 +353,19 @@ static int fm_match_launch(nvb_ctx* ctx, const nvb_fmindex* fmi, nvb_string_set 
     if (!FROM && q.count >= ctx->fm_share_min)
         if ((rc = nvb_fm_batch_table(ctx, f, q.count, 15u, s))) return rc;
     const bool kt = !FROM && f.ktab_k > 0;
+    // the CTA's query span goes to shared memory by one TMA bulk copy (NVB_FM_TMA=0: by per-thread 16-byte loads)
+    #define FM_LAUNCH(B, K, T) fm_match_kernel<B, FROM, K, REV, T><<<grid, FM_THREADS, 0, s>>>(f, q, ranges)
+    #define FM_LAUNCH_B(B) do { if (kt) { if (ctx->fm_tma) FM_LAUNCH(B, true, true); else FM_LAUNCH(B, true, false); } \
+                                else    { if (ctx->fm_tma) FM_LAUNCH(B, false, true); else FM_LAUNCH(B, false, false); } } while (0)
     switch (queries.bits)
     {
-    case 8: if (kt) fm_match_kernel<8, FROM, true, REV><<<grid, FM_THREADS, 0, s>>>(f, q, ranges);
-            else    fm_match_kernel<8, FROM, false, REV><<<grid, FM_THREADS, 0, s>>>(f, q, ranges); break;
-    case 4: if (kt) fm_match_kernel<4, FROM, true, REV><<<grid, FM_THREADS, 0, s>>>(f, q, ranges);
-            else    fm_match_kernel<4, FROM, false, REV><<<grid, FM_THREADS, 0, s>>>(f, q, ranges); break;
-    case 2: if (kt) fm_match_kernel<2, FROM, true, REV><<<grid, FM_THREADS, 0, s>>>(f, q, ranges);
-            else    fm_match_kernel<2, FROM, false, REV><<<grid, FM_THREADS, 0, s>>>(f, q, ranges); break;
+    case 8: FM_LAUNCH_B(8); break;
+    case 4: FM_LAUNCH_B(4); break;
+    case 2: FM_LAUNCH_B(2); break;
     default: return NVB_ERR_ARG;
     }
+    #undef FM_LAUNCH_B
+    #undef FM_LAUNCH
     NVB_LAUNCHED(ctx);
     return NVB_OK;
 }
