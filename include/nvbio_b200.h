@@ -319,6 +319,17 @@ int nvb_ops_to_cigar(nvb_ctx* ctx, const uint8_t* ops, uint32_t ops_stride, cons
                      uint32_t n, uint16_t* cigar, uint32_t cigar_stride, uint32_t* n_cigar,
                      void* stream);
 
+/* nvBowtie's MDS byte-code (the device-side precursor of SAM's MD:Z tag; finish_alignment_kernel,
+ * nvBowtie/bowtie2/cuda/traceback_inl.h:555-690, op codes nvbio/io/alignments.h:37-42, turned into the MD string by
+ * nvbio/io/output/output_sam.cpp:216-289) and the edit distance, from push-order op lists. Per alignment mds_stride
+ * bytes: [len lo, len hi], then (0, run <= 255) for equal symbols | (1, read symbol) for a mismatch |
+ * (2 insertion | 3 deletion, run & 255, the run's read / text symbols). alignments[i].source = (first text symbol,
+ * first pattern symbol) of the alignment; mds_len (may be NULL) receives the full length, which may exceed mds_stride
+ * (the stored code is then truncated); edit_distance may be NULL. 8/4/2-bit string sets. */
+int nvb_ops_to_mds(nvb_ctx* ctx, const uint8_t* ops, uint32_t ops_stride, const uint32_t* n_ops, uint32_t n,
+                   nvb_string_set patterns, nvb_string_set texts, const nvb_alignment* alignments,
+                   uint8_t* mds, uint32_t mds_stride, uint32_t* mds_len, uint32_t* edit_distance, void* stream);
+
 /* Quality-aware scoring schemes: the scheme interfaces of nvbio/alignment/alignment.h:411-436 (GotohScoringScheme) and :488-505
  * (SmithWatermanScoringScheme) evaluate match(q) and mismatch(a, b, q) at the quality q of each PATTERN position
  * (sw_inl.h:470-472, gotoh_inl.h:666,729, sw_banded_inl.h:391, gotoh_banded_inl.h:461); nvBowtie's scheme is one
@@ -412,6 +423,11 @@ int nvb_pack_2bit(nvb_ctx* ctx, const uint8_t* symbols_d, uint32_t n, uint32_t* 
 int nvb_map_reads(nvb_ctx* ctx, const nvb_fmindex* fmi_d, const uint32_t* genome_words_d, nvb_string_set reads,
                   uint32_t max_read_len, const nvb_map_params* params, uint32_t reads_per_batch,
                   nvb_read_hit* hits_d, uint8_t* ops_d, uint32_t ops_stride, nvb_map_stats* stats_h, void* stream);
+/* the same byte-code for the hits of nvb_map_reads: read r against the genome from hits_d[r].begin on the hit's strand
+ * (unaligned reads get the empty code [2, 0]); reads = the set that was mapped, ops_d / ops_stride = its op lists */
+int nvb_map_hits_to_mds(nvb_ctx* ctx, const nvb_read_hit* hits_d, const uint8_t* ops_d, uint32_t ops_stride,
+                        nvb_string_set reads, const uint32_t* genome_words_d, uint8_t* mds_d, uint32_t mds_stride,
+                        uint32_t* mds_len_d, uint32_t* edit_distance_d, void* stream);
 /* host buffers in / out, pipelined over read batches (reads of batch k+1 in, batch k mapped, results of batch k-1
  * out); synchronous. ops_h and cigar_h are both optional: cigar_h receives cigar_stride uint16 entries per read in
  * io::Cigar encoding (op | len << 2, forward order), the entry count in bits 8.. of the hit's flags; ops_stride is

@@ -16,6 +16,6 @@ from .alignment import (  # noqa: F401
     batch_alignment_score, batch_banded_alignment_score, batch_alignment_score_noalloc, NOALLOC_SCRATCH_BYTES,
     MyersTag, MyersAligner, batch_banded_myers_score, batch_alignment_score_best2, MYERS_BATCH_MIN_SCORE,
     batch_alignment_traceback, batch_banded_alignment_traceback,
-    batch_score_host, batch_traceback_host, ops_to_cigar, SINK_DT, ALN_DT,
+    batch_score_host, batch_traceback_host, ops_to_cigar, ops_to_mds, mds_to_md_string, SINK_DT, ALN_DT,
 )
-from .pipeline import MapParams, map_reads, map_reads_host, map_reads_host_multi, match_host_multi, pack_genome, ops_stride_for, HIT_DT, FLAG_REVERSE, FLAG_ALIGNED, pair_hits, PAIR_DT, PAIR_MATE1, PAIR_MATE2, PAIR_CONCORDANT  # noqa: F401
+from .pipeline import MapParams, map_reads, map_reads_host, map_reads_host_multi, match_host_multi, pack_genome, ops_stride_for, HIT_DT, FLAG_REVERSE, FLAG_ALIGNED, pair_hits, PAIR_DT, PAIR_MATE1, PAIR_MATE2, PAIR_CONCORDANT, map_hits_to_mds  # noqa: F401

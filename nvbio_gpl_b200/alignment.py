@@ -287,6 +287,46 @@ def ops_to_cigar(ops, n_ops, cigar_stride=None, ctx=None):
     return cigar, n_cigar
 
 
+def ops_to_mds(ops, n_ops, patterns, texts, alignments, mds_stride=None, ctx=None):
+    """nvBowtie's MDS byte-code and the edit distance of every alignment (``nvb_ops_to_mds``; finish_alignment_kernel,
+    nvBowtie/bowtie2/cuda/traceback_inl.h:555-690). alignments: the int32 [n,5] records of a traceback call (their source
+    gives the first aligned text / pattern symbol). Returns (mds uint8 [n, mds_stride], mds_len int32 [n], edit_distance int32 [n])."""
+    ctx = _ctx(ops, ctx)
+    n, stride = ops.shape
+    if mds_stride is None:
+        mds_stride = 2 + 3 * stride
+    mds = torch.zeros((n, mds_stride), dtype=torch.uint8, device=ops.device)
+    mds_len = torch.empty(n, dtype=torch.int32, device=ops.device)
+    ed = torch.empty(n, dtype=torch.int32, device=ops.device)
+    check(lib().nvb_ops_to_mds(ctx.h, ops.data_ptr(), stride, n_ops.data_ptr(), n, patterns.c(), texts.c(), alignments.data_ptr(),
+                               mds.data_ptr(), mds_stride, mds_len.data_ptr(), ed.data_ptr(), _lib.current_stream_ptr()), ctx.h)
+    return mds, mds_len, ed
+
+
+def mds_to_md_string(mds):
+    """SAM MD:Z text of one MDS byte-code, as SamOutput::generate_md_string writes it (nvbio/io/output/output_sam.cpp:216-289):
+    match runs as numbers, a mismatch as the READ's symbol (what the byte-code stores), a deletion as ^symbols followed by 0,
+    insertions skipped. Host-side formatting, not part of the device path. Returns (md, mismatches, gap_opens, gap_extensions)."""
+    m = [int(v) for v in mds]
+    n = m[0] | (m[1] << 8)
+    out, mm, gapo, gape, i = [], 0, 0, 0, 2
+    while i < n:
+        op = m[i]; i += 1
+        if op == 0:
+            run = m[i]; i += 1
+            while i + 1 < n and m[i] == 0:        # a run longer than 255 continues in further MATCH records
+                run += m[i + 1]; i += 2
+            out.append(str(run))
+        elif op == 1:
+            out.append("ACGTN"[min(m[i], 4)]); i += 1; mm += 1
+        elif op == 2:
+            l = m[i]; i += 1 + l; gapo += 1; gape += l - 1
+        else:
+            l = m[i]; i += 1
+            out.append("^" + "".join("ACGTN"[min(c, 4)] for c in m[i:i + l]) + "0"); i += l; gapo += 1; gape += l - 1
+    return "".join(out), mm, gapo, gape
+
+
 # host-buffer forms --------------------------------------------------------------------------------
 def batch_score_host(aligner, band, pat, pat_off, txt, txt_off, sinks_h=None, device=0, ctx=None):
     ctx = ctx or Context.default(device)

@@ -134,6 +134,23 @@ def match_host_multi(ctxs, fmis, symbols_h, offsets_h=None, query_len=0, count=N
     return ranges_h
 
 
+def map_hits_to_mds(hits, ops, symbols, offsets, genome_words, mds_stride=None, ctx=None):
+    """MDS byte-code + edit distance of the hits of ``map_reads`` (``nvb_map_hits_to_mds``): read r against the genome from
+    hits[r].begin on the hit's strand. Returns (mds uint8 [n, mds_stride], mds_len int32 [n], edit_distance int32 [n])."""
+    if not hits.is_cuda:
+        raise RuntimeError("map_hits_to_mds needs CUDA tensors; the hot path has no CPU fallback")
+    ctx = ctx or Context.default(hits.device.index)
+    n, stride = ops.shape
+    if mds_stride is None:
+        mds_stride = 2 + 3 * stride
+    mds = torch.zeros((n, mds_stride), dtype=torch.uint8, device=hits.device)
+    mds_len = torch.empty(n, dtype=torch.int32, device=hits.device)
+    ed = torch.empty(n, dtype=torch.int32, device=hits.device)
+    check(lib().nvb_map_hits_to_mds(ctx.h, hits.data_ptr(), ops.data_ptr(), stride, StringSetC(symbols.data_ptr(), offsets.data_ptr(), n, 8), genome_words.data_ptr(),
+                                    mds.data_ptr(), mds_stride, mds_len.data_ptr(), ed.data_ptr(), current_stream_ptr()), ctx.h)
+    return mds, mds_len, ed
+
+
 def pair_hits(hits, min_frag_len=0, max_frag_len=500, ctx=None):
     """mate pairing (``nvb_pair_hits``) over the device hits of 2 n independently mapped mates laid out pair by pair; forward-reverse
     policy with nvBowtie's fragment window (params.h:147-152). Returns int32 [n, 4] viewable as PAIR_DT."""

@@ -141,6 +141,9 @@ int ORC(fm_match_approx)(const orc_fmindex* fmi, const uint8_t* symbols, const u
                          int find_exact, uint32_t cap, uint32_t* ranges, uint32_t* counts, int threads);
 typedef struct { int32_t score; uint32_t frag_begin, frag_end, flags; } orc_pair_hit;
 int ORC(pair_hits)(const orc_read_hit* hits, uint32_t n_pairs, uint32_t min_frag, uint32_t max_frag, orc_pair_hit* out);
+/* MDS byte-code + edit distance of one alignment (nvBowtie/bowtie2/cuda/traceback_inl.h:555-690) */
+int ORC(ops_to_mds)(const uint8_t* ops, uint32_t n_ops, const uint8_t* pattern, const uint8_t* text, uint32_t j0, uint32_t k0,
+                    uint8_t* mds, uint32_t cap, uint32_t* mds_len_out, uint32_t* ed_out);
 
 #ifdef __cplusplus
 }

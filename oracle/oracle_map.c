@@ -214,3 +214,60 @@ int ORC(fm_match_approx)(const orc_fmindex* fmi, const uint8_t* symbols, const u
     }
     return 0;
 }
+
+/*
+ * MDS byte-code + edit distance of one alignment: a literal restatement of the CIGAR loop of finish_alignment_kernel
+ * (nvBowtie/bowtie2/cuda/traceback_inl.h:555-690; the reference function is a __global__ kernel over its pipeline state, not
+ * host-callable: "parity unpinned", checked against hand-worked vectors and against the reference's own consumer,
+ * nvbio/io/output/output_sam.cpp:216-289, restated in tests). ops: push order (the last op of the alignment first), as the
+ * reference's cigar_vector is indexed back to front (:574-575); runs longer than a 14-bit io::Cigar length are split.
+ * (j0, k0): first aligned pattern / text symbol (the reference starts at j = 0, k = cigar_offset, :572).
+ */
+int ORC(ops_to_mds)(const uint8_t* ops, uint32_t n_ops, const uint8_t* pattern, const uint8_t* text, uint32_t j0, uint32_t k0,
+                    uint8_t* mds, uint32_t cap, uint32_t* mds_len_out, uint32_t* ed_out)
+{
+    enum { SUB = 0, INS = 1, DEL = 2, CLP = 3, MDS_MATCH = 0, MDS_MISMATCH = 1, MDS_INSERTION = 2, MDS_DELETION = 3, MDS_INVALID = 4 };
+    uint8_t* local = (uint8_t*)malloc(2 + 3 * (size_t)n_ops + 8);
+    if (!local) return -1;
+    uint32_t mds_len = 2, ed = 0; uint8_t mds_op = MDS_INVALID;                              /* :566-570 */
+    uint32_t j = j0, k = k0, i = n_ops;
+    while (i > 0)
+    {
+        const uint32_t t = ops[i - 1] & 3u; uint32_t l = 1;
+        while (l < i && (ops[i - 1 - l] & 3u) == t && l < 16383u) ++l;
+        i -= l;
+        if (t == INS || t == DEL || t == CLP)                                                 /* :582-590 */
+        {
+            mds_op = t == DEL ? MDS_DELETION : MDS_INSERTION;
+            local[mds_len++] = mds_op;
+            local[mds_len++] = (uint8_t)l;
+        }
+        for (uint32_t n = 0; n < l; ++n)                                                      /* :592-641 */
+        {
+            j += (t == SUB || t == INS || t == CLP) ? 1u : 0u;
+            k += (t == SUB || t == DEL) ? 1u : 0u;
+            const uint8_t readc = j > 0 ? pattern[j - 1] : 255u;
+            const uint8_t refc  = k > 0 ? text[k - 1] : 255u;
+            if (t == SUB)
+            {
+                if (readc == refc)
+                {
+                    if (mds_op == MDS_MATCH && local[mds_len - 1] < 255) local[mds_len - 1]++;
+                    else { local[mds_len++] = mds_op = MDS_MATCH; local[mds_len++] = 1; }
+                }
+                else { local[mds_len++] = mds_op = MDS_MISMATCH; local[mds_len++] = readc; ++ed; }
+            }
+            else
+            {
+                local[mds_len++] = t == DEL ? refc : readc;
+                if (t != CLP) ++ed;
+            }
+        }
+    }
+    local[0] = (uint8_t)(mds_len & 0xFF); local[1] = (uint8_t)(mds_len >> 8);               /* :684-685 */
+    memcpy(mds, local, mds_len < cap ? mds_len : cap);
+    free(local);
+    if (mds_len_out) *mds_len_out = mds_len;
+    if (ed_out) *ed_out = ed;
+    return 0;
+}

@@ -316,6 +316,16 @@ class Oracle:
         assert rc == 0, rc
         return out
 
+    def ops_to_mds(self, ops, n_ops, pattern, text, j0=0, k0=0, cap=4096):
+        """MDS byte-code (uint8 array of its full length) and edit distance of one alignment (traceback_inl.h:555-690)"""
+        ops = np.ascontiguousarray(ops, dtype=np.uint8); pattern = np.ascontiguousarray(pattern, dtype=np.uint8)
+        text = np.ascontiguousarray(text, dtype=np.uint8)
+        out = np.zeros(cap, dtype=np.uint8); ln = C.c_uint32(0); ed = C.c_uint32(0)
+        rc = self._f("ops_to_mds")(_ptr(ops), C.c_uint32(int(n_ops)), _ptr(pattern), _ptr(text), C.c_uint32(j0), C.c_uint32(k0),
+                                   _ptr(out), C.c_uint32(cap), C.byref(ln), C.byref(ed))
+        assert rc == 0, rc
+        return out[:min(cap, ln.value)].copy(), ln.value, ed.value
+
     def fm_match_approx(self, idx, symbols, offsets, len1, find_exact=True, cap=64, threads=0):
         """nvBowtie's map<find_exact> (mapping_inl.h:114-184): (ranges[n, cap, 2], counts[n])"""
         symbols = np.ascontiguousarray(symbols, dtype=np.uint8)
@@ -328,3 +338,34 @@ class Oracle:
                                         C.c_uint32(cap), _ptr(ranges), _ptr(counts), C.c_int(threads))
         assert rc == 0, rc
         return ranges, counts
+
+
+def mds_to_md_string(mds):
+    """SAM MD:Z string from an MDS byte-code: restatement of SamOutput::generate_md_string (nvbio/io/output/output_sam.cpp:216-289),
+    including the '0' it appends after a deletion and its handling of a match run that continues in a second MATCH record
+    (:239-240 adds the record's OP byte, 0, and then resumes parsing at its count byte -- runs longer than 255 come out
+    garbled in the reference; reproduced literally, exercised only below that length by the pipeline's 150-bp reads).
+    Returns (md, mismatches, gap_opens, gap_extensions)."""
+    mds = [int(v) for v in mds]
+    mds_len = mds[0] | (mds[1] << 8)
+    out = []; mm = gapo = gape = 0
+    if mds_len <= 2:                              # never produced by the reference (an aligned read has >= 1 op); its do-while would read past the code
+        return "", 0, 0, 0
+    i = 2
+    while True:                                   # do { ... } while (i < mds_len)
+        op = mds[i]; i += 1
+        if op == 0:
+            l = mds[i]; i += 1
+            while i < mds_len and mds[i] == 0:    # :239-240, literally
+                l = (l + mds[i]) & 0xFF; i += 1
+            out.append(str(l))
+        elif op == 1:
+            out.append("ACGTN"[min(mds[i], 4)]); i += 1; mm += 1
+        elif op == 2:
+            l = mds[i]; i += 1 + l; gapo += 1; gape += l - 1
+        elif op == 3:
+            l = mds[i]; i += 1
+            out.append("^" + "".join("ACGTN"[min(c, 4)] for c in mds[i:i + l]) + "0"); i += l; gapo += 1; gape += l - 1
+        if not i < mds_len:
+            break
+    return "".join(out), mm, gapo, gape
