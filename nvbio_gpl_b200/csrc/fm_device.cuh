@@ -151,6 +151,59 @@ __device__ __forceinline__ uint2 fm_rank2_inner(const FMView& f, uint32_t x, uin
     return r;
 }
 
+__device__ __forceinline__ uint4 fm_rank4_at(const FMView& f, uint32_t k, const uint2* lut)
+{
+    // rank4(fmi, k) with the FM special cases (fmindex_inl.h:100-125)
+    if (k == 0xFFFFFFFFu) return make_uint4(0, 0, 0, 0);
+    if (k == f.length) return make_uint4(f.L2[1] - f.L2[0], f.L2[2] - f.L2[1], f.L2[3] - f.L2[2], f.L2[4] - f.L2[3]);
+    if (k >= f.primary) --k;
+    if (k == 0xFFFFFFFFu) return make_uint4(0, 0, 0, 0);
+    const FMBlock b = fm_load_block(f.blk, k >> 6);
+    return fm_block_rank4(b, k & 63u, lut);
+}
+__device__ __forceinline__ uint32_t fm_comp(const uint4& v, uint32_t c) { return (c & 2u) ? ((c & 1u) ? v.w : v.z) : ((c & 1u) ? v.y : v.x); }
+
+
+// map<find_exact> for one string: symbol(t) = the symbol search step t consumes, emit(x, y) receives every non-empty range in the
+// reference's push order (substitutions by position and symbol, then the exact match)
+template <typename Symbol, typename Emit>
+__device__ __forceinline__ void fm_approx_search(const FMView& f, const uint2* s_lut, const uint32_t* s_L2, uint32_t len, uint32_t len1,
+                                                 bool find_exact, Symbol symbol, Emit emit)
+{
+    const uint32_t l1 = min(len1, len);
+    // match_range over steps [t0, t_end)
+    auto tail = [&](uint32_t t0, uint32_t& x, uint32_t& y, uint32_t t_end)
+    {
+        for (uint32_t t = t0; t < t_end && x <= y; ++t)
+        {
+            const uint32_t c = symbol(t);
+            if (c > 3u) { x = 1; y = 0; return; }
+            const uint2 r = (x != 0u && f.primary != 0u) ? fm_rank2_inner(f, x - 1u, y, c, s_lut) : fm_rank2(f, x - 1u, y, c, s_lut);
+            x = s_L2[c] + r.x + 1u; y = s_L2[c] + r.y;
+        }
+    };
+    uint32_t bx = 0, by = f.length;
+    tail(0, bx, by, l1);
+    for (uint32_t t = l1; t < len && bx <= by; ++t)
+    {
+        const uint32_t c = symbol(t);
+        const uint4 lo = fm_rank4_at(f, bx - 1u, s_lut), hi = fm_rank4_at(f, by, s_lut);
+        for (uint32_t sub = 0; sub < 4u; ++sub)
+        {
+            const uint32_t ol = fm_comp(lo, sub), oh = fm_comp(hi, sub);
+            if (sub != c && oh > ol)
+            {
+                uint32_t x = s_L2[sub] + ol + 1u, y = s_L2[sub] + oh;
+                tail(t + 1u, x, y, len);
+                if (x <= y) emit(x, y);
+            }
+        }
+        if (c < 4u) { bx = s_L2[c] + fm_comp(lo, c) + 1u; by = s_L2[c] + fm_comp(hi, c); }
+        else { bx = 1; by = 0; break; }
+    }
+    if (find_exact && bx <= by) emit(bx, by);
+}
+
 __device__ __forceinline__ uint32_t fm_bwt_symbol(const FMBlock& b, uint32_t pos)
 {
     const uint32_t wi = pos >> 4;

@@ -152,18 +152,6 @@ fm_match_kernel(const FMView f, const StrSet q, uint32_t* __restrict__ ranges)
 // of all four symbols at both ends of the range (rank4, :146): the same one or two 32-byte blocks as a plain step, four
 // masked popcount pairs each. Behind a substitution the tail is searched like match_range (:74-86).
 // ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ uint4 fm_rank4_at(const FMView& f, uint32_t k, const uint2* lut)
-{
-    // rank4(fmi, k) with the FM special cases (fmindex_inl.h:100-125)
-    if (k == 0xFFFFFFFFu) return make_uint4(0, 0, 0, 0);
-    if (k == f.length) return make_uint4(f.L2[1] - f.L2[0], f.L2[2] - f.L2[1], f.L2[3] - f.L2[2], f.L2[4] - f.L2[3]);
-    if (k >= f.primary) --k;
-    if (k == 0xFFFFFFFFu) return make_uint4(0, 0, 0, 0);
-    const FMBlock b = fm_load_block(f.blk, k >> 6);
-    return fm_block_rank4(b, k & 63u, lut);
-}
-__device__ __forceinline__ uint32_t fm_comp(const uint4& v, uint32_t c) { return (c & 2u) ? ((c & 1u) ? v.w : v.z) : ((c & 1u) ? v.y : v.x); }
-
 __global__ void __launch_bounds__(FM_THREADS)
 fm_match_approx_kernel(const FMView f, const StrSet q, const uint32_t len1, const uint32_t find_exact, const uint32_t cap,
                        uint32_t* __restrict__ ranges, uint32_t* __restrict__ counts)
@@ -175,41 +163,11 @@ fm_match_approx_kernel(const FMView f, const StrSet q, const uint32_t len1, cons
     const uint32_t tid = blockIdx.x * FM_THREADS + threadIdx.x;
     if (tid >= q.count) return;
     const uint32_t beg = q.off[tid], len = q.off[tid + 1] - beg;
-    const uint32_t l1 = min(len1, len);
     uint2* out = (uint2*)ranges + (size_t)tid * cap;
     uint32_t n = 0;
-    auto symbol = [&](uint32_t t) -> uint32_t { return sym_at_rt(q.sym, q.bits, beg + (len - 1u - t)); };   // step t consumes q[len-1-t]
-    // match_range over steps [t0, len)
-    auto tail = [&](uint32_t t0, uint32_t& x, uint32_t& y, uint32_t t_end)
-    {
-        for (uint32_t t = t0; t < t_end && x <= y; ++t)
-        {
-            const uint32_t c = symbol(t);
-            if (c > 3u) { x = 1; y = 0; return; }
-            const uint2 r = (x != 0u && f.primary != 0u) ? fm_rank2_inner(f, x - 1u, y, c, s_lut) : fm_rank2(f, x - 1u, y, c, s_lut);
-            x = s_L2[c] + r.x + 1u; y = s_L2[c] + r.y;
-        }
-    };
-    uint32_t bx = 0, by = f.length;
-    tail(0, bx, by, l1);
-    for (uint32_t t = l1; t < len && bx <= by; ++t)
-    {
-        const uint32_t c = symbol(t);
-        const uint4 lo = fm_rank4_at(f, bx - 1u, s_lut), hi = fm_rank4_at(f, by, s_lut);
-        for (uint32_t sub = 0; sub < 4u; ++sub)
-        {
-            const uint32_t ol = fm_comp(lo, sub), oh = fm_comp(hi, sub);
-            if (sub != c && oh > ol)
-            {
-                uint32_t x = s_L2[sub] + ol + 1u, y = s_L2[sub] + oh;
-                tail(t + 1u, x, y, len);
-                if (x <= y) { if (n < cap) out[n] = make_uint2(x, y); ++n; }
-            }
-        }
-        if (c < 4u) { bx = s_L2[c] + fm_comp(lo, c) + 1u; by = s_L2[c] + fm_comp(hi, c); }
-        else { bx = 1; by = 0; break; }
-    }
-    if (find_exact && bx <= by) { if (n < cap) out[n] = make_uint2(bx, by); ++n; }
+    fm_approx_search(f, s_lut, s_L2, len, len1, find_exact != 0u,
+                     [&](uint32_t t) -> uint32_t { return sym_at_rt(q.sym, q.bits, beg + (len - 1u - t)); },   // step t consumes q[len-1-t]
+                     [&](uint32_t x, uint32_t y) { if (n < cap) out[n] = make_uint2(x, y); ++n; });
     counts[tid] = n;
 }
 

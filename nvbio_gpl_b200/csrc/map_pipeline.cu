@@ -34,15 +34,37 @@ enum { S_SEED = 8, S_COUNT, S_SCAN, S_KEYS_A, S_KEYS_B, S_CUB, S_NUM, S_POFF, S_
 struct MapGeom
 {
     uint32_t r0, n_reads;            // the batch: reads [r0, r0 + n_reads)
-    uint32_t S, n_strands;           // seed slots per strand (for the longest read), strands
+    uint32_t S, n_strands;           // seeds per strand (for the longest read), strands
+    uint32_t R;                      // range slots per seed: 1 (exact seeding) or max_seed_ranges (approximate seeding)
     uint32_t seed_len, interval, max_hits, max_range, band;
+    uint32_t len1;                   // approximate seeding: search steps that must match exactly
+    uint32_t priority, deque_cap, max_rows;   // range-size hit priority (map_priority_kernel)
 };
+// slot t of a batch = ((read * n_strands + strand) * S + seed) * R + range
+struct MapSlot { uint32_t r, strand, k, j; };
+__device__ __forceinline__ MapSlot map_slot(const MapGeom& g, uint32_t t)
+{
+    MapSlot s;
+    s.j = t % g.R; t /= g.R;
+    s.k = t % g.S; t /= g.S;
+    s.strand = t % g.n_strands; s.r = t / g.n_strands;
+    return s;
+}
 
 __device__ __forceinline__ uint32_t map_strand_symbol(const uint8_t* read, uint32_t L, uint32_t strand, uint32_t i)
 {
     if (!strand) return read[i];
     const uint32_t c = read[L - 1u - i];
     return c < 4u ? 3u - c : c;
+}
+
+// rows a range of `size` SA rows contributes: none when wider than max_range, else its first max_hits; under hit priority the
+// full size is kept here and map_priority_kernel allots the rows
+__device__ __forceinline__ uint32_t map_rows_of(const MapGeom& g, uint32_t size)
+{
+    if (g.max_range && size > g.max_range) return 0u;
+    if (g.priority) return size < 0x7FFFFFFFu ? size : 0x7FFFFFFFu;
+    return size < g.max_hits ? size : g.max_hits;
 }
 
 __global__ void __launch_bounds__(MAP_THREADS)
@@ -52,10 +74,10 @@ map_seed_kernel(const FMView f, const StrSet reads, const MapGeom g, uint2* __re
     __shared__ uint32_t s_L2[8];
     if (threadIdx.x < 5) s_L2[threadIdx.x] = f.L2[threadIdx.x];
     fm_lut_init(s_lut);
-    const uint32_t per_read = g.S * g.n_strands;
     const uint32_t t = blockIdx.x * MAP_THREADS + threadIdx.x;
-    if (t >= g.n_reads * per_read) return;
-    const uint32_t r = t / per_read, rem = t - r * per_read, strand = rem / g.S, k = rem - strand * g.S;
+    if (t >= g.n_reads * g.n_strands * g.S) return;
+    const MapSlot sl = map_slot(g, t);                       // R == 1 on this path
+    const uint32_t r = sl.r, strand = sl.strand, k = sl.k;
     const uint32_t beg = reads.off[g.r0 + r], L = reads.off[g.r0 + r + 1] - beg;
     const uint8_t* read = reads.sym + beg;
     const uint32_t o = k * g.interval;
@@ -83,14 +105,81 @@ map_seed_kernel(const FMView f, const StrSet reads, const MapGeom g, uint2* __re
             x = s_L2[c] + rk.x + 1u;
             y = s_L2[c] + rk.y;
         }
-        if (x <= y)
-        {
-            const uint32_t size = y - x + 1u;
-            if (!(g.max_range && size > g.max_range)) cnt = size < g.max_hits ? size : g.max_hits;
-        }
+        if (x <= y) cnt = map_rows_of(g, y - x + 1u);
     }
     seeds[t] = make_uint2(x, cnt);
     counts[t] = cnt;
+}
+
+// approximate seeding (nvb_map_params.seed_mismatches = 1): nvBowtie's map<CHECK_EXACT> on the forward index
+// (mapping_inl.h:114-184 as called at :395-397: exact over the first seed_len / 2 search steps, one substitution allowed in
+// the rest, plus the exact match); the first R ranges in the reference's push order fill the seed's R slots
+__global__ void __launch_bounds__(MAP_THREADS)
+map_seed_approx_kernel(const FMView f, const StrSet reads, const MapGeom g, uint2* __restrict__ seeds, uint32_t* __restrict__ counts)
+{
+    __shared__ uint2 s_lut[FM_LUT_ENTRIES];
+    __shared__ uint32_t s_L2[8];
+    if (threadIdx.x < 5) s_L2[threadIdx.x] = f.L2[threadIdx.x];
+    fm_lut_init(s_lut);
+    const uint32_t t = blockIdx.x * MAP_THREADS + threadIdx.x;
+    if (t >= g.n_reads * g.n_strands * g.S) return;
+    const MapSlot sl = map_slot(g, t * g.R);
+    const uint32_t beg = reads.off[g.r0 + sl.r], L = reads.off[g.r0 + sl.r + 1] - beg;
+    const uint8_t* read = reads.sym + beg;
+    const uint32_t o = sl.k * g.interval;
+    uint2* out = seeds + (size_t)t * g.R; uint32_t* cnt = counts + (size_t)t * g.R;
+    uint32_t n = 0;
+    if (o + g.seed_len <= L)
+        fm_approx_search(f, s_lut, s_L2, g.seed_len, g.len1, true,
+                         [&](uint32_t st) -> uint32_t { return map_strand_symbol(read, L, sl.strand, o + g.seed_len - 1u - st); },
+                         [&](uint32_t x, uint32_t y) { if (n < g.R) { const uint32_t c = map_rows_of(g, y - x + 1u); out[n] = make_uint2(x, c); cnt[n] = c; } ++n; });
+    for (uint32_t j = n < g.R ? n : g.R; j < g.R; ++j) { out[j] = make_uint2(1u, 0u); cnt[j] = 0u; }
+}
+
+// Range-size hit priority (nvb_map_params.hit_priority = 1), per read: nvBowtie keeps a read's seed hits in a priority deque
+// ordered by SA-range size (seed_hit.h:220-230 hit_compare, seed_hit_deque_array.h), pushes every new hit after dropping the
+// LARGEST one when the deque already holds max_hits entries (mapping_inl.h:158-160,176-178), and extends rows from the smallest
+// range first, front to back (select_inl.h:93-113). Here: the ranges of a read are pushed in slot order into a deque of
+// deque_cap entries (0 = unbounded) under that rule, the survivors are visited by (size, slot) ascending and each takes
+// min(size, max_hits, what is left of max_rows) rows from its front. Ties between equal sizes go by slot order (the reference's
+// interval heap leaves them unspecified). One thread per read; a read has a few dozen slots, so the quadratic scans stay in L1.
+__global__ void __launch_bounds__(MAP_THREADS)
+map_priority_kernel(const MapGeom g, uint2* __restrict__ seeds, uint32_t* __restrict__ counts)
+{
+    const uint32_t r = blockIdx.x * MAP_THREADS + threadIdx.x;
+    if (r >= g.n_reads) return;
+    const uint32_t per_read = g.n_strands * g.S * g.R;
+    uint2* sd = seeds + (size_t)r * per_read; uint32_t* cn = counts + (size_t)r * per_read;
+    // on entry sd[t].y = full size of the range (0 = empty or wider than max_range); cn[t] is scratch: 1 = in the deque
+    uint32_t held = 0;
+    for (uint32_t t = 0; t < per_read; ++t)
+    {
+        cn[t] = 0;
+        if (sd[t].y == 0) continue;
+        if (g.deque_cap && held == g.deque_cap)
+        {
+            uint32_t worst = 0, wsize = 0;
+            for (uint32_t u = 0; u < t; ++u) if (cn[u] && sd[u].y >= wsize) { wsize = sd[u].y; worst = u; }   // the largest, latest slot on ties
+            cn[worst] = 0; --held;
+        }
+        cn[t] = 1; ++held;
+    }
+    uint32_t budget = g.max_rows ? g.max_rows : 0xFFFFFFFFu;
+    for (uint32_t done = 0; done < held; ++done)
+    {
+        uint32_t pick = 0, psize = 0xFFFFFFFFu;
+        for (uint32_t u = 0; u < per_read; ++u) if (cn[u] == 1 && sd[u].y < psize) { psize = sd[u].y; pick = u; }   // the smallest, earliest slot on ties
+        uint32_t c = psize < g.max_hits ? psize : g.max_hits;
+        if (c > budget) c = budget;
+        budget -= c;
+        sd[pick].y = c | 0x80000000u;                        // allotted (the flag keeps it out of the next scans)
+        cn[pick] = 2;
+    }
+    for (uint32_t t = 0; t < per_read; ++t)
+    {
+        const uint32_t c = cn[t] == 2 ? sd[t].y & 0x7FFFFFFFu : 0u;
+        sd[t].y = c; cn[t] = c;
+    }
 }
 
 // one thread per seed slot: its selected SA rows go to their places in hit order (row, slot)
@@ -129,9 +218,9 @@ map_keys_kernel(const FMView f, const MapGeom g, const uint2* __restrict__ rows,
     if (h >= n_hits) return;
     const uint2 rec = rows[h];
     const uint32_t pos = __ldg(f.sa_tab + (rec.x >> f.sa_shift)) + steps[h];
-    const uint32_t per_read = g.S * g.n_strands;
-    const uint32_t r = rec.y / per_read, rem = rec.y - r * per_read, strand = rem / g.S, k = rem - strand * g.S;
-    const uint32_t o = k * g.interval;
+    const MapSlot sl = map_slot(g, rec.y);
+    const uint32_t r = sl.r, strand = sl.strand;
+    const uint32_t o = sl.k * g.interval;
     const uint32_t g_pos = pos > o ? pos - o : 0u;
     const uint32_t gb = g_pos > g.band / 2u ? g_pos - g.band / 2u : 0u;
     keys[h] = ((uint64_t)(r * 2u + strand) << 32) | gb;
@@ -470,6 +559,7 @@ extern "C" int nvb_map_reads(nvb_ctx* ctx, const nvb_fmindex* fmi, const uint32_
     if (reads_set.bits != 8 || fmi->occ_int != 64 || fmi->sa_int != 16) return NVB_ERR_UNSUPPORTED;
     if (mp->aligner.type != NVB_SEMI_GLOBAL || mp->seed_len == 0 || mp->seed_interval == 0 || mp->max_hits == 0) return NVB_ERR_UNSUPPORTED;
     if (mp->band < 2 || mp->band > NVB_MAX_BAND_LEN || maxL == 0) return NVB_ERR_UNSUPPORTED;
+    if (mp->seed_mismatches > 1u || mp->max_seed_ranges > 64u || mp->hit_priority > 1u) return NVB_ERR_UNSUPPORTED;
     const uint32_t tb_stride = ops ? ops_stride : ((2u * maxL + mp->band + 16u + 15u) & ~15u);
     if ((tb_stride & 15u) || tb_stride < 2u * maxL + mp->band || (ops && (((uintptr_t)ops) & 15u))) return NVB_ERR_ARG;
     cudaStream_t s = (cudaStream_t)stream;
@@ -482,8 +572,14 @@ extern "C" int nvb_map_reads(nvb_ctx* ctx, const nvb_fmindex* fmi, const uint32_
     g.n_strands = mp->both_strands ? 2u : 1u;
     g.S = maxL >= mp->seed_len ? (maxL - mp->seed_len) / mp->seed_interval + 1u : 0u;
     g.seed_len = mp->seed_len; g.interval = mp->seed_interval; g.max_hits = mp->max_hits; g.max_range = mp->max_range; g.band = mp->band;
-    const uint32_t per_read = g.S * g.n_strands;
-    // batch: bounded so that seed slots and worst-case hits stay below 2^31
+    g.R = mp->seed_mismatches ? (mp->max_seed_ranges ? mp->max_seed_ranges : 8u) : 1u;
+    g.len1 = mp->seed_len / 2u;                                       // mapping_inl.h:397
+    g.priority = mp->hit_priority; g.deque_cap = mp->max_seed_hits; g.max_rows = mp->max_rows;
+    const uint32_t per_read = g.S * g.n_strands * g.R;               // range slots per read
+    // worst-case rows of one read
+    uint64_t rows_per_read = (uint64_t)per_read * mp->max_hits;
+    if (g.priority && g.max_rows && g.max_rows < rows_per_read) rows_per_read = g.max_rows;
+    // batch: bounded so that slots and worst-case hits stay below 2^31
     uint64_t rb = reads_per_batch ? reads_per_batch : (1u << 20);
     if (per_read) { const uint64_t cap = 0x7FFFFFFFull / ((uint64_t)per_read * mp->max_hits); if (rb > cap) rb = cap; }
     if (rb == 0) return NVB_ERR_UNSUPPORTED;
@@ -493,7 +589,7 @@ extern "C" int nvb_map_reads(nvb_ctx* ctx, const nvb_fmindex* fmi, const uint32_
     // the seeds of the whole call share their first steps through one per-call k-mer table (as nvb_fm_match does per batch)
     {
         const uint64_t seeds = (uint64_t)n_total * ((uint64_t)(maxL >= mp->seed_len ? (maxL - mp->seed_len) / mp->seed_interval + 1u : 0u) * (mp->both_strands ? 2u : 1u));
-        if (seeds >= ctx->fm_share_min && (rc = nvb_fm_batch_table(ctx, f, seeds, mp->seed_len, s))) return rc;
+        if (!mp->seed_mismatches && seeds >= ctx->fm_share_min && (rc = nvb_fm_batch_table(ctx, f, seeds, mp->seed_len, s))) return rc;
     }
     MapTrace trace(s);
     for (uint32_t r0 = 0; r0 < n_total; r0 += (uint32_t)rb)
@@ -516,8 +612,14 @@ extern "C" int nvb_map_reads(nvb_ctx* ctx, const nvb_fmindex* fmi, const uint32_
             MAP_STAGE(S_COUNT, sizeof(uint32_t) * ((size_t)n_slots + 1), counts);
             MAP_STAGE(S_SCAN, sizeof(uint32_t) * ((size_t)n_slots + 1), scan);
             NVB_CUDA(ctx, cudaMemsetAsync(counts + n_slots, 0, sizeof(uint32_t), s));
-            map_seed_kernel<<<map_grid(n_slots), MAP_THREADS, 0, s>>>(f, reads, g, seeds, counts);
+            if (g.R == 1u) map_seed_kernel<<<map_grid(n_slots), MAP_THREADS, 0, s>>>(f, reads, g, seeds, counts);
+            else           map_seed_approx_kernel<<<map_grid(n_slots / g.R), MAP_THREADS, 0, s>>>(f, reads, g, seeds, counts);
             NVB_LAUNCHED(ctx);
+            if (g.priority)
+            {
+                map_priority_kernel<<<map_grid(nr), MAP_THREADS, 0, s>>>(g, seeds, counts);
+                NVB_LAUNCHED(ctx);
+            }
             tmp_bytes = 0;
             cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, counts, scan, (int)(n_slots + 1), s);
             MAP_STAGE(S_CUB, tmp_bytes, tmp);
@@ -545,10 +647,12 @@ extern "C" int nvb_map_reads(nvb_ctx* ctx, const nvb_fmindex* fmi, const uint32_
                 map_keys_kernel<<<map_grid(n_hits), MAP_THREADS, 0, s>>>(f, g, rows, steps, n_hits, keys_b);
                 NVB_LAUNCHED(ctx);
                 trace.mark(MapTrace::LOCATE);
-                uint32_t cap = 64; while (cap < per_read * mp->max_hits) cap <<= 1;
+                uint32_t cap = 64; while (cap < rows_per_read && cap < (1u << 30)) cap <<= 1;
                 size_t sel_bytes = 0;
                 if (cap <= 1024u)
                 {
+                    if (NVB_FIRST_ON_DEVICE(ctx))              // up to 64 KB of dynamic shared memory (8 warps x 1024 keys)
+                        NVB_CUDA(ctx, cudaFuncSetAttribute(map_dedupe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, MAP_DEDUPE_WARPS * 1024 * (int)sizeof(uint64_t)));
                     map_dedupe_kernel<<<(nr + MAP_DEDUPE_WARPS - 1) / MAP_DEDUPE_WARPS, MAP_DEDUPE_WARPS * 32, MAP_DEDUPE_WARPS * cap * sizeof(uint64_t), s>>>(
                         scan, per_read, nr, cap, keys_b);
                     NVB_LAUNCHED(ctx);
@@ -634,7 +738,7 @@ extern "C" int nvb_map_reads(nvb_ctx* ctx, const nvb_fmindex* fmi, const uint32_
                 trace.mark(MapTrace::FINISH);
             }
         }
-        if (stats) { stats->seeds += n_slots; stats->seed_hits += n_hits; stats->candidates += n_cand; stats->aligned += n_aligned; }
+        if (stats) { stats->seeds += n_slots / g.R; stats->seed_hits += n_hits; stats->candidates += n_cand; stats->aligned += n_aligned; }
     }
     return NVB_OK;
 }
@@ -719,7 +823,8 @@ extern "C" int nvb_map_reads_host(nvb_ctx* ctx, const nvb_fmindex* fmi, const ui
         uint32_t maxL0 = 0;
         for (uint32_t i = 0; i < cap; ++i) { const uint32_t l = off_h[i + 1] - off_h[i]; if (l > maxL0) maxL0 = l; }
         const uint64_t per_read = (mp->seed_len && mp->seed_interval && maxL0 >= mp->seed_len ? (maxL0 - mp->seed_len) / mp->seed_interval + 1u : 0u) * (mp->both_strands ? 2u : 1u);
-        if ((rc = nvb_with_batch_table(ctx, fmi, (uint64_t)n * per_read, mp->seed_len, s_k, &fmi_call))) return rc;
+        fmi_call = *fmi;
+        if (!mp->seed_mismatches && (rc = nvb_with_batch_table(ctx, fmi, (uint64_t)n * per_read, mp->seed_len, s_k, &fmi_call))) return rc;
         fmi = &fmi_call;
     }
     for (uint32_t k = 0; k < n_batches; ++k)

@@ -24,15 +24,22 @@ class MapParams:
     ``[g - band/2, g - band/2 + band + read_len)`` (score_inl.h:103-106)"""
 
     def __init__(self, aligner=None, seed_len=20, seed_interval=10, max_hits=4, max_range=0, band=15,
-                 both_strands=True, min_score=-(1 << 29)):
+                 both_strands=True, min_score=-(1 << 29), seed_mismatches=0, max_seed_ranges=0, hit_priority=False,
+                 max_seed_hits=0, max_rows=0):
+        """seed_mismatches = 1: nvBowtie's approximate seeds on the forward index (mapping_inl.h:114-184, :395-397), the first
+        max_seed_ranges ranges per seed (0 = 8). hit_priority: ranges visited by size, smallest first, through a deque of
+        max_seed_hits entries (0 = unbounded), max_rows rows per read (0 = no budget) (seed_hit.h:220-230, select_inl.h:93-113)"""
         self.aligner = aligner if aligner is not None else GotohAligner(SEMI_GLOBAL, 0, -5, -8, -3)
         assert isinstance(self.aligner, Aligner)
         self.seed_len, self.seed_interval, self.max_hits, self.max_range = seed_len, seed_interval, max_hits, max_range
         self.band, self.both_strands, self.min_score = band, both_strands, min_score
+        self.seed_mismatches, self.max_seed_ranges = int(seed_mismatches), int(max_seed_ranges)
+        self.hit_priority, self.max_seed_hits, self.max_rows = bool(hit_priority), int(max_seed_hits), int(max_rows)
 
     def c(self):
         return MapParamsC(self.seed_len, self.seed_interval, self.max_hits, self.max_range, self.band,
-                          1 if self.both_strands else 0, self.min_score, self.aligner.c())
+                          1 if self.both_strands else 0, self.min_score, self.aligner.c(), self.seed_mismatches, self.max_seed_ranges,
+                          1 if self.hit_priority else 0, self.max_seed_hits, self.max_rows)
 
 
 def ops_stride_for(max_read_len, band):

@@ -130,7 +130,10 @@ int ORC(banded_myers)(int32_t type, uint32_t alphabet, uint32_t band, int32_t mi
 /* seed-and-extend composition (oracle_map.c); flags: bit 0 = reverse-complement strand, bit 1 = aligned.
  * begin/end = genome coordinates of the first aligned symbol / one past the last; ops in push order (end -> start). */
 typedef struct { uint32_t seed_len, seed_interval, max_hits, max_range, band, both_strands; int32_t min_score;
-                 orc_aligner aligner; } orc_map_params;
+                 orc_aligner aligner;
+                 uint32_t seed_mismatches, max_seed_ranges;           /* nvBowtie's approximate seeds, forward index (mapping_inl.h:114-184) */
+                 uint32_t hit_priority, max_seed_hits, max_rows;      /* hit selection by SA-range size (seed_hit.h:220-230, select_inl.h:93-113) */
+               } orc_map_params;
 typedef struct { int32_t score, second_score; uint32_t begin, end, flags, n_ops; } orc_read_hit;
 int ORC(map_reads)(const orc_fmindex* fmi, const uint8_t* genome, const uint8_t* reads, const uint32_t* read_off,
                    uint32_t n_reads, const orc_map_params* p, orc_read_hit* hits, uint8_t* ops, uint32_t ops_stride,
@@ -141,6 +144,9 @@ int ORC(fm_match_approx)(const orc_fmindex* fmi, const uint8_t* symbols, const u
                          int find_exact, uint32_t cap, uint32_t* ranges, uint32_t* counts, int threads);
 typedef struct { int32_t score; uint32_t frag_begin, frag_end, flags; } orc_pair_hit;
 int ORC(pair_hits)(const orc_read_hit* hits, uint32_t n_pairs, uint32_t min_frag, uint32_t max_frag, orc_pair_hit* out);
+/* hit selection by SA-range size (seed_hit.h:220-230, mapping_inl.h:158-160, select_inl.h:93-113); see oracle_map.c */
+size_t ORC(hit_priority)(const uint32_t* sizes, uint32_t n, uint32_t max_hits, uint32_t max_seed_hits, uint32_t max_rows,
+                         uint32_t* take, uint32_t* order, uint32_t* n_order);
 /* MDS byte-code + edit distance of one alignment (nvBowtie/bowtie2/cuda/traceback_inl.h:555-690) */
 int ORC(ops_to_mds)(const uint8_t* ops, uint32_t n_ops, const uint8_t* pattern, const uint8_t* text, uint32_t j0, uint32_t k0,
                     uint8_t* mds, uint32_t cap, uint32_t* mds_len_out, uint32_t* ed_out);

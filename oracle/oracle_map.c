@@ -38,6 +38,45 @@ static int cmp_u64(const void* a, const void* b)
     return x < y ? -1 : x > y ? 1 : 0;
 }
 
+/* Hit selection by SA-range size. nvBowtie keeps a read's seed hits in a priority deque ordered by range size (hit_compare,
+ * nvBowtie/bowtie2/cuda/seed_hit.h:220-230; seed_hit_deque_array.h:144-145); a push into a deque that already holds max_seed_hits
+ * entries first drops the LARGEST range (mapping_inl.h:158-160,176-178); extension then takes rows from the smallest range first,
+ * front to back (select_inl.h:93-113). sizes[n] in push (slot) order, 0 = no range. take[i] = rows range i contributes:
+ * min(size, max_hits, what is left of max_rows) in visiting order; order[] (optional) = the visiting order, *n_order its length.
+ * Ties between equal sizes: dropped = the latest slot, visited = the earliest slot first (the reference's interval heap leaves
+ * them unspecified; pinned on the reference's own deque, ref_hit_order, for distinct sizes). Returns the total rows. */
+size_t ORC(hit_priority)(const uint32_t* sizes, uint32_t n, uint32_t max_hits, uint32_t max_seed_hits, uint32_t max_rows,
+                         uint32_t* take, uint32_t* order, uint32_t* n_order)
+{
+    uint8_t* in = (uint8_t*)calloc(n ? n : 1, 1);
+    uint32_t held = 0; size_t total = 0;
+    for (uint32_t t = 0; t < n; ++t)
+    {
+        take[t] = 0;
+        if (!sizes[t]) continue;
+        if (max_seed_hits && held == max_seed_hits)
+        {
+            uint32_t worst = 0, wsize = 0;
+            for (uint32_t u = 0; u < t; ++u) if (in[u] && sizes[u] >= wsize) { wsize = sizes[u]; worst = u; }
+            in[worst] = 0; --held;
+        }
+        in[t] = 1; ++held;
+    }
+    uint32_t budget = max_rows ? max_rows : 0xFFFFFFFFu;
+    for (uint32_t done = 0; done < held; ++done)
+    {
+        uint32_t pick = 0, psize = 0xFFFFFFFFu;
+        for (uint32_t u = 0; u < n; ++u) if (in[u] == 1 && sizes[u] < psize) { psize = sizes[u]; pick = u; }
+        uint32_t c = psize < max_hits ? psize : max_hits;
+        if (c > budget) c = budget;
+        budget -= c; take[pick] = c; in[pick] = 2; total += c;
+        if (order) order[done] = pick;
+    }
+    if (n_order) *n_order = held;
+    free(in);
+    return total;
+}
+
 int ORC(map_reads)(const orc_fmindex* fmi, const uint8_t* genome, const uint8_t* reads, const uint32_t* read_off,
                    uint32_t n_reads, const orc_map_params* p, orc_read_hit* hits, uint8_t* ops, uint32_t ops_stride,
                    uint32_t* n_candidates, int threads)
@@ -54,6 +93,7 @@ int ORC(map_reads)(const orc_fmindex* fmi, const uint8_t* genome, const uint8_t*
         uint8_t*  strand_read = NULL; size_t cap_read = 0;
         uint64_t* keys = NULL;        size_t cap_keys = 0;
         uint8_t*  tb_ops = NULL;      size_t cap_ops = 0;
+        uint32_t *sl_x = NULL, *sl_size = NULL, *sl_take = NULL, *sl_o = NULL, *ap = NULL; uint32_t* order = NULL; size_t cap_slots = 0, cap_order = 0;
 #ifdef _OPENMP
         #pragma omp for schedule(dynamic, 64)
 #endif
@@ -70,30 +110,67 @@ int ORC(map_reads)(const orc_fmindex* fmi, const uint8_t* genome, const uint8_t*
             for (uint32_t i = 0; i < L; ++i) { const uint8_t c = fwd[L - 1 - i]; strand_read[L + i] = c < 4 ? (uint8_t)(3 - c) : c; }
             const uint32_t n_strands = p->both_strands ? 2u : 1u;
             const uint32_t n_seeds = L >= p->seed_len ? (L - p->seed_len) / p->seed_interval + 1 : 0;
-            const size_t need = (size_t)n_strands * n_seeds * p->max_hits;
-            if (need > cap_keys) { cap_keys = need; keys = (uint64_t*)realloc(keys, sizeof(uint64_t) * cap_keys); }
-            size_t nk = 0;
+            /* ---- the SA ranges of the read, in slot order (strand, seed, range): exact seeds give one, approximate seeds
+             * (mapping_inl.h:114-184 through fm_match_approx, first R ranges in its push order) up to R */
+            const uint32_t R = p->seed_mismatches ? (p->max_seed_ranges ? p->max_seed_ranges : 8u) : 1u;
+            const size_t n_slots = (size_t)n_strands * n_seeds * R;
+            if (n_slots > cap_slots)
+            {
+                cap_slots = n_slots;
+                sl_x = (uint32_t*)realloc(sl_x, 4 * cap_slots); sl_size = (uint32_t*)realloc(sl_size, 4 * cap_slots);
+                sl_take = (uint32_t*)realloc(sl_take, 4 * cap_slots); sl_o = (uint32_t*)realloc(sl_o, 4 * cap_slots);
+                ap = (uint32_t*)realloc(ap, 8 * (size_t)R + 8);
+            }
+            size_t ns = 0;
             for (uint32_t s = 0; s < n_strands; ++s)
                 for (uint32_t k = 0; k < n_seeds; ++k)
                 {
                     const uint32_t o = k * p->seed_interval;
                     const uint32_t off[2] = { 0, p->seed_len };
-                    uint32_t range[2];
-                    if (ORC(fm_match)(fmi, strand_read + s * L + o, off, 1, range, NULL, 1)) { failed = 1; continue; }
-                    if (range[0] > range[1]) continue;
-                    const uint32_t size = range[1] - range[0] + 1;
-                    if (p->max_range && size > p->max_range) continue;
-                    const uint32_t cnt = size < p->max_hits ? size : p->max_hits;
-                    for (uint32_t t = 0; t < cnt; ++t)
+                    uint32_t n_rng = 0;
+                    if (!p->seed_mismatches)
                     {
-                        const uint32_t row = range[0] + t;
-                        uint32_t pos;
-                        if (ORC(fm_locate)(fmi, &row, 1, &pos, NULL, 1)) { failed = 1; continue; }
-                        const uint32_t g_pos = pos > o ? pos - o : 0;
-                        const uint32_t gb = g_pos > p->band / 2 ? g_pos - p->band / 2 : 0;
-                        keys[nk++] = ((uint64_t)s << 32) | gb;
+                        if (ORC(fm_match)(fmi, strand_read + s * L + o, off, 1, ap, NULL, 1)) { failed = 1; continue; }
+                        n_rng = ap[0] <= ap[1] ? 1u : 0u;
+                    }
+                    else
+                    {
+                        if (ORC(fm_match_approx)(fmi, strand_read + s * L + o, off, 1, p->seed_len / 2u, 1, R, ap, &n_rng, 1)) { failed = 1; continue; }
+                        if (n_rng > R) n_rng = R;
+                    }
+                    for (uint32_t j = 0; j < R; ++j, ++ns)
+                    {
+                        sl_o[ns] = o; sl_x[ns] = 0; sl_size[ns] = 0;
+                        if (j >= n_rng) continue;
+                        const uint32_t size = ap[2 * j + 1] - ap[2 * j] + 1;
+                        if (p->max_range && size > p->max_range) continue;
+                        sl_x[ns] = ap[2 * j]; sl_size[ns] = size;
                     }
                 }
+            /* ---- rows each range contributes */
+            size_t need = 0;
+            if (!p->hit_priority)
+                for (size_t t = 0; t < ns; ++t) { sl_take[t] = sl_size[t] < p->max_hits ? sl_size[t] : p->max_hits; need += sl_take[t]; }
+            else
+            {
+                if (ns > cap_order) { cap_order = ns; order = (uint32_t*)realloc(order, 4 * cap_order); }
+                need = ORC(hit_priority)(sl_size, (uint32_t)ns, p->max_hits, p->max_seed_hits, p->max_rows, sl_take, order, NULL);
+            }
+            if (need > cap_keys) { cap_keys = need; keys = (uint64_t*)realloc(keys, sizeof(uint64_t) * cap_keys); }
+            size_t nk = 0;
+            for (size_t t = 0; t < ns; ++t)
+            {
+                const uint32_t s = (uint32_t)(t / ((size_t)n_seeds * R)), o = sl_o[t];
+                for (uint32_t q = 0; q < sl_take[t]; ++q)
+                {
+                    const uint32_t row = sl_x[t] + q;
+                    uint32_t pos;
+                    if (ORC(fm_locate)(fmi, &row, 1, &pos, NULL, 1)) { failed = 1; continue; }
+                    const uint32_t g_pos = pos > o ? pos - o : 0;
+                    const uint32_t gb = g_pos > p->band / 2 ? g_pos - p->band / 2 : 0;
+                    keys[nk++] = ((uint64_t)s << 32) | gb;
+                }
+            }
             if (nk == 0) continue;
             qsort(keys, nk, sizeof(uint64_t), cmp_u64);
             size_t nu = 1;
@@ -129,7 +206,7 @@ int ORC(map_reads)(const orc_fmindex* fmi, const uint8_t* genome, const uint8_t*
                 if (ops && ops_stride) memcpy(ops + (size_t)r * ops_stride, tb_ops, n_ops < ops_stride ? n_ops : ops_stride);
             }
         }
-        free(strand_read); free(keys); free(tb_ops);
+        free(strand_read); free(keys); free(tb_ops); free(sl_x); free(sl_size); free(sl_take); free(sl_o); free(order); free(ap);
     }
     return failed ? -2 : 0;
 }

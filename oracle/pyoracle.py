@@ -58,7 +58,9 @@ class QScheme:
 
 class MapParamsC(C.Structure):
     _fields_ = [("seed_len", C.c_uint32), ("seed_interval", C.c_uint32), ("max_hits", C.c_uint32), ("max_range", C.c_uint32),
-                ("band", C.c_uint32), ("both_strands", C.c_uint32), ("min_score", C.c_int32), ("aligner", AlignerC)]
+                ("band", C.c_uint32), ("both_strands", C.c_uint32), ("min_score", C.c_int32), ("aligner", AlignerC),
+                ("seed_mismatches", C.c_uint32), ("max_seed_ranges", C.c_uint32), ("hit_priority", C.c_uint32),
+                ("max_seed_hits", C.c_uint32), ("max_rows", C.c_uint32)]
 
 
 HIT_DT = np.dtype([("score", "<i4"), ("second_score", "<i4"), ("begin", "<u4"), ("end", "<u4"), ("flags", "<u4"), ("n_ops", "<u4")])
@@ -315,6 +317,22 @@ class Oracle:
         rc = self._f("pair_hits")(_ptr(hits), C.c_uint32(n), C.c_uint32(min_frag), C.c_uint32(max_frag), _ptr(out))
         assert rc == 0, rc
         return out
+
+    def hit_priority(self, sizes, max_hits, max_seed_hits=0, max_rows=0):
+        """(take[n], visiting order) of oracle_map.c's hit selection by SA-range size"""
+        sizes = np.ascontiguousarray(sizes, dtype=np.uint32); n = len(sizes)
+        take = np.zeros(n, dtype=np.uint32); order = np.zeros(max(n, 1), dtype=np.uint32); no = C.c_uint32(0)
+        fn = self._f("hit_priority"); fn.restype = C.c_size_t
+        fn(_ptr(sizes), C.c_uint32(n), C.c_uint32(max_hits), C.c_uint32(max_seed_hits), C.c_uint32(max_rows), _ptr(take), _ptr(order), C.byref(no))
+        return take, order[:no.value].copy()
+
+    def ref_hit_order(self, sizes, cap=0):
+        """pop order of the REFERENCE's own seed-hit deque (oracle/_ref only): (slots, sizes)"""
+        sizes = np.ascontiguousarray(sizes, dtype=np.uint32); n = len(sizes)
+        slots = np.zeros(max(n, 1), dtype=np.uint32); out = np.zeros(max(n, 1), dtype=np.uint32); no = C.c_uint32(0)
+        rc = self.lib.ref_hit_order(_ptr(sizes), C.c_uint32(n), C.c_uint32(cap), _ptr(slots), _ptr(out), C.byref(no))
+        assert rc == 0, rc
+        return slots[:no.value].copy(), out[:no.value].copy()
 
     def ops_to_mds(self, ops, n_ops, pattern, text, j0=0, k0=0, cap=4096):
         """MDS byte-code (uint8 array of its full length) and edit distance of one alignment (traceback_inl.h:555-690)"""

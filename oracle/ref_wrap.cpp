@@ -184,3 +184,36 @@ int ref_fm_locate(const orc_fmindex* f, const uint32_t* rows, uint32_t count, ui
 } // extern "C"
 
 #include "ref_wrap_aln.inl"
+
+// ---------------------------------------------------------------------------------------------
+// nvBowtie's seed-hit deque, as its mapping kernels use it: SeedHit + hit_compare (nvBowtie/bowtie2/cuda/seed_hit.h:41-230) in
+// a priority_deque over a vector_view (seed_hit_deque_array.h:144-145; built like mapping_inl.h:441-444), pushes that drop the
+// bottom of a full deque (mapping_inl.h:158-160), then pop_top until empty (select_inl.h:93-113 visits hits in this order).
+// The hit's 10-bit pos field carries the caller's slot id. Pins oracle_map.c's hit-priority rule wherever sizes are distinct.
+// ---------------------------------------------------------------------------------------------
+#include <nvBowtie/bowtie2/cuda/seed_hit.h>
+#include <nvbio/basic/priority_deque.h>
+extern "C" int ref_hit_order(const uint32_t* sizes, uint32_t n, uint32_t cap, uint32_t* out_slots, uint32_t* out_sizes, uint32_t* n_out)
+{
+    using namespace nvbio::bowtie2::cuda;
+    if (n >= 1024u) return -1;
+    std::vector<SeedHit> storage(n + 1u);
+    typedef nvbio::vector_view<SeedHit*> hit_vector_type;
+    typedef nvbio::priority_deque<SeedHit, hit_vector_type, hit_compare> hit_deque_type;
+    hit_deque_type heap(hit_vector_type(0, &storage[0]), true);
+    for (uint32_t i = 0; i < n; ++i)
+    {
+        if (sizes[i] == 0 || sizes[i] >= (1u << 20)) continue;
+        if (cap && heap.size() == cap) heap.pop_bottom();
+        heap.push(SeedHit(SeedHit::build_flags(STANDARD, FORWARD, i), make_uint2(1000u, 1000u + sizes[i])));   // exclusive range: delta = size
+    }
+    uint32_t k = 0;
+    while (heap.size())
+    {
+        const SeedHit h = heap.top();
+        out_slots[k] = h.get_posinread(); out_sizes[k] = h.get_range_size(); ++k;
+        heap.pop_top();
+    }
+    *n_out = k;
+    return 0;
+}

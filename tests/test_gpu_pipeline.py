@@ -46,6 +46,7 @@ CASES = [
     (po.GOTOH, (2, -3, -6, -2), 15, 8, 6, 0, 0),
     (po.GOTOH, (0, -5, -8, -3), 12, 3, 0, 1, -60),      # a band only the int32 kernels take
     (po.ED, (0, -1, -1, -1), 15, 40, 0, 1, -20),         # more than 1024 possible hits per read: global sort path
+    (po.ED, (0, -1, -1, -1), 15, 20, 0, 1, -20),         # up to 1024 possible hits per read: the 64 KB shared-memory sort
 ]
 
 
@@ -103,6 +104,45 @@ def test_map_reads_seed_lengths(oracle, seed_len, interval):
     hits, ops, stats = nvb.map_reads(fmi, words, rs.symbols, rs.offsets, params)
     assert same(hits_np(hits), ops.cpu().numpy(), want_hits, want_ops)
     assert stats["candidates"] == int(want_nc.sum())
+
+
+MODES = [
+    dict(seed_mismatches=1, max_seed_ranges=4),
+    dict(seed_mismatches=1, max_seed_ranges=0),                                   # default: 8 ranges per seed
+    dict(hit_priority=1),                                                         # no caps: same rows as the default selection
+    dict(hit_priority=1, max_seed_hits=5, max_rows=9),
+    dict(hit_priority=1, max_seed_hits=3),
+    dict(hit_priority=1, max_rows=1),
+    dict(seed_mismatches=1, max_seed_ranges=6, hit_priority=1, max_seed_hits=10, max_rows=14),
+]
+
+
+@pytest.mark.parametrize("mode", MODES)
+def test_map_reads_modes(oracle, mode):
+    """approximate seeds (nvBowtie's map<CHECK_EXACT> on the forward index) and hit selection by SA-range size inside the pipeline"""
+    rng = np.random.default_rng(len(mode) * 13 + sum(mode.values()))
+    G = 50000
+    genome = rng.integers(0, 4, G).astype(np.uint8)
+    genome[7000:7600] = genome[21000:21600]
+    genome[30000:30300] = genome[21100:21400]
+    genome[40000:40200] = genome[21200:21400]
+    fmi, oidx = gu.fm_index_pair(oracle, genome)
+    words = nvb.pack_genome(torch.from_numpy(genome).to(gu.dev()))
+    sym, off = map_util.make_reads(rng, genome, 2500, sub=0.04)
+    pc = map_util.map_params(15, po.GOTOH, (0, -5, -8, -3), 20, 10, 4, 0, 1, -60, **mode)
+    want_hits, want_ops, want_nc = oracle.map_reads(oidx, genome, sym, off, pc)
+    params = nvb.MapParams(nvb.GotohAligner(nvb.SEMI_GLOBAL, 0, -5, -8, -3), 20, 10, 4, 0, 15, True, -60, **mode)
+    rs = gu.sset(sym, off)
+    for rpb in (0, 900):
+        hits, ops, stats = nvb.map_reads(fmi, words, rs.symbols, rs.offsets, params, reads_per_batch=rpb)
+        assert same(hits_np(hits), ops.cpu().numpy(), want_hits, want_ops)
+        assert stats["candidates"] == int(want_nc.sum())
+    h_hits, h_ops, _ = nvb.map_reads_host(fmi, words, sym, off, params, ops_h=np.zeros((len(off) - 1, nvb.ops_stride_for(150, 15)), np.uint8), reads_per_batch=700)
+    assert same(h_hits, h_ops, want_hits, want_ops)
+    if mode == dict(hit_priority=1):
+        plain, _, _ = oracle.map_reads(oidx, genome, sym, off, map_util.map_params(15, po.GOTOH, (0, -5, -8, -3), 20, 10, 4, 0, 1, -60))
+        assert (plain == want_hits).all()
+    assert ((want_hits["flags"] & 2) != 0).sum() > 1500
 
 
 def test_map_reads_edges(oracle):

@@ -57,3 +57,60 @@ def test_pair_hits_rules(oracle):
     assert list(out["score"][:4]) == [-10, -10, -10, -10] and out["score"][4] == -5
     assert (out["frag_begin"][0], out["frag_end"][0]) == (100, 400)
     assert list(oracle.pair_hits(H, 350, 500)["flags"]) == [3, 3, 3, 3, 1, 3]
+
+
+def test_hit_priority_rule_is_the_references_deque(oracle, ref):
+    """oracle_map.c's hit selection against the REFERENCE's own data structure (SeedHit + hit_compare in a priority_deque over a
+    vector_view, pushes that drop the bottom of a full deque: compiled from nvBowtie/bowtie2/cuda/seed_hit.h and
+    nvbio/basic/priority_deque.h in oracle/ref_wrap.cpp::ref_hit_order): identical visiting order for distinct sizes,
+    identical size sequence when sizes tie (the reference leaves the order among equals to its interval heap)."""
+    rng = np.random.default_rng(1)
+    for it in range(1500):
+        n = int(rng.integers(1, 60)); cap = int(rng.choice([0, 0, 1, 3, 8, 16]))
+        sizes = rng.permutation(np.arange(1, 400))[:n].astype(np.uint32)
+        sizes[rng.random(n) < 0.2] = 0
+        take, order = oracle.hit_priority(sizes, 4, cap, 0)
+        slots, rsizes = ref.ref_hit_order(sizes, cap)
+        assert list(order) == list(slots)
+        assert (take[order] == np.minimum(sizes[order], 4)).all() and take.sum() == np.minimum(sizes[order], 4).sum()
+        tied = rng.integers(0, 6, n).astype(np.uint32)
+        take, order = oracle.hit_priority(tied, 4, cap, 0)
+        slots, rsizes = ref.ref_hit_order(tied, cap)
+        assert list(tied[order]) == list(rsizes)
+    # the row budget is spent in visiting order
+    take, order = oracle.hit_priority(np.array([9, 2, 0, 5, 2], np.uint32), 4, 0, 7)
+    assert list(order) == [1, 4, 3, 0] and list(take) == [0, 2, 0, 3, 2]
+    # a full deque drops its largest range before every push, even for a larger newcomer (mapping_inl.h:158-160)
+    take, order = oracle.hit_priority(np.array([1, 2, 3, 10], np.uint32), 4, 3, 0)
+    assert list(order) == [0, 1, 3] and list(take) == [1, 2, 0, 4]
+
+
+def test_oracle_map_modes(oracle, ref):
+    """approximate seeds and hit priority in the composition: same results over the C restatement and over the reference's
+    headers; approximate seeding finds reads whose every exact seed is broken by a substitution"""
+    rng = np.random.default_rng(21)
+    genome = rng.integers(0, 4, 30000).astype(np.uint8)
+    genome[5000:5400] = genome[9000:9400]
+    idx = oracle.build_index(genome)
+    sym, off = map_util.make_reads(rng, genome, 200)
+    for kw in (dict(seed_mismatches=1, max_seed_ranges=4), dict(hit_priority=1, max_seed_hits=6, max_rows=10),
+               dict(seed_mismatches=1, max_seed_ranges=8, hit_priority=1, max_rows=12)):
+        P = map_util.map_params(min_score=-40, **kw)
+        h1, o1, c1 = oracle.map_reads(idx, genome, sym, off, P)
+        h2, o2, c2 = ref.map_reads(idx, genome, sym, off, P)
+        assert (h1 == h2).all() and (o1 == o2).all() and (c1 == c2).all(), kw
+        assert ((h1["flags"] & 2) != 0).sum() > 120, kw
+    # 40-bp reads with a substitution in the LAST half of each of their three 20-mer seeds (the half searched last is the seed's
+    # first half; the exact part is its second half): exact seeding finds nothing, approximate seeding maps them
+    reads = []
+    for i in range(60):
+        p = int(rng.integers(100, 29000)); r = genome[p:p + 40].copy()
+        r[3] = (r[3] + 1) % 4; r[13] = (r[13] + 2) % 4; r[23] = (r[23] + 3) % 4
+        reads.append(r)
+    sym2, off2 = po.concat(reads)
+    exact = map_util.map_params(min_score=-40, both=0)
+    approx = map_util.map_params(min_score=-40, both=0, seed_mismatches=1, max_seed_ranges=8)
+    he, _, _ = oracle.map_reads(idx, genome, sym2, off2, exact)
+    ha, _, _ = oracle.map_reads(idx, genome, sym2, off2, approx)
+    assert ((he["flags"] & 2) != 0).sum() == 0
+    assert ((ha["flags"] & 2) != 0).sum() >= 58
