@@ -722,6 +722,18 @@ def run_b200(args):
                                 concordant_frac=float(((fl & 4) != 0).float().mean().item()),
                                 both_aligned_frac=float(((fl & 3) == 3).float().mean().item()),
                                 note="mates mapped independently (seed, locate, banded Gotoh, traceback for the coordinates; op lists not kept), then nvb_pair_hits (FR, fragment <= 500)")
+            # the same with the opposite-mate window search between mapping and pairing (pairs with one aligned mate only)
+            rres = {}
+            def _pairs_rescue():
+                h, _, _ = nvb.map_reads(fmi, words, msym, moff, mparams, max_read_len=RL, want_ops=False, ctx=ctx)
+                rres["r"] = nvb.rescue_mates(h, None, msym, moff, words, int(genome.numel()), mparams.aligner, -90, 500, max_read_len=RL, ctx=ctx)
+                rres["h"] = h; rres["p"] = nvb.pair_hits(h, 0, 500, ctx=ctx)
+            _pairs_rescue()
+            barrier()
+            tms_r = time_steps(_pairs_rescue, 2, 1, flush)
+            ms_r = max_over_ranks(sum(tms_r) / len(tms_r))
+            out[ptag]["with_mate_rescue"] = dict(pairs_per_s=world * npairs / (ms_r * 1e-3), ms=ms_r, candidates=rres["r"][0], rescued=rres["r"][1],
+                                                 concordant_frac=float(((rres["p"][:, 3] & 4) != 0).float().mean().item()))
             if do_cpu:
                 # parity of the paired path: the first kp pairs through the checker's mapper and mate pairing
                 kp = int(min(npairs, max(10000, 5.0 * cpu_reads_per_s / 2)))
@@ -733,13 +745,19 @@ def run_b200(args):
                 out[ptag]["parity"] = dict(checked=kp, mate_hit_mismatches=int((got_h != wh.view(np.uint32).reshape(2 * kp, 6)).any(axis=1).sum()),
                                            pair_mismatches=int((got_p != wp.view(np.uint32).reshape(kp, 4)).any(axis=1).sum()))
                 out[ptag]["cpu"] = dict(pairs_per_s=kp / dt, cores=host_threads(), kind=kind, sample="first %d pairs" % kp)
+                # ... and of the rescue step on the same prefix (the checker rescues from ITS OWN hits, which equal ours)
+                wh2 = wh.copy()
+                rc_, rr_ = chk.rescue_mates(gh, mh, mo, po.aligner(po.GOTOH, po.SEMI_GLOBAL, (0, -5, -8, -3)), -90, 500, wh2)
+                got_r = rres["h"][:2 * kp].cpu().numpy().view(np.uint32).reshape(2 * kp, 6)
+                out[ptag]["with_mate_rescue"]["parity"] = dict(checked=kp, candidates=rc_, rescued=rr_,
+                                                               hit_mismatches=int((got_r != wh2.view(np.uint32).reshape(2 * kp, 6)).any(axis=1).sum()))
                 del mh, mo
             if strong is not None:
                 np_s = max(1, strong[1] // world)
                 if np_s == npairs:
                     ms_s = ms
                 else:
-                    del msym, moff; pres.clear()
+                    del msym, moff; pres.clear(); rres.clear()
                     msym, moff = gen_mates(genome, np_s, RL, 13 + rank, dev)
                     fn_s = lambda: _pairs(msym, moff)
                     fn_s(); barrier()
@@ -747,7 +765,7 @@ def run_b200(args):
                     ms_s = max_over_ranks(sum(tms) / len(tms))
                 out[ptag + "_strong"] = dict(pairs_per_s=world * np_s / (ms_s * 1e-3), ms=ms_s, pairs_total=world * np_s, pairs_per_rank=np_s,
                                              scaling="strong", n_gpus=world)
-            del msym, moff, pres
+            del msym, moff, pres, rres
         if do_cpu:
             del gh
         del words

@@ -433,6 +433,21 @@ int nvb_pack_2bit(nvb_ctx* ctx, const uint8_t* symbols_d, uint32_t n, uint32_t* 
 int nvb_map_reads(nvb_ctx* ctx, const nvb_fmindex* fmi_d, const uint32_t* genome_words_d, nvb_string_set reads,
                   uint32_t max_read_len, const nvb_map_params* params, uint32_t reads_per_batch,
                   nvb_read_hit* hits_d, uint8_t* ops_d, uint32_t ops_stride, nvb_map_stats* stats_h, void* stream);
+/* Opposite-mate window search for pairs with exactly one aligned mate (nvBowtie: BestOppositeScoreStream::init_context,
+ * nvBowtie/bowtie2/cuda/score_inl.h:318-411, frame_opposite_mate under PE_POLICY_FR; the opposite mate is scored with the full,
+ * unbanded aligner over at most max_frag_len text symbols, :312). mates: the 2 n reads of n pairs laid out pair by pair (the set
+ * nvb_map_reads mapped), hits_d[2 n] its hits, updated IN PLACE: the unaligned mate of such a pair is aligned on the strand the
+ * policy demands against the window in which it completes a concordant pair -- anchor forward: [anchor.begin, anchor.begin +
+ * max_frag_len), mate reverse-complemented; anchor reverse: [anchor.end - max_frag_len, anchor.end), mate forward; mates may
+ * overlap -- by full-matrix SEMI_GLOBAL scoring, and, where the score reaches min_score, the full-matrix traceback. A rescued
+ * mate gets flags = strand | 2 (aligned) | 4 (rescued), second_score = INT32_MIN, and its op list in ops_d (may be NULL; longer
+ * lists are truncated to ops_stride, n_ops keeps the full length). The pair-score targets and the max_text_gaps trimming of
+ * the reference's window (:341-392) are not part of it. Run nvb_pair_hits afterwards. Synchronises the stream twice. */
+int nvb_rescue_mates(nvb_ctx* ctx, const uint32_t* genome_words_d, uint32_t genome_len, nvb_string_set mates,
+                     uint32_t max_read_len, nvb_aligner aligner, int32_t min_score, uint32_t max_frag_len,
+                     nvb_read_hit* hits_d, uint8_t* ops_d, uint32_t ops_stride, uint32_t* n_candidates_h, uint32_t* n_rescued_h,
+                     void* stream);
+
 /* the same byte-code for the hits of nvb_map_reads: read r against the genome from hits_d[r].begin on the hit's strand
  * (unaligned reads get the empty code [2, 0]); reads = the set that was mapped, ops_d / ops_stride = its op lists */
 int nvb_map_hits_to_mds(nvb_ctx* ctx, const nvb_read_hit* hits_d, const uint8_t* ops_d, uint32_t ops_stride,

@@ -112,6 +112,7 @@ _PROTOS = {
     "nvb_batch_banded_traceback": (_i, [_vp, AlignerC, _u32, _u32, StringSetC, StringSetC, _vp, _vp, _u32, _vp, _u32, _u32, _vp, _sz, _vp]),
     "nvb_ops_to_cigar": (_i, [_vp, _vp, _u32, _vp, _u32, _vp, _u32, _vp, _vp]),
     "nvb_ops_to_mds": (_i, [_vp, _vp, _u32, _vp, _u32, StringSetC, StringSetC, _vp, _vp, _u32, _vp, _vp, _vp]),
+    "nvb_rescue_mates": (_i, [_vp, _vp, _u32, StringSetC, _u32, AlignerC, C.c_int32, _u32, _vp, _vp, _u32, _vp, _vp, _vp]),
     "nvb_map_hits_to_mds": (_i, [_vp, _vp, _vp, _u32, StringSetC, _vp, _vp, _u32, _vp, _vp, _vp]),
     "nvb_sinks_to_reference_layout": (_i, [_vp, _vp, _u32, _vp, _vp]),
     "nvb_alignments_to_reference_layout": (_i, [_vp, _vp, _u32, _vp, _vp]),

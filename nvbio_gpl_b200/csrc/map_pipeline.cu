@@ -743,6 +743,203 @@ extern "C" int nvb_map_reads(nvb_ctx* ctx, const nvb_fmindex* fmi, const uint32_
     return NVB_OK;
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Opposite-mate window search (mate rescue) for pairs with exactly one aligned mate. nvBowtie scores the opposite mate of an
+// anchor in the genome window where it would complete a concordant pair (BestOppositeScoreStream::init_context,
+// nvBowtie/bowtie2/cuda/score_inl.h:318-411; frame_opposite_mate under PE_POLICY_FR) with the full, unbanded aligner
+// (max_text_length = max_frag_len, :312). Kept from it: the window -- anchor on the forward strand: the mate lies to the right
+// on the reverse strand, [anchor.begin, anchor.begin + max_frag) (pe_overlap: the mates may overlap, :400-402); anchor on the
+// reverse strand: the mate lies to the left on the forward strand, [anchor.end - max_frag, anchor.end) (:393-397) -- clipped to
+// the genome, and full-matrix SEMI_GLOBAL scoring followed by the full-matrix traceback of the mates that reach min_score.
+// Not kept: the pair-score targets (compute_target_score) and max_text_gaps trimming of the window (:381-392).
+// ---------------------------------------------------------------------------------------------------------------
+struct RescueTask { uint32_t read, strand, gb, ge; };     // read index (the mate to rescue), its strand, genome window [gb, ge)
+
+__device__ __forceinline__ bool map_rescue_task(const nvb_read_hit* hits, uint32_t pair, uint32_t max_frag, uint32_t G, RescueTask& t)
+{
+    const nvb_read_hit a = hits[2 * (size_t)pair], b = hits[2 * (size_t)pair + 1];
+    const bool al1 = (a.flags & 2u) != 0, al2 = (b.flags & 2u) != 0;
+    if (al1 == al2) return false;
+    const nvb_read_hit& an = al1 ? a : b;
+    t.read = 2u * pair + (al1 ? 1u : 0u);
+    if (!(an.flags & 1u)) { t.strand = 1u; t.gb = an.begin; const uint64_t e = (uint64_t)an.begin + max_frag; t.ge = (uint32_t)(e < G ? e : G); }
+    else                  { t.strand = 0u; t.ge = an.end < G ? an.end : G; t.gb = t.ge > max_frag ? t.ge - max_frag : 0u; }
+    return t.ge > t.gb;
+}
+__global__ void __launch_bounds__(MAP_THREADS)
+map_rescue_flag_kernel(const nvb_read_hit* __restrict__ hits, uint32_t n_pairs, uint32_t max_frag, uint32_t G, const StrSet reads, uint8_t* __restrict__ flag)
+{
+    const uint32_t i = blockIdx.x * MAP_THREADS + threadIdx.x;
+    if (i >= n_pairs) return;
+    RescueTask t;
+    bool ok = map_rescue_task(hits, i, max_frag, G, t);
+    if (ok) { const uint32_t L = reads.off[t.read + 1] - reads.off[t.read]; ok = L > 0 && L <= t.ge - t.gb; }
+    flag[i] = ok ? 1 : 0;
+}
+// list[j] = pair index; lengths of task j (one extra zero entry for the scans)
+__global__ void __launch_bounds__(MAP_THREADS)
+map_rescue_lengths_kernel(const nvb_read_hit* __restrict__ hits, const uint32_t* __restrict__ list, uint32_t cnt, uint32_t max_frag, uint32_t G,
+                          const StrSet reads, uint32_t* __restrict__ plen, uint32_t* __restrict__ tlen)
+{
+    const uint32_t j = blockIdx.x * MAP_THREADS + threadIdx.x;
+    if (j > cnt) return;
+    if (j == cnt) { plen[j] = 0; tlen[j] = 0; return; }
+    RescueTask t; map_rescue_task(hits, list[j], max_frag, G, t);
+    plen[j] = reads.off[t.read + 1] - reads.off[t.read];
+    tlen[j] = t.ge - t.gb;
+}
+// one warp per task: strand read and genome window -> 8-bit string sets
+__global__ void __launch_bounds__(MAP_THREADS)
+map_rescue_extract_kernel(const nvb_read_hit* __restrict__ hits, const uint32_t* __restrict__ list, uint32_t cnt, uint32_t max_frag, uint32_t G,
+                          const StrSet reads, const uint32_t* __restrict__ genome, const uint32_t* __restrict__ poff, const uint32_t* __restrict__ toff,
+                          uint8_t* __restrict__ psym, uint8_t* __restrict__ tsym)
+{
+    const uint32_t w = (blockIdx.x * MAP_THREADS + threadIdx.x) >> 5, lane = threadIdx.x & 31u;
+    if (w >= cnt) return;
+    RescueTask t; map_rescue_task(hits, list[w], max_frag, G, t);
+    const uint32_t p0 = poff[w], L = poff[w + 1] - p0, t0 = toff[w], N = toff[w + 1] - t0;
+    const uint8_t* read = reads.sym + reads.off[t.read];
+    for (uint32_t i = lane; i < L; i += 32u) psym[p0 + i] = (uint8_t)map_strand_symbol(read, L, t.strand, i);
+    for (uint32_t i = lane; i < N; i += 32u)
+    {
+        const uint32_t p = t.gb + i;
+        tsym[t0 + i] = (uint8_t)((__ldg(genome + (p >> 4)) >> (30u - 2u * (p & 15u))) & 3u);
+    }
+}
+__global__ void __launch_bounds__(MAP_THREADS)
+map_rescue_pass_kernel(const nvb_best_sink* __restrict__ sinks, uint32_t cnt, int32_t min_score, uint8_t* __restrict__ flag)
+{
+    const uint32_t j = blockIdx.x * MAP_THREADS + threadIdx.x;
+    if (j < cnt) flag[j] = (sinks[j].score > MAP_INVALID && sinks[j].score >= min_score) ? 1 : 0;
+}
+// the rescued mate's hit: genome coordinates from the window, strand, aligned + rescued (bit 2) flags; its op list
+__global__ void __launch_bounds__(MAP_THREADS)
+map_rescue_finish_kernel(nvb_read_hit* __restrict__ hits, const uint32_t* __restrict__ list, uint32_t cnt, uint32_t max_frag, uint32_t G,
+                         const nvb_alignment* __restrict__ aln, const uint32_t* __restrict__ n_ops, const uint8_t* __restrict__ tb_ops, uint32_t tb_stride,
+                         uint8_t* __restrict__ ops, uint32_t ops_stride)
+{
+    const uint32_t w = (blockIdx.x * MAP_THREADS + threadIdx.x) >> 5, lane = threadIdx.x & 31u;
+    if (w >= cnt) return;
+    RescueTask t; map_rescue_task(hits, list[w], max_frag, G, t);
+    __syncwarp();                                            // every lane has read the pair before lane 0 rewrites it
+    const nvb_alignment a = aln[w];
+    const uint32_t n = n_ops[w];
+    if (lane == 0)
+    {
+        nvb_read_hit h; h.score = a.score; h.second_score = INT32_MIN;
+        h.begin = t.gb + a.source_x; h.end = t.gb + a.sink_x; h.flags = 2u | 4u | t.strand; h.n_ops = n;
+        hits[t.read] = h;
+    }
+    if (ops)
+    {
+        uint8_t* o = ops + (size_t)t.read * ops_stride; const uint8_t* src = tb_ops + (size_t)w * tb_stride;
+        const uint32_t m = n < ops_stride ? n : ops_stride;
+        for (uint32_t i = lane; i < ops_stride; i += 32u) o[i] = i < m ? src[i] : 0;
+    }
+}
+
+static int map_rescue_sets(nvb_ctx* ctx, const nvb_read_hit* hits, const uint32_t* list, uint32_t cnt, uint32_t max_frag, uint32_t G,
+                           const StrSet& reads, const uint32_t* genome, uint32_t maxL, nvb_string_set* P, nvb_string_set* T, cudaStream_t s)
+{
+    int rc;
+    uint32_t *poff, *toff; uint8_t *psym, *tsym; void* tmp;
+    MAP_STAGE(S_POFF, sizeof(uint32_t) * ((size_t)cnt + 1), poff);
+    MAP_STAGE(S_TOFF, sizeof(uint32_t) * ((size_t)cnt + 1), toff);
+    MAP_STAGE(S_PSYM, (size_t)cnt * maxL + 128, psym);
+    MAP_STAGE(S_TSYM, (size_t)cnt * max_frag + 128, tsym);
+    psym += 64; tsym += 64;
+    map_rescue_lengths_kernel<<<map_grid((uint64_t)cnt + 1), MAP_THREADS, 0, s>>>(hits, list, cnt, max_frag, G, reads, poff, toff);
+    NVB_LAUNCHED(ctx);
+    size_t tmp_bytes = 0;
+    cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, poff, poff, (int)(cnt + 1), s);
+    MAP_STAGE(S_CUB, tmp_bytes, tmp);
+    NVB_CUDA(ctx, cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, poff, poff, (int)(cnt + 1), s));
+    NVB_CUDA(ctx, cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, toff, toff, (int)(cnt + 1), s));
+    ctx->launches += 2;
+    map_rescue_extract_kernel<<<map_grid((uint64_t)cnt * 32u), MAP_THREADS, 0, s>>>(hits, list, cnt, max_frag, G, reads, genome, poff, toff, psym, tsym);
+    NVB_LAUNCHED(ctx);
+    P->symbols = psym; P->offsets = poff; P->count = cnt; P->bits = 8;
+    T->symbols = tsym; T->offsets = toff; T->count = cnt; T->bits = 8;
+    return NVB_OK;
+}
+
+extern "C" int nvb_rescue_mates(nvb_ctx* ctx, const uint32_t* genome, uint32_t genome_len, nvb_string_set mates, uint32_t maxL,
+                                nvb_aligner aligner, int32_t min_score, uint32_t max_frag_len, nvb_read_hit* hits,
+                                uint8_t* ops, uint32_t ops_stride, uint32_t* n_candidates_h, uint32_t* n_rescued_h, void* stream)
+{
+    if (!ctx) return NVB_ERR_ARG;
+    if (n_candidates_h) *n_candidates_h = 0;
+    if (n_rescued_h) *n_rescued_h = 0;
+    const uint32_t n_pairs = mates.count / 2u;
+    if (n_pairs == 0) return NVB_OK;
+    if (!genome || !mates.symbols || !mates.offsets || !hits || maxL == 0 || max_frag_len == 0) return NVB_ERR_ARG;
+    if (mates.bits != 8 || aligner.type != NVB_SEMI_GLOBAL || max_frag_len > 4096u || maxL > max_frag_len) return NVB_ERR_UNSUPPORTED;
+    if (ops && (ops_stride == 0 || (ops_stride & 15u) || (((uintptr_t)ops) & 15u))) return NVB_ERR_ARG;
+    cudaStream_t s = (cudaStream_t)stream;
+    const StrSet reads = make_set(mates);
+    int rc; void* tmp; size_t tmp_bytes = 0;
+    uint32_t* d_num; MAP_STAGE(S_NUM, 64, d_num);
+    // ---- pairs with exactly one aligned mate and a window the other mate fits into
+    uint8_t* flag; uint32_t* list;
+    MAP_STAGE(S_COUNT, (size_t)n_pairs, flag);
+    MAP_STAGE(S_SCAN, sizeof(uint32_t) * (size_t)n_pairs, list);
+    map_rescue_flag_kernel<<<map_grid(n_pairs), MAP_THREADS, 0, s>>>(hits, n_pairs, max_frag_len, genome_len, reads, flag);
+    NVB_LAUNCHED(ctx);
+    cub::DeviceSelect::Flagged(nullptr, tmp_bytes, thrust::counting_iterator<uint32_t>(0), flag, list, d_num, (int)n_pairs, s);
+    MAP_STAGE(S_CUB, tmp_bytes, tmp);
+    NVB_CUDA(ctx, cub::DeviceSelect::Flagged(tmp, tmp_bytes, thrust::counting_iterator<uint32_t>(0), flag, list, d_num, (int)n_pairs, s));
+    ctx->launches++;
+    uint32_t n_cand = 0;
+    NVB_CUDA(ctx, cudaMemcpyAsync(&n_cand, d_num, sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+    NVB_CUDA(ctx, cudaStreamSynchronize(s));
+    if (n_candidates_h) *n_candidates_h = n_cand;
+    if (n_cand == 0) return NVB_OK;
+    // ---- full-matrix scoring of every window, in chunks
+    const uint32_t chunk = 1u << 20;
+    nvb_best_sink* sinks; uint8_t* pass; uint32_t* surv;
+    MAP_STAGE(S_SINKS, sizeof(nvb_best_sink) * (size_t)n_cand, sinks);
+    MAP_STAGE(S_KEYS_A, (size_t)n_cand, pass);
+    MAP_STAGE(S_KEYS_B, sizeof(uint32_t) * (size_t)n_cand, surv);
+    for (uint32_t c0 = 0; c0 < n_cand; c0 += chunk)
+    {
+        const uint32_t cnt = n_cand - c0 < chunk ? n_cand - c0 : chunk;
+        nvb_string_set P, T;
+        if ((rc = map_rescue_sets(ctx, hits, list + c0, cnt, max_frag_len, genome_len, reads, genome, maxL, &P, &T, s))) return rc;
+        const size_t tb = nvb_temp_bytes(NVB_OP_SCORE, aligner, 0, 0, maxL, max_frag_len, cnt);
+        void* temp; MAP_STAGE(S_TBTEMP, tb, temp);
+        if ((rc = nvb_batch_score(ctx, aligner, P, T, sinks + c0, maxL, max_frag_len, temp, tb, s))) return rc;
+    }
+    map_rescue_pass_kernel<<<map_grid(n_cand), MAP_THREADS, 0, s>>>(sinks, n_cand, min_score, pass);
+    NVB_LAUNCHED(ctx);
+    tmp_bytes = 0;
+    cub::DeviceSelect::Flagged(nullptr, tmp_bytes, list, pass, surv, d_num, (int)n_cand, s);
+    MAP_STAGE(S_CUB, tmp_bytes, tmp);
+    NVB_CUDA(ctx, cub::DeviceSelect::Flagged(tmp, tmp_bytes, list, pass, surv, d_num, (int)n_cand, s));
+    ctx->launches++;
+    uint32_t n_surv = 0;
+    NVB_CUDA(ctx, cudaMemcpyAsync(&n_surv, d_num, sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+    NVB_CUDA(ctx, cudaStreamSynchronize(s));
+    if (n_rescued_h) *n_rescued_h = n_surv;
+    // ---- full-matrix traceback of the mates that passed
+    const uint32_t tb_stride = (maxL + max_frag_len + 15u) & ~15u, tb_chunk = 1u << 18;
+    for (uint32_t c0 = 0; c0 < n_surv; c0 += tb_chunk)
+    {
+        const uint32_t cnt = n_surv - c0 < tb_chunk ? n_surv - c0 : tb_chunk;
+        nvb_string_set P, T;
+        if ((rc = map_rescue_sets(ctx, hits, surv + c0, cnt, max_frag_len, genome_len, reads, genome, maxL, &P, &T, s))) return rc;
+        nvb_alignment* aln; uint8_t* tb_ops; uint32_t* tb_nops; void* temp;
+        const size_t tb = nvb_temp_bytes(NVB_OP_TRACEBACK, aligner, 0, 32, maxL, max_frag_len, cnt);
+        MAP_STAGE(S_ALN, sizeof(nvb_alignment) * (size_t)cnt, aln);
+        MAP_STAGE(S_TBOPS, (size_t)cnt * tb_stride, tb_ops);
+        MAP_STAGE(S_TBNOPS, sizeof(uint32_t) * (size_t)cnt, tb_nops);
+        MAP_STAGE(S_TBTEMP, tb, temp);
+        if ((rc = nvb_batch_traceback(ctx, aligner, 32, P, T, aln, tb_ops, tb_stride, tb_nops, maxL, max_frag_len, temp, tb, s))) return rc;
+        map_rescue_finish_kernel<<<map_grid((uint64_t)cnt * 32u), MAP_THREADS, 0, s>>>(hits, surv + c0, cnt, max_frag_len, genome_len, aln, tb_nops, tb_ops, tb_stride, ops, ops_stride);
+        NVB_LAUNCHED(ctx);
+    }
+    return NVB_OK;
+}
+
 // op lists (push order) -> forward run-length CIGARs (io::Cigar: op | len << 2, nvbio/io/alignments.h:48-65);
 // the number of entries goes to bits 8.. of the hit's flags
 __global__ void __launch_bounds__(MAP_THREADS)

@@ -141,6 +141,25 @@ def match_host_multi(ctxs, fmis, symbols_h, offsets_h=None, query_len=0, count=N
     return ranges_h
 
 
+def rescue_mates(hits, ops, symbols, offsets, genome_words, genome_len, aligner, min_score, max_frag_len=500, max_read_len=None, ctx=None):
+    """opposite-mate window search for pairs with exactly one aligned mate (``nvb_rescue_mates``; nvBowtie's
+    BestOppositeScoreStream, score_inl.h:318-411). hits (and ops, may be None) of the 2 n mates are updated in place.
+    Returns (n_candidates, n_rescued)."""
+    if not hits.is_cuda:
+        raise RuntimeError("rescue_mates needs CUDA tensors; the hot path has no CPU fallback")
+    ctx = ctx or Context.default(hits.device.index)
+    n = offsets.numel() - 1
+    if max_read_len is None:
+        o = offsets.to(torch.int64) & 0xFFFFFFFF
+        max_read_len = int((o[1:] - o[:-1]).max().item()) if n else 0
+    nc, nr = C.c_uint32(0), C.c_uint32(0)
+    check(lib().nvb_rescue_mates(ctx.h, genome_words.data_ptr(), int(genome_len), StringSetC(symbols.data_ptr(), offsets.data_ptr(), n, 8),
+                                 int(max_read_len), aligner.c(), int(min_score), int(max_frag_len), hits.data_ptr(),
+                                 ops.data_ptr() if ops is not None else None, int(ops.shape[1]) if ops is not None else 0,
+                                 C.byref(nc), C.byref(nr), current_stream_ptr()), ctx.h)
+    return nc.value, nr.value
+
+
 def map_hits_to_mds(hits, ops, symbols, offsets, genome_words, mds_stride=None, ctx=None):
     """MDS byte-code + edit distance of the hits of ``map_reads`` (``nvb_map_hits_to_mds``): read r against the genome from
     hits[r].begin on the hit's strand. Returns (mds uint8 [n, mds_stride], mds_len int32 [n], edit_distance int32 [n])."""

@@ -147,6 +147,10 @@ int ORC(pair_hits)(const orc_read_hit* hits, uint32_t n_pairs, uint32_t min_frag
 /* hit selection by SA-range size (seed_hit.h:220-230, mapping_inl.h:158-160, select_inl.h:93-113); see oracle_map.c */
 size_t ORC(hit_priority)(const uint32_t* sizes, uint32_t n, uint32_t max_hits, uint32_t max_seed_hits, uint32_t max_rows,
                          uint32_t* take, uint32_t* order, uint32_t* n_order);
+/* opposite-mate window search for pairs with one aligned mate (score_inl.h:318-411); see oracle_map.c */
+int ORC(rescue_mates)(const uint8_t* genome, uint32_t G, const uint8_t* reads, const uint32_t* read_off, uint32_t n_pairs,
+                      orc_aligner aligner, int32_t min_score, uint32_t max_frag, orc_read_hit* hits, uint8_t* ops, uint32_t ops_stride,
+                      uint32_t* n_candidates, uint32_t* n_rescued);
 /* MDS byte-code + edit distance of one alignment (nvBowtie/bowtie2/cuda/traceback_inl.h:555-690) */
 int ORC(ops_to_mds)(const uint8_t* ops, uint32_t n_ops, const uint8_t* pattern, const uint8_t* text, uint32_t j0, uint32_t k0,
                     uint8_t* mds, uint32_t cap, uint32_t* mds_len_out, uint32_t* ed_out);

@@ -348,3 +348,62 @@ int ORC(ops_to_mds)(const uint8_t* ops, uint32_t n_ops, const uint8_t* pattern, 
     if (ed_out) *ed_out = ed;
     return 0;
 }
+
+/*
+ * Opposite-mate window search for pairs with exactly one aligned mate: composition of the pinned full-matrix score / traceback
+ * entry points over the window nvBowtie frames for the opposite mate (BestOppositeScoreStream::init_context,
+ * nvBowtie/bowtie2/cuda/score_inl.h:318-411, PE_POLICY_FR, pe_overlap): anchor forward -> [anchor.begin, anchor.begin + max_frag),
+ * mate reverse-complemented (:398-404); anchor reverse -> [anchor.end - max_frag, anchor.end), mate forward (:391-397); clipped to
+ * the genome (:405). The pair-score targets and the max_text_gaps trimming (:341-392) are left out -- the composition is ours.
+ * hits[2 n_pairs] is updated in place (flags |= 4 on rescued mates), ops likewise (truncated to ops_stride).
+ */
+int ORC(rescue_mates)(const uint8_t* genome, uint32_t G, const uint8_t* reads, const uint32_t* read_off, uint32_t n_pairs,
+                      orc_aligner aligner, int32_t min_score, uint32_t max_frag, orc_read_hit* hits, uint8_t* ops, uint32_t ops_stride,
+                      uint32_t* n_candidates, uint32_t* n_rescued)
+{
+    uint32_t nc = 0, nr = 0; int failed = 0;
+    for (uint32_t i = 0; i < n_pairs; ++i)
+    {
+        const orc_read_hit a = hits[2 * (size_t)i], b = hits[2 * (size_t)i + 1];
+        const int al1 = (a.flags & 2u) != 0, al2 = (b.flags & 2u) != 0;
+        if (al1 == al2) continue;
+        const orc_read_hit an = al1 ? a : b;
+        const uint32_t read = 2 * i + (al1 ? 1u : 0u);
+        uint32_t strand, gb, ge;
+        if (!(an.flags & 1u)) { strand = 1; gb = an.begin; const uint64_t e = (uint64_t)an.begin + max_frag; ge = (uint32_t)(e < G ? e : G); }
+        else                  { strand = 0; ge = an.end < G ? an.end : G; gb = ge > max_frag ? ge - max_frag : 0; }
+        const uint32_t L = read_off[read + 1] - read_off[read];
+        if (ge <= gb || L == 0 || L > ge - gb) continue;
+        ++nc;
+        uint8_t* pat = (uint8_t*)malloc(L);
+        const uint8_t* fwd = reads + read_off[read];
+        for (uint32_t k = 0; k < L; ++k) { const uint8_t c = strand ? fwd[L - 1 - k] : fwd[k]; pat[k] = (strand && c < 4) ? (uint8_t)(3 - c) : c; }
+        const uint32_t poff[2] = { 0, L }, toff[2] = { 0, ge - gb };
+        orc_sink sink;
+        if (ORC(score)(aligner, pat, poff, genome + gb, toff, 1, &sink, 1)) { failed = 1; free(pat); continue; }
+        if (sink.score > MAP_INVALID && sink.score >= min_score)
+        {
+            const uint32_t stride = L + (ge - gb) + 16;
+            uint8_t* tb = (uint8_t*)malloc(stride);
+            orc_alignment al; uint32_t n_ops = 0;
+            if (ORC(traceback)(aligner, 32, pat, poff, genome + gb, toff, 1, &al, tb, stride, &n_ops, 1)) failed = 1;
+            else
+            {
+                orc_read_hit h; h.score = al.score; h.second_score = INT32_MIN; h.begin = gb + al.src_x; h.end = gb + al.sink_x;
+                h.flags = 2u | 4u | strand; h.n_ops = n_ops;
+                hits[read] = h;
+                if (ops && ops_stride)
+                {
+                    memset(ops + (size_t)read * ops_stride, 0, ops_stride);
+                    memcpy(ops + (size_t)read * ops_stride, tb, n_ops < ops_stride ? n_ops : ops_stride);
+                }
+                ++nr;
+            }
+            free(tb);
+        }
+        free(pat);
+    }
+    if (n_candidates) *n_candidates = nc;
+    if (n_rescued) *n_rescued = nr;
+    return failed ? -2 : 0;
+}

@@ -318,6 +318,18 @@ class Oracle:
         assert rc == 0, rc
         return out
 
+    def rescue_mates(self, genome, reads, read_off, a, min_score, max_frag, hits, ops=None):
+        """in-place opposite-mate window search over hits[2 n] (and ops[2 n, stride]); returns (n_candidates, n_rescued)"""
+        genome = np.ascontiguousarray(genome, dtype=np.uint8); reads = np.ascontiguousarray(reads, dtype=np.uint8)
+        read_off = np.ascontiguousarray(read_off, dtype=np.uint32)
+        n_pairs = (len(read_off) - 1) // 2
+        nc = C.c_uint32(0); nr = C.c_uint32(0)
+        rc = self._f("rescue_mates")(_ptr(genome), C.c_uint32(len(genome)), _ptr(reads), _ptr(read_off), C.c_uint32(n_pairs), a, C.c_int32(min_score),
+                                     C.c_uint32(max_frag), _ptr(hits), _ptr(ops) if ops is not None else None,
+                                     C.c_uint32(ops.shape[1] if ops is not None else 0), C.byref(nc), C.byref(nr))
+        assert rc == 0, rc
+        return nc.value, nr.value
+
     def hit_priority(self, sizes, max_hits, max_seed_hits=0, max_rows=0):
         """(take[n], visiting order) of oracle_map.c's hit selection by SA-range size"""
         sizes = np.ascontiguousarray(sizes, dtype=np.uint32); n = len(sizes)

@@ -212,6 +212,70 @@ def test_pair_hits(oracle):
     assert not conc[idx % 13 == 0].any()                                  # 900-bp fragments fall outside the window
 
 
+def test_rescue_mates(oracle):
+    """nvb_rescue_mates (opposite-mate window search, score_inl.h:318-411) vs the oracle's composition of the pinned full-matrix
+    score / traceback entry points, starting from the same mapped hits; then pairing again"""
+    rng = np.random.default_rng(4242)
+    G = 60000
+    genome = rng.integers(0, 4, G).astype(np.uint8)
+    fmi, oidx = gu.fm_index_pair(oracle, genome)
+    words = nvb.pack_genome(torch.from_numpy(genome).to(gu.dev()))
+    L, reads = 100, []
+    n = 600
+    for i in range(n):
+        F = int(rng.integers(180, 420))
+        p = int(rng.integers(0, G - F)) if i % 50 else (0 if i % 100 else G - F)      # some fragments hug the genome ends
+        m1 = genome[p:p + L].copy()
+        m2 = (3 - genome[p + F - L:p + F])[::-1].copy()
+        victim = m2 if i % 2 else m1
+        if i % 5 != 4:
+            # a substitution every 11 symbols: no exact 20-mer seed survives, the alignment still scores 9 x -5 = -45
+            for k in range(5, L, 11):
+                victim[k] = (victim[k] + 1 + i % 3) % 4
+            if i % 7 == 0:                                                          # and an indel
+                victim = np.delete(victim, 50) if i % 14 else np.insert(victim, 50, 2)
+        if i % 9 == 8:
+            victim = rng.integers(0, 4, L).astype(np.uint8)                           # unrelated: must stay unaligned
+        if i % 2:
+            m2 = victim
+        else:
+            m1 = victim
+        if i % 8 == 7:
+            m1, m2 = m2, m1
+        reads += [np.ascontiguousarray(m1, dtype=np.uint8), np.ascontiguousarray(m2, dtype=np.uint8)]
+    sym, off = po.concat(reads)
+    pc = map_util.map_params(15, po.GOTOH, (0, -5, -8, -3), 20, 10, 4, 0, 1, -60)
+    params = nvb.MapParams(nvb.GotohAligner(nvb.SEMI_GLOBAL, 0, -5, -8, -3), 20, 10, 4, 0, 15, True, -60)
+    want_hits, want_ops, _ = oracle.map_reads(oidx, genome, sym, off, pc)
+    rs = gu.sset(sym, off)
+    hits, ops, _ = nvb.map_reads(fmi, words, rs.symbols, rs.offsets, params)
+    assert same(hits_np(hits), ops.cpu().numpy(), want_hits, want_ops)
+    single = ((want_hits["flags"][0::2] & 2) != 0) != ((want_hits["flags"][1::2] & 2) != 0)
+    assert single.sum() > 350
+    stride = ops.shape[1]
+    w_hits, w_ops = want_hits.copy(), np.zeros((2 * n, stride), np.uint8)
+    w_ops[:, :want_ops.shape[1]] = want_ops[:, :stride]
+    a = po.aligner(po.GOTOH, po.SEMI_GLOBAL, (0, -5, -8, -3))
+    wc, wr = oracle.rescue_mates(genome, sym, off, a, -60, 500, w_hits, w_ops)
+    gc, gr = nvb.rescue_mates(hits, ops, rs.symbols, rs.offsets, words, G, params.aligner, -60, 500)
+    assert (gc, gr) == (wc, wr) and wr > 300 and wc > wr
+    got = hits_np(hits)
+    assert same(got, ops.cpu().numpy(), w_hits, w_ops)
+    rescued = (got["flags"] & 4) != 0
+    assert rescued.sum() == wr and ((got["flags"][rescued] & 2) != 0).all()
+    # untouched mates keep their hits bit for bit
+    assert (got[~rescued] == want_hits[~rescued]).all()
+    # pairing after the rescue: most of the rescued pairs are concordant now
+    pairs = nvb.pair_hits(hits, 0, 500).cpu().numpy().view(np.uint32).reshape(-1).view(nvb.PAIR_DT)
+    want_pairs = oracle.pair_hits(w_hits, 0, 500)
+    assert (pairs.view(np.uint32) == want_pairs.view(np.uint32)).all()
+    was_single = np.nonzero(single)[0]
+    assert ((pairs["flags"][was_single] & nvb.PAIR_CONCORDANT) != 0).sum() > 280
+    # a second call finds nothing new to do for the rescued pairs
+    gc2, gr2 = nvb.rescue_mates(hits, ops, rs.symbols, rs.offsets, words, G, params.aligner, -60, 500)
+    assert gc2 == wc - wr and gr2 == 0
+
+
 def test_multi_context_host_entries(oracle):
     """nvb_map_reads_host_multi / nvb_fm_match_host_multi (one host thread per context, contiguous slices of one host
     batch, disjoint ranges of one result array): three contexts -- on this box all on device 0, each with its own stream and

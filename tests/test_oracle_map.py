@@ -114,3 +114,40 @@ def test_oracle_map_modes(oracle, ref):
     ha, _, _ = oracle.map_reads(idx, genome, sym2, off2, approx)
     assert ((he["flags"] & 2) != 0).sum() == 0
     assert ((ha["flags"] & 2) != 0).sum() >= 58
+
+
+def test_rescue_mates_composition(oracle, ref):
+    """the opposite-mate window search over the C restatement and over the reference's headers agree; a mate no seed can find is
+    recovered next to its anchor, on the strand and side the FR policy demands"""
+    rng = np.random.default_rng(9)
+    G = 20000
+    genome = rng.integers(0, 4, G).astype(np.uint8)
+    idx = oracle.build_index(genome)
+    L, reads, truth = 80, [], []
+    for i in range(60):
+        F = int(rng.integers(150, 400)); p = int(rng.integers(0, G - F))
+        m1 = genome[p:p + L].copy(); m2 = (3 - genome[p + F - L:p + F])[::-1].copy()
+        victim = m1 if i % 4 == 3 else m2                # i % 4 == 3: the forward mate is broken, the anchor lies on the reverse strand
+        for k in range(4, L, 9):
+            victim[k] = (victim[k] + 1) % 4               # no exact 20-mer seed survives
+        reads += [m1, m2]; truth.append((p, F))
+    sym, off = po.concat(reads)
+    P = map_util.map_params(min_score=-60)
+    h, o, _ = oracle.map_reads(idx, genome, sym, off, P)
+    a = po.aligner(po.GOTOH, po.SEMI_GLOBAL, (0, -5, -8, -3))
+    h1, o1 = h.copy(), o.copy(); h2, o2 = h.copy(), o.copy()
+    r1 = oracle.rescue_mates(genome, sym, off, a, -60, 500, h1, o1)
+    r2 = ref.rescue_mates(genome, sym, off, a, -60, 500, h2, o2)
+    assert r1 == r2 and (h1 == h2).all() and (o1 == o2).all()
+    assert r1[0] == 60 and r1[1] >= 58
+    for i, (p, F) in enumerate(truth):
+        broken = 2 * i + (0 if i % 4 == 3 else 1)
+        if not h1["flags"][broken] & 4:
+            continue
+        if i % 4 == 3:                                    # left of the reverse-strand anchor, on the forward strand
+            assert not (h1["flags"][broken] & 1) and abs(int(h1["begin"][broken]) - p) <= 3
+        else:                                             # right of the forward-strand anchor, reverse-complemented
+            assert h1["flags"][broken] & 1 and abs(int(h1["end"][broken]) - (p + F)) <= 3
+        assert h1["score"][broken] >= -60
+    pairs = oracle.pair_hits(h1, 0, 500)
+    assert ((pairs["flags"] & 4) != 0).sum() >= 58
