@@ -587,7 +587,9 @@ def run_b200(args):
                 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 e0.record(); fn(); e1.record(); e1.synchronize(); ts.append(e0.elapsed_time(e1))
             return max_over_ranks(min(ts))
+        barrier()                                          # all ranks copy at the same time: the host's memory system is shared
         h2d_ms = _copy_ms(lambda: dq.copy_(hp, non_blocking=True))
+        barrier()
         d2h_ms = _copy_ms(lambda: hr2.copy_(dr, non_blocking=True))
         # both directions at once on two streams (what the pipelined call asks of the bus)
         s2 = torch.cuda.Stream(device=dev)
@@ -597,6 +599,7 @@ def run_b200(args):
                 hr2.copy_(dr, non_blocking=True)
             dq.copy_(hp, non_blocking=True)
             torch.cuda.current_stream().wait_stream(s2)
+        barrier()
         both_ms = _copy_ms(_both)
         out["fm"]["e2e_fixed4"]["copy_ceiling"] = dict(both_directions_ms=both_ms, lookups_per_s_both_directions=world * nq / (both_ms * 1e-3),
                                                        frac_of_both_directions=(both_ms / f4_ms),
