@@ -34,7 +34,8 @@ struct Full2Params
     uint32_t       n_pairs, n_tasks;
     uint32_t       lanes, tpw;     // stripes per couple, couples per warp
     uint32_t       tstride;        // text words per couple = ceil(maxN / 8)
-    uint32_t       cstride;        // candidate words per couple = maxN
+    uint32_t       cstride;        // candidate words per couple = maxN (+ lanes in the selector-stream kernels)
+    uint32_t       sstride;        // selector-stream words per couple = ceil((maxN + 2 lanes) / 2)
     int32_t        match, mismatch, ga, gb;
     int32_t        semi;           // 1 = SEMI_GLOBAL, 0 = GLOBAL
     uint32_t       one;
@@ -83,6 +84,50 @@ __device__ __forceinline__ void f2_pack_text(const StrSet& T, uint32_t* my_text,
             return word;
         };
         my_text[w] = rows8(tbA, NA, dirtyA) | (rows8(tbB, NB, dirtyB) << 2);
+    }
+}
+
+// the couple's two texts as a stream of ready-made PRMT selectors, one 16-bit entry per row: entry pad + r selects byte rA of
+// the first profile word into the low half and byte rB of the second into the high half, sign-extended
+// (((rA | rB << 8) * 0x11) + 0xC480). `pad` entries before row 0 and `pad + 1` after the last row hold a valid selector, so the
+// ramp-up and drain steps of the wavefront read the stream without a bounds check. One LDS.U16 per row replaces the nibble
+// extraction and selector arithmetic of the nibble stream (5 ALU-pipe instructions per row).
+__device__ __forceinline__ void f2_pack_selectors(const StrSet& T, uint16_t* my_sel, uint32_t k, uint32_t lanes, uint32_t pad, uint32_t tbA, uint32_t NA,
+                                                  uint32_t tbB, uint32_t NB, uint32_t Nmax, bool& dirtyA, bool& dirtyB)
+{
+    for (uint32_t e = k; e < pad; e += lanes) my_sel[e] = 0xC480u;
+    for (uint32_t e = k; e < pad + 1u; e += lanes) my_sel[pad + Nmax + e] = 0xC480u;
+    for (uint32_t w = k; w * 8 < Nmax; w += lanes)
+    {
+        const uint32_t i0 = w * 8;
+        auto rows8 = [&](const uint32_t tb, const uint32_t N, bool& dirty, uint32_t& lo, uint32_t& hi)
+        {
+            const uint8_t* src = T.sym + tb + i0;
+            if (T.bits == 8 && i0 + 8 <= N && ((uintptr_t)src & 3u) == 0)
+            {
+                lo = __ldg((const uint32_t*)src); hi = __ldg((const uint32_t*)src + 1);
+                dirty |= ((lo | hi) & 0xFCFCFCFCu) != 0;
+                lo &= 0x03030303u; hi &= 0x03030303u;
+                return;
+            }
+            lo = hi = 0;
+            #pragma unroll
+            for (uint32_t e = 0; e < 8; ++e)
+            {
+                const uint32_t r = i0 + e < N ? sym_at_rt(T.sym, T.bits, tb + i0 + e) : 0u;
+                dirty |= r > 3u;
+                if (e < 4) lo |= (r & 3u) << (8 * e); else hi |= (r & 3u) << (8 * (e - 4));
+            }
+        };
+        uint32_t al, ah, bl, bh;
+        rows8(tbA, NA, dirtyA, al, ah); rows8(tbB, NB, dirtyB, bl, bh);
+        #pragma unroll
+        for (uint32_t e = 0; e < 8; ++e)
+        {
+            if (i0 + e >= Nmax) break;
+            const uint32_t a = ((e < 4 ? al : ah) >> (8 * (e & 3))) & 3u, b = ((e < 4 ? bl : bh) >> (8 * (e & 3))) & 3u;
+            my_sel[pad + i0 + e] = (uint16_t)((a | (b << 8)) * 0x11u + 0xC480u);
+        }
     }
 }
 
@@ -137,9 +182,11 @@ dpf2_sw_kernel(const Full2Params p)
     const uint32_t Nmax = max(NA, NB);
     bool dirtyA = false, dirtyB = false;
 
-    uint32_t* my_text = s_mem + ((size_t)wib * p.tpw + (live ? g : 0)) * (p.tstride + p.cstride);
-    uint32_t* my_cand = my_text + p.tstride;
-    if (live) f2_pack_text(p.T, my_text, k, p.lanes, tbA, NA, tbB, NB, Nmax, dirtyA, dirtyB);
+    uint32_t* my_words = s_mem + ((size_t)wib * p.tpw + (live ? g : 0)) * (p.sstride + p.cstride);
+    uint16_t* my_sel   = (uint16_t*)my_words;                // selector of row r at entry pad + r
+    uint32_t* my_cand  = my_words + p.sstride;               // h[r][M] of both pairs as the last lane sends it, at entry r + pad
+    const uint32_t pad = p.lanes - 1u;
+    if (live) f2_pack_selectors(p.T, my_sel, k, p.lanes, pad, tbA, NA, tbB, NB, Nmax, dirtyA, dirtyB);
     __syncwarp();
 
     // substitution profiles in sheared scores: S' = S - G - I (0 past the pattern)
@@ -167,21 +214,22 @@ dpf2_sw_kernel(const Full2Params p)
     // column 0 of the matrix, the left input of lane 0: GLOBAL 0, SEMI_GLOBAL -G r; other lanes take their neighbour's last cell
     const uint32_t cin_mul = k == 0 ? 0u : r_one, col_mul = (k == 0 && p.semi) ? g2 : 0u;
     const bool last_lane = live && k == p.lanes - 1u;
-    uint32_t carry = 0u, send = 0u, tw = 0u;
+    uint32_t carry = 0u, send = 0u, colacc = 0u;
+    const uint16_t* sel_at = my_sel + pad - k;               // step t reads row t - k
+    uint32_t* cand_at = my_cand;                             // the last lane's step t is row t - pad
 
+    // step t: this lane's text row t - k (a dummy row while t < k, swept away by the reset at t == k)
     auto row_step = [&](const uint32_t t, const bool first)
     {
-        const uint32_t i = t - k;                               // this lane's text row (wraps while t < k: a dummy row)
-        const uint32_t cin = f2_imad(__shfl_up_sync(0xFFFFFFFFu, send, 1), cin_mul, f2_imad(i + 1u, col_mul, 0u));
+        colacc = f2_imad(col_mul, r_one, colacc);            // column 0 of lane 0: (row + 1) * col_mul
+        const uint32_t cin = f2_imad(__shfl_up_sync(0xFFFFFFFFu, send, 1), cin_mul, colacc);
         if (first && t == k)
         {
             #pragma unroll
             for (int j = 0; j < 16; ++j) H[j] = 0u;
             carry = 0u;
         }
-        if ((i & 7u) == 0 && i < Nmax) tw = my_text[i >> 3];
-        const uint32_t nib = tw & 15u; tw >>= 4;
-        const uint32_t sel = f2_imad((nib & 3u) | ((nib & 12u) << 6), 0x11u, 0xC480u);
+        const uint32_t sel = sel_at[t];
         // phase A: diagonal candidates from the previous row (FMA pipe)
         uint32_t d[16];
         {
@@ -203,8 +251,8 @@ dpf2_sw_kernel(const Full2Params p)
             H[j] = left;
         }
         send = left;
-        // h[r][M] of both pairs, un-sheared along the rows: + G r + const (const = -G Nmax keeps it >= 0)
-        if (last_lane && i < Nmax) my_cand[i] = f2_imad(Nmax - 1u - i, g2, send);
+        // h[r][M] of both pairs (still sheared along the rows) for the epilogue
+        if (last_lane) cand_at[t] = send;
     };
 
     const uint32_t steps = __reduce_max_sync(0xFFFFFFFFu, live ? Nmax + p.lanes - 1 : 0u);
@@ -220,17 +268,18 @@ dpf2_sw_kernel(const Full2Params p)
     {
         if (p.semi)
         {
+            // un-sheared along the rows: + G r + const (const = -G Nmax keeps it >= 0)
             for (uint32_t r = k; r < Nmax; r += p.lanes)
             {
-                const uint32_t c = my_cand[r];
+                const uint32_t c = f2_imad(Nmax - 1u - r, g2, my_cand[r + pad]);
                 if (r < NA) bA = max(bA, ((c & 0xFFFFu) << 16) | r);
                 if (r < NB) bB = max(bB, (c & 0xFFFF0000u) | r);
             }
         }
         else if (k == 0)
         {
-            if (NA) bA = ((my_cand[NA - 1u] & 0xFFFFu) << 16) | (NA - 1u);
-            if (NB) bB = (my_cand[NB - 1u] & 0xFFFF0000u) | (NB - 1u);
+            if (NA) bA = ((f2_imad(Nmax - NA, g2, my_cand[NA - 1u + pad]) & 0xFFFFu) << 16) | (NA - 1u);
+            if (NB) bB = (f2_imad(Nmax - NB, g2, my_cand[NB - 1u + pad]) & 0xFFFF0000u) | (NB - 1u);
         }
     }
     const uint32_t dmaskA = __ballot_sync(0xFFFFFFFFu, dirtyA), dmaskB = __ballot_sync(0xFFFFFFFFu, dirtyB);
@@ -621,13 +670,20 @@ dpf2_gotoh_kernel(const Gotoh2Params q)
     }
 }
 
-static bool full2_geometry(uint32_t maxM, uint32_t maxN, uint32_t* lanes, uint32_t* tpw, uint32_t* tstride, uint32_t* cstride, size_t* smem)
+// the largest shared-memory footprint among the kernels: the selector-stream kernels keep (maxN + 2 lanes) 16-bit selectors and
+// (maxN + lanes) candidate words per couple, the nibble-stream kernels maxN / 8 text words and maxN candidate words
+static bool full2_geometry(uint32_t maxM, uint32_t maxN, uint32_t* lanes, uint32_t* tpw, uint32_t* tstride, uint32_t* cstride, size_t* smem,
+                           uint32_t* sstride = nullptr, size_t* smem_sel = nullptr)
 {
     const uint32_t stripes = (maxM + 15u) / 16u;
     if (stripes == 0 || stripes > 32u) return false;
     *lanes = stripes; *tpw = 32u / stripes; *tstride = (maxN + 7u) / 8u; *cstride = maxN;
     *smem = (size_t)DF2_WARPS * *tpw * (*tstride + *cstride) * sizeof(uint32_t);
-    return *smem <= 160u * 1024u;
+    const uint32_t ss = (maxN + 2u * stripes + 1u) / 2u;
+    const size_t sel_bytes = (size_t)DF2_WARPS * *tpw * (ss + maxN + stripes) * sizeof(uint32_t);
+    if (sstride) *sstride = ss;
+    if (smem_sel) *smem_sel = sel_bytes;
+    return *smem <= 160u * 1024u && sel_bytes <= 160u * 1024u;
 }
 
 static bool sw_supported(const nvb_aligner& a)
@@ -665,8 +721,8 @@ int dpf2_full_score(nvb_ctx* ctx, const nvb_aligner& a, StrSet P, StrSet T, nvb_
     const Scheme s = make_scheme(a);
     Gotoh2Params q;
     Full2Params& p = q.f;
-    size_t smem;
-    if (!full2_geometry(maxM, maxN, &p.lanes, &p.tpw, &p.tstride, &p.cstride, &smem)) return NVB_ERR_UNSUPPORTED;
+    size_t smem, smem_sel;
+    if (!full2_geometry(maxM, maxN, &p.lanes, &p.tpw, &p.tstride, &p.cstride, &smem, &p.sstride, &smem_sel)) return NVB_ERR_UNSUPPORTED;
     p.P = P; p.T = T; p.sinks = sinks; p.worklist = worklist;
     p.n_pairs = P.count; p.n_tasks = (P.count + 1) / 2;
     p.match = s.match; p.mismatch = s.mismatch; p.ga = s.ga; p.gb = s.gb;
@@ -684,7 +740,10 @@ int dpf2_full_score(nvb_ctx* ctx, const nvb_aligner& a, StrSet P, StrSet T, nvb_
     const uint32_t n_warps = (p.n_tasks + p.tpw - 1) / p.tpw;
     const uint32_t grid = (n_warps + DF2_WARPS - 1) / DF2_WARPS;
     if (a.kind != NVB_GOTOH)
-        dpf2_sw_kernel<<<grid, DF2_THREADS, smem, st>>>(p);
+    {
+        p.cstride = maxN + p.lanes;
+        dpf2_sw_kernel<<<grid, DF2_THREADS, smem_sel, st>>>(p);
+    }
     else if (a.type == NVB_LOCAL)
     {
         const int32_t b = -s.gb;
