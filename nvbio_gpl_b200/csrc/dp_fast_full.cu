@@ -40,7 +40,7 @@ struct FullFastParams
     uint32_t       n_tasks;    // couples = ceil(n_pairs / 2)
     uint32_t       lanes;      // lanes (= stripes) per couple
     uint32_t       tpw;        // couples per warp = 32 / lanes
-    uint32_t       tstride;    // shared-memory words per couple = ceil(maxN / 8)
+    uint32_t       tstride;    // shared-memory words per couple = ceil((maxN + 2 lanes) / 2): one 16-bit selector per row + padding
     int32_t        match, mismatch, G, I, B;
     uint32_t       one, sixteen;   // runtime 1 and 16: keep the IMADs IMADs
     uint32_t       unshear;        // fix2(-16 b): the value handed to the next lane leaves the stripe's shear
@@ -83,7 +83,7 @@ dpf_full_sw_local_kernel(const FullFastParams p)
         const int32_t cj = j - 16 * BT * j;
         return cj < 0 ? ((((uint32_t)(cj - 1) & 0xFFFFu) << 16) | ((uint32_t)cj & 0xFFFFu)) : 0u;
     };
-    extern __shared__ uint32_t s_text[];   // [warp][couple slot][tstride]: 8 rows per word, nibble = rA | rB << 2
+    extern __shared__ uint32_t s_text[];   // [warp][couple slot][tstride]: the couple's selector stream
     const uint32_t lane = threadIdx.x & 31u, wib = threadIdx.x >> 5;
     const uint32_t warp = blockIdx.x * DPF_WARPS + wib;
     const uint32_t g = lane / p.lanes, k = lane - g * p.lanes;       // couple slot, stripe
@@ -102,36 +102,52 @@ dpf_full_sw_local_kernel(const FullFastParams p)
     const uint32_t Nmax = max(NA, NB);
     bool dirtyA = false, dirtyB = false;
 
-    // ---- prologue: the couple's lanes pack its two texts into the nibble stream
-    uint32_t* my_text = s_text + ((size_t)wib * p.tpw + (live ? g : 0)) * p.tstride;
+    // ---- prologue: the couple's lanes turn its two texts into a stream of ready-made PRMT selectors, one 16-bit entry per row:
+    // entry pad + r selects byte rA of the first profile word into the low half and byte rB of the second into the high half,
+    // sign-extended (((rA | rB << 8) * 0x11) + 0xC480). pad entries before row 0 and pad + 1 after the last row hold a valid selector,
+    // so the ramp-up and drain steps of the wavefront read the stream unconditionally: one LDS.U16 per row instead of the nibble
+    // extraction and selector arithmetic of a 4-bit stream (5 ALU-pipe instructions per row)
+    uint16_t* my_sel = (uint16_t*)(s_text + ((size_t)wib * p.tpw + (live ? g : 0)) * p.tstride);
+    const uint32_t pad = p.lanes - 1u;
     if (live)
     {
+        for (uint32_t e = k; e < pad; e += p.lanes) my_sel[e] = 0xC480u;
+        for (uint32_t e = k; e < pad + 1u; e += p.lanes) my_sel[pad + Nmax + e] = 0xC480u;
         for (uint32_t w = k; w * 8 < Nmax; w += p.lanes)
         {
-            // 8 rows of one text as 8 nibbles; whole aligned words of an 8-bit set are fetched with two 32-bit loads
-            auto rows8 = [&](const uint32_t tb, const uint32_t N, bool& dirty) -> uint32_t
+            const uint32_t i0 = w * 8;
+            // 8 rows of one text as 8 bytes; whole aligned words of an 8-bit set are fetched with two 32-bit loads
+            auto rows8 = [&](const uint32_t tb, const uint32_t N, bool& dirty, uint32_t& lo, uint32_t& hi)
             {
-                const uint32_t i0 = w * 8;
                 const uint8_t* src = p.T.sym + tb + i0;
                 if (p.T.bits == 8 && i0 + 8 <= N && ((uintptr_t)src & 3u) == 0)
                 {
-                    const uint32_t x0 = __ldg((const uint32_t*)src), x1 = __ldg((const uint32_t*)src + 1);
-                    dirty |= ((x0 | x1) & 0xFCFCFCFCu) != 0;
-                    return squeeze4(x0) | (squeeze4(x1) << 16);
+                    lo = __ldg((const uint32_t*)src); hi = __ldg((const uint32_t*)src + 1);
+                    dirty |= ((lo | hi) & 0xFCFCFCFCu) != 0;
+                    lo &= 0x03030303u; hi &= 0x03030303u;
+                    return;
                 }
-                uint32_t word = 0;
+                lo = hi = 0;
                 #pragma unroll
                 for (uint32_t e = 0; e < 8; ++e)
                 {
                     const uint32_t r = i0 + e < N ? sym_at_rt(p.T.sym, p.T.bits, tb + i0 + e) : 0u;
                     dirty |= r > 3u;
-                    word |= (r & 3u) << (4 * e);
+                    if (e < 4) lo |= (r & 3u) << (8 * e); else hi |= (r & 3u) << (8 * (e - 4));
                 }
-                return word;
             };
-            my_text[w] = rows8(tbA, NA, dirtyA) | (rows8(tbB, NB, dirtyB) << 2);
+            uint32_t al, ah, bl, bh;
+            rows8(tbA, NA, dirtyA, al, ah); rows8(tbB, NB, dirtyB, bl, bh);
+            #pragma unroll
+            for (uint32_t e = 0; e < 8; ++e)
+            {
+                if (i0 + e >= Nmax) break;
+                const uint32_t a = ((e < 4 ? al : ah) >> (8 * (e & 3))) & 3u, b = ((e < 4 ? bl : bh) >> (8 * (e & 3))) & 3u;
+                my_sel[pad + i0 + e] = (uint16_t)((a | (b << 8)) * 0x11u + 0xC480u);
+            }
         }
     }
+    const uint16_t* sel_at = my_sel + pad - k;               // step t reads row t - k
     __syncwarp();
 
     // ---- this lane's stripe: substitution profiles of 16 pattern columns of both pairs
@@ -191,7 +207,7 @@ dpf_full_sw_local_kernel(const FullFastParams p)
     asm volatile("mov.u32 %0, %1;" : "=r"(r_one) : "r"(p.one));
     asm volatile("mov.u32 %0, %1;" : "=r"(r_sixteen) : "r"(p.sixteen));
     const uint32_t zero_in = pack2(p.B + p.I);                  // H = 0 of the column left of the stripe (local j = -1)
-    uint32_t carry = zero_in, send = FLc(15), tw = 0;
+    uint32_t carry = zero_in, send = FLc(15);
 
     // one text row of the stripe. MASKED = false: every lane of the warp is on a row that exists in both of its pairs.
     // lane 0 of a couple has no left neighbour: column 0 of a LOCAL matrix is all zeros. Folded into the un-shear IMAD.
@@ -210,10 +226,8 @@ dpf_full_sw_local_kernel(const FullFastParams p)
             for (int j = 0; j < 16; ++j) H[j] = FLc(j);
             carry = zero_in;
         }
-        if ((i & 7u) == 0 && i < Nmax) tw = my_text[i >> 3];
-        const uint32_t nib = tw & 15u; tw >>= 4;
         // selector: byte rA of profA -> byte 0, its sign -> byte 1; byte rB of profB -> byte 2, sign -> byte 3
-        const uint32_t sel = imad((nib & 3u) | ((nib & 12u) << 6), 0x11u, 0xC480u);
+        const uint32_t sel = sel_at[t];
 
         // phase A: everything that only needs the previous row
         uint32_t v[16];
@@ -306,7 +320,7 @@ static bool full_geometry(uint32_t maxM, uint32_t maxN, uint32_t* lanes, uint32_
 {
     const uint32_t stripes = (maxM + 15u) / 16u;
     if (stripes == 0 || stripes > 32u) return false;
-    *lanes = stripes; *tpw = 32u / stripes; *tstride = (maxN + 7u) / 8u;
+    *lanes = stripes; *tpw = 32u / stripes; *tstride = (maxN + 2u * stripes + 1u) / 2u;
     *smem = (size_t)DPF_WARPS * *tpw * *tstride * sizeof(uint32_t);
     return *smem <= 160u * 1024u;
 }

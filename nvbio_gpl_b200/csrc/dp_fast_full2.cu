@@ -216,7 +216,7 @@ dpf2_sw_kernel(const Full2Params p)
     const bool last_lane = live && k == p.lanes - 1u;
     uint32_t carry = 0u, send = 0u, colacc = 0u;
     const uint16_t* sel_at = my_sel + pad - k;               // step t reads row t - k
-    uint32_t* cand_at = my_cand;                             // the last lane's step t is row t - pad
+    uint32_t* cand_at = my_cand + pad - k;                   // row r of the storing (last) lane at entry pad + r
 
     // step t: this lane's text row t - k (a dummy row while t < k, swept away by the reset at t == k)
     auto row_step = [&](const uint32_t t, const bool first)
@@ -374,9 +374,11 @@ dpf2_gotoh_local_kernel(const Gotoh2Params q)
     }
     const uint32_t Nmax = max(NA, NB);
     bool dirtyA = false, dirtyB = false;
-    uint32_t* my_text = s_mem + ((size_t)wib * p.tpw + (live ? g : 0)) * p.tstride;
-    if (live) f2_pack_text(p.T, my_text, k, p.lanes, tbA, NA, tbB, NB, Nmax, dirtyA, dirtyB);
+    uint16_t* my_sel = (uint16_t*)(s_mem + ((size_t)wib * p.tpw + (live ? g : 0)) * p.sstride);   // selector of row r at entry pad + r
+    const uint32_t pad = p.lanes - 1u;
+    if (live) f2_pack_selectors(p.T, my_sel, k, p.lanes, pad, tbA, NA, tbB, NB, Nmax, dirtyA, dirtyB);
     __syncwarp();
+    const uint16_t* sel_at = my_sel + pad - k;               // step t reads row t - k
 
     const int32_t go = p.ga, ge = p.gb, b = -ge, dd = go - ge, B = q.B;
     // profile bytes: S - go (the diagonal reads HO' = H' + d of the previous column: -d + b = -go)
@@ -410,7 +412,7 @@ dpf2_gotoh_local_kernel(const Gotoh2Params q)
     const uint32_t cin_mul = k == 0 ? 0u : r_one;
     const uint32_t ho_add = k == 0 ? ho_zero : q.unshear, e_add = k == 0 ? e_zero : q.unshear;
     uint32_t bestkey = f2_pack2(B) << 4, bestrow = 0u;
-    uint32_t carry = ho_zero, send_h = ho_zero, send_e = e_zero, tw = 0u;
+    uint32_t carry = ho_zero, send_h = ho_zero, send_e = e_zero;
 
     auto reset = [&]()
     {
@@ -426,9 +428,7 @@ dpf2_gotoh_local_kernel(const Gotoh2Params q)
         const uint32_t ein = f2_imad(__shfl_up_sync(0xFFFFFFFFu, send_e, 1), cin_mul, e_add);
         const uint32_t i = t - k;
         if (first && t == k) reset();
-        if ((i & 7u) == 0 && i < Nmax) tw = my_text[i >> 3];
-        const uint32_t nib = tw & 15u; tw >>= 4;
-        const uint32_t sel = f2_imad((nib & 3u) | ((nib & 12u) << 6), 0x11u, 0xC480u);
+        const uint32_t sel = sel_at[t];
 
         const uint32_t kb = f2_imad(bestkey & 0xFFF8FFF8u, r_one, 0xFFFEFFFFu);
         uint32_t acc = kb, left = hin, e = ein, diag = carry;
@@ -540,10 +540,14 @@ dpf2_gotoh_kernel(const Gotoh2Params q)
     }
     const uint32_t Nmax = max(NA, NB);
     bool dirtyA = false, dirtyB = false;
-    uint32_t* my_text = s_mem + ((size_t)wib * p.tpw + (live ? g : 0)) * (p.tstride + p.cstride);
-    uint32_t* my_cand = my_text + p.tstride;
-    if (live) f2_pack_text(p.T, my_text, k, p.lanes, tbA, NA, tbB, NB, Nmax, dirtyA, dirtyB);
+    uint32_t* my_words = s_mem + ((size_t)wib * p.tpw + (live ? g : 0)) * (p.sstride + p.cstride);
+    uint16_t* my_sel   = (uint16_t*)my_words;                // selector of row r at entry pad + r
+    uint32_t* my_cand  = my_words + p.sstride;               // captured column M of row r at entry pad + r
+    const uint32_t pad = p.lanes - 1u;
+    if (live) f2_pack_selectors(p.T, my_sel, k, p.lanes, pad, tbA, NA, tbB, NB, Nmax, dirtyA, dirtyB);
     __syncwarp();
+    const uint16_t* sel_at = my_sel + pad - k;               // step t reads row t - k
+    uint32_t* cand_at = my_cand + pad - k;
 
     const int32_t go = p.ga, ge = p.gb, b = -ge, dd = go - ge, B = q.B;
     const int32_t sm = p.match - ge - go, sx = p.mismatch - ge - go;       // >= 0
@@ -574,7 +578,7 @@ dpf2_gotoh_kernel(const Gotoh2Params q)
     const uint32_t cin_mul = k == 0 ? 0u : r_one;
     const uint32_t col_mul = (k == 0 && p.semi) ? b2 : 0u;                 // SEMI_GLOBAL: H[r][0] = 0 -> -ge r
     const uint32_t col_add = k == 0 ? (p.semi ? ho_origin : ho_row0) : 0u; // GLOBAL: H[r][0] = go + ge (r - 1) -> d, like row 0
-    uint32_t carry = 0u, send_h = 0u, send_e = 0u, tw = 0u;
+    uint32_t carry = 0u, send_h = 0u, send_e = 0u, colacc = col_add;
 
     auto reset = [&]()
     {
@@ -586,13 +590,11 @@ dpf2_gotoh_kernel(const Gotoh2Params q)
 
     auto row_step = [&](const uint32_t t, const bool first)
     {
-        const uint32_t i = t - k;
-        const uint32_t hin = f2_imad(__shfl_up_sync(0xFFFFFFFFu, send_h, 1), cin_mul, f2_imad(i + 1u, col_mul, col_add));
+        colacc = f2_imad(col_mul, r_one, colacc);            // column 0 of lane 0: col_add + (row + 1) * col_mul
+        const uint32_t hin = f2_imad(__shfl_up_sync(0xFFFFFFFFu, send_h, 1), cin_mul, colacc);
         const uint32_t ein = f2_imad(__shfl_up_sync(0xFFFFFFFFu, send_e, 1), cin_mul, 0u);        // column 0: E = -infinity
         if (first && t == k) reset();
-        if ((i & 7u) == 0 && i < Nmax) tw = my_text[i >> 3];
-        const uint32_t nib = tw & 15u; tw >>= 4;
-        const uint32_t sel = f2_imad((nib & 3u) | ((nib & 12u) << 6), 0x11u, 0xC480u);
+        const uint32_t sel = sel_at[t];
         uint32_t left = hin, e = ein, diag = carry, cap = 0u;
         carry = hin;
         #pragma unroll
@@ -609,8 +611,8 @@ dpf2_gotoh_kernel(const Gotoh2Params q)
             cap = f2_imad(left, OH[j], cap);
         }
         send_h = left; send_e = e;
-        // HO''[r][M] un-sheared along the rows: + ge r, shifted by -ge Nmax to stay >= 0
-        if (capture && i < Nmax) my_cand[i] = f2_imad(Nmax - 1u - i, b2, cap);
+        // HO''[r][M], still sheared along the rows, for the epilogue
+        if (capture) cand_at[t] = cap;
     };
 
     const uint32_t steps = __reduce_max_sync(0xFFFFFFFFu, live ? Nmax + p.lanes - 1 : 0u);
@@ -625,17 +627,18 @@ dpf2_gotoh_kernel(const Gotoh2Params q)
     {
         if (p.semi)
         {
+            // un-sheared along the rows: + ge r, shifted by -ge Nmax to stay >= 0
             for (uint32_t r = k; r < Nmax; r += p.lanes)
             {
-                const uint32_t c = my_cand[r];
+                const uint32_t c = f2_imad(Nmax - 1u - r, b2, my_cand[r + pad]);
                 if (r < NA) bA = max(bA, ((c & 0xFFFFu) << 16) | r);
                 if (r < NB) bB = max(bB, (c & 0xFFFF0000u) | r);
             }
         }
         else if (k == 0)
         {
-            if (NA) bA = ((my_cand[NA - 1u] & 0xFFFFu) << 16) | (NA - 1u);
-            if (NB) bB = (my_cand[NB - 1u] & 0xFFFF0000u) | (NB - 1u);
+            if (NA) bA = ((f2_imad(Nmax - NA, b2, my_cand[NA - 1u + pad]) & 0xFFFFu) << 16) | (NA - 1u);
+            if (NB) bB = (f2_imad(Nmax - NB, b2, my_cand[NB - 1u + pad]) & 0xFFFF0000u) | (NB - 1u);
         }
     }
     const uint32_t dmaskA = __ballot_sync(0xFFFFFFFFu, dirtyA), dmaskB = __ballot_sync(0xFFFFFFFFu, dirtyB);
@@ -680,7 +683,7 @@ static bool full2_geometry(uint32_t maxM, uint32_t maxN, uint32_t* lanes, uint32
     *lanes = stripes; *tpw = 32u / stripes; *tstride = (maxN + 7u) / 8u; *cstride = maxN;
     *smem = (size_t)DF2_WARPS * *tpw * (*tstride + *cstride) * sizeof(uint32_t);
     const uint32_t ss = (maxN + 2u * stripes + 1u) / 2u;
-    const size_t sel_bytes = (size_t)DF2_WARPS * *tpw * (ss + maxN + stripes) * sizeof(uint32_t);
+    const size_t sel_bytes = (size_t)DF2_WARPS * *tpw * (ss + maxN + 2u * stripes) * sizeof(uint32_t);
     if (sstride) *sstride = ss;
     if (smem_sel) *smem_sel = sel_bytes;
     return *smem <= 160u * 1024u && sel_bytes <= 160u * 1024u;
@@ -737,13 +740,11 @@ int dpf2_full_score(nvb_ctx* ctx, const nvb_aligner& a, StrSet P, StrSet T, nvb_
         NVB_CUDA(ctx, cudaFuncSetAttribute(dpf2_gotoh_local_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
         NVB_CUDA(ctx, cudaFuncSetAttribute(dpf2_gotoh_local_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
     }
+    p.cstride = maxN + 2u * p.lanes;                         // candidate rows are stored unconditionally: pad on both sides
     const uint32_t n_warps = (p.n_tasks + p.tpw - 1) / p.tpw;
     const uint32_t grid = (n_warps + DF2_WARPS - 1) / DF2_WARPS;
     if (a.kind != NVB_GOTOH)
-    {
-        p.cstride = maxN + p.lanes;
         dpf2_sw_kernel<<<grid, DF2_THREADS, smem_sel, st>>>(p);
-    }
     else if (a.type == NVB_LOCAL)
     {
         const int32_t b = -s.gb;
@@ -758,7 +759,7 @@ int dpf2_full_score(nvb_ctx* ctx, const nvb_aligner& a, StrSet P, StrSet T, nvb_
             const int32_t cj = j - 16 * b * j;
             q.CJ[j] = cj < 0 ? ((((uint32_t)(cj - 1) & 0xFFFFu) << 16) | ((uint32_t)cj & 0xFFFFu)) : (uint32_t)cj * 0x00010001u;
         }
-        const size_t smem_l = (size_t)DF2_WARPS * p.tpw * p.tstride * sizeof(uint32_t);
+        const size_t smem_l = (size_t)DF2_WARPS * p.tpw * p.sstride * sizeof(uint32_t);
         switch (bt)
         {
         case 1:  dpf2_gotoh_local_kernel<1><<<grid, DF2_THREADS, smem_l, st>>>(q); break;
@@ -772,7 +773,7 @@ int dpf2_full_score(nvb_ctx* ctx, const nvb_aligner& a, StrSet P, StrSet T, nvb_
         const int32_t dd = s.ga - s.gb;
         q.B = 3 * (-dd) + 4;
         q.sixteen = 16; q.unshear = 0;
-        dpf2_gotoh_kernel<<<grid, DF2_THREADS, smem, st>>>(q);
+        dpf2_gotoh_kernel<<<grid, DF2_THREADS, smem_sel, st>>>(q);
     }
     NVB_LAUNCHED(ctx);
     return NVB_OK;
