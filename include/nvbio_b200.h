@@ -473,6 +473,17 @@ typedef struct { int32_t score; uint32_t frag_begin, frag_end, flags; } nvb_pair
 int nvb_pair_hits(nvb_ctx* ctx, const nvb_read_hit* hits_d, uint32_t n_pairs, uint32_t min_frag_len, uint32_t max_frag_len,
                   nvb_pair_hit* pairs_d, void* stream);
 
+/* Mapping quality of every hit: nvBowtie's BowtieMapq2 (nvBowtie/bowtie2/cuda/mapq.h:145-316, Bowtie 2's V2 calculator) over
+ * (score, second_score) of the hit. The scheme enters through two things only, as in the reference (it asks its scheme for
+ * perfect_score(len), min_score(len) and m_monotone): match_bonus (perfect_score = len * match(0), scoring.h:254) and
+ * min_score_by_len_h[0 .. max_len], a HOST table of scheme.min_score(len) that the caller evaluates (a float expression,
+ * params.h:95-100; longer reads use entry max_len). monotone: 1 = end-to-end scoring, 0 = local. pairs_d (may be NULL): the
+ * records of nvb_pair_hits over the same hits (read 2 i, 2 i + 1 = mates of pair i); mates of a concordant pair are rated on
+ * the summed scores and ranges without a runner-up (io/alignments.h:220-228). Unaligned reads get 0. */
+int nvb_map_hits_mapq(nvb_ctx* ctx, const nvb_read_hit* hits_d, const uint32_t* read_offsets_d, uint32_t n_reads,
+                      const nvb_pair_hit* pairs_d, const int32_t* min_score_by_len_h, uint32_t max_len, int32_t match_bonus,
+                      uint32_t monotone, uint8_t* mapq_d, void* stream);
+
 /* ----------------------------------------------------------------------------------------- */
 /* One process, several contexts: the batch is cut into n_ctx contiguous slices, one host thread per context runs the   */
 /* single-context host entry point on its slice against ITS index (fmis_d[i], genome_words_d[i]: a replica per device, or the same */

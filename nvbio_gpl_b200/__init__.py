@@ -18,4 +18,4 @@ from .alignment import (  # noqa: F401
     batch_alignment_traceback, batch_banded_alignment_traceback,
     batch_score_host, batch_traceback_host, ops_to_cigar, ops_to_mds, mds_to_md_string, SINK_DT, ALN_DT,
 )
-from .pipeline import MapParams, map_reads, map_reads_host, map_reads_host_multi, match_host_multi, pack_genome, ops_stride_for, HIT_DT, FLAG_REVERSE, FLAG_ALIGNED, pair_hits, PAIR_DT, PAIR_MATE1, PAIR_MATE2, PAIR_CONCORDANT, map_hits_to_mds, rescue_mates  # noqa: F401
+from .pipeline import MapParams, map_reads, map_reads_host, map_reads_host_multi, match_host_multi, pack_genome, ops_stride_for, HIT_DT, FLAG_REVERSE, FLAG_ALIGNED, pair_hits, PAIR_DT, PAIR_MATE1, PAIR_MATE2, PAIR_CONCORDANT, map_hits_to_mds, rescue_mates, map_hits_mapq  # noqa: F401

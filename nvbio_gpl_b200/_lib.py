@@ -113,6 +113,7 @@ _PROTOS = {
     "nvb_ops_to_cigar": (_i, [_vp, _vp, _u32, _vp, _u32, _vp, _u32, _vp, _vp]),
     "nvb_ops_to_mds": (_i, [_vp, _vp, _u32, _vp, _u32, StringSetC, StringSetC, _vp, _vp, _u32, _vp, _vp, _vp]),
     "nvb_rescue_mates": (_i, [_vp, _vp, _u32, StringSetC, _u32, AlignerC, C.c_int32, _u32, _vp, _vp, _u32, _vp, _vp, _vp]),
+    "nvb_map_hits_mapq": (_i, [_vp, _vp, _vp, _u32, _vp, _vp, _u32, C.c_int32, _u32, _vp, _vp]),
     "nvb_map_hits_to_mds": (_i, [_vp, _vp, _vp, _u32, StringSetC, _vp, _vp, _u32, _vp, _vp, _vp]),
     "nvb_sinks_to_reference_layout": (_i, [_vp, _vp, _u32, _vp, _vp]),
     "nvb_alignments_to_reference_layout": (_i, [_vp, _vp, _u32, _vp, _vp]),

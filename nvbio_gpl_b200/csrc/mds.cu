@@ -137,3 +137,88 @@ extern "C" int nvb_map_hits_to_mds(nvb_ctx* ctx, const nvb_read_hit* hits, const
     NVB_LAUNCHED(ctx);
     return NVB_OK;
 }
+
+// ---------------------------------------------------------------------------------------------
+// Mapping quality of the hits of nvb_map_reads: nvBowtie's BowtieMapq2 (nvBowtie/bowtie2/cuda/mapq.h:145-316, Bowtie 2's "V2"
+// calculator), restated as tables. The scheme's min_score(len) is a float expression of the caller's scoring scheme
+// (nvBowtie/bowtie2/cuda/params.h:95-100), so the caller tabulates it by read length -- the same boundary as the quality tables --
+// and perfect_score(len) = len * match_bonus (scoring.h:254). All comparisons are single float operations in the reference's order.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t mapq_v2(int32_t best_i, bool has_second, int32_t second_i, int32_t perfect, int32_t min_score_i, bool monotone)
+{
+    // no runner-up: fraction of the score range the best score must reach -> value; last entry = otherwise     [local, end-to-end]
+    const float uniq_t[6] = { 0.8f, 0.7f, 0.6f, 0.5f, 0.4f, 0.3f };
+    const uint8_t uniq_v[2][7] = { { 44, 42, 41, 36, 28, 24, 22 }, { 42, 40, 24, 23, 8, 3, 0 } };
+    // runner-up: bands of | |best| - |second| | over the range, then tiers of the best score inside a band
+    const float top_t[4] = { 0.9f, 0.8f, 0.7f, 0.6f };
+    const uint8_t top_v[2][4][2] = { { {40,40}, {39,39}, {38,38}, {37,37} }, { {39,33}, {38,27}, {37,26}, {36,22} } };
+    const float band_t[5] = { 0.5f, 0.4f, 0.3f, 0.2f, 0.1f };
+    const float tier_t[2][5][2] = { { {.5f,.5f}, {.5f,.5f}, {.5f,.5f}, {.5f,.5f}, {.5f,.5f} },
+                                    { {.84f,.68f}, {.84f,.68f}, {.88f,.67f}, {.88f,.67f}, {.88f,.67f} } };
+    const uint8_t tier_v[2][5][4] = { { {35,25,25,20}, {34,21,21,19}, {33,18,18,16}, {32,17,17,12}, {31,14,14,9} },
+                                      { {35,25,16,5},  {34,21,14,4},  {32,18,15,3},  {31,17,11,0},  {30,12,7,0} } };
+    const float low_t[2] = { 0.5f, 0.67f };
+    const uint8_t low_v[2][2][2] = { { {11, 2}, {1, 0} }, { {6, 2}, {1, 0} } };
+    const int m = monotone ? 1 : 0;
+    const float min_score = (float)min_score_i, diff = (float)perfect - min_score, best = (float)best_i;
+    if (best < min_score) return 0u;
+    const float best_over = best - min_score;
+    if (!has_second)
+    {
+        #pragma unroll
+        for (int i = 0; i < 6; ++i) if (best_over >= __fmul_rn(diff, uniq_t[i])) return uniq_v[m][i];
+        return uniq_v[m][6];
+    }
+    const float best_diff = fabsf(fabsf(best) - fabsf((float)second_i));
+    #pragma unroll
+    for (int i = 0; i < 4; ++i) if (best_diff >= __fmul_rn(diff, top_t[i])) return top_v[m][i][best_over == diff ? 0 : 1];
+    #pragma unroll
+    for (int i = 0; i < 5; ++i)
+        if (best_diff >= __fmul_rn(diff, band_t[i]))
+        {
+            if (best_over == diff) return tier_v[m][i][0];
+            if (best_over >= __fmul_rn(diff, tier_t[m][i][0])) return tier_v[m][i][1];
+            if (best_over >= __fmul_rn(diff, tier_t[m][i][1])) return tier_v[m][i][2];
+            return tier_v[m][i][3];
+        }
+    return low_v[m][best_diff > 0.f ? 0 : 1][best_over >= __fmul_rn(diff, low_t[m]) ? 0 : 1];
+}
+
+__global__ void __launch_bounds__(MDS_THREADS)
+mapq_hits_kernel(const nvb_read_hit* __restrict__ hits, const uint32_t* __restrict__ off, uint32_t n, const nvb_pair_hit* __restrict__ pairs,
+                 const int32_t* __restrict__ min_by_len, uint32_t max_len, int32_t match_bonus, uint32_t monotone, uint8_t* __restrict__ mapq)
+{
+    const uint32_t r = blockIdx.x * MDS_THREADS + threadIdx.x;
+    if (r >= n) return;
+    const nvb_read_hit h = hits[r];
+    if (!(h.flags & 2u)) { mapq[r] = 0; return; }
+    auto len_of = [&](uint32_t i) { const uint32_t l = off[i + 1] - off[i]; return l < max_len ? l : max_len; };
+    const uint32_t L = len_of(r);
+    int32_t best = h.score, perfect = (int32_t)L * match_bonus, minsc = min_by_len[L];
+    bool has_second = h.second_score != INT32_MIN;
+    if (pairs && (pairs[r >> 1].flags & 4u))
+    {
+        // a concordant pair: scores, perfect and minimum scores of both mates summed (mapq.h:153-156, io/alignments.h:225); our
+        // reduction keeps per-mate runners-up only, so a pair has no paired second best (has_second_paired() false)
+        const uint32_t o = r ^ 1u, Lo = len_of(o);
+        best += hits[o].score; perfect += (int32_t)Lo * match_bonus; minsc += min_by_len[Lo];
+        has_second = false;
+    }
+    mapq[r] = (uint8_t)mapq_v2(best, has_second, h.second_score, perfect, minsc, monotone != 0u);
+}
+
+extern "C" int nvb_map_hits_mapq(nvb_ctx* ctx, const nvb_read_hit* hits, const uint32_t* read_offsets, uint32_t n, const nvb_pair_hit* pairs,
+                                 const int32_t* min_score_by_len_h, uint32_t max_len, int32_t match_bonus, uint32_t monotone,
+                                 uint8_t* mapq, void* stream)
+{
+    if (!ctx) return NVB_ERR_ARG;
+    if (n == 0) return NVB_OK;
+    if (!hits || !read_offsets || !min_score_by_len_h || !mapq || (pairs && (n & 1u))) return NVB_ERR_ARG;
+    void* d_tab; int rc;
+    if ((rc = nvb_stage(ctx, 56, sizeof(int32_t) * ((size_t)max_len + 1), &d_tab))) return rc;
+    NVB_CUDA(ctx, cudaMemcpyAsync(d_tab, min_score_by_len_h, sizeof(int32_t) * ((size_t)max_len + 1), cudaMemcpyHostToDevice, (cudaStream_t)stream));
+    mapq_hits_kernel<<<(n + MDS_THREADS - 1) / MDS_THREADS, MDS_THREADS, 0, (cudaStream_t)stream>>>(
+        hits, read_offsets, n, pairs, (const int32_t*)d_tab, max_len, match_bonus, monotone, mapq);
+    NVB_LAUNCHED(ctx);
+    return NVB_OK;
+}

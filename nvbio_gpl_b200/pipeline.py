@@ -160,6 +160,23 @@ def rescue_mates(hits, ops, symbols, offsets, genome_words, genome_len, aligner,
     return nc.value, nr.value
 
 
+def map_hits_mapq(hits, offsets, min_score_by_len, match_bonus=0, monotone=True, pairs=None, ctx=None):
+    """mapping quality of every hit (``nvb_map_hits_mapq``: nvBowtie's BowtieMapq2, mapq.h:145-316). min_score_by_len: host int32
+    array, entry L = scheme.min_score(L) as the caller's scoring scheme computes it; match_bonus: scheme.match(0);
+    monotone: end-to-end scoring. pairs: the tensor ``pair_hits`` returned for the same hits, or None. Returns uint8 [n]."""
+    if not hits.is_cuda:
+        raise RuntimeError("map_hits_mapq needs CUDA tensors; the hot path has no CPU fallback")
+    ctx = ctx or Context.default(hits.device.index)
+    n = offsets.numel() - 1
+    tab = np.ascontiguousarray(min_score_by_len, dtype=np.int32)
+    out = torch.empty(n, dtype=torch.uint8, device=hits.device)
+    check(lib().nvb_map_hits_mapq(ctx.h, hits.data_ptr(), offsets.data_ptr(), n, pairs.data_ptr() if pairs is not None else None,
+                                  tab.ctypes.data, len(tab) - 1, int(match_bonus), 1 if monotone else 0, out.data_ptr(),
+                                  current_stream_ptr()), ctx.h)
+    torch.cuda.current_stream().synchronize()      # the host table must outlive the staged copy
+    return out
+
+
 def map_hits_to_mds(hits, ops, symbols, offsets, genome_words, mds_stride=None, ctx=None):
     """MDS byte-code + edit distance of the hits of ``map_reads`` (``nvb_map_hits_to_mds``): read r against the genome from
     hits[r].begin on the hit's strand. Returns (mds uint8 [n, mds_stride], mds_len int32 [n], edit_distance int32 [n])."""

@@ -151,6 +151,8 @@ size_t ORC(hit_priority)(const uint32_t* sizes, uint32_t n, uint32_t max_hits, u
 int ORC(rescue_mates)(const uint8_t* genome, uint32_t G, const uint8_t* reads, const uint32_t* read_off, uint32_t n_pairs,
                       orc_aligner aligner, int32_t min_score, uint32_t max_frag, orc_read_hit* hits, uint8_t* ops, uint32_t ops_stride,
                       uint32_t* n_candidates, uint32_t* n_rescued);
+/* BowtieMapq2 (nvBowtie/bowtie2/cuda/mapq.h:145-316) on scores the caller supplies; see oracle_map.c */
+int ORC(mapq_v2)(int32_t best, int32_t has_second, int32_t second, int32_t perfect, int32_t min_score, int32_t monotone);
 /* MDS byte-code + edit distance of one alignment (nvBowtie/bowtie2/cuda/traceback_inl.h:555-690) */
 int ORC(ops_to_mds)(const uint8_t* ops, uint32_t n_ops, const uint8_t* pattern, const uint8_t* text, uint32_t j0, uint32_t k0,
                     uint8_t* mds, uint32_t cap, uint32_t* mds_len_out, uint32_t* ed_out);

@@ -407,3 +407,50 @@ int ORC(rescue_mates)(const uint8_t* genome, uint32_t G, const uint8_t* reads, c
     if (n_rescued) *n_rescued = nr;
     return failed ? -2 : 0;
 }
+
+/*
+ * Mapping quality: BowtieMapq2::operator() (nvBowtie/bowtie2/cuda/mapq.h:145-316; Bowtie 2's "V2" calculator), restated as tables.
+ * best / second: alignment scores (a pair: the sum of both mates, has_second = 0 there: our reduction keeps per-mate runners-up only);
+ * perfect / min_score: the scheme's perfect_score() and min_score() for the read (pair: sums), which the CALLER evaluates
+ * (min_score(len) is a float expression of the scheme, nvBowtie/bowtie2/cuda/params.h:95-100). All comparisons are made on floats in
+ * the reference's order. Pinned on the compiled calculator (oracle/ref_wrap.cpp::ref_bowtie_mapq2).
+ */
+int ORC(mapq_v2)(int32_t best_i, int32_t has_second, int32_t second_i, int32_t perfect, int32_t min_score_i, int32_t monotone)
+{
+    /* fraction of the score range the best score must reach, value returned (no runner-up); last entry = otherwise */
+    static const float uniq_t[6] = { 0.8f, 0.7f, 0.6f, 0.5f, 0.4f, 0.3f };
+    static const int   uniq_v[2][7] = { { 44, 42, 41, 36, 28, 24, 22 }, { 42, 40, 24, 23, 8, 3, 0 } };           /* [local, end-to-end] */
+    /* runner-up present: bands of |best| - |second| over the range, then tiers of the best score inside a band */
+    static const float top_t[4] = { 0.9f, 0.8f, 0.7f, 0.6f };
+    static const int   top_v[2][4][2] = { { {40,40}, {39,39}, {38,38}, {37,37} }, { {39,33}, {38,27}, {37,26}, {36,22} } };   /* {best == range, else} */
+    static const float band_t[5] = { 0.5f, 0.4f, 0.3f, 0.2f, 0.1f };
+    static const float tier_t[2][5][2] = { { {.5f,.5f}, {.5f,.5f}, {.5f,.5f}, {.5f,.5f}, {.5f,.5f} },
+                                           { {.84f,.68f}, {.84f,.68f}, {.88f,.67f}, {.88f,.67f}, {.88f,.67f} } };
+    static const int   tier_v[2][5][4] = { { {35,25,25,20}, {34,21,21,19}, {33,18,18,16}, {32,17,17,12}, {31,14,14,9} },
+                                           { {35,25,16,5},  {34,21,14,4},  {32,18,15,3},  {31,17,11,0},  {30,12,7,0} } };
+    static const float low_t[2] = { 0.5f, 0.67f };
+    static const int   low_v[2][2][2] = { { {11, 2}, {1, 0} }, { {6, 2}, {1, 0} } };                           /* [diff > 0, diff == 0][reached, not] */
+    const int m = monotone ? 1 : 0;
+    const float max_score = (float)perfect, min_score = (float)min_score_i;
+    const float diff = max_score - min_score, best = (float)best_i;
+    if (best < min_score) return 0;                                                                           /* :163-164 */
+    const float best_over = best - min_score;
+    if (!has_second)
+    {
+        for (int i = 0; i < 6; ++i) if (best_over >= diff * uniq_t[i]) return uniq_v[m][i];
+        return uniq_v[m][6];
+    }
+    const float second = (float)second_i;
+    float a = best < 0 ? -best : best, b = second < 0 ? -second : second;
+    float best_diff = a - b; if (best_diff < 0) best_diff = -best_diff;                                       /* fabsf(fabsf(best) - fabsf(second)) */
+    for (int i = 0; i < 4; ++i) if (best_diff >= diff * top_t[i]) return top_v[m][i][best_over == diff ? 0 : 1];
+    for (int i = 0; i < 5; ++i)
+        if (best_diff >= diff * band_t[i])
+        {
+            if (best_over == diff) return tier_v[m][i][0];
+            if (best_over >= diff * tier_t[m][i][0]) return tier_v[m][i][1];
+            if (best_over >= diff * tier_t[m][i][1]) return tier_v[m][i][2];
+            return tier_v[m][i][3];
+        }
+    return low_v[m][best_diff > 0 ? 0 : 1][best_over >= diff * low_t[m] ? 0 : 1];
+}

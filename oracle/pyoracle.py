@@ -330,6 +330,17 @@ class Oracle:
         assert rc == 0, rc
         return nc.value, nr.value
 
+    def mapq_v2(self, best, has_second, second, perfect, min_score, monotone):
+        """BowtieMapq2 on caller-supplied scores (mapq.h:145-316)"""
+        return int(self._f("mapq_v2")(C.c_int32(int(best)), C.c_int32(1 if has_second else 0), C.c_int32(int(second)), C.c_int32(int(perfect)),
+                                      C.c_int32(int(min_score)), C.c_int32(1 if monotone else 0)))
+
+    def ref_bowtie_mapq2(self, best, has_second, second, perfect, min_score, monotone, paired=False, o_best=0, o_perfect=0, o_min_score=0):
+        """the REFERENCE's compiled calculator (oracle/_ref only)"""
+        return int(self.lib.ref_bowtie_mapq2(C.c_int32(int(best)), C.c_int32(1 if has_second else 0), C.c_int32(int(second)), C.c_int32(int(perfect)),
+                                             C.c_int32(int(min_score)), C.c_int32(1 if monotone else 0), C.c_int32(1 if paired else 0),
+                                             C.c_int32(int(o_best)), C.c_int32(int(o_perfect)), C.c_int32(int(o_min_score))))
+
     def hit_priority(self, sizes, max_hits, max_seed_hits=0, max_rows=0):
         """(take[n], visiting order) of oracle_map.c's hit selection by SA-range size"""
         sizes = np.ascontiguousarray(sizes, dtype=np.uint32); n = len(sizes)

@@ -217,3 +217,30 @@ extern "C" int ref_hit_order(const uint32_t* sizes, uint32_t n, uint32_t cap, ui
     *n_out = k;
     return 0;
 }
+
+// ---------------------------------------------------------------------------------------------
+// nvBowtie's mapping quality: BowtieMapq2 (nvBowtie/bowtie2/cuda/mapq.h:132-316) instantiated over a scheme that returns the
+// caller's perfect / minimum scores (the calculator only asks its scheme for perfect_score(len), min_score(len) and m_monotone),
+// fed an io::BestPairedAlignments built the way the driver builds it (io/alignments.h:68-230).
+// ---------------------------------------------------------------------------------------------
+#include <nvBowtie/bowtie2/cuda/mapq.h>
+namespace {
+struct PinnedScheme
+{
+    int32 perfect, o_perfect, minsc, o_minsc; uint32 len; bool m_monotone;
+    int32 perfect_score(const uint32 l) const { return l == len ? perfect : o_perfect; }
+    int32 min_score(const uint32 l)     const { return l == len ? minsc : o_minsc; }
+};
+}
+extern "C" int ref_bowtie_mapq2(int32_t best, int32_t has_second, int32_t second, int32_t perfect, int32_t min_score, int32_t monotone,
+                           int32_t paired, int32_t o_best, int32_t o_perfect, int32_t o_min_score)
+{
+    using namespace nvbio;
+    PinnedScheme sc; sc.perfect = perfect; sc.o_perfect = o_perfect; sc.minsc = min_score; sc.o_minsc = o_min_score; sc.len = 100; sc.m_monotone = monotone != 0;
+    const io::Alignment a1(1000u, 0u, best, 0u, 0u, paired != 0);
+    const io::Alignment a2 = has_second ? io::Alignment(2000u, 0u, second, 0u, 0u, false) : io::Alignment::invalid();
+    const io::Alignment o1 = paired ? io::Alignment(1200u, 0u, o_best, 1u, 1u, true) : io::Alignment::invalid();
+    const io::BestPairedAlignments bp(io::BestAlignments(a1, a2), io::BestAlignments(o1, io::Alignment::invalid()));
+    nvbio::bowtie2::cuda::BowtieMapq2<PinnedScheme> mq(sc);
+    return mq(bp, 100u, 101u);
+}

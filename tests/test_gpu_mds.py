@@ -76,3 +76,54 @@ def test_map_hits_to_mds(oracle):
         if (opsh[r, :h["n_ops"][r]] == 0).all():
             assert h["score"][r] == -5 * int(ed[r])
     assert aligned > 1500
+
+
+@pytest.mark.parametrize("monotone", [True, False])
+def test_map_hits_mapq(oracle, monotone):
+    """nvb_map_hits_mapq (BowtieMapq2, mapq.h:145-316) vs the oracle restatement (itself pinned on the compiled calculator), on the
+    hits of the pipeline, unpaired and with the pair records"""
+    rng = np.random.default_rng(78 + monotone)
+    genome = rng.integers(0, 4, 40000).astype(np.uint8)
+    genome[5000:5600] = genome[20000:20600]                   # repeats: runners-up
+    genome[9000:9300] = genome[20100:20400]
+    fmi, oidx = gu.fm_index_pair(oracle, genome)
+    words = nvb.pack_genome(torch.from_numpy(genome).to(gu.dev()))
+    sym, off = map_util.make_reads(rng, genome, 3000, sub=0.03)
+    scores = (0, -5, -8, -3) if monotone else (2, -5, -8, -3)
+    params = nvb.MapParams(nvb.GotohAligner(nvb.SEMI_GLOBAL, *scores), 20, 10, 4, 0, 15, True, -60 if monotone else 30)
+    rs = gu.sset(sym, off)
+    hits, ops, _ = nvb.map_reads(fmi, words, rs.symbols, rs.offsets, params)
+    max_len = 160
+    lens = np.arange(max_len + 1)
+    tab = (np.float32(-0.6) + np.float32(-0.6) * lens.astype(np.float32)).astype(np.int32) if monotone else \
+          (np.float32(20) + np.float32(8) * np.log(np.maximum(lens, 1).astype(np.float32))).astype(np.int32)
+    bonus = scores[0]
+    h = hits.cpu().numpy().view(np.uint32).reshape(-1).view(nvb.HIT_DT)
+    L = np.minimum(np.diff(off.astype(np.int64)), max_len)
+    got = nvb.map_hits_mapq(hits, rs.offsets, tab, bonus, monotone).cpu().numpy()
+    with_second = 0
+    for r in range(len(h)):
+        if not h["flags"][r] & 2:
+            assert got[r] == 0
+            continue
+        hs = h["second_score"][r] != -(1 << 31)
+        with_second += int(hs)
+        assert got[r] == oracle.mapq_v2(h["score"][r], hs, h["second_score"][r], int(L[r]) * bonus, tab[L[r]], monotone), r
+    assert with_second > 20 and len(set(got.tolist())) > 6
+    # paired: reads 2 i, 2 i + 1 taken as mates (whatever their geometry, the rule only looks at the concordant flag)
+    n2 = len(h) // 2 * 2
+    pairs = nvb.pair_hits(hits[:n2], 0, 100000)
+    pr = pairs.cpu().numpy().view(np.uint32).reshape(-1).view(nvb.PAIR_DT)
+    gotp = nvb.map_hits_mapq(hits[:n2], rs.offsets[:n2 + 1], tab, bonus, monotone, pairs=pairs).cpu().numpy()
+    conc = 0
+    for r in range(n2):
+        if not h["flags"][r] & 2:
+            assert gotp[r] == 0
+            continue
+        if pr["flags"][r >> 1] & nvb.PAIR_CONCORDANT:
+            o = r ^ 1; conc += 1
+            want = oracle.mapq_v2(int(h["score"][r]) + int(h["score"][o]), False, 0, (int(L[r]) + int(L[o])) * bonus, int(tab[L[r]]) + int(tab[L[o]]), monotone)
+        else:
+            want = got[r]
+        assert gotp[r] == want, r
+    assert conc > 10

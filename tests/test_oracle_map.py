@@ -151,3 +151,28 @@ def test_rescue_mates_composition(oracle, ref):
         assert h1["score"][broken] >= -60
     pairs = oracle.pair_hits(h1, 0, 500)
     assert ((pairs["flags"] & 4) != 0).sum() >= 58
+
+
+def test_mapq_v2_is_the_references_calculator(oracle, ref):
+    """oracle_map.c::mapq_v2 (tables) against the compiled BowtieMapq2 (nvBowtie/bowtie2/cuda/mapq.h:145-316, instantiated in
+    oracle/ref_wrap.cpp::ref_bowtie_mapq2 over a scheme that returns the given perfect / minimum scores): end-to-end and local
+    scoring, with and without a runner-up, below the minimum score, pairs (summed scores and ranges, no runner-up)"""
+    rng = np.random.default_rng(3)
+    seen = set()
+    for it in range(40000):
+        L = int(rng.integers(30, 300)); mono = bool(rng.integers(0, 2))
+        perfect = 0 if mono else 2 * L
+        minsc = int(-0.6 - 0.6 * L) if mono else int(20 + 8 * np.log(L))
+        best = int(rng.integers(minsc - 5, perfect + 1))
+        hs = bool(rng.integers(0, 2)); second = int(rng.integers(minsc - 8, max(best, minsc - 7) + 1))
+        a = oracle.mapq_v2(best, hs, second, perfect, minsc, mono)
+        assert a == ref.ref_bowtie_mapq2(best, hs, second, perfect, minsc, mono), (best, hs, second, perfect, minsc, mono)
+        seen.add(a)
+    assert len(seen) >= 40                                    # the tables are exercised broadly
+    for it in range(5000):
+        best, ob = int(rng.integers(-60, 1)), int(rng.integers(-61, 1))
+        assert oracle.mapq_v2(best + ob, False, 0, 0, -60 - 61, True) == ref.ref_bowtie_mapq2(best, False, 0, 0, -60, True, True, ob, 0, -61)
+    # every boundary of the score range
+    for best in range(-61, 1):
+        for second in range(-61, best + 1):
+            assert oracle.mapq_v2(best, True, second, 0, -60, True) == ref.ref_bowtie_mapq2(best, True, second, 0, -60, True)
