@@ -393,8 +393,9 @@ void nvb_force_generic(nvb_ctx* ctx, int on);
 /* The nvBowtie steps it replaces, as one call: seed matching (nvBowtie/bowtie2/cuda/          */
 /* mapping_inl.h:73-86), SA-row selection and locate (locate_inl.h:115-200), banded window     */
 /* scoring (score_inl.h:85-130,482-583), best/second-best reduction (reduce_inl.h) and the     */
-/* banded traceback of the best hit (traceback_inl.h:224-277). Seed priorities, re-seeding,    */
-/* effort limits, MAPQ and mate pairing of nvBowtie are NOT part of it.                         */
+/* banded traceback of the best hit (traceback_inl.h:224-277). Re-seeding and effort limits    */
+/* beyond a row budget are NOT part of it; approximate seeds and hit selection by range size   */
+/* are modes of nvb_map_params, pairing / mate rescue / MDS / MAPQ separate calls below.        */
 /* ----------------------------------------------------------------------------------------- */
 typedef struct {
     uint32_t    seed_len;       /* symbols per seed                              (params.h:131 seed_len)  */
