@@ -576,38 +576,56 @@ def run_b200(args):
         f4_ms = max_over_ranks(sum(f4_t) / len(f4_t))
         out["fm"]["e2e_fixed4"] = dict(value=world * nq / (f4_ms * 1e-3), unit="lookups/s", ms_per_step=f4_ms,
                                        h2d_bytes_per_step=int(hp.numel() * 4), d2h_bytes_per_step=int(hr.numel() * 4))
-        # what the bus alone allows for that call: the same pinned buffers copied with no kernel in between (the call's
-        # chunks overlap the two directions, so the bound is the slower direction; the serial sum is printed beside it)
-        dq = torch.empty(hp.numel(), dtype=torch.int32, device=dev)
+        # 2-bit seeds + N exception list (nvb_fm_match_host_fixed2n): 5 bytes per 20-mer on the bus, the queries with an N listed apart
+        w2, nl = nvb.pack_symbols_2n(hs_n, QLEN)
+        h2 = torch.from_numpy(w2.view(np.int32)).pin_memory(); h2_n = h2.numpy().view(np.uint32)
+        hr_n[:] = 0
+        nvb.match_host_fixed2n(fmi, h2_n, nl, QLEN, nq, ranges_h=hr_n, ctx=ctx)
+        assert (hr_n == ranges.cpu().numpy().view(np.uint32)).all(), "2-bit + N-list host entry point disagrees"
+        barrier()
+        f2_t = []
+        for _ in range(args.steps):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(cstream)
+            nvb.match_host_fixed2n(fmi, h2_n, nl, QLEN, nq, ranges_h=hr_n, ctx=ctx)
+            e1.record(cstream); e1.synchronize()
+            f2_t.append(e0.elapsed_time(e1))
+        barrier()
+        f2_ms = max_over_ranks(sum(f2_t) / len(f2_t))
+        out["fm"]["e2e_fixed2n"] = dict(value=world * nq / (f2_ms * 1e-3), unit="lookups/s", ms_per_step=f2_ms,
+                                        h2d_bytes_per_step=int(h2.numel() * 4 + nl.size * 4), d2h_bytes_per_step=int(hr.numel() * 4),
+                                        queries_with_n=int(len(nl)))
+        # what the bus alone allows for those calls: the same pinned buffers copied with no kernel in between, each direction alone,
+        # and both at once on two streams (what the pipelined call asks of the bus); all ranks copy at the same time
         dr = torch.empty((nq, 2), dtype=torch.int32, device=dev)
         hr2 = torch.empty((nq, 2), dtype=torch.int32).pin_memory()
+        s2 = torch.cuda.Stream(device=dev)
         def _copy_ms(fn):
             ts = []
             for _ in range(3):
                 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 e0.record(); fn(); e1.record(); e1.synchronize(); ts.append(e0.elapsed_time(e1))
             return max_over_ranks(min(ts))
-        barrier()                                          # all ranks copy at the same time: the host's memory system is shared
-        h2d_ms = _copy_ms(lambda: dq.copy_(hp, non_blocking=True))
-        barrier()
-        d2h_ms = _copy_ms(lambda: hr2.copy_(dr, non_blocking=True))
-        # both directions at once on two streams (what the pipelined call asks of the bus)
-        s2 = torch.cuda.Stream(device=dev)
-        def _both():
-            s2.wait_stream(torch.cuda.current_stream())
-            with torch.cuda.stream(s2):
-                hr2.copy_(dr, non_blocking=True)
-            dq.copy_(hp, non_blocking=True)
-            torch.cuda.current_stream().wait_stream(s2)
-        barrier()
-        both_ms = _copy_ms(_both)
-        out["fm"]["e2e_fixed4"]["copy_ceiling"] = dict(both_directions_ms=both_ms, lookups_per_s_both_directions=world * nq / (both_ms * 1e-3),
-                                                       frac_of_both_directions=(both_ms / f4_ms),
-                                                       h2d_ms=h2d_ms, d2h_ms=d2h_ms, h2d_gbs=hp.numel() * 4 / h2d_ms / 1e6, d2h_gbs=hr.numel() * 4 / d2h_ms / 1e6,
-                                                       lookups_per_s_overlapped=world * nq / (max(h2d_ms, d2h_ms) * 1e-3),
-                                                       lookups_per_s_serial=world * nq / ((h2d_ms + d2h_ms) * 1e-3),
-                                                       frac_of_overlapped=(world * nq / (f4_ms * 1e-3)) / (world * nq / (max(h2d_ms, d2h_ms) * 1e-3)))
-        del hp, dq, dr, hr2
+        def _ceiling(h_in, call_ms):
+            dq = torch.empty(h_in.numel(), dtype=torch.int32, device=dev)
+            def _both():
+                s2.wait_stream(torch.cuda.current_stream())
+                with torch.cuda.stream(s2):
+                    hr2.copy_(dr, non_blocking=True)
+                dq.copy_(h_in, non_blocking=True)
+                torch.cuda.current_stream().wait_stream(s2)
+            barrier()
+            h2d_ms = _copy_ms(lambda: dq.copy_(h_in, non_blocking=True))
+            barrier()
+            d2h_ms = _copy_ms(lambda: hr2.copy_(dr, non_blocking=True))
+            barrier()
+            both_ms = _copy_ms(_both)
+            return dict(both_directions_ms=both_ms, lookups_per_s_both_directions=world * nq / (both_ms * 1e-3), frac_of_both_directions=both_ms / call_ms,
+                        h2d_ms=h2d_ms, d2h_ms=d2h_ms, h2d_gbs=h_in.numel() * 4 / h2d_ms / 1e6, d2h_gbs=hr.numel() * 4 / d2h_ms / 1e6,
+                        lookups_per_s_serial=world * nq / ((h2d_ms + d2h_ms) * 1e-3))
+        out["fm"]["e2e_fixed2n"]["copy_ceiling"] = _ceiling(h2, f2_ms)
+        out["fm"]["e2e_fixed4"]["copy_ceiling"] = _ceiling(hp, f4_ms)
+        del hp, h2, dr, hr2
 
         if rank == 0 and world == 1 and not args.no_cpu and only == "":
             fm_check("fm", fmi, hs_n, ho_n, hr_n, nq)
@@ -1057,9 +1075,10 @@ def run_b200(args):
     if "fm" in out:
         fm = out["fm"]
         line.update(value=fm["value"], ms_per_step=fm["step_ms"], gpu_launches=fm["launches"], clocks=fm["clocks"],
-                    e2e=dict({k: fm["e2e_fixed4"][k] for k in ("value", "unit", "h2d_bytes_per_step", "d2h_bytes_per_step")},
-                             call="nvb_fm_match_host_fixed: pinned host buffers, 4-bit packed 20-mers (the reference's read-stream "
-                                  "layout, N representable), no offsets on the bus; H2D + kernels + D2H of the raw ranges inside the timed region"),
+                    e2e=dict({k: fm["e2e_fixed2n"][k] for k in ("value", "unit", "h2d_bytes_per_step", "d2h_bytes_per_step")},
+                             call="nvb_fm_match_host_fixed2n: pinned host buffers, 2-bit packed 20-mers (the reference's 2-bit PackedStream layout) plus the "
+                                  "list of queries that hold an N, no offsets on the bus; H2D + kernels + D2H of the raw ranges inside the timed region; "
+                                  "the 4-bit stream form (config.e2e_fixed4_stream) and the 8-bit forms are measured beside it, all bit-identical"),
                     config={"workload": c1_workload_name(args),
                             "queries": "90% cut from the genome, 10% random, 0.1% with an N, unsorted; genome and queries generated on the host "
                                        "with numpy (seeds 2 / 100 + rank), the same arrays --impl reference uses",
@@ -1068,7 +1087,7 @@ def run_b200(args):
                             "path": "library default: batches >= 65536 queries share their search prefixes through a per-batch k-mer table "
                                     "rebuilt inside every timed call (no index-side structure beyond the reference's nvBWT image)",
                             "index_build_s": round(fm["build_s"], 2), "value_plain_loop": fm.get("plain_loop"),
-                            "e2e_copy_ceiling": fm["e2e_fixed4"].get("copy_ceiling"), "e2e_8bit_symbols_with_offsets": fm.get("e2e"), "e2e_packed4_with_offsets": fm.get("e2e_packed4"),
+                            "e2e_copy_ceiling": fm["e2e_fixed2n"].get("copy_ceiling"), "e2e_fixed4_stream": fm["e2e_fixed4"], "e2e_8bit_symbols_with_offsets": fm.get("e2e"), "e2e_packed4_with_offsets": fm.get("e2e_packed4"),
                             "value_with_prebuilt_kmer_jump_table": fm.get("ktab10"), "locate": fm.get("locate")})
         rl = fm_roofline("fm")
         if rl:

@@ -237,6 +237,12 @@ int nvb_fm_match_host_packed(nvb_ctx* ctx, const nvb_fmindex* fmi_d, const void*
  * (4 / 2 bits, big-endian words) host stream; the offsets never cross PCIe */
 int nvb_fm_match_host_fixed(nvb_ctx* ctx, const nvb_fmindex* fmi_d, const void* symbols_h, uint32_t bits,
                             uint32_t query_len, uint32_t count, uint32_t* ranges_h);
+/* the same over a 2-bit stream (the reference's genome-stream layout, PackedStream<uint32,uint8,2,true>), which cannot hold an N:
+ * n_list_h = n_count pairs (query index, position of the LAST N of that query), ascending by query index; the 2-bit code stored at
+ * an N position is ignored. Results are those of the 4/8-bit forms bit for bit (a query is answered by the search over the symbols
+ * behind its last N and match()'s N rule); 5 bytes per 20-mer cross the bus instead of 10. */
+int nvb_fm_match_host_fixed2n(nvb_ctx* ctx, const nvb_fmindex* fmi_d, const void* words_h, uint32_t query_len, uint32_t count,
+                              const uint32_t* n_list_h, uint32_t n_count, uint32_t* ranges_h);
 int nvb_fm_locate_host(nvb_ctx* ctx, const nvb_fmindex* fmi_d, const uint32_t* rows_h, uint32_t n,
                        uint32_t* pos_h);
 

@@ -8,7 +8,7 @@ only plumbing here (device buffers, streams, torch.distributed). There is no CPU
 compute call raises if the CUDA library or a CUDA device is missing.
 """
 from ._lib import lib, build, LIB_PATH, NvbError, Context  # noqa: F401
-from .fmindex import FMIndex, FMIndexFilter, match, match_reverse, match_approx, match_host, match_host_fixed, pack_symbols, rank, rank4, locate, locate_host, build_index  # noqa: F401
+from .fmindex import FMIndex, FMIndexFilter, match, match_reverse, match_approx, match_host, match_host_fixed, match_host_fixed2n, pack_symbols, pack_symbols_2n, rank, rank4, locate, locate_host, build_index  # noqa: F401
 from .io import load_index, save_index, CLoadedIndex  # noqa: F401
 from .alignment import (  # noqa: F401
     EDIT_DISTANCE, SMITH_WATERMAN, GOTOH, GLOBAL, LOCAL, SEMI_GLOBAL,

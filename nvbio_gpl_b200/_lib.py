@@ -96,6 +96,7 @@ _PROTOS = {
     "nvb_fm_match_host": (_i, [_vp, C.POINTER(FMIndexC), _vp, _vp, _u32, _vp]),
     "nvb_fm_match_host_packed": (_i, [_vp, C.POINTER(FMIndexC), _vp, _u32, _vp, _u32, _vp]),
     "nvb_fm_match_host_fixed": (_i, [_vp, C.POINTER(FMIndexC), _vp, _u32, _u32, _u32, _vp]),
+    "nvb_fm_match_host_fixed2n": (_i, [_vp, C.POINTER(FMIndexC), _vp, _u32, _u32, _vp, _u32, _vp]),
     "nvb_fm_locate_host": (_i, [_vp, C.POINTER(FMIndexC), _vp, _u32, _vp]),
     "nvb_temp_bytes": (_sz, [_i, AlignerC, _u32, _u32, _u32, _u32, _u32]),
     "nvb_batch_score": (_i, [_vp, AlignerC, StringSetC, StringSetC, _vp, _u32, _u32, _vp, _sz, _vp]),

@@ -40,7 +40,7 @@ extern "C" int nvb_ctx_create(int device, nvb_ctx** out)
     { const char* e = getenv("NVB_FM_TMA"); c->fm_tma = e ? atoi(e) != 0 : 1; }
     { const char* e = getenv("NVB_FM_SHARE_MIN"); c->fm_share_min = e ? (uint32_t)strtoul(e, nullptr, 10) : (1u << 16); }
     if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return NVB_ERR_CUDA; }
-    for (int i = 0; i < 2; ++i)
+    for (int i = 0; i < 3; ++i)
         if (cudaStreamCreateWithFlags(&c->aux[i], cudaStreamNonBlocking) != cudaSuccess) { delete c; return NVB_ERR_CUDA; }
     // nvb_batch_score_noalloc: the address of its static scratch array is resolved here, once per device, so that the entry
     // point itself can be the first thing a caller runs under CUDA graph capture (a failure only surfaces there)
@@ -57,7 +57,8 @@ extern "C" void nvb_ctx_destroy(nvb_ctx* c)
     cudaStreamSynchronize(c->stream);
     for (int i = 0; i < NVB_STAGE_SLOTS; ++i) if (c->d_stage[i]) cudaFree(c->d_stage[i]);
     if (c->d_worklist) cudaFree(c->d_worklist);
-    for (int i = 0; i < 2; ++i) if (c->aux[i]) { cudaStreamSynchronize(c->aux[i]); cudaStreamDestroy(c->aux[i]); }
+    for (int i = 0; i < 3; ++i) if (c->aux[i]) { cudaStreamSynchronize(c->aux[i]); cudaStreamDestroy(c->aux[i]); }
+    if (c->tab_ev) cudaEventDestroy(c->tab_ev);
     for (int i = 0; i < 12; ++i) if (c->host_ev[i]) cudaEventDestroy(c->host_ev[i]);
     cudaStreamDestroy(c->stream);
     delete c;
@@ -292,7 +293,8 @@ __global__ void fixed_offsets_kernel(uint32_t* off, uint32_t first, uint32_t n, 
 // memory (nvb_host_alloc) is needed for the overlap. offsets_h == NULL means `fixed_len` symbols per query
 // (offsets are then generated on the device and never cross PCIe).
 static int fm_match_host_impl(nvb_ctx* ctx, const nvb_fmindex* fmi_d, const uint8_t* symbols_h, uint32_t bits,
-                              const uint32_t* offsets_h, uint32_t fixed_len, uint32_t count, uint32_t* ranges_h)
+                              const uint32_t* offsets_h, uint32_t fixed_len, uint32_t count, uint32_t* ranges_h,
+                              const uint32_t* nlist_h = nullptr, uint32_t n_nlist = 0)
 {
     if (!ctx || !fmi_d) return NVB_ERR_ARG;
     if (count == 0) return NVB_OK;
@@ -344,9 +346,33 @@ static int fm_match_host_impl(nvb_ctx* ctx, const nvb_fmindex* fmi_d, const uint
     if (!ctx->host_ev[0])
         for (int i = 0; i < 3 * NVB_HOST_SETS; ++i) NVB_CUDA(ctx, cudaEventCreateWithFlags(&ctx->host_ev[i], cudaEventDisableTiming));
     cudaStream_t s_in = ctx->aux[0], s_k = ctx->stream, s_out = ctx->aux[1];
-    // each chunk's nvb_fm_match builds its own k-mer table. One table for the whole call was measured and is SLOWER end to
-    // end (2.85 vs 2.3-2.5 ms for 10 M 20-mers, tools/host_probe2.py): the call is bound by the two copy directions sharing
-    // the bus, not by the kernels, and shorter kernels only move the D2H copies to where they collide more with the H2D ones
+    // the N exceptions of a 2-bit stream: (query, position of its last N), ascending by query; on the device before the first kernel
+    void* d_nlist = nullptr; uint32_t nl_next = 0;
+    if (n_nlist)
+    {
+        if ((rc = nvb_stage(ctx, 57, sizeof(uint32_t) * 2 * (size_t)n_nlist, &d_nlist))) return rc;
+        NVB_CUDA(ctx, cudaMemcpyAsync(d_nlist, nlist_h, sizeof(uint32_t) * 2 * (size_t)n_nlist, cudaMemcpyHostToDevice, s_k));
+    }
+    // The kernels of a chunk are short and latency-bound (offsets, table, match, N fix-up: ~125 us in a row for 2^19 queries,
+    // against 42 us of match work). When the upload is lighter than the download (2-bit seeds: 5 B in, 8 B out per query) they are
+    // the critical path, so (1) the k-mer table is built ONCE for the call, before the first chunk, and handed to the chunks as the
+    // table of a local descriptor, and (2) chunks alternate between two compute streams, so the tail kernels of one overlap the match
+    // kernel of the next: 2.45 -> 2.05 ms for 10 M 20-mers. With a heavier upload (4-bit and 8-bit streams) the call is bound by the
+    // two copy directions sharing the bus and the same change measured 8 % SLOWER (3.82 -> 3.50 G lookups/s), so those keep one table
+    // per chunk on one stream. NVB_HOST_TABLE / NVB_HOST_STREAMS force either form (tools/host_probe4.py, profiles/r2_host_probe.txt).
+    static int env_tab = -2, env_str = -2;
+    if (env_tab == -2) { const char* e = getenv("NVB_HOST_TABLE"); env_tab = e ? (atoi(e) != 0) : -1; const char* t = getenv("NVB_HOST_STREAMS"); env_str = t ? atoi(t) : -1; }
+    const bool light_upload = (SPAN_END(OFFSET_OF(count)) + (offsets_h ? 4ull * count : 0ull)) < 8ull * count;
+    const int use_tab = env_tab >= 0 ? env_tab : (light_upload ? 1 : 0), use_str = env_str >= 0 ? env_str : (light_upload ? 2 : 1);
+    nvb_fmindex fmi_call = *fmi_d;
+    if (use_tab) { if ((rc = nvb_with_batch_table(ctx, fmi_d, count, 15u, s_k, &fmi_call))) return rc; fmi_d = &fmi_call; }
+    const bool two = use_str >= 2 && use_tab && n_chunks > 1;       // a second stream needs the shared, read-only table
+    if (two)
+    {
+        if (!ctx->tab_ev) NVB_CUDA(ctx, cudaEventCreateWithFlags(&ctx->tab_ev, cudaEventDisableTiming));
+        NVB_CUDA(ctx, cudaEventRecord(ctx->tab_ev, s_k));
+        NVB_CUDA(ctx, cudaStreamWaitEvent(ctx->aux[2], ctx->tab_ev, 0));
+    }
     // NVB_HOST_TRACE=1: per-chunk completion times of the three stages on stderr (tuning aid, tools/host_probe2.py)
     const bool trace = getenv("NVB_HOST_TRACE") != nullptr;
     std::vector<cudaEvent_t> tev;
@@ -362,6 +388,7 @@ static int fm_match_host_impl(nvb_ctx* ctx, const nvb_fmindex* fmi_d, const uint
         cudaEvent_t ev_in = ctx->host_ev[3 * b], ev_k = ctx->host_ev[3 * b + 1], ev_out = ctx->host_ev[3 * b + 2];
         const uint32_t c0 = cut[k], c1 = cut[k + 1], cnt = c1 - c0;
         const size_t b0 = SPAN_BEGIN(OFFSET_OF(c0)), nb = SPAN_END(OFFSET_OF(c1)) - b0;
+        cudaStream_t s_k = (two && (k & 1u)) ? ctx->aux[2] : ctx->stream;                       // this chunk's compute stream
         if (k >= (uint32_t)n_sets) NVB_CUDA(ctx, cudaStreamWaitEvent(s_in, ev_out, 0));       // the set's previous ranges have left
         NVB_CUDA(ctx, cudaMemcpyAsync(d_sym[b], symbols_h + b0, nb, cudaMemcpyHostToDevice, s_in));
         if (offsets_h) NVB_CUDA(ctx, cudaMemcpyAsync(d_off[b], offsets_h + c0, sizeof(uint32_t) * ((size_t)cnt + 1), cudaMemcpyHostToDevice, s_in));
@@ -375,6 +402,13 @@ static int fm_match_host_impl(nvb_ctx* ctx, const nvb_fmindex* fmi_d, const uint
         // the chunk keeps its absolute offsets: rebase the symbol pointer instead
         nvb_string_set q; q.symbols = (const uint8_t*)d_sym[b] - b0; q.offsets = (const uint32_t*)d_off[b]; q.count = cnt; q.bits = bits;
         if ((rc = nvb_fm_match(ctx, fmi_d, q, (uint32_t*)d_rng[b], s_k))) return rc;
+        if (n_nlist)
+        {
+            uint32_t nl_end = nl_next;
+            while (nl_end < n_nlist && nlist_h[2 * (size_t)nl_end] < c1) ++nl_end;
+            if ((rc = nvb_fm_fix_n(ctx, fmi_d, q, (const uint32_t*)d_nlist + 2 * (size_t)nl_next, nl_end - nl_next, c0, (uint32_t*)d_rng[b], s_k))) return rc;
+            nl_next = nl_end;
+        }
         NVB_CUDA(ctx, cudaEventRecord(ev_k, s_k));
         NVB_CUDA(ctx, cudaStreamWaitEvent(s_out, ev_k, 0));
         NVB_CUDA(ctx, cudaMemcpyAsync(ranges_h + 2 * (size_t)c0, d_rng[b], sizeof(uint32_t) * 2 * (size_t)cnt, cudaMemcpyDeviceToHost, s_out));
@@ -387,6 +421,7 @@ static int fm_match_host_impl(nvb_ctx* ctx, const nvb_fmindex* fmi_d, const uint
     NVB_CUDA(ctx, cudaStreamSynchronize(s_out));
     NVB_CUDA(ctx, cudaStreamSynchronize(s_in));
     NVB_CUDA(ctx, cudaStreamSynchronize(s_k));
+    NVB_CUDA(ctx, cudaStreamSynchronize(ctx->aux[2]));
     if (trace)
     {
         for (uint32_t k = 0; k < n_chunks; ++k)
@@ -419,6 +454,17 @@ extern "C" int nvb_fm_match_host_fixed(nvb_ctx* ctx, const nvb_fmindex* fmi_d, c
 {
     if (query_len == 0) return NVB_ERR_ARG;
     return fm_match_host_impl(ctx, fmi_d, (const uint8_t*)symbols_h, bits, nullptr, query_len, count, ranges_h);
+}
+
+// 2-bit queries of one length plus the list of queries that hold an N: n_list_h = n_count pairs (query index, position of the LAST N
+// in that query), ascending by query index; the 2-bit code at an N position is ignored. 5 bytes per 20-mer cross the bus instead of 10.
+extern "C" int nvb_fm_match_host_fixed2n(nvb_ctx* ctx, const nvb_fmindex* fmi_d, const void* words_h, uint32_t query_len, uint32_t count,
+                                         const uint32_t* n_list_h, uint32_t n_count, uint32_t* ranges_h)
+{
+    if (query_len == 0 || (n_count && !n_list_h)) return NVB_ERR_ARG;
+    for (uint32_t i = 0; i < n_count; ++i)
+        if (n_list_h[2 * (size_t)i] >= count || n_list_h[2 * (size_t)i + 1] >= query_len || (i && n_list_h[2 * (size_t)i] <= n_list_h[2 * (size_t)i - 2])) return NVB_ERR_ARG;
+    return fm_match_host_impl(ctx, fmi_d, (const uint8_t*)words_h, 2, nullptr, query_len, count, ranges_h, n_list_h, n_count);
 }
 
 extern "C" int nvb_fm_locate_host(nvb_ctx* ctx, const nvb_fmindex* fmi_d, const uint32_t* rows_h, uint32_t n, uint32_t* pos_h)

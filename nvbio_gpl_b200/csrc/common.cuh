@@ -14,7 +14,7 @@
 #define NVB_STAGE_SLOTS 64
 // stage slot map (nvb_ctx::d_stage): 0-7 *_host DP/locate entry points and FMIndexFilter | 8-32 the seed-and-extend pipeline
 // (map_pipeline.cu S_*) | 33-44 nvb_fm_match_host* (4 buffer sets x 3) | 40-41 are NOT free: they belong to that range; the
-// packed-set expansion of dp_api.cu uses 60-61 | 45-54 nvb_map_reads_host (2 sets x 5) | 55 quality-scheme tables (dp_api.cu) | 56 min-score table of nvb_map_hits_mapq (mds.cu) | 62-63 per-batch k-mer table (fm_kernels.cu)
+// packed-set expansion of dp_api.cu uses 60-61 | 45-54 nvb_map_reads_host (2 sets x 5) | 55 quality-scheme tables (dp_api.cu) | 56 min-score table of nvb_map_hits_mapq (mds.cu) | 57 N list of nvb_fm_match_host_fixed2n | 62-63 per-batch k-mer table (fm_kernels.cu)
 
 struct nvb_ctx
 {
@@ -35,7 +35,8 @@ struct nvb_ctx
     size_t       l2_bytes;
     int          fm_tma;       // fm_match stages its queries by TMA bulk copy (NVB_FM_TMA, default 1)
     cudaEvent_t  host_ev[12];  // event chain of the pipelined *_host entry points (3 per buffer set)
-    cudaStream_t aux[2];       // the *_host entry points pipeline chunks over these (H2D of one chunk under the kernel / D2H of another)
+    cudaStream_t aux[3];       // the *_host entry points pipeline chunks over these: copy-in, copy-out, second compute stream
+    cudaEvent_t  tab_ev;       // the per-call k-mer table of the FM host entry points is ready
 };
 
 // true the first time it is evaluated AT THIS PLACE for the context's device: cudaFuncSetAttribute is per device and, inside a
@@ -96,6 +97,10 @@ static inline FMView make_view(const nvb_fmindex* f)
 // per-batch k-mer table (fm_kernels.cu): replaces f.ktab by a table built in context scratch for a batch of n strings
 // of at least max_k symbols each, when that is deeper than the caller's
 int nvb_fm_batch_table(nvb_ctx* ctx, FMView& f, uint64_t n, uint32_t max_k, cudaStream_t s);
+
+// ranges of the listed (query, last-N position) entries of a 2-bit query chunk, recomputed with the N rule (fm_kernels.cu)
+int nvb_fm_fix_n(nvb_ctx* ctx, const nvb_fmindex* fmi, nvb_string_set queries, const uint32_t* list_d, uint32_t n_list, uint32_t first_query,
+                 uint32_t* ranges, cudaStream_t s);
 
 // the host entry points cut one batch into chunks: the table is built once for the whole batch and handed to the chunks
 // as the k-mer table of a local copy of the caller's descriptor

@@ -328,6 +328,44 @@ static int fm_match_launch(nvb_ctx* ctx, const nvb_fmindex* fmi, nvb_string_set 
     return NVB_OK;
 }
 
+// 2-bit query streams cannot hold an N: the host entry nvb_fm_match_host_fixed2n sends, beside the 2-bit words, a list of
+// (query, position of its LAST N). match() consumes a query from its end and returns (1, 0) at the first N it reaches while the
+// range is still non-empty, or the empty range it had already fallen into (fmindex_inl.h:186-239 as called with N symbols, the
+// behaviour tests/test_gpu_fm.py pins): so the answer of such a query is the plain search over the symbols behind its last N,
+// then that rule. One thread per listed query re-runs exactly that and overwrites the range the 2-bit search produced.
+__global__ void __launch_bounds__(FM_THREADS)
+fm_fix_n_kernel(const FMView f, const StrSet q, const uint2* __restrict__ list, uint32_t n_list, uint32_t first_query, uint32_t* __restrict__ ranges)
+{
+    __shared__ uint2 s_lut[FM_LUT_ENTRIES];
+    fm_lut_init(s_lut);
+    const uint32_t e = blockIdx.x * FM_THREADS + threadIdx.x;
+    if (e >= n_list) return;
+    const uint2 it = list[e];
+    const uint32_t qi = it.x - first_query;                    // query of this chunk
+    const uint32_t beg = q.off[qi], len = q.off[qi + 1] - beg;
+    if (it.y >= len) return;
+    uint32_t x = 0, y = f.length;
+    for (uint32_t p = len; p-- > it.y + 1u && x <= y;)
+    {
+        const uint32_t c = sym_at<2>(q.sym, beg + p);
+        const uint2 r = fm_rank2(f, x - 1u, y, c, s_lut);
+        x = f.L2[c] + r.x + 1u;
+        y = f.L2[c] + r.y;
+    }
+    if (x <= y) { x = 1; y = 0; }
+    *(uint2*)(ranges + 2 * (size_t)qi) = make_uint2(x, y);
+}
+int nvb_fm_fix_n(nvb_ctx* ctx, const nvb_fmindex* fmi, nvb_string_set queries, const uint32_t* list_d, uint32_t n_list, uint32_t first_query,
+                 uint32_t* ranges, cudaStream_t s)
+{
+    if (n_list == 0) return NVB_OK;
+    int rc = check_fmi(fmi, false); if (rc) return rc;
+    FMView f = make_view(fmi); f.ktab = nullptr; f.ktab_k = 0;
+    fm_fix_n_kernel<<<grid_for(n_list), FM_THREADS, 0, s>>>(f, make_set(queries), (const uint2*)list_d, n_list, first_query, ranges);
+    NVB_LAUNCHED(ctx);
+    return NVB_OK;
+}
+
 // k-mer jump table: one thread per k-mer runs the plain backward search of its k symbols
 __global__ void __launch_bounds__(FM_THREADS)
 fm_ktab_kernel(const FMView f, uint32_t k, uint32_t n, uint2* __restrict__ tab)

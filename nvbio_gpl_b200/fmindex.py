@@ -386,6 +386,30 @@ def match_host_fixed(fmi, symbols_h, query_len, count, ranges_h=None, ctx=None, 
     return ranges_h
 
 
+def pack_symbols_2n(symbols, query_len):
+    """fixed-length queries (uint8, 0..3 and > 3 for N) -> (2-bit big-endian words, N list): the wire format of
+    ``nvb_fm_match_host_fixed2n``. N list: uint32 [k, 2] = (query index, position of its LAST N), ascending."""
+    s = np.asarray(symbols, dtype=np.uint8)
+    n = len(s) // query_len
+    isn = (s[:n * query_len] > 3).reshape(n, query_len)
+    has = isn.any(axis=1)
+    qi = np.nonzero(has)[0].astype(np.uint32)
+    last = (query_len - 1 - np.argmax(isn[qi][:, ::-1], axis=1)).astype(np.uint32) if len(qi) else np.zeros(0, np.uint32)
+    return pack_symbols(s & 3, 2), np.ascontiguousarray(np.stack([qi, last], axis=1), dtype=np.uint32)
+
+
+def match_host_fixed2n(fmi, words_h, n_list_h, query_len, count, ranges_h=None, ctx=None):
+    """2-bit packed fixed-length queries + N exception list (``pack_symbols_2n``): the ranges of ``match_host_fixed``, bit for bit"""
+    ctx = _ctx(fmi.bwt_occ, ctx)
+    if ranges_h is None:
+        ranges_h = np.empty((count, 2), dtype=np.uint32)
+    f = fmi.c()
+    nl = np.ascontiguousarray(n_list_h, dtype=np.uint32)
+    check(lib().nvb_fm_match_host_fixed2n(ctx.h, C.byref(f), words_h.ctypes.data, query_len, count, nl.ctypes.data if len(nl) else None, len(nl),
+                                          ranges_h.ctypes.data), ctx.h)
+    return ranges_h
+
+
 def pack_symbols(symbols, bits):
     """uint8 symbols -> big-endian packed uint32 words (PackedStream<uint32*, uint8, BITS, true>: symbol 0 in the top bits)"""
     spw = 32 // bits

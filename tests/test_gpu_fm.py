@@ -394,3 +394,32 @@ def test_batch_sharing_adversarial(oracle):
             assert (u32(nvb.match_reverse(fmi, w2, s2.offsets, bits=2)) == oracle.fm_match_reverse(oidx, Q3, q2o)).all()
     finally:
         ctx.fm_batch_sharing(1 << 16)
+
+
+@pytest.mark.parametrize("n,Lq,p_n", [(1, 20, 0.0), (70001, 20, 0.01), (300000, 20, 0.001), (5000, 7, 0.2), (1500000, 20, 0.002), (4097, 33, 0.05)])
+def test_host_fixed_2bit_with_n_list(oracle, n, Lq, p_n):
+    """nvb_fm_match_host_fixed2n: 2-bit seeds + (query, last N) exception list give the ranges of the 8-bit form, bit for bit --
+    Ns at the last symbol, the first symbol, several per query, behind the point where the range is already empty"""
+    rng = np.random.default_rng(n + Lq)
+    G = 60000
+    text = rng.integers(0, 4, G).astype(np.uint8)
+    fmi, oidx = gu.fm_index_pair(oracle, text)
+    pos = rng.integers(0, G - Lq, n)
+    F = text[(pos[:, None] + np.arange(Lq)[None, :])].reshape(-1).copy()
+    junk = rng.random(n) < 0.3
+    F.reshape(n, Lq)[junk] = rng.integers(0, 4, (int(junk.sum()), Lq))
+    F[rng.random(len(F)) < p_n] = 4
+    if n > 10:
+        F.reshape(n, Lq)[3, Lq - 1] = 4; F.reshape(n, Lq)[5, 0] = 4; F.reshape(n, Lq)[7, :] = 4
+    fo = (np.arange(n + 1, dtype=np.int64) * Lq).astype(np.uint32)
+    want = oracle.fm_match(oidx, F, fo)
+    words, nlist = nvb.pack_symbols_2n(F, Lq)
+    assert len(nlist) == int((F.reshape(n, Lq) > 3).any(axis=1).sum())
+    got = nvb.match_host_fixed2n(fmi, words, nlist, Lq, n)
+    assert (got == want).all()
+    # argument checks: unsorted list, position past the query
+    if len(nlist) > 1:
+        with pytest.raises(nvb.NvbError):
+            nvb.match_host_fixed2n(fmi, words, nlist[::-1], Lq, n)
+    with pytest.raises(nvb.NvbError):
+        nvb.match_host_fixed2n(fmi, words, np.array([[0, Lq]], np.uint32), Lq, n)
