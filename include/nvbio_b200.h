@@ -415,13 +415,18 @@ typedef struct {
     /* nvBowtie's approximate seed mapping (mapping_inl.h:114-184, as called at :395-397 on the forward index): exact over the
      * first seed_len / 2 search steps, one substitution allowed in the rest, plus the exact match. 0 = exact seeds (default). The
      * first max_seed_ranges SA ranges of a seed in the reference's push order are kept (0 = 8, at most 64). The reverse-index
-     * half of nvBowtie's scheme (:399-402, mismatches in the other half of the seed) is not part of it. */
+     * half of nvBowtie's scheme (:399-402, mismatches in the other half of the seed) needs reverse_index below. */
     uint32_t    seed_mismatches, max_seed_ranges;
     /* nvBowtie's hit selection by SA-range size (seed_hit.h:220-230, select_inl.h:93-113): 0 = every range contributes its first
      * max_hits rows (default); 1 = the ranges of a read go through a deque of max_seed_hits entries that drops its largest
      * range when full (0 = unbounded; mapping_inl.h:158-160), are visited smallest first (ties: seed order) and take at most
      * max_hits rows each until max_rows rows of the read are spent (0 = no budget) */
     uint32_t    hit_priority, max_seed_hits, max_rows;
+    /* the FM-index of the REVERSED text (nvBWT's .rbwt / .rsa, loaded with nvb_fmindex_load(..., reverse = 1)), or NULL. With
+     * seed_mismatches = 1 it adds the other half of nvBowtie's approximate seeds: exact over the first (seed_len + 1) / 2 symbols
+     * of the seed, one substitution in the rest, the exact match excluded (map<IGNORE_EXACT> on rfmi, mapping_inl.h:399-402);
+     * max_seed_ranges more range slots per seed; rows are located on this index and mapped back (length - q - seed_len) */
+    const nvb_fmindex* reverse_index;
 } nvb_map_params;
 
 /* flags: bit 0 = reverse-complement strand, bit 1 = aligned. begin/end = genome coordinates of the first

@@ -35,7 +35,8 @@ struct MapGeom
 {
     uint32_t r0, n_reads;            // the batch: reads [r0, r0 + n_reads)
     uint32_t S, n_strands;           // seeds per strand (for the longest read), strands
-    uint32_t R;                      // range slots per seed: 1 (exact seeding) or max_seed_ranges (approximate seeding)
+    uint32_t R;                      // range slots per seed: 1 (exact seeding) or Rf + Rr (approximate seeding)
+    uint32_t Rf;                     // slots [0, Rf) of a seed hold forward-index ranges, [Rf, R) reverse-index ranges
     uint32_t seed_len, interval, max_hits, max_range, band;
     uint32_t len1;                   // approximate seeding: search steps that must match exactly
     uint32_t priority, deque_cap, max_rows;   // range-size hit priority (map_priority_kernel)
@@ -115,11 +116,11 @@ map_seed_kernel(const FMView f, const StrSet reads, const MapGeom g, uint2* __re
 // (mapping_inl.h:114-184 as called at :395-397: exact over the first seed_len / 2 search steps, one substitution allowed in
 // the rest, plus the exact match); the first R ranges in the reference's push order fill the seed's R slots
 __global__ void __launch_bounds__(MAP_THREADS)
-map_seed_approx_kernel(const FMView f, const StrSet reads, const MapGeom g, uint2* __restrict__ seeds, uint32_t* __restrict__ counts)
+map_seed_approx_kernel(const FMView f, const FMView rf, const StrSet reads, const MapGeom g, uint2* __restrict__ seeds, uint32_t* __restrict__ counts)
 {
     __shared__ uint2 s_lut[FM_LUT_ENTRIES];
-    __shared__ uint32_t s_L2[8];
-    if (threadIdx.x < 5) s_L2[threadIdx.x] = f.L2[threadIdx.x];
+    __shared__ uint32_t s_L2[16];
+    if (threadIdx.x < 5) { s_L2[threadIdx.x] = f.L2[threadIdx.x]; s_L2[8 + threadIdx.x] = rf.L2[threadIdx.x]; }
     fm_lut_init(s_lut);
     const uint32_t t = blockIdx.x * MAP_THREADS + threadIdx.x;
     if (t >= g.n_reads * g.n_strands * g.S) return;
@@ -128,12 +129,27 @@ map_seed_approx_kernel(const FMView f, const StrSet reads, const MapGeom g, uint
     const uint8_t* read = reads.sym + beg;
     const uint32_t o = sl.k * g.interval;
     uint2* out = seeds + (size_t)t * g.R; uint32_t* cnt = counts + (size_t)t * g.R;
+    const bool seeded = o + g.seed_len <= L;
+    // forward index: the search consumes the seed from its end; exact over its last half, one substitution in its first half
     uint32_t n = 0;
-    if (o + g.seed_len <= L)
+    if (seeded)
         fm_approx_search(f, s_lut, s_L2, g.seed_len, g.len1, true,
                          [&](uint32_t st) -> uint32_t { return map_strand_symbol(read, L, sl.strand, o + g.seed_len - 1u - st); },
-                         [&](uint32_t x, uint32_t y) { if (n < g.R) { const uint32_t c = map_rows_of(g, y - x + 1u); out[n] = make_uint2(x, c); cnt[n] = c; } ++n; });
-    for (uint32_t j = n < g.R ? n : g.R; j < g.R; ++j) { out[j] = make_uint2(1u, 0u); cnt[j] = 0u; }
+                         [&](uint32_t x, uint32_t y) { if (n < g.Rf) { const uint32_t c = map_rows_of(g, y - x + 1u); out[n] = make_uint2(x, c); cnt[n] = c; } ++n; });
+    for (uint32_t j = n < g.Rf ? n : g.Rf; j < g.Rf; ++j) { out[j] = make_uint2(1u, 0u); cnt[j] = 0u; }
+    // reverse index (the FM-index of the reversed text, nvBWT's .rbwt/.rsa): the search consumes the seed from its START, so
+    // the first half is exact and the substitution falls into the last half -- map<IGNORE_EXACT>(r_reader, (seed_len + 1) / 2,
+    // seed_len, rfmi, ...) of mapping_inl.h:399-402; the exact match was reported by the forward search already
+    if (g.R > g.Rf)
+    {
+        uint32_t m = 0;
+        const uint32_t Rr = g.R - g.Rf;
+        if (seeded)
+            fm_approx_search(rf, s_lut, s_L2 + 8, g.seed_len, (g.seed_len + 1u) / 2u, false,
+                             [&](uint32_t st) -> uint32_t { return map_strand_symbol(read, L, sl.strand, o + st); },
+                             [&](uint32_t x, uint32_t y) { if (m < Rr) { const uint32_t c = map_rows_of(g, y - x + 1u); out[g.Rf + m] = make_uint2(x, c); cnt[g.Rf + m] = c; } ++m; });
+        for (uint32_t j = m < Rr ? m : Rr; j < Rr; ++j) { out[g.Rf + j] = make_uint2(1u, 0u); cnt[g.Rf + j] = 0u; }
+    }
 }
 
 // Range-size hit priority (nvb_map_params.hit_priority = 1), per read: nvBowtie keeps a read's seed hits in a priority deque
@@ -198,27 +214,37 @@ map_expand_kernel(const uint2* __restrict__ seeds, const uint32_t* __restrict__ 
 // 10^7 hits walks more than 255 steps -- seen on the 3.1 Gbp genome), hence 32-bit step counts:
 // each thread owns a strided list of hits and starts its next walk as soon as one ends, so the lanes of a warp do
 // not wait for the longest walk among them. rows[h].x becomes the sampled row, steps[h] the distance walked.
+// REV selects the rows of one index when a reverse index takes part (slots [Rf, R) of a seed): rows of the other index pass
+// through as already-sampled dummies and are left untouched
 template <bool DENSE>
 __global__ void __launch_bounds__(MAP_THREADS)
-map_walk_kernel(const FMView f, uint32_t n_hits, uint2* __restrict__ rows, uint32_t* __restrict__ steps)
+map_walk_kernel(const FMView f, uint32_t n_hits, uint2* __restrict__ rows, uint32_t* __restrict__ steps, uint32_t R, uint32_t Rf, uint32_t rev)
 {
     __shared__ uint2 s_lut[FM_LUT_ENTRIES];
     fm_lut_init(s_lut);
+    auto mine = [&](uint32_t slot) { return R == Rf || ((slot % R) >= Rf) == (rev != 0u); };
     fm_walk_balanced<DENSE>(f, n_hits, blockIdx.x * MAP_THREADS + threadIdx.x, gridDim.x * MAP_THREADS, s_lut,
-                     [&](uint32_t h) { return rows[h].x; },
-                     [&](uint32_t h, uint32_t j, uint32_t t) { rows[h].x = j; steps[h] = t; });
+                     [&](uint32_t h) { const uint2 r = rows[h]; return mine(r.y) ? r.x : 0u; },
+                     [&](uint32_t h, uint32_t j, uint32_t t) { if (mine(rows[h].y)) { rows[h].x = j; steps[h] = t; } });
 }
 
 // sampled row + steps -> text position -> candidate key ((read * 2 + strand) << 32 | window begin)
 __global__ void __launch_bounds__(MAP_THREADS)
-map_keys_kernel(const FMView f, const MapGeom g, const uint2* __restrict__ rows, const uint32_t* __restrict__ steps,
+map_keys_kernel(const FMView f, const FMView rf, const MapGeom g, const uint2* __restrict__ rows, const uint32_t* __restrict__ steps,
                 uint32_t n_hits, uint64_t* __restrict__ keys)
 {
     const uint32_t h = blockIdx.x * MAP_THREADS + threadIdx.x;
     if (h >= n_hits) return;
     const uint2 rec = rows[h];
-    const uint32_t pos = __ldg(f.sa_tab + (rec.x >> f.sa_shift)) + steps[h];
     const MapSlot sl = map_slot(g, rec.y);
+    uint32_t pos;
+    if (sl.j < g.Rf) pos = __ldg(f.sa_tab + (rec.x >> f.sa_shift)) + steps[h];
+    else
+    {
+        // an occurrence of the reversed seed at q in the reversed text is an occurrence of the seed at length - q - seed_len
+        const uint32_t q = __ldg(rf.sa_tab + (rec.x >> rf.sa_shift)) + steps[h];
+        pos = f.length - q - g.seed_len;
+    }
     const uint32_t r = sl.r, strand = sl.strand;
     const uint32_t o = sl.k * g.interval;
     const uint32_t g_pos = pos > o ? pos - o : 0u;
@@ -572,7 +598,12 @@ extern "C" int nvb_map_reads(nvb_ctx* ctx, const nvb_fmindex* fmi, const uint32_
     g.n_strands = mp->both_strands ? 2u : 1u;
     g.S = maxL >= mp->seed_len ? (maxL - mp->seed_len) / mp->seed_interval + 1u : 0u;
     g.seed_len = mp->seed_len; g.interval = mp->seed_interval; g.max_hits = mp->max_hits; g.max_range = mp->max_range; g.band = mp->band;
-    g.R = mp->seed_mismatches ? (mp->max_seed_ranges ? mp->max_seed_ranges : 8u) : 1u;
+    // approximate seeds: Rf forward-index range slots per seed, and as many reverse-index slots when a reverse index is given
+    const nvb_fmindex* rfmi = mp->seed_mismatches ? mp->reverse_index : nullptr;
+    if (rfmi && (!rfmi->bwt_occ || !rfmi->ssa || rfmi->occ_int != 64 || rfmi->sa_int != 16 || rfmi->length != fmi->length || (((uintptr_t)rfmi->bwt_occ) & 31u))) return NVB_ERR_ARG;
+    const FMView rf = rfmi ? make_view(rfmi) : f;
+    g.Rf = mp->seed_mismatches ? (mp->max_seed_ranges ? mp->max_seed_ranges : 8u) : 1u;
+    g.R = rfmi ? 2u * g.Rf : g.Rf;
     g.len1 = mp->seed_len / 2u;                                       // mapping_inl.h:397
     g.priority = mp->hit_priority; g.deque_cap = mp->max_seed_hits; g.max_rows = mp->max_rows;
     const uint32_t per_read = g.S * g.n_strands * g.R;               // range slots per read
@@ -613,7 +644,7 @@ extern "C" int nvb_map_reads(nvb_ctx* ctx, const nvb_fmindex* fmi, const uint32_
             MAP_STAGE(S_SCAN, sizeof(uint32_t) * ((size_t)n_slots + 1), scan);
             NVB_CUDA(ctx, cudaMemsetAsync(counts + n_slots, 0, sizeof(uint32_t), s));
             if (g.R == 1u) map_seed_kernel<<<map_grid(n_slots), MAP_THREADS, 0, s>>>(f, reads, g, seeds, counts);
-            else           map_seed_approx_kernel<<<map_grid(n_slots / g.R), MAP_THREADS, 0, s>>>(f, reads, g, seeds, counts);
+            else           map_seed_approx_kernel<<<map_grid(n_slots / g.R), MAP_THREADS, 0, s>>>(f, rf, reads, g, seeds, counts);
             NVB_LAUNCHED(ctx);
             if (g.priority)
             {
@@ -640,11 +671,18 @@ extern "C" int nvb_map_reads(nvb_ctx* ctx, const nvb_fmindex* fmi, const uint32_
                 NVB_LAUNCHED(ctx);
                 {
                     const uint32_t want = map_grid(n_hits), persistent = (uint32_t)ctx->sm_count * 8u;
-                    if (f.sa_mask != 15u) map_walk_kernel<true><<<want < persistent ? want : persistent, MAP_THREADS, 0, s>>>(f, n_hits, rows, steps);
-                    else                  map_walk_kernel<false><<<want < persistent ? want : persistent, MAP_THREADS, 0, s>>>(f, n_hits, rows, steps);
+                    const uint32_t wg = want < persistent ? want : persistent;
+                    if (f.sa_mask != 15u) map_walk_kernel<true><<<wg, MAP_THREADS, 0, s>>>(f, n_hits, rows, steps, g.R, g.Rf, 0u);
+                    else                  map_walk_kernel<false><<<wg, MAP_THREADS, 0, s>>>(f, n_hits, rows, steps, g.R, g.Rf, 0u);
                     NVB_LAUNCHED(ctx);
+                    if (g.R > g.Rf)
+                    {
+                        if (rf.sa_mask != 15u) map_walk_kernel<true><<<wg, MAP_THREADS, 0, s>>>(rf, n_hits, rows, steps, g.R, g.Rf, 1u);
+                        else                   map_walk_kernel<false><<<wg, MAP_THREADS, 0, s>>>(rf, n_hits, rows, steps, g.R, g.Rf, 1u);
+                        NVB_LAUNCHED(ctx);
+                    }
                 }
-                map_keys_kernel<<<map_grid(n_hits), MAP_THREADS, 0, s>>>(f, g, rows, steps, n_hits, keys_b);
+                map_keys_kernel<<<map_grid(n_hits), MAP_THREADS, 0, s>>>(f, rf, g, rows, steps, n_hits, keys_b);
                 NVB_LAUNCHED(ctx);
                 trace.mark(MapTrace::LOCATE);
                 uint32_t cap = 64; while (cap < rows_per_read && cap < (1u << 30)) cap <<= 1;

@@ -25,21 +25,30 @@ class MapParams:
 
     def __init__(self, aligner=None, seed_len=20, seed_interval=10, max_hits=4, max_range=0, band=15,
                  both_strands=True, min_score=-(1 << 29), seed_mismatches=0, max_seed_ranges=0, hit_priority=False,
-                 max_seed_hits=0, max_rows=0):
+                 max_seed_hits=0, max_rows=0, reverse_index=None):
         """seed_mismatches = 1: nvBowtie's approximate seeds on the forward index (mapping_inl.h:114-184, :395-397), the first
         max_seed_ranges ranges per seed (0 = 8). hit_priority: ranges visited by size, smallest first, through a deque of
-        max_seed_hits entries (0 = unbounded), max_rows rows per read (0 = no budget) (seed_hit.h:220-230, select_inl.h:93-113)"""
+        max_seed_hits entries (0 = unbounded), max_rows rows per read (0 = no budget) (seed_hit.h:220-230, select_inl.h:93-113).
+        reverse_index: the FMIndex of the reversed genome; with seed_mismatches = 1 it adds the other half of nvBowtie's approximate
+        seeds (substitution in the last half of the seed, mapping_inl.h:399-402)"""
         self.aligner = aligner if aligner is not None else GotohAligner(SEMI_GLOBAL, 0, -5, -8, -3)
         assert isinstance(self.aligner, Aligner)
         self.seed_len, self.seed_interval, self.max_hits, self.max_range = seed_len, seed_interval, max_hits, max_range
         self.band, self.both_strands, self.min_score = band, both_strands, min_score
         self.seed_mismatches, self.max_seed_ranges = int(seed_mismatches), int(max_seed_ranges)
         self.hit_priority, self.max_seed_hits, self.max_rows = bool(hit_priority), int(max_seed_hits), int(max_rows)
+        self.reverse_index = reverse_index
 
     def c(self):
         return MapParamsC(self.seed_len, self.seed_interval, self.max_hits, self.max_range, self.band,
                           1 if self.both_strands else 0, self.min_score, self.aligner.c(), self.seed_mismatches, self.max_seed_ranges,
-                          1 if self.hit_priority else 0, self.max_seed_hits, self.max_rows)
+                          1 if self.hit_priority else 0, self.max_seed_hits, self.max_rows, self._reverse_ptr())
+
+    def _reverse_ptr(self):
+        if self.reverse_index is None:
+            return None
+        self._rc = self.reverse_index.c()           # the descriptor must outlive the call
+        return C.addressof(self._rc)
 
 
 def ops_stride_for(max_read_len, band):

@@ -133,6 +133,7 @@ typedef struct { uint32_t seed_len, seed_interval, max_hits, max_range, band, bo
                  orc_aligner aligner;
                  uint32_t seed_mismatches, max_seed_ranges;           /* nvBowtie's approximate seeds, forward index (mapping_inl.h:114-184) */
                  uint32_t hit_priority, max_seed_hits, max_rows;      /* hit selection by SA-range size (seed_hit.h:220-230, select_inl.h:93-113) */
+                 const orc_fmindex* reverse_index;                    /* index of the reversed text: the other half of the approximate seeds (mapping_inl.h:399-402) */
                } orc_map_params;
 typedef struct { int32_t score, second_score; uint32_t begin, end, flags, n_ops; } orc_read_hit;
 int ORC(map_reads)(const orc_fmindex* fmi, const uint8_t* genome, const uint8_t* reads, const uint32_t* read_off,

@@ -93,7 +93,7 @@ int ORC(map_reads)(const orc_fmindex* fmi, const uint8_t* genome, const uint8_t*
         uint8_t*  strand_read = NULL; size_t cap_read = 0;
         uint64_t* keys = NULL;        size_t cap_keys = 0;
         uint8_t*  tb_ops = NULL;      size_t cap_ops = 0;
-        uint32_t *sl_x = NULL, *sl_size = NULL, *sl_take = NULL, *sl_o = NULL, *ap = NULL; uint32_t* order = NULL; size_t cap_slots = 0, cap_order = 0;
+        uint32_t *sl_x = NULL, *sl_size = NULL, *sl_take = NULL, *sl_o = NULL, *ap = NULL; uint32_t* order = NULL; uint8_t* rseed = NULL; size_t cap_slots = 0, cap_order = 0;
 #ifdef _OPENMP
         #pragma omp for schedule(dynamic, 64)
 #endif
@@ -112,13 +112,16 @@ int ORC(map_reads)(const orc_fmindex* fmi, const uint8_t* genome, const uint8_t*
             const uint32_t n_seeds = L >= p->seed_len ? (L - p->seed_len) / p->seed_interval + 1 : 0;
             /* ---- the SA ranges of the read, in slot order (strand, seed, range): exact seeds give one, approximate seeds
              * (mapping_inl.h:114-184 through fm_match_approx, first R ranges in its push order) up to R */
-            const uint32_t R = p->seed_mismatches ? (p->max_seed_ranges ? p->max_seed_ranges : 8u) : 1u;
+            const uint32_t Rf = p->seed_mismatches ? (p->max_seed_ranges ? p->max_seed_ranges : 8u) : 1u;
+            const orc_fmindex* rfmi = p->seed_mismatches ? p->reverse_index : NULL;
+            const uint32_t R = rfmi ? 2 * Rf : Rf;              /* slots [0, Rf): forward-index ranges, [Rf, R): reverse-index ranges */
             const size_t n_slots = (size_t)n_strands * n_seeds * R;
             if (n_slots > cap_slots)
             {
                 cap_slots = n_slots;
                 sl_x = (uint32_t*)realloc(sl_x, 4 * cap_slots); sl_size = (uint32_t*)realloc(sl_size, 4 * cap_slots);
                 sl_take = (uint32_t*)realloc(sl_take, 4 * cap_slots); sl_o = (uint32_t*)realloc(sl_o, 4 * cap_slots);
+                rseed = (uint8_t*)realloc(rseed, p->seed_len + 1);
                 ap = (uint32_t*)realloc(ap, 8 * (size_t)R + 8);
             }
             size_t ns = 0;
@@ -135,16 +138,33 @@ int ORC(map_reads)(const orc_fmindex* fmi, const uint8_t* genome, const uint8_t*
                     }
                     else
                     {
-                        if (ORC(fm_match_approx)(fmi, strand_read + s * L + o, off, 1, p->seed_len / 2u, 1, R, ap, &n_rng, 1)) { failed = 1; continue; }
-                        if (n_rng > R) n_rng = R;
+                        if (ORC(fm_match_approx)(fmi, strand_read + s * L + o, off, 1, p->seed_len / 2u, 1, Rf, ap, &n_rng, 1)) { failed = 1; continue; }
+                        if (n_rng > Rf) n_rng = Rf;
                     }
-                    for (uint32_t j = 0; j < R; ++j, ++ns)
+                    for (uint32_t j = 0; j < Rf; ++j, ++ns)
                     {
                         sl_o[ns] = o; sl_x[ns] = 0; sl_size[ns] = 0;
                         if (j >= n_rng) continue;
                         const uint32_t size = ap[2 * j + 1] - ap[2 * j] + 1;
                         if (p->max_range && size > p->max_range) continue;
                         sl_x[ns] = ap[2 * j]; sl_size[ns] = size;
+                    }
+                    if (rfmi)
+                    {
+                        /* the other half (mapping_inl.h:399-402, map<IGNORE_EXACT> on rfmi): the REVERSED seed on the index of the
+                         * reversed text is consumed from the seed's start; exact over (seed_len + 1) / 2 steps, no exact match */
+                        for (uint32_t e = 0; e < p->seed_len; ++e) rseed[e] = strand_read[s * L + o + p->seed_len - 1 - e];
+                        uint32_t m_rng = 0;
+                        if (ORC(fm_match_approx)(rfmi, rseed, off, 1, (p->seed_len + 1u) / 2u, 0, Rf, ap, &m_rng, 1)) { failed = 1; m_rng = 0; }
+                        if (m_rng > Rf) m_rng = Rf;
+                        for (uint32_t j = 0; j < Rf; ++j, ++ns)
+                        {
+                            sl_o[ns] = o; sl_x[ns] = 0; sl_size[ns] = 0;
+                            if (j >= m_rng) continue;
+                            const uint32_t size = ap[2 * j + 1] - ap[2 * j] + 1;
+                            if (p->max_range && size > p->max_range) continue;
+                            sl_x[ns] = ap[2 * j]; sl_size[ns] = size;
+                        }
                     }
                 }
             /* ---- rows each range contributes */
@@ -161,11 +181,13 @@ int ORC(map_reads)(const orc_fmindex* fmi, const uint8_t* genome, const uint8_t*
             for (size_t t = 0; t < ns; ++t)
             {
                 const uint32_t s = (uint32_t)(t / ((size_t)n_seeds * R)), o = sl_o[t];
+                const int rev = (t % R) >= Rf;
                 for (uint32_t q = 0; q < sl_take[t]; ++q)
                 {
                     const uint32_t row = sl_x[t] + q;
                     uint32_t pos;
-                    if (ORC(fm_locate)(fmi, &row, 1, &pos, NULL, 1)) { failed = 1; continue; }
+                    if (ORC(fm_locate)(rev ? rfmi : fmi, &row, 1, &pos, NULL, 1)) { failed = 1; continue; }
+                    if (rev) pos = G - pos - p->seed_len;           /* the reversed seed at q in the reversed text = the seed at G - q - seed_len */
                     const uint32_t g_pos = pos > o ? pos - o : 0;
                     const uint32_t gb = g_pos > p->band / 2 ? g_pos - p->band / 2 : 0;
                     keys[nk++] = ((uint64_t)s << 32) | gb;
@@ -206,7 +228,7 @@ int ORC(map_reads)(const orc_fmindex* fmi, const uint8_t* genome, const uint8_t*
                 if (ops && ops_stride) memcpy(ops + (size_t)r * ops_stride, tb_ops, n_ops < ops_stride ? n_ops : ops_stride);
             }
         }
-        free(strand_read); free(keys); free(tb_ops); free(sl_x); free(sl_size); free(sl_take); free(sl_o); free(order); free(ap);
+        free(strand_read); free(keys); free(tb_ops); free(sl_x); free(sl_size); free(sl_take); free(sl_o); free(order); free(ap); free(rseed);
     }
     return failed ? -2 : 0;
 }

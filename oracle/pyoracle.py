@@ -60,7 +60,7 @@ class MapParamsC(C.Structure):
     _fields_ = [("seed_len", C.c_uint32), ("seed_interval", C.c_uint32), ("max_hits", C.c_uint32), ("max_range", C.c_uint32),
                 ("band", C.c_uint32), ("both_strands", C.c_uint32), ("min_score", C.c_int32), ("aligner", AlignerC),
                 ("seed_mismatches", C.c_uint32), ("max_seed_ranges", C.c_uint32), ("hit_priority", C.c_uint32),
-                ("max_seed_hits", C.c_uint32), ("max_rows", C.c_uint32)]
+                ("max_seed_hits", C.c_uint32), ("max_rows", C.c_uint32), ("reverse_index", C.c_void_p)]
 
 
 HIT_DT = np.dtype([("score", "<i4"), ("second_score", "<i4"), ("begin", "<u4"), ("end", "<u4"), ("flags", "<u4"), ("n_ops", "<u4")])

@@ -37,6 +37,12 @@ def make_reads(rng, genome, n, len_range=(60, 151), sub=0.02, indel=0.3, alpha=4
 
 
 def map_params(band=15, kind=po.GOTOH, scores=(0, -5, -8, -3), seed_len=20, interval=10, max_hits=4, max_range=0,
-               both=1, min_score=-60, seed_mismatches=0, max_seed_ranges=0, hit_priority=0, max_seed_hits=0, max_rows=0):
-    return po.MapParamsC(seed_len, interval, max_hits, max_range, band, both, min_score, po.aligner(kind, po.SEMI_GLOBAL, scores),
-                         seed_mismatches, max_seed_ranges, hit_priority, max_seed_hits, max_rows)
+               both=1, min_score=-60, seed_mismatches=0, max_seed_ranges=0, hit_priority=0, max_seed_hits=0, max_rows=0,
+               reverse_index=None):
+    """reverse_index: a pyoracle.Index of the reversed genome (its descriptor is kept alive on the returned struct)"""
+    import ctypes as C
+    rc = reverse_index.c() if reverse_index is not None else None
+    P = po.MapParamsC(seed_len, interval, max_hits, max_range, band, both, min_score, po.aligner(kind, po.SEMI_GLOBAL, scores),
+                      seed_mismatches, max_seed_ranges, hit_priority, max_seed_hits, max_rows, C.addressof(rc) if rc is not None else None)
+    P._rc = rc
+    return P

@@ -145,6 +145,35 @@ def test_map_reads_modes(oracle, mode):
     assert ((want_hits["flags"] & 2) != 0).sum() > 1500
 
 
+@pytest.mark.parametrize("mode", [dict(max_seed_ranges=4), dict(max_seed_ranges=0), dict(max_seed_ranges=3, hit_priority=1, max_seed_hits=9, max_rows=11)])
+@pytest.mark.parametrize("dense", [0, 2])
+def test_map_reads_reverse_index(oracle, mode, dense):
+    """both halves of nvBowtie's approximate seeds: forward index (substitution in the first half of a seed) and the index of the
+    reversed text (substitution in the last half, mapping_inl.h:399-402), rows of the latter located on it and mapped back"""
+    rng = np.random.default_rng(91 + len(mode) + dense)
+    G = 50000
+    genome = rng.integers(0, 4, G).astype(np.uint8)
+    genome[7000:7600] = genome[21000:21600]
+    fmi, oidx = gu.fm_index_pair(oracle, genome)
+    rfmi, ridx = gu.fm_index_pair(oracle, genome[::-1].copy())
+    if dense:
+        fmi.build_dssa(dense); rfmi.build_dssa(dense)
+    words = nvb.pack_genome(torch.from_numpy(genome).to(gu.dev()))
+    sym, off = map_util.make_reads(rng, genome, 2500, sub=0.05)
+    pc = map_util.map_params(15, po.GOTOH, (0, -5, -8, -3), 20, 10, 4, 0, 1, -60, seed_mismatches=1, reverse_index=ridx, **mode)
+    want_hits, want_ops, want_nc = oracle.map_reads(oidx, genome, sym, off, pc)
+    fwd_hits, _, fwd_nc = oracle.map_reads(oidx, genome, sym, off, map_util.map_params(15, po.GOTOH, (0, -5, -8, -3), 20, 10, 4, 0, 1, -60, seed_mismatches=1, **mode))
+    assert want_nc.sum() > fwd_nc.sum()                                          # the reverse half contributes candidates
+    params = nvb.MapParams(nvb.GotohAligner(nvb.SEMI_GLOBAL, 0, -5, -8, -3), 20, 10, 4, 0, 15, True, -60, seed_mismatches=1, reverse_index=rfmi, **mode)
+    rs = gu.sset(sym, off)
+    for rpb in (0, 800):
+        hits, ops, stats = nvb.map_reads(fmi, words, rs.symbols, rs.offsets, params, reads_per_batch=rpb)
+        assert same(hits_np(hits), ops.cpu().numpy(), want_hits, want_ops)
+        assert stats["candidates"] == int(want_nc.sum())
+    h_hits, h_ops, _ = nvb.map_reads_host(fmi, words, sym, off, params, ops_h=np.zeros((len(off) - 1, nvb.ops_stride_for(150, 15)), np.uint8), reads_per_batch=700)
+    assert same(h_hits, h_ops, want_hits, want_ops)
+
+
 def test_map_reads_edges(oracle):
     rng = np.random.default_rng(3)
     genome = rng.integers(0, 4, 5000).astype(np.uint8)

@@ -176,3 +176,36 @@ def test_mapq_v2_is_the_references_calculator(oracle, ref):
     for best in range(-61, 1):
         for second in range(-61, best + 1):
             assert oracle.mapq_v2(best, True, second, 0, -60, True) == ref.ref_bowtie_mapq2(best, True, second, 0, -60, True)
+
+
+def test_oracle_map_reverse_index_half(oracle, ref):
+    """approximate seeds with the reverse index: reads whose every seed carries a substitution in its LAST half map only when the
+    index of the reversed text takes part (the forward half covers substitutions in the first half of a seed)"""
+    rng = np.random.default_rng(31)
+    G = 30000
+    genome = rng.integers(0, 4, G).astype(np.uint8)
+    idx = oracle.build_index(genome)
+    ridx = oracle.build_index(genome[::-1].copy())
+    reads = []
+    for i in range(80):
+        p = int(rng.integers(100, G - 200)); r = genome[p:p + 40].copy()
+        for k in (16, 26, 36):                                # seeds start at 0, 10, 20: positions 16 / 26 / 36 sit in their last halves
+            r[k] = (r[k] + 1 + i % 3) % 4
+        reads.append(r)
+    sym, off = po.concat(reads)
+    fwd_only = map_util.map_params(min_score=-40, both=0, seed_mismatches=1, max_seed_ranges=8)
+    both = map_util.map_params(min_score=-40, both=0, seed_mismatches=1, max_seed_ranges=8, reverse_index=ridx)
+    hf, _, _ = oracle.map_reads(idx, genome, sym, off, fwd_only)
+    hb, ob, cb = oracle.map_reads(idx, genome, sym, off, both)
+    assert ((hf["flags"] & 2) != 0).sum() == 0
+    assert ((hb["flags"] & 2) != 0).sum() >= 78
+    hr, orr, cr = ref.map_reads(idx, genome, sym, off, both)
+    assert (hb == hr).all() and (ob == orr).all() and (cb == cr).all()
+    # general reads: the union of both halves finds at least what the forward half finds
+    sym2, off2 = map_util.make_reads(rng, genome, 300, sub=0.05)
+    p1 = map_util.map_params(min_score=-60, seed_mismatches=1, max_seed_ranges=4)
+    p2 = map_util.map_params(min_score=-60, seed_mismatches=1, max_seed_ranges=4, reverse_index=ridx)
+    h1, _, c1 = oracle.map_reads(idx, genome, sym2, off2, p1)
+    h2, _, c2 = oracle.map_reads(idx, genome, sym2, off2, p2)
+    assert (c2 >= c1).all() and ((h2["flags"] & 2) != 0).sum() >= ((h1["flags"] & 2) != 0).sum()
+    assert (h2["score"][(h1["flags"] & 2) != 0] >= h1["score"][(h1["flags"] & 2) != 0]).all()
