@@ -262,6 +262,14 @@ int nvb_batch_score(nvb_ctx* ctx, nvb_aligner aligner, nvb_string_set patterns, 
                     nvb_best_sink* sinks, uint32_t max_pattern_len, uint32_t max_text_len,
                     void* temp, size_t temp_bytes, void* stream);
 
+/* the same for the aligner's TextBlockingTag variant (nvbio/alignment/alignment.h:266-279, aln::transpose :395-540; kernels
+ * sw/sw_inl.h:872+, gotoh/gotoh_inl.h:848+; scoring only, as in the reference): same scores, LOCAL ties resolved in the
+ * text-blocking visiting order (stripes of 8 text columns, pattern row by pattern row). temp: size it with
+ * nvb_temp_bytes(NVB_OP_SCORE, aligner, 0, 0, max_text_len, max_pattern_len, n) for GLOBAL and LOCAL (the batch runs transposed). */
+int nvb_batch_score_text_blocking(nvb_ctx* ctx, nvb_aligner aligner, nvb_string_set patterns, nvb_string_set texts,
+                                  nvb_best_sink* sinks, uint32_t max_pattern_len, uint32_t max_text_len,
+                                  void* temp, size_t temp_bytes, void* stream);
+
 /* nvb_batch_score without any allocation. NO COUNTERPART IN THE REFERENCE: added for
  * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
  * Same inputs, outputs and results as nvb_batch_score; the scratch (one int16 score column of max_text_len cells per pair,

@@ -129,10 +129,18 @@ void batch_alignment_score(const aligner_type aligner, const pattern_set_type pa
                            BestSink<int32>* sinks, const DeviceB200Scheduler sch, const uint32 max_pattern_length, const uint32 max_text_length)
 {
     const nvb_aligner a = b200_aligner( aligner );
-    const size_t bytes = nvb_temp_bytes( NVB_OP_SCORE, a, 0, 0, max_pattern_length, max_text_length, patterns.size() );
+    // aligners carrying TextBlockingTag (aln::transpose( aligner ), alignment.h:266-279, :395-540) keep their own tie order
+    const bool text_blocking = equal<typename aligner_type::algorithm_tag, TextBlockingTag>();
+    const uint32 longest = max_pattern_length > max_text_length ? max_pattern_length : max_text_length;
+    const size_t bytes = text_blocking ? nvb_temp_bytes( NVB_OP_SCORE, a, 0, 0, longest, longest, patterns.size() )
+                                       : nvb_temp_bytes( NVB_OP_SCORE, a, 0, 0, max_pattern_length, max_text_length, patterns.size() );
     nvb_best_sink* packed = (nvb_best_sink*)sch.c->staging( sizeof(nvb_best_sink) * patterns.size() );
-    sch.c->check( nvb_batch_score( sch.c->ctx, a, b200_set( patterns ), b200_set( texts ), packed,
-                                   max_pattern_length, max_text_length, sch.c->scratch( bytes ), bytes, sch.stream ) );
+    if (text_blocking)
+        sch.c->check( nvb_batch_score_text_blocking( sch.c->ctx, a, b200_set( patterns ), b200_set( texts ), packed,
+                                                     max_pattern_length, max_text_length, sch.c->scratch( bytes ), bytes, sch.stream ) );
+    else
+        sch.c->check( nvb_batch_score( sch.c->ctx, a, b200_set( patterns ), b200_set( texts ), packed,
+                                       max_pattern_length, max_text_length, sch.c->scratch( bytes ), bytes, sch.stream ) );
     b200_store_sinks( sch, packed, patterns.size(), sinks );
 }
 /// aln::batch_banded_alignment_score<BAND_LEN> (batched.h:142-192)

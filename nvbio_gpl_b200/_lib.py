@@ -100,6 +100,7 @@ _PROTOS = {
     "nvb_fm_locate_host": (_i, [_vp, C.POINTER(FMIndexC), _vp, _u32, _vp]),
     "nvb_temp_bytes": (_sz, [_i, AlignerC, _u32, _u32, _u32, _u32, _u32]),
     "nvb_batch_score": (_i, [_vp, AlignerC, StringSetC, StringSetC, _vp, _u32, _u32, _vp, _sz, _vp]),
+    "nvb_batch_score_text_blocking": (_i, [_vp, AlignerC, StringSetC, StringSetC, _vp, _u32, _u32, _vp, _sz, _vp]),
     "nvb_batch_score_noalloc_bytes": (_sz, [AlignerC, _u32, _u32]),
     "nvb_batch_score_noalloc": (_i, [_vp, AlignerC, StringSetC, StringSetC, _vp, _u32, _u32, _vp]),
     "nvb_batch_score_q": (_i, [_vp, AlignerC, C.POINTER(QualitySchemeC), StringSetC, _vp, StringSetC, _vp, _u32, _u32, _vp, _sz, _vp]),

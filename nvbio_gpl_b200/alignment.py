@@ -112,16 +112,25 @@ def _temp(op, aligner, band, chk, maxM, maxN, n, device, temp):
     return temp
 
 
-def batch_alignment_score(aligner, patterns, texts, sinks=None, temp=None, ctx=None, scheme=None, quals=None):
+def batch_alignment_score(aligner, patterns, texts, sinks=None, temp=None, ctx=None, scheme=None, quals=None, text_blocking=False):
     """aln::batch_alignment_score(aligner, patterns, [quals,] texts, sinks, scheduler, maxM, maxN) (batched.h:98-192).
     sinks: int32 [n,3] = (score, sink.x = text end, sink.y = pattern end). scheme / quals: a QualityScheme and the pattern
-    qualities (the reference's quals overload, batched.h:126-148)"""
+    qualities (the reference's quals overload, batched.h:126-148). text_blocking: the aligner's TextBlockingTag variant
+    (``nvb_batch_score_text_blocking``; alignment.h:266-279: same scores, LOCAL ties in the text-blocking visiting order)"""
     ctx = _ctx(patterns.offsets, ctx)
     n = patterns.count
     dev = patterns.offsets.device
     if sinks is None:
         sinks = torch.empty((n, 3), dtype=torch.int32, device=dev)
     maxM, maxN = patterns.max_len, texts.max_len
+    if text_blocking:
+        if scheme is not None:
+            raise _lib.NvbError("text_blocking is available for the simple schemes only")
+        transposed = aligner.type != SEMI_GLOBAL
+        temp = _temp(_lib.OP_SCORE, aligner, 0, 0, maxN if transposed else maxM, maxM if transposed else maxN, n, dev, temp)
+        check(lib().nvb_batch_score_text_blocking(ctx.h, aligner.c(), patterns.c(), texts.c(), sinks.data_ptr(), maxM, maxN,
+                                                  temp.data_ptr(), temp.numel(), _lib.current_stream_ptr()), ctx.h)
+        return sinks
     temp = _temp(_lib.OP_SCORE, aligner, 0, 0, maxM, maxN, n, dev, temp)
     if scheme is not None:
         qs = scheme.c()

@@ -226,6 +226,47 @@ extern "C" int nvb_batch_score(nvb_ctx* ctx, nvb_aligner a, nvb_string_set patte
                                nvb_best_sink* sinks, uint32_t maxM, uint32_t maxN, void* temp, size_t temp_bytes, void* stream)
 { return batch_score_impl(ctx, a, nullptr, nullptr, patterns, texts, sinks, maxM, maxN, temp, temp_bytes, stream); }
 
+// TextBlockingTag scoring (alignment.h:266-279; sw/sw_inl.h:872+, gotoh/gotoh_inl.h:848+; scoring only in the reference too): stripes of
+// 8 text columns, pattern row by pattern row. Scores equal those of the default blocking; what changes is the order in which a LOCAL
+// sink meets equal scores -- and that is the default order of the TRANSPOSED problem (aln::transpose, alignment.h:395-540: pattern
+// and text exchanged, deletion and insertion exchanged). So LOCAL and GLOBAL run the transposed batch through the same kernels and swap
+// the sink coordinates back; SEMI_GLOBAL (not symmetric) walks the last row in text order under both blockings.
+__global__ void dp_swap_sinks_kernel(nvb_best_sink* sinks, uint32_t n)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t x = sinks[i].sink_x; sinks[i].sink_x = sinks[i].sink_y; sinks[i].sink_y = x;
+}
+// SEMI_GLOBAL, empty pattern, non-empty text: the text-blocking sweep ends on the boundary cell of the last row, (N, 0) with score 0
+__global__ void dp_tb_semi_empty_kernel(nvb_best_sink* sinks, const uint32_t* poff, const uint32_t* toff, uint32_t n)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t N = toff[i + 1] - toff[i];
+    if (poff[i + 1] == poff[i] && N > 0) { nvb_best_sink s; s.score = 0; s.sink_x = N; s.sink_y = 0; sinks[i] = s; }
+}
+extern "C" int nvb_batch_score_text_blocking(nvb_ctx* ctx, nvb_aligner a, nvb_string_set patterns, nvb_string_set texts,
+                                             nvb_best_sink* sinks, uint32_t maxM, uint32_t maxN, void* temp, size_t temp_bytes, void* stream)
+{
+    const uint32_t n = patterns.count;
+    if (a.type == NVB_SEMI_GLOBAL)
+    {
+        const int rc = batch_score_impl(ctx, a, nullptr, nullptr, patterns, texts, sinks, maxM, maxN, temp, temp_bytes, stream);
+        if (rc || n == 0) return rc;
+        dp_tb_semi_empty_kernel<<<(n + 255u) / 256u, 256, 0, (cudaStream_t)stream>>>(sinks, patterns.offsets, texts.offsets, n);
+        NVB_LAUNCHED(ctx);
+        return NVB_OK;
+    }
+    // GLOBAL and LOCAL are symmetric: the transposed batch (degenerate shapes included: an empty TEXT reports nothing here)
+    nvb_aligner t = a;
+    if (a.kind == NVB_SMITH_WATERMAN) { t.gap_a = a.gap_b; t.gap_b = a.gap_a; }
+    const int rc = batch_score_impl(ctx, t, nullptr, nullptr, texts, patterns, sinks, maxN, maxM, temp, temp_bytes, stream);
+    if (rc || n == 0) return rc;
+    dp_swap_sinks_kernel<<<(n + 255u) / 256u, 256, 0, (cudaStream_t)stream>>>(sinks, n);
+    NVB_LAUNCHED(ctx);
+    return NVB_OK;
+}
+
 extern "C" int nvb_batch_score_q(nvb_ctx* ctx, nvb_aligner a, const nvb_quality_scheme* qs, nvb_string_set patterns, const uint8_t* quals,
                                  nvb_string_set texts, nvb_best_sink* sinks, uint32_t maxM, uint32_t maxN, void* temp, size_t temp_bytes, void* stream)
 { if (!qs) return NVB_ERR_ARG; return batch_score_impl(ctx, a, qs, quals, patterns, texts, sinks, maxM, maxN, temp, temp_bytes, stream); }

@@ -82,6 +82,10 @@ int ORC(fm_locate)(const orc_fmindex* fmi, const uint32_t* rows, uint32_t count,
 int ORC(score)(orc_aligner a, const uint8_t* pat, const uint32_t* pat_off, const uint8_t* txt,
                const uint32_t* txt_off, uint32_t count, orc_sink* sinks, int threads);
 
+/* the same with the aligner's TextBlockingTag variant (alignment.h:266-279); see oracle_aln.c */
+int ORC(score_text_blocking)(orc_aligner a, const uint8_t* pat, const uint32_t* pat_off, const uint8_t* txt,
+                             const uint32_t* txt_off, uint32_t count, orc_sink* sinks, int threads);
+
 /* banded scoring */
 int ORC(banded_score)(orc_aligner a, uint32_t band, const uint8_t* pat, const uint32_t* pat_off,
                       const uint8_t* txt, const uint32_t* txt_off, uint32_t count, orc_sink* sinks,

@@ -341,6 +341,32 @@ int orc_score(orc_aligner a, const uint8_t* pat, const uint32_t* pat_off, const 
               const uint32_t* txt_off, uint32_t count, orc_sink* sinks, int threads)
 { return orc_score_q(a, NULL, NULL, pat, pat_off, txt, txt_off, count, sinks, threads); }
 
+/* TextBlockingTag scoring (alignment.h:266-279; sw/sw_inl.h:872+, gotoh/gotoh_inl.h:848+): the matrix is swept in stripes of 8
+ * TEXT columns, pattern row by pattern row. Scores are those of the default blocking; only the order in which a LOCAL sink sees
+ * equal scores changes. That order is the pattern-blocking order of the TRANSPOSED problem (pattern and text exchanged, deletion
+ * and insertion exchanged: aln::transpose, alignment.h:395-540), so LOCAL and GLOBAL = transposed call with the sink coordinates
+ * swapped back (this also reproduces the degenerate shapes: an empty TEXT reports nothing, an empty pattern the boundary cell);
+ * SEMI_GLOBAL walks the last row in text order under both blockings. Pinned on the reference's
+ * TextBlockingTag aligners (oracle/ref_wrap_aln.inl::ref_score_text_blocking). */
+int orc_score_text_blocking(orc_aligner a, const uint8_t* pat, const uint32_t* pat_off, const uint8_t* txt,
+                            const uint32_t* txt_off, uint32_t count, orc_sink* sinks, int threads)
+{
+    if (a.type == 2)
+    {
+        /* SEMI_GLOBAL is not symmetric: same sweep results as the default blocking; an EMPTY pattern, which the pattern-blocking
+         * sweep reports nothing for, here ends on the last row's boundary: score 0 at (N, 0) */
+        const int rc = orc_score(a, pat, pat_off, txt, txt_off, count, sinks, threads);
+        for (uint32_t i = 0; i < count; ++i)
+            if (pat_off[i + 1] == pat_off[i] && txt_off[i + 1] > txt_off[i]) { sinks[i].score = 0; sinks[i].x = txt_off[i + 1] - txt_off[i]; sinks[i].y = 0; }
+        return rc;
+    }
+    orc_aligner t = a;
+    if (a.kind == 1) { t.p2 = a.p3; t.p3 = a.p2; }
+    const int rc = orc_score(t, txt, txt_off, pat, pat_off, count, sinks, threads);
+    for (uint32_t i = 0; i < count; ++i) { const uint32_t x = sinks[i].x; sinks[i].x = sinks[i].y; sinks[i].y = x; }
+    return rc;
+}
+
 int orc_traceback_q(orc_aligner a, const orc_qscheme* qs, const uint8_t* quals, uint32_t checkpoints, const uint8_t* pat, const uint32_t* pat_off,
                     const uint8_t* txt, const uint32_t* txt_off, uint32_t count, orc_alignment* out,
                     uint8_t* ops, uint32_t ops_stride, uint32_t* n_ops, int threads)

@@ -233,6 +233,15 @@ class Oracle:
         assert rc == 0, rc
         return sinks
 
+    def score_text_blocking(self, a, pat, pat_off, txt, txt_off, threads=0):
+        """scoring with the aligner's TextBlockingTag variant (alignment.h:266-279)"""
+        pat, pat_off, txt, txt_off = self._sets(pat, pat_off, txt, txt_off)
+        n = len(pat_off) - 1
+        sinks = np.zeros(n, dtype=SINK_DT)
+        rc = self._f("score_text_blocking")(a, _ptr(pat), _ptr(pat_off), _ptr(txt), _ptr(txt_off), C.c_uint32(n), _ptr(sinks), C.c_int(threads))
+        assert rc == 0, rc
+        return sinks
+
     def banded_score(self, a, band, pat, pat_off, txt, txt_off, threads=0, qs=None, quals=None):
         pat, pat_off, txt, txt_off = self._sets(pat, pat_off, txt, txt_off)
         n = len(pat_off) - 1

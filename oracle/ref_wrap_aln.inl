@@ -60,7 +60,7 @@ void score_batch(const aligner_type aligner, const quals_type quals, const uint8
         {
             const uint32 M = pat_off[i+1] - pat_off[i];
             const uint32 N = txt_off[i+1] - txt_off[i];
-            if (column.size() < N + 1u) column.resize( N + 1u );
+            if (column.size() < (M > N ? M : N) + 1u) column.resize( (M > N ? M : N) + 1u );   // TextBlockingTag keeps a column over the pattern
             aln::BestSink<int32> sink;
             aln::alignment_score( aligner, sym_string( M, pat + pat_off[i] ), quals.get( i, M ),
                                   sym_string( N, txt + txt_off[i] ), MIN_SCORE, sink, &column[0] );
@@ -210,6 +210,11 @@ struct ScoreF { Args g;
     { if (g.quals) { const ByteQuals q = { g.quals, g.pat_off }; score_batch( a, q, g.pat, g.pat_off, g.txt, g.txt_off, g.count, g.sinks, g.threads ); }
       else score_batch( a, NoQuals(), g.pat, g.pat_off, g.txt, g.txt_off, g.count, g.sinks, g.threads ); } };
 
+// the same through the aligner's TextBlockingTag variant (aln::transpose, alignment.h:395-540; sw_inl.h:872+, gotoh_inl.h:848+)
+struct ScoreTextBlockingF { Args g;
+    template <typename A> void operator()(const A a) const
+    { score_batch( aln::transpose( a ), NoQuals(), g.pat, g.pat_off, g.txt, g.txt_off, g.count, g.sinks, g.threads ); } };
+
 template <uint32 BAND> struct BandedScoreF { Args g;
     template <typename A> void operator()(const A a) const
     { if (g.quals) { const ByteQuals q = { g.quals, g.pat_off }; banded_score_batch<BAND>( a, q, g.pat, g.pat_off, g.txt, g.txt_off, g.count, g.sinks, g.threads ); }
@@ -250,6 +255,15 @@ int ref_score_q(orc_aligner a, const orc_qscheme* qs, const uint8_t* quals, cons
 int ref_score(orc_aligner a, const uint8_t* pat, const uint32_t* pat_off, const uint8_t* txt,
               const uint32_t* txt_off, uint32_t count, orc_sink* sinks, int threads)
 { return ref_score_q( a, 0, 0, pat, pat_off, txt, txt_off, count, sinks, threads ); }
+
+int ref_score_text_blocking(orc_aligner a, const uint8_t* pat, const uint32_t* pat_off, const uint8_t* txt,
+                            const uint32_t* txt_off, uint32_t count, orc_sink* sinks, int threads)
+{
+    if (threads <= 0) threads = omp_get_max_threads();
+    Args g = { pat, pat_off, txt, txt_off, count, sinks, 0, 0, 0, 0, threads, 0 };
+    ScoreTextBlockingF f = { g };
+    return dispatch_aligner( a, f, 0 );
+}
 
 int ref_banded_score_q(orc_aligner a, const orc_qscheme* qs, const uint8_t* quals, uint32_t band, const uint8_t* pat, const uint32_t* pat_off,
                        const uint8_t* txt, const uint32_t* txt_off, uint32_t count, orc_sink* sinks, int threads)
@@ -335,7 +349,7 @@ struct Score2F { Args2 g;
             {
                 const uint32 M = g.pat_off[i+1] - g.pat_off[i];
                 const uint32 N = g.txt_off[i+1] - g.txt_off[i];
-                if (column.size() < N + 1u) column.resize( N + 1u );
+                if (column.size() < (M > N ? M : N) + 1u) column.resize( (M > N ? M : N) + 1u );   // TextBlockingTag keeps a column over the pattern
                 aln::Best2Sink<int32> sink( g.distinct );
                 aln::alignment_score( aligner, sym_string( M, g.pat + g.pat_off[i] ), aln::trivial_quality_string(),
                                       sym_string( N, g.txt + g.txt_off[i] ), MIN_SCORE, sink, &column[0] );

@@ -71,6 +71,14 @@ static int check_scoring(B200Context& c, const char* name, const aligner_type al
     for (uint32 i = 0; i < n; ++i) bad += (got[i].score != want[i].score || got[i].sink.x != want[i].x || got[i].sink.y != want[i].y);
     char label[128]; snprintf( label, sizeof(label), "batch_alignment_score             %s", name ); report( label, bad, n );
 
+    // the same aligner with TextBlockingTag (aln::transpose, alignment.h:395-540): its own tie order, same call shape
+    aln::batch_alignment_score( aln::transpose( aligner ), patterns, texts, d_sinks, aln::DeviceB200Scheduler( c ), 150u, 200u );
+    CK( cudaMemcpy( got.data(), d_sinks, n * sizeof(aln::BestSink<int32>), cudaMemcpyDeviceToHost ) );
+    ref_score_text_blocking( oa, P.data(), Po.data(), T.data(), To.data(), n, want.data(), 0 );
+    bad = 0;
+    for (uint32 i = 0; i < n; ++i) bad += (got[i].score != want[i].score || got[i].sink.x != want[i].x || got[i].sink.y != want[i].y);
+    snprintf( label, sizeof(label), "batch_alignment_score TextBlocking %s", name ); report( label, bad, n );
+
     // traceback<64>
     aln::Alignment<int32>* d_aln; uint8* d_ops; uint32* d_nops; const uint32 stride = 150u + 200u + 8u;
     CK( cudaMalloc( &d_aln, n * sizeof(aln::Alignment<int32>) ) ); CK( cudaMalloc( &d_ops, (size_t)n * stride ) ); CK( cudaMalloc( &d_nops, n * 4 ) );

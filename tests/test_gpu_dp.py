@@ -248,3 +248,28 @@ def test_quality_aware_schemes(oracle, kind, ty):
                 assert (got == oracle.banded_score(oa, band, P, Po, T, To, qs=oqs, quals=Q)).all(), band
                 got = gu.tb_np(nvb.batch_banded_alignment_traceback(a, band, 16, ps, ts, scheme=qs, quals=qd))
                 assert gu.tb_equal(got, oracle.banded_traceback(oa, band, 16, P, Po, T, To, qs=oqs, quals=Q)), band
+
+
+@pytest.mark.parametrize("alpha", [4, 2])
+def test_text_blocking_scoring(oracle, alpha):
+    """nvb_batch_score_text_blocking (TextBlockingTag, alignment.h:266-279) vs the oracle (pinned on the reference's transposed
+    aligners): every kind and type, binary alphabets with many LOCAL ties, the configs[0] shape through the packed kernels"""
+    rng = np.random.default_rng(140 + alpha)
+    pat, pat_off, txt, txt_off = util.rand_pairs(rng, 800, (0, 120), lambda M: max(0, M + int(rng.integers(-8, 60))), alpha=alpha)   # incl. empty strings
+    ps, ts = gu.sset(pat, pat_off), gu.sset(txt, txt_off)
+    ctx = nvb.Context.default(0)
+    for kind, sc in ((po.ED, (0, -1, -1, -1)), (po.SW, (2, -1, -2, -3)), (po.SW, (1, -1, -1, -1)), (po.GOTOH, (2, -2, -5, -3))):
+        for ty in (po.GLOBAL, po.LOCAL, po.SEMI_GLOBAL):
+            want = oracle.score_text_blocking(po.aligner(kind, ty, sc), pat, pat_off, txt, txt_off)
+            for force in (0, 1):
+                ctx.force_generic(force)
+                got = gu.sinks_np(nvb.batch_alignment_score(gu.aligner(kind, ty, sc), ps, ts, text_blocking=True))
+                ctx.force_generic(0)
+                assert (got == want).all(), (kind, ty, sc, force)
+    # configs[0] shape: the transposed LOCAL batch (500-symbol "patterns") still takes a packed kernel
+    P, Po, T, To = util.rand_pairs(rng, 300, (150, 151), lambda M: 500, alpha=alpha)
+    a = po.aligner(po.SW, po.LOCAL, (2, -1, -1, -1))
+    want = oracle.score_text_blocking(a, P, Po, T, To)
+    got = gu.sinks_np(nvb.batch_alignment_score(gu.aligner(po.SW, po.LOCAL, (2, -1, -1, -1)), gu.sset(P, Po), gu.sset(T, To), text_blocking=True))
+    assert (got == want).all()
+    assert (want != oracle.score(a, P, Po, T, To)).any() or alpha == 4

@@ -100,3 +100,20 @@ def test_quality_aware_schemes(oracle, ref, kind, ty):
                 assert (ref.banded_score(a, band, P, Po, T, To, qs=qs, quals=Q) == oracle.banded_score(a, band, P, Po, T, To, qs=qs, quals=Q)).all(), band
                 assert util.ops_equal(ref.banded_traceback(a, band, 16, P, Po, T, To, qs=qs, quals=Q),
                                       oracle.banded_traceback(a, band, 16, P, Po, T, To, qs=qs, quals=Q)), band
+
+
+@pytest.mark.parametrize("alpha", [4, 2])
+def test_text_blocking_scoring(oracle, ref, alpha):
+    """TextBlockingTag (alignment.h:266-279): the oracle's transposition identity against the reference's own text-blocking aligners
+    (aln::transpose of every simple aligner, compiled in ref_wrap_aln.inl), incl. binary alphabets where LOCAL ties abound"""
+    rng = np.random.default_rng(40 + alpha)
+    pat, pat_off, txt, txt_off = util.rand_pairs(rng, 500, (0, 90), lambda M: max(0, M + int(rng.integers(-8, 40))), alpha=alpha)
+    differs = 0
+    for kind, sc in ((po.ED, (0, -1, -1, -1)), (po.SW, (2, -1, -2, -3)), (po.SW, (1, -1, -1, -1)), (po.GOTOH, (2, -2, -5, -3)), (po.GOTOH, (1, -1, -1, -1))):
+        for ty in (po.GLOBAL, po.LOCAL, po.SEMI_GLOBAL):
+            a = po.aligner(kind, ty, sc)
+            want = ref.score_text_blocking(a, pat, pat_off, txt, txt_off)
+            got = oracle.score_text_blocking(a, pat, pat_off, txt, txt_off)
+            assert (got == want).all(), (kind, ty, sc)
+            differs += int((want != ref.score(a, pat, pat_off, txt, txt_off)).sum())
+    assert differs > 20          # the blocking does change LOCAL tie winners
