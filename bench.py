@@ -814,6 +814,8 @@ def run_b200(args):
             hTo = torch.empty(To.numel(), dtype=torch.int32).pin_memory(); hTo.copy_(To)
             hS = torch.empty((n, 3), dtype=torch.int32).pin_memory()
             hS_n = hS.numpy().reshape(-1).view(nvb.SINK_DT)
+            hP2 = torch.from_numpy(nvb.pack_symbols(hP.numpy(), 2).view(np.int32)).pin_memory()
+            hT2 = torch.from_numpy(nvb.pack_symbols(hT.numpy(), 2).view(np.int32)).pin_memory()
             cstream = torch.cuda.ExternalStream(ctx.stream, device=dev)
 
             def full_leg(a, oa, steps, check_pairs):
@@ -836,6 +838,18 @@ def run_b200(args):
                 r["e2e"] = dict(gcups=world * n * M * N / (e_ms * 1e-3) / 1e9, ms=e_ms, h2d_bytes=int(hP.numel() + hT.numel() + 4 * (hPo.numel() + hTo.numel())),
                                 d2h_bytes=int(hS.numel() * 4), call="nvb_batch_score_host, pinned host buffers")
                 assert (hS.numpy() == sinks.cpu().numpy()).all(), "host and device scoring entry points disagree"
+                # the same with 2-bit packed host strings (the layout of the reference's own alignment benchmark): 4x fewer bytes on the bus
+                args_p = (a, 0, hP2.numpy().view(np.uint32), hPo.numpy().view(np.uint32), hT2.numpy().view(np.uint32), hTo.numpy().view(np.uint32))
+                hS.zero_(); nvb.batch_score_host(*args_p, sinks_h=hS_n, ctx=ctx, bits=2)
+                assert (hS.numpy() == sinks.cpu().numpy()).all(), "packed host scoring entry point disagrees"
+                et = []
+                for _ in range(2):
+                    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    e0.record(cstream); nvb.batch_score_host(*args_p, sinks_h=hS_n, ctx=ctx, bits=2); e1.record(cstream); e1.synchronize()
+                    et.append(e0.elapsed_time(e1))
+                p_ms = max_over_ranks(min(et))
+                r["e2e_packed2"] = dict(gcups=world * n * M * N / (p_ms * 1e-3) / 1e9, ms=p_ms, h2d_bytes=int(4 * (hP2.numel() + hT2.numel() + hPo.numel() + hTo.numel())),
+                                        d2h_bytes=int(hS.numel() * 4), call="nvb_batch_score_host_packed(bits = 2), pinned host buffers")
                 if do_cpu:
                     k = min(n, check_pairs)
                     t = time.time(); want = chk.score(oa, Ph[:k * M], Poh[:k + 1], Th[:k * N], Toh[:k + 1], threads=host_threads()); dt = time.time() - t
@@ -876,6 +890,8 @@ def run_b200(args):
                 Poh, Toh = (np.arange(k_chk + 1, dtype=np.int64) * M).astype(np.uint32), (np.arange(k_chk + 1, dtype=np.int64) * N).astype(np.uint32)
             hP = torch.empty(k_e2e * M, dtype=torch.uint8).pin_memory(); hP.copy_(P[:k_e2e * M])
             hT = torch.empty(k_e2e * N, dtype=torch.uint8).pin_memory(); hT.copy_(T[:k_e2e * N])
+            hP2 = torch.from_numpy(nvb.pack_symbols(hP.numpy(), 2).view(np.int32)).pin_memory()
+            hT2 = torch.from_numpy(nvb.pack_symbols(hT.numpy(), 2).view(np.int32)).pin_memory()
             hPo = torch.empty(k_e2e + 1, dtype=torch.int32).pin_memory(); hPo.copy_(Po[:k_e2e + 1])
             hTo = torch.empty(k_e2e + 1, dtype=torch.int32).pin_memory(); hTo.copy_(To[:k_e2e + 1])
             hS = torch.empty((k_e2e, 3), dtype=torch.int32).pin_memory()
@@ -905,6 +921,15 @@ def run_b200(args):
                                         h2d_bytes=int(hP.numel() + hT.numel() + 4 * (hPo.numel() + hTo.numel())), d2h_bytes=int(hS.numel() * 4),
                                         call="nvb_batch_score_host(band = 15), pinned host buffers")
                 assert (hS.numpy() == sinks[:k_e2e].cpu().numpy()).all(), "host and device banded scoring disagree"
+                args_p = (a, W, hP2.numpy().view(np.uint32), hPo.numpy().view(np.uint32), hT2.numpy().view(np.uint32), hTo.numpy().view(np.uint32))
+                hS.zero_(); nvb.batch_score_host(*args_p, sinks_h=hS_n, ctx=ctx, bits=2)
+                assert (hS.numpy() == sinks[:k_e2e].cpu().numpy()).all(), "packed host banded scoring disagrees"
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(cstream); nvb.batch_score_host(*args_p, sinks_h=hS_n, ctx=ctx, bits=2); e1.record(cstream); e1.synchronize()
+                p_ms = max_over_ranks(e0.elapsed_time(e1))
+                res[name]["e2e_packed2"] = dict(gcups=world * k_e2e * M * W / (p_ms * 1e-3) / 1e9, ms=p_ms, pairs=k_e2e,
+                                                h2d_bytes=int(4 * (hP2.numel() + hT2.numel() + hPo.numel() + hTo.numel())), d2h_bytes=int(hS.numel() * 4),
+                                                call="nvb_batch_score_host_packed(band = 15, bits = 2), pinned host buffers")
                 if do_cpu:
                     oa = po.aligner(getattr(po, okind), a.type, osc)
                     t = time.time(); want = chk.banded_score(oa, W, Ph, Poh, Th, Toh, threads=host_threads()); dt = time.time() - t

@@ -390,6 +390,12 @@ int nvb_alignments_to_reference_layout(nvb_ctx* ctx, const nvb_alignment* alignm
 int nvb_batch_score_host(nvb_ctx* ctx, nvb_aligner aligner, uint32_t band /* 0 = full matrix */,
                          const uint8_t* pat_h, const uint32_t* pat_off_h, const uint8_t* txt_h,
                          const uint32_t* txt_off_h, uint32_t n, nvb_best_sink* sinks_h);
+/* the same over packed host string sets (bits = 4 or 2: PackedStream<uint32,uint8,BITS,true> words, symbol 0 of the set in the top
+ * bits of word 0 -- the layout the reference's own alignment benchmark feeds): 2x / 4x fewer bytes cross the bus. Both forms cut
+ * batches of >= 65536 pairs into chunks and overlap the upload of one chunk with the kernels of another. */
+int nvb_batch_score_host_packed(nvb_ctx* ctx, nvb_aligner aligner, uint32_t band /* 0 = full matrix */, uint32_t bits,
+                                const void* pat_words_h, const uint32_t* pat_off_h, const void* txt_words_h,
+                                const uint32_t* txt_off_h, uint32_t n, nvb_best_sink* sinks_h);
 int nvb_batch_traceback_host(nvb_ctx* ctx, nvb_aligner aligner, uint32_t band /* 0 = full matrix */,
                              uint32_t checkpoints, const uint8_t* pat_h, const uint32_t* pat_off_h,
                              const uint8_t* txt_h, const uint32_t* txt_off_h, uint32_t n,

@@ -120,6 +120,7 @@ _PROTOS = {
     "nvb_sinks_to_reference_layout": (_i, [_vp, _vp, _u32, _vp, _vp]),
     "nvb_alignments_to_reference_layout": (_i, [_vp, _vp, _u32, _vp, _vp]),
     "nvb_batch_score_host": (_i, [_vp, AlignerC, _u32, _vp, _vp, _vp, _vp, _u32, _vp]),
+    "nvb_batch_score_host_packed": (_i, [_vp, AlignerC, _u32, _u32, _vp, _vp, _vp, _vp, _u32, _vp]),
     "nvb_batch_traceback_host": (_i, [_vp, AlignerC, _u32, _u32, _vp, _vp, _vp, _vp, _u32, _vp, _vp, _u32, _vp]),
     "nvb_pack_2bit": (_i, [_vp, _vp, _u32, _vp, _vp]),
     "nvb_map_reads": (_i, [_vp, C.POINTER(FMIndexC), _vp, StringSetC, _u32, C.POINTER(MapParamsC), _u32, _vp, _vp, _u32,

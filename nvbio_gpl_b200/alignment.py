@@ -337,11 +337,17 @@ def mds_to_md_string(mds):
 
 
 # host-buffer forms --------------------------------------------------------------------------------
-def batch_score_host(aligner, band, pat, pat_off, txt, txt_off, sinks_h=None, device=0, ctx=None):
+def batch_score_host(aligner, band, pat, pat_off, txt, txt_off, sinks_h=None, device=0, ctx=None, bits=8):
+    """host string sets in, host sinks out (``nvb_batch_score_host[_packed]``); bits = 4 / 2: pat and txt are packed uint32 words
+    (``pack_symbols``), offsets stay in symbols. Large batches are pipelined in chunks (upload under the kernels)."""
     ctx = ctx or Context.default(device)
     n = len(pat_off) - 1
     if sinks_h is None:
         sinks_h = np.empty(n, dtype=SINK_DT)
+    if bits != 8:
+        check(lib().nvb_batch_score_host_packed(ctx.h, aligner.c(), band, bits, pat.ctypes.data, pat_off.ctypes.data, txt.ctypes.data,
+                                                txt_off.ctypes.data, n, sinks_h.ctypes.data), ctx.h)
+        return sinks_h
     check(lib().nvb_batch_score_host(ctx.h, aligner.c(), band, pat.ctypes.data, pat_off.ctypes.data, txt.ctypes.data,
                                      txt_off.ctypes.data, n, sinks_h.ctypes.data), ctx.h)
     return sinks_h

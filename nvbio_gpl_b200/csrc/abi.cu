@@ -490,36 +490,104 @@ static uint32_t max_len(const uint32_t* off, uint32_t n)
     return m;
 }
 
-extern "C" int nvb_batch_score_host(nvb_ctx* ctx, nvb_aligner aligner, uint32_t band,
-                                    const uint8_t* pat_h, const uint32_t* pat_off_h, const uint8_t* txt_h,
-                                    const uint32_t* txt_off_h, uint32_t n, nvb_best_sink* sinks_h)
+// Host string sets in, host sinks out. Batches of >= 65536 pairs are cut into chunks that run as a three-stage pipeline (H2D of the
+// symbols and offsets of chunk k+1 on the copy-in stream, the kernels of chunk k, D2H of the sinks of chunk k-1; two buffer sets),
+// so a call costs about max(copies, kernels) instead of their sum. bits = 8, 4 or 2: packed streams (the reference's
+// PackedStream<uint32,uint8,BITS,true> layout, what its own sw-benchmark feeds) put 2x / 4x fewer bytes on the bus; a chunk keeps
+// its absolute offsets and the device symbol pointer is rebased to the chunk's first (word-aligned) byte.
+static int batch_score_host_impl(nvb_ctx* ctx, nvb_aligner aligner, uint32_t band, uint32_t bits,
+                                 const uint8_t* pat_h, const uint32_t* pat_off_h, const uint8_t* txt_h,
+                                 const uint32_t* txt_off_h, uint32_t n, nvb_best_sink* sinks_h)
 {
     if (!ctx) return NVB_ERR_ARG;
     if (n == 0) return NVB_OK;
     if (!pat_h || !pat_off_h || !txt_h || !txt_off_h || !sinks_h) return NVB_ERR_ARG;
+    if (bits != 8 && bits != 4 && bits != 2) return NVB_ERR_ARG;
     NVB_CUDA(ctx, cudaSetDevice(ctx->device));
-    const size_t np = pat_off_h[n], nt = txt_off_h[n];
-    const uint32_t maxM = max_len(pat_off_h, n), maxN = max_len(txt_off_h, n);
-    const size_t tb = nvb_temp_bytes(band ? NVB_OP_BANDED_SCORE : NVB_OP_SCORE, aligner, band, 0, maxM, maxN, n);
-    void *d_p, *d_po, *d_t, *d_to, *d_s, *d_tmp; int rc;
-    const size_t ob = sizeof(uint32_t) * ((size_t)n + 1);
-    if ((rc = nvb_stage(ctx, 0, np + 32, &d_p))) return rc;
-    if ((rc = nvb_stage(ctx, 1, ob, &d_po))) return rc;
-    if ((rc = nvb_stage(ctx, 2, nt + 32, &d_t))) return rc;
-    if ((rc = nvb_stage(ctx, 3, ob, &d_to))) return rc;
-    if ((rc = nvb_stage(ctx, 4, sizeof(nvb_best_sink) * (size_t)n, &d_s))) return rc;
-    if ((rc = nvb_stage(ctx, 5, tb, &d_tmp))) return rc;
-    NVB_CUDA(ctx, cudaMemcpyAsync(d_p, pat_h, np, cudaMemcpyHostToDevice, ctx->stream));
-    NVB_CUDA(ctx, cudaMemcpyAsync(d_po, pat_off_h, ob, cudaMemcpyHostToDevice, ctx->stream));
-    NVB_CUDA(ctx, cudaMemcpyAsync(d_t, txt_h, nt, cudaMemcpyHostToDevice, ctx->stream));
-    NVB_CUDA(ctx, cudaMemcpyAsync(d_to, txt_off_h, ob, cudaMemcpyHostToDevice, ctx->stream));
-    nvb_string_set P = { d_p, (const uint32_t*)d_po, n, 8 }, T = { d_t, (const uint32_t*)d_to, n, 8 };
-    if (band) rc = nvb_batch_banded_score(ctx, aligner, band, P, T, (nvb_best_sink*)d_s, maxM, maxN, d_tmp, tb, ctx->stream);
-    else      rc = nvb_batch_score(ctx, aligner, P, T, (nvb_best_sink*)d_s, maxM, maxN, d_tmp, tb, ctx->stream);
-    if (rc) return rc;
-    NVB_CUDA(ctx, cudaMemcpyAsync(sinks_h, d_s, sizeof(nvb_best_sink) * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
-    NVB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    const uint32_t spw = 32u / bits;
+    auto span_begin = [&](uint32_t s0) -> size_t { return bits == 8 ? (size_t)s0 : (size_t)(s0 / spw) * 4u; };
+    auto span_end   = [&](uint32_t s1) -> size_t { return bits == 8 ? (size_t)s1 : (size_t)((s1 + spw - 1u) / spw) * 4u; };
+    uint32_t chunk = n;
+    if (n >= 65536u) { chunk = ((n + 7u) / 8u + 1023u) & ~1023u; if (chunk < 16384u) chunk = 16384u; }
+    const uint32_t n_chunks = (n + chunk - 1u) / chunk;
+    const int n_sets = n_chunks > 1 ? 2 : 1;
+    // per-chunk sizes
+    size_t max_pb = 0, max_tb = 0; uint32_t maxM = 0, maxN = 0;
+    for (uint32_t k = 0; k < n_chunks; ++k)
+    {
+        const uint32_t c0 = k * chunk, c1 = c0 + chunk < n ? c0 + chunk : n;
+        const size_t pb = span_end(pat_off_h[c1]) - span_begin(pat_off_h[c0]), tb = span_end(txt_off_h[c1]) - span_begin(txt_off_h[c0]);
+        if (pb > max_pb) max_pb = pb;
+        if (tb > max_tb) max_tb = tb;
+    }
+    maxM = max_len(pat_off_h, n); maxN = max_len(txt_off_h, n);
+    const uint32_t cap = n < chunk ? n : chunk;
+    const size_t temp_bytes = nvb_temp_bytes(band ? NVB_OP_BANDED_SCORE : NVB_OP_SCORE, aligner, band, 0, maxM, maxN, cap);
+    const size_t ob = sizeof(uint32_t) * ((size_t)cap + 1);
+    void *d_p[2], *d_po[2], *d_t[2], *d_to[2], *d_s[2], *d_tmp; int rc;
+    for (int b = 0; b < n_sets; ++b)
+    {
+        // 64 spare bytes on both sides: a chunk's first / last string sits at the edge of ITS copy, and the banded kernels fetch whole
+        // aligned 16-byte blocks (they guard the ends of the set they are given, which here spans the caller's whole array)
+        if ((rc = nvb_stage(ctx, 64 + 5 * b + 0, max_pb + 128, &d_p[b]))) return rc;
+        if ((rc = nvb_stage(ctx, 64 + 5 * b + 1, ob, &d_po[b]))) return rc;
+        if ((rc = nvb_stage(ctx, 64 + 5 * b + 2, max_tb + 128, &d_t[b]))) return rc;
+        if ((rc = nvb_stage(ctx, 64 + 5 * b + 3, ob, &d_to[b]))) return rc;
+        if ((rc = nvb_stage(ctx, 64 + 5 * b + 4, sizeof(nvb_best_sink) * (size_t)cap, &d_s[b]))) return rc;
+    }
+    if ((rc = nvb_stage(ctx, 74, temp_bytes, &d_tmp))) return rc;
+    if (!ctx->host_ev[0])
+        for (int i = 0; i < 12; ++i) NVB_CUDA(ctx, cudaEventCreateWithFlags(&ctx->host_ev[i], cudaEventDisableTiming));
+    cudaStream_t s_in = n_sets > 1 ? ctx->aux[0] : ctx->stream, s_k = ctx->stream, s_out = n_sets > 1 ? ctx->aux[1] : ctx->stream;
+    for (uint32_t k = 0; k < n_chunks; ++k)
+    {
+        const int b = (int)(k & 1u) % n_sets;
+        cudaEvent_t ev_in = ctx->host_ev[3 * b], ev_k = ctx->host_ev[3 * b + 1], ev_out = ctx->host_ev[3 * b + 2];
+        const uint32_t c0 = k * chunk, c1 = c0 + chunk < n ? c0 + chunk : n, cnt = c1 - c0;
+        const size_t pb0 = span_begin(pat_off_h[c0]), pbn = span_end(pat_off_h[c1]) - pb0;
+        const size_t tb0 = span_begin(txt_off_h[c0]), tbn = span_end(txt_off_h[c1]) - tb0;
+        if (k >= (uint32_t)n_sets) NVB_CUDA(ctx, cudaStreamWaitEvent(s_in, ev_out, 0));          // the set's previous sinks have left
+        NVB_CUDA(ctx, cudaMemcpyAsync((uint8_t*)d_p[b] + 64, pat_h + pb0, pbn, cudaMemcpyHostToDevice, s_in));
+        NVB_CUDA(ctx, cudaMemcpyAsync(d_po[b], pat_off_h + c0, sizeof(uint32_t) * ((size_t)cnt + 1), cudaMemcpyHostToDevice, s_in));
+        NVB_CUDA(ctx, cudaMemcpyAsync((uint8_t*)d_t[b] + 64, txt_h + tb0, tbn, cudaMemcpyHostToDevice, s_in));
+        NVB_CUDA(ctx, cudaMemcpyAsync(d_to[b], txt_off_h + c0, sizeof(uint32_t) * ((size_t)cnt + 1), cudaMemcpyHostToDevice, s_in));
+        if (n_sets > 1)
+        {
+            NVB_CUDA(ctx, cudaEventRecord(ev_in, s_in));
+            NVB_CUDA(ctx, cudaStreamWaitEvent(s_k, ev_in, 0));
+        }
+        nvb_string_set P = { (const uint8_t*)d_p[b] + 64 - pb0, (const uint32_t*)d_po[b], cnt, bits }, T = { (const uint8_t*)d_t[b] + 64 - tb0, (const uint32_t*)d_to[b], cnt, bits };
+        ctx->dp_first[0] = pat_off_h[c0]; ctx->dp_first[1] = txt_off_h[c0];
+        if (band) rc = nvb_batch_banded_score(ctx, aligner, band, P, T, (nvb_best_sink*)d_s[b], maxM, maxN, d_tmp, temp_bytes, s_k);
+        else      rc = nvb_batch_score(ctx, aligner, P, T, (nvb_best_sink*)d_s[b], maxM, maxN, d_tmp, temp_bytes, s_k);
+        ctx->dp_first[0] = ctx->dp_first[1] = 0;
+        if (rc) return rc;
+        if (n_sets > 1)
+        {
+            NVB_CUDA(ctx, cudaEventRecord(ev_k, s_k));
+            NVB_CUDA(ctx, cudaStreamWaitEvent(s_out, ev_k, 0));
+        }
+        NVB_CUDA(ctx, cudaMemcpyAsync(sinks_h + c0, d_s[b], sizeof(nvb_best_sink) * (size_t)cnt, cudaMemcpyDeviceToHost, s_out));
+        if (n_sets > 1) NVB_CUDA(ctx, cudaEventRecord(ev_out, s_out));
+    }
+    NVB_CUDA(ctx, cudaStreamSynchronize(s_out));
+    NVB_CUDA(ctx, cudaStreamSynchronize(s_in));
+    NVB_CUDA(ctx, cudaStreamSynchronize(s_k));
     return NVB_OK;
+}
+
+extern "C" int nvb_batch_score_host(nvb_ctx* ctx, nvb_aligner aligner, uint32_t band,
+                                    const uint8_t* pat_h, const uint32_t* pat_off_h, const uint8_t* txt_h,
+                                    const uint32_t* txt_off_h, uint32_t n, nvb_best_sink* sinks_h)
+{ return batch_score_host_impl(ctx, aligner, band, 8, pat_h, pat_off_h, txt_h, txt_off_h, n, sinks_h); }
+
+// packed host string sets: bits = 4 or 2, big-endian 32-bit words
+extern "C" int nvb_batch_score_host_packed(nvb_ctx* ctx, nvb_aligner aligner, uint32_t band, uint32_t bits,
+                                           const void* pat_words_h, const uint32_t* pat_off_h, const void* txt_words_h,
+                                           const uint32_t* txt_off_h, uint32_t n, nvb_best_sink* sinks_h)
+{
+    if (bits != 4 && bits != 2) return NVB_ERR_ARG;
+    return batch_score_host_impl(ctx, aligner, band, bits, (const uint8_t*)pat_words_h, pat_off_h, (const uint8_t*)txt_words_h, txt_off_h, n, sinks_h);
 }
 
 extern "C" int nvb_batch_traceback_host(nvb_ctx* ctx, nvb_aligner aligner, uint32_t band, uint32_t checkpoints,

@@ -11,10 +11,10 @@
 #endif
 
 #define NVB_SM_COUNT 148
-#define NVB_STAGE_SLOTS 64
+#define NVB_STAGE_SLOTS 80
 // stage slot map (nvb_ctx::d_stage): 0-7 *_host DP/locate entry points and FMIndexFilter | 8-32 the seed-and-extend pipeline
 // (map_pipeline.cu S_*) | 33-44 nvb_fm_match_host* (4 buffer sets x 3) | 40-41 are NOT free: they belong to that range; the
-// packed-set expansion of dp_api.cu uses 60-61 | 45-54 nvb_map_reads_host (2 sets x 5) | 55 quality-scheme tables (dp_api.cu) | 56 min-score table of nvb_map_hits_mapq (mds.cu) | 57 N list of nvb_fm_match_host_fixed2n | 62-63 per-batch k-mer table (fm_kernels.cu)
+// packed-set expansion of dp_api.cu uses 60-61 | 45-54 nvb_map_reads_host (2 sets x 5) | 55 quality-scheme tables (dp_api.cu) | 56 min-score table of nvb_map_hits_mapq (mds.cu) | 57 N list of nvb_fm_match_host_fixed2n | 64-75 pipelined nvb_batch_score_host* (2 sets x 5, temp) | 62-63 per-batch k-mer table (fm_kernels.cu)
 
 struct nvb_ctx
 {
@@ -37,6 +37,7 @@ struct nvb_ctx
     cudaEvent_t  host_ev[12];  // event chain of the pipelined *_host entry points (3 per buffer set)
     cudaStream_t aux[3];       // the *_host entry points pipeline chunks over these: copy-in, copy-out, second compute stream
     cudaEvent_t  tab_ev;       // the per-call k-mer table of the FM host entry points is ready
+    uint32_t     dp_first[2];  // offsets[0] of the (pattern, text) sets of the next DP call when a host entry point passes a chunk with absolute offsets; else 0
 };
 
 // true the first time it is evaluated AT THIS PLACE for the context's device: cudaFuncSetAttribute is per device and, inside a

@@ -79,16 +79,17 @@ static uint32_t batch_pairs(const TempPlan& p, size_t temp_bytes, uint32_t n)
 // its own scratch from it as well): the expansion covers count * max_len symbols.
 // ---------------------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
-dp_unpack_kernel(const uint32_t* __restrict__ words, uint32_t bits, const uint32_t* __restrict__ total_d, uint64_t cap, uint8_t* __restrict__ out)
+dp_unpack_kernel(const uint32_t* __restrict__ words, uint32_t bits, const uint32_t* __restrict__ total_d, uint32_t first16, uint64_t cap, uint8_t* __restrict__ out)
 {
     const uint64_t g = (uint64_t)blockIdx.x * 256u + threadIdx.x;        // one group of 16 symbols per thread
-    const uint64_t total = min((uint64_t)*total_d, cap);
-    const uint64_t i0 = g * 16u;
+    const uint64_t total = min((uint64_t)*total_d, first16 + cap);
+    const uint64_t i0 = first16 + g * 16u;                               // absolute symbol index of the group
     if (i0 >= total) return;
+    const uint64_t gw = i0 >> 4;
     uint32_t b[4];
     if (bits == 4)
     {
-        const uint32_t w0 = __ldg(words + 2 * g), w1 = (i0 + 8u < total) ? __ldg(words + 2 * g + 1) : 0u;
+        const uint32_t w0 = __ldg(words + 2 * gw), w1 = (i0 + 8u < total) ? __ldg(words + 2 * gw + 1) : 0u;
         #pragma unroll
         for (int k = 0; k < 4; ++k)
         {
@@ -98,7 +99,7 @@ dp_unpack_kernel(const uint32_t* __restrict__ words, uint32_t bits, const uint32
     }
     else
     {
-        const uint32_t w = __ldg(words + g);
+        const uint32_t w = __ldg(words + gw);
         #pragma unroll
         for (int k = 0; k < 4; ++k)
         {
@@ -106,23 +107,27 @@ dp_unpack_kernel(const uint32_t* __restrict__ words, uint32_t bits, const uint32
             b[k] = ((w >> base) & 3u) | (((w >> (base - 2)) & 3u) << 8) | (((w >> (base - 4)) & 3u) << 16) | (((w >> (base - 6)) & 3u) << 24);
         }
     }
-    *(uint4*)(out + i0) = make_uint4(b[0], b[1], b[2], b[3]);          // the scratch is padded to whole groups
+    *(uint4*)(out + g * 16u) = make_uint4(b[0], b[1], b[2], b[3]);       // the scratch is padded to whole groups
 }
 
 enum { DP_STAGE_UNPACK_P = 60, DP_STAGE_UNPACK_T = 61 };   // slot map in common.cuh (40/41 collided with nvb_fm_match_host's 4th buffer set)
 
-static int unpack_set(nvb_ctx* ctx, StrSet& S, uint32_t max_len, int slot, cudaStream_t s)
+// `first`: symbol index of the set's first symbol (offsets[0]); 0 for a caller's set, the chunk's first symbol when a host entry
+// point hands over a chunk that keeps the absolute offsets of the caller's array (ctx->dp_first). The expansion covers the
+// count * max_len symbols from there and the returned pointer is rebased so that absolute indices keep working.
+static int unpack_set(nvb_ctx* ctx, StrSet& S, uint32_t max_len, int slot, cudaStream_t s, uint32_t first)
 {
     if (S.bits == 8) return NVB_OK;
-    const uint64_t cap = (uint64_t)S.count * max_len;
+    const uint32_t first16 = first & ~15u;
+    const uint64_t cap = (uint64_t)S.count * max_len + (first - first16);
     if (cap == 0 || cap > 0xFFFFFFF0ull) return NVB_ERR_UNSUPPORTED;
     void* out = nullptr;
-    int rc = nvb_stage(ctx, slot, (size_t)((cap + 15u) & ~15ull) + 64, &out);
+    int rc = nvb_stage(ctx, slot, (size_t)((cap + 15u) & ~15ull) + 128, &out);
     if (rc) return rc;
     const uint64_t groups = (cap + 15u) / 16u;
-    dp_unpack_kernel<<<(uint32_t)((groups + 255u) / 256u), 256, 0, s>>>((const uint32_t*)S.sym, S.bits, S.off + S.count, cap, (uint8_t*)out);
+    dp_unpack_kernel<<<(uint32_t)((groups + 255u) / 256u), 256, 0, s>>>((const uint32_t*)S.sym, S.bits, S.off + S.count, first16, cap, (uint8_t*)out + 64);
     NVB_LAUNCHED(ctx);
-    S.sym = (const uint8_t*)out; S.bits = 8;
+    S.sym = (const uint8_t*)out + 64 - first16; S.bits = 8;             // 64 spare bytes in front: aligned block fetches of the first string
     return NVB_OK;
 }
 
@@ -135,7 +140,7 @@ static int unpack_for_fast_path(nvb_ctx* ctx, StrSet& P, StrSet& T, uint32_t max
     if (!supported(P8, T8)) return NVB_OK;
     if ((uint64_t)P.count * maxM > 0xFFFFFFF0ull || (uint64_t)T.count * maxN > 0xFFFFFFF0ull) return NVB_OK;
     int rc;
-    if ((rc = unpack_set(ctx, P, maxM, DP_STAGE_UNPACK_P, s)) || (rc = unpack_set(ctx, T, maxN, DP_STAGE_UNPACK_T, s))) return rc;
+    if ((rc = unpack_set(ctx, P, maxM, DP_STAGE_UNPACK_P, s, ctx->dp_first[0])) || (rc = unpack_set(ctx, T, maxN, DP_STAGE_UNPACK_T, s, ctx->dp_first[1]))) return rc;
     return NVB_OK;
 }
 

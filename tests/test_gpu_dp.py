@@ -273,3 +273,24 @@ def test_text_blocking_scoring(oracle, alpha):
     got = gu.sinks_np(nvb.batch_alignment_score(gu.aligner(po.SW, po.LOCAL, (2, -1, -1, -1)), gu.sset(P, Po), gu.sset(T, To), text_blocking=True))
     assert (got == want).all()
     assert (want != oracle.score(a, P, Po, T, To)).any() or alpha == 4
+
+
+@pytest.mark.parametrize("bits", [8, 4, 2])
+def test_host_scoring_pipelined_and_packed(oracle, bits):
+    """nvb_batch_score_host / _packed on batches large enough to be cut into pipelined chunks (ragged strings, chunk boundaries that
+    do not fall on word boundaries of the packed streams), banded and full matrix, against the oracle"""
+    rng = np.random.default_rng(300 + bits)
+    n = 70001
+    M = rng.integers(20, 61, n); N = M + rng.integers(15, 30, n)
+    Po = np.concatenate([[0], np.cumsum(M)]).astype(np.uint32); To = np.concatenate([[0], np.cumsum(N)]).astype(np.uint32)
+    P = rng.integers(0, 4, int(Po[-1])).astype(np.uint8); T = rng.integers(0, 4, int(To[-1])).astype(np.uint8)
+    for i in range(0, n, 3):                                          # implant the pattern with a few substitutions
+        s = int(rng.integers(0, N[i] - M[i] + 1)); seg = P[Po[i]:Po[i + 1]].copy()
+        seg[rng.random(len(seg)) < 0.05] = rng.integers(0, 4)
+        T[To[i] + s:To[i] + s + M[i]] = seg
+    Ph, Th = (P, T) if bits == 8 else (nvb.pack_symbols(P, bits), nvb.pack_symbols(T, bits))
+    for kind, ty, sc, band in ((po.GOTOH, 2, (0, -5, -8, -3), 15), (po.ED, 2, (0, -1, -1, -1), 15), (po.SW, 1, (2, -1, -1, -1), 0), (po.SW, 2, (2, -1, -2, -3), 0)):
+        a, oa = gu.aligner(kind, ty, sc), po.aligner(kind, ty, sc)
+        got = nvb.batch_score_host(a, band, Ph, Po, Th, To, bits=bits)
+        want = oracle.banded_score(oa, band, P, Po, T, To) if band else oracle.score(oa, P, Po, T, To)
+        assert (got["score"] == want["score"]).all() and (got["x"] == want["x"]).all() and (got["y"] == want["y"]).all(), (kind, ty, band)
