@@ -21,7 +21,7 @@
 // ---------------------------------------------------------------------------------------------
 // REV: match_reverse (fmindex_inl.h:252-278) -- the same loop consuming the pattern front to back.
 template <int BITS, bool FROM, bool KTAB, bool REV, bool TMA>
-__global__ void __launch_bounds__(FM_THREADS)
+__global__ void __launch_bounds__(FM_THREADS, 8)
 fm_match_kernel(const FMView f, const StrSet q, uint32_t* __restrict__ ranges)
 {
     __shared__ __align__(16) uint8_t s_sym[FM_STAGE_BYTES];
@@ -211,7 +211,7 @@ fm_rank4_kernel(const FMView f, const uint32_t* __restrict__ k, uint32_t n, uint
 }
 
 template <bool DENSE>
-__global__ void __launch_bounds__(FM_THREADS)
+__global__ void __launch_bounds__(FM_THREADS, 8)
 fm_locate_kernel(const FMView f, const uint32_t* __restrict__ rows, uint32_t n, uint32_t* __restrict__ pos)
 {
     __shared__ uint2 s_lut[FM_LUT_ENTRIES];

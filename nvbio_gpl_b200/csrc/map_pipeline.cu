@@ -217,7 +217,7 @@ map_expand_kernel(const uint2* __restrict__ seeds, const uint32_t* __restrict__ 
 // REV selects the rows of one index when a reverse index takes part (slots [Rf, R) of a seed): rows of the other index pass
 // through as already-sampled dummies and are left untouched
 template <bool DENSE>
-__global__ void __launch_bounds__(MAP_THREADS)
+__global__ void __launch_bounds__(MAP_THREADS, 8)
 map_walk_kernel(const FMView f, uint32_t n_hits, uint2* __restrict__ rows, uint32_t* __restrict__ steps, uint32_t R, uint32_t Rf, uint32_t rev)
 {
     __shared__ uint2 s_lut[FM_LUT_ENTRIES];
