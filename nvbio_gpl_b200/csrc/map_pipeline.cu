@@ -75,8 +75,11 @@ map_seed_kernel(const FMView f, const StrSet reads, const MapGeom g, uint2* __re
     __shared__ uint32_t s_L2[8];
     if (threadIdx.x < 5) s_L2[threadIdx.x] = f.L2[threadIdx.x];
     fm_lut_init(s_lut);
-    const uint32_t t = blockIdx.x * MAP_THREADS + threadIdx.x;
-    if (t >= g.n_reads * g.n_strands * g.S) return;
+    // a grid that just fills the device walks the slots with a stride: the LUT set-up of a CTA serves many seeds (a seed lives for
+    // 3 - 5 dependent DRAM accesses only)
+    const uint32_t n_slots = g.n_reads * g.n_strands * g.S;
+    for (uint32_t t = blockIdx.x * MAP_THREADS + threadIdx.x; t < n_slots; t += gridDim.x * MAP_THREADS)
+    {
     const MapSlot sl = map_slot(g, t);                       // R == 1 on this path
     const uint32_t r = sl.r, strand = sl.strand, k = sl.k;
     const uint32_t beg = reads.off[g.r0 + r], L = reads.off[g.r0 + r + 1] - beg;
@@ -110,6 +113,7 @@ map_seed_kernel(const FMView f, const StrSet reads, const MapGeom g, uint2* __re
     }
     seeds[t] = make_uint2(x, cnt);
     counts[t] = cnt;
+    }
 }
 
 // approximate seeding (nvb_map_params.seed_mismatches = 1): nvBowtie's map<CHECK_EXACT> on the forward index
@@ -643,7 +647,13 @@ extern "C" int nvb_map_reads(nvb_ctx* ctx, const nvb_fmindex* fmi, const uint32_
             MAP_STAGE(S_COUNT, sizeof(uint32_t) * ((size_t)n_slots + 1), counts);
             MAP_STAGE(S_SCAN, sizeof(uint32_t) * ((size_t)n_slots + 1), scan);
             NVB_CUDA(ctx, cudaMemsetAsync(counts + n_slots, 0, sizeof(uint32_t), s));
-            if (g.R == 1u) map_seed_kernel<<<map_grid(n_slots), MAP_THREADS, 0, s>>>(f, reads, g, seeds, counts);
+            if (g.R == 1u)
+            {
+                static int seed_waves = -1;
+                if (seed_waves < 0) { const char* e = getenv("NVB_MAP_SEED_WAVES"); seed_waves = e ? atoi(e) : 16; }
+                const uint32_t want = map_grid(n_slots), fill = (uint32_t)ctx->sm_count * 6u * (uint32_t)(seed_waves > 0 ? seed_waves : 1);
+                map_seed_kernel<<<(seed_waves > 0 && fill < want) ? fill : want, MAP_THREADS, 0, s>>>(f, reads, g, seeds, counts);
+            }
             else           map_seed_approx_kernel<<<map_grid(n_slots / g.R), MAP_THREADS, 0, s>>>(f, rf, reads, g, seeds, counts);
             NVB_LAUNCHED(ctx);
             if (g.priority)
