@@ -1004,7 +1004,9 @@ def run_b200(args):
             pt, tt = nvb.StringSet(P, Po, 8, M), nvb.StringSet(T, To, 8, N)
             res = {}
             for name, a, okind, osc in (("sw_local", nvb.SmithWatermanAligner(nvb.LOCAL, 2, -1, -1, -1), "SW", (2, -1, -1, -1)),
-                                        ("gotoh_semi_global", nvb.GotohAligner(nvb.SEMI_GLOBAL, 2, -2, -5, -3), "GOTOH", (2, -2, -5, -3))):
+                                        ("gotoh_semi_global", nvb.GotohAligner(nvb.SEMI_GLOBAL, 2, -2, -5, -3), "GOTOH", (2, -2, -5, -3)),
+                                        ("sw_semi_global", nvb.SmithWatermanAligner(nvb.SEMI_GLOBAL, 2, -1, -1, -1), "SW", (2, -1, -1, -1)),
+                                        ("ed_global", nvb.EditDistanceAligner(nvb.GLOBAL), "ED", (0, -1, -1, -1))):
                 ttemp = torch.empty(int(nvb.lib().nvb_temp_bytes(2, a.c(), 0, 64, M, N, nt)), dtype=torch.uint8, device=dev)
                 bufs = {}
                 def fn():
@@ -1012,7 +1014,8 @@ def run_b200(args):
                 tms = time_steps(fn, 2, 1, flush)
                 ms = max_over_ranks(sum(tms) / len(tms))
                 res[name] = dict(pairs_per_s=world * nt / (ms * 1e-3), ms=ms, pairs=nt, paths=ctx.last_paths, gcups_equiv=world * nt * M * N / (ms * 1e-3) / 1e9,
-                                 note="int32 one-pair-per-thread kernels (score pass + per-checkpoint recomputation); no packed kernel yet")
+                                 note=("packed forward pass writing 2 flow bits per cell + one walk thread per pair" if ctx.last_paths & 4 else
+                                       "int32 one-pair-per-thread kernels (score pass + per-checkpoint recomputation)"))
                 if rank == 0 and world == 1 and not args.no_cpu and only == "":
                     po, chk, kind = load_checker()
                     kt = min(nt, 5000)

@@ -238,7 +238,7 @@ def batch_alignment_traceback(aligner, checkpoints, patterns, texts, ops_stride=
     dev = patterns.offsets.device
     maxM, maxN = patterns.max_len, texts.max_len
     if ops_stride is None:
-        ops_stride = maxM + maxN + 8
+        ops_stride = (maxM + maxN + 8 + 15) & ~15         # rows 16-byte aligned: the packed walk stores 16 ops at a time
     out = torch.empty((n, 5), dtype=torch.int32, device=dev)
     ops = torch.zeros((n, ops_stride), dtype=torch.uint8, device=dev)
     n_ops = torch.empty(n, dtype=torch.int32, device=dev)

@@ -370,14 +370,39 @@ static int batch_traceback_impl(nvb_ctx* ctx, nvb_aligner a, const nvb_quality_s
     const TempPlan p = plan(NVB_OP_TRACEBACK, a, 0, chk, maxM, maxN);
     const uint32_t bp = batch_pairs(p, temp_bytes, n);
     if (bp == 0) return NVB_ERR_TEMP;
-    ctx->last_paths = 2u;
+    ctx->last_paths = 0;
     const uint32_t bp128 = (bp + 127u) & ~127u;
+    const uint32_t* list = nullptr; const uint32_t* d_count = nullptr;
+    if (!qd && ctx->force_generic == 0 && dpf2_traceback_supported(a, maxM, maxN))
+    {
+        // SW / ED GLOBAL and SEMI_GLOBAL: one tagged packed forward pass + a walk per pair (the directions do not depend on the
+        // checkpoints); the flow of a launch lives in temp. Pairs the packed kernel cannot represent are re-done below.
+        const size_t per_couple = dpf2_tb_bytes_per_couple(maxM, maxN);
+        uint8_t* flow = (uint8_t*)(((uintptr_t)temp + 15u) & ~(uintptr_t)15u);
+        const size_t avail = temp_bytes > 32 ? temp_bytes - 32 : 0;
+        uint64_t fit = 2ull * (avail / per_couple);
+        if (fit >= 2)
+        {
+            if (fit > n) fit = ((uint64_t)n + 1) & ~1ull;
+            uint32_t* wl = nullptr;
+            if ((rc = nvb_worklist(ctx, n, &wl))) return rc;
+            NVB_CUDA(ctx, cudaMemsetAsync(wl, 0, sizeof(uint32_t), s));
+            for (uint64_t first = 0; first < n; first += fit)
+            {
+                const uint32_t cnt = (uint32_t)(n - first < fit ? n - first : fit);
+                if ((rc = dpf2_traceback(ctx, a, P, T, (uint32_t)first, cnt, out, ops, ops_stride, n_ops, maxM, maxN, flow, wl, s))) return rc;
+            }
+            ctx->last_paths |= 4u;
+            list = wl + 1; d_count = wl;
+        }
+    }
+    if (!list) ctx->last_paths |= 2u;
     for (uint32_t first = 0; first < n; first += bp)
     {
         const uint32_t cnt = n - first < bp ? n - first : bp;
         int16_t* t16 = (int16_t*)temp;
         uint8_t* flow = (uint8_t*)temp + p.i16_per_pair * 2 * (size_t)bp128;
-        if ((rc = dpg_full_traceback(ctx, a, P, T, first, cnt, chk, out, ops, ops_stride, n_ops, t16, flow, maxM, maxN, s, qd))) return rc;
+        if ((rc = dpg_full_traceback(ctx, a, P, T, list, d_count, first, cnt, chk, out, ops, ops_stride, n_ops, t16, flow, maxM, maxN, s, qd))) return rc;
     }
     return NVB_OK;
 }

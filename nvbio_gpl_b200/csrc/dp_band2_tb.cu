@@ -287,45 +287,6 @@ band2_tb_forward_kernel(const Band2TbParams q)
     }
 }
 
-// ops of one pair, pushed one at a time; written 16 at a time when the pair's op row is 16-byte aligned (a byte
-// store per op costs a 32-byte sector write each: the walk would be bound by them)
-struct OpSink
-{
-    uint8_t* ops; uint32_t cap, n; bool wide;
-    uint32_t cur, w0, w1, w2;          // the block of 16 ops being filled: three finished words + the current one
-    __device__ __forceinline__ void init(uint8_t* o, uint32_t c)
-    { ops = o; cap = c; n = 0; cur = w0 = w1 = w2 = 0; wide = (((uintptr_t)o) & 15u) == 0u; }
-    // bytes [0, cnt) of the current block go to ops[base ..], clipped to cap; `done` words of the block are finished
-    __device__ __forceinline__ void spill(uint32_t base, uint32_t cnt, uint32_t done)
-    {
-        for (uint32_t k = 0; k < cnt; ++k)
-        {
-            const uint32_t wi = k >> 2;
-            const uint32_t word = wi >= done ? cur : (wi == 0u ? w0 : wi == 1u ? w1 : w2);
-            if (base + k < cap) ops[base + k] = (uint8_t)(word >> (8u * (k & 3u)));
-        }
-    }
-    __device__ __forceinline__ void push(uint32_t op)
-    {
-        if (!wide) { if (n < cap) ops[n] = (uint8_t)op; ++n; return; }
-        cur |= op << (8u * (n & 3u));
-        if ((n & 3u) == 3u)
-        {
-            const uint32_t k = (n >> 2) & 3u;
-            if (k == 0u) w0 = cur; else if (k == 1u) w1 = cur; else if (k == 2u) w2 = cur;
-            else if (n < cap) *(uint4*)(ops + (n & ~15u)) = make_uint4(w0, w1, w2, cur);
-            else spill(n & ~15u, 16u, 3u);
-            cur = 0;
-        }
-        ++n;
-    }
-    __device__ __forceinline__ void finish()
-    {
-        const uint32_t pend = n & 15u;
-        if (wide && pend) spill(n - pend, pend, pend >> 2);
-    }
-};
-
 // ---------------------------------------------------------------------------------------------
 // the walk: one thread per pair (sw_banded_inl.h:740-800, gotoh_banded_inl.h:883-950 without the windows)
 // ---------------------------------------------------------------------------------------------

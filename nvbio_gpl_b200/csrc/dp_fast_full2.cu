@@ -778,3 +778,263 @@ int dpf2_full_score(nvb_ctx* ctx, const nvb_aligner& a, StrSet P, StrSet T, nvb_
     NVB_LAUNCHED(ctx);
     return NVB_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// part 3: full-matrix traceback, Smith-Waterman / edit distance GLOBAL and SEMI_GLOBAL (aln::alignment_traceback,
+// alignment_inl.h:355-455 over sw_inl.h:1321-1693). The reference sweeps the matrix once for the sink while saving a
+// checkpoint column every CHECKPOINTS pattern columns, then recomputes one window of columns at a time, keeping a flow byte per
+// cell, and walks it; the int32 kernel (dp_generic_full.cuh) does exactly that. Here ONE packed forward pass -- the sweep of
+// dpf2_sw_kernel -- writes the direction of every cell, and one thread per pair walks them: the directions of a cell do not depend
+// on where the checkpoints are.
+//
+// The direction comes out of the maximum itself (the trick of dp_band2_tb.cu): every value is kept times four and each candidate
+// carries its move in the two low bits -- diagonal 2, left (insertion) 1, top (deletion) 0 -- so VIMNMX3 picks, among equal scores,
+// exactly what sw_inl.h:488-490 picks: the diagonal unless a gap is strictly better, the insertion unless the deletion is strictly
+// better. A cell costs PRMT + VIMNMX3 + LOP3 (re-tag as `left`) + LOP3 (its tag) on the ALU pipe and three IMADs on the FMA pipe.
+// Flow: 2 bits per cell and pair, one 64-bit word per stripe and row (columns 0..7 of both pairs in .x, 8..15 in .y, column j at
+// bits 2 (7 - j mod 8), pair B 16 bits up), laid out [couple][stripe][row] so that a lane streams its rows.
+// ---------------------------------------------------------------------------------------------------------------
+struct Full2TbParams
+{
+    Full2Params    f;              // sinks unused
+    nvb_alignment* out;
+    uint32_t*      n_ops;
+    uint8_t*       ops;
+    uint32_t       ops_stride;
+    uint2*         flow;
+    uint32_t       first, n_launch;        // pairs [first, first + n_launch)
+    uint32_t       maxM, maxN;
+};
+
+__global__ void __launch_bounds__(DF2_THREADS, 4)
+dpf2_sw_tb_forward_kernel(const Full2TbParams q)
+{
+    const Full2Params& p = q.f;
+    extern __shared__ uint32_t s_mem[];
+    const uint32_t lane = threadIdx.x & 31u, wib = threadIdx.x >> 5;
+    const uint32_t warp = blockIdx.x * DF2_WARPS + wib;
+    const uint32_t g = lane / p.lanes, k = lane - g * p.lanes;
+    const uint32_t task = warp * p.tpw + g;
+    const bool live = g < p.tpw && task < p.n_tasks;
+    const uint32_t gbase = g * p.lanes;
+
+    uint32_t idA = 0, idB = 0, pbA = 0, pbB = 0, tbA = 0, tbB = 0, MA = 0, MB = 0, NA = 0, NB = 0;
+    bool hasB = false, longA = false, longB = false;
+    if (live)
+    {
+        idA = q.first + 2 * task; hasB = idA + 1 < q.first + q.n_launch; idB = hasB ? idA + 1 : idA;
+        pbA = p.P.off[idA]; MA = p.P.off[idA + 1] - pbA; pbB = p.P.off[idB]; MB = p.P.off[idB + 1] - pbB;
+        tbA = p.T.off[idA]; NA = p.T.off[idA + 1] - tbA; tbB = p.T.off[idB]; NB = p.T.off[idB + 1] - tbB;
+        // a pair longer than the launch was sized for is left to the int32 kernel (which reports it as invalid) and swept as empty
+        longA = MA > q.maxM || NA > q.maxN; longB = MB > q.maxM || NB > q.maxN;
+        if (longA) MA = NA = 0;
+        if (longB) MB = NB = 0;
+    }
+    const uint32_t Nmax = max(NA, NB);
+    bool dirtyA = false, dirtyB = false;
+
+    uint32_t* my_words = s_mem + ((size_t)wib * p.tpw + (live ? g : 0)) * (p.sstride + p.cstride);
+    uint16_t* my_sel   = (uint16_t*)my_words;
+    uint32_t* my_cand  = my_words + p.sstride;
+    const uint32_t pad = p.lanes - 1u;
+    if (live) f2_pack_selectors(p.T, my_sel, k, p.lanes, pad, tbA, NA, tbB, NB, Nmax, dirtyA, dirtyB);
+    __syncwarp();
+
+    // profiles: 4 S' + 2 (the diagonal's tag) inside the pattern, 0 past it
+    const int32_t sm = 4 * (p.match - p.ga - p.gb) + 2, sx = 4 * (p.mismatch - p.ga - p.gb) + 2;
+    const uint32_t base  = ((uint32_t)sx & 0xFFu) * 0x01010101u;
+    const uint32_t delta = ((uint32_t)(sx ^ sm)) & 0xFFu;
+    const uint32_t block = k * 16u;
+    uint32_t TA[16], TB[16], H[16];          // H: the row above, clean (tag 0 = the deletion's)
+    {
+        uint32_t qa[4] = { 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu }, qb[4] = { 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu };
+        if (live) { f2_stripe16(p.P, pbA, MA, block, qa); f2_stripe16(p.P, pbB, MB, block, qb); }
+        #pragma unroll
+        for (int j = 0; j < 16; ++j)
+        {
+            const uint32_t c = block + j;
+            const uint32_t a = (qa[j >> 2] >> (8 * (j & 3))) & 255u, b = (qb[j >> 2] >> (8 * (j & 3))) & 255u;
+            uint32_t wa = 0u, wb = 0u;
+            if (live && c < MA) { dirtyA |= a > 3u; wa = base ^ (delta << (8u * (a & 3u))); }
+            if (live && c < MB) { dirtyB |= b > 3u; wb = base ^ (delta << (8u * (b & 3u))); }
+            TA[j] = wa; TB[j] = wb; H[j] = 0u;
+        }
+    }
+    uint32_t r_one; asm volatile("mov.u32 %0, %1;" : "=r"(r_one) : "r"(p.one));
+    const uint32_t g2 = f2_pack2(-4 * p.ga);                               // -4 G in both halves
+    const uint32_t minus1 = 0u - 0x00010001u;                              // takes the `left` tag off both halves (each half >= 1)
+    const uint32_t cin_mul = k == 0 ? 0u : r_one, col_mul = (k == 0 && p.semi) ? g2 : 0u;
+    const bool last_lane = live && k == p.lanes - 1u;
+    // column 0 of the matrix as lane 0's left input, tagged as a left candidate: 4 h + 1
+    uint32_t carry = 0u, send = 0u, colacc = k == 0 ? 0x00010001u : 0u;
+    const uint16_t* sel_at = my_sel + pad - k;
+    uint32_t* cand_at = my_cand + pad - k;
+    uint2* flow_at = q.flow + ((size_t)task * p.lanes + k) * q.maxN;       // row r of this stripe at flow_at[r]
+
+    auto row_step = [&](const uint32_t t, const bool first)
+    {
+        colacc = f2_imad(col_mul, r_one, colacc);
+        const uint32_t cin = f2_imad(__shfl_up_sync(0xFFFFFFFFu, send, 1), cin_mul, colacc);
+        if (first && t == k)
+        {
+            #pragma unroll
+            for (int j = 0; j < 16; ++j) H[j] = 0u;
+            carry = 0u;
+        }
+        const uint32_t sel = sel_at[t];
+        uint32_t d[16];
+        {
+            uint32_t diag = carry;
+            #pragma unroll
+            for (int j = 0; j < 16; ++j)
+            {
+                d[j] = f2_imad(diag, r_one, f2_prmt(TA[j], TB[j], sel));
+                diag = H[j];
+            }
+        }
+        carry = f2_imad(r_one, minus1, cin);                 // this row's column-0 neighbour, clean: the next row's first diagonal
+        uint32_t left = cin, acc0 = 0u, acc1 = 0u;
+        #pragma unroll
+        for (int j = 0; j < 16; ++j)
+        {
+            const uint32_t hn = __vimax3_s16x2(d[j], H[j], left);
+            left = (hn & 0xFFFCFFFCu) | 0x00010001u;
+            H[j] = f2_imad(r_one, minus1, left);
+            const uint32_t tag = hn & 0x00030003u;
+            if (j < 8) acc0 = f2_imad(acc0, 4u, tag); else acc1 = f2_imad(acc1, 4u, tag);
+        }
+        send = left;
+        if (last_lane) cand_at[t] = send;
+        const uint32_t r = t - k;
+        if (live && t >= k && r < Nmax) flow_at[r] = make_uint2(acc0, acc1);
+    };
+
+    const uint32_t steps = __reduce_max_sync(0xFFFFFFFFu, live ? Nmax + p.lanes - 1 : 0u);
+    const uint32_t t_lo  = min(p.lanes, steps);
+    uint32_t t = 0;
+    for (; t < t_lo; ++t)  row_step(t, true);
+    for (; t < steps; ++t) row_step(t, false);
+    __syncwarp();
+
+    // ---- sinks from the candidate column (4 h + 1, sheared along the rows), as in dpf2_sw_kernel
+    uint32_t bA = 0u, bB = 0u;
+    if (live)
+    {
+        if (p.semi)
+        {
+            for (uint32_t r = k; r < Nmax; r += p.lanes)
+            {
+                const uint32_t c = f2_imad(Nmax - 1u - r, g2, my_cand[r + pad]);
+                if (r < NA) bA = max(bA, ((c & 0xFFFFu) << 16) | r);
+                if (r < NB) bB = max(bB, (c & 0xFFFF0000u) | r);
+            }
+        }
+        else if (k == 0)
+        {
+            if (NA) bA = ((f2_imad(Nmax - NA, g2, my_cand[NA - 1u + pad]) & 0xFFFFu) << 16) | (NA - 1u);
+            if (NB) bB = (f2_imad(Nmax - NB, g2, my_cand[NB - 1u + pad]) & 0xFFFF0000u) | (NB - 1u);
+        }
+    }
+    const uint32_t dmaskA = __ballot_sync(0xFFFFFFFFu, dirtyA), dmaskB = __ballot_sync(0xFFFFFFFFu, dirtyB);
+    const uint32_t gmask = (p.lanes >= 32 ? 0xFFFFFFFFu : ((1u << p.lanes) - 1u)) << gbase;
+    uint32_t wA = 0u, wB = 0u;
+    for (uint32_t dd = 0; dd < p.lanes; ++dd)
+    {
+        const uint32_t src = min(gbase + dd, 31u);
+        wA = max(wA, __shfl_sync(0xFFFFFFFFu, bA, src));
+        wB = max(wB, __shfl_sync(0xFFFFFFFFu, bB, src));
+    }
+    if (!live || k != 0) return;
+
+    #pragma unroll
+    for (int h = 0; h < 2; ++h)
+    {
+        if (h == 1 && !hasB) break;
+        const uint32_t id = h ? idB : idA;
+        const uint32_t M = h ? MB : MA, N = h ? NB : NA;
+        bool dirty = ((h ? dmaskB : dmaskA) & gmask) != 0 || (h ? longB : longA);
+        if (M == 0 || N == 0) dirty = true;
+        const uint32_t pos = p.match > 0 ? (uint32_t)p.match : 0u;
+        if (4ull * ((uint64_t)pos * min(max(MA, MB), Nmax) + 2ull * (uint32_t)(-p.ga) * Nmax + (uint64_t)(uint32_t)(-p.gb) * (16u * p.lanes)) + 8ull >= 32000ull) dirty = true;
+        nvb_alignment a;
+        a.score = NVB_SINK_MIN; a.source_x = a.source_y = a.sink_x = a.sink_y = 0xFFFFFFFFu;
+        if (dirty) f2_mark_dirty(p.worklist, id);
+        else
+        {
+            const uint32_t w = h ? wB : wA;
+            a.score  = (int32_t)(w >> 18) + p.ga * (int32_t)Nmax + p.gb * (int32_t)M;
+            a.sink_x = (w & 0xFFFFu) + 1u;
+            a.sink_y = M;
+        }
+        q.out[id] = a;                // the walk fills in the source
+        q.n_ops[id] = 0;
+    }
+}
+
+// the walk (sw_inl.h:1644-1693 without the windows, then alignment_inl.h:437-450): one thread per pair
+__global__ void __launch_bounds__(256)
+dpf2_sw_tb_walk_kernel(const Full2TbParams q)
+{
+    const uint32_t lp = blockIdx.x * 256 + threadIdx.x;
+    if (lp >= q.n_launch) return;
+    const uint32_t id = q.first + lp;
+    const nvb_alignment a = q.out[id];
+    if (a.sink_x == 0xFFFFFFFFu) return;                       // left to the int32 kernel
+    const uint32_t up = (lp & 1u) * 16u;
+    const uint2* flow = q.flow + (size_t)(lp >> 1) * q.f.lanes * q.maxN;
+    OpSink sink; sink.init(q.ops + (size_t)id * q.ops_stride, q.ops_stride);
+    uint32_t row = a.sink_x, col = a.sink_y;                   // cells still to explain: text rows, pattern columns
+    while (row > 0 && col > 0)
+    {
+        const uint32_t c = col - 1u;
+        const uint2 w = flow[(size_t)(c >> 4) * q.maxN + (row - 1u)];
+        const uint32_t tag = (((c & 8u) ? w.y : w.x) >> (2u * (7u - (c & 7u)) + up)) & 3u;
+        if (tag == 2u)      { --row; --col; sink.push(OP_SUB); }
+        else if (tag == 1u) { --col; sink.push(OP_INS); }
+        else                { --row; sink.push(OP_DEL); }
+    }
+    if (row == 0) for (; col > 0; --col) sink.push(OP_INS);
+    if (!q.f.semi && col == 0) for (; row > 0; --row) sink.push(OP_DEL);
+    sink.finish();
+    q.out[id].source_x = row;
+    q.out[id].source_y = col;
+    q.n_ops[id] = sink.n;
+}
+
+bool dpf2_traceback_supported(const nvb_aligner& a, uint32_t maxM, uint32_t maxN)
+{
+    if (!sw_supported(a) || maxN == 0 || maxM == 0 || maxN > 65535u) return false;
+    const Scheme s = make_scheme(a);
+    if (4 * (s.match - s.ga - s.gb) + 2 > 127 || 4 * (s.mismatch - s.ga - s.gb) + 2 > 127) return false;   // profile bytes
+    uint32_t lanes, tpw, tstride, cstride; size_t smem;
+    return full2_geometry(maxM, maxN, &lanes, &tpw, &tstride, &cstride, &smem);
+}
+
+size_t dpf2_tb_bytes_per_couple(uint32_t maxM, uint32_t maxN) { return (size_t)((maxM + 15u) / 16u) * maxN * sizeof(uint2); }
+
+// pairs [first, first + n) (first even); flow scratch of at least ceil(n / 2) * dpf2_tb_bytes_per_couple bytes, 8-byte aligned
+int dpf2_traceback(nvb_ctx* ctx, const nvb_aligner& a, StrSet P, StrSet T, uint32_t first, uint32_t n, nvb_alignment* out, uint8_t* ops,
+                   uint32_t ops_stride, uint32_t* n_ops, uint32_t maxM, uint32_t maxN, uint8_t* flow, uint32_t* worklist, cudaStream_t st)
+{
+    const Scheme s = make_scheme(a);
+    Full2TbParams q;
+    Full2Params& p = q.f;
+    size_t smem, smem_sel;
+    if (!full2_geometry(maxM, maxN, &p.lanes, &p.tpw, &p.tstride, &p.cstride, &smem, &p.sstride, &smem_sel)) return NVB_ERR_UNSUPPORTED;
+    p.P = P; p.T = T; p.sinks = nullptr; p.worklist = worklist;
+    p.n_pairs = P.count; p.n_tasks = (n + 1) / 2;
+    p.match = s.match; p.mismatch = s.mismatch; p.ga = s.ga; p.gb = s.gb;
+    p.semi = a.type == NVB_SEMI_GLOBAL ? 1 : 0;
+    p.one = 1;
+    p.cstride = maxN + 2u * p.lanes;
+    q.out = out; q.n_ops = n_ops; q.ops = ops; q.ops_stride = ops_stride; q.flow = (uint2*)flow;
+    q.first = first; q.n_launch = n; q.maxM = maxM; q.maxN = maxN;
+    if (NVB_FIRST_ON_DEVICE(ctx))
+        NVB_CUDA(ctx, cudaFuncSetAttribute(dpf2_sw_tb_forward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+    const uint32_t n_warps = (p.n_tasks + p.tpw - 1) / p.tpw;
+    dpf2_sw_tb_forward_kernel<<<(n_warps + DF2_WARPS - 1) / DF2_WARPS, DF2_THREADS, smem_sel, st>>>(q);
+    NVB_LAUNCHED(ctx);
+    dpf2_sw_tb_walk_kernel<<<(n + 255) / 256, 256, 0, st>>>(q);
+    NVB_LAUNCHED(ctx);
+    return NVB_OK;
+}

@@ -32,26 +32,26 @@ int dpg_full_score(nvb_ctx* ctx, const nvb_aligner& a, StrSet P, StrSet T, const
 }
 
 template <bool GOTOH, int TYPE>
-static int tb_t(nvb_ctx* ctx, Scheme sc, StrSet P, StrSet T, uint32_t first, uint32_t n, uint32_t chk,
+static int tb_t(nvb_ctx* ctx, Scheme sc, StrSet P, StrSet T, const uint32_t* list, const uint32_t* d_count, uint32_t first, uint32_t n, uint32_t chk,
                 nvb_alignment* out, uint8_t* ops, uint32_t ops_stride, uint32_t* n_ops, int16_t* temp16,
                 uint8_t* flow, uint32_t maxM, uint32_t maxN, cudaStream_t s)
 {
     if (sc.qm) dpg_full_traceback_kernel<GOTOH, TYPE, true><<<(n + DPG_THREADS - 1) / DPG_THREADS, DPG_THREADS, 0, s>>>(
-        sc, P, T, first, n, chk, out, ops, ops_stride, n_ops, temp16, flow, maxM, maxN);
+        sc, P, T, list, d_count, first, n, chk, out, ops, ops_stride, n_ops, temp16, flow, maxM, maxN);
     else dpg_full_traceback_kernel<GOTOH, TYPE, false><<<(n + DPG_THREADS - 1) / DPG_THREADS, DPG_THREADS, 0, s>>>(
-        sc, P, T, first, n, chk, out, ops, ops_stride, n_ops, temp16, flow, maxM, maxN);
+        sc, P, T, list, d_count, first, n, chk, out, ops, ops_stride, n_ops, temp16, flow, maxM, maxN);
     NVB_LAUNCHED(ctx);
     return NVB_OK;
 }
 
-int dpg_full_traceback(nvb_ctx* ctx, const nvb_aligner& a, StrSet P, StrSet T, uint32_t first, uint32_t n, uint32_t chk,
+int dpg_full_traceback(nvb_ctx* ctx, const nvb_aligner& a, StrSet P, StrSet T, const uint32_t* list, const uint32_t* d_count, uint32_t first, uint32_t n, uint32_t chk,
                        nvb_alignment* out, uint8_t* ops, uint32_t ops_stride, uint32_t* n_ops, int16_t* temp16,
                        uint8_t* flow, uint32_t maxM, uint32_t maxN, cudaStream_t s, const QualDev* qd)
 {
     if (n == 0) return NVB_OK;
     const Scheme sc = make_scheme_q(a, qd);
     const bool g = a.kind == NVB_GOTOH;
-    #define GO(G, TY) return tb_t<G, TY>(ctx, sc, P, T, first, n, chk, out, ops, ops_stride, n_ops, temp16, flow, maxM, maxN, s)
+    #define GO(G, TY) return tb_t<G, TY>(ctx, sc, P, T, list, d_count, first, n, chk, out, ops, ops_stride, n_ops, temp16, flow, maxM, maxN, s)
     switch (a.type)
     {
     case NVB_GLOBAL:      if (g) GO(true, T_GLOBAL); else GO(false, T_GLOBAL);

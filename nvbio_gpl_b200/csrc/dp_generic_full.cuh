@@ -269,14 +269,16 @@ dpg_full_score_kernel(Scheme s, StrSet P, StrSet T, const uint32_t* __restrict__
 // traceback: scratch per pair = 2 columns + 2*nchk*N checkpoints (int16) + N*CHK flow bytes
 template <bool GOTOH, int TYPE, bool QUAL>
 __global__ void __launch_bounds__(DPG_THREADS)
-dpg_full_traceback_kernel(Scheme s, StrSet P, StrSet T, uint32_t first, uint32_t n, uint32_t CHK,
+dpg_full_traceback_kernel(Scheme s, StrSet P, StrSet T, const uint32_t* __restrict__ list, const uint32_t* __restrict__ d_count,
+                          uint32_t first, uint32_t n, uint32_t CHK,
                           nvb_alignment* __restrict__ out, uint8_t* __restrict__ ops, uint32_t ops_stride,
                           uint32_t* __restrict__ n_ops, int16_t* __restrict__ temp16, uint8_t* __restrict__ flow,
                           uint32_t maxM, uint32_t maxN)
 {
     const uint32_t lp = blockIdx.x * DPG_THREADS + threadIdx.x;
     if (lp >= n) return;
-    const uint32_t id = first + lp;
+    if (d_count && first + lp >= *d_count) return;
+    const uint32_t id = list ? list[first + lp] : first + lp;     // list: the pairs a packed kernel left behind
     const uint32_t nchk = (maxM + CHK - 1) / CHK + 1;
     FullDP<GOTOH, TYPE, QUAL> dp;
     dp.s = s; dp.v = make_pair_view(P, T, id, s.quals);

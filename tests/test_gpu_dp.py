@@ -294,3 +294,31 @@ def test_host_scoring_pipelined_and_packed(oracle, bits):
         got = nvb.batch_score_host(a, band, Ph, Po, Th, To, bits=bits)
         want = oracle.banded_score(oa, band, P, Po, T, To) if band else oracle.score(oa, P, Po, T, To)
         assert (got["score"] == want["score"]).all() and (got["x"] == want["x"]).all() and (got["y"] == want["y"]).all(), (kind, ty, band)
+
+
+@pytest.mark.parametrize("kind,scheme", [(po.ED, (0, -1, -1, -1)), (po.SW, (2, -1, -1, -1)), (po.SW, (1, -3, -2, -2)), (po.SW, (3, -2, -4, -1)),
+                                         (po.SW, (0, -1, -1, -2))])
+@pytest.mark.parametrize("ty", [0, 2])
+def test_full_traceback_packed(oracle, kind, scheme, ty):
+    """full-matrix traceback of SW / ED GLOBAL and SEMI_GLOBAL on the tagged packed forward pass + walk: configs[0]-shaped
+    pairs, ragged couples over 1..17 stripes, a few N (those pairs go to the int32 kernel), a scratch that forces several
+    launches, an unaligned op stride"""
+    c = nvb.Context.default(0)
+    c.force_generic(0)
+    rng = np.random.default_rng(hash((kind, scheme, ty, 11)) & 0xFFFF)
+    a, oa = gu.aligner(kind, ty, scheme), po.aligner(kind, ty, scheme)
+    for alpha, m_range, n_of_m, n in ((4, (140, 151), lambda M: 500, 201), (2, (1, 270), lambda M: int(rng.integers(1, 420)), 401),
+                                      (4, (1, 70), lambda M: int(rng.integers(1, 120)), 700)):
+        P, Po, T, To = util.rand_pairs(rng, n, m_range, n_of_m, alpha)
+        if alpha == 4:
+            P = P.copy(); T = T.copy()
+            P[rng.integers(0, len(P), 5)] = 4
+            T[rng.integers(0, len(T), 5)] = rng.integers(4, 7, 5)
+        ps, ts = gu.sset(P, Po), gu.sset(T, To)
+        want = oracle.traceback(oa, 64, P, Po, T, To)
+        got = gu.tb_np(nvb.batch_alignment_traceback(a, 64, ps, ts, ctx=c))
+        assert c.last_paths & 4, "the packed traceback did not run"
+        assert gu.tb_equal(got, want), (alpha, "default")
+        small = torch.empty(int(nvb.lib().nvb_temp_bytes(2, a.c(), 0, 64, ps.max_len, ts.max_len, 128)), dtype=torch.uint8, device=gu.dev())
+        got = gu.tb_np(nvb.batch_alignment_traceback(a, 64, ps, ts, temp=small, ops_stride=ps.max_len + ts.max_len + 3, ctx=c))
+        assert gu.tb_equal(got, want), (alpha, "small scratch")
