@@ -375,9 +375,9 @@ static int batch_traceback_impl(nvb_ctx* ctx, nvb_aligner a, const nvb_quality_s
     const uint32_t* list = nullptr; const uint32_t* d_count = nullptr;
     if (!qd && ctx->force_generic == 0 && dpf2_traceback_supported(a, maxM, maxN))
     {
-        // SW / ED GLOBAL and SEMI_GLOBAL: one tagged packed forward pass + a walk per pair (the directions do not depend on the
+        // SW / ED / Gotoh GLOBAL and SEMI_GLOBAL: one tagged packed forward pass + a walk per pair (the directions do not depend on the
         // checkpoints); the flow of a launch lives in temp. Pairs the packed kernel cannot represent are re-done below.
-        const size_t per_couple = dpf2_tb_bytes_per_couple(maxM, maxN);
+        const size_t per_couple = dpf2_tb_bytes_per_couple(a, maxM, maxN);
         uint8_t* flow = (uint8_t*)(((uintptr_t)temp + 15u) & ~(uintptr_t)15u);
         const size_t avail = temp_bytes > 32 ? temp_bytes - 32 : 0;
         uint64_t fit = 2ull * (avail / per_couple);

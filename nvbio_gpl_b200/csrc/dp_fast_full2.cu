@@ -1001,23 +1001,256 @@ dpf2_sw_tb_walk_kernel(const Full2TbParams q)
     q.n_ops[id] = sink.n;
 }
 
+// ---- Gotoh GLOBAL / SEMI_GLOBAL traceback (gotoh_inl.h:1259-1639): the sweep of dpf2_gotoh_kernel with three tagged maxima per
+// cell, as in dp_band2_tb.cu. Everything is kept times four; HO travels as 4 HO + 1 ("HO1"), E as 4 E + 1, F clean:
+//   F  = max(F, HO1 top)              low bit set = the gap was opened (the extension only wins when strictly larger, gotoh_inl.h:506)
+//   E  = max(E1, HO1 left + 2)        bit 1 set   = opened
+//   h  = max3(HO1 diag + (4 S'' + 1), F, E1)      tags 2 = substitution, 1 = insertion (E), 0 = deletion (F)
+// One nibble per cell and pair: tag | opened-E << 2 | opened-F << 3; one 128-bit word per stripe and row (columns 4 q .. 4 q + 3 in
+// word q, column j at bits 4 (j mod 4), pair B 16 bits up), [couple][stripe][row].
+struct Gotoh2TbParams
+{
+    Full2TbParams t;
+    int32_t       B;              // bias
+};
+
+__global__ void __launch_bounds__(DF2_THREADS, 3)
+dpf2_gotoh_tb_forward_kernel(const Gotoh2TbParams gq)
+{
+    const Full2TbParams& q = gq.t;
+    const Full2Params& p = q.f;
+    extern __shared__ uint32_t s_mem[];
+    const uint32_t lane = threadIdx.x & 31u, wib = threadIdx.x >> 5;
+    const uint32_t warp = blockIdx.x * DF2_WARPS + wib;
+    const uint32_t g = lane / p.lanes, k = lane - g * p.lanes;
+    const uint32_t task = warp * p.tpw + g;
+    const bool live = g < p.tpw && task < p.n_tasks;
+    const uint32_t gbase = g * p.lanes;
+
+    uint32_t idA = 0, idB = 0, pbA = 0, pbB = 0, tbA = 0, tbB = 0, MA = 0, MB = 0, NA = 0, NB = 0;
+    bool hasB = false, longA = false, longB = false;
+    if (live)
+    {
+        idA = q.first + 2 * task; hasB = idA + 1 < q.first + q.n_launch; idB = hasB ? idA + 1 : idA;
+        pbA = p.P.off[idA]; MA = p.P.off[idA + 1] - pbA; pbB = p.P.off[idB]; MB = p.P.off[idB + 1] - pbB;
+        tbA = p.T.off[idA]; NA = p.T.off[idA + 1] - tbA; tbB = p.T.off[idB]; NB = p.T.off[idB + 1] - tbB;
+        longA = MA > q.maxM || NA > q.maxN; longB = MB > q.maxM || NB > q.maxN;
+        if (longA) MA = NA = 0;
+        if (longB) MB = NB = 0;
+    }
+    const uint32_t Nmax = max(NA, NB);
+    bool dirtyA = false, dirtyB = false;
+    uint32_t* my_words = s_mem + ((size_t)wib * p.tpw + (live ? g : 0)) * (p.sstride + p.cstride);
+    uint16_t* my_sel   = (uint16_t*)my_words;
+    uint32_t* my_cand  = my_words + p.sstride;
+    const uint32_t pad = p.lanes - 1u;
+    if (live) f2_pack_selectors(p.T, my_sel, k, p.lanes, pad, tbA, NA, tbB, NB, Nmax, dirtyA, dirtyB);
+    __syncwarp();
+    const uint16_t* sel_at = my_sel + pad - k;
+    uint32_t* cand_at = my_cand + pad - k;
+    uint4* flow_at = (uint4*)q.flow + ((size_t)task * p.lanes + k) * q.maxN;
+
+    const int32_t go = p.ga, ge = p.gb, b = -ge, dd = go - ge, B = gq.B;
+    const int32_t sm = 4 * (p.match - ge - go) + 1, sx = 4 * (p.mismatch - ge - go) + 1;
+    const uint32_t base  = ((uint32_t)sx & 0xFFu) * 0x01010101u;
+    const uint32_t delta = ((uint32_t)(sx ^ sm)) & 0xFFu;
+    const uint32_t block = k * 16u;
+    uint32_t TA[16], TB[16], HO[16], F[16], OH[16];
+    const int32_t d1 = 4 * dd + 1;                                          // clean h -> HO1
+    const uint32_t dfix1 = d1 < 0 ? f2_fix2(d1) : f2_pack2(d1);
+    const uint32_t b2 = f2_pack2(4 * b);
+    const bool capture = live && MA > 0 && k == (MA - 1u) / 16u;
+    {
+        uint32_t qa[4] = { 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu }, qb[4] = { 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu };
+        if (live) { f2_stripe16(p.P, pbA, MA, block, qa); f2_stripe16(p.P, pbB, MB, block, qb); }
+        #pragma unroll
+        for (int j = 0; j < 16; ++j)
+        {
+            const uint32_t c = block + j;
+            const uint32_t a = (qa[j >> 2] >> (8 * (j & 3))) & 255u, bb = (qb[j >> 2] >> (8 * (j & 3))) & 255u;
+            uint32_t wa = 0x01010101u, wb = 0x01010101u;                    // past the pattern: S'' = 0, still the diagonal's tag
+            if (live && c < MA) { dirtyA |= a > 3u; wa = base ^ (delta << (8u * (a & 3u))); }
+            if (live && c < MB) { dirtyB |= bb > 3u; wb = base ^ (delta << (8u * (bb & 3u))); }
+            TA[j] = wa; TB[j] = wb;
+            OH[j] = (capture && (uint32_t)j == ((MA - 1u) & 15u)) ? 1u : 0u;
+        }
+    }
+    uint32_t r_one; asm volatile("mov.u32 %0, %1;" : "=r"(r_one) : "r"(p.one));
+    const uint32_t ho_row0 = f2_pack2(4 * (2 * dd + B) + 1), ho_origin = f2_pack2(4 * (dd + B) + 1);
+    const uint32_t cin_mul = k == 0 ? 0u : r_one;
+    const uint32_t col_mul = (k == 0 && p.semi) ? b2 : 0u;
+    const uint32_t col_add = k == 0 ? (p.semi ? ho_origin : ho_row0) : 0u;
+    uint32_t carry = 0u, send_h = 0u, send_e = 0u, colacc = col_add;
+
+    auto reset = [&]()
+    {
+        #pragma unroll
+        for (int j = 0; j < 16; ++j) { HO[j] = ho_row0; F[j] = 0u; }
+        carry = k == 0 ? ho_origin : ho_row0;
+    };
+    reset();
+
+    auto row_step = [&](const uint32_t t, const bool first)
+    {
+        colacc = f2_imad(col_mul, r_one, colacc);
+        const uint32_t hin = f2_imad(__shfl_up_sync(0xFFFFFFFFu, send_h, 1), cin_mul, colacc);
+        const uint32_t ein = f2_imad(__shfl_up_sync(0xFFFFFFFFu, send_e, 1), cin_mul, 0u);
+        if (first && t == k) reset();
+        const uint32_t sel = sel_at[t];
+        uint32_t left = hin, e = ein, diag = carry, cap = 0u;
+        uint32_t acc[4] = { 0u, 0u, 0u, 0u };
+        carry = hin;
+        #pragma unroll
+        for (int j = 0; j < 16; ++j)
+        {
+            const uint32_t top = HO[j];
+            const uint32_t ft = __vmaxs2(F[j], top);
+            const uint32_t xF = ft & 0x00010001u;
+            const uint32_t fn = ft - xF;
+            const uint32_t dg = f2_imad(diag, r_one, f2_prmt(TA[j], TB[j], sel));
+            const uint32_t et = __vmaxs2(e, left + 0x00020002u);
+            const uint32_t xE = et & 0x00020002u;
+            e = et - xE;
+            const uint32_t h = __vimax3_s16x2(dg, fn, e);
+            const uint32_t th = h & 0x00030003u;
+            F[j] = fn; diag = top;
+            left = f2_imad(h - th, r_one, dfix1);
+            HO[j] = left;
+            cap = f2_imad(left, OH[j], cap);
+            const uint32_t m = 1u << (4 * (j & 3));
+            acc[j >> 2] = f2_imad(th, m, f2_imad(xE, 2u * m, f2_imad(xF, 8u * m, acc[j >> 2])));
+        }
+        send_h = left; send_e = e;
+        if (capture) cand_at[t] = cap;
+        const uint32_t r = t - k;
+        if (live && t >= k && r < Nmax) flow_at[r] = make_uint4(acc[0], acc[1], acc[2], acc[3]);
+    };
+
+    const uint32_t steps = __reduce_max_sync(0xFFFFFFFFu, live ? Nmax + p.lanes - 1 : 0u);
+    const uint32_t t_lo  = min(p.lanes, steps);
+    uint32_t t = 0;
+    for (; t < t_lo; ++t)  row_step(t, true);
+    for (; t < steps; ++t) row_step(t, false);
+    __syncwarp();
+
+    uint32_t bA = 0u, bB = 0u;
+    if (live)
+    {
+        if (p.semi)
+        {
+            for (uint32_t r = k; r < Nmax; r += p.lanes)
+            {
+                const uint32_t c = f2_imad(Nmax - 1u - r, b2, my_cand[r + pad]);
+                if (r < NA) bA = max(bA, ((c & 0xFFFFu) << 16) | r);
+                if (r < NB) bB = max(bB, (c & 0xFFFF0000u) | r);
+            }
+        }
+        else if (k == 0)
+        {
+            if (NA) bA = ((f2_imad(Nmax - NA, b2, my_cand[NA - 1u + pad]) & 0xFFFFu) << 16) | (NA - 1u);
+            if (NB) bB = (f2_imad(Nmax - NB, b2, my_cand[NB - 1u + pad]) & 0xFFFF0000u) | (NB - 1u);
+        }
+    }
+    const uint32_t dmaskA = __ballot_sync(0xFFFFFFFFu, dirtyA), dmaskB = __ballot_sync(0xFFFFFFFFu, dirtyB);
+    const uint32_t gmask = (p.lanes >= 32 ? 0xFFFFFFFFu : ((1u << p.lanes) - 1u)) << gbase;
+    uint32_t wA = 0u, wB = 0u;
+    for (uint32_t l = 0; l < p.lanes; ++l)
+    {
+        const uint32_t src = min(gbase + l, 31u);
+        wA = max(wA, __shfl_sync(0xFFFFFFFFu, bA, src));
+        wB = max(wB, __shfl_sync(0xFFFFFFFFu, bB, src));
+    }
+    if (!live || k != 0) return;
+
+    #pragma unroll
+    for (int h = 0; h < 2; ++h)
+    {
+        if (h == 1 && !hasB) break;
+        const uint32_t id = h ? idB : idA;
+        const uint32_t M = h ? MB : MA, N = h ? NB : NA;
+        bool dirty = ((h ? dmaskB : dmaskA) & gmask) != 0 || longA || longB;
+        if (M == 0 || N == 0 || (hasB && MA != MB)) dirty = true;
+        const uint32_t pos = p.match > 0 ? (uint32_t)p.match : 0u;
+        if (4ull * ((uint64_t)pos * min(M, Nmax) + (uint64_t)(uint32_t)b * (2ull * Nmax + 16u * p.lanes) + (uint32_t)B) + 8ull >= 32000ull) dirty = true;
+        nvb_alignment a;
+        a.score = NVB_SINK_MIN; a.source_x = a.source_y = a.sink_x = a.sink_y = 0xFFFFFFFFu;
+        if (dirty) f2_mark_dirty(p.worklist, id);
+        else
+        {
+            const uint32_t w = h ? wB : wA;
+            a.score  = (int32_t)(w >> 18) - dd - B + ge * (int32_t)(Nmax + M);
+            a.sink_x = (w & 0xFFFFu) + 1u;
+            a.sink_y = M;
+        }
+        q.out[id] = a;
+        q.n_ops[id] = 0;
+    }
+}
+
+// the Gotoh walk (gotoh_inl.h:1573-1639 without the windows, then alignment_inl.h:437-450)
+__global__ void __launch_bounds__(256)
+dpf2_gotoh_tb_walk_kernel(const Full2TbParams q)
+{
+    const uint32_t lp = blockIdx.x * 256 + threadIdx.x;
+    if (lp >= q.n_launch) return;
+    const uint32_t id = q.first + lp;
+    const nvb_alignment a = q.out[id];
+    if (a.sink_x == 0xFFFFFFFFu) return;
+    const uint32_t up = (lp & 1u) * 16u;
+    const uint4* flow = (const uint4*)q.flow + (size_t)(lp >> 1) * q.f.lanes * q.maxN;
+    OpSink sink; sink.init(q.ops + (size_t)id * q.ops_stride, q.ops_stride);
+    uint32_t row = a.sink_x, col = a.sink_y, state = ST_H;
+    while (row > 0 && col > 0)
+    {
+        const uint32_t c = col - 1u;
+        const uint4 w = flow[(size_t)(c >> 4) * q.maxN + (row - 1u)];
+        const uint32_t word = (c & 8u) ? ((c & 4u) ? w.w : w.z) : ((c & 4u) ? w.y : w.x);
+        const uint32_t nib = (word >> (4u * (c & 3u) + up)) & 15u;
+        if (state == ST_E)      { if (nib & 4u) state = ST_H; --col; sink.push(OP_INS); }
+        else if (state == ST_F) { if (nib & 8u) state = ST_H; --row; sink.push(OP_DEL); }
+        else
+        {
+            const uint32_t tag = nib & 3u;
+            if (tag == 1u)      state = ST_E;
+            else if (tag == 0u) state = ST_F;
+            else                { --row; --col; sink.push(OP_SUB); }
+        }
+    }
+    if (row == 0) for (; col > 0; --col) sink.push(OP_INS);
+    if (!q.f.semi && col == 0) for (; row > 0; --row) sink.push(OP_DEL);
+    sink.finish();
+    q.out[id].source_x = row;
+    q.out[id].source_y = col;
+    q.n_ops[id] = sink.n;
+}
+
 bool dpf2_traceback_supported(const nvb_aligner& a, uint32_t maxM, uint32_t maxN)
 {
-    if (!sw_supported(a) || maxN == 0 || maxM == 0 || maxN > 65535u) return false;
+    if (maxN == 0 || maxM == 0 || maxN > 65535u) return false;
     const Scheme s = make_scheme(a);
-    if (4 * (s.match - s.ga - s.gb) + 2 > 127 || 4 * (s.mismatch - s.ga - s.gb) + 2 > 127) return false;   // profile bytes
+    if (sw_supported(a))
+    {
+        if (4 * (s.match - s.ga - s.gb) + 2 > 127 || 4 * (s.mismatch - s.ga - s.gb) + 2 > 127) return false;   // profile bytes
+    }
+    else if (gotoh_supported(a) && a.type != NVB_LOCAL)
+    {
+        if (4 * (s.match - s.ga - s.gb) + 1 > 127 || 4 * (s.mismatch - s.ga - s.gb) + 1 > 127) return false;
+    }
+    else return false;
     uint32_t lanes, tpw, tstride, cstride; size_t smem;
     return full2_geometry(maxM, maxN, &lanes, &tpw, &tstride, &cstride, &smem);
 }
 
-size_t dpf2_tb_bytes_per_couple(uint32_t maxM, uint32_t maxN) { return (size_t)((maxM + 15u) / 16u) * maxN * sizeof(uint2); }
+size_t dpf2_tb_bytes_per_couple(const nvb_aligner& a, uint32_t maxM, uint32_t maxN)
+{ return (size_t)((maxM + 15u) / 16u) * maxN * (a.kind == NVB_GOTOH ? sizeof(uint4) : sizeof(uint2)); }
 
-// pairs [first, first + n) (first even); flow scratch of at least ceil(n / 2) * dpf2_tb_bytes_per_couple bytes, 8-byte aligned
+// pairs [first, first + n) (first even); flow scratch of at least ceil(n / 2) * dpf2_tb_bytes_per_couple bytes, 16-byte aligned
 int dpf2_traceback(nvb_ctx* ctx, const nvb_aligner& a, StrSet P, StrSet T, uint32_t first, uint32_t n, nvb_alignment* out, uint8_t* ops,
                    uint32_t ops_stride, uint32_t* n_ops, uint32_t maxM, uint32_t maxN, uint8_t* flow, uint32_t* worklist, cudaStream_t st)
 {
     const Scheme s = make_scheme(a);
-    Full2TbParams q;
+    Gotoh2TbParams gq;
+    Full2TbParams& q = gq.t;
     Full2Params& p = q.f;
     size_t smem, smem_sel;
     if (!full2_geometry(maxM, maxN, &p.lanes, &p.tpw, &p.tstride, &p.cstride, &smem, &p.sstride, &smem_sel)) return NVB_ERR_UNSUPPORTED;
@@ -1030,11 +1263,25 @@ int dpf2_traceback(nvb_ctx* ctx, const nvb_aligner& a, StrSet P, StrSet T, uint3
     q.out = out; q.n_ops = n_ops; q.ops = ops; q.ops_stride = ops_stride; q.flow = (uint2*)flow;
     q.first = first; q.n_launch = n; q.maxM = maxM; q.maxN = maxN;
     if (NVB_FIRST_ON_DEVICE(ctx))
+    {
         NVB_CUDA(ctx, cudaFuncSetAttribute(dpf2_sw_tb_forward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+        NVB_CUDA(ctx, cudaFuncSetAttribute(dpf2_gotoh_tb_forward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+    }
     const uint32_t n_warps = (p.n_tasks + p.tpw - 1) / p.tpw;
-    dpf2_sw_tb_forward_kernel<<<(n_warps + DF2_WARPS - 1) / DF2_WARPS, DF2_THREADS, smem_sel, st>>>(q);
-    NVB_LAUNCHED(ctx);
-    dpf2_sw_tb_walk_kernel<<<(n + 255) / 256, 256, 0, st>>>(q);
+    const uint32_t grid = (n_warps + DF2_WARPS - 1) / DF2_WARPS;
+    if (a.kind == NVB_GOTOH)
+    {
+        gq.B = 3 * (-(s.ga - s.gb)) + 4;
+        dpf2_gotoh_tb_forward_kernel<<<grid, DF2_THREADS, smem_sel, st>>>(gq);
+        NVB_LAUNCHED(ctx);
+        dpf2_gotoh_tb_walk_kernel<<<(n + 255) / 256, 256, 0, st>>>(q);
+    }
+    else
+    {
+        dpf2_sw_tb_forward_kernel<<<grid, DF2_THREADS, smem_sel, st>>>(q);
+        NVB_LAUNCHED(ctx);
+        dpf2_sw_tb_walk_kernel<<<(n + 255) / 256, 256, 0, st>>>(q);
+    }
     NVB_LAUNCHED(ctx);
     return NVB_OK;
 }

@@ -297,17 +297,19 @@ def test_host_scoring_pipelined_and_packed(oracle, bits):
 
 
 @pytest.mark.parametrize("kind,scheme", [(po.ED, (0, -1, -1, -1)), (po.SW, (2, -1, -1, -1)), (po.SW, (1, -3, -2, -2)), (po.SW, (3, -2, -4, -1)),
-                                         (po.SW, (0, -1, -1, -2))])
+                                         (po.SW, (0, -1, -1, -2)), (po.GOTOH, (2, -2, -5, -3)), (po.GOTOH, (0, -5, -8, -3)), (po.GOTOH, (1, -1, -1, -1)),
+                                         (po.GOTOH, (2, -1, -2, -1)), (po.GOTOH, (2, -6, -5, -3))])
 @pytest.mark.parametrize("ty", [0, 2])
 def test_full_traceback_packed(oracle, kind, scheme, ty):
-    """full-matrix traceback of SW / ED GLOBAL and SEMI_GLOBAL on the tagged packed forward pass + walk: configs[0]-shaped
-    pairs, ragged couples over 1..17 stripes, a few N (those pairs go to the int32 kernel), a scratch that forces several
-    launches, an unaligned op stride"""
+    """full-matrix traceback of SW / ED / Gotoh GLOBAL and SEMI_GLOBAL on the tagged packed forward pass + walk: configs[0]-shaped
+    pairs, couples of equal pattern length (the ones the Gotoh kernel keeps), ragged couples over 1..17 stripes, a few N (those
+    pairs go to the int32 kernel), a scratch that forces several launches, an unaligned op stride"""
     c = nvb.Context.default(0)
     c.force_generic(0)
     rng = np.random.default_rng(hash((kind, scheme, ty, 11)) & 0xFFFF)
     a, oa = gu.aligner(kind, ty, scheme), po.aligner(kind, ty, scheme)
-    for alpha, m_range, n_of_m, n in ((4, (140, 151), lambda M: 500, 201), (2, (1, 270), lambda M: int(rng.integers(1, 420)), 401),
+    for alpha, m_range, n_of_m, n in ((4, (140, 151), lambda M: 500, 201), (4, (150, 151), lambda M: int(rng.integers(250, 500)), 301),
+                                      (2, (100, 101), lambda M: int(rng.integers(1, 300)), 301), (2, (1, 270), lambda M: int(rng.integers(1, 420)), 401),
                                       (4, (1, 70), lambda M: int(rng.integers(1, 120)), 700)):
         P, Po, T, To = util.rand_pairs(rng, n, m_range, n_of_m, alpha)
         if alpha == 4:
