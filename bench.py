@@ -1006,7 +1006,8 @@ def run_b200(args):
             for name, a, okind, osc in (("sw_local", nvb.SmithWatermanAligner(nvb.LOCAL, 2, -1, -1, -1), "SW", (2, -1, -1, -1)),
                                         ("gotoh_semi_global", nvb.GotohAligner(nvb.SEMI_GLOBAL, 2, -2, -5, -3), "GOTOH", (2, -2, -5, -3)),
                                         ("sw_semi_global", nvb.SmithWatermanAligner(nvb.SEMI_GLOBAL, 2, -1, -1, -1), "SW", (2, -1, -1, -1)),
-                                        ("ed_global", nvb.EditDistanceAligner(nvb.GLOBAL), "ED", (0, -1, -1, -1))):
+                                        ("ed_global", nvb.EditDistanceAligner(nvb.GLOBAL), "ED", (0, -1, -1, -1)),
+                                        ("gotoh_local", nvb.GotohAligner(nvb.LOCAL, 2, -2, -5, -3), "GOTOH", (2, -2, -5, -3))):
                 ttemp = torch.empty(int(nvb.lib().nvb_temp_bytes(2, a.c(), 0, 64, M, N, nt)), dtype=torch.uint8, device=dev)
                 bufs = {}
                 def fn():

@@ -41,7 +41,7 @@ struct Full2Params
     uint32_t       one;
 };
 
-__device__ __forceinline__ uint32_t f2_pack2(int32_t v) { return ((uint32_t)v & 0xFFFFu) * 0x00010001u; }
+__host__ __device__ __forceinline__ uint32_t f2_pack2(int32_t v) { return ((uint32_t)v & 0xFFFFu) * 0x00010001u; }
 __device__ __forceinline__ uint32_t f2_prmt(uint32_t a, uint32_t b, uint32_t s)
 { uint32_t d; asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(s)); return d; }
 __device__ __forceinline__ uint32_t f2_imad(uint32_t a, uint32_t b, uint32_t c)
@@ -322,7 +322,7 @@ dpf2_sw_kernel(const Full2Params p)
 // maximum each, and shear the coordinates by ge so that extending costs nothing.
 // ---------------------------------------------------------------------------------------------------------------
 // addend that adds g <= 0 to both halves of a register whose low half is >= -g (the low half's carry completes the high half's g - 1)
-__device__ __forceinline__ uint32_t f2_fix2(int32_t g) { return g == 0 ? 0u : ((((uint32_t)(g - 1) & 0xFFFFu) << 16) | ((uint32_t)g & 0xFFFFu)); }
+__host__ __device__ __forceinline__ uint32_t f2_fix2(int32_t g) { return g == 0 ? 0u : ((((uint32_t)(g - 1) & 0xFFFFu) << 16) | ((uint32_t)g & 0xFFFFu)); }
 
 struct Gotoh2Params
 {
@@ -989,12 +989,16 @@ dpf2_sw_tb_walk_kernel(const Full2TbParams q)
         const uint32_t c = col - 1u;
         const uint2 w = flow[(size_t)(c >> 4) * q.maxN + (row - 1u)];
         const uint32_t tag = (((c & 8u) ? w.y : w.x) >> (2u * (7u - (c & 7u)) + up)) & 3u;
+        if (tag == 3u)      break;                             // LOCAL: a cell of score 0 is the source
         if (tag == 2u)      { --row; --col; sink.push(OP_SUB); }
         else if (tag == 1u) { --col; sink.push(OP_INS); }
         else                { --row; sink.push(OP_DEL); }
     }
-    if (row == 0) for (; col > 0; --col) sink.push(OP_INS);
-    if (!q.f.semi && col == 0) for (; row > 0; --row) sink.push(OP_DEL);
+    if (q.f.semi != 2)                                         // GLOBAL / SEMI_GLOBAL: the rest of the pattern, GLOBAL: and of the text
+    {
+        if (row == 0) for (; col > 0; --col) sink.push(OP_INS);
+        if (!q.f.semi && col == 0) for (; row > 0; --row) sink.push(OP_DEL);
+    }
     sink.finish();
     q.out[id].source_x = row;
     q.out[id].source_y = col;
@@ -1211,17 +1215,385 @@ dpf2_gotoh_tb_walk_kernel(const Full2TbParams q)
         else
         {
             const uint32_t tag = nib & 3u;
+            if (tag == 3u)      break;                         // LOCAL: a cell of score 0 is the source (gotoh_inl.h:1597-1604)
             if (tag == 1u)      state = ST_E;
             else if (tag == 0u) state = ST_F;
             else                { --row; --col; sink.push(OP_SUB); }
         }
     }
-    if (row == 0) for (; col > 0; --col) sink.push(OP_INS);
-    if (!q.f.semi && col == 0) for (; row > 0; --row) sink.push(OP_DEL);
+    if (q.f.semi != 2)
+    {
+        if (row == 0) for (; col > 0; --col) sink.push(OP_INS);
+        if (!q.f.semi && col == 0) for (; row > 0; --row) sink.push(OP_DEL);
+    }
     sink.finish();
     q.out[id].source_x = row;
     q.out[id].source_y = col;
     q.n_ops[id] = sink.n;
+}
+
+// ---- Smith-Waterman / edit distance LOCAL traceback: the sweep of dpf_full_sw_local_kernel (dp_fast_full.cu: sheared along the
+// columns of a stripe, biased by B, arg-max keys score << 4 | column) on values kept times four, with the move in the two low bits:
+//   h = max3( left | 1, max(diag + (4 (S + b) + 2), top + 4 G), floor_j | 3 )
+// The floor carries the highest tag: a cell whose score is 0 is a SINK whatever else ties with it (sw_inl.h:1376). The clean value
+// (4 h') times four is the scoring kernel's key, so the sink comes out of the same pass.
+struct Local2TbParams
+{
+    Full2TbParams t;
+    uint32_t      FL[16];         // floor of stripe column j, tagged: pack2(4 (B + b j) + 3)
+    uint32_t      CJ[16];         // key addend, as in dp_fast_full.cu
+    uint32_t      unshear;        // fix2(-64 b)
+    int32_t       B;
+};
+
+__global__ void __launch_bounds__(DF2_THREADS, 4)
+dpf2_sw_local_tb_forward_kernel(const Local2TbParams lq)
+{
+    const Full2TbParams& q = lq.t;
+    const Full2Params& p = q.f;
+    extern __shared__ uint32_t s_mem[];
+    const uint32_t lane = threadIdx.x & 31u, wib = threadIdx.x >> 5;
+    const uint32_t warp = blockIdx.x * DF2_WARPS + wib;
+    const uint32_t g = lane / p.lanes, k = lane - g * p.lanes;
+    const uint32_t task = warp * p.tpw + g;
+    const bool live = g < p.tpw && task < p.n_tasks;
+    const uint32_t gbase = g * p.lanes;
+
+    uint32_t idA = 0, idB = 0, pbA = 0, pbB = 0, tbA = 0, tbB = 0, MA = 0, MB = 0, NA = 0, NB = 0;
+    bool hasB = false, longA = false, longB = false;
+    if (live)
+    {
+        idA = q.first + 2 * task; hasB = idA + 1 < q.first + q.n_launch; idB = hasB ? idA + 1 : idA;
+        pbA = p.P.off[idA]; MA = p.P.off[idA + 1] - pbA; pbB = p.P.off[idB]; MB = p.P.off[idB + 1] - pbB;
+        tbA = p.T.off[idA]; NA = p.T.off[idA + 1] - tbA; tbB = p.T.off[idB]; NB = p.T.off[idB + 1] - tbB;
+        longA = MA > q.maxM || NA > q.maxN; longB = MB > q.maxM || NB > q.maxN;
+        if (longA) MA = NA = 0;
+        if (longB) MB = NB = 0;
+    }
+    const uint32_t Nmax = max(NA, NB);
+    bool dirtyA = false, dirtyB = false;
+    uint16_t* my_sel = (uint16_t*)(s_mem + ((size_t)wib * p.tpw + (live ? g : 0)) * p.sstride);
+    const uint32_t pad = p.lanes - 1u;
+    if (live) f2_pack_selectors(p.T, my_sel, k, p.lanes, pad, tbA, NA, tbB, NB, Nmax, dirtyA, dirtyB);
+    __syncwarp();
+    const uint16_t* sel_at = my_sel + pad - k;
+    uint2* flow_at = q.flow + ((size_t)task * p.lanes + k) * q.maxN;
+
+    const int32_t G = p.ga, I = p.gb, B = lq.B;
+    const int32_t sm = 4 * (p.match - I) + 2, sx = 4 * (p.mismatch - I) + 2;
+    const uint32_t base  = ((uint32_t)sx & 0xFFu) * 0x01010101u;
+    const uint32_t delta = ((uint32_t)(sx ^ sm)) & 0xFFu;
+    const uint32_t block = k * 16u;
+    const uint32_t Gf = f2_fix2(4 * G);
+    uint32_t TA[16], TB[16], H[16];          // H: the row above, clean
+    {
+        uint32_t qa[4] = { 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu }, qb[4] = { 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu };
+        if (live) { f2_stripe16(p.P, pbA, MA, block, qa); f2_stripe16(p.P, pbB, MB, block, qb); }
+        #pragma unroll
+        for (int j = 0; j < 16; ++j)
+        {
+            const uint32_t c = block + j;
+            const uint32_t a = (qa[j >> 2] >> (8 * (j & 3))) & 255u, bb = (qb[j >> 2] >> (8 * (j & 3))) & 255u;
+            uint32_t wa = 0x80808080u, wb = 0x80808080u;       // columns past the pattern: -128
+            if (live && c < MA) { dirtyA |= a > 3u; wa = base ^ (delta << (8u * (a & 3u))); }
+            if (live && c < MB) { dirtyB |= bb > 3u; wb = base ^ (delta << (8u * (bb & 3u))); }
+            TA[j] = wa; TB[j] = wb; H[j] = lq.FL[j] - 0x00030003u;
+        }
+    }
+    const uint32_t smask = (block < MA ? 0x0000FFFFu : 0u) | (block < MB ? 0xFFFF0000u : 0u);
+    uint32_t bestkey = f2_pack2(B) << 4, bestrow = 0u;
+    uint32_t r_one, r_four, r_m1;
+    asm volatile("mov.u32 %0, %1;" : "=r"(r_one) : "r"(p.one));
+    asm volatile("mov.u32 %0, %1;" : "=r"(r_four) : "r"(4u * p.one));
+    asm volatile("mov.u32 %0, %1;" : "=r"(r_m1) : "r"(0u - p.one));
+    const uint32_t minus1 = 0u - 0x00010001u;
+    const uint32_t zero_in = f2_pack2(4 * (B + I) + 1);         // H = 0 of the column left of the stripe, tagged as a left candidate
+    uint32_t carry = zero_in - 0x00010001u, send = zero_in;
+    const uint32_t cin_mul = k == 0 ? 0u : r_one, cin_add = k == 0 ? zero_in : lq.unshear;
+
+    auto row_step = [&](const uint32_t t, const bool masked, const bool first)
+    {
+        const uint32_t cin = f2_imad(__shfl_up_sync(0xFFFFFFFFu, send, 1), cin_mul, cin_add);
+        const uint32_t i = t - k;
+        if (first && t == k)
+        {
+            #pragma unroll
+            for (int j = 0; j < 16; ++j) H[j] = lq.FL[j] - 0x00030003u;
+            carry = zero_in - 0x00010001u;
+        }
+        const uint32_t sel = sel_at[t];
+        uint32_t v[16];
+        {
+            uint32_t diag = carry;
+            #pragma unroll
+            for (int j = 0; j < 16; ++j)
+            {
+                const uint32_t S = f2_prmt(TA[j], TB[j], sel);
+                const uint32_t u = f2_imad(H[j], r_one, Gf);
+                v[j] = __viaddmax_s16x2(diag, S, u);
+                diag = H[j];
+            }
+        }
+        carry = f2_imad(r_one, minus1, cin);
+        const uint32_t kb = f2_imad(bestkey & 0xFFF0FFF0u, r_one, 0xFFFEFFFFu);
+        uint32_t acc = kb, left = cin, a0 = 0u, a1 = 0u;
+        #pragma unroll
+        for (int j = 0; j < 16; j += 2)
+        {
+            const uint32_t h0 = __vimax3_s16x2(left, v[j], lq.FL[j]);
+            const uint32_t t0 = h0 & 0x00030003u;
+            const uint32_t c0 = h0 - t0;
+            const uint32_t h1 = __vimax3_s16x2((h0 & 0xFFFCFFFCu) | 0x00010001u, v[j + 1], lq.FL[j + 1]);
+            const uint32_t t1 = h1 & 0x00030003u;
+            const uint32_t c1 = h1 - t1;
+            H[j] = c0; H[j + 1] = c1; left = (h1 & 0xFFFCFFFCu) | 0x00010001u;
+            acc = __vimax3_s16x2(acc, f2_imad(c0, r_four, lq.CJ[j]), f2_imad(c1, r_four, lq.CJ[j + 1]));
+            if (j < 8) a0 = f2_imad(f2_imad(a0, 4u, t0), 4u, t1); else a1 = f2_imad(f2_imad(a1, 4u, t0), 4u, t1);
+        }
+        send = left;
+        const uint32_t d = f2_imad(kb, r_m1, acc);
+        const uint32_t sgn = f2_imad(d, r_one, 0x7FFF7FFFu);
+        uint32_t m = f2_prmt(sgn, sgn, 0xBB99u) & smask;
+        if (masked) m &= (i < NA ? 0x0000FFFFu : 0u) | (i < NB ? 0xFFFF0000u : 0u);
+        bestkey = (acc & m) | (bestkey & ~m);
+        bestrow = (f2_imad(i, 0x00010001u, 0u) & m) | (bestrow & ~m);
+        if (live && t >= k && i < Nmax) flow_at[i] = make_uint2(a0, a1);
+    };
+
+    const uint32_t steps = __reduce_max_sync(0xFFFFFFFFu, live ? Nmax + p.lanes - 1 : 0u);
+    const uint32_t Nmin  = __reduce_min_sync(0xFFFFFFFFu, live ? min(NA, hasB ? NB : NA) : 0xFFFFFFFFu);
+    const uint32_t t_lo  = min(p.lanes, steps);
+    const uint32_t t_hi  = max(t_lo, min(Nmin, steps));
+    uint32_t t = 0;
+    for (; t < t_lo; ++t)  row_step(t, true, true);
+    for (; t < t_hi; ++t)  row_step(t, false, false);
+    for (; t < steps; ++t) row_step(t, true, false);
+
+    const uint32_t dmaskA = __ballot_sync(0xFFFFFFFFu, dirtyA), dmaskB = __ballot_sync(0xFFFFFFFFu, dirtyB);
+    const uint32_t gmask = (p.lanes >= 32 ? 0xFFFFFFFFu : ((1u << p.lanes) - 1u)) << gbase;
+    uint32_t wkA = 0, wkB = 0, wlaneA = 0, wlaneB = 0;
+    for (uint32_t l = 0; l < p.lanes; ++l)
+    {
+        const uint32_t src = min(gbase + l, 31u);
+        const uint32_t ok = __shfl_sync(0xFFFFFFFFu, bestkey, src);
+        const uint32_t sA = (ok & 0xFFFFu) >> 4, sB = ok >> 20;
+        if (sA >= (wkA >> 4)) { wkA = ok & 0xFFFFu; wlaneA = l; }
+        if (sB >= (wkB >> 4)) { wkB = ok >> 16; wlaneB = l; }
+    }
+    const uint32_t rowsA = __shfl_sync(0xFFFFFFFFu, bestrow, min(gbase + wlaneA, 31u));
+    const uint32_t rowsB = __shfl_sync(0xFFFFFFFFu, bestrow, min(gbase + wlaneB, 31u));
+    if (!live || k != 0) return;
+
+    #pragma unroll
+    for (int h = 0; h < 2; ++h)
+    {
+        if (h == 1 && !hasB) break;
+        const uint32_t id = h ? idB : idA;
+        const uint32_t M = h ? MB : MA, N = h ? NB : NA;
+        bool dirty = ((h ? dmaskB : dmaskA) & gmask) != 0 || (h ? longB : longA) || M == 0 || N == 0;
+        if (p.match > 0 && (uint64_t)p.match * min(M, Nmax) + (uint32_t)B + 15u * (uint32_t)(-I) >= 2047u) dirty = true;
+        nvb_alignment a;
+        a.score = NVB_SINK_MIN; a.source_x = a.source_y = a.sink_x = a.sink_y = 0xFFFFFFFFu;
+        if (dirty) f2_mark_dirty(p.worklist, id);
+        else
+        {
+            const uint32_t wk = h ? wkB : wkA;
+            const uint32_t stripe = h ? wlaneB : wlaneA;
+            const uint32_t row = h ? (rowsB >> 16) : (rowsA & 0xFFFFu);
+            const int32_t score = (int32_t)(wk >> 4) - B;
+            if (score <= 0) { a.score = 0; a.sink_x = N; a.sink_y = M; }          // all cells tie at 0: the last one visited
+            else { a.score = score; a.sink_x = row + 1u; a.sink_y = stripe * 16u + (wk & 15u) + 1u; }
+        }
+        q.out[id] = a;
+        q.n_ops[id] = 0;
+    }
+}
+
+// ---- Gotoh LOCAL traceback: the sweep of dpf2_gotoh_local_kernel (sheared along the columns of a stripe, biased, keys compared per
+// 8-column stripe of the reference) with the three tagged maxima of dpf2_gotoh_tb_forward_kernel and the floor tagged 3 (SINK).
+struct GotohLocal2TbParams
+{
+    Full2TbParams t;
+    uint32_t      FL[16];         // pack2(4 (B + b j) + 3)
+    uint32_t      CJ[16];
+    uint32_t      unshear;        // fix2(-64 b)
+    int32_t       B;
+};
+
+__global__ void __launch_bounds__(DF2_THREADS, 3)
+dpf2_gotoh_local_tb_forward_kernel(const GotohLocal2TbParams lq)
+{
+    const Full2TbParams& q = lq.t;
+    const Full2Params& p = q.f;
+    extern __shared__ uint32_t s_mem[];
+    const uint32_t lane = threadIdx.x & 31u, wib = threadIdx.x >> 5;
+    const uint32_t warp = blockIdx.x * DF2_WARPS + wib;
+    const uint32_t g = lane / p.lanes, k = lane - g * p.lanes;
+    const uint32_t task = warp * p.tpw + g;
+    const bool live = g < p.tpw && task < p.n_tasks;
+    const uint32_t gbase = g * p.lanes;
+
+    uint32_t idA = 0, idB = 0, pbA = 0, pbB = 0, tbA = 0, tbB = 0, MA = 0, MB = 0, NA = 0, NB = 0;
+    bool hasB = false, longA = false, longB = false;
+    if (live)
+    {
+        idA = q.first + 2 * task; hasB = idA + 1 < q.first + q.n_launch; idB = hasB ? idA + 1 : idA;
+        pbA = p.P.off[idA]; MA = p.P.off[idA + 1] - pbA; pbB = p.P.off[idB]; MB = p.P.off[idB + 1] - pbB;
+        tbA = p.T.off[idA]; NA = p.T.off[idA + 1] - tbA; tbB = p.T.off[idB]; NB = p.T.off[idB + 1] - tbB;
+        longA = MA > q.maxM || NA > q.maxN; longB = MB > q.maxM || NB > q.maxN;
+        if (longA) MA = NA = 0;
+        if (longB) MB = NB = 0;
+    }
+    const uint32_t Nmax = max(NA, NB);
+    bool dirtyA = false, dirtyB = false;
+    uint16_t* my_sel = (uint16_t*)(s_mem + ((size_t)wib * p.tpw + (live ? g : 0)) * p.sstride);
+    const uint32_t pad = p.lanes - 1u;
+    if (live) f2_pack_selectors(p.T, my_sel, k, p.lanes, pad, tbA, NA, tbB, NB, Nmax, dirtyA, dirtyB);
+    __syncwarp();
+    const uint16_t* sel_at = my_sel + pad - k;
+    uint4* flow_at = (uint4*)q.flow + ((size_t)task * p.lanes + k) * q.maxN;
+
+    const int32_t go = p.ga, ge = p.gb, b = -ge, dd = go - ge, B = lq.B;
+    const int32_t sm = 4 * (p.match - go) + 1, sx = 4 * (p.mismatch - go) + 1;
+    const uint32_t base  = ((uint32_t)sx & 0xFFu) * 0x01010101u;
+    const uint32_t delta = ((uint32_t)(sx ^ sm)) & 0xFFu;
+    const uint32_t block = k * 16u;
+    uint32_t TA[16], TB[16], HO[16], F[16];
+    const int32_t d1 = 4 * dd + 1;
+    const uint32_t dfix1 = d1 < 0 ? f2_fix2(d1) : f2_pack2(d1);
+    const uint32_t ge4 = f2_fix2(4 * ge);
+    {
+        uint32_t qa[4] = { 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu }, qb[4] = { 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu };
+        if (live) { f2_stripe16(p.P, pbA, MA, block, qa); f2_stripe16(p.P, pbB, MB, block, qb); }
+        #pragma unroll
+        for (int j = 0; j < 16; ++j)
+        {
+            const uint32_t c = block + j;
+            const uint32_t a = (qa[j >> 2] >> (8 * (j & 3))) & 255u, bb = (qb[j >> 2] >> (8 * (j & 3))) & 255u;
+            uint32_t wa = 0x80808080u, wb = 0x80808080u;
+            if (live && c < MA) { dirtyA |= a > 3u; wa = base ^ (delta << (8u * (a & 3u))); }
+            if (live && c < MB) { dirtyB |= bb > 3u; wb = base ^ (delta << (8u * (bb & 3u))); }
+            TA[j] = wa; TB[j] = wb;
+        }
+    }
+    const uint32_t smask = (block < MA ? 0x0000FFFFu : 0u) | (block < MB ? 0xFFFF0000u : 0u);
+    uint32_t r_one, r_four, r_m1;
+    asm volatile("mov.u32 %0, %1;" : "=r"(r_one) : "r"(p.one));
+    asm volatile("mov.u32 %0, %1;" : "=r"(r_four) : "r"(4u * p.one));
+    asm volatile("mov.u32 %0, %1;" : "=r"(r_m1) : "r"(0u - p.one));
+    // column 0 of the matrix in the shear of local column -1: H = 0 -> HO1 = 4 (B - b + d) + 1; E = 0 -> 4 (B - b) + 1
+    const uint32_t ho_zero = f2_pack2(4 * (B - b + dd) + 1), e_zero = f2_pack2(4 * (B - b) + 1);
+    const uint32_t cin_mul = k == 0 ? 0u : r_one;
+    const uint32_t ho_add = k == 0 ? ho_zero : lq.unshear, e_add = k == 0 ? e_zero : lq.unshear;
+    uint32_t bestkey = f2_pack2(B) << 4, bestrow = 0u;
+    uint32_t carry = ho_zero, send_h = ho_zero, send_e = e_zero;
+
+    auto reset = [&]()
+    {
+        #pragma unroll
+        for (int j = 0; j < 16; ++j) { HO[j] = f2_imad(lq.FL[j] - 0x00030003u, r_one, dfix1); F[j] = 0u; }     // row 0: H = 0, F = -inf
+        carry = ho_zero;
+    };
+    reset();
+
+    auto row_step = [&](const uint32_t t, const bool masked, const bool first)
+    {
+        const uint32_t hin = f2_imad(__shfl_up_sync(0xFFFFFFFFu, send_h, 1), cin_mul, ho_add);
+        const uint32_t ein = f2_imad(__shfl_up_sync(0xFFFFFFFFu, send_e, 1), cin_mul, e_add);
+        const uint32_t i = t - k;
+        if (first && t == k) reset();
+        const uint32_t sel = sel_at[t];
+        const uint32_t kb = f2_imad(bestkey & 0xFFF8FFF8u, r_one, 0xFFFEFFFFu);
+        uint32_t acc = kb, left = hin, e = ein, diag = carry;
+        uint32_t fl[4] = { 0u, 0u, 0u, 0u };
+        carry = hin;
+        #pragma unroll
+        for (int j = 0; j < 16; j += 2)
+        {
+            uint32_t cc[2];
+            #pragma unroll
+            for (int u = 0; u < 2; ++u)
+            {
+                const int jj = j + u;
+                const uint32_t S = f2_prmt(TA[jj], TB[jj], sel);
+                const uint32_t top = HO[jj];
+                const uint32_t ft = __vmaxs2(F[jj], top);
+                const uint32_t xF = ft & 0x00010001u;
+                const uint32_t fn = f2_imad(ft - xF, r_one, ge4);                       // max(F, HO top) + ge, clean
+                const uint32_t dg = __viaddmax_s16x2(diag, S, lq.FL[jj]);               // max(diagonal | 2, floor | 3)
+                const uint32_t et = __vmaxs2(e, left + 0x00020002u);
+                const uint32_t xE = et & 0x00020002u;
+                e = et - xE;
+                const uint32_t h = __vimax3_s16x2(dg, fn, e);
+                const uint32_t th = h & 0x00030003u;
+                const uint32_t clean = h - th;
+                F[jj] = fn; diag = top;
+                left = f2_imad(clean, r_one, dfix1);
+                HO[jj] = left;
+                cc[u] = clean;
+                const uint32_t m = 1u << (4 * (jj & 3));
+                fl[jj >> 2] = f2_imad(th, m, f2_imad(xE, 2u * m, f2_imad(xF, 8u * m, fl[jj >> 2])));
+            }
+            acc = __vimax3_s16x2(acc, f2_imad(cc[0], r_four, lq.CJ[j]), f2_imad(cc[1], r_four, lq.CJ[j + 1]));
+        }
+        send_h = left; send_e = e;
+
+        const uint32_t df = f2_imad(kb, r_m1, acc);
+        const uint32_t sgn = f2_imad(df, r_one, 0x7FFF7FFFu);
+        uint32_t m = f2_prmt(sgn, sgn, 0xBB99u) & smask;
+        if (masked) m &= (i < NA ? 0x0000FFFFu : 0u) | (i < NB ? 0xFFFF0000u : 0u);
+        bestkey = (acc & m) | (bestkey & ~m);
+        bestrow = (f2_imad(i, 0x00010001u, 0u) & m) | (bestrow & ~m);
+        if (live && t >= k && i < Nmax) flow_at[i] = make_uint4(fl[0], fl[1], fl[2], fl[3]);
+    };
+
+    const uint32_t steps = __reduce_max_sync(0xFFFFFFFFu, live ? Nmax + p.lanes - 1 : 0u);
+    const uint32_t Nmin  = __reduce_min_sync(0xFFFFFFFFu, live ? min(NA, hasB ? NB : NA) : 0xFFFFFFFFu);
+    const uint32_t t_lo  = min(p.lanes, steps);
+    const uint32_t t_hi  = max(t_lo, min(Nmin, steps));
+    uint32_t t = 0;
+    for (; t < t_lo; ++t)  row_step(t, true, true);
+    for (; t < t_hi; ++t)  row_step(t, false, false);
+    for (; t < steps; ++t) row_step(t, true, false);
+
+    const uint32_t dmaskA = __ballot_sync(0xFFFFFFFFu, dirtyA), dmaskB = __ballot_sync(0xFFFFFFFFu, dirtyB);
+    const uint32_t gmask = (p.lanes >= 32 ? 0xFFFFFFFFu : ((1u << p.lanes) - 1u)) << gbase;
+    uint32_t wkA = 0, wkB = 0, wlaneA = 0, wlaneB = 0;
+    for (uint32_t l = 0; l < p.lanes; ++l)
+    {
+        const uint32_t src = min(gbase + l, 31u);
+        const uint32_t ok = __shfl_sync(0xFFFFFFFFu, bestkey, src);
+        const uint32_t sA = (ok & 0xFFFFu) >> 4, sB = ok >> 20;
+        if (sA >= (wkA >> 4)) { wkA = ok & 0xFFFFu; wlaneA = l; }
+        if (sB >= (wkB >> 4)) { wkB = ok >> 16; wlaneB = l; }
+    }
+    const uint32_t rowsA = __shfl_sync(0xFFFFFFFFu, bestrow, min(gbase + wlaneA, 31u));
+    const uint32_t rowsB = __shfl_sync(0xFFFFFFFFu, bestrow, min(gbase + wlaneB, 31u));
+    if (!live || k != 0) return;
+
+    #pragma unroll
+    for (int h = 0; h < 2; ++h)
+    {
+        if (h == 1 && !hasB) break;
+        const uint32_t id = h ? idB : idA;
+        const uint32_t M = h ? MB : MA, N = h ? NB : NA;
+        bool dirty = ((h ? dmaskB : dmaskA) & gmask) != 0 || (h ? longB : longA) || M == 0 || N == 0;
+        if (p.match > 0 && (uint64_t)p.match * min(max(MA, MB), Nmax) + (uint32_t)B + 15u * (uint32_t)b >= 2047u) dirty = true;
+        nvb_alignment a;
+        a.score = NVB_SINK_MIN; a.source_x = a.source_y = a.sink_x = a.sink_y = 0xFFFFFFFFu;
+        if (dirty) f2_mark_dirty(p.worklist, id);
+        else
+        {
+            const uint32_t wk = h ? wkB : wkA;
+            const uint32_t stripe = h ? wlaneB : wlaneA;
+            const uint32_t row = h ? (rowsB >> 16) : (rowsA & 0xFFFFu);
+            const int32_t score = (int32_t)(wk >> 4) - B;
+            if (score <= 0) { a.score = 0; a.sink_x = N; a.sink_y = M; }
+            else { a.score = score; a.sink_x = row + 1u; a.sink_y = stripe * 16u + (wk & 15u) + 1u; }
+        }
+        q.out[id] = a;
+        q.n_ops[id] = 0;
+    }
 }
 
 bool dpf2_traceback_supported(const nvb_aligner& a, uint32_t maxM, uint32_t maxN)
@@ -1232,9 +1604,18 @@ bool dpf2_traceback_supported(const nvb_aligner& a, uint32_t maxM, uint32_t maxN
     {
         if (4 * (s.match - s.ga - s.gb) + 2 > 127 || 4 * (s.mismatch - s.ga - s.gb) + 2 > 127) return false;   // profile bytes
     }
+    else if (a.type == NVB_LOCAL && (a.kind == NVB_SMITH_WATERMAN || a.kind == NVB_EDIT_DISTANCE))
+    {
+        if (s.ga >= 0 || s.gb >= 0 || s.ga < -64 || s.gb < -64) return false;
+        if (s.match - s.gb < -32 || s.match - s.gb > 31 || s.mismatch - s.gb < -32 || s.mismatch - s.gb > 31) return false;   // bytes 4 (S + b) + 2
+    }
     else if (gotoh_supported(a) && a.type != NVB_LOCAL)
     {
         if (4 * (s.match - s.ga - s.gb) + 1 > 127 || 4 * (s.mismatch - s.ga - s.gb) + 1 > 127) return false;
+    }
+    else if (gotoh_supported(a))
+    {
+        if (s.match - s.ga > 31 || s.match - s.ga < -32 || s.mismatch - s.ga > 31 || s.mismatch - s.ga < -32) return false;      // bytes 4 (S - go) + 1
     }
     else return false;
     uint32_t lanes, tpw, tstride, cstride; size_t smem;
@@ -1269,7 +1650,45 @@ int dpf2_traceback(nvb_ctx* ctx, const nvb_aligner& a, StrSet P, StrSet T, uint3
     }
     const uint32_t n_warps = (p.n_tasks + p.tpw - 1) / p.tpw;
     const uint32_t grid = (n_warps + DF2_WARPS - 1) / DF2_WARPS;
-    if (a.kind == NVB_GOTOH)
+    if (a.type == NVB_LOCAL && a.kind == NVB_GOTOH)
+    {
+        GotohLocal2TbParams lq;
+        lq.t = q; lq.t.f.semi = 2;
+        const int32_t b = -s.gb;
+        lq.B = DF2_BIAS;
+        lq.unshear = f2_fix2(-64 * b);
+        for (int j = 0; j < 16; ++j)
+        {
+            lq.FL[j] = f2_pack2(4 * (lq.B + b * j) + 3);
+            const int32_t cj = j - 16 * b * j;
+            lq.CJ[j] = cj < 0 ? f2_fix2(cj) : (uint32_t)cj * 0x00010001u;
+        }
+        if (NVB_FIRST_ON_DEVICE(ctx))
+            NVB_CUDA(ctx, cudaFuncSetAttribute(dpf2_gotoh_local_tb_forward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+        dpf2_gotoh_local_tb_forward_kernel<<<grid, DF2_THREADS, (size_t)DF2_WARPS * p.tpw * p.sstride * sizeof(uint32_t), st>>>(lq);
+        NVB_LAUNCHED(ctx);
+        dpf2_gotoh_tb_walk_kernel<<<(n + 255) / 256, 256, 0, st>>>(lq.t);
+    }
+    else if (a.type == NVB_LOCAL)
+    {
+        Local2TbParams lq;
+        lq.t = q; lq.t.f.semi = 2;                                          // the walk's "LOCAL" mark
+        const int32_t b = -s.gb;
+        lq.B = 64;
+        lq.unshear = f2_fix2(-64 * b);
+        for (int j = 0; j < 16; ++j)
+        {
+            lq.FL[j] = f2_pack2(4 * (lq.B + b * j) + 3);
+            const int32_t cj = j - 16 * b * j;
+            lq.CJ[j] = cj < 0 ? f2_fix2(cj) : 0u;
+        }
+        if (NVB_FIRST_ON_DEVICE(ctx))
+            NVB_CUDA(ctx, cudaFuncSetAttribute(dpf2_sw_local_tb_forward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+        dpf2_sw_local_tb_forward_kernel<<<grid, DF2_THREADS, (size_t)DF2_WARPS * p.tpw * p.sstride * sizeof(uint32_t), st>>>(lq);
+        NVB_LAUNCHED(ctx);
+        dpf2_sw_tb_walk_kernel<<<(n + 255) / 256, 256, 0, st>>>(lq.t);
+    }
+    else if (a.kind == NVB_GOTOH)
     {
         gq.B = 3 * (-(s.ga - s.gb)) + 4;
         dpf2_gotoh_tb_forward_kernel<<<grid, DF2_THREADS, smem_sel, st>>>(gq);

@@ -299,9 +299,9 @@ def test_host_scoring_pipelined_and_packed(oracle, bits):
 @pytest.mark.parametrize("kind,scheme", [(po.ED, (0, -1, -1, -1)), (po.SW, (2, -1, -1, -1)), (po.SW, (1, -3, -2, -2)), (po.SW, (3, -2, -4, -1)),
                                          (po.SW, (0, -1, -1, -2)), (po.GOTOH, (2, -2, -5, -3)), (po.GOTOH, (0, -5, -8, -3)), (po.GOTOH, (1, -1, -1, -1)),
                                          (po.GOTOH, (2, -1, -2, -1)), (po.GOTOH, (2, -6, -5, -3))])
-@pytest.mark.parametrize("ty", [0, 2])
+@pytest.mark.parametrize("ty", [0, 1, 2])
 def test_full_traceback_packed(oracle, kind, scheme, ty):
-    """full-matrix traceback of SW / ED / Gotoh GLOBAL and SEMI_GLOBAL on the tagged packed forward pass + walk: configs[0]-shaped
+    """full-matrix traceback of every aligner and type on the tagged packed forward passes + walks: configs[0]-shaped
     pairs, couples of equal pattern length (the ones the Gotoh kernel keeps), ragged couples over 1..17 stripes, a few N (those
     pairs go to the int32 kernel), a scratch that forces several launches, an unaligned op stride"""
     c = nvb.Context.default(0)
