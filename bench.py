@@ -1012,7 +1012,7 @@ def run_b200(args):
                 bufs = {}
                 def fn():
                     bufs["r"] = nvb.batch_alignment_traceback(a, 64, pt, tt, temp=ttemp, ctx=ctx)
-                tms = time_steps(fn, 2, 1, flush)
+                tms = time_steps(fn, 5, 3, flush)
                 ms = max_over_ranks(sum(tms) / len(tms))
                 res[name] = dict(pairs_per_s=world * nt / (ms * 1e-3), ms=ms, pairs=nt, paths=ctx.last_paths, gcups_equiv=world * nt * M * N / (ms * 1e-3) / 1e9,
                                  note=("packed forward pass writing 2 flow bits per cell + one walk thread per pair" if ctx.last_paths & 4 else

@@ -16,7 +16,7 @@ bool dpf2_full_score_supported(const nvb_aligner& a, uint32_t maxM, uint32_t max
 int  dpf2_full_score(nvb_ctx* ctx, const nvb_aligner& a, StrSet P, StrSet T, nvb_best_sink* sinks, uint32_t maxM,
                      uint32_t maxN, uint32_t* worklist, cudaStream_t s);
 // full-matrix traceback of SW / ED / Gotoh GLOBAL + SEMI_GLOBAL (dp_fast_full2.cu, part 3): one tagged forward pass writing two (Gotoh:
-// four) flow bits per cell ([couple][stripe][row]), then one walk thread per pair; pairs [first, first + n), first even
+// four) flow bits per cell, then one walk thread per pair; pairs [first, first + n), first even
 bool   dpf2_traceback_supported(const nvb_aligner& a, uint32_t maxM, uint32_t maxN);
 size_t dpf2_tb_bytes_per_couple(const nvb_aligner& a, uint32_t maxM, uint32_t maxN);
 int    dpf2_traceback(nvb_ctx* ctx, const nvb_aligner& a, StrSet P, StrSet T, uint32_t first, uint32_t n, nvb_alignment* out, uint8_t* ops,

@@ -792,7 +792,7 @@ int dpf2_full_score(nvb_ctx* ctx, const nvb_aligner& a, StrSet P, StrSet T, nvb_
 // exactly what sw_inl.h:488-490 picks: the diagonal unless a gap is strictly better, the insertion unless the deletion is strictly
 // better. A cell costs PRMT + VIMNMX3 + LOP3 (re-tag as `left`) + LOP3 (its tag) on the ALU pipe and three IMADs on the FMA pipe.
 // Flow: 2 bits per cell and pair, one 64-bit word per stripe and row (columns 0..7 of both pairs in .x, 8..15 in .y, column j at
-// bits 2 (7 - j mod 8), pair B 16 bits up), laid out [couple][stripe][row] so that a lane streams its rows.
+// bits 2 (7 - j mod 8), pair B 16 bits up); for the layout see f2_flow_base.
 // ---------------------------------------------------------------------------------------------------------------
 struct Full2TbParams
 {
@@ -804,7 +804,18 @@ struct Full2TbParams
     uint2*         flow;
     uint32_t       first, n_launch;        // pairs [first, first + n_launch)
     uint32_t       maxM, maxN;
+    uint32_t       by_step;                // flow layout: 1 = [couple][step][stripe], 0 = [couple][stripe][row]
 };
+
+// where stripe k stores the flow word of step t (row t - k); the first form makes the lanes of a couple write one contiguous run per
+// step (the SW / ED sweeps were bound by their scattered stores), the second keeps a stripe's rows together for the walk (the Gotoh
+// sweeps are bound by the ALU pipe, their walks by the 16-byte words they fetch). Rows that do not exist are stored too (the scratch
+// holds maxN + lanes entries per stripe either way).
+__device__ __forceinline__ size_t f2_flow_base(const Full2TbParams& q, uint32_t task, uint32_t k)
+{ return (size_t)task * q.f.lanes * (q.maxN + q.f.lanes) + (q.by_step ? (size_t)k : (size_t)k * (q.maxN + q.f.lanes)); }
+__device__ __forceinline__ size_t f2_flow_step(const Full2TbParams& q) { return q.by_step ? (size_t)q.f.lanes : (size_t)1; }
+__device__ __forceinline__ size_t f2_flow_at(const Full2TbParams& q, uint32_t couple, uint32_t stripe, uint32_t row)
+{ return f2_flow_base(q, couple, stripe) + (size_t)(row + stripe) * f2_flow_step(q); }
 
 __global__ void __launch_bounds__(DF2_THREADS, 4)
 dpf2_sw_tb_forward_kernel(const Full2TbParams q)
@@ -869,7 +880,8 @@ dpf2_sw_tb_forward_kernel(const Full2TbParams q)
     uint32_t carry = 0u, send = 0u, colacc = k == 0 ? 0x00010001u : 0u;
     const uint16_t* sel_at = my_sel + pad - k;
     uint32_t* cand_at = my_cand + pad - k;
-    uint2* flow_at = q.flow + ((size_t)task * p.lanes + k) * q.maxN;       // row r of this stripe at flow_at[r]
+    uint2* flow_at = q.flow + f2_flow_base(q, task, k);
+    const size_t flow_step = f2_flow_step(q);
 
     auto row_step = [&](const uint32_t t, const bool first)
     {
@@ -905,8 +917,7 @@ dpf2_sw_tb_forward_kernel(const Full2TbParams q)
         }
         send = left;
         if (last_lane) cand_at[t] = send;
-        const uint32_t r = t - k;
-        if (live && t >= k && r < Nmax) flow_at[r] = make_uint2(acc0, acc1);
+        if (live) flow_at[t * flow_step] = make_uint2(acc0, acc1);
     };
 
     const uint32_t steps = __reduce_max_sync(0xFFFFFFFFu, live ? Nmax + p.lanes - 1 : 0u);
@@ -981,13 +992,13 @@ dpf2_sw_tb_walk_kernel(const Full2TbParams q)
     const nvb_alignment a = q.out[id];
     if (a.sink_x == 0xFFFFFFFFu) return;                       // left to the int32 kernel
     const uint32_t up = (lp & 1u) * 16u;
-    const uint2* flow = q.flow + (size_t)(lp >> 1) * q.f.lanes * q.maxN;
+    const uint2* flow = q.flow;
     OpSink sink; sink.init(q.ops + (size_t)id * q.ops_stride, q.ops_stride);
     uint32_t row = a.sink_x, col = a.sink_y;                   // cells still to explain: text rows, pattern columns
     while (row > 0 && col > 0)
     {
         const uint32_t c = col - 1u;
-        const uint2 w = flow[(size_t)(c >> 4) * q.maxN + (row - 1u)];
+        const uint2 w = flow[f2_flow_at(q, lp >> 1, c >> 4, row - 1u)];
         const uint32_t tag = (((c & 8u) ? w.y : w.x) >> (2u * (7u - (c & 7u)) + up)) & 3u;
         if (tag == 3u)      break;                             // LOCAL: a cell of score 0 is the source
         if (tag == 2u)      { --row; --col; sink.push(OP_SUB); }
@@ -1011,7 +1022,7 @@ dpf2_sw_tb_walk_kernel(const Full2TbParams q)
 //   E  = max(E1, HO1 left + 2)        bit 1 set   = opened
 //   h  = max3(HO1 diag + (4 S'' + 1), F, E1)      tags 2 = substitution, 1 = insertion (E), 0 = deletion (F)
 // One nibble per cell and pair: tag | opened-E << 2 | opened-F << 3; one 128-bit word per stripe and row (columns 4 q .. 4 q + 3 in
-// word q, column j at bits 4 (j mod 4), pair B 16 bits up), [couple][stripe][row].
+// word q, column j at bits 4 (j mod 4), pair B 16 bits up).
 struct Gotoh2TbParams
 {
     Full2TbParams t;
@@ -1052,7 +1063,8 @@ dpf2_gotoh_tb_forward_kernel(const Gotoh2TbParams gq)
     __syncwarp();
     const uint16_t* sel_at = my_sel + pad - k;
     uint32_t* cand_at = my_cand + pad - k;
-    uint4* flow_at = (uint4*)q.flow + ((size_t)task * p.lanes + k) * q.maxN;
+    uint4* flow_at = (uint4*)q.flow + f2_flow_base(q, task, k);
+    const size_t flow_step = f2_flow_step(q);
 
     const int32_t go = p.ga, ge = p.gb, b = -ge, dd = go - ge, B = gq.B;
     const int32_t sm = 4 * (p.match - ge - go) + 1, sx = 4 * (p.mismatch - ge - go) + 1;
@@ -1126,8 +1138,7 @@ dpf2_gotoh_tb_forward_kernel(const Gotoh2TbParams gq)
         }
         send_h = left; send_e = e;
         if (capture) cand_at[t] = cap;
-        const uint32_t r = t - k;
-        if (live && t >= k && r < Nmax) flow_at[r] = make_uint4(acc[0], acc[1], acc[2], acc[3]);
+        if (live) flow_at[t * flow_step] = make_uint4(acc[0], acc[1], acc[2], acc[3]);
     };
 
     const uint32_t steps = __reduce_max_sync(0xFFFFFFFFu, live ? Nmax + p.lanes - 1 : 0u);
@@ -1201,13 +1212,13 @@ dpf2_gotoh_tb_walk_kernel(const Full2TbParams q)
     const nvb_alignment a = q.out[id];
     if (a.sink_x == 0xFFFFFFFFu) return;
     const uint32_t up = (lp & 1u) * 16u;
-    const uint4* flow = (const uint4*)q.flow + (size_t)(lp >> 1) * q.f.lanes * q.maxN;
+    const uint4* flow = (const uint4*)q.flow;
     OpSink sink; sink.init(q.ops + (size_t)id * q.ops_stride, q.ops_stride);
     uint32_t row = a.sink_x, col = a.sink_y, state = ST_H;
     while (row > 0 && col > 0)
     {
         const uint32_t c = col - 1u;
-        const uint4 w = flow[(size_t)(c >> 4) * q.maxN + (row - 1u)];
+        const uint4 w = flow[f2_flow_at(q, lp >> 1, c >> 4, row - 1u)];
         const uint32_t word = (c & 8u) ? ((c & 4u) ? w.w : w.z) : ((c & 4u) ? w.y : w.x);
         const uint32_t nib = (word >> (4u * (c & 3u) + up)) & 15u;
         if (state == ST_E)      { if (nib & 4u) state = ST_H; --col; sink.push(OP_INS); }
@@ -1277,7 +1288,8 @@ dpf2_sw_local_tb_forward_kernel(const Local2TbParams lq)
     if (live) f2_pack_selectors(p.T, my_sel, k, p.lanes, pad, tbA, NA, tbB, NB, Nmax, dirtyA, dirtyB);
     __syncwarp();
     const uint16_t* sel_at = my_sel + pad - k;
-    uint2* flow_at = q.flow + ((size_t)task * p.lanes + k) * q.maxN;
+    uint2* flow_at = q.flow + f2_flow_base(q, task, k);
+    const size_t flow_step = f2_flow_step(q);
 
     const int32_t G = p.ga, I = p.gb, B = lq.B;
     const int32_t sm = 4 * (p.match - I) + 2, sx = 4 * (p.mismatch - I) + 2;
@@ -1357,7 +1369,7 @@ dpf2_sw_local_tb_forward_kernel(const Local2TbParams lq)
         if (masked) m &= (i < NA ? 0x0000FFFFu : 0u) | (i < NB ? 0xFFFF0000u : 0u);
         bestkey = (acc & m) | (bestkey & ~m);
         bestrow = (f2_imad(i, 0x00010001u, 0u) & m) | (bestrow & ~m);
-        if (live && t >= k && i < Nmax) flow_at[i] = make_uint2(a0, a1);
+        if (live) flow_at[t * flow_step] = make_uint2(a0, a1);
     };
 
     const uint32_t steps = __reduce_max_sync(0xFFFFFFFFu, live ? Nmax + p.lanes - 1 : 0u);
@@ -1451,7 +1463,8 @@ dpf2_gotoh_local_tb_forward_kernel(const GotohLocal2TbParams lq)
     if (live) f2_pack_selectors(p.T, my_sel, k, p.lanes, pad, tbA, NA, tbB, NB, Nmax, dirtyA, dirtyB);
     __syncwarp();
     const uint16_t* sel_at = my_sel + pad - k;
-    uint4* flow_at = (uint4*)q.flow + ((size_t)task * p.lanes + k) * q.maxN;
+    uint4* flow_at = (uint4*)q.flow + f2_flow_base(q, task, k);
+    const size_t flow_step = f2_flow_step(q);
 
     const int32_t go = p.ga, ge = p.gb, b = -ge, dd = go - ge, B = lq.B;
     const int32_t sm = 4 * (p.match - go) + 1, sx = 4 * (p.mismatch - go) + 1;
@@ -1544,7 +1557,7 @@ dpf2_gotoh_local_tb_forward_kernel(const GotohLocal2TbParams lq)
         if (masked) m &= (i < NA ? 0x0000FFFFu : 0u) | (i < NB ? 0xFFFF0000u : 0u);
         bestkey = (acc & m) | (bestkey & ~m);
         bestrow = (f2_imad(i, 0x00010001u, 0u) & m) | (bestrow & ~m);
-        if (live && t >= k && i < Nmax) flow_at[i] = make_uint4(fl[0], fl[1], fl[2], fl[3]);
+        if (live) flow_at[t * flow_step] = make_uint4(fl[0], fl[1], fl[2], fl[3]);
     };
 
     const uint32_t steps = __reduce_max_sync(0xFFFFFFFFu, live ? Nmax + p.lanes - 1 : 0u);
@@ -1623,7 +1636,7 @@ bool dpf2_traceback_supported(const nvb_aligner& a, uint32_t maxM, uint32_t maxN
 }
 
 size_t dpf2_tb_bytes_per_couple(const nvb_aligner& a, uint32_t maxM, uint32_t maxN)
-{ return (size_t)((maxM + 15u) / 16u) * maxN * (a.kind == NVB_GOTOH ? sizeof(uint4) : sizeof(uint2)); }
+{ const size_t lanes = (maxM + 15u) / 16u; return lanes * (maxN + lanes) * (a.kind == NVB_GOTOH ? sizeof(uint4) : sizeof(uint2)); }
 
 // pairs [first, first + n) (first even); flow scratch of at least ceil(n / 2) * dpf2_tb_bytes_per_couple bytes, 16-byte aligned
 int dpf2_traceback(nvb_ctx* ctx, const nvb_aligner& a, StrSet P, StrSet T, uint32_t first, uint32_t n, nvb_alignment* out, uint8_t* ops,
@@ -1643,6 +1656,13 @@ int dpf2_traceback(nvb_ctx* ctx, const nvb_aligner& a, StrSet P, StrSet T, uint3
     p.cstride = maxN + 2u * p.lanes;
     q.out = out; q.n_ops = n_ops; q.ops = ops; q.ops_stride = ops_stride; q.flow = (uint2*)flow;
     q.first = first; q.n_launch = n; q.maxM = maxM; q.maxN = maxN;
+    {
+        // bit 0 SW / ED GLOBAL + SEMI_GLOBAL, 1 SW / ED LOCAL, 2 Gotoh GLOBAL + SEMI_GLOBAL, 3 Gotoh LOCAL (NVB_TB_LAYOUT: tuning aid)
+        static int mask = -1;
+        if (mask < 0) { const char* e = getenv("NVB_TB_LAYOUT"); mask = e ? atoi(e) : 1; }
+        const int bit = (a.kind == NVB_GOTOH ? 2 : 0) + (a.type == NVB_LOCAL ? 1 : 0);
+        q.by_step = (mask >> bit) & 1;
+    }
     if (NVB_FIRST_ON_DEVICE(ctx))
     {
         NVB_CUDA(ctx, cudaFuncSetAttribute(dpf2_sw_tb_forward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
