@@ -805,6 +805,7 @@ struct Full2TbParams
     uint32_t       first, n_launch;        // pairs [first, first + n_launch)
     uint32_t       maxM, maxN;
     uint32_t       by_step;                // flow layout: 1 = [couple][step][stripe], 0 = [couple][stripe][row]
+    uint32_t       ahead;                  // rows the walk prefetches ahead of itself
 };
 
 // where stripe k stores the flow word of step t (row t - k); the first form makes the lanes of a couple write one contiguous run per
@@ -999,6 +1000,8 @@ dpf2_sw_tb_walk_kernel(const Full2TbParams q)
     {
         const uint32_t c = col - 1u;
         const uint2 w = flow[f2_flow_at(q, lp >> 1, c >> 4, row - 1u)];
+        // the path climbs a row at most every step: ask for the word it will need `ahead` rows up now (a dependent DRAM round trip per row otherwise)
+        if (row > q.ahead) asm volatile("prefetch.global.L1 [%0];" :: "l"(flow + f2_flow_at(q, lp >> 1, c >> 4, row - 1u - q.ahead)));
         const uint32_t tag = (((c & 8u) ? w.y : w.x) >> (2u * (7u - (c & 7u)) + up)) & 3u;
         if (tag == 3u)      break;                             // LOCAL: a cell of score 0 is the source
         if (tag == 2u)      { --row; --col; sink.push(OP_SUB); }
@@ -1219,6 +1222,7 @@ dpf2_gotoh_tb_walk_kernel(const Full2TbParams q)
     {
         const uint32_t c = col - 1u;
         const uint4 w = flow[f2_flow_at(q, lp >> 1, c >> 4, row - 1u)];
+        if (row > q.ahead) asm volatile("prefetch.global.L1 [%0];" :: "l"(flow + f2_flow_at(q, lp >> 1, c >> 4, row - 1u - q.ahead)));
         const uint32_t word = (c & 8u) ? ((c & 4u) ? w.w : w.z) : ((c & 4u) ? w.y : w.x);
         const uint32_t nib = (word >> (4u * (c & 3u) + up)) & 15u;
         if (state == ST_E)      { if (nib & 4u) state = ST_H; --col; sink.push(OP_INS); }
@@ -1662,6 +1666,9 @@ int dpf2_traceback(nvb_ctx* ctx, const nvb_aligner& a, StrSet P, StrSet T, uint3
         if (mask < 0) { const char* e = getenv("NVB_TB_LAYOUT"); mask = e ? atoi(e) : 1; }
         const int bit = (a.kind == NVB_GOTOH ? 2 : 0) + (a.type == NVB_LOCAL ? 1 : 0);
         q.by_step = (mask >> bit) & 1;
+        static int ahead = -1;
+        if (ahead < 0) { const char* e = getenv("NVB_TB_AHEAD"); ahead = e ? atoi(e) : 4; if (ahead < 1) ahead = 0x7FFFFFFF; }
+        q.ahead = (uint32_t)ahead;
     }
     if (NVB_FIRST_ON_DEVICE(ctx))
     {
