@@ -14,7 +14,7 @@
 #define NVB_STAGE_SLOTS 80
 // stage slot map (nvb_ctx::d_stage): 0-7 *_host DP/locate entry points and FMIndexFilter | 8-32 the seed-and-extend pipeline
 // (map_pipeline.cu S_*) | 33-44 nvb_fm_match_host* (4 buffer sets x 3) | 40-41 are NOT free: they belong to that range; the
-// packed-set expansion of dp_api.cu uses 60-61 | 45-54 nvb_map_reads_host (2 sets x 5) | 55 quality-scheme tables (dp_api.cu) | 56 min-score table of nvb_map_hits_mapq (mds.cu) | 57 N list of nvb_fm_match_host_fixed2n | 64-75 pipelined nvb_batch_score_host* (2 sets x 5, temp) | 62-63 per-batch k-mer table (fm_kernels.cu)
+// packed-set expansion of dp_api.cu uses 60-61 | 45-54 nvb_map_reads_host (2 sets x 5) | 55 quality-scheme tables (dp_api.cu) | 56 min-score table of nvb_map_hits_mapq (mds.cu) | 57 N list of nvb_fm_match_host_fixed2n | 64-75 pipelined nvb_batch_score_host* (2 sets x 5, temp) | 62-63 per-batch k-mer table (fm_kernels.cu) | 76 coupling order of the Gotoh sweeps (dp_fast_full2.cu)
 
 struct nvb_ctx
 {

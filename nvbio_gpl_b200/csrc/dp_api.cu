@@ -195,7 +195,13 @@ static int batch_score_impl(nvb_ctx* ctx, nvb_aligner a, const nvb_quality_schem
         if ((rc = nvb_worklist(ctx, n, &wl))) return rc;
         NVB_CUDA(ctx, cudaMemsetAsync(wl, 0, sizeof(uint32_t), s));
         if (fast_local) { if ((rc = dpf_full_score(ctx, a, P, T, sinks, maxM, maxN, wl, temp, s))) return rc; }
-        else { if ((rc = dpf2_full_score(ctx, a, P, T, sinks, maxM, maxN, wl, s))) return rc; ctx->last_paths |= 4u; }
+        else
+        {
+            const uint32_t* order = nullptr;
+            if (dpf2_wants_order(a) && (rc = dpf2_order_by_length(ctx, P, maxM, &order, s))) return rc;
+            if ((rc = dpf2_full_score(ctx, a, P, T, sinks, maxM, maxN, wl, s, order))) return rc;
+            ctx->last_paths |= 4u;
+        }
         ctx->last_paths |= 1u;
         if (!temp && p.i16_per_pair) return NVB_ERR_TEMP;
         uint32_t n_dirty = n;
@@ -383,14 +389,17 @@ static int batch_traceback_impl(nvb_ctx* ctx, nvb_aligner a, const nvb_quality_s
         uint64_t fit = 2ull * (avail / per_couple);
         if (fit >= 2)
         {
-            if (fit > n) fit = ((uint64_t)n + 1) & ~1ull;
             uint32_t* wl = nullptr;
             if ((rc = nvb_worklist(ctx, n, &wl))) return rc;
             NVB_CUDA(ctx, cudaMemsetAsync(wl, 0, sizeof(uint32_t), s));
-            for (uint64_t first = 0; first < n; first += fit)
+            const uint32_t* order = nullptr;
+            if (dpf2_wants_order(a) && (rc = dpf2_order_by_length(ctx, P, maxM, &order, s))) return rc;
+            const uint64_t n_sweep = order ? dpf2_order_entries(n, maxM) : n;   // the sweeps walk the (padded) coupling order
+            if (fit > n_sweep) fit = (n_sweep + 1) & ~1ull;
+            for (uint64_t first = 0; first < n_sweep; first += fit)
             {
-                const uint32_t cnt = (uint32_t)(n - first < fit ? n - first : fit);
-                if ((rc = dpf2_traceback(ctx, a, P, T, (uint32_t)first, cnt, out, ops, ops_stride, n_ops, maxM, maxN, flow, wl, s))) return rc;
+                const uint32_t cnt = (uint32_t)(n_sweep - first < fit ? n_sweep - first : fit);
+                if ((rc = dpf2_traceback(ctx, a, P, T, (uint32_t)first, cnt, out, ops, ops_stride, n_ops, maxM, maxN, flow, wl, s, order))) return rc;
             }
             ctx->last_paths |= 4u;
             list = wl + 1; d_count = wl;

@@ -24,6 +24,7 @@
 #include "dp_fast.h"
 
 #define DF2_WARPS   4
+#define F2_NO_PAIR  0xFFFFFFFFu     // entry of a coupling order: no pair here (dpf2_order_by_length)
 #define DF2_THREADS (DF2_WARPS * 32)
 
 struct Full2Params
@@ -39,6 +40,7 @@ struct Full2Params
     int32_t        match, mismatch, ga, gb;
     int32_t        semi;           // 1 = SEMI_GLOBAL, 0 = GLOBAL
     uint32_t       one;
+    const uint32_t* order;         // pair ids in the order they are coupled (NULL: 0, 1, 2, ...); see dpf2_order_by_length
 };
 
 __host__ __device__ __forceinline__ uint32_t f2_pack2(int32_t v) { return ((uint32_t)v & 0xFFFFu) * 0x00010001u; }
@@ -516,8 +518,8 @@ dpf2_gotoh_local_kernel(const Gotoh2Params q)
 // gotoh_inl.h:675) and column 0 of GLOBAL become the constant d, column 0 of SEMI_GLOBAL (0) becomes -ge r; E of column 0
 // and F of row 0 are -infinity = 0 below every biased value. The opening surcharge is paid on every move to the right, so
 // columns past M do NOT carry h[r][M] along (as they do in part 1): the lane holding column M picks it out of its 16
-// registers with a one-hot multiply-add chain on the FMA pipe, which needs both pairs of a couple to have the same M --
-// couples that do not go to the int32 kernel.
+// registers with a one-hot multiply-add chain on the FMA pipe, which needs both pairs of a couple to have the same M:
+// the pairs of a batch are coupled in the order of a counting sort by pattern length (dpf2_order_by_length below).
 __global__ void __launch_bounds__(DF2_THREADS, 4)
 dpf2_gotoh_kernel(const Gotoh2Params q)
 {
@@ -527,14 +529,16 @@ dpf2_gotoh_kernel(const Gotoh2Params q)
     const uint32_t warp = blockIdx.x * DF2_WARPS + wib;
     const uint32_t g = lane / p.lanes, k = lane - g * p.lanes;
     const uint32_t task = warp * p.tpw + g;
-    const bool live = g < p.tpw && task < p.n_tasks;
+    const bool live = g < p.tpw && task < p.n_tasks && !(p.order && p.order[2 * min(task, p.n_tasks - 1u)] == F2_NO_PAIR);   // pads past the last run
     const uint32_t gbase = g * p.lanes;
 
     uint32_t idA = 0, idB = 0, pbA = 0, pbB = 0, tbA = 0, tbB = 0, MA = 0, MB = 0, NA = 0, NB = 0;
     bool hasB = false;
     if (live)
     {
-        idA = 2 * task; hasB = idA + 1 < p.n_pairs; idB = hasB ? idA + 1 : idA;
+        hasB = 2 * task + 1 < p.n_pairs;
+        idA = p.order ? p.order[2 * task] : 2 * task; idB = hasB ? (p.order ? p.order[2 * task + 1] : idA + 1) : idA;
+        if (idB == F2_NO_PAIR) { hasB = false; idB = idA; }                  // a run of odd count: the pair sweeps alone
         pbA = p.P.off[idA]; MA = p.P.off[idA + 1] - pbA; pbB = p.P.off[idB]; MB = p.P.off[idB + 1] - pbB;
         tbA = p.T.off[idA]; NA = p.T.off[idA + 1] - tbA; tbB = p.T.off[idB]; NB = p.T.off[idB + 1] - tbB;
     }
@@ -710,6 +714,94 @@ static bool gotoh_supported(const nvb_aligner& a)
     return !(sm < 0 || sm > 127 || sx < 0 || sx > 127);
 }
 
+// The Gotoh GLOBAL / SEMI_GLOBAL sweeps capture column M of a couple in ONE lane and register, so both pairs of a couple must have
+// the same pattern length. Reads of one length are the common case; for a batch of mixed lengths the pairs are coupled in the order of
+// a counting sort by pattern length (histogram, scan, scatter: three small launches, warp-aggregated atomics). Every length's run is
+// padded to an even count with the entry 0xFFFFFFFF ("no second pair"), so no couple ever mixes two lengths -- a single pair left to
+// the int32 kernel would cost that kernel's full one-thread latency (milliseconds at 150 x 500). The order array therefore has
+// dpf2_order_entries(n, maxM) >= n entries; entries past the last run are 0xFFFFFFFF too. Which pairs share a register does not
+// change any pair's result.
+__global__ void __launch_bounds__(256)
+f2_len_hist_kernel(const uint32_t* __restrict__ off, uint32_t n, uint32_t cap, uint32_t* __restrict__ bins)
+{
+    const uint32_t i = blockIdx.x * 256 + threadIdx.x;
+    const bool on = i < n;
+    const uint32_t len = on ? min(off[i + 1] - off[i], cap) : 0xFFFFFFFFu;
+    const uint32_t peers = __match_any_sync(0xFFFFFFFFu, len);
+    if (on && (threadIdx.x & 31u) == (uint32_t)(__ffs(peers) - 1)) atomicAdd(bins + len, (uint32_t)__popc(peers));
+}
+// counts -> start of every length's run, each run padded to an even number of entries (one block)
+__global__ void __launch_bounds__(1024)
+f2_len_scan_kernel(uint32_t* __restrict__ bins, uint32_t nb)
+{
+    __shared__ uint32_t s_warp[32];
+    uint32_t run = 0;
+    for (uint32_t b0 = 0; b0 < nb; b0 += 1024u)
+    {
+        const uint32_t b = b0 + threadIdx.x;
+        const uint32_t c = b < nb ? ((bins[b] + 1u) & ~1u) : 0u;
+        uint32_t x = c;
+        #pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const uint32_t y = __shfl_up_sync(0xFFFFFFFFu, x, d); if ((threadIdx.x & 31u) >= (uint32_t)d) x += y; }
+        if ((threadIdx.x & 31u) == 31u) s_warp[threadIdx.x >> 5] = x;
+        __syncthreads();
+        if (threadIdx.x < 32u)
+        {
+            uint32_t w = s_warp[threadIdx.x];
+            #pragma unroll
+            for (int d = 1; d < 32; d <<= 1) { const uint32_t y = __shfl_up_sync(0xFFFFFFFFu, w, d); if (threadIdx.x >= (uint32_t)d) w += y; }
+            s_warp[threadIdx.x] = w;
+        }
+        __syncthreads();
+        const uint32_t before = (threadIdx.x >> 5) ? s_warp[(threadIdx.x >> 5) - 1u] : 0u;
+        if (b < nb) bins[b] = run + before + x - c;
+        run += s_warp[31];
+        __syncthreads();
+    }
+}
+__global__ void __launch_bounds__(256)
+f2_len_scatter_kernel(const uint32_t* __restrict__ off, uint32_t n, uint32_t cap, uint32_t* __restrict__ bins, uint32_t* __restrict__ order)
+{
+    const uint32_t i = blockIdx.x * 256 + threadIdx.x;
+    const bool on = i < n;
+    const uint32_t len = on ? min(off[i + 1] - off[i], cap) : 0xFFFFFFFFu;
+    const uint32_t peers = __match_any_sync(0xFFFFFFFFu, len);
+    const uint32_t lane = threadIdx.x & 31u, leader = (uint32_t)(__ffs(peers) - 1);
+    uint32_t base = 0;
+    if (on && lane == leader) base = atomicAdd(bins + len, (uint32_t)__popc(peers));
+    base = __shfl_sync(0xFFFFFFFFu, base, leader);
+    if (on) order[base + __popc(peers & ((1u << lane) - 1u))] = i;
+}
+
+enum { F2_SLOT_ORDER = 76 };        // slot map in common.cuh
+bool dpf2_wants_order(const nvb_aligner& a)
+{
+    static int off = -1;                                   // NVB_NO_ORDER=1: couple the pairs as they come (tools/ragged_probe.py)
+    if (off < 0) { const char* e = getenv("NVB_NO_ORDER"); off = e ? atoi(e) : 0; }
+    return !off && a.kind == NVB_GOTOH && a.type != NVB_LOCAL;
+}
+// entries of the order array: n pairs + at most one pad per length bin, rounded up to whole couples
+uint32_t dpf2_order_entries(uint32_t n, uint32_t maxM) { return (n + maxM + 2u + 1u) & ~1u; }
+int dpf2_order_by_length(nvb_ctx* ctx, const StrSet& P, uint32_t maxM, const uint32_t** order, cudaStream_t st)
+{
+    const uint32_t n = P.count, nb = maxM + 2u;            // lengths 0 .. maxM, and "longer"
+    const uint32_t entries = dpf2_order_entries(n, maxM);
+    void* buf = nullptr;
+    int rc = nvb_stage(ctx, F2_SLOT_ORDER, sizeof(uint32_t) * ((size_t)entries + nb), &buf);
+    if (rc) return rc;
+    uint32_t* bins = (uint32_t*)buf; uint32_t* ord = bins + nb;
+    NVB_CUDA(ctx, cudaMemsetAsync(bins, 0, sizeof(uint32_t) * nb, st));
+    NVB_CUDA(ctx, cudaMemsetAsync(ord, 0xFF, sizeof(uint32_t) * (size_t)entries, st));
+    f2_len_hist_kernel<<<(n + 255) / 256, 256, 0, st>>>(P.off, n, maxM + 1u, bins);
+    NVB_LAUNCHED(ctx);
+    f2_len_scan_kernel<<<1, 1024, 0, st>>>(bins, nb);
+    NVB_LAUNCHED(ctx);
+    f2_len_scatter_kernel<<<(n + 255) / 256, 256, 0, st>>>(P.off, n, maxM + 1u, bins, ord);
+    NVB_LAUNCHED(ctx);
+    *order = ord;
+    return NVB_OK;
+}
+
 bool dpf2_full_score_supported(const nvb_aligner& a, uint32_t maxM, uint32_t maxN)
 {
     if (!sw_supported(a) && !gotoh_supported(a)) return false;
@@ -719,15 +811,15 @@ bool dpf2_full_score_supported(const nvb_aligner& a, uint32_t maxM, uint32_t max
 }
 
 int dpf2_full_score(nvb_ctx* ctx, const nvb_aligner& a, StrSet P, StrSet T, nvb_best_sink* sinks, uint32_t maxM,
-                    uint32_t maxN, uint32_t* worklist, cudaStream_t st)
+                    uint32_t maxN, uint32_t* worklist, cudaStream_t st, const uint32_t* order)
 {
     const Scheme s = make_scheme(a);
     Gotoh2Params q;
     Full2Params& p = q.f;
     size_t smem, smem_sel;
     if (!full2_geometry(maxM, maxN, &p.lanes, &p.tpw, &p.tstride, &p.cstride, &smem, &p.sstride, &smem_sel)) return NVB_ERR_UNSUPPORTED;
-    p.P = P; p.T = T; p.sinks = sinks; p.worklist = worklist;
-    p.n_pairs = P.count; p.n_tasks = (P.count + 1) / 2;
+    p.P = P; p.T = T; p.sinks = sinks; p.worklist = worklist; p.order = dpf2_wants_order(a) ? order : nullptr;
+    p.n_pairs = p.order ? dpf2_order_entries(P.count, maxM) : P.count; p.n_tasks = (p.n_pairs + 1) / 2;
     p.match = s.match; p.mismatch = s.mismatch; p.ga = s.ga; p.gb = s.gb;
     p.semi = a.type == NVB_SEMI_GLOBAL ? 1 : 0;
     p.one = 1;
@@ -1042,14 +1134,16 @@ dpf2_gotoh_tb_forward_kernel(const Gotoh2TbParams gq)
     const uint32_t warp = blockIdx.x * DF2_WARPS + wib;
     const uint32_t g = lane / p.lanes, k = lane - g * p.lanes;
     const uint32_t task = warp * p.tpw + g;
-    const bool live = g < p.tpw && task < p.n_tasks;
+    const bool live = g < p.tpw && task < p.n_tasks && !(p.order && p.order[q.first + 2 * min(task, p.n_tasks - 1u)] == F2_NO_PAIR);
     const uint32_t gbase = g * p.lanes;
 
     uint32_t idA = 0, idB = 0, pbA = 0, pbB = 0, tbA = 0, tbB = 0, MA = 0, MB = 0, NA = 0, NB = 0;
     bool hasB = false, longA = false, longB = false;
     if (live)
     {
-        idA = q.first + 2 * task; hasB = idA + 1 < q.first + q.n_launch; idB = hasB ? idA + 1 : idA;
+        hasB = 2 * task + 1 < q.n_launch;
+        idA = p.order ? p.order[q.first + 2 * task] : q.first + 2 * task; idB = hasB ? (p.order ? p.order[q.first + 2 * task + 1] : idA + 1) : idA;
+        if (idB == F2_NO_PAIR) { hasB = false; idB = idA; }
         pbA = p.P.off[idA]; MA = p.P.off[idA + 1] - pbA; pbB = p.P.off[idB]; MB = p.P.off[idB + 1] - pbB;
         tbA = p.T.off[idA]; NA = p.T.off[idA + 1] - tbA; tbB = p.T.off[idB]; NB = p.T.off[idB + 1] - tbB;
         longA = MA > q.maxM || NA > q.maxN; longB = MB > q.maxM || NB > q.maxN;
@@ -1211,7 +1305,8 @@ dpf2_gotoh_tb_walk_kernel(const Full2TbParams q)
 {
     const uint32_t lp = blockIdx.x * 256 + threadIdx.x;
     if (lp >= q.n_launch) return;
-    const uint32_t id = q.first + lp;
+    const uint32_t id = q.f.order ? q.f.order[q.first + lp] : q.first + lp;
+    if (id == F2_NO_PAIR) return;
     const nvb_alignment a = q.out[id];
     if (a.sink_x == 0xFFFFFFFFu) return;
     const uint32_t up = (lp & 1u) * 16u;
@@ -1644,7 +1739,8 @@ size_t dpf2_tb_bytes_per_couple(const nvb_aligner& a, uint32_t maxM, uint32_t ma
 
 // pairs [first, first + n) (first even); flow scratch of at least ceil(n / 2) * dpf2_tb_bytes_per_couple bytes, 16-byte aligned
 int dpf2_traceback(nvb_ctx* ctx, const nvb_aligner& a, StrSet P, StrSet T, uint32_t first, uint32_t n, nvb_alignment* out, uint8_t* ops,
-                   uint32_t ops_stride, uint32_t* n_ops, uint32_t maxM, uint32_t maxN, uint8_t* flow, uint32_t* worklist, cudaStream_t st)
+                   uint32_t ops_stride, uint32_t* n_ops, uint32_t maxM, uint32_t maxN, uint8_t* flow, uint32_t* worklist, cudaStream_t st,
+                   const uint32_t* order)
 {
     const Scheme s = make_scheme(a);
     Gotoh2TbParams gq;
@@ -1652,7 +1748,7 @@ int dpf2_traceback(nvb_ctx* ctx, const nvb_aligner& a, StrSet P, StrSet T, uint3
     Full2Params& p = q.f;
     size_t smem, smem_sel;
     if (!full2_geometry(maxM, maxN, &p.lanes, &p.tpw, &p.tstride, &p.cstride, &smem, &p.sstride, &smem_sel)) return NVB_ERR_UNSUPPORTED;
-    p.P = P; p.T = T; p.sinks = nullptr; p.worklist = worklist;
+    p.P = P; p.T = T; p.sinks = nullptr; p.worklist = worklist; p.order = dpf2_wants_order(a) ? order : nullptr;
     p.n_pairs = P.count; p.n_tasks = (n + 1) / 2;
     p.match = s.match; p.mismatch = s.mismatch; p.ga = s.ga; p.gb = s.gb;
     p.semi = a.type == NVB_SEMI_GLOBAL ? 1 : 0;
