@@ -190,8 +190,8 @@ dpf_full_sw_local_kernel(const FullFastParams p)
             const uint32_t c = block + j;
             const uint32_t a = (qa[j >> 2] >> (8 * (j & 3))) & 255u, b = (qb[j >> 2] >> (8 * (j & 3))) & 255u;
             uint32_t wa = 0x80808080u, wb = 0x80808080u;       // columns past the pattern: S = -128
-            if (live && c < MA) { dirtyA |= a > 3u; wa = base ^ (delta << (8u * (a & 3u))); }
-            if (live && c < MB) { dirtyB |= b > 3u; wb = base ^ (delta << (8u * (b & 3u))); }
+            if (live && c < MA) wa = a > 3u ? base : base ^ (delta << (8u * a));                 // a pattern N matches no text symbol 0..3: mismatch in every row
+            if (live && c < MB) wb = b > 3u ? base : base ^ (delta << (8u * b));
             TA[j] = wa; TB[j] = wb; H[j] = FLc(j);
         }
     }

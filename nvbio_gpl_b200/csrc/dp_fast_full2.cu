@@ -206,8 +206,8 @@ dpf2_sw_kernel(const Full2Params p)
             const uint32_t c = block + j;
             const uint32_t a = (qa[j >> 2] >> (8 * (j & 3))) & 255u, b = (qb[j >> 2] >> (8 * (j & 3))) & 255u;
             uint32_t wa = 0u, wb = 0u;
-            if (live && c < MA) { dirtyA |= a > 3u; wa = base ^ (delta << (8u * (a & 3u))); }
-            if (live && c < MB) { dirtyB |= b > 3u; wb = base ^ (delta << (8u * (b & 3u))); }
+            if (live && c < MA) wa = a > 3u ? base : base ^ (delta << (8u * a));                 // a pattern N matches no text symbol 0..3: mismatch in every row
+            if (live && c < MB) wb = b > 3u ? base : base ^ (delta << (8u * b));
             TA[j] = wa; TB[j] = wb; H[j] = 0u;
         }
     }
@@ -398,8 +398,8 @@ dpf2_gotoh_local_kernel(const Gotoh2Params q)
             const uint32_t c = block + j;
             const uint32_t a = (qa[j >> 2] >> (8 * (j & 3))) & 255u, bb = (qb[j >> 2] >> (8 * (j & 3))) & 255u;
             uint32_t wa = 0x80808080u, wb = 0x80808080u;       // columns past the pattern: S = -128
-            if (live && c < MA) { dirtyA |= a > 3u; wa = base ^ (delta << (8u * (a & 3u))); }
-            if (live && c < MB) { dirtyB |= bb > 3u; wb = base ^ (delta << (8u * (bb & 3u))); }
+            if (live && c < MA) wa = a > 3u ? base : base ^ (delta << (8u * a));                 // a pattern N matches no text symbol 0..3: mismatch in every row
+            if (live && c < MB) wb = bb > 3u ? base : base ^ (delta << (8u * bb));
             TA[j] = wa; TB[j] = wb;
         }
     }
@@ -570,8 +570,8 @@ dpf2_gotoh_kernel(const Gotoh2Params q)
             const uint32_t c = block + j;
             const uint32_t a = (qa[j >> 2] >> (8 * (j & 3))) & 255u, bb = (qb[j >> 2] >> (8 * (j & 3))) & 255u;
             uint32_t wa = 0u, wb = 0u;
-            if (live && c < MA) { dirtyA |= a > 3u; wa = base ^ (delta << (8u * (a & 3u))); }
-            if (live && c < MB) { dirtyB |= bb > 3u; wb = base ^ (delta << (8u * (bb & 3u))); }
+            if (live && c < MA) wa = a > 3u ? base : base ^ (delta << (8u * a));                 // a pattern N matches no text symbol 0..3: mismatch in every row
+            if (live && c < MB) wb = bb > 3u ? base : base ^ (delta << (8u * bb));
             TA[j] = wa; TB[j] = wb;
             OH[j] = (capture && (uint32_t)j == ((MA - 1u) & 15u)) ? 1u : 0u;
         }
@@ -959,8 +959,8 @@ dpf2_sw_tb_forward_kernel(const Full2TbParams q)
             const uint32_t c = block + j;
             const uint32_t a = (qa[j >> 2] >> (8 * (j & 3))) & 255u, b = (qb[j >> 2] >> (8 * (j & 3))) & 255u;
             uint32_t wa = 0u, wb = 0u;
-            if (live && c < MA) { dirtyA |= a > 3u; wa = base ^ (delta << (8u * (a & 3u))); }
-            if (live && c < MB) { dirtyB |= b > 3u; wb = base ^ (delta << (8u * (b & 3u))); }
+            if (live && c < MA) wa = a > 3u ? base : base ^ (delta << (8u * a));                 // a pattern N matches no text symbol 0..3: mismatch in every row
+            if (live && c < MB) wb = b > 3u ? base : base ^ (delta << (8u * b));
             TA[j] = wa; TB[j] = wb; H[j] = 0u;
         }
     }
@@ -1182,8 +1182,8 @@ dpf2_gotoh_tb_forward_kernel(const Gotoh2TbParams gq)
             const uint32_t c = block + j;
             const uint32_t a = (qa[j >> 2] >> (8 * (j & 3))) & 255u, bb = (qb[j >> 2] >> (8 * (j & 3))) & 255u;
             uint32_t wa = 0x01010101u, wb = 0x01010101u;                    // past the pattern: S'' = 0, still the diagonal's tag
-            if (live && c < MA) { dirtyA |= a > 3u; wa = base ^ (delta << (8u * (a & 3u))); }
-            if (live && c < MB) { dirtyB |= bb > 3u; wb = base ^ (delta << (8u * (bb & 3u))); }
+            if (live && c < MA) wa = a > 3u ? base : base ^ (delta << (8u * a));                 // a pattern N matches no text symbol 0..3: mismatch in every row
+            if (live && c < MB) wb = bb > 3u ? base : base ^ (delta << (8u * bb));
             TA[j] = wa; TB[j] = wb;
             OH[j] = (capture && (uint32_t)j == ((MA - 1u) & 15u)) ? 1u : 0u;
         }
@@ -1406,8 +1406,8 @@ dpf2_sw_local_tb_forward_kernel(const Local2TbParams lq)
             const uint32_t c = block + j;
             const uint32_t a = (qa[j >> 2] >> (8 * (j & 3))) & 255u, bb = (qb[j >> 2] >> (8 * (j & 3))) & 255u;
             uint32_t wa = 0x80808080u, wb = 0x80808080u;       // columns past the pattern: -128
-            if (live && c < MA) { dirtyA |= a > 3u; wa = base ^ (delta << (8u * (a & 3u))); }
-            if (live && c < MB) { dirtyB |= bb > 3u; wb = base ^ (delta << (8u * (bb & 3u))); }
+            if (live && c < MA) wa = a > 3u ? base : base ^ (delta << (8u * a));                 // a pattern N matches no text symbol 0..3: mismatch in every row
+            if (live && c < MB) wb = bb > 3u ? base : base ^ (delta << (8u * bb));
             TA[j] = wa; TB[j] = wb; H[j] = lq.FL[j] - 0x00030003u;
         }
     }
@@ -1583,8 +1583,8 @@ dpf2_gotoh_local_tb_forward_kernel(const GotohLocal2TbParams lq)
             const uint32_t c = block + j;
             const uint32_t a = (qa[j >> 2] >> (8 * (j & 3))) & 255u, bb = (qb[j >> 2] >> (8 * (j & 3))) & 255u;
             uint32_t wa = 0x80808080u, wb = 0x80808080u;
-            if (live && c < MA) { dirtyA |= a > 3u; wa = base ^ (delta << (8u * (a & 3u))); }
-            if (live && c < MB) { dirtyB |= bb > 3u; wb = base ^ (delta << (8u * (bb & 3u))); }
+            if (live && c < MA) wa = a > 3u ? base : base ^ (delta << (8u * a));                 // a pattern N matches no text symbol 0..3: mismatch in every row
+            if (live && c < MB) wb = bb > 3u ? base : base ^ (delta << (8u * bb));
             TA[j] = wa; TB[j] = wb;
         }
     }

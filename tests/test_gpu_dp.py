@@ -324,3 +324,29 @@ def test_full_traceback_packed(oracle, kind, scheme, ty):
         small = torch.empty(int(nvb.lib().nvb_temp_bytes(2, a.c(), 0, 64, ps.max_len, ts.max_len, 128)), dtype=torch.uint8, device=gu.dev())
         got = gu.tb_np(nvb.batch_alignment_traceback(a, 64, ps, ts, temp=small, ops_stride=ps.max_len + ts.max_len + 3, ctx=c))
         assert gu.tb_equal(got, want), (alpha, "small scratch")
+
+
+@pytest.mark.parametrize("kind,scheme,ty", [(po.SW, (2, -1, -1, -1), 1), (po.SW, (2, -1, -1, -1), 2), (po.ED, (0, -1, -1, -1), 0),
+                                            (po.GOTOH, (2, -2, -5, -3), 2), (po.GOTOH, (2, -2, -5, -3), 1), (po.GOTOH, (0, -5, -8, -3), 0)])
+def test_pattern_n_on_the_packed_kernels(oracle, kind, scheme, ty):
+    """an N (code > 3) in the PATTERN only is a column that mismatches every text symbol: the packed full-matrix kernels keep such
+    pairs (reads with an N against clean genome windows); a pair whose text holds a code > 3 as well still goes to the int32
+    kernel, where equal codes match (every 16th pair here)"""
+    c = nvb.Context.default(0)
+    c.force_generic(0)
+    rng = np.random.default_rng(hash((kind, scheme, ty, 23)) & 0xFFFF)
+    a, oa = gu.aligner(kind, ty, scheme), po.aligner(kind, ty, scheme)
+    n, M, N = 320, 150, 400
+    P, Po, T, To = util.rand_pairs(rng, n, (M, M + 1), lambda m: N, 4)
+    P = P.copy(); T = T.copy()
+    for i in range(n):
+        pos = rng.integers(0, M, 3)
+        P[Po[i] + pos] = rng.integers(4, 6, 3)
+        if i % 16 == 0:
+            T[To[i] + rng.integers(0, N, 6)] = rng.integers(4, 6, 6)
+    ps, ts = gu.sset(P, Po), gu.sset(T, To)
+    got = gu.sinks_np(nvb.batch_alignment_score(a, ps, ts, ctx=c))
+    want = oracle.score(oa, P, Po, T, To)
+    assert (got == want).all(), np.nonzero(got != want)[0][:5]
+    got = gu.tb_np(nvb.batch_alignment_traceback(a, 64, ps, ts, ctx=c))
+    assert gu.tb_equal(got, oracle.traceback(oa, 64, P, Po, T, To))
