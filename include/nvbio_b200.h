@@ -310,7 +310,10 @@ int nvb_batch_banded_myers_score(nvb_ctx* ctx, int32_t type, uint32_t alphabet, 
 /* BatchedAlignmentTraceback<CHECKPOINTS,...>::enact (nvbio/alignment/batched.h:335-380,
  * batched_inl.h:599-680,760-830; per pair aln::alignment_traceback, alignment_inl.h:355-455).
  * ops: ops_stride bytes per pair, n_ops[i] of them valid (if n_ops[i] > ops_stride the list was
- * truncated); checkpoints must be a positive multiple of 16 (64 in nvBowtie, defs.h:96). */
+ * truncated); checkpoints must be a positive multiple of 16 (64 in nvBowtie, defs.h:96). The result does not depend on
+ * it: pairs of 2-bit symbols whose scores fit 15 bits are traced by one packed forward pass that keeps the direction of
+ * every cell plus a walk, everything else by the reference's checkpointed scheme. ops rows that are 16-byte aligned
+ * (ops and ops_stride multiples of 16) are written 16 ops at a time. */
 int nvb_batch_traceback(nvb_ctx* ctx, nvb_aligner aligner, uint32_t checkpoints,
                         nvb_string_set patterns, nvb_string_set texts, nvb_alignment* out,
                         uint8_t* ops, uint32_t ops_stride, uint32_t* n_ops,
