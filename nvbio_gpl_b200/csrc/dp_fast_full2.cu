@@ -964,7 +964,9 @@ dpf2_sw_tb_forward_kernel(const Full2TbParams q)
             TA[j] = wa; TB[j] = wb; H[j] = 0u;
         }
     }
-    uint32_t r_one; asm volatile("mov.u32 %0, %1;" : "=r"(r_one) : "r"(p.one));
+    uint32_t r_one, r_m1;
+    asm volatile("mov.u32 %0, %1;" : "=r"(r_one) : "r"(p.one));
+    asm volatile("mov.u32 %0, %1;" : "=r"(r_m1) : "r"(0u - p.one));
     const uint32_t g2 = f2_pack2(-4 * p.ga);                               // -4 G in both halves
     const uint32_t minus1 = 0u - 0x00010001u;                              // takes the `left` tag off both halves (each half >= 1)
     const uint32_t cin_mul = k == 0 ? 0u : r_one, col_mul = (k == 0 && p.semi) ? g2 : 0u;
@@ -1005,8 +1007,8 @@ dpf2_sw_tb_forward_kernel(const Full2TbParams q)
             const uint32_t hn = __vimax3_s16x2(d[j], H[j], left);
             left = (hn & 0xFFFCFFFCu) | 0x00010001u;
             H[j] = f2_imad(r_one, minus1, left);
-            const uint32_t tag = hn & 0x00030003u;
-            if (j < 8) acc0 = f2_imad(acc0, 4u, tag); else acc1 = f2_imad(acc1, 4u, tag);
+            // acc * 4 + tag with tag = hn - H[j] (each half of hn is >= that of H[j]): two IMADs, nothing on the ALU pipe
+            if (j < 8) acc0 = f2_imad(H[j], r_m1, f2_imad(acc0, 4u, hn)); else acc1 = f2_imad(H[j], r_m1, f2_imad(acc1, 4u, hn));
         }
         send = left;
         if (last_lane) cand_at[t] = send;
