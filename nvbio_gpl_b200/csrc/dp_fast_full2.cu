@@ -882,7 +882,7 @@ int dpf2_full_score(nvb_ctx* ctx, const nvb_aligner& a, StrSet P, StrSet T, nvb_
 // The direction comes out of the maximum itself (the trick of dp_band2_tb.cu): every value is kept times four and each candidate
 // carries its move in the two low bits -- diagonal 2, left (insertion) 1, top (deletion) 0 -- so VIMNMX3 picks, among equal scores,
 // exactly what sw_inl.h:488-490 picks: the diagonal unless a gap is strictly better, the insertion unless the deletion is strictly
-// better. A cell costs PRMT + VIMNMX3 + LOP3 (re-tag as `left`) + LOP3 (its tag) on the ALU pipe and three IMADs on the FMA pipe.
+// better. A cell costs PRMT + VIMNMX3 + LOP3 (re-tag as `left`) on the ALU pipe and four IMADs on the FMA pipe (the tag is h - clean).
 // Flow: 2 bits per cell and pair, one 64-bit word per stripe and row (columns 0..7 of both pairs in .x, 8..15 in .y, column j at
 // bits 2 (7 - j mod 8), pair B 16 bits up); for the layout see f2_flow_base.
 // ---------------------------------------------------------------------------------------------------------------
